@@ -1,0 +1,442 @@
+"""gpupathtracer_b200 -- Python host mirror of the C ABI in include/firefly.h (libfirefly_b200.so).
+
+The product is the shared library; this module is a thin ctypes binding whose names follow the reference's host
+surface (LoadMesh -> load_obj, Geometry ctor -> Scene.add_obj/add_triangles/add_plane, Camera, render).
+There is no CPU fallback: importing works without a GPU (so the symbol table can be checked), but creating a
+Context raises FireflyError when no CUDA device is present, and a missing library raises ImportError loudly.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libfirefly_b200.so")
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError("%s is missing: run `python gpupathtracer_b200/build.py` (or __graft_entry__.build()); "
+                      "there is no fallback implementation" % LIB_PATH)
+lib = C.CDLL(LIB_PATH)
+
+INTEGRATOR_WAVEFRONT, INTEGRATOR_MEGAKERNEL, INTEGRATOR_AS_CODED = 0, 1, 2
+BUILDER_LBVH, BUILDER_SAH = 0, 1
+TRACE_BVH8, TRACE_BRUTE, TRACE_BVH2 = 0, 1, 2
+TRACE_COUNT = 0x100
+MAT_EMITTER, MAT_DIFFUSE, MAT_MIRROR, MAT_GLASS = 0, 1, 2, 3
+
+
+class FireflyError(RuntimeError):
+    def __init__(self, code, message):
+        super().__init__("firefly error %d: %s" % (code, message))
+        self.code = code
+
+
+class CCamera(C.Structure):
+    _fields_ = [("pos", C.c_float * 3), ("world_up", C.c_float * 3), ("yaw_deg", C.c_float), ("pitch_deg", C.c_float),
+                ("fov_deg", C.c_float), ("width", C.c_int), ("height", C.c_int), ("near_clip", C.c_float),
+                ("far_clip", C.c_float)]
+
+
+class CMaterial(C.Structure):
+    _fields_ = [("type", C.c_int), ("albedo", C.c_float * 3), ("emissive", C.c_float * 3), ("intensity", C.c_float)]
+
+
+class CRenderParams(C.Structure):
+    _fields_ = [("spp", C.c_int), ("max_bounces", C.c_int), ("seed", C.c_uint64), ("integrator", C.c_int), ("nee", C.c_int),
+                ("first_sample", C.c_int), ("aa", C.c_int), ("background", C.c_float * 3), ("ray_eps", C.c_float),
+                ("samples_per_pass", C.c_int), ("total_spp", C.c_int)]
+
+
+class CStats(C.Structure):
+    _fields_ = [("gpu_ms", C.c_double), ("trace_ms", C.c_double), ("h2d_ms", C.c_double), ("d2h_ms", C.c_double),
+                ("rays", C.c_uint64), ("shadow_rays", C.c_uint64), ("paths", C.c_uint64), ("nodes_visited", C.c_uint64),
+                ("tris_tested", C.c_uint64), ("kernel_launches", C.c_uint32), ("reserved", C.c_uint32)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}
+
+
+class CSceneInfo(C.Structure):
+    _fields_ = [("n_triangles", C.c_uint64), ("n_geometries", C.c_uint64), ("n_planes", C.c_uint64), ("n_nodes", C.c_uint64),
+                ("node_bytes", C.c_uint64), ("triangle_bytes", C.c_uint64), ("depth", C.c_uint32), ("builder", C.c_uint32),
+                ("bounds_lo", C.c_float * 3), ("bounds_hi", C.c_float * 3), ("build_ms", C.c_double), ("sah_cost", C.c_double)]
+
+    def as_dict(self):
+        d = {k: getattr(self, k) for k, _ in self._fields_}
+        d["bounds_lo"] = list(self.bounds_lo)
+        d["bounds_hi"] = list(self.bounds_hi)
+        return d
+
+
+lib.ff_last_error.restype = C.c_char_p
+lib.ff_load_obj.restype = C.c_long
+lib.ff_load_obj.argtypes = [C.c_char_p, C.c_void_p, C.c_size_t]
+_vp, _sz = C.c_void_p, C.c_size_t
+lib.ff_context_create.argtypes = [C.POINTER(_vp), C.c_int]
+lib.ff_context_destroy.argtypes = [_vp]
+lib.ff_context_synchronize.argtypes = [_vp]
+lib.ff_scene_create.argtypes = [_vp, C.POINTER(_vp)]
+lib.ff_scene_destroy.argtypes = [_vp]
+lib.ff_scene_add_obj.argtypes = [_vp, C.c_char_p, _vp, _vp, _vp, _vp, C.c_int, C.POINTER(C.c_int)]
+lib.ff_scene_add_triangles.argtypes = [_vp, _vp, _sz, _vp, _vp, _vp, _vp, C.POINTER(C.c_int)]
+lib.ff_scene_add_plane.argtypes = [_vp, _vp, _vp, _vp, _vp, C.POINTER(C.c_int)]
+lib.ff_scene_commit.argtypes = [_vp, C.c_int, C.POINTER(C.c_double)]
+lib.ff_scene_get_info.argtypes = [_vp, C.POINTER(CSceneInfo)]
+lib.ff_scene_get_flat.argtypes = [_vp, _vp, _vp, _vp, _sz]
+lib.ff_scene_get_matrices.argtypes = [_vp, C.c_int, _vp, _vp]
+lib.ff_trace_closest.argtypes = [_vp, _vp, _sz, C.c_int, _vp, _vp, _vp, C.POINTER(CStats)]
+lib.ff_trace_closest_device.argtypes = [_vp, _vp, _sz, C.c_int, _vp, C.POINTER(CStats)]
+lib.ff_trace_any.argtypes = [_vp, _vp, _vp, _sz, C.c_int, _vp, C.POINTER(CStats)]
+lib.ff_hits_unpack.argtypes = [_vp, _vp, _sz, _vp, _vp, _vp]
+lib.ff_camera_rays.argtypes = [_vp, C.POINTER(CCamera), _vp, _vp]
+lib.ff_camera_basis.argtypes = [C.POINTER(CCamera), _vp, _vp, _vp]
+lib.ff_camera_inverse_matrices.argtypes = [C.POINTER(CCamera), _vp, _vp]
+lib.ff_render.argtypes = [_vp, C.POINTER(CCamera), C.POINTER(CRenderParams), _vp, _vp, C.POINTER(CStats)]
+lib.ff_render_u8.argtypes = [_vp, C.POINTER(CCamera), C.POINTER(CRenderParams), _vp, C.c_int, C.POINTER(CStats)]
+lib.ff_render_accumulate.argtypes = [_vp, C.POINTER(CCamera), C.POINTER(CRenderParams), _vp, C.POINTER(CStats)]
+lib.ff_resolve.argtypes = [_vp, _vp, C.c_int, C.c_int, C.c_int, _vp, _vp]
+lib.ff_reduce_resolve_peers.argtypes = [_vp, C.POINTER(_vp), C.c_int, C.c_int, C.c_int, C.c_int, _vp, _vp]
+lib.ff_make_soup.argtypes = [_vp, _sz, C.c_float, _vp]
+lib.ff_make_rays_uniform.argtypes = [_vp, C.c_uint64, _sz, C.c_uint32, _vp, _vp]
+lib.ff_make_rays_bounce.argtypes = [_vp, _vp, _vp, _sz, C.c_uint64, _vp, C.POINTER(_sz)]
+lib.ff_device_malloc.argtypes = [_vp, _sz, C.POINTER(_vp)]
+lib.ff_device_free.argtypes = [_vp, _vp]
+lib.ff_device_memset.argtypes = [_vp, _vp, C.c_int, _sz]
+lib.ff_memcpy_h2d.argtypes = [_vp, _vp, _vp, _sz]
+lib.ff_memcpy_d2h.argtypes = [_vp, _vp, _vp, _sz]
+lib.ff_host_alloc_pinned.argtypes = [_sz, C.POINTER(_vp)]
+lib.ff_host_free_pinned.argtypes = [_vp]
+lib.ff_ipc_get_handle.argtypes = [_vp, _vp, _vp]
+lib.ff_ipc_open_handle.argtypes = [_vp, _vp, C.POINTER(_vp)]
+lib.ff_ipc_close_handle.argtypes = [_vp, _vp]
+lib.ff_flush_l2.argtypes = [_vp]
+lib.ff_write_image.argtypes = [C.c_char_p, _vp, C.c_int, C.c_int]
+lib.ff_write_image_u8.argtypes = [C.c_char_p, _vp, C.c_int, C.c_int]
+lib.ff_philox4x32_10.argtypes = [_vp, _vp, _vp]
+lib.ff_philox4x32_10.restype = None
+lib.ff_context_destroy.restype = None
+lib.ff_scene_destroy.restype = None
+
+
+def _check(rc):
+    if rc != 0:
+        raise FireflyError(rc, lib.ff_last_error().decode(errors="replace"))
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _f3(v):
+    return None if v is None else np.ascontiguousarray(v, np.float32).reshape(3)
+
+
+def device_count():
+    return lib.ff_device_count()
+
+
+def load_obj(path):
+    """OBJ file -> float32 [n, 9] triangle positions (LoadMesh, utilities.h:781-840)."""
+    n = lib.ff_load_obj(os.fsencode(path), None, 0)
+    if n < 0:
+        _check(int(n))
+    out = np.zeros((n, 9), np.float32)
+    if n:
+        lib.ff_load_obj(os.fsencode(path), _p(out), n)
+    return out
+
+
+def philox4x32_10(ctr, key):
+    c = np.array(ctr, np.uint32)
+    k = np.array(key, np.uint32)
+    o = np.zeros(4, np.uint32)
+    lib.ff_philox4x32_10(_p(c), _p(k), _p(o))
+    return o
+
+
+def material(type=MAT_DIFFUSE, albedo=(0.8, 0.8, 0.8), emissive=(0, 0, 0), intensity=0.0):
+    m = CMaterial()
+    m.type = int(type)
+    m.albedo[:] = [float(x) for x in albedo]
+    m.emissive[:] = [float(x) for x in emissive]
+    m.intensity = float(intensity)
+    return m
+
+
+def _material_from(obj):
+    if obj is None or isinstance(obj, CMaterial):
+        return obj
+    return material(obj.get("type", MAT_DIFFUSE), obj.get("albedo", (0.8, 0.8, 0.8)), obj.get("emissive", (0, 0, 0)),
+                    obj.get("intensity", 0.0))
+
+
+class Camera:
+    """Mirrors the Camera fields main() sets (kernel.cu:311-322)."""
+
+    def __init__(self, pos=(0, 0, 15), yaw=-90.0, pitch=0.0, fov=70.0, width=800, height=800, near=0.1, far=1000.0,
+                 world_up=(0, 1, 0)):
+        self.c = CCamera()
+        self.c.pos[:] = [float(x) for x in pos]
+        self.c.world_up[:] = [float(x) for x in world_up]
+        self.c.yaw_deg, self.c.pitch_deg, self.c.fov_deg = float(yaw), float(pitch), float(fov)
+        self.c.width, self.c.height = int(width), int(height)
+        self.c.near_clip, self.c.far_clip = float(near), float(far)
+
+    @classmethod
+    def from_dict(cls, d):
+        return cls(d["pos"], d["yaw"], d["pitch"], d["fov"], d["width"], d["height"], d["near"], d["far"],
+                   d.get("world_up", (0, 1, 0)))
+
+    @property
+    def width(self):
+        return self.c.width
+
+    @property
+    def height(self):
+        return self.c.height
+
+    def basis(self):
+        f, r, u = (np.zeros(3, np.float32) for _ in range(3))
+        _check(lib.ff_camera_basis(C.byref(self.c), _p(f), _p(r), _p(u)))
+        return f, r, u
+
+    def inverse_matrices(self):
+        iv, ip = np.zeros(16, np.float32), np.zeros(16, np.float32)
+        _check(lib.ff_camera_inverse_matrices(C.byref(self.c), _p(iv), _p(ip)))
+        return iv, ip
+
+
+def render_params(spp=1, max_bounces=4, seed=1234, integrator=INTEGRATOR_WAVEFRONT, nee=0, first_sample=0, aa=0,
+                  background=(0, 0, 0), ray_eps=1e-4, samples_per_pass=0, total_spp=0):
+    p = CRenderParams()
+    p.spp, p.max_bounces, p.seed, p.integrator, p.nee = int(spp), int(max_bounces), int(seed), int(integrator), int(nee)
+    p.first_sample, p.aa = int(first_sample), int(aa)
+    p.background[:] = [float(x) for x in background]
+    p.ray_eps = float(ray_eps)
+    p.samples_per_pass, p.total_spp = int(samples_per_pass), int(total_spp)
+    return p
+
+
+class DeviceBuffer:
+    def __init__(self, ctx, nbytes):
+        self.ctx, self.nbytes = ctx, int(nbytes)
+        self.ptr = C.c_void_p()
+        _check(lib.ff_device_malloc(ctx.h, self.nbytes, C.byref(self.ptr)))
+
+    def upload(self, arr):
+        arr = np.ascontiguousarray(arr)
+        assert arr.nbytes <= self.nbytes
+        _check(lib.ff_memcpy_h2d(self.ctx.h, self.ptr, _p(arr), arr.nbytes))
+
+    def download(self, dtype, count):
+        out = np.empty(count, dtype)
+        assert out.nbytes <= self.nbytes
+        _check(lib.ff_memcpy_d2h(self.ctx.h, _p(out), self.ptr, out.nbytes))
+        return out
+
+    def zero(self):
+        _check(lib.ff_device_memset(self.ctx.h, self.ptr, 0, self.nbytes))
+
+    def free(self):
+        if self.ptr:
+            lib.ff_device_free(self.ctx.h, self.ptr)
+            self.ptr = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class Context:
+    def __init__(self, device=0):
+        self.h = C.c_void_p()
+        _check(lib.ff_context_create(C.byref(self.h), int(device)))
+        self.device = int(device)
+
+    def close(self):
+        if self.h:
+            lib.ff_context_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def scene(self):
+        return Scene(self)
+
+    def alloc(self, nbytes):
+        return DeviceBuffer(self, nbytes)
+
+    def synchronize(self):
+        _check(lib.ff_context_synchronize(self.h))
+
+    def flush_l2(self):
+        _check(lib.ff_flush_l2(self.h))
+
+    def make_soup(self, n, s=None):
+        s = float(n) ** (-1.0 / 3.0) if s is None else float(s)
+        out = np.empty((n, 9), np.float32)
+        _check(lib.ff_make_soup(self.h, n, C.c_float(s), _p(out)))
+        return out
+
+    def make_rays_uniform(self, first, n, salt=0, device_buffer=None, host=True):
+        out = np.empty((n, 6), np.float32) if host else None
+        _check(lib.ff_make_rays_uniform(self.h, int(first), int(n), int(salt), _p(out),
+                                        device_buffer.ptr if device_buffer is not None else None))
+        return out
+
+    def camera_rays(self, cam, device_buffer=None, host=True):
+        n = cam.width * cam.height
+        out = np.empty((n, 6), np.float32) if host else None
+        _check(lib.ff_camera_rays(self.h, C.byref(cam.c), _p(out), device_buffer.ptr if device_buffer is not None else None))
+        return out
+
+    def resolve(self, accum, width, height, total_spp):
+        out = np.empty((height, width, 4), np.float32)
+        _check(lib.ff_resolve(self.h, accum.ptr if isinstance(accum, DeviceBuffer) else C.c_void_p(accum), width, height,
+                              int(total_spp), None, _p(out)))
+        return out
+
+    def reduce_resolve_peers(self, ptrs, width, height, total_spp):
+        arr = (C.c_void_p * len(ptrs))(*[C.c_void_p(int(p)) for p in ptrs])
+        out = np.empty((height, width, 4), np.float32)
+        _check(lib.ff_reduce_resolve_peers(self.h, arr, len(ptrs), width, height, int(total_spp), None, _p(out)))
+        return out
+
+
+class Scene:
+    def __init__(self, ctx):
+        self.ctx = ctx
+        self.h = C.c_void_p()
+        _check(lib.ff_scene_create(ctx.h, C.byref(self.h)))
+
+    def close(self):
+        if self.h:
+            lib.ff_scene_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- geometry (Geometry ctor, utilities.h:176-213)
+    def add_obj(self, path, pos=(0, 0, 0), rot=(0, 0, 0), scale=(1, 1, 1), material=None, flip_winding=False):
+        idx = C.c_int(-1)
+        m = _material_from(material)
+        _check(lib.ff_scene_add_obj(self.h, os.fsencode(path), _p(_f3(pos)), _p(_f3(rot)), _p(_f3(scale)),
+                                    C.byref(m) if m is not None else None, int(flip_winding), C.byref(idx)))
+        return idx.value
+
+    def add_triangles(self, xyz9, pos=(0, 0, 0), rot=(0, 0, 0), scale=(1, 1, 1), material=None):
+        xyz9 = np.ascontiguousarray(xyz9, np.float32).reshape(-1, 9)
+        idx = C.c_int(-1)
+        m = _material_from(material)
+        _check(lib.ff_scene_add_triangles(self.h, _p(xyz9), len(xyz9), _p(_f3(pos)), _p(_f3(rot)), _p(_f3(scale)),
+                                          C.byref(m) if m is not None else None, C.byref(idx)))
+        return idx.value
+
+    add_mesh = add_triangles
+
+    def add_plane(self, pos=(0, 0, 0), rot=(0, 0, 0), scale=(1, 1, 1), material=None):
+        idx = C.c_int(-1)
+        m = _material_from(material)
+        _check(lib.ff_scene_add_plane(self.h, _p(_f3(pos)), _p(_f3(rot)), _p(_f3(scale)),
+                                      C.byref(m) if m is not None else None, C.byref(idx)))
+        return idx.value
+
+    def commit(self, builder=BUILDER_LBVH):
+        ms = C.c_double(0)
+        _check(lib.ff_scene_commit(self.h, int(builder), C.byref(ms)))
+        return ms.value
+
+    def info(self):
+        i = CSceneInfo()
+        _check(lib.ff_scene_get_info(self.h, C.byref(i)))
+        return i.as_dict()
+
+    def flat(self):
+        n = self.info()["n_triangles"]
+        xyz9, geom, tri = np.empty((n, 9), np.float32), np.empty(n, np.int32), np.empty(n, np.int32)
+        _check(lib.ff_scene_get_flat(self.h, _p(xyz9), _p(geom), _p(tri), n))
+        return xyz9, geom, tri
+
+    def matrices(self, gi):
+        m, inv = np.empty(16, np.float32), np.empty(16, np.float32)
+        _check(lib.ff_scene_get_matrices(self.h, int(gi), _p(m), _p(inv)))
+        return m, inv
+
+    # ---- closest hit (intersectRays, kernel.cu:127-176)
+    def trace_closest(self, rays, mode=TRACE_BVH8, want_stats=False):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
+        n = len(rays)
+        geom, tri, t = np.empty(n, np.int32), np.empty(n, np.int32), np.empty(n, np.float32)
+        st = CStats()
+        _check(lib.ff_trace_closest(self.h, _p(rays), n, int(mode), _p(geom), _p(tri), _p(t), C.byref(st)))
+        out = dict(hit=(geom >= 0).astype(np.uint8), geom=geom, tri=tri, t=t)
+        return (out, st.as_dict()) if want_stats else out
+
+    def trace_closest_device(self, d_rays, n, d_hits, mode=TRACE_BVH8):
+        st = CStats()
+        _check(lib.ff_trace_closest_device(self.h, d_rays.ptr, int(n), int(mode), d_hits.ptr, C.byref(st)))
+        return st.as_dict()
+
+    def hits_unpack(self, d_hits, n):
+        geom, tri, t = np.empty(n, np.int32), np.empty(n, np.int32), np.empty(n, np.float32)
+        _check(lib.ff_hits_unpack(self.h, d_hits.ptr, int(n), _p(geom), _p(tri), _p(t)))
+        return dict(hit=(geom >= 0).astype(np.uint8), geom=geom, tri=tri, t=t)
+
+    def trace_any(self, rays, tmax=None, mode=TRACE_BVH8):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
+        n = len(rays)
+        tm = None if tmax is None else np.ascontiguousarray(tmax, np.float32)
+        occ = np.empty(n, np.uint8)
+        st = CStats()
+        _check(lib.ff_trace_any(self.h, _p(rays), _p(tm), n, int(mode), _p(occ), C.byref(st)))
+        return occ
+
+    def make_rays_bounce(self, d_rays_in, d_hits_in, n, seed, d_rays_out):
+        out_n = C.c_size_t(0)
+        _check(lib.ff_make_rays_bounce(self.h, d_rays_in.ptr, d_hits_in.ptr, int(n), int(seed), d_rays_out.ptr, C.byref(out_n)))
+        return out_n.value
+
+    # ---- render (launchPathTrace, kernel.cu:218-221,342)
+    def render(self, cam, spp=1, max_bounces=4, want_stats=False, host=True, device_out=None, **kw):
+        p = render_params(spp, max_bounces, **kw)
+        out = np.empty((cam.height, cam.width, 4), np.float32) if host else None
+        st = CStats()
+        _check(lib.ff_render(self.h, C.byref(cam.c), C.byref(p), _p(out), device_out.ptr if device_out is not None else None,
+                             C.byref(st)))
+        return (out, st.as_dict()) if want_stats else out
+
+    def render_u8(self, cam, spp=1, max_bounces=0, integrator=INTEGRATOR_AS_CODED, want_stats=False, **kw):
+        p = render_params(spp, max_bounces, integrator=integrator, **kw)
+        out = np.empty((cam.height, cam.width, 3), np.uint8)
+        st = CStats()
+        _check(lib.ff_render_u8(self.h, C.byref(cam.c), C.byref(p), _p(out), 0, C.byref(st)))
+        return (out, st.as_dict()) if want_stats else out
+
+    def render_accumulate(self, cam, d_accum, spp, max_bounces, **kw):
+        p = render_params(spp, max_bounces, **kw)
+        st = CStats()
+        ptr = d_accum.ptr if isinstance(d_accum, DeviceBuffer) else C.c_void_p(int(d_accum))
+        _check(lib.ff_render_accumulate(self.h, C.byref(cam.c), C.byref(p), ptr, C.byref(st)))
+        return st.as_dict()
+
+
+def write_image(path, rgba):
+    rgba = np.ascontiguousarray(rgba)
+    if rgba.dtype == np.uint8:
+        h, w = rgba.shape[:2]
+        _check(lib.ff_write_image_u8(os.fsencode(path), _p(rgba), w, h))
+    else:
+        rgba = np.ascontiguousarray(rgba, np.float32)
+        h, w = rgba.shape[:2]
+        assert rgba.shape[2] == 4
+        _check(lib.ff_write_image(os.fsencode(path), _p(rgba), w, h))

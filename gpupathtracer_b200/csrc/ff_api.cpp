@@ -1,0 +1,947 @@
+// ff_api.cpp -- the C ABI of include/firefly.h: context, scene building / commit, trace and render entry points.
+// Host counterpart of the reference's main() set-up code (kernel.cu:223-329) and per-frame launch (kernel.cu:331-344).
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <limits>
+#include <string>
+#include <vector>
+
+#include "ff_hostmath.h"
+#include "ff_internal.h"
+
+namespace ff {
+static thread_local std::string g_error;
+void set_error(const std::string& msg) { g_error = msg; }
+bool load_obj_positions(const char* path, std::vector<float>& xyz9);
+int write_image_float(const char* path, const float* rgba, int w, int h);
+int write_image_u8(const char* path, const unsigned char* rgb, int w, int h);
+}  // namespace ff
+
+using namespace ff;
+using ffm::M4;
+using ffm::V3;
+
+#define FF_CUDA(call)                                                                               \
+    do {                                                                                            \
+        cudaError_t e_ = (call);                                                                    \
+        if (e_ != cudaSuccess) {                                                                    \
+            set_error(std::string(#call) + ": " + cudaGetErrorString(e_));                          \
+            return FF_ERR_CUDA;                                                                     \
+        }                                                                                           \
+    } while (0)
+#define FF_REQUIRE(cond, msg)                                                                       \
+    do {                                                                                            \
+        if (!(cond)) { set_error(msg); return FF_ERR_INVALID; }                                     \
+    } while (0)
+
+struct ff_context {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    std::vector<cudaEvent_t> trace_events;
+    float4* flush_buf = nullptr;
+    size_t flush_n = 0;
+};
+
+struct HostGeom {
+    int type;  // 1 plane, 2 triangle mesh (GeometryType, utilities.h:141-146)
+    M4 model, inv;
+    ff_material mat;
+    std::vector<float> xyz9;  // object space
+};
+
+struct ff_scene {
+    ff_context* ctx = nullptr;
+    std::vector<HostGeom> geoms;
+    bool committed = false;
+    // device
+    float4* d_flat = nullptr;  // baked triangles in flat order
+    float4* d_tris = nullptr;  // baked triangles in leaf order
+    float4* d_nodes = nullptr;
+    int* d_ord_geom = nullptr;
+    int* d_ord_tri = nullptr;
+    float4* d_materials = nullptr;
+    DevPlane* d_planes = nullptr;
+    int2* d_bvh2_children = nullptr;
+    float4* d_bvh2_lo = nullptr;
+    float4* d_bvh2_hi = nullptr;
+    uint32_t* d_leaf_slot = nullptr;
+    DevScene dev;
+    ff_scene_info info;
+    // render scratch (grown on demand)
+    WaveBuffers wb;
+    size_t wb_capacity = 0;
+    int wb_counts = 0;
+    float4* d_accum = nullptr;
+    float4* d_out = nullptr;
+    size_t fb_pixels = 0;
+    uint32_t* d_work_counter = nullptr;
+    unsigned long long* d_ray_counter = nullptr;
+    TraceCounters* d_trace_counters = nullptr;
+};
+
+static void free_scene_device(ff_scene* s) {
+    cudaFree(s->d_flat); cudaFree(s->d_tris); cudaFree(s->d_nodes); cudaFree(s->d_ord_geom); cudaFree(s->d_ord_tri);
+    cudaFree(s->d_materials); cudaFree(s->d_planes); cudaFree(s->d_bvh2_children); cudaFree(s->d_bvh2_lo);
+    cudaFree(s->d_bvh2_hi); cudaFree(s->d_leaf_slot);
+    s->d_flat = s->d_tris = s->d_nodes = nullptr; s->d_ord_geom = s->d_ord_tri = nullptr; s->d_materials = nullptr;
+    s->d_planes = nullptr; s->d_bvh2_children = nullptr; s->d_bvh2_lo = s->d_bvh2_hi = nullptr; s->d_leaf_slot = nullptr;
+    s->committed = false;
+}
+static void free_render_scratch(ff_scene* s) {
+    for (int k = 0; k < 2; ++k) { cudaFree(s->wb.ray_o[k]); cudaFree(s->wb.ray_d[k]); cudaFree(s->wb.beta[k]); s->wb.ray_o[k] = s->wb.ray_d[k] = s->wb.beta[k] = nullptr; }
+    cudaFree(s->wb.hits); cudaFree(s->wb.radiance); cudaFree(s->wb.counts);
+    s->wb.hits = nullptr; s->wb.radiance = nullptr; s->wb.counts = nullptr; s->wb_capacity = 0; s->wb_counts = 0;
+    cudaFree(s->d_accum); cudaFree(s->d_out); s->d_accum = s->d_out = nullptr; s->fb_pixels = 0;
+}
+
+template <class T>
+static cudaError_t upload(T** dptr, const std::vector<T>& h, cudaStream_t st) {
+    *dptr = nullptr;
+    if (h.empty()) return cudaSuccess;
+    cudaError_t e = cudaMalloc((void**)dptr, sizeof(T) * h.size());
+    if (e != cudaSuccess) return e;
+    return cudaMemcpyAsync(*dptr, h.data(), sizeof(T) * h.size(), cudaMemcpyHostToDevice, st);
+}
+
+extern "C" {
+
+const char* ff_last_error(void) { return g_error.c_str(); }
+int ff_version(void) { return FF_VERSION; }
+int ff_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int ff_context_create(ff_context** out, int device_id) {
+    FF_REQUIRE(out, "ff_context_create: out is NULL");
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        cudaGetLastError();
+        set_error(std::string("ff_context_create: no CUDA device (") + (e != cudaSuccess ? cudaGetErrorString(e) : "count 0") +
+                  "); this library has no CPU fallback");
+        return FF_ERR_CUDA;
+    }
+    FF_REQUIRE(device_id >= 0 && device_id < n, "ff_context_create: device id out of range");
+    FF_CUDA(cudaSetDevice(device_id));
+    ff_context* c = new ff_context();
+    c->device = device_id;
+    FF_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    for (int k = 0; k < 4; ++k) FF_CUDA(cudaEventCreate(&c->ev[k]));
+    *out = c;
+    return FF_OK;
+}
+void ff_context_destroy(ff_context* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    for (auto e : ctx->trace_events) cudaEventDestroy(e);
+    for (int k = 0; k < 4; ++k) cudaEventDestroy(ctx->ev[k]);
+    cudaFree(ctx->flush_buf);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+int ff_context_device(const ff_context* ctx) { return ctx ? ctx->device : -1; }
+int ff_context_synchronize(ff_context* ctx) {
+    FF_REQUIRE(ctx, "ff_context_synchronize: NULL context");
+    FF_CUDA(cudaStreamSynchronize(ctx->stream));
+    return FF_OK;
+}
+
+// ------------------------------------------------------------------------------------------ scene building
+int ff_scene_create(ff_context* ctx, ff_scene** out) {
+    FF_REQUIRE(ctx && out, "ff_scene_create: NULL argument");
+    ff_scene* s = new ff_scene();
+    s->ctx = ctx;
+    memset(&s->dev, 0, sizeof(s->dev));
+    memset(&s->info, 0, sizeof(s->info));
+    memset(&s->wb, 0, sizeof(s->wb));
+    *out = s;
+    return FF_OK;
+}
+void ff_scene_destroy(ff_scene* scene) {
+    if (!scene) return;
+    cudaSetDevice(scene->ctx->device);
+    cudaStreamSynchronize(scene->ctx->stream);
+    free_scene_device(scene);
+    free_render_scratch(scene);
+    cudaFree(scene->d_work_counter); cudaFree(scene->d_ray_counter); cudaFree(scene->d_trace_counters);
+    delete scene;
+}
+static ff_material default_material() {
+    ff_material m;
+    m.type = FF_MAT_DIFFUSE;
+    m.albedo[0] = m.albedo[1] = m.albedo[2] = 0.8f;
+    m.emissive[0] = m.emissive[1] = m.emissive[2] = 0.f;
+    m.intensity = 0.f;
+    return m;
+}
+static int add_geom(ff_scene* scene, int type, std::vector<float>&& xyz9, const float pos[3], const float rot[3], const float scl[3],
+                    const ff_material* material, int* out_index) {
+    static const float zero[3] = {0, 0, 0}, one[3] = {1, 1, 1};
+    HostGeom g;
+    g.type = type;
+    ffh::model_from_trs(pos ? pos : zero, rot ? rot : zero, scl ? scl : one, g.model, g.inv);
+    g.mat = material ? *material : default_material();
+    g.xyz9 = std::move(xyz9);
+    scene->geoms.push_back(std::move(g));
+    scene->committed = false;
+    if (out_index) *out_index = (int)scene->geoms.size() - 1;
+    return FF_OK;
+}
+long ff_load_obj(const char* obj_path, float* xyz9, size_t capacity_tris) {
+    if (!obj_path) { set_error("ff_load_obj: NULL path"); return FF_ERR_INVALID; }
+    std::vector<float> v;
+    if (!load_obj_positions(obj_path, v)) return FF_ERR_IO;
+    const size_t n = v.size() / 9;
+    if (xyz9) memcpy(xyz9, v.data(), sizeof(float) * 9 * std::min(n, capacity_tris));
+    return (long)n;
+}
+int ff_scene_add_obj(ff_scene* scene, const char* obj_path, const float pos[3], const float rot_deg[3], const float scale[3],
+                     const ff_material* material, int flip_winding, int* out_geometry_index) {
+    FF_REQUIRE(scene && obj_path, "ff_scene_add_obj: NULL argument");
+    std::vector<float> v;
+    if (!load_obj_positions(obj_path, v)) return FF_ERR_IO;
+    if (flip_winding)
+        for (size_t t = 0; t + 8 < v.size(); t += 9)
+            for (int a = 0; a < 3; ++a) std::swap(v[t + 3 + a], v[t + 6 + a]);
+    return add_geom(scene, 2, std::move(v), pos, rot_deg, scale, material, out_geometry_index);
+}
+int ff_scene_add_triangles(ff_scene* scene, const float* xyz9, size_t n_tris, const float pos[3], const float rot_deg[3],
+                           const float scale[3], const ff_material* material, int* out_geometry_index) {
+    FF_REQUIRE(scene && (xyz9 || n_tris == 0), "ff_scene_add_triangles: NULL argument");
+    std::vector<float> v(xyz9, xyz9 + 9 * n_tris);
+    return add_geom(scene, 2, std::move(v), pos, rot_deg, scale, material, out_geometry_index);
+}
+int ff_scene_add_plane(ff_scene* scene, const float pos[3], const float rot_deg[3], const float scale[3], const ff_material* material,
+                       int* out_geometry_index) {
+    FF_REQUIRE(scene, "ff_scene_add_plane: NULL scene");
+    return add_geom(scene, 1, std::vector<float>(), pos, rot_deg, scale, material, out_geometry_index);
+}
+
+int ff_scene_commit(ff_scene* scene, int builder, double* out_build_ms) {
+    FF_REQUIRE(scene, "ff_scene_commit: NULL scene");
+    FF_REQUIRE(builder == FF_BUILDER_LBVH || builder == FF_BUILDER_SAH, "ff_scene_commit: unknown builder");
+    ff_context* ctx = scene->ctx;
+    FF_CUDA(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    FF_CUDA(cudaStreamSynchronize(st));
+    free_scene_device(scene);
+
+    // flat numbering: ord = position in the reference's scan over (geometry, triangle), planes take one slot
+    size_t n_tris = 0, n_planes = 0;
+    for (auto& g : scene->geoms) { if (g.type == 2) n_tris += g.xyz9.size() / 9; else ++n_planes; }
+    FF_REQUIRE(n_tris + n_planes < 0x3fffffffu, "ff_scene_commit: too many primitives");
+    std::vector<int> ord_geom, ord_tri;
+    ord_geom.reserve(n_tris + n_planes); ord_tri.reserve(n_tris + n_planes);
+    std::vector<uint32_t> geom_of(n_tris), ord_of(n_tris);
+    std::vector<M4> models(scene->geoms.size());
+    std::vector<float4> materials(2 * scene->geoms.size());
+    std::vector<DevPlane> planes;
+    float maxabs = 0.f;
+    size_t flat = 0;
+    for (size_t gi = 0; gi < scene->geoms.size(); ++gi) {
+        const HostGeom& g = scene->geoms[gi];
+        models[gi] = g.model;
+        float type_bits; int ty = g.mat.type; memcpy(&type_bits, &ty, 4);
+        materials[2 * gi] = make_float4(type_bits, g.mat.albedo[0], g.mat.albedo[1], g.mat.albedo[2]);
+        materials[2 * gi + 1] = make_float4(g.mat.emissive[0], g.mat.emissive[1], g.mat.emissive[2], g.mat.intensity);
+        if (g.type == 2) {
+            const size_t nt = g.xyz9.size() / 9;
+            for (size_t t = 0; t < nt; ++t, ++flat) {
+                geom_of[flat] = (uint32_t)gi; ord_of[flat] = (uint32_t)ord_geom.size();
+                ord_geom.push_back((int)gi); ord_tri.push_back((int)t);
+            }
+        } else {
+            DevPlane p;
+            p.model = g.model; p.inv = g.inv;
+            const ffm::V4 nw = ffh::matvec(ffh::inverted(ffh::transposed(g.model)), ffh::v4(0, 0, 1, 0));
+            p.normal_world[0] = nw.x; p.normal_world[1] = nw.y; p.normal_world[2] = nw.z; p.normal_world[3] = 0;
+            p.ord = (int)ord_geom.size(); p.geom = (int)gi; p.pad0 = p.pad1 = 0;
+            planes.push_back(p);
+            ord_geom.push_back((int)gi); ord_tri.push_back(-1);
+        }
+    }
+
+    FF_CUDA(upload(&scene->d_ord_geom, ord_geom, st));
+    FF_CUDA(upload(&scene->d_ord_tri, ord_tri, st));
+    FF_CUDA(upload(&scene->d_materials, materials, st));
+    FF_CUDA(upload(&scene->d_planes, planes, st));
+
+    BuildOut bo; bo.n_nodes = 0; bo.depth = 0; bo.sah_cost = 0;
+    float blo[3] = {0, 0, 0}, bhi[3] = {0, 0, 0};
+    double build_ms = 0;
+    uint32_t launches = 0;
+    if (n_tris) {
+        // stage object-space triangles, bake on the device (same single-rounding op order as the reference's M * v)
+        float* d_obj = nullptr; M4* d_models = nullptr; uint32_t *d_geom_of = nullptr, *d_ord_of = nullptr;
+        FF_CUDA(cudaMalloc((void**)&d_obj, sizeof(float) * 9 * n_tris));
+        size_t off = 0;
+        for (auto& g : scene->geoms) {
+            if (g.type != 2 || g.xyz9.empty()) continue;
+            FF_CUDA(cudaMemcpyAsync(d_obj + off, g.xyz9.data(), sizeof(float) * g.xyz9.size(), cudaMemcpyHostToDevice, st));
+            off += g.xyz9.size();
+        }
+        FF_CUDA(upload(&d_models, models, st));
+        FF_CUDA(upload(&d_geom_of, geom_of, st));
+        FF_CUDA(upload(&d_ord_of, ord_of, st));
+        FF_CUDA(cudaMalloc((void**)&scene->d_flat, sizeof(float4) * 3 * n_tris));
+        FF_CUDA(cudaMalloc((void**)&scene->d_tris, sizeof(float4) * 3 * n_tris));
+        const uint32_t node_cap = (uint32_t)(n_tris / 2 + 64);
+        FF_CUDA(cudaMalloc((void**)&scene->d_nodes, sizeof(float4) * 5 * (size_t)node_cap));
+        FF_CUDA(cudaMalloc((void**)&scene->d_bvh2_children, sizeof(int2) * std::max<size_t>(1, n_tris)));
+        FF_CUDA(cudaMalloc((void**)&scene->d_bvh2_lo, sizeof(float4) * 2 * n_tris));
+        FF_CUDA(cudaMalloc((void**)&scene->d_bvh2_hi, sizeof(float4) * 2 * n_tris));
+        FF_CUDA(cudaMalloc((void**)&scene->d_leaf_slot, sizeof(uint32_t) * n_tris));
+        k_bake_triangles(d_obj, d_models, d_geom_of, d_ord_of, (uint32_t)n_tris, scene->d_flat, st);
+        FF_CUDA(cudaStreamSynchronize(st));
+        cudaFree(d_obj); cudaFree(d_models); cudaFree(d_geom_of); cudaFree(d_ord_of);
+        // the conservative pad needs the scene's largest |coordinate|: take it from the host copies' model-space
+        // bounds pushed through |M| (cheap upper bound), refined by the device bounds after the build
+        for (auto& g : scene->geoms) {
+            if (g.type != 2) continue;
+            float lo[3] = {1e30f, 1e30f, 1e30f}, hi[3] = {-1e30f, -1e30f, -1e30f};
+            for (size_t k = 0; k < g.xyz9.size(); ++k) { const int a = (int)(k % 3); lo[a] = std::min(lo[a], g.xyz9[k]); hi[a] = std::max(hi[a], g.xyz9[k]); }
+            for (int r = 0; r < 3; ++r) {
+                float ext = std::fabs(ffh::at(g.model, 3, r));
+                for (int c = 0; c < 3; ++c) ext += std::fabs(ffh::at(g.model, c, r)) * std::max(std::fabs(lo[c]), std::fabs(hi[c]));
+                maxabs = std::max(maxabs, ext);
+            }
+        }
+        const float pad = maxabs * (1.0f / 65536.0f);
+        scene->dev.pad = pad;
+        FF_CUDA(cudaEventRecord(ctx->ev[0], st));
+        cudaError_t be = bvh_build(scene->d_flat, (uint32_t)n_tris, builder, pad, scene->d_tris, scene->d_nodes, node_cap,
+                                   scene->d_bvh2_children, scene->d_bvh2_lo, scene->d_bvh2_hi, scene->d_leaf_slot, blo, bhi, &bo,
+                                   &launches, st);
+        if (be != cudaSuccess) { set_error(std::string("bvh_build: ") + cudaGetErrorString(be)); cudaGetLastError(); return FF_ERR_CUDA; }
+        FF_CUDA(cudaEventRecord(ctx->ev[1], st));
+        FF_CUDA(cudaEventSynchronize(ctx->ev[1]));
+        float ms = 0;
+        FF_CUDA(cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]));
+        build_ms = ms;
+        FF_REQUIRE(bo.depth <= FF_MAX_WIDE_DEPTH, "ff_scene_commit: hierarchy deeper than the traversal stack");
+    }
+    FF_CUDA(cudaStreamSynchronize(st));
+
+    DevScene& d = scene->dev;
+    d.tris = scene->d_tris; d.nodes = scene->d_nodes; d.ord_geom = scene->d_ord_geom; d.ord_tri = scene->d_ord_tri;
+    d.materials = scene->d_materials; d.planes = scene->d_planes; d.bvh2_children = scene->d_bvh2_children;
+    d.bvh2_lo = scene->d_bvh2_lo; d.bvh2_hi = scene->d_bvh2_hi; d.bvh2_leaf_slot = scene->d_leaf_slot;
+    d.n_tris = (uint32_t)n_tris; d.n_nodes = bo.n_nodes; d.n_planes = (uint32_t)n_planes; d.n_geoms = (uint32_t)scene->geoms.size();
+    d.wide_depth = bo.depth;
+    for (int k = 0; k < 3; ++k) { d.bounds_lo[k] = blo[k]; d.bounds_hi[k] = bhi[k]; }
+
+    ff_scene_info& in = scene->info;
+    memset(&in, 0, sizeof(in));
+    in.n_triangles = n_tris; in.n_geometries = scene->geoms.size(); in.n_planes = n_planes; in.n_nodes = bo.n_nodes;
+    in.node_bytes = 80ull * bo.n_nodes; in.triangle_bytes = 48ull * n_tris; in.depth = bo.depth; in.builder = (uint32_t)builder;
+    for (int k = 0; k < 3; ++k) { in.bounds_lo[k] = blo[k]; in.bounds_hi[k] = bhi[k]; }
+    in.build_ms = build_ms; in.sah_cost = bo.sah_cost;
+    scene->committed = true;
+    if (out_build_ms) *out_build_ms = build_ms;
+    return FF_OK;
+}
+int ff_scene_get_info(const ff_scene* scene, ff_scene_info* out) {
+    FF_REQUIRE(scene && out, "ff_scene_get_info: NULL argument");
+    FF_REQUIRE(scene->committed, "ff_scene_get_info: scene not committed");
+    *out = scene->info;
+    return FF_OK;
+}
+int ff_scene_get_flat(const ff_scene* scene, float* xyz9, int* geom, int* tri, size_t capacity_tris) {
+    FF_REQUIRE(scene && scene->committed, "ff_scene_get_flat: scene not committed");
+    const size_t n = std::min<size_t>(scene->dev.n_tris, capacity_tris);
+    if (n == 0) return FF_OK;
+    FF_CUDA(cudaSetDevice(scene->ctx->device));
+    std::vector<float4> h(3 * n);
+    FF_CUDA(cudaMemcpy(h.data(), scene->d_flat, sizeof(float4) * 3 * n, cudaMemcpyDeviceToHost));
+    std::vector<int> og(scene->info.n_triangles + scene->info.n_planes), ot(og.size());
+    FF_CUDA(cudaMemcpy(og.data(), scene->d_ord_geom, sizeof(int) * og.size(), cudaMemcpyDeviceToHost));
+    FF_CUDA(cudaMemcpy(ot.data(), scene->d_ord_tri, sizeof(int) * ot.size(), cudaMemcpyDeviceToHost));
+    for (size_t i = 0; i < n; ++i) {
+        if (xyz9)
+            for (int v = 0; v < 3; ++v) { xyz9[9 * i + 3 * v] = h[3 * i + v].x; xyz9[9 * i + 3 * v + 1] = h[3 * i + v].y; xyz9[9 * i + 3 * v + 2] = h[3 * i + v].z; }
+        int ord; memcpy(&ord, &h[3 * i].w, 4);
+        if (geom) geom[i] = og[ord];
+        if (tri) tri[i] = ot[ord];
+    }
+    return FF_OK;
+}
+int ff_scene_get_matrices(const ff_scene* scene, int gi, float model16[16], float inverse16[16]) {
+    FF_REQUIRE(scene && gi >= 0 && gi < (int)scene->geoms.size(), "ff_scene_get_matrices: bad geometry index");
+    if (model16) memcpy(model16, &scene->geoms[gi].model, 64);
+    if (inverse16) memcpy(inverse16, &scene->geoms[gi].inv, 64);
+    return FF_OK;
+}
+
+}  // extern "C"
+
+// ================================================================================================ trace
+namespace {
+struct ScopedTimer {  // CUDA-event bracket on the context's stream
+    ff_context* c; int a, b;
+    ScopedTimer(ff_context* c_, int a_, int b_) : c(c_), a(a_), b(b_) { cudaEventRecord(c->ev[a], c->stream); }
+    double stop() {
+        cudaEventRecord(c->ev[b], c->stream);
+        cudaEventSynchronize(c->ev[b]);
+        float ms = 0;
+        cudaEventElapsedTime(&ms, c->ev[a], c->ev[b]);
+        return ms;
+    }
+};
+int check_scene(ff_scene* scene, const char* who) {
+    if (!scene) { set_error(std::string(who) + ": NULL scene"); return FF_ERR_INVALID; }
+    if (!scene->committed) { set_error(std::string(who) + ": scene not committed"); return FF_ERR_INVALID; }
+    cudaError_t e = cudaSetDevice(scene->ctx->device);
+    if (e != cudaSuccess) { set_error(cudaGetErrorString(e)); return FF_ERR_CUDA; }
+    return FF_OK;
+}
+int ensure_counters(ff_scene* s) {
+    if (!s->d_trace_counters) {
+        FF_CUDA(cudaMalloc((void**)&s->d_trace_counters, sizeof(TraceCounters)));
+        FF_CUDA(cudaMalloc((void**)&s->d_work_counter, sizeof(uint32_t)));
+        FF_CUDA(cudaMalloc((void**)&s->d_ray_counter, sizeof(unsigned long long)));
+    }
+    return FF_OK;
+}
+bool valid_mode(int mode) { const int m = mode & 0xff; return m == FF_TRACE_BVH8 || m == FF_TRACE_BRUTE || m == FF_TRACE_BVH2; }
+}  // namespace
+
+extern "C" {
+
+int ff_trace_closest_device(ff_scene* scene, const void* d_rays, size_t n, int mode, void* d_hits, ff_stats* stats) {
+    int rc = check_scene(scene, "ff_trace_closest_device");
+    if (rc) return rc;
+    FF_REQUIRE(valid_mode(mode), "ff_trace_closest_device: unknown mode");
+    FF_REQUIRE(n < 0xffffffffull, "ff_trace_closest_device: batch too large");
+    FF_REQUIRE((d_rays && d_hits) || n == 0, "ff_trace_closest_device: NULL buffer");
+    ff_context* c = scene->ctx;
+    rc = ensure_counters(scene);
+    if (rc) return rc;
+    const bool count = (mode & FF_TRACE_COUNT) != 0;
+    if (count) FF_CUDA(cudaMemsetAsync(scene->d_trace_counters, 0, sizeof(TraceCounters), c->stream));
+    const float4* ro = (const float4*)d_rays;
+    ScopedTimer t(c, 0, 1);
+    k_trace_closest(scene->dev, ro, ro + n, nullptr, (uint32_t)n, mode, (HitRec*)d_hits, scene->d_trace_counters, c->stream);
+    const double ms = t.stop();
+    FF_CUDA(cudaGetLastError());
+    if (stats) {
+        memset(stats, 0, sizeof(*stats));
+        stats->gpu_ms = ms; stats->trace_ms = ms; stats->rays = n; stats->kernel_launches = n ? 1 : 0;
+        if (count) {
+            TraceCounters h;
+            FF_CUDA(cudaMemcpy(&h, scene->d_trace_counters, sizeof(h), cudaMemcpyDeviceToHost));
+            stats->nodes_visited = h.nodes; stats->tris_tested = h.tris;
+        }
+    }
+    return FF_OK;
+}
+
+int ff_hits_unpack(ff_scene* scene, const void* d_hits, size_t n, int* out_geom, int* out_tri, float* out_t) {
+    int rc = check_scene(scene, "ff_hits_unpack");
+    if (rc) return rc;
+    if (n == 0) return FF_OK;
+    cudaStream_t st = scene->ctx->stream;
+    int *dg = nullptr, *dt = nullptr; float* dk = nullptr;
+    FF_CUDA(cudaMalloc((void**)&dg, sizeof(int) * n)); FF_CUDA(cudaMalloc((void**)&dt, sizeof(int) * n)); FF_CUDA(cudaMalloc((void**)&dk, sizeof(float) * n));
+    k_unpack_hits(scene->dev, (const HitRec*)d_hits, n, dg, dt, dk, st);
+    if (out_geom) FF_CUDA(cudaMemcpyAsync(out_geom, dg, sizeof(int) * n, cudaMemcpyDeviceToHost, st));
+    if (out_tri) FF_CUDA(cudaMemcpyAsync(out_tri, dt, sizeof(int) * n, cudaMemcpyDeviceToHost, st));
+    if (out_t) FF_CUDA(cudaMemcpyAsync(out_t, dk, sizeof(float) * n, cudaMemcpyDeviceToHost, st));
+    FF_CUDA(cudaStreamSynchronize(st));
+    cudaFree(dg); cudaFree(dt); cudaFree(dk);
+    return FF_OK;
+}
+
+int ff_trace_closest(ff_scene* scene, const float* rays6, size_t n, int mode, int* out_geom, int* out_tri, float* out_t, ff_stats* stats) {
+    int rc = check_scene(scene, "ff_trace_closest");
+    if (rc) return rc;
+    FF_REQUIRE(valid_mode(mode), "ff_trace_closest: unknown mode");
+    FF_REQUIRE(rays6 || n == 0, "ff_trace_closest: NULL rays");
+    if (stats) memset(stats, 0, sizeof(*stats));
+    if (n == 0) return FF_OK;
+    ff_context* c = scene->ctx;
+    cudaStream_t st = c->stream;
+    float* d6 = nullptr; float4* dr = nullptr; HitRec* dh = nullptr;
+    int *dg = nullptr, *dt = nullptr; float* dk = nullptr;
+    FF_CUDA(cudaMalloc((void**)&d6, sizeof(float) * 6 * n));
+    FF_CUDA(cudaMalloc((void**)&dr, sizeof(float4) * 2 * n));
+    FF_CUDA(cudaMalloc((void**)&dh, sizeof(HitRec) * n));
+    FF_CUDA(cudaMalloc((void**)&dg, sizeof(int) * n)); FF_CUDA(cudaMalloc((void**)&dt, sizeof(int) * n)); FF_CUDA(cudaMalloc((void**)&dk, sizeof(float) * n));
+    double h2d, d2h;
+    {
+        ScopedTimer t(c, 2, 3);
+        FF_CUDA(cudaMemcpyAsync(d6, rays6, sizeof(float) * 6 * n, cudaMemcpyHostToDevice, st));
+        k_pack_rays(d6, n, dr, dr + n, st);
+        h2d = t.stop();
+    }
+    ff_stats inner;
+    rc = ff_trace_closest_device(scene, dr, n, mode, dh, &inner);
+    if (rc == FF_OK) {
+        ScopedTimer t(c, 2, 3);
+        k_unpack_hits(scene->dev, dh, n, dg, dt, dk, st);
+        if (out_geom) cudaMemcpyAsync(out_geom, dg, sizeof(int) * n, cudaMemcpyDeviceToHost, st);
+        if (out_tri) cudaMemcpyAsync(out_tri, dt, sizeof(int) * n, cudaMemcpyDeviceToHost, st);
+        if (out_t) cudaMemcpyAsync(out_t, dk, sizeof(float) * n, cudaMemcpyDeviceToHost, st);
+        d2h = t.stop();
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) { set_error(cudaGetErrorString(e)); rc = FF_ERR_CUDA; }
+        if (stats) { *stats = inner; stats->h2d_ms = h2d; stats->d2h_ms = d2h; stats->gpu_ms += h2d + d2h; stats->kernel_launches += 2; }
+    }
+    cudaFree(d6); cudaFree(dr); cudaFree(dh); cudaFree(dg); cudaFree(dt); cudaFree(dk);
+    return rc;
+}
+
+int ff_trace_any(ff_scene* scene, const float* rays6, const float* tmax, size_t n, int mode, unsigned char* out_occluded, ff_stats* stats) {
+    int rc = check_scene(scene, "ff_trace_any");
+    if (rc) return rc;
+    FF_REQUIRE(valid_mode(mode), "ff_trace_any: unknown mode");
+    FF_REQUIRE((rays6 && out_occluded) || n == 0, "ff_trace_any: NULL buffer");
+    if (stats) memset(stats, 0, sizeof(*stats));
+    if (n == 0) return FF_OK;
+    ff_context* c = scene->ctx;
+    cudaStream_t st = c->stream;
+    float* d6 = nullptr; float4* dr = nullptr; float* dtm = nullptr; unsigned char* docc = nullptr;
+    FF_CUDA(cudaMalloc((void**)&d6, sizeof(float) * 6 * n));
+    FF_CUDA(cudaMalloc((void**)&dr, sizeof(float4) * 2 * n));
+    FF_CUDA(cudaMalloc((void**)&docc, n));
+    if (tmax) { FF_CUDA(cudaMalloc((void**)&dtm, sizeof(float) * n)); FF_CUDA(cudaMemcpyAsync(dtm, tmax, sizeof(float) * n, cudaMemcpyHostToDevice, st)); }
+    FF_CUDA(cudaMemcpyAsync(d6, rays6, sizeof(float) * 6 * n, cudaMemcpyHostToDevice, st));
+    k_pack_rays(d6, n, dr, dr + n, st);
+    ScopedTimer t(c, 0, 1);
+    k_trace_any(scene->dev, dr, dr + n, dtm, (uint32_t)n, mode, docc, st);
+    const double ms = t.stop();
+    FF_CUDA(cudaMemcpy(out_occluded, docc, n, cudaMemcpyDeviceToHost));
+    if (stats) { stats->gpu_ms = ms; stats->trace_ms = ms; stats->shadow_rays = n; stats->kernel_launches = 2; }
+    cudaFree(d6); cudaFree(dr); cudaFree(dtm); cudaFree(docc);
+    return FF_OK;
+}
+
+// ================================================================================================ camera
+static CamDev make_cam(const ff_camera* cam) {
+    CamDev d;
+    V3 f, r, u;
+    ffh::camera_basis(cam->world_up, cam->yaw_deg, cam->pitch_deg, f, r, u);
+    const V3 pos = ffm::v3(cam->pos[0], cam->pos[1], cam->pos[2]);
+    const M4 iv = ffh::inverted(ffh::look_at_rh(pos, ffm::add(pos, f), u));
+    const M4 ip = ffh::inverted(ffh::perspective_fov_rh_no(ffh::to_radians(cam->fov_deg), (float)cam->width, (float)cam->height,
+                                                           cam->near_clip, cam->far_clip));
+    d.inv_vp = ffh::matmul(iv, ip);
+    d.pos[0] = cam->pos[0]; d.pos[1] = cam->pos[1]; d.pos[2] = cam->pos[2];
+    d.width = (float)cam->width; d.height = (float)cam->height; d.far_clip = cam->far_clip;
+    d.w = cam->width; d.h = cam->height;
+    return d;
+}
+static int check_cam(const ff_camera* cam, const char* who) {
+    if (!cam) { set_error(std::string(who) + ": NULL camera"); return FF_ERR_INVALID; }
+    if (cam->width <= 0 || cam->height <= 0 || (uint64_t)cam->width * (uint64_t)cam->height > 0x7fffffffull) {
+        set_error(std::string(who) + ": bad image size"); return FF_ERR_INVALID;
+    }
+    return FF_OK;
+}
+int ff_camera_basis(const ff_camera* cam, float forward[3], float right[3], float up[3]) {
+    FF_REQUIRE(cam, "ff_camera_basis: NULL camera");
+    V3 f, r, u;
+    ffh::camera_basis(cam->world_up, cam->yaw_deg, cam->pitch_deg, f, r, u);
+    if (forward) { forward[0] = f.x; forward[1] = f.y; forward[2] = f.z; }
+    if (right) { right[0] = r.x; right[1] = r.y; right[2] = r.z; }
+    if (up) { up[0] = u.x; up[1] = u.y; up[2] = u.z; }
+    return FF_OK;
+}
+int ff_camera_inverse_matrices(const ff_camera* cam, float inv_view16[16], float inv_proj16[16]) {
+    FF_REQUIRE(cam, "ff_camera_inverse_matrices: NULL camera");
+    V3 f, r, u;
+    ffh::camera_basis(cam->world_up, cam->yaw_deg, cam->pitch_deg, f, r, u);
+    const V3 pos = ffm::v3(cam->pos[0], cam->pos[1], cam->pos[2]);
+    const M4 iv = ffh::inverted(ffh::look_at_rh(pos, ffm::add(pos, f), u));
+    const M4 ip = ffh::inverted(ffh::perspective_fov_rh_no(ffh::to_radians(cam->fov_deg), (float)cam->width, (float)cam->height,
+                                                           cam->near_clip, cam->far_clip));
+    if (inv_view16) memcpy(inv_view16, &iv, 64);
+    if (inv_proj16) memcpy(inv_proj16, &ip, 64);
+    return FF_OK;
+}
+int ff_camera_rays(ff_context* ctx, const ff_camera* cam, float* rays6_host, void* d_rays) {
+    FF_REQUIRE(ctx, "ff_camera_rays: NULL context");
+    int rc = check_cam(cam, "ff_camera_rays");
+    if (rc) return rc;
+    FF_CUDA(cudaSetDevice(ctx->device));
+    const size_t n = (size_t)cam->width * cam->height;
+    float4* dr = (float4*)d_rays;
+    if (!dr) FF_CUDA(cudaMalloc((void**)&dr, sizeof(float4) * 2 * n));
+    k_camera_rays(make_cam(cam), dr, dr + n, ctx->stream);
+    if (rays6_host) {
+        float* d6 = nullptr;
+        FF_CUDA(cudaMalloc((void**)&d6, sizeof(float) * 6 * n));
+        k_unpack_rays(dr, dr + n, n, d6, ctx->stream);
+        FF_CUDA(cudaMemcpyAsync(rays6_host, d6, sizeof(float) * 6 * n, cudaMemcpyDeviceToHost, ctx->stream));
+        FF_CUDA(cudaStreamSynchronize(ctx->stream));
+        cudaFree(d6);
+    }
+    FF_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (!d_rays) cudaFree(dr);
+    return FF_OK;
+}
+
+}  // extern "C"
+
+// ================================================================================================ render
+namespace {
+int ensure_wave(ff_scene* s, size_t capacity, int n_counts) {
+    if (s->wb_capacity < capacity) {
+        for (int k = 0; k < 2; ++k) { cudaFree(s->wb.ray_o[k]); cudaFree(s->wb.ray_d[k]); cudaFree(s->wb.beta[k]); s->wb.ray_o[k] = s->wb.ray_d[k] = s->wb.beta[k] = nullptr; }
+        cudaFree(s->wb.hits); cudaFree(s->wb.radiance);
+        s->wb.hits = nullptr; s->wb.radiance = nullptr; s->wb_capacity = 0;
+        for (int k = 0; k < 2; ++k) {
+            FF_CUDA(cudaMalloc((void**)&s->wb.ray_o[k], sizeof(float4) * capacity));
+            FF_CUDA(cudaMalloc((void**)&s->wb.ray_d[k], sizeof(float4) * capacity));
+            FF_CUDA(cudaMalloc((void**)&s->wb.beta[k], sizeof(float4) * capacity));
+        }
+        FF_CUDA(cudaMalloc((void**)&s->wb.hits, sizeof(HitRec) * capacity));
+        FF_CUDA(cudaMalloc((void**)&s->wb.radiance, sizeof(float4) * capacity));
+        s->wb_capacity = capacity;
+        s->wb.capacity = (uint32_t)capacity;
+    }
+    if (s->wb_counts < n_counts) {
+        cudaFree(s->wb.counts); s->wb.counts = nullptr;
+        FF_CUDA(cudaMalloc((void**)&s->wb.counts, sizeof(uint32_t) * n_counts));
+        s->wb_counts = n_counts;
+    }
+    return FF_OK;
+}
+int ensure_fb(ff_scene* s, size_t npix) {
+    if (s->fb_pixels < npix) {
+        cudaFree(s->d_accum); cudaFree(s->d_out); s->d_accum = s->d_out = nullptr; s->fb_pixels = 0;
+        FF_CUDA(cudaMalloc((void**)&s->d_accum, sizeof(float4) * npix));
+        FF_CUDA(cudaMalloc((void**)&s->d_out, sizeof(float4) * npix));
+        s->fb_pixels = npix;
+    }
+    return FF_OK;
+}
+int check_params(const ff_render_params* p, const char* who) {
+    if (!p) { set_error(std::string(who) + ": NULL params"); return FF_ERR_INVALID; }
+    if (p->spp <= 0 || p->max_bounces < 0 || p->max_bounces > 1024 || p->first_sample < 0) {
+        set_error(std::string(who) + ": bad spp / max_bounces / first_sample"); return FF_ERR_INVALID;
+    }
+    if (p->integrator != FF_INTEGRATOR_WAVEFRONT && p->integrator != FF_INTEGRATOR_MEGAKERNEL) {
+        set_error(std::string(who) + ": integrator must be wavefront or megakernel here"); return FF_ERR_INVALID;
+    }
+    if (p->nee) { set_error(std::string(who) + ": next-event estimation is not available in this build"); return FF_ERR_UNSUPPORTED; }
+    return FF_OK;
+}
+// Adds params->spp samples (as sums, in sample-index order) into d_accum.
+int accumulate_samples(ff_scene* scene, const ff_camera* cam, const ff_render_params* p, float4* d_accum, ff_stats* stats) {
+    ff_context* c = scene->ctx;
+    cudaStream_t st = c->stream;
+    const size_t npix = (size_t)cam->width * cam->height;
+    // samples per pass: fill the machine (>= ~2M paths in flight) without exceeding ~16M paths of state
+    size_t spb = p->samples_per_pass > 0 ? (size_t)p->samples_per_pass : std::max<size_t>(1, (4u << 20) / npix);
+    spb = std::min<size_t>(spb, (size_t)p->spp);
+    while (spb > 1 && spb * npix > (32u << 20)) --spb;
+    FF_REQUIRE(spb * npix < 0xffffffffull, "render: too many paths per pass");
+    int rc = ensure_wave(scene, spb * npix, p->max_bounces + 2);
+    if (rc) return rc;
+    rc = ensure_counters(scene);
+    if (rc) return rc;
+    const CamDev cd = make_cam(cam);
+    RenderDev rd;
+    rd.seed_lo = (uint32_t)(p->seed & 0xffffffffull); rd.seed_hi = (uint32_t)(p->seed >> 32);
+    rd.max_bounces = p->max_bounces; rd.aa = p->aa; rd.nee = p->nee; rd.npix = (uint32_t)npix;
+    rd.background[0] = p->background[0]; rd.background[1] = p->background[1]; rd.background[2] = p->background[2];
+    rd.ray_eps = p->ray_eps;
+    const int n_pass = (int)((p->spp + spb - 1) / spb);
+    const bool wave = p->integrator == FF_INTEGRATOR_WAVEFRONT;
+    // one event pair per extend stage, so trace_ms can be reported separately from the bookkeeping
+    const size_t need_events = wave ? (size_t)2 * n_pass * (p->max_bounces + 1) : 0;
+    const bool time_trace = stats && need_events <= 8192;
+    if (time_trace) while (c->trace_events.size() < need_events) { cudaEvent_t e; FF_CUDA(cudaEventCreate(&e)); c->trace_events.push_back(e); }
+    int n_ev = 0;
+    uint32_t launches = 0;
+    uint64_t rays = 0;
+    std::vector<uint32_t> h_counts((size_t)n_pass * (p->max_bounces + 2));
+    FF_CUDA(cudaMemsetAsync(scene->d_ray_counter, 0, sizeof(unsigned long long), st));
+    ScopedTimer t(c, 0, 1);
+    for (int pass = 0; pass < n_pass; ++pass) {
+        const size_t s0 = (size_t)pass * spb;
+        rd.first_sample = (uint32_t)(p->first_sample + s0);
+        rd.samples = (uint32_t)std::min<size_t>(spb, p->spp - s0);
+        if (wave) {
+            k_wavefront_pass(scene->dev, cd, rd, scene->wb, FF_TRACE_BVH8, &launches, time_trace ? c->trace_events.data() : nullptr, &n_ev, st);
+            FF_CUDA(cudaMemcpyAsync(h_counts.data() + (size_t)pass * (p->max_bounces + 2), scene->wb.counts,
+                                    sizeof(uint32_t) * (p->max_bounces + 2), cudaMemcpyDeviceToHost, st));
+        } else {
+            k_megakernel_pass(scene->dev, cd, rd, scene->wb.radiance, scene->d_work_counter, scene->d_ray_counter, &launches, st);
+        }
+        k_accumulate_pass(scene->wb.radiance, (uint32_t)npix, rd.samples, d_accum, st);
+        ++launches;
+    }
+    const double ms = t.stop();
+    FF_CUDA(cudaGetLastError());
+    if (wave) {
+        for (int pass = 0; pass < n_pass; ++pass)
+            for (int b = 0; b <= p->max_bounces; ++b) rays += h_counts[(size_t)pass * (p->max_bounces + 2) + b];
+    } else {
+        unsigned long long r = 0;
+        FF_CUDA(cudaMemcpy(&r, scene->d_ray_counter, sizeof(r), cudaMemcpyDeviceToHost));
+        rays = r;
+    }
+    if (stats) {
+        stats->gpu_ms += ms; stats->rays += rays; stats->paths += (uint64_t)p->spp * npix; stats->kernel_launches += launches;
+        if (time_trace) {
+            double tr = 0;
+            for (int k = 0; k + 1 < n_ev; k += 2) { float m = 0; cudaEventElapsedTime(&m, c->trace_events[k], c->trace_events[k + 1]); tr += m; }
+            stats->trace_ms += tr;
+        }
+    }
+    return FF_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int ff_render_accumulate(ff_scene* scene, const ff_camera* cam, const ff_render_params* params, void* d_accum_rgba, ff_stats* stats) {
+    int rc = check_scene(scene, "ff_render_accumulate");
+    if (rc) return rc;
+    if ((rc = check_cam(cam, "ff_render_accumulate"))) return rc;
+    if ((rc = check_params(params, "ff_render_accumulate"))) return rc;
+    FF_REQUIRE(d_accum_rgba, "ff_render_accumulate: NULL accumulator");
+    if (stats) memset(stats, 0, sizeof(*stats));
+    return accumulate_samples(scene, cam, params, (float4*)d_accum_rgba, stats);
+}
+
+int ff_resolve(ff_context* ctx, const void* d_accum_rgba, int width, int height, int total_spp, void* d_out_rgba, float* out_rgba_host) {
+    const void* one[1] = {d_accum_rgba};
+    return ff_reduce_resolve_peers(ctx, one, 1, width, height, total_spp, d_out_rgba, out_rgba_host);
+}
+int ff_reduce_resolve_peers(ff_context* ctx, const void* const* d_accum_peers, int n_peers, int width, int height, int total_spp,
+                            void* d_out_rgba, float* out_rgba_host) {
+    FF_REQUIRE(ctx && d_accum_peers && n_peers >= 1 && n_peers <= 8, "ff_reduce_resolve_peers: bad argument");
+    FF_REQUIRE(width > 0 && height > 0 && total_spp > 0, "ff_reduce_resolve_peers: bad size");
+    FF_REQUIRE(d_out_rgba || out_rgba_host, "ff_reduce_resolve_peers: no output");
+    FF_CUDA(cudaSetDevice(ctx->device));
+    const size_t npix = (size_t)width * height;
+    float4* d_out = (float4*)d_out_rgba;
+    if (!d_out) FF_CUDA(cudaMalloc((void**)&d_out, sizeof(float4) * npix));
+    const float inv = 1.0f / (float)total_spp;
+    k_resolve((const float4* const*)d_accum_peers, n_peers, (uint32_t)npix, inv, d_out, ctx->stream);
+    if (out_rgba_host) FF_CUDA(cudaMemcpyAsync(out_rgba_host, d_out, sizeof(float4) * npix, cudaMemcpyDeviceToHost, ctx->stream));
+    FF_CUDA(cudaStreamSynchronize(ctx->stream));
+    FF_CUDA(cudaGetLastError());
+    if (!d_out_rgba) cudaFree(d_out);
+    return FF_OK;
+}
+
+int ff_render(ff_scene* scene, const ff_camera* cam, const ff_render_params* params, float* out_rgba_host, void* out_rgba_device,
+              ff_stats* stats) {
+    int rc = check_scene(scene, "ff_render");
+    if (rc) return rc;
+    if ((rc = check_cam(cam, "ff_render"))) return rc;
+    FF_REQUIRE(params, "ff_render: NULL params");
+    if (stats) memset(stats, 0, sizeof(*stats));
+    ff_context* c = scene->ctx;
+    const size_t npix = (size_t)cam->width * cam->height;
+    if ((rc = ensure_fb(scene, npix))) return rc;
+    if (params->integrator == FF_INTEGRATOR_AS_CODED) {
+        // 8-bit as-coded frame widened to float RGBA (value / 255), for callers that want one code path
+        unsigned char* d_rgb = nullptr;
+        FF_CUDA(cudaMalloc((void**)&d_rgb, npix * 3));
+        rc = ff_render_u8(scene, cam, params, d_rgb, 1, stats);
+        std::vector<unsigned char> h(npix * 3);
+        if (rc == FF_OK) FF_CUDA(cudaMemcpy(h.data(), d_rgb, npix * 3, cudaMemcpyDeviceToHost));
+        cudaFree(d_rgb);
+        if (rc) return rc;
+        std::vector<float> f(npix * 4);
+        for (size_t i = 0; i < npix; ++i) { for (int k = 0; k < 3; ++k) f[4 * i + k] = h[3 * i + k] / 255.0f; f[4 * i + 3] = 1.0f; }
+        if (out_rgba_host) memcpy(out_rgba_host, f.data(), sizeof(float) * 4 * npix);
+        if (out_rgba_device) FF_CUDA(cudaMemcpy(out_rgba_device, f.data(), sizeof(float) * 4 * npix, cudaMemcpyHostToDevice));
+        return FF_OK;
+    }
+    if ((rc = check_params(params, "ff_render"))) return rc;
+    FF_CUDA(cudaMemsetAsync(scene->d_accum, 0, sizeof(float4) * npix, c->stream));
+    if ((rc = accumulate_samples(scene, cam, params, scene->d_accum, stats))) return rc;
+    float4* d_out = out_rgba_device ? (float4*)out_rgba_device : scene->d_out;
+    const int total = params->total_spp > 0 ? params->total_spp : params->spp;
+    const float4* one[1] = {scene->d_accum};
+    ScopedTimer t(c, 2, 3);
+    k_resolve(one, 1, (uint32_t)npix, 1.0f / (float)total, d_out, c->stream);
+    if (out_rgba_host) FF_CUDA(cudaMemcpyAsync(out_rgba_host, d_out, sizeof(float4) * npix, cudaMemcpyDeviceToHost, c->stream));
+    const double ms = t.stop();
+    FF_CUDA(cudaGetLastError());
+    if (stats) { stats->gpu_ms += ms; stats->d2h_ms = out_rgba_host ? ms : 0; stats->kernel_launches += 1; }
+    return FF_OK;
+}
+
+int ff_render_u8(ff_scene* scene, const ff_camera* cam, const ff_render_params* params, unsigned char* out_rgb, int out_is_device,
+                 ff_stats* stats) {
+    int rc = check_scene(scene, "ff_render_u8");
+    if (rc) return rc;
+    if ((rc = check_cam(cam, "ff_render_u8"))) return rc;
+    FF_REQUIRE(params && out_rgb, "ff_render_u8: NULL argument");
+    ff_context* c = scene->ctx;
+    const size_t npix = (size_t)cam->width * cam->height;
+    unsigned char* d_rgb = out_is_device ? out_rgb : nullptr;
+    if (!d_rgb) FF_CUDA(cudaMalloc((void**)&d_rgb, npix * 3));
+    if (params->integrator == FF_INTEGRATOR_AS_CODED) {
+        if (stats) memset(stats, 0, sizeof(*stats));
+        ScopedTimer t(c, 0, 1);
+        k_as_coded(scene->dev, make_cam(cam), d_rgb, c->stream);
+        const double ms = t.stop();
+        FF_CUDA(cudaGetLastError());
+        if (stats) { stats->gpu_ms = ms; stats->trace_ms = ms; stats->rays = npix; stats->paths = npix; stats->kernel_launches = 1; }
+    } else {
+        if ((rc = ensure_fb(scene, npix))) return rc;
+        rc = ff_render(scene, cam, params, nullptr, scene->d_out, stats);
+        if (rc) { if (!out_is_device) cudaFree(d_rgb); return rc; }
+        k_rgba_to_u8(scene->d_out, (uint32_t)npix, d_rgb, c->stream);
+        FF_CUDA(cudaStreamSynchronize(c->stream));
+        if (stats) stats->kernel_launches += 1;
+    }
+    if (!out_is_device) {
+        FF_CUDA(cudaMemcpy(out_rgb, d_rgb, npix * 3, cudaMemcpyDeviceToHost));
+        cudaFree(d_rgb);
+    }
+    return FF_OK;
+}
+
+// ================================================================================================ workloads, memory, output
+int ff_make_soup(ff_context* ctx, size_t n_tris, float s, float* xyz9_host) {
+    FF_REQUIRE(ctx && (xyz9_host || n_tris == 0), "ff_make_soup: NULL argument");
+    if (!n_tris) return FF_OK;
+    FF_CUDA(cudaSetDevice(ctx->device));
+    float* d = nullptr;
+    FF_CUDA(cudaMalloc((void**)&d, sizeof(float) * 9 * n_tris));
+    k_make_soup(n_tris, s, d, ctx->stream);
+    FF_CUDA(cudaMemcpyAsync(xyz9_host, d, sizeof(float) * 9 * n_tris, cudaMemcpyDeviceToHost, ctx->stream));
+    FF_CUDA(cudaStreamSynchronize(ctx->stream));
+    cudaFree(d);
+    return FF_OK;
+}
+int ff_make_rays_uniform(ff_context* ctx, uint64_t first, size_t n, uint32_t salt, float* rays6_host, void* d_rays) {
+    FF_REQUIRE(ctx, "ff_make_rays_uniform: NULL context");
+    if (!n) return FF_OK;
+    FF_CUDA(cudaSetDevice(ctx->device));
+    float4* dr = (float4*)d_rays;
+    if (!dr) FF_CUDA(cudaMalloc((void**)&dr, sizeof(float4) * 2 * n));
+    k_make_rays_uniform(first, n, salt, dr, dr + n, ctx->stream);
+    if (rays6_host) {
+        float* d6 = nullptr;
+        FF_CUDA(cudaMalloc((void**)&d6, sizeof(float) * 6 * n));
+        k_unpack_rays(dr, dr + n, n, d6, ctx->stream);
+        FF_CUDA(cudaMemcpyAsync(rays6_host, d6, sizeof(float) * 6 * n, cudaMemcpyDeviceToHost, ctx->stream));
+        FF_CUDA(cudaStreamSynchronize(ctx->stream));
+        cudaFree(d6);
+    }
+    FF_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (!d_rays) cudaFree(dr);
+    return FF_OK;
+}
+int ff_make_rays_bounce(ff_scene* scene, const void* d_rays_in, const void* d_hits_in, size_t n, uint64_t seed, void* d_rays_out, size_t* out_n) {
+    int rc = check_scene(scene, "ff_make_rays_bounce");
+    if (rc) return rc;
+    FF_REQUIRE(d_rays_in && d_hits_in && d_rays_out && out_n && n < 0xffffffffull, "ff_make_rays_bounce: bad argument");
+    if ((rc = ensure_counters(scene))) return rc;
+    cudaStream_t st = scene->ctx->stream;
+    FF_CUDA(cudaMemsetAsync(scene->d_work_counter, 0, sizeof(uint32_t), st));
+    const float4* ri = (const float4*)d_rays_in;
+    // survivors are written compacted: n_out origins at [0, n_out), directions start at offset n (the input count)
+    float4* ro = (float4*)d_rays_out;
+    k_make_rays_bounce(scene->dev, ri, ri + n, (const HitRec*)d_hits_in, (uint32_t)n, (uint32_t)seed, (uint32_t)(seed >> 32), ro, ro + n,
+                       scene->d_work_counter, st);
+    uint32_t cnt = 0;
+    FF_CUDA(cudaMemcpyAsync(&cnt, scene->d_work_counter, sizeof(cnt), cudaMemcpyDeviceToHost, st));
+    FF_CUDA(cudaStreamSynchronize(st));
+    // make the output a dense [cnt origins][cnt directions] batch
+    if (cnt && cnt != n) FF_CUDA(cudaMemcpy(ro + cnt, ro + n, sizeof(float4) * cnt, cudaMemcpyDeviceToDevice));
+    *out_n = cnt;
+    return FF_OK;
+}
+
+int ff_device_malloc(ff_context* ctx, size_t bytes, void** out) {
+    FF_REQUIRE(ctx && out, "ff_device_malloc: NULL argument");
+    FF_CUDA(cudaSetDevice(ctx->device));
+    FF_CUDA(cudaMalloc(out, bytes ? bytes : 16));
+    return FF_OK;
+}
+int ff_device_free(ff_context* ctx, void* p) {
+    FF_REQUIRE(ctx, "ff_device_free: NULL context");
+    FF_CUDA(cudaSetDevice(ctx->device));
+    FF_CUDA(cudaFree(p));
+    return FF_OK;
+}
+int ff_device_memset(ff_context* ctx, void* p, int value, size_t bytes) {
+    FF_REQUIRE(ctx && p, "ff_device_memset: NULL argument");
+    FF_CUDA(cudaSetDevice(ctx->device));
+    FF_CUDA(cudaMemsetAsync(p, value, bytes, ctx->stream));
+    FF_CUDA(cudaStreamSynchronize(ctx->stream));
+    return FF_OK;
+}
+int ff_memcpy_h2d(ff_context* ctx, void* dst, const void* src, size_t bytes) {
+    FF_REQUIRE(ctx && dst && src, "ff_memcpy_h2d: NULL argument");
+    FF_CUDA(cudaSetDevice(ctx->device));
+    FF_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    FF_CUDA(cudaStreamSynchronize(ctx->stream));
+    return FF_OK;
+}
+int ff_memcpy_d2h(ff_context* ctx, void* dst, const void* src, size_t bytes) {
+    FF_REQUIRE(ctx && dst && src, "ff_memcpy_d2h: NULL argument");
+    FF_CUDA(cudaSetDevice(ctx->device));
+    FF_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    FF_CUDA(cudaStreamSynchronize(ctx->stream));
+    return FF_OK;
+}
+int ff_host_alloc_pinned(size_t bytes, void** out) {
+    FF_REQUIRE(out, "ff_host_alloc_pinned: NULL argument");
+    FF_CUDA(cudaMallocHost(out, bytes ? bytes : 16));
+    return FF_OK;
+}
+int ff_host_free_pinned(void* p) {
+    FF_CUDA(cudaFreeHost(p));
+    return FF_OK;
+}
+int ff_ipc_get_handle(ff_context* ctx, void* d_ptr, unsigned char handle64[64]) {
+    FF_REQUIRE(ctx && d_ptr && handle64, "ff_ipc_get_handle: NULL argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    FF_CUDA(cudaSetDevice(ctx->device));
+    cudaIpcMemHandle_t h;
+    FF_CUDA(cudaIpcGetMemHandle(&h, d_ptr));
+    memcpy(handle64, &h, 64);
+    return FF_OK;
+}
+int ff_ipc_open_handle(ff_context* ctx, const unsigned char handle64[64], void** out_d_ptr) {
+    FF_REQUIRE(ctx && handle64 && out_d_ptr, "ff_ipc_open_handle: NULL argument");
+    FF_CUDA(cudaSetDevice(ctx->device));
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, 64);
+    FF_CUDA(cudaIpcOpenMemHandle(out_d_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return FF_OK;
+}
+int ff_ipc_close_handle(ff_context* ctx, void* d_ptr) {
+    FF_REQUIRE(ctx && d_ptr, "ff_ipc_close_handle: NULL argument");
+    FF_CUDA(cudaSetDevice(ctx->device));
+    FF_CUDA(cudaIpcCloseMemHandle(d_ptr));
+    return FF_OK;
+}
+int ff_flush_l2(ff_context* ctx) {
+    FF_REQUIRE(ctx, "ff_flush_l2: NULL context");
+    FF_CUDA(cudaSetDevice(ctx->device));
+    if (!ctx->flush_buf) {
+        ctx->flush_n = (256u << 20) / sizeof(float4);  // 256 MiB > 126 MB L2
+        FF_CUDA(cudaMalloc((void**)&ctx->flush_buf, ctx->flush_n * sizeof(float4)));
+    }
+    k_flush(ctx->flush_buf, ctx->flush_n, ctx->stream);
+    FF_CUDA(cudaStreamSynchronize(ctx->stream));
+    return FF_OK;
+}
+
+int ff_write_image(const char* path, const float* rgba, int width, int height) { return write_image_float(path, rgba, width, height); }
+int ff_write_image_u8(const char* path, const unsigned char* rgb, int width, int height) { return write_image_u8(path, rgb, width, height); }
+void ff_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) {
+    const ffm::U4 r = ffm::philox4x32_10(ffm::U4{ctr[0], ctr[1], ctr[2], ctr[3]}, key[0], key[1]);
+    out[0] = r.x; out[1] = r.y; out[2] = r.z; out[3] = r.w;
+}
+
+}  // extern "C"

@@ -1,0 +1,128 @@
+// ff_internal.h -- structures shared by the host layer (ff_host.cpp) and the CUDA translation units.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include <string>
+#include <vector>
+
+#include "../../include/firefly.h"
+#include "ff_math.h"
+
+#define FF_SM_STACK 8      // traversal stack entries kept in shared memory per thread
+#define FF_LOCAL_STACK 56  // spill entries in local memory
+#define FF_MAX_WIDE_DEPTH (FF_SM_STACK + FF_LOCAL_STACK)
+#define FF_TRACE_BLOCK 128
+
+namespace ff {
+
+// ---------------------------------------------------------------- device-side scene (HBM layout)
+// All arrays are 16-byte aligned SoA / packed float4; see DESIGN.md section 3.
+//   tris      3 float4 per triangle in BVH-leaf order ("slot" order):
+//             {v0.xyz, ord}, {v1.xyz, geometry index}, {v2.xyz, flat index}   (integers as raw bits)
+//             ord = position in the reference's (geometry, triangle) scan, planes included, i.e. the
+//             tie-break order of intersectRays (kernel.cu:133,145).
+//   nodes     5 float4 (80 B) per 8-wide compressed node, see ff_bvh.cu for the field layout.
+//   ord_geom / ord_tri   ord -> (geometryIndex, triangleIndex) in the reference's numbering.
+//   materials 2 float4 per geometry: {type, albedo.rgb}, {emissive.rgb * intensity, intensity}
+struct DevPlane {
+    ffm::M4 model, inv;   // Geometry::m_modelMatrix / m_invModelMatrix (utilities.h:188-189)
+    float normal_world[4];  // inverse(transpose(model)) * (0,0,1,0), not normalised (kernel.cu:117)
+    int ord, geom, pad0, pad1;
+};
+struct DevScene {
+    const float4* tris;
+    const float4* nodes;
+    const int* ord_geom;
+    const int* ord_tri;
+    const float4* materials;
+    const DevPlane* planes;
+    // binary LBVH kept for the BVH2 comparison kernel
+    const int2* bvh2_children;   // internal node i: {left, right}; id >= n_internal is leaf (id - n_internal = slot2)
+    const float4* bvh2_lo;       // per node id (internal then leaves): box min, w unused
+    const float4* bvh2_hi;
+    const uint32_t* bvh2_leaf_slot;  // sorted position -> slot in tris
+    uint32_t n_tris, n_nodes, n_planes, n_geoms;
+    uint32_t wide_depth;
+    float pad;                   // absolute inflation applied to every leaf box (conservative culling)
+    float bounds_lo[3], bounds_hi[3];
+};
+
+struct HitRec {  // 16 B
+    float key;      // reference closest-hit key: world distance (kernel.cu:113-115); +inf on a miss
+    float t;        // t along the normalised direction (object-space t for planes)
+    int slot;       // triangle slot in DevScene::tris; 0x40000000 | plane index for a plane; -1 on a miss
+    int ord;        // tie-break order / index into ord_geom, ord_tri; -1 on a miss
+};
+
+struct CamDev {
+    ffm::M4 inv_vp;      // inverse(view) * inverse(proj)   (kernel.cu:203)
+    float pos[3];
+    float width, height, far_clip;
+    int w, h;
+};
+
+struct RenderDev {
+    uint32_t seed_lo, seed_hi;
+    int max_bounces, aa, nee;
+    uint32_t first_sample;   // global sample index of local sample 0 of this pass
+    uint32_t samples;        // samples in this pass
+    uint32_t npix;
+    float background[3];
+    float ray_eps;
+};
+
+struct TraceCounters { unsigned long long nodes, tris; };
+
+// ---------------------------------------------------------------- kernel launch wrappers
+// (implemented in the .cu files; all asynchronous on `st`)
+void k_bake_triangles(const float* d_xyz9_obj, const ffm::M4* d_model_per_geom, const uint32_t* d_geom_of_flat,
+                      const uint32_t* d_ord_of_flat, uint32_t n, float4* d_flat_tris, cudaStream_t st);
+
+struct BuildOut {
+    uint32_t n_nodes, depth;
+    double sah_cost;
+};
+// Builds into caller-allocated arrays; returns via *out after synchronising `st`.
+cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float pad, float4* d_tris_out,
+                      float4* d_nodes_out, uint32_t node_capacity, int2* d_bvh2_children, float4* d_bvh2_lo,
+                      float4* d_bvh2_hi, uint32_t* d_bvh2_leaf_slot, float bounds_lo[3], float bounds_hi[3],
+                      BuildOut* out, uint32_t* launches, cudaStream_t st);
+
+void k_trace_closest(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const uint32_t* d_count,
+                     uint32_t n_max, int mode, HitRec* d_hits, TraceCounters* d_counters, cudaStream_t st);
+void k_trace_any(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const float* d_tmax, uint32_t n, int mode,
+                 unsigned char* d_occluded, cudaStream_t st);
+
+void k_camera_rays(const CamDev& cam, float4* d_ray_o, float4* d_ray_d, cudaStream_t st);
+void k_pack_rays(const float* d_rays6, size_t n, float4* d_ray_o, float4* d_ray_d, cudaStream_t st);
+void k_unpack_rays(const float4* d_ray_o, const float4* d_ray_d, size_t n, float* d_rays6, cudaStream_t st);
+void k_unpack_hits(const DevScene& sc, const HitRec* d_hits, size_t n, int* d_geom, int* d_tri, float* d_t,
+                   cudaStream_t st);
+void k_make_soup(size_t n, float s, float* d_xyz9, cudaStream_t st);
+void k_make_rays_uniform(uint64_t first, size_t n, uint32_t salt, float4* d_ray_o, float4* d_ray_d, cudaStream_t st);
+void k_make_rays_bounce(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const HitRec* d_hits, uint32_t n,
+                        uint32_t seed_lo, uint32_t seed_hi, float4* d_out_o, float4* d_out_d, uint32_t* d_count, cudaStream_t st);
+
+// wavefront / megakernel integrators.  Path state is SoA, one float4 array per field, double-buffered
+// across bounces (queue compaction writes the survivors densely into the other buffer).
+struct WaveBuffers {
+    float4* ray_o[2];      // {o.xyz, path id}
+    float4* ray_d[2];      // {d.xyz, 0}
+    float4* beta[2];       // {throughput.rgb, 0}
+    HitRec* hits;
+    float4* radiance;      // per path of the pass: L.rgb, indexed by path id = sample_in_pass * npix + pixel
+    uint32_t* counts;      // [max_bounces + 2] active paths entering bounce b
+    uint32_t capacity;     // paths per pass
+};
+void k_wavefront_pass(const DevScene& sc, const CamDev& cam, const RenderDev& rp, const WaveBuffers& wb, int trace_mode,
+                      uint32_t* launches, cudaEvent_t* trace_events, int* n_trace_events, cudaStream_t st);
+void k_megakernel_pass(const DevScene& sc, const CamDev& cam, const RenderDev& rp, float4* d_radiance,
+                       uint32_t* d_work_counter, unsigned long long* d_ray_counter, uint32_t* launches, cudaStream_t st);
+void k_accumulate_pass(const float4* d_radiance, uint32_t npix, uint32_t samples, float4* d_accum, cudaStream_t st);
+void k_resolve(const float4* const* accums, int n_accums, uint32_t npix, float inv_spp, float4* d_out, cudaStream_t st);
+void k_as_coded(const DevScene& sc, const CamDev& cam, unsigned char* d_rgb, cudaStream_t st);
+void k_rgba_to_u8(const float4* d_rgba, uint32_t npix, unsigned char* d_rgb, cudaStream_t st);
+void k_flush(float4* d_buf, size_t n_float4, cudaStream_t st);
+
+}  // namespace ff

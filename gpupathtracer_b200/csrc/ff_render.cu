@@ -1,0 +1,287 @@
+// ff_render.cu -- the two integrators (wavefront stages; persistent megakernel), the as-coded normal shader,
+// sample accumulation and the resolve / peer-reduce kernels.
+//
+// Replaces launchPathTrace / generateRays / shade (reference kernel.cu:178-221) and implements the bounce loop
+// the reference intends but stops short of (readme.md:39-46; BXDF::bsdf utilities.h:90-129), exactly as it is
+// written down in DESIGN.md section 5 and restated on the CPU in oracle/firefly_oracle.cpp (trace_path).
+// Every arithmetic step uses ffm:: single-rounding operations, and samples are summed per pixel in sample-index
+// order, so a single-GPU render is bit-identical to the CPU restatement.
+#include "ff_trace.cuh"
+
+namespace ff {
+
+using namespace ffm;
+
+static inline int grid_for(size_t n, int block, int max_blocks) {
+    size_t g = (n + block - 1) / block;
+    if (g < 1) g = 1;
+    if (g > (size_t)max_blocks) g = max_blocks;
+    return (int)g;
+}
+
+__device__ __forceinline__ void camera_ray_dev(const CamDev& cam, float px, float py, V3& o, V3& d) {
+    o = v3(cam.pos[0], cam.pos[1], cam.pos[2]);
+    const float Px = fsub(fmul(fdiv(px, cam.width), 2.f), 1.f);
+    const float Py = fsub(1.f, fmul(fdiv(py, cam.height), 2.f));
+    const V4 look = mul_mv(cam.inv_vp, fmul(Px, cam.far_clip), fmul(Py, cam.far_clip), fmul(1.f, cam.far_clip),
+                           fmul(1.f, cam.far_clip));
+    d = normalize(sub(v3(look.x, look.y, look.z), o));
+}
+// primary ray of path (pixel, sample): integer pixel corner (kernel.cu:200-201) or Philox-jittered
+__device__ __forceinline__ void primary_ray(const CamDev& cam, const RenderDev& rp, uint32_t pixel, uint32_t sample, V3& o, V3& d) {
+    float px = (float)(pixel % (uint32_t)cam.w), py = (float)(pixel / (uint32_t)cam.w);
+    if (rp.aa) {
+        const U4 j = philox4x32_10(U4{pixel, sample, 0u, 1u}, rp.seed_lo, rp.seed_hi);
+        px = fadd(px, u01(j.z));
+        py = fadd(py, u01(j.w));
+    }
+    camera_ray_dev(cam, px, py, o, d);
+}
+
+// Surface data of a hit: world point, geometric normal as the reference returns it, geometry index.
+__device__ __forceinline__ void hit_surface(const DevScene& sc, const HitRec& h, V3 o, V3 d_raw, V3& point, V3& normal, int& geom) {
+    if (h.slot & 0x40000000) {
+        const DevPlane& pl = sc.planes[h.slot & 0x3fffffff];
+        float key, tl;
+        plane_hit(pl, o, d_raw, key, tl, point);
+        normal = v3(pl.normal_world[0], pl.normal_world[1], pl.normal_world[2]);
+        geom = pl.geom;
+    } else {
+        const float4 a = __ldg(sc.tris + 3 * (size_t)h.slot), b = __ldg(sc.tris + 3 * (size_t)h.slot + 1),
+                     c = __ldg(sc.tris + 3 * (size_t)h.slot + 2);
+        const V3 dn = normalize(d_raw);
+        point = add(o, mul(dn, h.t));                                    // kernel.cu:99
+        normal = normalize(cross(sub(ld3(b), ld3(a)), sub(ld3(c), ld3(a))));  // kernel.cu:101
+        geom = __float_as_int(b.w);
+    }
+}
+
+// One shading event of the written-down algorithm.  Returns true when the path continues (o, d, beta updated);
+// otherwise L has received the path's terminal contribution.
+__device__ __forceinline__ bool shade_event(const DevScene& sc, const RenderDev& rp, const HitRec& h, uint32_t pixel, uint32_t sample,
+                                            int bounce, V3& o, V3& d, V3& beta, V3& L) {
+    if (h.slot < 0) {
+        L = add(L, mul3(beta, v3(rp.background[0], rp.background[1], rp.background[2])));
+        return false;
+    }
+    V3 P, nrm;
+    int geom;
+    hit_surface(sc, h, o, d, P, nrm, geom);
+    const float4 m0 = __ldg(sc.materials + 2 * geom), m1 = __ldg(sc.materials + 2 * geom + 1);
+    if (__float_as_int(m0.x) == FF_MAT_EMITTER) {
+        L = add(L, mul3(beta, mul(v3(m1.x, m1.y, m1.z), m1.w)));
+        return false;
+    }
+    if (bounce == rp.max_bounces) return false;
+    V3 n = normalize(nrm);
+    if (dot(n, d) > 0.0f) n = neg(n);
+    beta = mul3(beta, v3(m0.y, m0.z, m0.w));
+    const U4 r = philox4x32_10(U4{pixel, sample, (uint32_t)bounce, 0u}, rp.seed_lo, rp.seed_hi);
+    const V3 w = cosine_sample_hemisphere(u01(r.x), u01(r.y));
+    V3 t, bt;
+    onb(n, t, bt);
+    d = add(add(mul(t, w.x), mul(bt, w.y)), mul(n, w.z));
+    o = add(P, mul(n, rp.ray_eps));
+    return true;
+}
+
+// ------------------------------------------------------------------ wavefront stages
+__global__ void wf_raygen_kernel(CamDev cam, RenderDev rp, float4* __restrict__ ray_o, float4* __restrict__ ray_d,
+                                 float4* __restrict__ beta, float4* __restrict__ radiance, uint32_t* __restrict__ counts, int n_counts) {
+    const uint32_t n = rp.samples * rp.npix;
+    if (blockIdx.x == 0 && threadIdx.x < n_counts) counts[threadIdx.x] = threadIdx.x == 0 ? n : 0u;
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
+        const uint32_t s = p / rp.npix, pixel = p - s * rp.npix;
+        V3 o, d;
+        primary_ray(cam, rp, pixel, rp.first_sample + s, o, d);
+        ray_o[p] = make_float4(o.x, o.y, o.z, __uint_as_float(p));
+        ray_d[p] = make_float4(d.x, d.y, d.z, 0.f);
+        beta[p] = make_float4(1.f, 1.f, 1.f, 0.f);
+        radiance[p] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+}
+
+// shade + BSDF sampling + warp-aggregated queue compaction: survivors are appended to the next bounce's queue
+// with one atomicAdd per warp (ballot + popc), so the next extend stage reads a dense, coalesced ray array.
+__global__ void __launch_bounds__(256) wf_shade_kernel(DevScene sc, RenderDev rp, int bounce, const uint32_t* __restrict__ count_in,
+                                                        uint32_t cap, const HitRec* __restrict__ hits,
+                                                        const float4* __restrict__ ray_o_in, const float4* __restrict__ ray_d_in,
+                                                        const float4* __restrict__ beta_in, float4* __restrict__ ray_o_out,
+                                                        float4* __restrict__ ray_d_out, float4* __restrict__ beta_out,
+                                                        float4* __restrict__ radiance, uint32_t* __restrict__ count_out) {
+    const uint32_t n = min(*count_in, cap);
+    const uint32_t total = ((n + 31u) / 32u) * 32u;
+    const int lane = threadIdx.x & 31;
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < total; k += gridDim.x * blockDim.x) {
+        bool alive = false;
+        V3 o, d, beta;
+        uint32_t path = 0;
+        if (k < n) {
+            const float4 o4 = ray_o_in[k], d4 = ray_d_in[k], b4 = beta_in[k];
+            const HitRec h = hits[k];
+            path = __float_as_uint(o4.w);
+            const uint32_t s = path / rp.npix, pixel = path - s * rp.npix;
+            o = ld3(o4); d = ld3(d4); beta = ld3(b4);
+            V3 L = v3(0.f, 0.f, 0.f);
+            alive = shade_event(sc, rp, h, pixel, rp.first_sample + s, bounce, o, d, beta, L);
+            if (!alive) radiance[path] = make_float4(L.x, L.y, L.z, 0.f);
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, alive);
+        if (m) {
+            const int leader = __ffs(m) - 1;
+            uint32_t base = 0;
+            if (lane == leader) base = atomicAdd(count_out, (uint32_t)__popc(m));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (alive) {
+                const uint32_t q = base + __popc(m & ((1u << lane) - 1u));
+                ray_o_out[q] = make_float4(o.x, o.y, o.z, __uint_as_float(path));
+                ray_d_out[q] = make_float4(d.x, d.y, d.z, 0.f);
+                beta_out[q] = make_float4(beta.x, beta.y, beta.z, 0.f);
+            }
+        }
+    }
+}
+
+void k_trace_closest(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const uint32_t* d_count,
+                     uint32_t n_max, int mode, HitRec* d_hits, TraceCounters* d_counters, cudaStream_t st);
+
+void k_wavefront_pass(const DevScene& sc, const CamDev& cam, const RenderDev& rp, const WaveBuffers& wb, int trace_mode,
+                      uint32_t* launches, cudaEvent_t* trace_events, int* n_trace_events, cudaStream_t st) {
+    const uint32_t n = rp.samples * rp.npix;
+    const int n_counts = rp.max_bounces + 2;
+    wf_raygen_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(cam, rp, wb.ray_o[0], wb.ray_d[0], wb.beta[0], wb.radiance, wb.counts, n_counts);
+    ++*launches;
+    for (int b = 0; b <= rp.max_bounces; ++b) {
+        const int in = b & 1, out = in ^ 1;
+        if (trace_events) cudaEventRecord(trace_events[(*n_trace_events)++], st);
+        k_trace_closest(sc, wb.ray_o[in], wb.ray_d[in], wb.counts + b, n, trace_mode, wb.hits, nullptr, st);
+        if (trace_events) cudaEventRecord(trace_events[(*n_trace_events)++], st);
+        wf_shade_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(sc, rp, b, wb.counts + b, n, wb.hits, wb.ray_o[in], wb.ray_d[in],
+                                                                   wb.beta[in], wb.ray_o[out], wb.ray_d[out], wb.beta[out],
+                                                                   wb.radiance, wb.counts + b + 1);
+        *launches += 2;
+    }
+}
+
+// ------------------------------------------------------------------ persistent megakernel
+// One thread owns one path from camera to termination; warps pull 32 path ids at a time from a global counter.
+__global__ void __launch_bounds__(FF_TRACE_BLOCK) megakernel(DevScene sc, CamDev cam, RenderDev rp, float4* __restrict__ radiance,
+                                                              uint32_t* work_counter, unsigned long long* ray_counter) {
+    __shared__ uint2 sm_stack[FF_SM_STACK * FF_TRACE_BLOCK];
+    const uint32_t n = rp.samples * rp.npix;
+    const int lane = threadIdx.x & 31;
+    unsigned rays = 0, cn = 0, ct = 0;
+    for (;;) {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(work_counter, 32u);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) break;
+        const uint32_t p = base + lane;
+        if (p < n) {
+            const uint32_t s = p / rp.npix, pixel = p - s * rp.npix, sample = rp.first_sample + s;
+            V3 o, d, beta = v3(1.f, 1.f, 1.f), L = v3(0.f, 0.f, 0.f);
+            primary_ray(cam, rp, pixel, sample, o, d);
+            for (int b = 0; b <= rp.max_bounces; ++b) {
+                const V3 dn = normalize(d);
+                Best best;
+                best_init(best, INFINITY);
+                test_planes<false>(sc, o, d, best);
+                trace_bvh8<false, false>(sc, o, dn, best, sm_stack + threadIdx.x, FF_TRACE_BLOCK, cn, ct);
+                ++rays;
+                HitRec h;
+                h.key = best.key; h.t = best.t; h.slot = best.slot; h.ord = best.slot < 0 ? -1 : best.ord;
+                if (!shade_event(sc, rp, h, pixel, sample, b, o, d, beta, L)) break;
+            }
+            radiance[p] = make_float4(L.x, L.y, L.z, 0.f);
+        }
+    }
+    for (int off = 16; off; off >>= 1) rays += __shfl_xor_sync(0xffffffffu, rays, off);
+    if (lane == 0) atomicAdd(ray_counter, (unsigned long long)rays);
+}
+void k_megakernel_pass(const DevScene& sc, const CamDev& cam, const RenderDev& rp, float4* d_radiance, uint32_t* d_work_counter,
+                       unsigned long long* d_ray_counter, uint32_t* launches, cudaStream_t st) {
+    cudaMemsetAsync(d_work_counter, 0, sizeof(uint32_t), st);
+    const uint32_t n = rp.samples * rp.npix;
+    megakernel<<<grid_for(n, FF_TRACE_BLOCK, 148 * 16), FF_TRACE_BLOCK, 0, st>>>(sc, cam, rp, d_radiance, d_work_counter, d_ray_counter);
+    ++*launches;
+}
+
+// ------------------------------------------------------------------ accumulate / resolve
+// accum[pixel] = (((accum + L[0]) + L[1]) + ...): samples in index order, like the oracle's per-pixel loop.
+__global__ void accumulate_kernel(const float4* __restrict__ radiance, uint32_t npix, uint32_t samples, float4* __restrict__ accum) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += gridDim.x * blockDim.x) {
+        float4 a = accum[i];
+        for (uint32_t s = 0; s < samples; ++s) {
+            const float4 l = radiance[(size_t)s * npix + i];
+            a.x = fadd(a.x, l.x); a.y = fadd(a.y, l.y); a.z = fadd(a.z, l.z);
+        }
+        accum[i] = a;
+    }
+}
+void k_accumulate_pass(const float4* d_radiance, uint32_t npix, uint32_t samples, float4* d_accum, cudaStream_t st) {
+    accumulate_kernel<<<grid_for(npix, 256, 148 * 16), 256, 0, st>>>(d_radiance, npix, samples, d_accum);
+}
+// out = (sum over accumulators in rank order) * (1 / total_spp); alpha = 1.  With n_accums > 1 the pointers may be
+// peer-GPU memory (CUDA IPC over NVLink): the framebuffer reduce and the resolve are one kernel.
+struct PeerPtrs { const float4* p[8]; };
+__global__ void resolve_kernel(PeerPtrs peers, int n_accums, uint32_t npix, float inv_spp, float4* __restrict__ out) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += gridDim.x * blockDim.x) {
+        float4 a = peers.p[0][i];
+        for (int r = 1; r < n_accums; ++r) {
+            const float4 b = peers.p[r][i];
+            a.x = fadd(a.x, b.x); a.y = fadd(a.y, b.y); a.z = fadd(a.z, b.z);
+        }
+        out[i] = make_float4(fmul(a.x, inv_spp), fmul(a.y, inv_spp), fmul(a.z, inv_spp), 1.0f);
+    }
+}
+void k_resolve(const float4* const* accums, int n_accums, uint32_t npix, float inv_spp, float4* d_out, cudaStream_t st) {
+    PeerPtrs pp;
+    for (int i = 0; i < 8; ++i) pp.p[i] = i < n_accums ? accums[i] : nullptr;
+    resolve_kernel<<<grid_for(npix, 256, 148 * 16), 256, 0, st>>>(pp, n_accums, npix, inv_spp, d_out);
+}
+
+// ------------------------------------------------------------------ as-coded frame (kernel.cu:186-216)
+// colour = abs(normal) -> uchar3 (kernel.cu:183,214); misses keep the cleared pixel (kernel.cu:340).
+__global__ void __launch_bounds__(FF_TRACE_BLOCK) as_coded_kernel(DevScene sc, CamDev cam, unsigned char* __restrict__ rgb) {
+    __shared__ uint2 sm_stack[FF_SM_STACK * FF_TRACE_BLOCK];
+    const uint32_t npix = (uint32_t)cam.w * cam.h;
+    unsigned cn = 0, ct = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += gridDim.x * blockDim.x) {
+        V3 o, d;
+        camera_ray_dev(cam, (float)(i % cam.w), (float)(i / cam.w), o, d);
+        const V3 dn = normalize(d);
+        Best best;
+        best_init(best, INFINITY);
+        test_planes<false>(sc, o, d, best);
+        trace_bvh8<false, false>(sc, o, dn, best, sm_stack + threadIdx.x, FF_TRACE_BLOCK, cn, ct);
+        unsigned char px[3] = {0, 0, 0};
+        if (best.slot >= 0) {
+            HitRec h;
+            h.key = best.key; h.t = best.t; h.slot = best.slot; h.ord = best.ord;
+            V3 P, n;
+            int geom;
+            hit_surface(sc, h, o, d, P, n, geom);
+            const float c[3] = {fmul(fabsf(n.x), 255.f), fmul(fabsf(n.y), 255.f), fmul(fabsf(n.z), 255.f)};
+            for (int k = 0; k < 3; ++k) px[k] = (unsigned char)(c[k] > 255.f ? 255.f : c[k]);
+        }
+        rgb[3 * (size_t)i] = px[0]; rgb[3 * (size_t)i + 1] = px[1]; rgb[3 * (size_t)i + 2] = px[2];
+    }
+}
+void k_as_coded(const DevScene& sc, const CamDev& cam, unsigned char* d_rgb, cudaStream_t st) {
+    const size_t n = (size_t)cam.w * cam.h;
+    as_coded_kernel<<<grid_for(n, FF_TRACE_BLOCK, 148 * 16), FF_TRACE_BLOCK, 0, st>>>(sc, cam, d_rgb);
+}
+// linear radiance -> 8-bit: clamp to [0,1], x255, truncate (the kernel.cu:214 conversion)
+__global__ void rgba_to_u8_kernel(const float4* __restrict__ rgba, uint32_t npix, unsigned char* __restrict__ rgb) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += gridDim.x * blockDim.x) {
+        const float4 v = rgba[i];
+        rgb[3 * (size_t)i] = (unsigned char)(fminf(fmaxf(v.x, 0.f), 1.f) * 255.f);
+        rgb[3 * (size_t)i + 1] = (unsigned char)(fminf(fmaxf(v.y, 0.f), 1.f) * 255.f);
+        rgb[3 * (size_t)i + 2] = (unsigned char)(fminf(fmaxf(v.z, 0.f), 1.f) * 255.f);
+    }
+}
+void k_rgba_to_u8(const float4* d_rgba, uint32_t npix, unsigned char* d_rgb, cudaStream_t st) {
+    rgba_to_u8_kernel<<<grid_for(npix, 256, 148 * 16), 256, 0, st>>>(d_rgba, npix, d_rgb);
+}
+
+}  // namespace ff

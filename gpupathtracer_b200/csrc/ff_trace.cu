@@ -1,0 +1,295 @@
+// ff_trace.cu -- ray-batch kernels: closest hit (8-wide BVH, binary BVH, brute force), any hit, camera-ray
+// generation, synthetic workload generators and the pack/unpack helpers of the C ABI.
+// Reference seams: intersectRays kernel.cu:127-176 (trace), generateRays kernel.cu:186-205 (camera rays).
+#include "ff_trace.cuh"
+
+namespace ff {
+
+using namespace ffm;
+
+static inline int grid_for(size_t n, int block, int max_blocks) {
+    size_t g = (n + block - 1) / block;
+    if (g < 1) g = 1;
+    if (g > (size_t)max_blocks) g = max_blocks;
+    return (int)g;
+}
+
+__device__ __forceinline__ void store_hit(HitRec* hits, size_t i, const Best& b) {
+    int4 v;
+    if (b.slot < 0) { v.x = __float_as_int(INFINITY); v.y = 0; v.z = -1; v.w = -1; }
+    else { v.x = __float_as_int(b.key); v.y = __float_as_int(b.t); v.z = b.slot; v.w = b.ord; }
+    reinterpret_cast<int4*>(hits)[i] = v;
+}
+
+// ------------------------------------------------------------------ closest hit, one thread per ray
+template <int MODE, bool COUNT>
+__global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_closest_kernel(DevScene sc, const float4* __restrict__ ray_o,
+                                                                        const float4* __restrict__ ray_d,
+                                                                        const uint32_t* __restrict__ count_ptr, uint32_t n_max,
+                                                                        HitRec* __restrict__ hits, TraceCounters* ctr) {
+    __shared__ uint2 sm_stack[FF_SM_STACK * FF_TRACE_BLOCK];
+    const uint32_t n = count_ptr ? min(*count_ptr, n_max) : n_max;
+    unsigned cn = 0, ct = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float4 o4 = __ldg(ray_o + i), d4 = __ldg(ray_d + i);
+        const V3 o = ld3(o4), draw = ld3(d4);
+        const V3 dn = normalize(draw);  // kernel.cu:138
+        Best best;
+        best_init(best, INFINITY);
+        test_planes<false>(sc, o, draw, best);
+        if (MODE == FF_TRACE_BVH8) trace_bvh8<false, COUNT>(sc, o, dn, best, sm_stack + threadIdx.x, FF_TRACE_BLOCK, cn, ct);
+        else trace_bvh2<false, COUNT>(sc, o, dn, best, cn, ct);
+        store_hit(hits, i, best);
+    }
+    if (COUNT) {
+        atomicAdd(&ctr->nodes, (unsigned long long)cn);
+        atomicAdd(&ctr->tris, (unsigned long long)ct);
+    }
+}
+
+// Brute force: the reference's own algorithm (every ray against every triangle), tiles of triangles staged
+// in shared memory.  Same leaf test and accept rule, so it is order independent.
+#define FF_BRUTE_TILE 256
+template <bool COUNT>
+__global__ void __launch_bounds__(FF_BRUTE_TILE) trace_brute_kernel(DevScene sc, const float4* __restrict__ ray_o,
+                                                                     const float4* __restrict__ ray_d,
+                                                                     const uint32_t* __restrict__ count_ptr, uint32_t n_max,
+                                                                     HitRec* __restrict__ hits, TraceCounters* ctr) {
+    __shared__ float4 sv[3 * FF_BRUTE_TILE];
+    const uint32_t n = count_ptr ? min(*count_ptr, n_max) : n_max;
+    const uint32_t rounds = (n + gridDim.x * blockDim.x - 1) / (gridDim.x * blockDim.x);
+    unsigned long long ct = 0;
+    for (uint32_t r = 0; r < rounds; ++r) {
+        const uint32_t i = (r * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x;
+        const bool live = i < n;
+        V3 o = v3(0, 0, 0), draw = v3(0, 0, 1);
+        if (live) { o = ld3(__ldg(ray_o + i)); draw = ld3(__ldg(ray_d + i)); }
+        const V3 dn = normalize(draw);
+        Best best;
+        best_init(best, INFINITY);
+        if (live) test_planes<false>(sc, o, draw, best);
+        for (uint32_t base = 0; base < sc.n_tris; base += FF_BRUTE_TILE) {
+            const uint32_t m = min((uint32_t)FF_BRUTE_TILE, sc.n_tris - base);
+            __syncthreads();
+            for (uint32_t k = threadIdx.x; k < 3 * m; k += blockDim.x) sv[k] = __ldg(sc.tris + 3 * (size_t)base + k);
+            __syncthreads();
+            if (live) {
+                for (uint32_t k = 0; k < m; ++k) {
+                    float t;
+                    const float4 a = sv[3 * k];
+                    if (intersect_triangle(ld3(a), ld3(sv[3 * k + 1]), ld3(sv[3 * k + 2]), o, dn, t)) {
+                        V3 p;
+                        const float key = hit_key(o, dn, t, p);
+                        const int ord = __float_as_int(a.w);
+                        if (best_accepts(best, key, ord)) { best.key = key; best.t = t; best.slot = (int)(base + k); best.ord = ord; }
+                    }
+                }
+                if (COUNT) ct += m;
+            }
+        }
+        if (live) store_hit(hits, i, best);
+    }
+    if (COUNT) atomicAdd(&ctr->tris, ct);
+}
+
+void k_trace_closest(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const uint32_t* d_count,
+                     uint32_t n_max, int mode, HitRec* d_hits, TraceCounters* d_counters, cudaStream_t st) {
+    if (n_max == 0) return;
+    const bool count = (mode & FF_TRACE_COUNT) != 0;
+    const int m = mode & 0xff;
+    if (m == FF_TRACE_BRUTE) {
+        const int g = grid_for(n_max, FF_BRUTE_TILE, 148 * 8);
+        if (count) trace_brute_kernel<true><<<g, FF_BRUTE_TILE, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);
+        else trace_brute_kernel<false><<<g, FF_BRUTE_TILE, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);
+        return;
+    }
+    const int g = grid_for(n_max, FF_TRACE_BLOCK, 148 * 64);
+    if (m == FF_TRACE_BVH2) {
+        if (count) trace_closest_kernel<FF_TRACE_BVH2, true><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);
+        else trace_closest_kernel<FF_TRACE_BVH2, false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);
+    } else {
+        if (count) trace_closest_kernel<FF_TRACE_BVH8, true><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);
+        else trace_closest_kernel<FF_TRACE_BVH8, false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);
+    }
+}
+
+// ------------------------------------------------------------------ any hit (occlusion)
+template <int MODE>
+__global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_any_kernel(DevScene sc, const float4* __restrict__ ray_o,
+                                                                    const float4* __restrict__ ray_d,
+                                                                    const float* __restrict__ tmax, uint32_t n,
+                                                                    unsigned char* __restrict__ occluded) {
+    __shared__ uint2 sm_stack[FF_SM_STACK * FF_TRACE_BLOCK];
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const V3 o = ld3(__ldg(ray_o + i)), draw = ld3(__ldg(ray_d + i));
+        const V3 dn = normalize(draw);
+        Best best;
+        best_init(best, tmax ? tmax[i] : INFINITY);
+        unsigned cn = 0, ct = 0;
+        test_planes<true>(sc, o, draw, best);
+        if (best.slot < 0) {
+            if (MODE == FF_TRACE_BRUTE) {
+                for (uint32_t k = 0; k < sc.n_tris && best.slot < 0; ++k) test_slot<true>(sc.tris, (int)k, o, dn, best);
+            } else if (MODE == FF_TRACE_BVH2) trace_bvh2<true, false>(sc, o, dn, best, cn, ct);
+            else trace_bvh8<true, false>(sc, o, dn, best, sm_stack + threadIdx.x, FF_TRACE_BLOCK, cn, ct);
+        }
+        occluded[i] = best.slot >= 0 ? 1 : 0;
+    }
+}
+void k_trace_any(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const float* d_tmax, uint32_t n, int mode,
+                 unsigned char* d_occluded, cudaStream_t st) {
+    if (n == 0) return;
+    const int g = grid_for(n, FF_TRACE_BLOCK, 148 * 64);
+    const int m = mode & 0xff;
+    if (m == FF_TRACE_BRUTE) trace_any_kernel<FF_TRACE_BRUTE><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_tmax, n, d_occluded);
+    else if (m == FF_TRACE_BVH2) trace_any_kernel<FF_TRACE_BVH2><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_tmax, n, d_occluded);
+    else trace_any_kernel<FF_TRACE_BVH8><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_tmax, n, d_occluded);
+}
+
+// ------------------------------------------------------------------ camera rays (kernel.cu:198-205)
+__device__ __forceinline__ void camera_ray(const CamDev& cam, float px, float py, V3& o, V3& d) {
+    o = v3(cam.pos[0], cam.pos[1], cam.pos[2]);
+    const float Px = fsub(fmul(fdiv(px, cam.width), 2.f), 1.f);
+    const float Py = fsub(1.f, fmul(fdiv(py, cam.height), 2.f));
+    const V4 look = mul_mv(cam.inv_vp, fmul(Px, cam.far_clip), fmul(Py, cam.far_clip), fmul(1.f, cam.far_clip),
+                           fmul(1.f, cam.far_clip));
+    d = normalize(sub(v3(look.x, look.y, look.z), o));
+}
+__global__ void camera_rays_kernel(CamDev cam, float4* ray_o, float4* ray_d) {
+    const uint32_t npix = (uint32_t)cam.w * cam.h;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += gridDim.x * blockDim.x) {
+        const uint32_t x = i % cam.w, y = i / cam.w;
+        V3 o, d;
+        camera_ray(cam, (float)x, (float)y, o, d);
+        ray_o[i] = make_float4(o.x, o.y, o.z, 0.f);
+        ray_d[i] = make_float4(d.x, d.y, d.z, 0.f);
+    }
+}
+void k_camera_rays(const CamDev& cam, float4* d_ray_o, float4* d_ray_d, cudaStream_t st) {
+    const size_t n = (size_t)cam.w * cam.h;
+    camera_rays_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(cam, d_ray_o, d_ray_d);
+}
+
+// ------------------------------------------------------------------ pack / unpack
+__global__ void pack_rays_kernel(const float* __restrict__ r6, size_t n, float4* ray_o, float4* ray_d) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        ray_o[i] = make_float4(r6[6 * i], r6[6 * i + 1], r6[6 * i + 2], 0.f);
+        ray_d[i] = make_float4(r6[6 * i + 3], r6[6 * i + 4], r6[6 * i + 5], 0.f);
+    }
+}
+void k_pack_rays(const float* d_rays6, size_t n, float4* d_ray_o, float4* d_ray_d, cudaStream_t st) {
+    if (n) pack_rays_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(d_rays6, n, d_ray_o, d_ray_d);
+}
+__global__ void unpack_rays_kernel(const float4* __restrict__ ray_o, const float4* __restrict__ ray_d, size_t n, float* r6) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const float4 o = ray_o[i], d = ray_d[i];
+        r6[6 * i] = o.x; r6[6 * i + 1] = o.y; r6[6 * i + 2] = o.z;
+        r6[6 * i + 3] = d.x; r6[6 * i + 4] = d.y; r6[6 * i + 5] = d.z;
+    }
+}
+void k_unpack_rays(const float4* d_ray_o, const float4* d_ray_d, size_t n, float* d_rays6, cudaStream_t st) {
+    if (n) unpack_rays_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(d_ray_o, d_ray_d, n, d_rays6);
+}
+__global__ void unpack_hits_kernel(DevScene sc, const HitRec* __restrict__ hits, size_t n, int* geom, int* tri, float* t) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const HitRec h = hits[i];
+        if (geom) geom[i] = h.ord >= 0 ? sc.ord_geom[h.ord] : -1;
+        if (tri) tri[i] = h.ord >= 0 ? sc.ord_tri[h.ord] : -1;
+        if (t) t[i] = h.key;
+    }
+}
+void k_unpack_hits(const DevScene& sc, const HitRec* d_hits, size_t n, int* d_geom, int* d_tri, float* d_t, cudaStream_t st) {
+    if (n) unpack_hits_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(sc, d_hits, n, d_geom, d_tri, d_t);
+}
+
+// ------------------------------------------------------------------ synthetic workloads
+// Triangle i: centroid c ~ U[0,1)^3, vertices c + s*U[-1,1)^3; Philox key {0xF1EEF1E5, N}, counter {i, vertex, 0, 0}.
+__global__ void make_soup_kernel(size_t n, float s, float* xyz9) {
+    const uint32_t k0 = 0xF1EEF1E5u, k1 = (uint32_t)n;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        U4 c = philox4x32_10(U4{(uint32_t)i, 0u, 0u, 0u}, k0, k1);
+        const float cx = u01(c.x), cy = u01(c.y), cz = u01(c.z);
+        for (uint32_t v = 0; v < 3; ++v) {
+            U4 r = philox4x32_10(U4{(uint32_t)i, v + 1u, 0u, 0u}, k0, k1);
+            xyz9[9 * i + 3 * v + 0] = fadd(cx, fmul(s, fsub(fmul(u01(r.x), 2.0f), 1.0f)));
+            xyz9[9 * i + 3 * v + 1] = fadd(cy, fmul(s, fsub(fmul(u01(r.y), 2.0f), 1.0f)));
+            xyz9[9 * i + 3 * v + 2] = fadd(cz, fmul(s, fsub(fmul(u01(r.z), 2.0f), 1.0f)));
+        }
+    }
+}
+void k_make_soup(size_t n, float s, float* d_xyz9, cudaStream_t st) {
+    if (n) make_soup_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(n, s, d_xyz9);
+}
+// Batch A: origin ~ U[0,1)^3, direction uniform on the sphere; key {0xF1EEF1E5, 1}, counter {i, 0|1, salt, 0}.
+__global__ void make_rays_uniform_kernel(uint64_t first, size_t n, uint32_t salt, float4* ray_o, float4* ray_d) {
+    for (size_t k = blockIdx.x * (size_t)blockDim.x + threadIdx.x; k < n; k += (size_t)gridDim.x * blockDim.x) {
+        const uint32_t i = (uint32_t)(first + k);
+        U4 a = philox4x32_10(U4{i, 0u, salt, 0u}, 0xF1EEF1E5u, 1u);
+        U4 b = philox4x32_10(U4{i, 1u, salt, 0u}, 0xF1EEF1E5u, 1u);
+        const float z = fsub(1.0f, fmul(2.0f, u01(b.x)));
+        const float r = fsqrt(fmaxf(0.0f, fsub(1.0f, fmul(z, z))));
+        float sn, cs;
+        sincos2pi(u01(b.y), sn, cs);
+        ray_o[k] = make_float4(u01(a.x), u01(a.y), u01(a.z), 0.f);
+        ray_d[k] = make_float4(fmul(r, cs), fmul(r, sn), z, 0.f);
+    }
+}
+void k_make_rays_uniform(uint64_t first, size_t n, uint32_t salt, float4* d_ray_o, float4* d_ray_d, cudaStream_t st) {
+    if (n) make_rays_uniform_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(first, n, salt, d_ray_o, d_ray_d);
+}
+
+// Batch B: one cosine-hemisphere bounce off every hit of an input batch (compacted, warp-aggregated append).
+__global__ void make_rays_bounce_kernel(DevScene sc, const float4* __restrict__ ray_o, const float4* __restrict__ ray_d,
+                                        const HitRec* __restrict__ hits, uint32_t n, uint32_t seed_lo, uint32_t seed_hi,
+                                        float4* out_o, float4* out_d, uint32_t* count) {
+    const uint32_t total = ((n + 31) / 32) * 32;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        bool alive = false;
+        V3 no, nd;
+        if (i < n) {
+            const HitRec h = hits[i];
+            if (h.slot >= 0 && h.slot < 0x40000000) {
+                const V3 o = ld3(ray_o[i]), draw = ld3(ray_d[i]);
+                const V3 dn = normalize(draw);
+                const V3 P = add(o, mul(dn, h.t));
+                const V3 a = ld3(sc.tris[3 * (size_t)h.slot]), b = ld3(sc.tris[3 * (size_t)h.slot + 1]), c = ld3(sc.tris[3 * (size_t)h.slot + 2]);
+                V3 nrm = normalize(normalize(cross(sub(b, a), sub(c, a))));
+                if (dot(nrm, draw) > 0.0f) nrm = neg(nrm);
+                U4 r = philox4x32_10(U4{i, 0u, 0u, 0u}, seed_lo, seed_hi);
+                const V3 w = cosine_sample_hemisphere(u01(r.x), u01(r.y));
+                V3 t, bt;
+                onb(nrm, t, bt);
+                nd = add(add(mul(t, w.x), mul(bt, w.y)), mul(nrm, w.z));
+                no = add(P, mul(nrm, 1e-4f));
+                alive = true;
+            }
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, alive);
+        if (m) {
+            const int lane = threadIdx.x & 31;
+            uint32_t base = 0;
+            if (lane == __ffs(m) - 1) base = atomicAdd(count, (uint32_t)__popc(m));
+            base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+            if (alive) {
+                const uint32_t k = base + __popc(m & ((1u << lane) - 1u));
+                out_o[k] = make_float4(no.x, no.y, no.z, 0.f);
+                out_d[k] = make_float4(nd.x, nd.y, nd.z, 0.f);
+            }
+        }
+    }
+}
+void k_make_rays_bounce(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const HitRec* d_hits, uint32_t n,
+                        uint32_t seed_lo, uint32_t seed_hi, float4* d_out_o, float4* d_out_d, uint32_t* d_count, cudaStream_t st) {
+    if (n) make_rays_bounce_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(sc, d_ray_o, d_ray_d, d_hits, n, seed_lo, seed_hi,
+                                                                              d_out_o, d_out_d, d_count);
+}
+
+__global__ void flush_kernel(float4* buf, size_t n) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        buf[i] = make_float4((float)i, 0.f, 0.f, 0.f);
+}
+void k_flush(float4* d_buf, size_t n_float4, cudaStream_t st) {
+    if (n_float4) flush_kernel<<<148 * 8, 256, 0, st>>>(d_buf, n_float4);
+}
+
+}  // namespace ff

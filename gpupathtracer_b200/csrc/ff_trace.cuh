@@ -1,0 +1,263 @@
+// ff_trace.cuh -- device-side closest-hit / any-hit traversal shared by the trace kernels, the wavefront
+// extend stage and the persistent megakernel.
+//
+// Replaces intersectRays (reference kernel.cu:127-176): the O(rays x triangles) scan becomes a
+// traversal of an 8-wide compressed BVH; the leaf test IS the reference's test (ffm::intersect_triangle,
+// kernel.cu:35-108) and the accept rule reproduces its closest-hit key and its scan-order tie-break:
+//     key = distance(o + d*t, o)                       (setIntersection, kernel.cu:113-115)
+//     accept  <=>  key < best || (key == best && ord < best_ord)   (strict '<' in scan order, kernel.cu:115,133,145)
+// Box culling is conservative: leaf boxes are inflated by DevScene::pad at build time and a node is
+// skipped only when its entry distance exceeds best*(1+2^-15).  DESIGN.md section 4.
+#pragma once
+#include "ff_internal.h"
+
+namespace ff {
+
+using ffm::V3;
+
+
+struct Best {
+    float key, t;
+    int slot, ord;
+};
+__device__ __forceinline__ void best_init(Best& b, float tmax) {
+    b.key = tmax; b.t = 0.f; b.slot = -1; b.ord = 0x7fffffff;
+}
+__device__ __forceinline__ bool best_accepts(const Best& b, float key, int ord) {
+    return key < b.key || (key == b.key && ord < b.ord);
+}
+
+__device__ __forceinline__ V3 ld3(const float4& v) { return ffm::v3(v.x, v.y, v.z); }
+
+// One triangle slot against the ray: the reference's test + key + tie-break.
+template <bool ANY>
+__device__ __forceinline__ bool test_slot(const float4* __restrict__ tris, int slot, V3 o, V3 dn, Best& best) {
+    const float4 a = __ldg(tris + 3 * (size_t)slot);
+    const float4 b = __ldg(tris + 3 * (size_t)slot + 1);
+    const float4 c = __ldg(tris + 3 * (size_t)slot + 2);
+    float t;
+    if (!ffm::intersect_triangle(ld3(a), ld3(b), ld3(c), o, dn, t)) return false;
+    V3 p;
+    float key = ffm::hit_key(o, dn, t, p);
+    int ord = __float_as_int(a.w);
+    if (ANY) {
+        if (key < best.key) { best.slot = slot; best.ord = ord; best.t = t; return true; }
+        return false;
+    }
+    if (best_accepts(best, key, ord)) {
+        best.key = key; best.t = t; best.slot = slot; best.ord = ord;
+        return true;
+    }
+    return false;
+}
+
+// glm mat4*vec4 (type_mat4x4.inl:536-575)
+__device__ __forceinline__ ffm::V4 mul_mv(const ffm::M4& m, float x, float y, float z, float w) {
+    using namespace ffm;
+    V4 r;
+    r.x = fadd(fadd(fmul(m.c[0].x, x), fmul(m.c[1].x, y)), fadd(fmul(m.c[2].x, z), fmul(m.c[3].x, w)));
+    r.y = fadd(fadd(fmul(m.c[0].y, x), fmul(m.c[1].y, y)), fadd(fmul(m.c[2].y, z), fmul(m.c[3].y, w)));
+    r.z = fadd(fadd(fmul(m.c[0].z, x), fmul(m.c[1].z, y)), fadd(fmul(m.c[2].z, z), fmul(m.c[3].z, w)));
+    r.w = fadd(fadd(fmul(m.c[0].w, x), fmul(m.c[1].w, y)), fadd(fmul(m.c[2].w, z), fmul(m.c[3].w, w)));
+    return r;
+}
+
+// intersectPlane (kernel.cu:8-32) + setIntersection (kernel.cu:110-125) for one analytic plane.
+// `d_raw` is the ray direction as given (the reference normalises it in object space, kernel.cu:138).
+__device__ __forceinline__ bool plane_hit(const DevPlane& pl, V3 o, V3 d_raw, float& key, float& t_local, V3& world_point) {
+    using namespace ffm;
+    V4 o4 = mul_mv(pl.inv, o.x, o.y, o.z, 1.0f);
+    V4 d4 = mul_mv(pl.inv, d_raw.x, d_raw.y, d_raw.z, 0.0f);
+    float dd = fadd(fadd(fmul(d4.x, d4.x), fmul(d4.y, d4.y)), fadd(fmul(d4.z, d4.z), fmul(d4.w, d4.w)));
+    float inv = inversesqrt(dd);
+    V3 od = v3(fmul(d4.x, inv), fmul(d4.y, inv), fmul(d4.z, inv));
+    V3 oo = v3(o4.x, o4.y, o4.z);
+    V3 n = v3(0.f, 0.f, 1.f);
+    float denom = dot(n, od);
+    if (!((double)fabsf(denom) > 1e-7)) return false;
+    float t = fdiv(dot(neg(oo), n), denom);
+    V3 P = add(oo, mul(od, t));
+    if (!(P.x >= -0.5f && P.x <= 0.5f && P.y >= -0.5f && P.y <= 0.5f)) return false;
+    if (!(t > 0.0f)) return false;
+    V4 w = mul_mv(pl.model, P.x, P.y, P.z, 1.0f);
+    world_point = v3(w.x, w.y, w.z);
+    key = distance(world_point, o);
+    t_local = t;
+    return true;
+}
+
+template <bool ANY>
+__device__ __forceinline__ void test_planes(const DevScene& sc, V3 o, V3 d_raw, Best& best) {
+    for (uint32_t i = 0; i < sc.n_planes; ++i) {
+        float key, tl;
+        V3 wp;
+        if (plane_hit(sc.planes[i], o, d_raw, key, tl, wp)) {
+            int ord = sc.planes[i].ord;
+            if (ANY ? (key < best.key) : best_accepts(best, key, ord)) {
+                if (!ANY) best.key = key;
+                best.t = tl; best.slot = 0x40000000 | (int)i; best.ord = ord;
+                if (ANY) return;
+            }
+        }
+    }
+}
+
+__device__ __forceinline__ float safe_rcp(float d) {
+    const float tiny = 1e-20f;
+    return 1.0f / (fabsf(d) > tiny ? d : copysignf(tiny, d));
+}
+
+// ------------------------------------------------------------------------------------------------
+// 8-wide compressed BVH traversal (node layout in ff_bvh.cu / DESIGN.md section 3).
+// `sm_stack` points at this thread's column of a [FF_SM_STACK][blockDim.x] uint2 array.
+template <bool ANY, bool COUNT>
+__device__ __forceinline__ void trace_bvh8(const DevScene& sc, V3 o, V3 dn, Best& best, uint2* sm_stack, int sm_stride,
+                                           unsigned& n_nodes, unsigned& n_tris) {
+    if (sc.n_nodes == 0) return;
+    const float4* __restrict__ nodes = sc.nodes;
+    const float4* __restrict__ tris = sc.tris;
+    const float idx_ = safe_rcp(dn.x), idy_ = safe_rcp(dn.y), idz_ = safe_rcp(dn.z);
+    const uint32_t octinv = (dn.x < 0.f ? 0u : 4u) | (dn.y < 0.f ? 0u : 2u) | (dn.z < 0.f ? 0u : 1u);
+    const uint32_t octinv4 = octinv * 0x01010101u;
+    const float slack = 1.000030517578125f;  // 1 + 2^-15
+
+    uint2 lstack[FF_LOCAL_STACK];
+    int sp = 0;
+    uint2 ngroup = make_uint2(0u, 0x80000000u);
+    uint2 tgroup = make_uint2(0u, 0u);
+    float tlimit = best.key * slack;
+
+    for (;;) {
+        if (ngroup.y & 0xff000000u) {
+            const uint32_t hits_imask = ngroup.y;
+            const uint32_t bit = 31u - __clz(hits_imask);
+            const uint32_t base = ngroup.x;
+            ngroup.y &= ~(1u << bit);
+            if (ngroup.y & 0xff000000u) {
+                if (sp < FF_SM_STACK) sm_stack[sp * sm_stride] = ngroup;
+                else lstack[sp - FF_SM_STACK] = ngroup;
+                ++sp;
+            }
+            const uint32_t slot_index = (bit - 24u) ^ octinv;
+            const uint32_t rel = __popc(hits_imask & ~(0xffffffffu << slot_index) & 0xffu);
+            const size_t ni = (size_t)(base + rel) * 5;
+            const float4 n0 = __ldg(nodes + ni), n1 = __ldg(nodes + ni + 1), n2 = __ldg(nodes + ni + 2),
+                         n3 = __ldg(nodes + ni + 3), n4 = __ldg(nodes + ni + 4);
+            if (COUNT) ++n_nodes;
+            const uint32_t eb = __float_as_uint(n0.w);
+            const float ax = __uint_as_float((eb & 0xffu) << 23) * idx_;
+            const float ay = __uint_as_float(((eb >> 8) & 0xffu) << 23) * idy_;
+            const float az = __uint_as_float(((eb >> 16) & 0xffu) << 23) * idz_;
+            const float ox = (n0.x - o.x) * idx_, oy = (n0.y - o.y) * idy_, oz = (n0.z - o.z) * idz_;
+            ngroup.x = __float_as_uint(n1.x);
+            tgroup.x = __float_as_uint(n1.y);
+            uint32_t hitmask = 0;
+            // near / far plane bytes per axis, selected by the direction sign
+            const bool nx = dn.x < 0.f, ny = dn.y < 0.f, nz = dn.z < 0.f;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const uint32_t meta4 = __float_as_uint(h ? n1.w : n1.z);
+                const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+                const uint32_t inner_mask4 = (is_inner4 >> 4) * 0xffu;
+                const uint32_t bit_index4 = (meta4 ^ (octinv4 & inner_mask4)) & 0x1f1f1f1fu;
+                const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+                const uint32_t qlox = __float_as_uint(h ? n2.y : n2.x), qloy = __float_as_uint(h ? n2.w : n2.z);
+                const uint32_t qloz = __float_as_uint(h ? n3.y : n3.x), qhix = __float_as_uint(h ? n3.w : n3.z);
+                const uint32_t qhiy = __float_as_uint(h ? n4.y : n4.x), qhiz = __float_as_uint(h ? n4.w : n4.z);
+                const uint32_t nearx = nx ? qhix : qlox, farx = nx ? qlox : qhix;
+                const uint32_t neary = ny ? qhiy : qloy, fary = ny ? qloy : qhiy;
+                const uint32_t nearz = nz ? qhiz : qloz, farz = nz ? qloz : qhiz;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float tnx = fmaf((float)((nearx >> (8 * j)) & 0xffu), ax, ox);
+                    const float tny = fmaf((float)((neary >> (8 * j)) & 0xffu), ay, oy);
+                    const float tnz = fmaf((float)((nearz >> (8 * j)) & 0xffu), az, oz);
+                    const float tfx = fmaf((float)((farx >> (8 * j)) & 0xffu), ax, ox);
+                    const float tfy = fmaf((float)((fary >> (8 * j)) & 0xffu), ay, oy);
+                    const float tfz = fmaf((float)((farz >> (8 * j)) & 0xffu), az, oz);
+                    const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
+                    const float tf = fminf(fminf(tfx, tfy), fminf(tfz, tlimit));
+                    if (tn <= tf) {
+                        const uint32_t cb = (child_bits4 >> (8 * j)) & 0xffu;
+                        const uint32_t bi = (bit_index4 >> (8 * j)) & 0xffu;
+                        hitmask |= cb << bi;
+                    }
+                }
+            }
+            ngroup.y = (hitmask & 0xff000000u) | (eb >> 24);
+            tgroup.y = hitmask & 0x00ffffffu;
+        } else {
+            tgroup = ngroup;
+            ngroup = make_uint2(0u, 0u);
+        }
+
+        while (tgroup.y != 0u) {
+            const uint32_t ti = 31u - __clz(tgroup.y);
+            tgroup.y &= ~(1u << ti);
+            if (COUNT) ++n_tris;
+            if (test_slot<ANY>(tris, (int)(tgroup.x + ti), o, dn, best)) {
+                if (ANY) return;
+                tlimit = best.key * slack;
+            }
+        }
+
+        if ((ngroup.y & 0xff000000u) == 0u) {
+            if (sp == 0) break;
+            --sp;
+            ngroup = (sp < FF_SM_STACK) ? sm_stack[sp * sm_stride] : lstack[sp - FF_SM_STACK];
+        }
+    }
+}
+
+// Binary LBVH traversal (comparison / bridge variant).
+template <bool ANY, bool COUNT>
+__device__ __forceinline__ void trace_bvh2(const DevScene& sc, V3 o, V3 dn, Best& best, unsigned& n_nodes, unsigned& n_tris) {
+    if (sc.n_tris == 0) return;
+    const uint32_t n_internal = sc.n_tris - 1;
+    const float idx_ = safe_rcp(dn.x), idy_ = safe_rcp(dn.y), idz_ = safe_rcp(dn.z);
+    const float slack = 1.000030517578125f;
+    uint32_t stack[64];
+    int sp = 0;
+    uint32_t node = 0;
+    if (n_internal == 0) {
+        if (COUNT) ++n_tris;
+        test_slot<ANY>(sc.tris, (int)sc.bvh2_leaf_slot[0], o, dn, best);
+        return;
+    }
+    for (;;) {
+        if (node >= n_internal) {
+            if (COUNT) ++n_tris;
+            if (test_slot<ANY>(sc.tris, (int)sc.bvh2_leaf_slot[node - n_internal], o, dn, best) && ANY) return;
+        } else {
+            if (COUNT) ++n_nodes;
+            const int2 ch = sc.bvh2_children[node];
+            float tn[2];
+            bool hit[2];
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+                const uint32_t c = (uint32_t)(k ? ch.y : ch.x);
+                const float4 lo = __ldg(sc.bvh2_lo + c), hi = __ldg(sc.bvh2_hi + c);
+                const float x0 = (lo.x - o.x) * idx_, x1 = (hi.x - o.x) * idx_;
+                const float y0 = (lo.y - o.y) * idy_, y1 = (hi.y - o.y) * idy_;
+                const float z0 = (lo.z - o.z) * idz_, z1 = (hi.z - o.z) * idz_;
+                const float a = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.0f));
+                const float b = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), best.key * slack));
+                // widen by a relative 2^-20 so rounding in the slab arithmetic can never cull
+                hit[k] = a * 0.99999905f <= b * 1.00000095f;
+                tn[k] = a;
+            }
+            if (hit[0] && hit[1]) {
+                const bool first0 = tn[0] <= tn[1];
+                stack[sp++] = (uint32_t)(first0 ? ch.y : ch.x);
+                node = (uint32_t)(first0 ? ch.x : ch.y);
+                continue;
+            }
+            if (hit[0]) { node = (uint32_t)ch.x; continue; }
+            if (hit[1]) { node = (uint32_t)ch.y; continue; }
+        }
+        if (sp == 0) break;
+        node = stack[--sp];
+    }
+}
+
+}  // namespace ff

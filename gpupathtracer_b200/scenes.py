@@ -1,0 +1,130 @@
+"""Scene descriptions of the five BASELINE.json configs plus the reference's own main() scene.
+
+A description is plain data -- a list of geometries (mesh name or triangle array, TRS, material, flip) and a camera
+dict -- so the same description can be instantiated on the GPU library (`instantiate`) and, by the tests, on the CPU
+oracle.  The reference hard-codes its one scene in main() (kernel.cu:227-266, 311-322); `reference_main` restates it.
+
+Meshes are the reference's scene assets (sceneResources/*.obj).  /root/reference does not exist on the GPU box, so
+`load_meshes` reads the triangle-position fixture made from them by tools/make_golden.py, falling back to the OBJ
+files (through this library's own OBJ reader) where the reference tree is mounted.
+"""
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+MESH_FIXTURE = os.path.join(_HERE, "..", "tests", "golden", "meshes.npz")
+REFERENCE_OBJ_DIR = "/root/reference/sceneResources"
+MESH_NAMES = ["cube", "triangle", "rocketman", "sphere", "sphereBlender", "wahoo"]
+
+DIFFUSE_GREY = dict(type=1, albedo=(0.8, 0.8, 0.8))
+DIFFUSE_RED = dict(type=1, albedo=(1.0, 0.0, 0.0))        # kernel.cu:237-239
+EMITTER_WHITE2 = dict(type=0, emissive=(1.0, 1.0, 1.0), intensity=2.0)   # kernel.cu:241-244
+
+
+def load_meshes():
+    if os.path.exists(MESH_FIXTURE):
+        z = np.load(MESH_FIXTURE)
+        return {k: z[k] for k in z.files}
+    if os.path.isdir(REFERENCE_OBJ_DIR):
+        import gpupathtracer_b200 as ff
+        return {k: ff.load_obj(os.path.join(REFERENCE_OBJ_DIR, k + ".obj")) for k in MESH_NAMES}
+    raise FileNotFoundError("no mesh fixture (%s) and no reference tree" % MESH_FIXTURE)
+
+
+def camera(pos, yaw=-90.0, pitch=0.0, fov=70.0, width=256, height=256, near=0.1, far=1000.0):
+    return dict(pos=tuple(pos), world_up=(0, 1, 0), yaw=yaw, pitch=pitch, fov=fov, width=width, height=height, near=near, far=far)
+
+
+def geom(mesh, pos=(0, 0, 0), rot=(0, 0, 0), scale=(1, 1, 1), material=None, flip=False, plane=False):
+    return dict(mesh=mesh, pos=pos, rot=rot, scale=scale, material=material or DIFFUSE_GREY, flip=flip, plane=plane)
+
+
+def flip_winding(xyz9):
+    a = np.array(xyz9, np.float32).reshape(-1, 9).copy()
+    a[:, 3:6], a[:, 6:9] = a[:, 6:9].copy(), a[:, 3:6].copy()
+    return a
+
+
+def config1(width=256, height=256):
+    """cube.obj + triangle.obj, 256x256, 1 spp, closest hit."""
+    return dict(name="C1", geoms=[geom("cube"), geom("triangle", pos=(-0.5, -0.5, 1.0))],
+                camera=camera((0, 0, 4), fov=40.0, width=width, height=height), spp=1, max_bounces=1)
+
+
+def _cube_faces(cube):
+    """Splits the 12 cube triangles by the axis/sign of their face so the ceiling can be its own (emissive) geometry."""
+    cube = np.asarray(cube, np.float32).reshape(-1, 9)
+    top = np.array([np.allclose(t.reshape(3, 3)[:, 1], 0.5) for t in cube])
+    return cube[top], cube[~top]
+
+
+def config2(meshes, width=1024, height=1024, spp=64, max_bounces=4):
+    """rocketman.obj inside cube.obj (the README box), ceiling emissive, 64 spp, 4 bounces diffuse."""
+    top, rest = _cube_faces(meshes["cube"])
+    return dict(name="C2",
+                geoms=[geom(rest, scale=(5, 5, 5), flip=True),
+                       geom(top, scale=(5, 5, 5), flip=True, material=EMITTER_WHITE2),
+                       geom("rocketman", rot=(0, 90, 180), material=DIFFUSE_RED)],   # kernel.cu:229
+                camera=camera((0, 0, 2.4), fov=70.0, width=width, height=height), spp=spp, max_bounces=max_bounces)
+
+
+def config3(meshes, width=1920, height=1080, spp=256, max_bounces=8):
+    """wahoo.obj + sphere.obj light + two-triangle floor, wavefront vs megakernel."""
+    y = -0.07
+    floor = np.array([[-60, y, 60, 60, y, 60, 60, y, -60], [-60, y, 60, 60, y, -60, -60, y, -60]], np.float32)
+    return dict(name="C3",
+                geoms=[geom("wahoo"), geom("sphere", pos=(0, 18, 0), material=dict(type=0, emissive=(1, 1, 1), intensity=5.0)),
+                       geom(floor)],
+                camera=camera((0, 8, 30), fov=40.0, width=width, height=height), spp=spp, max_bounces=max_bounces)
+
+
+def reference_main(width=800, height=800):
+    """The scene main() hard-codes (kernel.cu:227-266, 311-322): rocketman + four unit planes scaled x5."""
+    return dict(name="main",
+                geoms=[geom("rocketman", rot=(0, 90, 180), material=DIFFUSE_RED),
+                       geom(None, pos=(0, 0, -2.5), scale=(5, 5, 5), plane=True, material=DIFFUSE_RED),
+                       geom(None, pos=(0, 2.5, 0), rot=(90, 0, 0), scale=(5, 5, 5), plane=True, material=DIFFUSE_RED),
+                       geom(None, pos=(0, -2.5, 0), rot=(90, 0, 0), scale=(5, 5, 5), plane=True, material=DIFFUSE_RED),
+                       geom(None, pos=(0, 0, 2.5), scale=(5, 5, 5), plane=True, material=DIFFUSE_RED)],
+                camera=camera((0, 0, 15), fov=70.0, width=width, height=height), spp=1, max_bounces=0)
+
+
+def soup_scale(n):
+    return float(np.float32(float(n) ** (-1.0 / 3.0)))
+
+
+def config4_camera(width=3840, height=2160):
+    return camera((0.5, 0.5, -1.5), yaw=90.0, fov=40.0, width=width, height=height)
+
+
+def resolve_mesh(g, meshes):
+    m = g["mesh"]
+    if isinstance(m, str):
+        m = meshes[m]
+    m = np.ascontiguousarray(m, np.float32).reshape(-1, 9)
+    return flip_winding(m) if g["flip"] else m
+
+
+def instantiate(desc, ctx, meshes=None, builder=0, commit=True):
+    """Builds the description on the GPU library; returns (Scene, Camera)."""
+    import gpupathtracer_b200 as ff
+    sc = ctx.scene()
+    for g in desc["geoms"]:
+        if g["plane"]:
+            sc.add_plane(g["pos"], g["rot"], g["scale"], g["material"])
+        else:
+            sc.add_triangles(resolve_mesh(g, meshes), g["pos"], g["rot"], g["scale"], g["material"])
+    if commit:
+        sc.commit(builder)
+    return sc, ff.Camera.from_dict(desc["camera"])
+
+
+def instantiate_on(desc, scene, meshes=None):
+    """Same on any object with add_mesh/add_plane (the test oracle's scene classes)."""
+    for g in desc["geoms"]:
+        if g["plane"]:
+            scene.add_plane(g["pos"], g["rot"], g["scale"], g["material"])
+        else:
+            scene.add_mesh(resolve_mesh(g, meshes), g["pos"], g["rot"], g["scale"], g["material"])
+    return scene

@@ -1,0 +1,215 @@
+/* firefly.h -- C ABI of the B200-native path-tracing core (libfirefly_b200.so).
+ *
+ * Drop-in boundary for the one hot path of FireflyRenderEngine/GPUPathTracer: scene in (OBJ or
+ * triangle arrays + TRS + material), camera in, render() / trace() out.  Plain pointers and sizes
+ * only; no C++, glm or torch types.  The reference has no FFI of its own (the path is called inline
+ * from main()), so each entry point cites the seam in the reference it replaces; paths are relative
+ * to the reference tree, kernel.cu = PathTracer/FireflyEngine/kernel.cu, utilities.h likewise.
+ *
+ * Conventions: every int-returning function returns FF_OK (0) or a negative ff_status; the message
+ * is available from ff_last_error() (thread-local).  Nothing here ever calls exit() (the reference's
+ * cudaCheckErrors macro, utilities.h:27-37, does).  The library owns handles and all device memory
+ * it allocates; the caller owns every buffer it passes in.  A context is bound to one CUDA device and
+ * one internal stream and is not thread-safe; calls are synchronous on return unless stated.
+ * There is no CPU fallback: without a CUDA device ff_context_create fails with FF_ERR_CUDA.
+ */
+#ifndef FIREFLY_H
+#define FIREFLY_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FF_VERSION 100
+
+typedef enum ff_status {
+    FF_OK = 0,
+    FF_ERR_INVALID = -1,     /* bad argument / handle state */
+    FF_ERR_IO = -2,          /* file could not be read / written / parsed */
+    FF_ERR_CUDA = -3,        /* CUDA runtime error (message has the cudaError string) */
+    FF_ERR_NOMEM = -4,
+    FF_ERR_UNSUPPORTED = -5
+} ff_status;
+
+typedef struct ff_context ff_context; /* replaces PathTracerState, kernel.h:12-20 */
+typedef struct ff_scene ff_scene;     /* replaces Geometry[] + per-geometry Triangle[]/BXDF, kernel.cu:268-298 */
+
+/* Camera, mirrors the fields main() sets (kernel.cu:311-322; struct at utilities.h:269-285).
+ * forward/right/up are derived from yaw/pitch exactly like Camera::UpdateBasisAxis (utilities.h:407-418). */
+typedef struct ff_camera {
+    float pos[3];
+    float world_up[3];
+    float yaw_deg, pitch_deg, fov_deg;
+    int width, height;
+    float near_clip, far_clip;
+} ff_camera;
+
+/* Material, mirrors BXDF (utilities.h:77-88); type follows BXDFTyp (utilities.h:68-75). */
+enum { FF_MAT_EMITTER = 0, FF_MAT_DIFFUSE = 1, FF_MAT_MIRROR = 2, FF_MAT_GLASS = 3 };
+typedef struct ff_material {
+    int type;
+    float albedo[3];
+    float emissive[3];
+    float intensity;
+} ff_material;
+
+enum { FF_INTEGRATOR_WAVEFRONT = 0, FF_INTEGRATOR_MEGAKERNEL = 1, FF_INTEGRATOR_AS_CODED = 2 };
+enum { FF_BUILDER_LBVH = 0, FF_BUILDER_SAH = 1 };
+enum { FF_TRACE_BVH8 = 0, FF_TRACE_BRUTE = 1, FF_TRACE_BVH2 = 2 };
+
+typedef struct ff_render_params {
+    int spp;                 /* samples per pixel rendered by THIS call */
+    int max_bounces;         /* path segments = max_bounces + 1 */
+    uint64_t seed;           /* Philox key {lo, hi}; the reference's constant is 1234 (utilities.h:118) */
+    int integrator;          /* FF_INTEGRATOR_* */
+    int nee;                 /* next-event estimation with shadow rays (0 = plain loop) */
+    int first_sample;        /* global index of the first sample (multi-GPU sample split, resume) */
+    int aa;                  /* 0: integer pixel corner like kernel.cu:200-201; 1: Philox jitter */
+    float background[3];     /* radiance of a miss; the reference leaves misses black (kernel.cu:340) */
+    float ray_eps;           /* offset of spawned rays along the normal */
+    int samples_per_pass;    /* samples in flight per wavefront pass; 0 = pick from image size */
+    int total_spp;           /* divisor of the final mean; 0 = spp (single GPU) */
+} ff_render_params;
+
+/* Per-call measurements, all taken with CUDA events on the context's stream. */
+typedef struct ff_stats {
+    double gpu_ms;           /* device time of the whole call's kernels */
+    double trace_ms;         /* of which closest-hit / any-hit traversal kernels */
+    double h2d_ms, d2h_ms;   /* host<->device copies made by the call (0 for *_device entry points) */
+    uint64_t rays;           /* closest-hit queries executed */
+    uint64_t shadow_rays;    /* any-hit queries executed */
+    uint64_t paths;          /* complete samples */
+    uint64_t nodes_visited;  /* instrumented runs only (ff_trace flag FF_TRACE_COUNT), else 0 */
+    uint64_t tris_tested;    /* idem */
+    uint32_t kernel_launches;
+    uint32_t reserved;
+} ff_stats;
+
+typedef struct ff_scene_info {
+    uint64_t n_triangles, n_geometries, n_planes;
+    uint64_t n_nodes;        /* 8-wide compressed nodes (80 B each) */
+    uint64_t node_bytes, triangle_bytes;
+    uint32_t depth;          /* depth of the wide hierarchy */
+    uint32_t builder;
+    float bounds_lo[3], bounds_hi[3];
+    double build_ms;         /* device time of the last commit (sort + hierarchy + refit + collapse) */
+    double sah_cost;         /* SAH cost of the wide hierarchy, for comparing builders */
+} ff_scene_info;
+
+const char* ff_last_error(void);
+int ff_version(void);
+int ff_device_count(void);
+
+/* -- context: device + stream.  Replaces the implicit default device/stream of main(). */
+int ff_context_create(ff_context** out, int device_id);
+void ff_context_destroy(ff_context* ctx);
+int ff_context_device(const ff_context* ctx);
+int ff_context_synchronize(ff_context* ctx);
+
+/* -- scene building.  LoadMesh (utilities.h:781-840) + Geometry ctor (utilities.h:176-213) + the
+ *    m_bxdf assignment (kernel.cu:246-250).  model = T * Rx * Ry * Rz * S, rotations in degrees.
+ *    Geometry indices are assigned in call order, like the std::vector in kernel.cu:253-258. */
+int ff_scene_create(ff_context* ctx, ff_scene** out);
+void ff_scene_destroy(ff_scene* scene);
+int ff_scene_add_obj(ff_scene* scene, const char* obj_path, const float pos[3], const float rot_deg[3],
+                     const float scale[3], const ff_material* material, int flip_winding,
+                     int* out_geometry_index);
+int ff_scene_add_triangles(ff_scene* scene, const float* xyz9, size_t n_tris, const float pos[3],
+                           const float rot_deg[3], const float scale[3], const ff_material* material,
+                           int* out_geometry_index);
+/* GeometryType::PLANE (utilities.h:141-146, intersectPlane kernel.cu:8-32): unit square at object z=0. */
+int ff_scene_add_plane(ff_scene* scene, const float pos[3], const float rot_deg[3], const float scale[3],
+                       const ff_material* material, int* out_geometry_index);
+/* OBJ -> xyz9 triangle list without a scene (the LoadMesh half on its own).  Call with xyz9 = NULL
+ * to get the count. Returns the triangle count or a negative ff_status. */
+long ff_load_obj(const char* obj_path, float* xyz9, size_t capacity_tris);
+
+/* Flatten to world-space SoA, upload, build the BVH on the device.  Replaces kernel.cu:268-298. */
+int ff_scene_commit(ff_scene* scene, int builder, double* out_build_ms);
+int ff_scene_get_info(const ff_scene* scene, ff_scene_info* out);
+/* World-space (baked) triangles in flat order = (geometry, triangle) order, and their source ids. */
+int ff_scene_get_flat(const ff_scene* scene, float* xyz9, int* geom, int* tri, size_t capacity_tris);
+int ff_scene_get_matrices(const ff_scene* scene, int geometry_index, float model16[16], float inverse16[16]);
+
+/* -- closest hit on caller-supplied ray batches: the parity / benchmark entry.  Replaces
+ *    intersectRays (kernel.cu:127-176).  rays6 = n x {ox,oy,oz,dx,dy,dz}; directions need not be
+ *    normalised (the routine normalises, kernel.cu:138).  Outputs use the reference's numbering:
+ *    geometryIndex, triangleIndex (-1,-1 on a miss; triangleIndex -1 for a plane), t = the
+ *    reference's closest-hit key (world-space distance, kernel.cu:113-121), +inf on a miss. */
+#define FF_TRACE_COUNT 0x100 /* OR into `mode`: instrumented kernel, fills nodes_visited / tris_tested */
+int ff_trace_closest(ff_scene* scene, const float* rays6, size_t n, int mode, int* out_geom, int* out_tri,
+                     float* out_t, ff_stats* stats);
+/* Same with device-resident buffers (no copies): d_rays = n x 2 float4 {o.xyz,0},{d.xyz,0};
+ * d_hits = n x int4-sized records {key t (f32 bits), t along the ray (f32 bits), triangle slot, flat id}. */
+int ff_trace_closest_device(ff_scene* scene, const void* d_rays, size_t n, int mode, void* d_hits,
+                            ff_stats* stats);
+/* Any-hit (occlusion) query: out_occluded[i] = 1 when a front-facing triangle is hit with key < tmax[i]. */
+int ff_trace_any(ff_scene* scene, const float* rays6, const float* tmax, size_t n, int mode,
+                 unsigned char* out_occluded, ff_stats* stats);
+/* Unpack device hit records into the reference's numbering (host arrays, may be NULL). */
+int ff_hits_unpack(ff_scene* scene, const void* d_hits, size_t n, int* out_geom, int* out_tri, float* out_t);
+
+/* -- camera rays exactly as generateRays builds them (kernel.cu:198-205), host or device output. */
+int ff_camera_rays(ff_context* ctx, const ff_camera* cam, float* rays6_host, void* d_rays);
+int ff_camera_basis(const ff_camera* cam, float forward[3], float right[3], float up[3]);
+int ff_camera_inverse_matrices(const ff_camera* cam, float inv_view16[16], float inv_proj16[16]);
+
+/* -- render.  Replaces launchPathTrace<<<>>>(pbo, geometries, camera, n) (kernel.cu:218-221,342)
+ *    with the bounce loop the reference intends (readme.md:39-46, BXDF utilities.h:90-139).
+ *    ff_render: mean radiance, RGBA fp32, row 0 = top (kernel orientation), to a host buffer and/or a
+ *    caller-owned device buffer.  ff_render_u8: byte-compatible with the uchar3 PBO the viewer maps
+ *    (kernel.cu:337-344, 349-351): W*H*3, tightly packed. */
+int ff_render(ff_scene* scene, const ff_camera* cam, const ff_render_params* params, float* out_rgba_host,
+              void* out_rgba_device, ff_stats* stats);
+int ff_render_u8(ff_scene* scene, const ff_camera* cam, const ff_render_params* params,
+                 unsigned char* out_rgb, int out_is_device, ff_stats* stats);
+/* Multi-GPU building blocks: add this call's samples (as SUMS, not means) into a caller-owned
+ * device accumulator of W*H float4 (zero it first with ff_device_memset), then after the
+ * framebuffer reduce, divide by the total sample count. */
+int ff_render_accumulate(ff_scene* scene, const ff_camera* cam, const ff_render_params* params,
+                         void* d_accum_rgba, ff_stats* stats);
+int ff_resolve(ff_context* ctx, const void* d_accum_rgba, int width, int height, int total_spp,
+               void* d_out_rgba, float* out_rgba_host);
+/* Fused peer reduce + resolve: sums n_peers accumulators (device pointers valid on this device, e.g.
+ * CUDA-IPC mapped peers over NVLink) in rank order and divides by total_spp in one kernel. */
+int ff_reduce_resolve_peers(ff_context* ctx, const void* const* d_accum_peers, int n_peers, int width,
+                            int height, int total_spp, void* d_out_rgba, float* out_rgba_host);
+
+/* -- synthetic workloads of BASELINE.json configs 4/5, generated on the device with the same
+ *    Philox streams as the oracle (bit-identical to the host generators). */
+int ff_make_soup(ff_context* ctx, size_t n_tris, float s, float* xyz9_host);
+int ff_make_rays_uniform(ff_context* ctx, uint64_t first, size_t n, uint32_t salt, float* rays6_host,
+                         void* d_rays);
+/* Diffuse-bounce batch: cosine-hemisphere rays leaving the given hits (batch B of config 4). */
+int ff_make_rays_bounce(ff_scene* scene, const void* d_rays_in, const void* d_hits_in, size_t n,
+                        uint64_t seed, void* d_rays_out, size_t* out_n);
+
+/* -- device memory helpers so callers can keep batches resident without another CUDA binding. */
+int ff_device_malloc(ff_context* ctx, size_t bytes, void** out);
+int ff_device_free(ff_context* ctx, void* p);
+int ff_device_memset(ff_context* ctx, void* p, int value, size_t bytes);
+int ff_memcpy_h2d(ff_context* ctx, void* dst_device, const void* src_host, size_t bytes);
+int ff_memcpy_d2h(ff_context* ctx, void* dst_host, const void* src_device, size_t bytes);
+int ff_host_alloc_pinned(size_t bytes, void** out);
+int ff_host_free_pinned(void* p);
+int ff_ipc_get_handle(ff_context* ctx, void* d_ptr, unsigned char handle64[64]);
+int ff_ipc_open_handle(ff_context* ctx, const unsigned char handle64[64], void** out_d_ptr);
+int ff_ipc_close_handle(ff_context* ctx, void* d_ptr);
+/* Writes > L2-size scratch so the next timed launch starts cold. */
+int ff_flush_l2(ff_context* ctx);
+
+/* -- headless output.  Replaces saveToPPM (utilities.h:842-856).  Format by extension:
+ *    .ppm (binary P6), .png (8-bit sRGB), .exr (fp32 scanline, uncompressed), .pfm. */
+int ff_write_image(const char* path, const float* rgba, int width, int height);
+int ff_write_image_u8(const char* path, const unsigned char* rgb, int width, int height);
+
+/* -- Philox4x32-10 on the host (the generator all kernels use), for cross-checks. */
+void ff_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FIREFLY_H */

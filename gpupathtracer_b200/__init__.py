@@ -296,16 +296,17 @@ class Context:
         _check(lib.ff_camera_rays(self.h, C.byref(cam.c), _p(out), device_buffer.ptr if device_buffer is not None else None))
         return out
 
-    def resolve(self, accum, width, height, total_spp):
-        out = np.empty((height, width, 4), np.float32)
+    def resolve(self, accum, width, height, total_spp, host=True, device_out=None):
+        out = np.empty((height, width, 4), np.float32) if host else None
         _check(lib.ff_resolve(self.h, accum.ptr if isinstance(accum, DeviceBuffer) else C.c_void_p(accum), width, height,
-                              int(total_spp), None, _p(out)))
+                              int(total_spp), C.c_void_p(device_out) if device_out is not None else None, _p(out)))
         return out
 
-    def reduce_resolve_peers(self, ptrs, width, height, total_spp):
+    def reduce_resolve_peers(self, ptrs, width, height, total_spp, host=True, device_out=None):
         arr = (C.c_void_p * len(ptrs))(*[C.c_void_p(int(p)) for p in ptrs])
-        out = np.empty((height, width, 4), np.float32)
-        _check(lib.ff_reduce_resolve_peers(self.h, arr, len(ptrs), width, height, int(total_spp), None, _p(out)))
+        out = np.empty((height, width, 4), np.float32) if host else None
+        _check(lib.ff_reduce_resolve_peers(self.h, arr, len(ptrs), width, height, int(total_spp),
+                                           C.c_void_p(device_out) if device_out is not None else None, _p(out)))
         return out
 
 

@@ -627,7 +627,7 @@ int check_params(const ff_render_params* p, const char* who) {
     if (p->spp <= 0 || p->max_bounces < 0 || p->max_bounces > 1024 || p->first_sample < 0) {
         set_error(std::string(who) + ": bad spp / max_bounces / first_sample"); return FF_ERR_INVALID;
     }
-    if (p->integrator != FF_INTEGRATOR_WAVEFRONT && p->integrator != FF_INTEGRATOR_MEGAKERNEL) {
+    if ((p->integrator & 0xff) != FF_INTEGRATOR_WAVEFRONT && (p->integrator & 0xff) != FF_INTEGRATOR_MEGAKERNEL) {
         set_error(std::string(who) + ": integrator must be wavefront or megakernel here"); return FF_ERR_INVALID;
     }
     if (p->nee) { set_error(std::string(who) + ": next-event estimation is not available in this build"); return FF_ERR_UNSUPPORTED; }
@@ -654,7 +654,9 @@ int accumulate_samples(ff_scene* scene, const ff_camera* cam, const ff_render_pa
     rd.background[0] = p->background[0]; rd.background[1] = p->background[1]; rd.background[2] = p->background[2];
     rd.ray_eps = p->ray_eps;
     const int n_pass = (int)((p->spp + spb - 1) / spb);
-    const bool wave = p->integrator == FF_INTEGRATOR_WAVEFRONT;
+    const bool wave = (p->integrator & 0xff) == FF_INTEGRATOR_WAVEFRONT;
+    const bool count = wave && (p->integrator & FF_TRACE_COUNT) != 0;  // instrumented extend kernels
+    if (count) FF_CUDA(cudaMemsetAsync(scene->d_trace_counters, 0, sizeof(TraceCounters), st));
     // one event pair per extend stage, so trace_ms can be reported separately from the bookkeeping
     const size_t need_events = wave ? (size_t)2 * n_pass * (p->max_bounces + 1) : 0;
     const bool time_trace = stats && need_events <= 8192;
@@ -670,7 +672,7 @@ int accumulate_samples(ff_scene* scene, const ff_camera* cam, const ff_render_pa
         rd.first_sample = (uint32_t)(p->first_sample + s0);
         rd.samples = (uint32_t)std::min<size_t>(spb, p->spp - s0);
         if (wave) {
-            k_wavefront_pass(scene->dev, cd, rd, scene->wb, FF_TRACE_BVH8, &launches, time_trace ? c->trace_events.data() : nullptr, &n_ev, st);
+            k_wavefront_pass(scene->dev, cd, rd, scene->wb, FF_TRACE_BVH8 | (count ? FF_TRACE_COUNT : 0), scene->d_trace_counters, &launches, time_trace ? c->trace_events.data() : nullptr, &n_ev, st);
             FF_CUDA(cudaMemcpyAsync(h_counts.data() + (size_t)pass * (p->max_bounces + 2), scene->wb.counts,
                                     sizeof(uint32_t) * (p->max_bounces + 2), cudaMemcpyDeviceToHost, st));
         } else {
@@ -688,6 +690,11 @@ int accumulate_samples(ff_scene* scene, const ff_camera* cam, const ff_render_pa
         unsigned long long r = 0;
         FF_CUDA(cudaMemcpy(&r, scene->d_ray_counter, sizeof(r), cudaMemcpyDeviceToHost));
         rays = r;
+    }
+    if (stats && count) {
+        TraceCounters h;
+        FF_CUDA(cudaMemcpy(&h, scene->d_trace_counters, sizeof(h), cudaMemcpyDeviceToHost));
+        stats->nodes_visited += h.nodes; stats->tris_tested += h.tris;
     }
     if (stats) {
         stats->gpu_ms += ms; stats->rays += rays; stats->paths += (uint64_t)p->spp * npix; stats->kernel_launches += launches;
@@ -745,7 +752,7 @@ int ff_render(ff_scene* scene, const ff_camera* cam, const ff_render_params* par
     ff_context* c = scene->ctx;
     const size_t npix = (size_t)cam->width * cam->height;
     if ((rc = ensure_fb(scene, npix))) return rc;
-    if (params->integrator == FF_INTEGRATOR_AS_CODED) {
+    if ((params->integrator & 0xff) == FF_INTEGRATOR_AS_CODED) {
         // 8-bit as-coded frame widened to float RGBA (value / 255), for callers that want one code path
         unsigned char* d_rgb = nullptr;
         FF_CUDA(cudaMalloc((void**)&d_rgb, npix * 3));
@@ -785,7 +792,7 @@ int ff_render_u8(ff_scene* scene, const ff_camera* cam, const ff_render_params* 
     const size_t npix = (size_t)cam->width * cam->height;
     unsigned char* d_rgb = out_is_device ? out_rgb : nullptr;
     if (!d_rgb) FF_CUDA(cudaMalloc((void**)&d_rgb, npix * 3));
-    if (params->integrator == FF_INTEGRATOR_AS_CODED) {
+    if ((params->integrator & 0xff) == FF_INTEGRATOR_AS_CODED) {
         if (stats) memset(stats, 0, sizeof(*stats));
         ScopedTimer t(c, 0, 1);
         k_as_coded(scene->dev, make_cam(cam), d_rgb, c->stream);

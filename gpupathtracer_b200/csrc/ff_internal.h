@@ -116,7 +116,8 @@ struct WaveBuffers {
     uint32_t capacity;     // paths per pass
 };
 void k_wavefront_pass(const DevScene& sc, const CamDev& cam, const RenderDev& rp, const WaveBuffers& wb, int trace_mode,
-                      uint32_t* launches, cudaEvent_t* trace_events, int* n_trace_events, cudaStream_t st);
+                      TraceCounters* d_counters, uint32_t* launches, cudaEvent_t* trace_events, int* n_trace_events,
+                      cudaStream_t st);
 void k_megakernel_pass(const DevScene& sc, const CamDev& cam, const RenderDev& rp, float4* d_radiance,
                        uint32_t* d_work_counter, unsigned long long* d_ray_counter, uint32_t* launches, cudaStream_t st);
 void k_accumulate_pass(const float4* d_radiance, uint32_t npix, uint32_t samples, float4* d_accum, cudaStream_t st);

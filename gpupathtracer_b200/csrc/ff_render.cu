@@ -146,7 +146,8 @@ void k_trace_closest(const DevScene& sc, const float4* d_ray_o, const float4* d_
                      uint32_t n_max, int mode, HitRec* d_hits, TraceCounters* d_counters, cudaStream_t st);
 
 void k_wavefront_pass(const DevScene& sc, const CamDev& cam, const RenderDev& rp, const WaveBuffers& wb, int trace_mode,
-                      uint32_t* launches, cudaEvent_t* trace_events, int* n_trace_events, cudaStream_t st) {
+                      TraceCounters* d_counters, uint32_t* launches, cudaEvent_t* trace_events, int* n_trace_events,
+                      cudaStream_t st) {
     const uint32_t n = rp.samples * rp.npix;
     const int n_counts = rp.max_bounces + 2;
     wf_raygen_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(cam, rp, wb.ray_o[0], wb.ray_d[0], wb.beta[0], wb.radiance, wb.counts, n_counts);
@@ -154,7 +155,7 @@ void k_wavefront_pass(const DevScene& sc, const CamDev& cam, const RenderDev& rp
     for (int b = 0; b <= rp.max_bounces; ++b) {
         const int in = b & 1, out = in ^ 1;
         if (trace_events) cudaEventRecord(trace_events[(*n_trace_events)++], st);
-        k_trace_closest(sc, wb.ray_o[in], wb.ray_d[in], wb.counts + b, n, trace_mode, wb.hits, nullptr, st);
+        k_trace_closest(sc, wb.ray_o[in], wb.ray_d[in], wb.counts + b, n, trace_mode, wb.hits, d_counters, st);
         if (trace_events) cudaEventRecord(trace_events[(*n_trace_events)++], st);
         wf_shade_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(sc, rp, b, wb.counts + b, n, wb.hits, wb.ray_o[in], wb.ray_d[in],
                                                                    wb.beta[in], wb.ray_o[out], wb.ray_d[out], wb.beta[out],

@@ -64,7 +64,7 @@ typedef struct ff_render_params {
     int spp;                 /* samples per pixel rendered by THIS call */
     int max_bounces;         /* path segments = max_bounces + 1 */
     uint64_t seed;           /* Philox key {lo, hi}; the reference's constant is 1234 (utilities.h:118) */
-    int integrator;          /* FF_INTEGRATOR_* */
+    int integrator;          /* FF_INTEGRATOR_*, optionally OR FF_TRACE_COUNT (instrumented extend kernels) */
     int nee;                 /* next-event estimation with shadow rays (0 = plain loop) */
     int first_sample;        /* global index of the first sample (multi-GPU sample split, resume) */
     int aa;                  /* 0: integer pixel corner like kernel.cu:200-201; 1: Philox jitter */
@@ -142,8 +142,9 @@ int ff_scene_get_matrices(const ff_scene* scene, int geometry_index, float model
 #define FF_TRACE_COUNT 0x100 /* OR into `mode`: instrumented kernel, fills nodes_visited / tris_tested */
 int ff_trace_closest(ff_scene* scene, const float* rays6, size_t n, int mode, int* out_geom, int* out_tri,
                      float* out_t, ff_stats* stats);
-/* Same with device-resident buffers (no copies): d_rays = n x 2 float4 {o.xyz,0},{d.xyz,0};
- * d_hits = n x int4-sized records {key t (f32 bits), t along the ray (f32 bits), triangle slot, flat id}. */
+/* Same with device-resident buffers (no copies): d_rays = 2n float4, SoA: n origins {o.xyz, 0} followed by
+ * n directions {d.xyz, 0}; d_hits = n 16-byte records {key t (f32), t along the ray (f32), triangle slot
+ * (i32), scan-order id (i32)} -- see ff_hits_unpack. */
 int ff_trace_closest_device(ff_scene* scene, const void* d_rays, size_t n, int mode, void* d_hits,
                             ff_stats* stats);
 /* Any-hit (occlusion) query: out_occluded[i] = 1 when a front-facing triangle is hit with key < tmax[i]. */

@@ -1,0 +1,245 @@
+"""GPU: closest-hit parity of the CUDA path (through the C ABI) against the CPU oracle -- bit-exact geometryIndex,
+triangleIndex and key t -- on the reference's scenes, on edge cases, and on synthetic soups (oracle on a ray subset,
+GPU brute force as the bridge at full size)."""
+import numpy as np
+import pytest
+
+from conftest import assert_hits_equal, bits
+from gpupathtracer_b200 import scenes as S
+
+pytestmark = pytest.mark.gpu
+MODES = ["BVH8", "BVH2", "BRUTE"]
+
+
+def mode_of(ff, name):
+    return {"BVH8": ff.TRACE_BVH8, "BVH2": ff.TRACE_BVH2, "BRUTE": ff.TRACE_BRUTE}[name]
+
+
+def random_rays(rng, lo, hi, n, normalise=True):
+    o = rng.uniform(lo - 0.5 * (hi - lo) - 0.1, hi + 0.5 * (hi - lo) + 0.1, (n, 3)).astype(np.float32)
+    tgt = rng.uniform(lo, hi, (n, 3)).astype(np.float32)
+    d = (tgt - o).astype(np.float32)
+    if normalise:
+        d = (d / np.maximum(np.linalg.norm(d, axis=1, keepdims=True), 1e-12)).astype(np.float32)
+    return np.concatenate([o, d], 1).astype(np.float32)
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_golden_identity_scenes(ff, ctx, golden, meshes, mode):
+    """Straight against the reference's own outputs (tests/golden/ref_identity.npz)."""
+    g = golden("ref_identity.npz")
+    for name in ("rocketman", "wahoo", "cube", "sphereBlender"):
+        sc = ctx.scene()
+        sc.add_triangles(meshes[name])
+        if name == "wahoo":
+            sc.add_triangles(meshes["sphere"])
+        sc.commit()
+        got = sc.trace_closest(g[name + "_rays"], mode_of(ff, mode))
+        want = {k: g[name + "_" + k] for k in ("geom", "tri", "t")}
+        assert_hits_equal(got, want, "%s %s" % (name, mode))
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("cfg", ["C1", "C2", "C3", "main"])
+def test_config_scenes_vs_oracle(ff, ctx, orc, meshes, golden, cfg, mode):
+    desc = {"C1": S.config1(), "C2": S.config2(meshes, 160, 160), "C3": S.config3(meshes, 192, 108),
+            "main": S.reference_main(128, 128)}[cfg]
+    sc, cam = S.instantiate(desc, ctx, meshes)
+    osc = S.instantiate_on(desc, orc.scene(), meshes)
+    rays = ctx.camera_rays(cam)
+    orays, _ = orc.camera_rays(desc["camera"])
+    assert (bits(rays) == bits(orays)).all()
+    flat, fg, ft = sc.flat()
+    oflat, og, ot = osc.flat()
+    assert (bits(flat) == bits(oflat)).all() and (fg == og).all() and (ft == ot).all()
+    lo, hi = flat.reshape(-1, 3).min(0), flat.reshape(-1, 3).max(0)
+    rng = np.random.default_rng({"C1": 1, "C2": 2, "C3": 3, "main": 4}[cfg])
+    extra = np.concatenate([random_rays(rng, lo, hi, 20000), random_rays(rng, lo, hi, 2000, normalise=False)])
+    allrays = np.concatenate([orays, extra])
+    want = osc.intersect(allrays, mode=1)
+    got = sc.trace_closest(allrays, mode_of(ff, mode))
+    assert_hits_equal(got, want, "%s %s" % (cfg, mode))
+    assert want["hit"].sum() > 1000
+    if cfg == "C1":  # and against the reference's own object-space path: same ids, t within 1e-5 relative
+        g = golden("ref_c1.npz")
+        n = len(g["rays"])
+        assert (got["geom"][:n] == g["geom"]).all() and (got["tri"][:n] == g["tri"]).all()
+        h = g["hit"].astype(bool)
+        assert np.allclose(got["t"][:n][h], g["t"][h], rtol=1e-5, atol=0)
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_ties_lowest_index_wins(ff, ctx, orc, meshes, mode):
+    """The same mesh twice, and shared edges / vertices: strict '<' in scan order means the lowest (geometry, triangle) wins."""
+    sc, osc = ctx.scene(), orc.scene()
+    for s in (sc, osc):
+        (s.add_triangles if s is sc else s.add_mesh)(meshes["sphereBlender"])
+        (s.add_triangles if s is sc else s.add_mesh)(meshes["cube"])
+        (s.add_triangles if s is sc else s.add_mesh)(meshes["sphereBlender"])
+        (s.add_triangles if s is sc else s.add_mesh)(meshes["cube"])
+    sc.commit()
+    rng = np.random.default_rng(4)
+    rays = random_rays(rng, np.float32([-1, -1, -1]), np.float32([1, 1, 1]), 30000)
+    # rays aimed exactly at mesh vertices and edge midpoints
+    v = meshes["sphereBlender"].reshape(-1, 3, 3)
+    targets = np.concatenate([v[:, 0], 0.5 * (v[:, 0] + v[:, 1]), meshes["cube"].reshape(-1, 3, 3)[:, 0],
+                              0.5 * (meshes["cube"].reshape(-1, 3, 3)[:, 0] + meshes["cube"].reshape(-1, 3, 3)[:, 1])]).astype(np.float32)
+    o = (targets * 3 + np.float32([0.01, 0.02, 0.03])).astype(np.float32)
+    d = (targets - o).astype(np.float32)
+    rays = np.concatenate([rays, np.concatenate([o, d], 1)])
+    want = osc.intersect(rays, mode=1)
+    got = sc.trace_closest(rays, mode_of(ff, mode))
+    assert_hits_equal(got, want, "ties " + mode)
+    assert set(np.unique(got["geom"])) <= {-1, 0, 1}  # duplicates (geometries 2, 3) never win
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_edge_cases(ff, ctx, orc, meshes, mode):
+    m = mode_of(ff, mode)
+    rng = np.random.default_rng(8)
+    rays = random_rays(rng, np.float32([-1, -1, -1]), np.float32([1, 1, 1]), 4096)
+    axis = np.zeros((6, 6), np.float32)  # axis-parallel rays with exact zeros in the direction
+    for k in range(6):
+        axis[k, k % 3] = -3 if k < 3 else 3
+        axis[k, 3 + k % 3] = 1 if k < 3 else -1
+    rays = np.concatenate([rays, axis, np.float32([[0, 0, 0, 0, 0, 0]]), np.float32([[np.nan, 0, 0, 1, 0, 0]])])
+    # empty scene, and empty batch
+    sc = ctx.scene()
+    sc.commit()
+    r = sc.trace_closest(rays, m)
+    assert (r["geom"] == -1).all() and np.isinf(r["t"]).all()
+    assert len(sc.trace_closest(np.zeros((0, 6), np.float32), m)["geom"]) == 0
+    # 1..9 triangles (tiny trees), degenerate triangles mixed in
+    for n in (1, 2, 3, 4, 5, 9):
+        tris = meshes["cube"][:n].copy()
+        if n >= 4:
+            tris[1, 3:6] = tris[1, 0:3]  # zero-area triangle
+        sc, osc = ctx.scene(), orc.scene()
+        sc.add_triangles(tris)
+        osc.add_mesh(tris)
+        sc.commit()
+        assert_hits_equal(sc.trace_closest(rays, m), osc.intersect(rays, mode=1), "n=%d %s" % (n, mode))
+    # all triangles identical (Morton duplicates), and a mesh far from the origin with a large extent
+    same = np.repeat(meshes["triangle"], 300, 0)
+    big = (meshes["sphereBlender"] * 500 + 2000).astype(np.float32)
+    for tris, lo, hi in ((same, np.float32([0, 0, -1]), np.float32([1, 1, 1])), (big, np.float32([1500] * 3), np.float32([2500] * 3))):
+        sc, osc = ctx.scene(), orc.scene()
+        sc.add_triangles(tris)
+        osc.add_mesh(tris)
+        sc.commit()
+        rr = random_rays(rng, lo, hi, 8192)
+        want = osc.intersect(rr, mode=1)
+        assert_hits_equal(sc.trace_closest(rr, m), want, mode)
+        assert want["hit"].sum() > 100
+
+
+def test_transforms_match_oracle(ff, ctx, orc, meshes, golden):
+    mats = golden("ref_matrices.npz")
+    sc, osc = ctx.scene(), orc.scene()
+    for trs in mats["trs"]:
+        sc.add_triangles(meshes["sphere"], trs[0], trs[1], trs[2])
+        osc.add_mesh(meshes["sphere"], trs[0], trs[1], trs[2])
+    sc.commit()
+    for gi, want in enumerate(mats["mats"]):
+        m, inv = sc.matrices(gi)
+        assert (bits(np.concatenate([m, inv])) == bits(want)).all()
+    flat, _, _ = sc.flat()
+    oflat, _, _ = osc.flat()
+    assert (bits(flat) == bits(oflat)).all()
+    rng = np.random.default_rng(12)
+    rays = random_rays(rng, flat.reshape(-1, 3).min(0), flat.reshape(-1, 3).max(0), 20000)
+    assert_hits_equal(sc.trace_closest(rays), osc.intersect(rays, mode=1), "transformed spheres")
+
+
+@pytest.mark.parametrize("n_tris", [20000, 200000])
+def test_soup_vs_oracle_and_bridge(ff, ctx, orc, n_tris):
+    """Config-4 generator at reduced size: generators bit-identical to the oracle's, BVH == oracle on a subset,
+    BVH == GPU brute force on a larger batch."""
+    soup = ctx.make_soup(n_tris)
+    assert (bits(soup) == bits(orc.make_soup(n_tris))).all()
+    rays = ctx.make_rays_uniform(0, 1 << 17)
+    assert (bits(rays[:8192]) == bits(orc.make_rays_uniform(0, 8192))).all()
+    assert (bits(ctx.make_rays_uniform(5000, 100, salt=3)) == bits(orc.make_rays_uniform(5000, 100, salt=3))).all()
+    sc, osc = ctx.scene(), orc.scene()
+    sc.add_triangles(soup)
+    osc.add_mesh(soup)
+    sc.commit()
+    info = sc.info()
+    assert info["n_triangles"] == n_tris and info["n_nodes"] > 0 and info["depth"] <= 64
+    sub = rays[:4096 if n_tris <= 20000 else 1024]
+    want = osc.intersect(sub, mode=1)
+    for mode in (ff.TRACE_BVH8, ff.TRACE_BVH2, ff.TRACE_BRUTE):
+        assert_hits_equal(sc.trace_closest(sub, mode), want, "soup subset")
+    nb = 1 << 17 if n_tris <= 20000 else 1 << 15
+    brute = sc.trace_closest(rays[:nb], ff.TRACE_BRUTE)
+    assert_hits_equal(sc.trace_closest(rays[:nb], ff.TRACE_BVH8), brute, "bvh8 vs brute")
+    assert_hits_equal(sc.trace_closest(rays[:nb], ff.TRACE_BVH2), brute, "bvh2 vs brute")
+    assert 0.5 < brute["hit"].mean() <= 1.0
+
+
+def test_full_size_config4_properties(ff, ctx):
+    """BASELINE config 4 at full size (1M triangles): properties that need no oracle -- the two hierarchies agree on
+    every ray, results are independent of batch order, and a hit's t reproduces from (ray, triangle)."""
+    n = 1000000
+    soup = ctx.make_soup(n)
+    sc = ctx.scene()
+    sc.add_triangles(soup)
+    sc.commit()
+    nr = 1 << 20
+    rays = ctx.make_rays_uniform(0, nr)
+    a = sc.trace_closest(rays, ff.TRACE_BVH8)
+    b = sc.trace_closest(rays, ff.TRACE_BVH2)
+    assert_hits_equal(a, b, "bvh8 vs bvh2 at 1M")
+    perm = np.random.default_rng(0).permutation(nr)
+    c = sc.trace_closest(rays[perm], ff.TRACE_BVH8)
+    assert (c["tri"] == a["tri"][perm]).all() and (bits(c["t"]) == bits(a["t"][perm])).all()
+    brute = sc.trace_closest(rays[:4096], ff.TRACE_BRUTE)
+    assert_hits_equal({k: v[:4096] for k, v in a.items()}, brute, "bvh8 vs brute at 1M")
+    h = a["geom"] >= 0
+    assert 0.9 < h.mean()
+    # geometric check of t in float64 against the hit triangle's plane
+    idx = np.nonzero(h)[0][:50000]
+    tri = soup[a["tri"][idx]].astype(np.float64).reshape(-1, 3, 3)
+    nrm = np.cross(tri[:, 1] - tri[:, 0], tri[:, 2] - tri[:, 0])
+    o, d = rays[idx, :3].astype(np.float64), rays[idx, 3:].astype(np.float64)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    t = np.einsum("ij,ij->i", tri[:, 0] - o, nrm) / np.einsum("ij,ij->i", d, nrm)
+    assert np.abs(t - a["t"][idx]).max() < 1e-4
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_any_hit_consistent_with_closest(ff, ctx, meshes, mode):
+    desc = S.config2(meshes, 64, 64)
+    sc, cam = S.instantiate(desc, ctx, meshes)
+    rng = np.random.default_rng(6)
+    rays = random_rays(rng, np.float32([-2.5] * 3), np.float32([2.5] * 3), 20000)
+    m = mode_of(ff, mode)
+    closest = sc.trace_closest(rays, m)
+    assert (sc.trace_any(rays, None, m) == (closest["geom"] >= 0)).all()
+    tmax = rng.uniform(0.1, 6, len(rays)).astype(np.float32)
+    occ = sc.trace_any(rays, tmax, m)
+    assert (occ == (closest["t"] < tmax)).all()
+
+
+def test_instrumented_counts_and_device_entry(ff, ctx):
+    soup = ctx.make_soup(50000)
+    sc = ctx.scene()
+    sc.add_triangles(soup)
+    sc.commit()
+    n = 1 << 16
+    d_rays, d_hits = ctx.alloc(n * 32), ctx.alloc(n * 16)
+    host = ctx.make_rays_uniform(0, n, device_buffer=d_rays)
+    st = sc.trace_closest_device(d_rays, n, d_hits, ff.TRACE_BVH8 | ff.TRACE_COUNT)
+    assert st["rays"] == n and st["nodes_visited"] > n and st["tris_tested"] > 0 and st["gpu_ms"] > 0
+    got = sc.hits_unpack(d_hits, n)
+    assert_hits_equal(got, sc.trace_closest(host, ff.TRACE_BVH8), "device entry vs host entry")
+    sb = sc.trace_closest_device(d_rays, n, d_hits, ff.TRACE_BRUTE | ff.TRACE_COUNT)
+    assert sb["tris_tested"] == n * 50000
+    # bounce batch: cosine-hemisphere rays leaving the hits
+    st = sc.trace_closest_device(d_rays, n, d_hits, ff.TRACE_BVH8)
+    d_out = ctx.alloc(n * 32)
+    nb = sc.make_rays_bounce(d_rays, d_hits, n, 77, d_out)
+    assert nb == int((got["geom"] >= 0).sum())
+    out = d_out.download(np.float32, nb * 8).reshape(2, nb, 4)
+    assert np.allclose(np.linalg.norm(out[1, :, :3], axis=1), 1, atol=1e-5)
+    assert (out[0, :, :3] > -0.1).all() and (out[0, :, :3] < 1.1).all()

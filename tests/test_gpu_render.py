@@ -1,0 +1,116 @@
+"""GPU: the integrators against the CPU oracle's as-intended path tracer (same Philox stream, same operation order,
+samples summed in index order) -- the images are required to be BIT-IDENTICAL on one GPU, which is far inside the
+per-pixel RMSE <= 1e-3 the north star asks for -- plus the as-coded normal frame, sample splitting and u8 output."""
+import numpy as np
+import pytest
+
+from conftest import bits
+from gpupathtracer_b200 import multigpu as M
+from gpupathtracer_b200 import scenes as S
+
+pytestmark = pytest.mark.gpu
+
+
+def descs(meshes):
+    return {"C1": S.config1(96, 96), "C2": S.config2(meshes, 72, 72, 6, 4), "C3": S.config3(meshes, 96, 54, 5, 8)}
+
+
+@pytest.mark.parametrize("cfg", ["C1", "C2", "C3"])
+@pytest.mark.parametrize("aa", [0, 1])
+def test_wavefront_and_megakernel_bit_identical_to_oracle(ff, ctx, orc, meshes, cfg, aa):
+    desc = descs(meshes)[cfg]
+    sc, cam = S.instantiate(desc, ctx, meshes)
+    osc = S.instantiate_on(desc, orc.scene(), meshes)
+    bg = (0.1, 0.2, 0.3) if cfg == "C1" else (0, 0, 0)
+    want, want_rays = osc.render(desc["camera"], desc["spp"], desc["max_bounces"], seed=1234, aa=aa, background=bg)
+    for integ in (ff.INTEGRATOR_WAVEFRONT, ff.INTEGRATOR_MEGAKERNEL):
+        got, st = sc.render(cam, desc["spp"], desc["max_bounces"], want_stats=True, integrator=integ, seed=1234, aa=aa, background=bg)
+        assert (bits(got) == bits(want)).all(), "%s integrator %d: max abs diff %g" % (cfg, integ, np.abs(got - want).max())
+        assert st["rays"] == want_rays and st["paths"] == desc["spp"] * cam.width * cam.height
+        rmse = float(np.sqrt(np.mean((got[..., :3] - want[..., :3]) ** 2)))
+        assert rmse <= 1e-3  # the stated tolerance (trivially met: the images are identical)
+    assert want[..., :3].max() > 0
+
+
+def test_samples_per_pass_and_seed(ff, ctx, orc, meshes):
+    desc = descs(meshes)["C2"]
+    sc, cam = S.instantiate(desc, ctx, meshes)
+    base = sc.render(cam, 6, 4, seed=99)
+    for spb in (1, 2, 4, 6):
+        assert (bits(sc.render(cam, 6, 4, seed=99, samples_per_pass=spb)) == bits(base)).all()
+        assert (bits(sc.render(cam, 6, 4, seed=99, samples_per_pass=spb, integrator=ff.INTEGRATOR_MEGAKERNEL)) == bits(base)).all()
+    other = sc.render(cam, 6, 4, seed=100)
+    assert (other != base).any()
+    big_seed = (0xABCDEF01 << 32) | 0x12345678
+    osc = S.instantiate_on(desc, orc.scene(), meshes)
+    want, _ = osc.render(desc["camera"], 2, 4, seed=big_seed)
+    assert (bits(sc.render(cam, 2, 4, seed=big_seed)) == bits(want)).all()
+
+
+def test_sample_split_matches_full_render(ff, ctx, meshes):
+    """What the multi-GPU path does, on one GPU: disjoint sample ranges accumulated separately, reduced in rank order."""
+    desc = descs(meshes)["C2"]
+    sc, cam = S.instantiate(desc, ctx, meshes)
+    spp, world = 8, 4
+    full = sc.render(cam, spp, 4)
+    npix = cam.width * cam.height
+    bufs, partial = [], []
+    for r in range(world):
+        first, count = M.sample_range(r, world, spp)
+        buf = ctx.alloc(npix * 16)
+        buf.zero()
+        sc.render_accumulate(cam, buf, count, 4, first_sample=first)
+        bufs.append(buf)
+        partial.append(buf.download(np.float32, npix * 4).reshape(cam.height, cam.width, 4))
+    want = M.combine_sums(partial, spp)
+    got = ctx.reduce_resolve_peers([b.ptr.value for b in bufs], cam.width, cam.height, spp)
+    assert (bits(got) == bits(want)).all()  # fused reduce+resolve == host statement, bit for bit
+    assert np.abs(got[..., :3] - full[..., :3]).max() <= 1e-5 * max(1.0, float(full.max()))  # vs in-order sum: fp32 re-association only
+    # resuming: accumulate the second half into the first half's buffer == one render of all samples, bit for bit
+    buf = ctx.alloc(npix * 16)
+    buf.zero()
+    sc.render_accumulate(cam, buf, 4, 4, first_sample=0)
+    sc.render_accumulate(cam, buf, 4, 4, first_sample=4)
+    assert (bits(ctx.resolve(buf, cam.width, cam.height, spp)) == bits(full)).all()
+
+
+@pytest.mark.parametrize("cfg", ["C1", "C2", "C3", "main"])
+def test_as_coded_frame(ff, ctx, orc, meshes, golden, cfg):
+    desc = dict(descs(meshes), main=S.reference_main(160, 160))[cfg]
+    sc, cam = S.instantiate(desc, ctx, meshes)
+    osc = S.instantiate_on(desc, orc.scene(), meshes)
+    got = sc.render_u8(cam)
+    assert (got == osc.render_as_coded(desc["camera"], mode=1)).all()
+    if cfg == "main":  # against the reference's own frame: same pixels hit; colours within one level where the
+        g = golden("ref_main.npz")["as_coded"]  # mesh is only rotated (baked normal vs inverse-transpose normal)
+        assert ((got.sum(-1) > 0) == (g.sum(-1) > 0)).all()
+        assert np.abs(got.astype(int) - g.astype(int)).max() <= 1
+
+
+def test_render_u8_and_device_output(ff, ctx, meshes):
+    desc = descs(meshes)["C2"]
+    sc, cam = S.instantiate(desc, ctx, meshes)
+    img = sc.render(cam, 4, 4)
+    u8 = sc.render_u8(cam, 4, 4, integrator=ff.INTEGRATOR_WAVEFRONT)
+    want = (np.clip(img[..., :3], 0, 1) * np.float32(255)).astype(np.uint8)
+    assert (u8 == want).all()
+    d_out = ctx.alloc(cam.width * cam.height * 16)
+    sc.render(cam, 4, 4, host=False, device_out=d_out)
+    assert (bits(d_out.download(np.float32, cam.width * cam.height * 4)) == bits(img).ravel()).all()
+
+
+def test_errors(ff, ctx, meshes):
+    sc = ctx.scene()
+    sc.add_triangles(meshes["cube"])
+    cam = ff.Camera(width=8, height=8)
+    with pytest.raises(ff.FireflyError):
+        sc.render(cam, 1, 1)  # not committed
+    sc.commit()
+    with pytest.raises(ff.FireflyError):
+        sc.render(cam, 0, 1)
+    with pytest.raises(ff.FireflyError):
+        sc.render(cam, 1, 1, nee=1)
+    with pytest.raises(ff.FireflyError):
+        sc.trace_closest(np.zeros((4, 6), np.float32), mode=77)
+    with pytest.raises(ff.FireflyError):
+        ff.Context(10 ** 6)

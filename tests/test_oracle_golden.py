@@ -1,0 +1,166 @@
+"""CPU: the oracle restatement (oracle/firefly_oracle.cpp) against the golden vectors that tools/make_golden.py
+produced from the reference's own routine text (oracle/_ref), and -- where that library is present -- against it live.
+This is what pins the oracle; the GPU parity tests then compare the CUDA path with the oracle."""
+import numpy as np
+import pytest
+
+from conftest import assert_hits_equal, bits
+from gpupathtracer_b200 import scenes as S
+
+
+def test_triangle_known_answers(orc, golden):
+    g = golden("kat_triangle.npz")
+    n = len(g["hit"])
+    assert n > 2000 and g["hit"].sum() > 100
+    for i in range(n):
+        hit, t, p, nn = orc.intersect_triangle(g["v9"][i], g["o"][i], g["d"][i])
+        assert hit == bool(g["hit"][i]), i
+        if hit:
+            assert bits(t) == bits(g["t"][i]), i
+            assert (bits(p) == bits(g["point"][i])).all(), i
+            assert (bits(nn) == bits(g["normal"][i])).all(), i
+    # analytic pins: front hit at t=1, back face culled, inclusive edges
+    assert g["hit"][0] == 1 and g["t"][0] == 1.0
+    assert g["hit"][1] == 0
+    assert g["hit"][2] == 1 and g["hit"][3] == 1 and g["hit"][4] == 1 and g["hit"][5] == 1
+    assert g["hit"][6] == 0
+
+
+@pytest.mark.parametrize("name", ["rocketman", "wahoo", "cube", "sphereBlender"])
+def test_identity_scenes_bit_exact(orc, golden, meshes, name):
+    g = golden("ref_identity.npz")
+    sc = orc.scene()
+    sc.add_mesh(meshes[name])
+    if name == "wahoo":
+        sc.add_mesh(meshes["sphere"])
+    want = {k: g[name + "_" + k] for k in ("hit", "geom", "tri", "t", "point", "normal")}
+    for mode in (0, 1):  # the reference's object-space path, and the baked path the GPU implements
+        got = sc.intersect(g[name + "_rays"], mode=mode)
+        assert_hits_equal(got, want, "%s mode %d" % (name, mode))
+        assert (got["hit"] == want["hit"]).all()
+        h = want["hit"].astype(bool)
+        assert (bits(got["point"][h]) == bits(want["point"][h])).all()
+        if mode == 0:
+            assert (bits(got["normal"][h]) == bits(want["normal"][h])).all()
+        else:  # baked mode skips the multiply by inverse(transpose(I)), which turns -0 into +0: same values
+            assert (got["normal"][h] == want["normal"][h]).all()
+
+
+def test_cube_semantics(orc, meshes):
+    """Back-face culling pin: from outside exactly the front faces are visible, from inside nothing."""
+    sc = orc.scene()
+    sc.add_mesh(meshes["cube"])
+    rng = np.random.default_rng(1)
+    d = rng.normal(size=(512, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    inside = np.concatenate([np.zeros((512, 3), np.float32), d], 1)
+    assert sc.intersect(inside)["hit"].sum() == 0
+    outside = np.concatenate([-3 * d, d], 1).astype(np.float32)
+    r = sc.intersect(outside)
+    assert r["hit"].all()
+    assert np.allclose(r["t"], np.linalg.norm(r["point"] + 3 * d, axis=1), rtol=1e-5)
+
+
+def test_config1_reference_path(orc, golden, meshes):
+    """Config 1 has a translated triangle: mode 0 (object-space, the reference's own path) must be bit-exact; the baked
+    mode the GPU uses must give the same ids and t within 1e-5 relative (BASELINE.json north_star)."""
+    g = golden("ref_c1.npz")
+    desc = S.config1()
+    sc = S.instantiate_on(desc, orc.scene(), meshes)
+    rays, _ = orc.camera_rays(desc["camera"])
+    assert (bits(rays) == bits(g["rays"])).all()
+    got0 = sc.intersect(rays, mode=0)
+    assert_hits_equal(got0, g, "C1 mode 0")
+    got1 = sc.intersect(rays, mode=1)
+    assert (got1["geom"] == g["geom"]).all() and (got1["tri"] == g["tri"]).all()
+    h = g["hit"].astype(bool)
+    assert np.allclose(got1["t"][h], g["t"][h], rtol=1e-5, atol=0)
+    assert (sc.render_as_coded(desc["camera"], mode=0) == g["as_coded"]).all()
+
+
+def test_main_scene_with_planes(orc, golden, meshes):
+    g = golden("ref_main.npz")
+    desc = S.reference_main(160, 160)
+    sc = S.instantiate_on(desc, orc.scene(), meshes)
+    got = sc.intersect(g["rays"], mode=0)
+    assert_hits_equal(got, g, "main() scene mode 0")
+    assert (sc.render_as_coded(desc["camera"], mode=0) == g["as_coded"]).all()
+    got1 = sc.intersect(g["rays"], mode=1)
+    assert (got1["geom"] == g["geom"]).all() and (got1["tri"] == g["tri"]).all()
+    h = g["hit"].astype(bool)
+    assert np.allclose(got1["t"][h], g["t"][h], rtol=1e-5)
+
+
+def test_camera_and_matrices(orc, golden):
+    g = golden("ref_camera.npz")
+    for i in range(3):
+        c = g["cam%d" % i]
+        cam = S.camera(c[0:3], yaw=c[3], pitch=c[4], fov=c[5], width=int(c[6]), height=int(c[7]), near=c[8], far=c[9])
+        rays, basis = orc.camera_rays(cam)
+        iv, ip = orc.camera_inverse_matrices(cam)
+        assert (bits(rays) == bits(g["rays%d" % i])).all()
+        assert (bits(basis) == bits(g["basis%d" % i])).all()
+        assert (bits(iv) == bits(g["iv%d" % i])).all() and (bits(ip) == bits(g["ip%d" % i])).all()
+    m = golden("ref_matrices.npz")
+    tri = np.array([[0, 0, 0, 1, 0, 0, 0, 1, 0]], np.float32)
+    for trs, want in zip(m["trs"], m["mats"]):
+        sc = orc.scene()
+        gi = sc.add_mesh(tri, trs[0], trs[1], trs[2])
+        mm, inv = sc.matrices(gi)
+        assert (bits(np.concatenate([mm, inv])) == bits(want)).all()
+
+
+def test_philox_known_answers(orc):
+    """Random123 kat_vectors for philox4x32_10."""
+    kats = [((0, 0, 0, 0), (0, 0), (0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8)),
+            ((0xffffffff,) * 4, (0xffffffff,) * 2, (0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd)),
+            ((0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344), (0xa4093822, 0x299f31d0), (0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1))]
+    for ctr, key, want in kats:
+        assert tuple(int(x) for x in orc.philox(ctr, key)) == want
+
+
+def test_sampling_primitives(orc):
+    u = np.linspace(0, 1, 4097, dtype=np.float32)[:-1]
+    s, c = orc.sincos2pi(u)
+    assert np.abs(s - np.sin(2 * np.pi * u.astype(np.float64))).max() < 2e-7
+    assert np.abs(c - np.cos(2 * np.pi * u.astype(np.float64))).max() < 2e-7
+    rng = np.random.default_rng(3)
+    for _ in range(200):
+        n = rng.normal(size=3)
+        n = (n / np.linalg.norm(n)).astype(np.float32)
+        t, b = orc.onb(n)
+        assert abs(np.dot(t, b)) < 1e-6 and abs(np.dot(t, n)) < 1e-6 and abs(np.dot(b, n)) < 1e-6
+        assert abs(np.linalg.norm(t) - 1) < 1e-6 and abs(np.linalg.norm(b) - 1) < 1e-6
+    w = orc.cosine_sample_hemisphere(0.25, 0.125)
+    assert abs(np.linalg.norm(w) - 1) < 1e-6 and w[2] > 0
+
+
+def test_oracle_vs_reference_live(orc, ref, meshes):
+    """Where oracle/_ref is present: fresh random rays, restatement vs the reference's own text, bit for bit."""
+    rng = np.random.default_rng(99)
+    desc = S.reference_main(64, 64)
+    a = S.instantiate_on(desc, orc.scene(), meshes)
+    b = S.instantiate_on(desc, ref.scene(), meshes)
+    o = rng.uniform(-6, 6, (3000, 3)).astype(np.float32)
+    d = rng.normal(size=(3000, 3)).astype(np.float32)
+    rays = np.concatenate([o, d], 1)  # un-normalised directions on purpose
+    assert_hits_equal(a.intersect(rays, mode=0), b.intersect(rays), "live main()")
+    assert (a.render_as_coded(desc["camera"], mode=0) == b.render_as_coded(desc["camera"])).all()
+
+
+def test_path_tracer_properties(orc, meshes):
+    """The as-intended tracer (no reference counterpart): furnace test and determinism."""
+    cube = S.flip_winding(meshes["cube"])
+    sc = orc.scene()
+    sc.add_mesh(cube, scale=(4, 4, 4), material=dict(type=1, albedo=(1, 1, 1)))
+    cam = S.camera((0, 0, 0), fov=60, width=8, height=8)
+    img, n = sc.render(cam, 4, 3, background=(1, 1, 1))
+    assert (img[..., :3] == 0).all()  # closed box, no light, paths die at max bounce without contribution
+    sc2 = orc.scene()
+    sc2.add_mesh(cube, scale=(4, 4, 4), material=dict(type=0, emissive=(1, 0.5, 0.25), intensity=2.0))
+    img2, n2 = sc2.render(cam, 2, 3)
+    assert np.allclose(img2[..., :3], [2, 1, 0.5]) and n2 == 8 * 8 * 2
+    a, _ = sc.render(cam, 4, 3, seed=7)
+    b, _ = sc.render(cam, 2, 3, seed=7)
+    c, _ = sc.render(cam, 2, 3, seed=7, first_sample=2)
+    assert np.allclose(a, (b + c) / 2, atol=1e-6)

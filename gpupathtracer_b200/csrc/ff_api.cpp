@@ -325,7 +325,7 @@ int ff_scene_commit(ff_scene* scene, int builder, double* out_build_ms) {
         float ms = 0;
         FF_CUDA(cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]));
         build_ms = ms;
-        FF_REQUIRE(bo.depth <= FF_MAX_WIDE_DEPTH, "ff_scene_commit: hierarchy deeper than the traversal stack");
+        FF_REQUIRE(2 * bo.depth <= FF_MAX_WIDE_DEPTH, "ff_scene_commit: hierarchy deeper than the traversal stack (postponed triangle groups share it)");
     }
     FF_CUDA(cudaStreamSynchronize(st));
 

@@ -279,11 +279,18 @@ __global__ void hierarchy_kernel(const uint32_t* __restrict__ keys, int n, int2*
     }
 }
 
+#define FF_COUNT_MASK 0x3fffffff
+#define FF_PREFER_OPEN 0x40000000
+#define FF_SLOT_COST 0.25f   // cost of one more child slot (box test + share of the node fetch) in triangle tests
+__device__ __forceinline__ float box_area_lohi(const float4& lo, const float4& hi) {
+    const float dx = hi.x - lo.x, dy = hi.y - lo.y, dz = hi.z - lo.z;
+    return 2.0f * (dx * dy + dy * dz + dz * dx);
+}
 // ------------------------------------------------------------------ bottom-up refit
 // lo.w = triangle count (int bits), hi.w = first sorted position (int bits)
 __global__ void refit_kernel(const float4* __restrict__ flat_tris, const uint32_t* __restrict__ sorted_idx, int n, float pad,
                              const int2* __restrict__ children, const uint32_t* __restrict__ parent, uint32_t* __restrict__ flags,
-                             float4* __restrict__ box_lo, float4* __restrict__ box_hi) {
+                             float4* __restrict__ box_lo, float4* __restrict__ box_hi, float* __restrict__ cost) {
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
         const uint32_t src = sorted_idx[k];
         const float4 a = flat_tris[3 * (size_t)src], b = flat_tris[3 * (size_t)src + 1], c = flat_tris[3 * (size_t)src + 2];
@@ -292,6 +299,7 @@ __global__ void refit_kernel(const float4* __restrict__ flat_tris, const uint32_
         uint32_t node = (uint32_t)(n - 1 + k);
         box_lo[node] = lo;
         box_hi[node] = hi;
+        cost[node] = box_area_lohi(lo, hi) * (FF_SLOT_COST + 1.0f);
         if (n == 1) return;
         for (;;) {
             const uint32_t p = parent[node];
@@ -307,8 +315,21 @@ __global__ void refit_kernel(const float4* __restrict__ flat_tris, const uint32_
             l1.x = vlo[ch.y].x; l1.y = vlo[ch.y].y; l1.z = vlo[ch.y].z; l1.w = vlo[ch.y].w;
             h0.x = vhi[ch.x].x; h0.y = vhi[ch.x].y; h0.z = vhi[ch.x].z; h0.w = vhi[ch.x].w;
             h1.x = vhi[ch.y].x; h1.y = vhi[ch.y].y; h1.z = vhi[ch.y].z; h1.w = vhi[ch.y].w;
-            lo = make_float4(fminf(l0.x, l1.x), fminf(l0.y, l1.y), fminf(l0.z, l1.z), __int_as_float(__float_as_int(l0.w) + __float_as_int(l1.w)));
+            const int cnt = (__float_as_int(l0.w) & FF_COUNT_MASK) + (__float_as_int(l1.w) & FF_COUNT_MASK);
+            lo = make_float4(fminf(l0.x, l1.x), fminf(l0.y, l1.y), fminf(l0.z, l1.z), 0.f);
             hi = make_float4(fmaxf(h0.x, h1.x), fmaxf(h0.y, h1.y), fmaxf(h0.z, h1.z), h0.w);
+            // leaf-or-open decision by expected cost: a <=3-triangle subtree becomes ONE leaf child only when
+            // testing all its triangles under the merged box is cheaper than keeping the children apart
+            const volatile float* vc = cost;
+            const float split = vc[ch.x] + vc[ch.y];
+            int flag = 0;
+            float best = split;
+            if (cnt <= 3) {
+                const float leaf = box_area_lohi(lo, hi) * (FF_SLOT_COST + (float)cnt);
+                if (split < leaf) flag = FF_PREFER_OPEN; else best = leaf;
+            }
+            cost[p] = best;
+            lo.w = __int_as_float(cnt | flag);
             box_lo[p] = lo;
             box_hi[p] = hi;
             node = p;
@@ -367,7 +388,7 @@ __global__ void collapse_kernel(const uint2* __restrict__ queue_in, uint32_t n_i
     uint32_t ch[8];
     int nch = 0;
     const float4 plo = box_lo[bnode], phi = box_hi[bnode];
-    if (bnode >= n_internal || __float_as_int(plo.w) <= 3) {
+    if (bnode >= n_internal || (__float_as_int(plo.w) & FF_COUNT_MASK) <= 3) {
         ch[nch++] = bnode;  // tiny scene: the whole tree is one leaf child
     } else {
         ch[0] = (uint32_t)children[bnode].x;
@@ -377,7 +398,8 @@ __global__ void collapse_kernel(const uint2* __restrict__ queue_in, uint32_t n_i
             int pick = -1;
             float best = -1.f;
             for (int k = 0; k < nch; ++k) {
-                if (ch[k] < n_internal && __float_as_int(box_lo[ch[k]].w) > 3) {
+                const int cw = __float_as_int(box_lo[ch[k]].w);
+                if (ch[k] < n_internal && ((cw & FF_COUNT_MASK) > 3 || (cw & FF_PREFER_OPEN))) {
                     const float a = box_area(box_lo[ch[k]], box_hi[ch[k]]);
                     if (a > best) { best = a; pick = k; }
                 }
@@ -424,7 +446,7 @@ __global__ void collapse_kernel(const uint2* __restrict__ queue_in, uint32_t n_i
         const int k = slot_child[s];
         if (k < 0) continue;
         const uint32_t c = ch[k];
-        const int cnt = __float_as_int(box_lo[c].w);
+        const int cnt = __float_as_int(box_lo[c].w) & FF_COUNT_MASK;
         if (c < n_internal && cnt > 3) { imask |= 1u << s; ++n_inner; }
         else n_leaf_tris += (uint32_t)cnt;
     }
@@ -442,7 +464,7 @@ __global__ void collapse_kernel(const uint2* __restrict__ queue_in, uint32_t n_i
         if (k < 0) continue;
         const uint32_t c = ch[k];
         const float4 l = box_lo[c], h = box_hi[c];
-        const int cnt = __float_as_int(l.w);
+        const int cnt = __float_as_int(l.w) & FF_COUNT_MASK;
         uint32_t m;
         if (imask & (1u << s)) {
             m = 0x20u | (24u + (uint32_t)s);
@@ -491,6 +513,7 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
     int* d_bounds = nullptr;
     uint32_t *d_keys_a = nullptr, *d_keys_b = nullptr, *d_vals_a = nullptr, *d_vals_b = nullptr, *d_hist = nullptr;
     uint32_t *d_parent = nullptr, *d_flags = nullptr;
+    float* d_cost = nullptr;
     uint2 *d_q0 = nullptr, *d_q1 = nullptr;
     CollapseCounters* d_ctr = nullptr;
     CK(cudaMalloc(&d_bounds, 12 * sizeof(int)));
@@ -499,6 +522,7 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
     CK(cudaMalloc(&d_hist, sizeof(uint32_t) * 256 * (size_t)n_tiles));
     CK(cudaMalloc(&d_parent, sizeof(uint32_t) * (2 * (size_t)n)));
     CK(cudaMalloc(&d_flags, sizeof(uint32_t) * n));
+    CK(cudaMalloc(&d_cost, sizeof(float) * (2 * (size_t)n)));
     CK(cudaMalloc(&d_q0, sizeof(uint2) * (size_t)node_capacity)); CK(cudaMalloc(&d_q1, sizeof(uint2) * (size_t)node_capacity));
     CK(cudaMalloc(&d_ctr, sizeof(CollapseCounters)));
     CK(cudaMemsetAsync(d_flags, 0, sizeof(uint32_t) * n, st));
@@ -513,7 +537,7 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
         ++*launches;
     }
     refit_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(d_flat_tris, d_vals_a, (int)n, pad, d_bvh2_children, d_parent, d_flags,
-                                                            d_bvh2_lo, d_bvh2_hi);
+                                                            d_bvh2_lo, d_bvh2_hi, d_cost);
     ++*launches;
 
     int h_bounds[12];
@@ -553,7 +577,7 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
     out->depth = depth;
     out->sah_cost = h_ctr.sah;
     cudaFree(d_bounds); cudaFree(d_keys_a); cudaFree(d_keys_b); cudaFree(d_vals_a); cudaFree(d_vals_b); cudaFree(d_hist);
-    cudaFree(d_parent); cudaFree(d_flags); cudaFree(d_q0); cudaFree(d_q1); cudaFree(d_ctr);
+    cudaFree(d_parent); cudaFree(d_flags); cudaFree(d_cost); cudaFree(d_q0); cudaFree(d_q1); cudaFree(d_ctr);
     return h_ctr.tri_count == n ? cudaSuccess : cudaErrorUnknown;
 }
 

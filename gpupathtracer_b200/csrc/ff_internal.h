@@ -13,6 +13,7 @@
 #define FF_LOCAL_STACK 56  // spill entries in local memory
 #define FF_MAX_WIDE_DEPTH (FF_SM_STACK + FF_LOCAL_STACK)
 #define FF_TRACE_BLOCK 128
+#define FF_POSTPONE_DIV 5   // postpone triangle tests when fewer than 1/5 of the live lanes have any
 
 namespace ff {
 

@@ -57,24 +57,26 @@ FF_HD float distance(V3 p0, V3 p1) { return length(sub(p1, p0)); }
 // normalised.  Returns true on an accepted hit and sets t (distance along d).  Comparison senses are
 // kept exactly (NaNs fall through the same way).
 FF_HD bool intersect_triangle(V3 v0, V3 v1, V3 v2, V3 o, V3 d, float& t_out) {
+    // Written without early returns (on the GPU divergent exits cost more than the arithmetic they skip); the
+    // accept condition is the conjunction of the reference's tests with their comparison senses unchanged.
     const float EPSILON = 0.000001f;
     V3 edge1 = sub(v1, v0), edge2 = sub(v2, v0);
     V3 N = cross(edge1, edge2);
-    if (dot(d, N) > 0.0f) return false;
+    const bool back = dot(d, N) > 0.0f;              // kernel.cu:48-51
     V3 pvec = cross(d, edge2);
     float det = dot(edge1, pvec);
-    if (det < EPSILON) return false;
+    const bool flat = det < EPSILON;                 // kernel.cu:57
     V3 tvec = sub(o, v0);
     float u = dot(tvec, pvec);
-    if (u < 0.0f || u > det) return false;
+    const bool out_u = u < 0.0f || u > det;          // kernel.cu:64
     V3 qvec = cross(tvec, edge1);
     float v = dot(d, qvec);
-    if (v < 0.0f || fadd(u, v) > det) return false;
+    const bool out_v = v < 0.0f || fadd(u, v) > det;  // kernel.cu:71
     float t = dot(edge2, qvec);
     float invDet = fdiv(1.0f, det);  // kernel.cu:77 divides in double; rounds to the same float
     t = fmul(t, invDet);
-    if (t > EPSILON) { t_out = t; return true; }
-    return false;
+    t_out = t;
+    return !back && !flat && !out_u && !out_v && t > EPSILON;  // kernel.cu:97
 }
 // Closest-hit key of setIntersection (kernel.cu:113-115) for a baked (M = I) triangle.
 FF_HD float hit_key(V3 o, V3 d, float t, V3& point) {

@@ -191,7 +191,17 @@ __device__ __forceinline__ void trace_bvh8(const DevScene& sc, V3 o, V3 dn, Best
             ngroup = make_uint2(0u, 0u);
         }
 
+        // triangle phase.  When only a small fraction of the warp's live lanes has triangles pending, the group is
+        // postponed (pushed back on the stack) so those lanes rejoin the others in the node phase instead of
+        // serialising the warp (Ylitie et al. 2017, section 4.4).  Order independence of the accept rule makes this safe.
+        const unsigned live = __popc(__activemask());
         while (tgroup.y != 0u) {
+            if (!ANY && (ngroup.y & 0xff000000u) != 0u && __popc(__activemask()) * FF_POSTPONE_DIV < live && sp < FF_MAX_WIDE_DEPTH - 1) {
+                if (sp < FF_SM_STACK) sm_stack[sp * sm_stride] = tgroup;
+                else lstack[sp - FF_SM_STACK] = tgroup;
+                ++sp;
+                break;
+            }
             const uint32_t ti = 31u - __clz(tgroup.y);
             tgroup.y &= ~(1u << ti);
             if (COUNT) ++n_tris;

@@ -22,6 +22,7 @@ INTEGRATOR_WAVEFRONT, INTEGRATOR_MEGAKERNEL, INTEGRATOR_AS_CODED = 0, 1, 2
 BUILDER_LBVH, BUILDER_SAH = 0, 1
 TRACE_BVH8, TRACE_BRUTE, TRACE_BVH2 = 0, 1, 2
 TRACE_COUNT = 0x100
+TRACE_STATIC = 0x200  # one-thread-per-ray kernel instead of the persistent dynamic-fetch kernel
 MAT_EMITTER, MAT_DIFFUSE, MAT_MIRROR, MAT_GLASS = 0, 1, 2, 3
 
 

@@ -409,7 +409,7 @@ int ensure_counters(ff_scene* s) {
     }
     return FF_OK;
 }
-bool valid_mode(int mode) { const int m = mode & 0xff; return m == FF_TRACE_BVH8 || m == FF_TRACE_BRUTE || m == FF_TRACE_BVH2; }
+bool valid_mode(int mode) { const int m = mode & 0xff; if (mode & ~(0xff | FF_TRACE_COUNT | FF_TRACE_STATIC)) return false; return m == FF_TRACE_BVH8 || m == FF_TRACE_BRUTE || m == FF_TRACE_BVH2; }
 }  // namespace
 
 extern "C" {
@@ -426,8 +426,9 @@ int ff_trace_closest_device(ff_scene* scene, const void* d_rays, size_t n, int m
     const bool count = (mode & FF_TRACE_COUNT) != 0;
     if (count) FF_CUDA(cudaMemsetAsync(scene->d_trace_counters, 0, sizeof(TraceCounters), c->stream));
     const float4* ro = (const float4*)d_rays;
+    FF_CUDA(cudaMemsetAsync(scene->d_work_counter, 0, sizeof(uint32_t), c->stream));
     ScopedTimer t(c, 0, 1);
-    k_trace_closest(scene->dev, ro, ro + n, nullptr, (uint32_t)n, mode, (HitRec*)d_hits, scene->d_trace_counters, c->stream);
+    k_trace_closest(scene->dev, ro, ro + n, nullptr, (uint32_t)n, mode, (HitRec*)d_hits, scene->d_trace_counters, scene->d_work_counter, c->stream);
     const double ms = t.stop();
     FF_CUDA(cudaGetLastError());
     if (stats) {
@@ -608,7 +609,7 @@ int ensure_wave(ff_scene* s, size_t capacity, int n_counts) {
     }
     if (s->wb_counts < n_counts) {
         cudaFree(s->wb.counts); s->wb.counts = nullptr;
-        FF_CUDA(cudaMalloc((void**)&s->wb.counts, sizeof(uint32_t) * n_counts));
+        FF_CUDA(cudaMalloc((void**)&s->wb.counts, sizeof(uint32_t) * 2 * n_counts));
         s->wb_counts = n_counts;
     }
     return FF_OK;

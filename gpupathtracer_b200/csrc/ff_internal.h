@@ -13,6 +13,9 @@
 #define FF_LOCAL_STACK 56  // spill entries in local memory
 #define FF_MAX_WIDE_DEPTH (FF_SM_STACK + FF_LOCAL_STACK)
 #define FF_TRACE_BLOCK 128
+#define FF_REFILL_LANES 20            // persistent trace: refill idle lanes when fewer than this many still traverse
+#define FF_PERSISTENT_BLOCKS_PER_SM 12
+#define FF_TRACE_STATIC 0x200          // OR into a trace mode: one-thread-per-ray kernel instead of the persistent one
 #define FF_POSTPONE_DIV 5   // postpone triangle tests when fewer than 1/5 of the live lanes have any
 
 namespace ff {
@@ -91,7 +94,7 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
                       BuildOut* out, uint32_t* launches, cudaStream_t st);
 
 void k_trace_closest(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const uint32_t* d_count,
-                     uint32_t n_max, int mode, HitRec* d_hits, TraceCounters* d_counters, cudaStream_t st);
+                     uint32_t n_max, int mode, HitRec* d_hits, TraceCounters* d_counters, uint32_t* d_work_counter, cudaStream_t st);
 void k_trace_any(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const float* d_tmax, uint32_t n, int mode,
                  unsigned char* d_occluded, cudaStream_t st);
 
@@ -113,7 +116,7 @@ struct WaveBuffers {
     float4* beta[2];       // {throughput.rgb, 0}
     HitRec* hits;
     float4* radiance;      // per path of the pass: L.rgb, indexed by path id = sample_in_pass * npix + pixel
-    uint32_t* counts;      // [max_bounces + 2] active paths entering bounce b
+    uint32_t* counts;      // [max_bounces + 2] active paths entering bounce b, then [max_bounces + 2] work counters
     uint32_t capacity;     // paths per pass
 };
 void k_wavefront_pass(const DevScene& sc, const CamDev& cam, const RenderDev& rp, const WaveBuffers& wb, int trace_mode,

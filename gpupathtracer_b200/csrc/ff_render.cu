@@ -89,7 +89,7 @@ __device__ __forceinline__ bool shade_event(const DevScene& sc, const RenderDev&
 __global__ void wf_raygen_kernel(CamDev cam, RenderDev rp, float4* __restrict__ ray_o, float4* __restrict__ ray_d,
                                  float4* __restrict__ beta, float4* __restrict__ radiance, uint32_t* __restrict__ counts, int n_counts) {
     const uint32_t n = rp.samples * rp.npix;
-    if (blockIdx.x == 0 && threadIdx.x < n_counts) counts[threadIdx.x] = threadIdx.x == 0 ? n : 0u;
+    if (blockIdx.x == 0 && threadIdx.x < 2 * n_counts) counts[threadIdx.x] = threadIdx.x == 0 ? n : 0u;  // + work counters
     for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
         const uint32_t s = p / rp.npix, pixel = p - s * rp.npix;
         V3 o, d;
@@ -142,8 +142,6 @@ __global__ void __launch_bounds__(256) wf_shade_kernel(DevScene sc, RenderDev rp
     }
 }
 
-void k_trace_closest(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const uint32_t* d_count,
-                     uint32_t n_max, int mode, HitRec* d_hits, TraceCounters* d_counters, cudaStream_t st);
 
 void k_wavefront_pass(const DevScene& sc, const CamDev& cam, const RenderDev& rp, const WaveBuffers& wb, int trace_mode,
                       TraceCounters* d_counters, uint32_t* launches, cudaEvent_t* trace_events, int* n_trace_events,
@@ -155,7 +153,7 @@ void k_wavefront_pass(const DevScene& sc, const CamDev& cam, const RenderDev& rp
     for (int b = 0; b <= rp.max_bounces; ++b) {
         const int in = b & 1, out = in ^ 1;
         if (trace_events) cudaEventRecord(trace_events[(*n_trace_events)++], st);
-        k_trace_closest(sc, wb.ray_o[in], wb.ray_d[in], wb.counts + b, n, trace_mode, wb.hits, d_counters, st);
+        k_trace_closest(sc, wb.ray_o[in], wb.ray_d[in], wb.counts + b, n, trace_mode, wb.hits, d_counters, wb.counts + n_counts + b, st);
         if (trace_events) cudaEventRecord(trace_events[(*n_trace_events)++], st);
         wf_shade_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(sc, rp, b, wb.counts + b, n, wb.hits, wb.ray_o[in], wb.ray_d[in],
                                                                    wb.beta[in], wb.ray_o[out], wb.ray_d[out], wb.beta[out],

@@ -47,6 +47,62 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_closest_kernel(DevScene 
     }
 }
 
+// ------------------------------------------------------------------ closest hit, persistent warps + dynamic ray fetch
+// Warps pull rays from a global counter; when fewer than FF_REFILL_LANES lanes of a warp are still traversing, the
+// idle lanes fetch new rays instead of waiting for the slowest one (Aila & Laine 2009).  Results do not depend on
+// the schedule (the accept rule is order independent).
+__global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_closest_persistent_kernel(DevScene sc, const float4* __restrict__ ray_o,
+                                                                                   const float4* __restrict__ ray_d,
+                                                                                   const uint32_t* __restrict__ count_ptr, uint32_t n_max,
+                                                                                   HitRec* __restrict__ hits, uint32_t* work_counter) {
+    __shared__ uint2 sm_stack[FF_SM_STACK * FF_TRACE_BLOCK];
+    const uint32_t n = count_ptr ? min(*count_ptr, n_max) : n_max;
+    const int lane = threadIdx.x & 31;
+    uint2* my_stack = sm_stack + threadIdx.x;
+    bool has = false, exhausted = false;
+    uint32_t ray_index = 0;
+    RayCtx r;
+    Trav tv;
+    Best best;
+    unsigned cn = 0, ct = 0;
+    for (;;) {
+        const unsigned need = __ballot_sync(0xffffffffu, !has);
+        if (need && !exhausted) {
+            uint32_t base = 0;
+            const int leader = __ffs(need) - 1;
+            if (lane == leader) base = atomicAdd(work_counter, (uint32_t)__popc(need));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (base + (uint32_t)__popc(need) >= n) exhausted = true;
+            if (!has) {
+                const uint32_t i = base + __popc(need & ((1u << lane) - 1u));
+                if (i < n) {
+                    const V3 o = ld3(__ldg(ray_o + i)), draw = ld3(__ldg(ray_d + i));
+                    const V3 dn = normalize(draw);  // kernel.cu:138
+                    best_init(best, INFINITY);
+                    test_planes<false>(sc, o, draw, best);
+                    r = make_ray_ctx(o, dn);
+                    tv.start(best.key);
+                    ray_index = i;
+                    has = sc.n_nodes != 0;
+                    if (!has) store_hit(hits, i, best);
+                }
+            }
+        }
+        if (!__any_sync(0xffffffffu, has)) break;
+        if (has) {
+            for (;;) {
+                if (!bvh8_step<false, false>(sc, r, tv, best, my_stack, FF_TRACE_BLOCK, cn, ct)) {
+                    store_hit(hits, ray_index, best);
+                    has = false;
+                    break;
+                }
+                if (!exhausted && __popc(__activemask()) < FF_REFILL_LANES) break;
+            }
+        }
+        __syncwarp();
+    }
+}
+
 // Brute force: the reference's own algorithm (every ray against every triangle), tiles of triangles staged
 // in shared memory.  Same leaf test and accept rule, so it is order independent.
 #define FF_BRUTE_TILE 256
@@ -93,10 +149,17 @@ __global__ void __launch_bounds__(FF_BRUTE_TILE) trace_brute_kernel(DevScene sc,
 }
 
 void k_trace_closest(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const uint32_t* d_count,
-                     uint32_t n_max, int mode, HitRec* d_hits, TraceCounters* d_counters, cudaStream_t st) {
+                     uint32_t n_max, int mode, HitRec* d_hits, TraceCounters* d_counters, uint32_t* d_work_counter, cudaStream_t st) {
     if (n_max == 0) return;
     const bool count = (mode & FF_TRACE_COUNT) != 0;
     const int m = mode & 0xff;
+    if (m == FF_TRACE_BVH8 && !count && d_work_counter && !(mode & FF_TRACE_STATIC)) {
+        // persistent: enough warps to fill the machine, each pulling rays until the batch is drained.
+        // *d_work_counter must be zero (the caller clears it on the same stream).
+        const int g = grid_for(n_max, FF_TRACE_BLOCK, 148 * FF_PERSISTENT_BLOCKS_PER_SM);
+        trace_closest_persistent_kernel<<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_work_counter);
+        return;
+    }
     if (m == FF_TRACE_BRUTE) {
         const int g = grid_for(n_max, FF_BRUTE_TILE, 148 * 8);
         if (count) trace_brute_kernel<true><<<g, FF_BRUTE_TILE, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);

@@ -109,114 +109,145 @@ __device__ __forceinline__ float safe_rcp(float d) {
 
 // ------------------------------------------------------------------------------------------------
 // 8-wide compressed BVH traversal (node layout in ff_bvh.cu / DESIGN.md section 3).
-// `sm_stack` points at this thread's column of a [FF_SM_STACK][blockDim.x] uint2 array.
+struct RayCtx {
+    V3 o, dn;
+    float idx, idy, idz;   // reciprocal direction
+    uint32_t octinv;       // 7 - octant of the direction: traversal order of the child slots
+};
+__device__ __forceinline__ RayCtx make_ray_ctx(V3 o, V3 dn) {
+    RayCtx r;
+    r.o = o; r.dn = dn;
+    r.idx = safe_rcp(dn.x); r.idy = safe_rcp(dn.y); r.idz = safe_rcp(dn.z);
+    r.octinv = (dn.x < 0.f ? 0u : 4u) | (dn.y < 0.f ? 0u : 2u) | (dn.z < 0.f ? 0u : 1u);
+    return r;
+}
+#define FF_SLACK 1.000030517578125f  // 1 + 2^-15: a node is culled only beyond best * FF_SLACK
+
+// Fetches one node (5 x LDG.128), tests its 8 quantised child boxes against the ray and returns the hit mask:
+// bits 24..31 = inner children in traversal order, bits 0..23 = triangles of the leaf children.
+__device__ __forceinline__ uint32_t bvh8_child_hits(const float4* __restrict__ nodes, uint32_t node_index, const RayCtx& r, float tlimit,
+                                                    uint32_t& child_base, uint32_t& tri_base, uint32_t& imask) {
+    const size_t ni = (size_t)node_index * 5;
+    const float4 n0 = __ldg(nodes + ni), n1 = __ldg(nodes + ni + 1), n2 = __ldg(nodes + ni + 2), n3 = __ldg(nodes + ni + 3),
+                 n4 = __ldg(nodes + ni + 4);
+    const uint32_t eb = __float_as_uint(n0.w);
+    const float ax = __uint_as_float((eb & 0xffu) << 23) * r.idx;
+    const float ay = __uint_as_float(((eb >> 8) & 0xffu) << 23) * r.idy;
+    const float az = __uint_as_float(((eb >> 16) & 0xffu) << 23) * r.idz;
+    const float ox = (n0.x - r.o.x) * r.idx, oy = (n0.y - r.o.y) * r.idy, oz = (n0.z - r.o.z) * r.idz;
+    child_base = __float_as_uint(n1.x);
+    tri_base = __float_as_uint(n1.y);
+    imask = eb >> 24;
+    const uint32_t octinv4 = r.octinv * 0x01010101u;
+    const bool nx = r.dn.x < 0.f, ny = r.dn.y < 0.f, nz = r.dn.z < 0.f;
+    uint32_t hitmask = 0;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const uint32_t meta4 = __float_as_uint(h ? n1.w : n1.z);
+        const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+        const uint32_t inner_mask4 = (is_inner4 >> 4) * 0xffu;
+        const uint32_t bit_index4 = (meta4 ^ (octinv4 & inner_mask4)) & 0x1f1f1f1fu;
+        const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+        const uint32_t qlox = __float_as_uint(h ? n2.y : n2.x), qloy = __float_as_uint(h ? n2.w : n2.z);
+        const uint32_t qloz = __float_as_uint(h ? n3.y : n3.x), qhix = __float_as_uint(h ? n3.w : n3.z);
+        const uint32_t qhiy = __float_as_uint(h ? n4.y : n4.x), qhiz = __float_as_uint(h ? n4.w : n4.z);
+        const uint32_t nearx = nx ? qhix : qlox, farx = nx ? qlox : qhix;
+        const uint32_t neary = ny ? qhiy : qloy, fary = ny ? qloy : qhiy;
+        const uint32_t nearz = nz ? qhiz : qloz, farz = nz ? qloz : qhiz;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float tnx = fmaf((float)((nearx >> (8 * j)) & 0xffu), ax, ox);
+            const float tny = fmaf((float)((neary >> (8 * j)) & 0xffu), ay, oy);
+            const float tnz = fmaf((float)((nearz >> (8 * j)) & 0xffu), az, oz);
+            const float tfx = fmaf((float)((farx >> (8 * j)) & 0xffu), ax, ox);
+            const float tfy = fmaf((float)((fary >> (8 * j)) & 0xffu), ay, oy);
+            const float tfz = fmaf((float)((farz >> (8 * j)) & 0xffu), az, oz);
+            const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
+            const float tf = fminf(fminf(tfx, tfy), fminf(tfz, tlimit));
+            if (tn <= tf) {
+                const uint32_t cb = (child_bits4 >> (8 * j)) & 0xffu;
+                const uint32_t bi = (bit_index4 >> (8 * j)) & 0xffu;
+                hitmask |= cb << bi;
+            }
+        }
+    }
+    return hitmask;
+}
+
+// Traversal state of one ray; `sm_stack` is this thread's column of a [FF_SM_STACK][stride] shared array.
+struct Trav {
+    uint2 ngroup, tgroup;
+    int sp;
+    float tlimit;
+    uint2 lstack[FF_LOCAL_STACK];
+    __device__ __forceinline__ void start(float best_key) {
+        ngroup = make_uint2(0u, 0x80000000u);
+        tgroup = make_uint2(0u, 0u);
+        sp = 0;
+        tlimit = best_key * FF_SLACK;
+    }
+    __device__ __forceinline__ void push(uint2 v, uint2* sm_stack, int stride) {
+        if (sp < FF_SM_STACK) sm_stack[sp * stride] = v;
+        else lstack[sp - FF_SM_STACK] = v;
+        ++sp;
+    }
+    __device__ __forceinline__ uint2 pop(uint2* sm_stack, int stride) {
+        --sp;
+        return (sp < FF_SM_STACK) ? sm_stack[sp * stride] : lstack[sp - FF_SM_STACK];
+    }
+};
+
+// One traversal iteration: visit one node (or take over a popped triangle group), test pending triangles (postponing
+// them when few lanes have any, Ylitie et al. 2017 section 4.4), pop.  Returns false when the ray is finished.
+template <bool ANY, bool COUNT>
+__device__ __forceinline__ bool bvh8_step(const DevScene& sc, const RayCtx& r, Trav& tv, Best& best, uint2* sm_stack, int stride,
+                                          unsigned& n_nodes, unsigned& n_tris) {
+    if (tv.ngroup.y & 0xff000000u) {
+        const uint32_t hits_imask = tv.ngroup.y;
+        const uint32_t bit = 31u - __clz(hits_imask);
+        const uint32_t base = tv.ngroup.x;
+        tv.ngroup.y &= ~(1u << bit);
+        if (tv.ngroup.y & 0xff000000u) tv.push(tv.ngroup, sm_stack, stride);
+        const uint32_t slot_index = (bit - 24u) ^ r.octinv;
+        const uint32_t rel = __popc(hits_imask & ~(0xffffffffu << slot_index) & 0xffu);
+        uint32_t imask;
+        const uint32_t hitmask = bvh8_child_hits(sc.nodes, base + rel, r, tv.tlimit, tv.ngroup.x, tv.tgroup.x, imask);
+        if (COUNT) ++n_nodes;
+        tv.ngroup.y = (hitmask & 0xff000000u) | imask;
+        tv.tgroup.y = hitmask & 0x00ffffffu;
+    } else {
+        tv.tgroup = tv.ngroup;
+        tv.ngroup = make_uint2(0u, 0u);
+    }
+    const unsigned live = __popc(__activemask());
+    while (tv.tgroup.y != 0u) {
+        if (!ANY && (tv.ngroup.y & 0xff000000u) != 0u && __popc(__activemask()) * FF_POSTPONE_DIV < live && tv.sp < FF_MAX_WIDE_DEPTH - 1) {
+            tv.push(tv.tgroup, sm_stack, stride);
+            break;
+        }
+        const uint32_t ti = 31u - __clz(tv.tgroup.y);
+        tv.tgroup.y &= ~(1u << ti);
+        if (COUNT) ++n_tris;
+        if (test_slot<ANY>(sc.tris, (int)(tv.tgroup.x + ti), r.o, r.dn, best)) {
+            if (ANY) return false;
+            tv.tlimit = best.key * FF_SLACK;
+        }
+    }
+    if ((tv.ngroup.y & 0xff000000u) == 0u) {
+        if (tv.sp == 0) return false;
+        tv.ngroup = tv.pop(sm_stack, stride);
+    }
+    return true;
+}
+
 template <bool ANY, bool COUNT>
 __device__ __forceinline__ void trace_bvh8(const DevScene& sc, V3 o, V3 dn, Best& best, uint2* sm_stack, int sm_stride,
                                            unsigned& n_nodes, unsigned& n_tris) {
     if (sc.n_nodes == 0) return;
-    const float4* __restrict__ nodes = sc.nodes;
-    const float4* __restrict__ tris = sc.tris;
-    const float idx_ = safe_rcp(dn.x), idy_ = safe_rcp(dn.y), idz_ = safe_rcp(dn.z);
-    const uint32_t octinv = (dn.x < 0.f ? 0u : 4u) | (dn.y < 0.f ? 0u : 2u) | (dn.z < 0.f ? 0u : 1u);
-    const uint32_t octinv4 = octinv * 0x01010101u;
-    const float slack = 1.000030517578125f;  // 1 + 2^-15
-
-    uint2 lstack[FF_LOCAL_STACK];
-    int sp = 0;
-    uint2 ngroup = make_uint2(0u, 0x80000000u);
-    uint2 tgroup = make_uint2(0u, 0u);
-    float tlimit = best.key * slack;
-
-    for (;;) {
-        if (ngroup.y & 0xff000000u) {
-            const uint32_t hits_imask = ngroup.y;
-            const uint32_t bit = 31u - __clz(hits_imask);
-            const uint32_t base = ngroup.x;
-            ngroup.y &= ~(1u << bit);
-            if (ngroup.y & 0xff000000u) {
-                if (sp < FF_SM_STACK) sm_stack[sp * sm_stride] = ngroup;
-                else lstack[sp - FF_SM_STACK] = ngroup;
-                ++sp;
-            }
-            const uint32_t slot_index = (bit - 24u) ^ octinv;
-            const uint32_t rel = __popc(hits_imask & ~(0xffffffffu << slot_index) & 0xffu);
-            const size_t ni = (size_t)(base + rel) * 5;
-            const float4 n0 = __ldg(nodes + ni), n1 = __ldg(nodes + ni + 1), n2 = __ldg(nodes + ni + 2),
-                         n3 = __ldg(nodes + ni + 3), n4 = __ldg(nodes + ni + 4);
-            if (COUNT) ++n_nodes;
-            const uint32_t eb = __float_as_uint(n0.w);
-            const float ax = __uint_as_float((eb & 0xffu) << 23) * idx_;
-            const float ay = __uint_as_float(((eb >> 8) & 0xffu) << 23) * idy_;
-            const float az = __uint_as_float(((eb >> 16) & 0xffu) << 23) * idz_;
-            const float ox = (n0.x - o.x) * idx_, oy = (n0.y - o.y) * idy_, oz = (n0.z - o.z) * idz_;
-            ngroup.x = __float_as_uint(n1.x);
-            tgroup.x = __float_as_uint(n1.y);
-            uint32_t hitmask = 0;
-            // near / far plane bytes per axis, selected by the direction sign
-            const bool nx = dn.x < 0.f, ny = dn.y < 0.f, nz = dn.z < 0.f;
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                const uint32_t meta4 = __float_as_uint(h ? n1.w : n1.z);
-                const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
-                const uint32_t inner_mask4 = (is_inner4 >> 4) * 0xffu;
-                const uint32_t bit_index4 = (meta4 ^ (octinv4 & inner_mask4)) & 0x1f1f1f1fu;
-                const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
-                const uint32_t qlox = __float_as_uint(h ? n2.y : n2.x), qloy = __float_as_uint(h ? n2.w : n2.z);
-                const uint32_t qloz = __float_as_uint(h ? n3.y : n3.x), qhix = __float_as_uint(h ? n3.w : n3.z);
-                const uint32_t qhiy = __float_as_uint(h ? n4.y : n4.x), qhiz = __float_as_uint(h ? n4.w : n4.z);
-                const uint32_t nearx = nx ? qhix : qlox, farx = nx ? qlox : qhix;
-                const uint32_t neary = ny ? qhiy : qloy, fary = ny ? qloy : qhiy;
-                const uint32_t nearz = nz ? qhiz : qloz, farz = nz ? qloz : qhiz;
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const float tnx = fmaf((float)((nearx >> (8 * j)) & 0xffu), ax, ox);
-                    const float tny = fmaf((float)((neary >> (8 * j)) & 0xffu), ay, oy);
-                    const float tnz = fmaf((float)((nearz >> (8 * j)) & 0xffu), az, oz);
-                    const float tfx = fmaf((float)((farx >> (8 * j)) & 0xffu), ax, ox);
-                    const float tfy = fmaf((float)((fary >> (8 * j)) & 0xffu), ay, oy);
-                    const float tfz = fmaf((float)((farz >> (8 * j)) & 0xffu), az, oz);
-                    const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
-                    const float tf = fminf(fminf(tfx, tfy), fminf(tfz, tlimit));
-                    if (tn <= tf) {
-                        const uint32_t cb = (child_bits4 >> (8 * j)) & 0xffu;
-                        const uint32_t bi = (bit_index4 >> (8 * j)) & 0xffu;
-                        hitmask |= cb << bi;
-                    }
-                }
-            }
-            ngroup.y = (hitmask & 0xff000000u) | (eb >> 24);
-            tgroup.y = hitmask & 0x00ffffffu;
-        } else {
-            tgroup = ngroup;
-            ngroup = make_uint2(0u, 0u);
-        }
-
-        // triangle phase.  When only a small fraction of the warp's live lanes has triangles pending, the group is
-        // postponed (pushed back on the stack) so those lanes rejoin the others in the node phase instead of
-        // serialising the warp (Ylitie et al. 2017, section 4.4).  Order independence of the accept rule makes this safe.
-        const unsigned live = __popc(__activemask());
-        while (tgroup.y != 0u) {
-            if (!ANY && (ngroup.y & 0xff000000u) != 0u && __popc(__activemask()) * FF_POSTPONE_DIV < live && sp < FF_MAX_WIDE_DEPTH - 1) {
-                if (sp < FF_SM_STACK) sm_stack[sp * sm_stride] = tgroup;
-                else lstack[sp - FF_SM_STACK] = tgroup;
-                ++sp;
-                break;
-            }
-            const uint32_t ti = 31u - __clz(tgroup.y);
-            tgroup.y &= ~(1u << ti);
-            if (COUNT) ++n_tris;
-            if (test_slot<ANY>(tris, (int)(tgroup.x + ti), o, dn, best)) {
-                if (ANY) return;
-                tlimit = best.key * slack;
-            }
-        }
-
-        if ((ngroup.y & 0xff000000u) == 0u) {
-            if (sp == 0) break;
-            --sp;
-            ngroup = (sp < FF_SM_STACK) ? sm_stack[sp * sm_stride] : lstack[sp - FF_SM_STACK];
-        }
-    }
+    const RayCtx r = make_ray_ctx(o, dn);
+    Trav tv;
+    tv.start(best.key);
+    while (bvh8_step<ANY, COUNT>(sc, r, tv, best, sm_stack, sm_stride, n_nodes, n_tris)) {}
 }
 
 // Binary LBVH traversal (comparison / bridge variant).
@@ -225,7 +256,7 @@ __device__ __forceinline__ void trace_bvh2(const DevScene& sc, V3 o, V3 dn, Best
     if (sc.n_tris == 0) return;
     const uint32_t n_internal = sc.n_tris - 1;
     const float idx_ = safe_rcp(dn.x), idy_ = safe_rcp(dn.y), idz_ = safe_rcp(dn.z);
-    const float slack = 1.000030517578125f;
+    const float slack = FF_SLACK;
     uint32_t stack[64];
     int sp = 0;
     uint32_t node = 0;

@@ -51,7 +51,7 @@ def main():
     ap.add_argument("--builder", type=int, default=0)
     a = ap.parse_args()
     cases = a.cases.split(",")
-    modes = {"bvh8": ff.TRACE_BVH8, "bvh2": ff.TRACE_BVH2}
+    modes = {"bvh8": ff.TRACE_BVH8, "bvh8s": ff.TRACE_BVH8 | ff.TRACE_STATIC, "bvh2": ff.TRACE_BVH2}
     ctx = ff.Context(0)
     if "soupA" in cases or "soupB" in cases:
         soup = ctx.make_soup(a.tris)

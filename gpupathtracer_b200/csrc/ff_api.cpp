@@ -335,6 +335,7 @@ int ff_scene_commit(ff_scene* scene, int builder, double* out_build_ms) {
     d.bvh2_lo = scene->d_bvh2_lo; d.bvh2_hi = scene->d_bvh2_hi; d.bvh2_leaf_slot = scene->d_leaf_slot;
     d.n_tris = (uint32_t)n_tris; d.n_nodes = bo.n_nodes; d.n_planes = (uint32_t)n_planes; d.n_geoms = (uint32_t)scene->geoms.size();
     d.wide_depth = bo.depth;
+    d.postpone_div = (uint32_t)tuning().postpone_div; d.refill_lanes = (uint32_t)tuning().refill_lanes;
     for (int k = 0; k < 3; ++k) { d.bounds_lo[k] = blo[k]; d.bounds_hi[k] = bhi[k]; }
 
     ff_scene_info& in = scene->info;
@@ -945,6 +946,12 @@ int ff_flush_l2(ff_context* ctx) {
     return FF_OK;
 }
 
+int ff_debug_set_tuning(int postpone_div, int refill_lanes, int blocks_per_sm) {
+    if (postpone_div > 0) tuning().postpone_div = postpone_div;
+    if (refill_lanes >= 0) tuning().refill_lanes = refill_lanes;
+    if (blocks_per_sm > 0) tuning().blocks_per_sm = blocks_per_sm;
+    return FF_OK;
+}
 int ff_write_image(const char* path, const float* rgba, int width, int height) { return write_image_float(path, rgba, width, height); }
 int ff_write_image_u8(const char* path, const unsigned char* rgb, int width, int height) { return write_image_u8(path, rgb, width, height); }
 void ff_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) {

@@ -13,10 +13,10 @@
 #define FF_LOCAL_STACK 56  // spill entries in local memory
 #define FF_MAX_WIDE_DEPTH (FF_SM_STACK + FF_LOCAL_STACK)
 #define FF_TRACE_BLOCK 128
-#define FF_REFILL_LANES 20            // persistent trace: refill idle lanes when fewer than this many still traverse
+#define FF_REFILL_LANES 28            // persistent trace: refill idle lanes when fewer than this many still traverse
 #define FF_PERSISTENT_BLOCKS_PER_SM 12
 #define FF_TRACE_STATIC 0x200          // OR into a trace mode: one-thread-per-ray kernel instead of the persistent one
-#define FF_POSTPONE_DIV 5   // postpone triangle tests when fewer than 1/5 of the live lanes have any
+#define FF_POSTPONE_DIV 1000000  // postpone triangle tests when fewer than live/DIV lanes have any (off by default: dynamic fetch does better)
 
 namespace ff {
 
@@ -49,6 +49,8 @@ struct DevScene {
     uint32_t n_tris, n_nodes, n_planes, n_geoms;
     uint32_t wide_depth;
     float pad;                   // absolute inflation applied to every leaf box (conservative culling)
+    uint32_t postpone_div;       // triangle groups are postponed when fewer than live/postpone_div lanes have any
+    uint32_t refill_lanes;       // persistent kernel: refill idle lanes when fewer than this many still traverse
     float bounds_lo[3], bounds_hi[3];
 };
 
@@ -129,5 +131,8 @@ void k_resolve(const float4* const* accums, int n_accums, uint32_t npix, float i
 void k_as_coded(const DevScene& sc, const CamDev& cam, unsigned char* d_rgb, cudaStream_t st);
 void k_rgba_to_u8(const float4* d_rgba, uint32_t npix, unsigned char* d_rgb, cudaStream_t st);
 void k_flush(float4* d_buf, size_t n_float4, cudaStream_t st);
+
+struct Tuning { int postpone_div, refill_lanes, blocks_per_sm; };
+Tuning& tuning();
 
 }  // namespace ff

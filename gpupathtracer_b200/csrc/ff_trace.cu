@@ -7,6 +7,11 @@ namespace ff {
 
 using namespace ffm;
 
+Tuning& tuning() {
+    static Tuning t = {FF_POSTPONE_DIV, FF_REFILL_LANES, FF_PERSISTENT_BLOCKS_PER_SM};
+    return t;
+}
+
 static inline int grid_for(size_t n, int block, int max_blocks) {
     size_t g = (n + block - 1) / block;
     if (g < 1) g = 1;
@@ -96,7 +101,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_closest_persistent_kerne
                     has = false;
                     break;
                 }
-                if (!exhausted && __popc(__activemask()) < FF_REFILL_LANES) break;
+                if (!exhausted && __popc(__activemask()) < sc.refill_lanes) break;
             }
         }
         __syncwarp();
@@ -156,7 +161,7 @@ void k_trace_closest(const DevScene& sc, const float4* d_ray_o, const float4* d_
     if (m == FF_TRACE_BVH8 && !count && d_work_counter && !(mode & FF_TRACE_STATIC)) {
         // persistent: enough warps to fill the machine, each pulling rays until the batch is drained.
         // *d_work_counter must be zero (the caller clears it on the same stream).
-        const int g = grid_for(n_max, FF_TRACE_BLOCK, 148 * FF_PERSISTENT_BLOCKS_PER_SM);
+        const int g = grid_for(n_max, FF_TRACE_BLOCK, 148 * tuning().blocks_per_sm);
         trace_closest_persistent_kernel<<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_work_counter);
         return;
     }

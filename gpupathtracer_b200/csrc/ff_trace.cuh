@@ -221,7 +221,7 @@ __device__ __forceinline__ bool bvh8_step(const DevScene& sc, const RayCtx& r, T
     }
     const unsigned live = __popc(__activemask());
     while (tv.tgroup.y != 0u) {
-        if (!ANY && (tv.ngroup.y & 0xff000000u) != 0u && __popc(__activemask()) * FF_POSTPONE_DIV < live && tv.sp < FF_MAX_WIDE_DEPTH - 1) {
+        if (!ANY && (tv.ngroup.y & 0xff000000u) != 0u && __popc(__activemask()) * sc.postpone_div < live && tv.sp < FF_MAX_WIDE_DEPTH - 1) {
             tv.push(tv.tgroup, sm_stack, stride);
             break;
         }

@@ -207,6 +207,9 @@ int ff_flush_l2(ff_context* ctx);
 int ff_write_image(const char* path, const float* rgba, int width, int height);
 int ff_write_image_u8(const char* path, const unsigned char* rgb, int width, int height);
 
+/* -- development knobs of the traversal scheduler (take effect at the next ff_scene_commit); <= 0 keeps a value. */
+int ff_debug_set_tuning(int postpone_div, int refill_lanes, int blocks_per_sm);
+
 /* -- Philox4x32-10 on the host (the generator all kernels use), for cross-checks. */
 void ff_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]);
 

@@ -49,10 +49,13 @@ def main():
     ap.add_argument("--cases", default="soupA,soupB,c2,c3")
     ap.add_argument("--modes", default="bvh8")
     ap.add_argument("--builder", type=int, default=0)
+    ap.add_argument("--tune", default="")  # postpone_div,refill_lanes,blocks_per_sm
     a = ap.parse_args()
     cases = a.cases.split(",")
     modes = {"bvh8": ff.TRACE_BVH8, "bvh8s": ff.TRACE_BVH8 | ff.TRACE_STATIC, "bvh2": ff.TRACE_BVH2}
     ctx = ff.Context(0)
+    if a.tune:
+        ff.lib.ff_debug_set_tuning(*[int(x) for x in a.tune.split(",")])
     if "soupA" in cases or "soupB" in cases:
         soup = ctx.make_soup(a.tris)
         sc = ctx.scene()

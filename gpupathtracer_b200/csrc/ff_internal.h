@@ -10,6 +10,7 @@
 #include "ff_math.h"
 
 #define FF_SM_STACK 8      // traversal stack entries kept in shared memory per thread
+#define FF_TRI_QUEUE 8     // ring of pending triangle groups per thread in shared memory (power of two)
 #define FF_LOCAL_STACK 56  // spill entries in local memory
 #define FF_MAX_WIDE_DEPTH (FF_SM_STACK + FF_LOCAL_STACK)
 #define FF_TRACE_BLOCK 128

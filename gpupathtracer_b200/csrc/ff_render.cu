@@ -163,36 +163,74 @@ void k_wavefront_pass(const DevScene& sc, const CamDev& cam, const RenderDev& rp
 }
 
 // ------------------------------------------------------------------ persistent megakernel
-// One thread owns one path from camera to termination; warps pull 32 path ids at a time from a global counter.
+// One thread owns one path from camera to termination (the shape of the reference's launchPathTrace, kernel.cu:186-221,
+// with the bounce loop it intends).  Warps are persistent: a lane whose path has terminated pulls the next path id from
+// a global counter as soon as a few lanes are idle, so a warp never waits for its longest path.
 __global__ void __launch_bounds__(FF_TRACE_BLOCK) megakernel(DevScene sc, CamDev cam, RenderDev rp, float4* __restrict__ radiance,
                                                               uint32_t* work_counter, unsigned long long* ray_counter) {
-    __shared__ uint2 sm_stack[FF_SM_STACK * FF_TRACE_BLOCK];
+    __shared__ uint2 sm_stack[(FF_SM_STACK + FF_TRI_QUEUE) * FF_TRACE_BLOCK];
     const uint32_t n = rp.samples * rp.npix;
     const int lane = threadIdx.x & 31;
+    uint2* my = sm_stack + threadIdx.x;
+    bool has = false, exhausted = false;
+    uint32_t path = 0, pixel = 0, sample = 0;
+    int bounce = 0;
+    V3 o = v3(0, 0, 0), d = v3(0, 0, 1), beta = v3(1, 1, 1), L = v3(0, 0, 0);
+    RayCtx r;
+    Trav tv;
+    Best best;
     unsigned rays = 0, cn = 0, ct = 0;
     for (;;) {
-        uint32_t base = 0;
-        if (lane == 0) base = atomicAdd(work_counter, 32u);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= n) break;
-        const uint32_t p = base + lane;
-        if (p < n) {
-            const uint32_t s = p / rp.npix, pixel = p - s * rp.npix, sample = rp.first_sample + s;
-            V3 o, d, beta = v3(1.f, 1.f, 1.f), L = v3(0.f, 0.f, 0.f);
-            primary_ray(cam, rp, pixel, sample, o, d);
-            for (int b = 0; b <= rp.max_bounces; ++b) {
-                const V3 dn = normalize(d);
-                Best best;
-                best_init(best, INFINITY);
-                test_planes<false>(sc, o, d, best);
-                trace_bvh8<false, false>(sc, o, dn, best, sm_stack + threadIdx.x, FF_TRACE_BLOCK, cn, ct);
-                ++rays;
-                HitRec h;
-                h.key = best.key; h.t = best.t; h.slot = best.slot; h.ord = best.slot < 0 ? -1 : best.ord;
-                if (!shade_event(sc, rp, h, pixel, sample, b, o, d, beta, L)) break;
+        const unsigned need = __ballot_sync(0xffffffffu, !has);
+        if (need && !exhausted) {
+            uint32_t base = 0;
+            const int leader = __ffs(need) - 1;
+            if (lane == leader) base = atomicAdd(work_counter, (uint32_t)__popc(need));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (base + (uint32_t)__popc(need) >= n) exhausted = true;
+            if (!has) {
+                const uint32_t p = base + __popc(need & ((1u << lane) - 1u));
+                if (p < n) {
+                    path = p;
+                    const uint32_t s = p / rp.npix;
+                    pixel = p - s * rp.npix;
+                    sample = rp.first_sample + s;
+                    beta = v3(1.f, 1.f, 1.f); L = v3(0.f, 0.f, 0.f);
+                    bounce = 0;
+                    primary_ray(cam, rp, pixel, sample, o, d);
+                    best_init(best, INFINITY);
+                    test_planes<false>(sc, o, d, best);
+                    r = make_ray_ctx(o, normalize(d));
+                    tv.start(best.key);
+                    if (sc.n_nodes == 0) tv.ngroup.y = 0u;
+                    has = true;
+                }
             }
-            radiance[p] = make_float4(L.x, L.y, L.z, 0.f);
         }
+        if (!__any_sync(0xffffffffu, has)) break;
+        if (has) {
+            for (;;) {
+                if (!bvh8_step<false, false>(sc, r, tv, best, my, FF_TRACE_BLOCK, cn, ct)) {
+                    ++rays;
+                    HitRec h;
+                    h.key = best.key; h.t = best.t; h.slot = best.slot; h.ord = best.slot < 0 ? -1 : best.ord;
+                    if (shade_event(sc, rp, h, pixel, sample, bounce, o, d, beta, L)) {
+                        ++bounce;
+                        best_init(best, INFINITY);
+                        test_planes<false>(sc, o, d, best);
+                        r = make_ray_ctx(o, normalize(d));
+                        tv.start(best.key);
+                        if (sc.n_nodes == 0) tv.ngroup.y = 0u;
+                    } else {
+                        radiance[path] = make_float4(L.x, L.y, L.z, 0.f);
+                        has = false;
+                        break;
+                    }
+                }
+                if (!exhausted && __popc(__activemask()) < sc.refill_lanes) break;
+            }
+        }
+        __syncwarp();
     }
     for (int off = 16; off; off >>= 1) rays += __shfl_xor_sync(0xffffffffu, rays, off);
     if (lane == 0) atomicAdd(ray_counter, (unsigned long long)rays);
@@ -201,7 +239,7 @@ void k_megakernel_pass(const DevScene& sc, const CamDev& cam, const RenderDev& r
                        unsigned long long* d_ray_counter, uint32_t* launches, cudaStream_t st) {
     cudaMemsetAsync(d_work_counter, 0, sizeof(uint32_t), st);
     const uint32_t n = rp.samples * rp.npix;
-    megakernel<<<grid_for(n, FF_TRACE_BLOCK, 148 * 16), FF_TRACE_BLOCK, 0, st>>>(sc, cam, rp, d_radiance, d_work_counter, d_ray_counter);
+    megakernel<<<grid_for(n, FF_TRACE_BLOCK, 148 * tuning().blocks_per_sm), FF_TRACE_BLOCK, 0, st>>>(sc, cam, rp, d_radiance, d_work_counter, d_ray_counter);
     ++*launches;
 }
 
@@ -242,7 +280,7 @@ void k_resolve(const float4* const* accums, int n_accums, uint32_t npix, float i
 // ------------------------------------------------------------------ as-coded frame (kernel.cu:186-216)
 // colour = abs(normal) -> uchar3 (kernel.cu:183,214); misses keep the cleared pixel (kernel.cu:340).
 __global__ void __launch_bounds__(FF_TRACE_BLOCK) as_coded_kernel(DevScene sc, CamDev cam, unsigned char* __restrict__ rgb) {
-    __shared__ uint2 sm_stack[FF_SM_STACK * FF_TRACE_BLOCK];
+    __shared__ uint2 sm_stack[(FF_SM_STACK + FF_TRI_QUEUE) * FF_TRACE_BLOCK];
     const uint32_t npix = (uint32_t)cam.w * cam.h;
     unsigned cn = 0, ct = 0;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += gridDim.x * blockDim.x) {

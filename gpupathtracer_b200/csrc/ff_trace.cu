@@ -32,7 +32,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_closest_kernel(DevScene 
                                                                         const float4* __restrict__ ray_d,
                                                                         const uint32_t* __restrict__ count_ptr, uint32_t n_max,
                                                                         HitRec* __restrict__ hits, TraceCounters* ctr) {
-    __shared__ uint2 sm_stack[FF_SM_STACK * FF_TRACE_BLOCK];
+    __shared__ uint2 sm_stack[(FF_SM_STACK + FF_TRI_QUEUE) * FF_TRACE_BLOCK];
     const uint32_t n = count_ptr ? min(*count_ptr, n_max) : n_max;
     unsigned cn = 0, ct = 0;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
@@ -60,7 +60,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_closest_persistent_kerne
                                                                                    const float4* __restrict__ ray_d,
                                                                                    const uint32_t* __restrict__ count_ptr, uint32_t n_max,
                                                                                    HitRec* __restrict__ hits, uint32_t* work_counter) {
-    __shared__ uint2 sm_stack[FF_SM_STACK * FF_TRACE_BLOCK];
+    __shared__ uint2 sm_stack[(FF_SM_STACK + FF_TRI_QUEUE) * FF_TRACE_BLOCK];
     const uint32_t n = count_ptr ? min(*count_ptr, n_max) : n_max;
     const int lane = threadIdx.x & 31;
     uint2* my_stack = sm_stack + threadIdx.x;
@@ -187,7 +187,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_any_kernel(DevScene sc, 
                                                                     const float4* __restrict__ ray_d,
                                                                     const float* __restrict__ tmax, uint32_t n,
                                                                     unsigned char* __restrict__ occluded) {
-    __shared__ uint2 sm_stack[FF_SM_STACK * FF_TRACE_BLOCK];
+    __shared__ uint2 sm_stack[(FF_SM_STACK + FF_TRI_QUEUE) * FF_TRACE_BLOCK];
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const V3 o = ld3(__ldg(ray_o + i)), draw = ld3(__ldg(ray_d + i));
         const V3 dn = normalize(draw);

@@ -123,6 +123,13 @@ __device__ __forceinline__ RayCtx make_ray_ctx(V3 o, V3 dn) {
 }
 #define FF_SLACK 1.000030517578125f  // 1 + 2^-15: a node is culled only beyond best * FF_SLACK
 
+// Byte j of q as a float WITHOUT the int->float converter (I2F runs on the quarter-rate XU pipe, and 48 of them per
+// node saturated it: profiles/r01b): PRMT builds the bits of 2^23 + byte, one exact FADD removes the 2^23.
+template <int J>
+__device__ __forceinline__ float byte_to_float(uint32_t q) {
+    return __uint_as_float(__byte_perm(q, 0x4B000000u, 0x7540u + J)) - 8388608.0f;
+}
+
 // Fetches one node (5 x LDG.128), tests its 8 quantised child boxes against the ray and returns the hit mask:
 // bits 24..31 = inner children in traversal order, bits 0..23 = triangles of the leaf children.
 __device__ __forceinline__ uint32_t bvh8_child_hits(const float4* __restrict__ nodes, uint32_t node_index, const RayCtx& r, float tlimit,
@@ -156,12 +163,12 @@ __device__ __forceinline__ uint32_t bvh8_child_hits(const float4* __restrict__ n
         const uint32_t nearz = nz ? qhiz : qloz, farz = nz ? qloz : qhiz;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            const float tnx = fmaf((float)((nearx >> (8 * j)) & 0xffu), ax, ox);
-            const float tny = fmaf((float)((neary >> (8 * j)) & 0xffu), ay, oy);
-            const float tnz = fmaf((float)((nearz >> (8 * j)) & 0xffu), az, oz);
-            const float tfx = fmaf((float)((farx >> (8 * j)) & 0xffu), ax, ox);
-            const float tfy = fmaf((float)((fary >> (8 * j)) & 0xffu), ay, oy);
-            const float tfz = fmaf((float)((farz >> (8 * j)) & 0xffu), az, oz);
+            const float tnx = fmaf(j == 0 ? byte_to_float<0>(nearx) : j == 1 ? byte_to_float<1>(nearx) : j == 2 ? byte_to_float<2>(nearx) : byte_to_float<3>(nearx), ax, ox);
+            const float tny = fmaf(j == 0 ? byte_to_float<0>(neary) : j == 1 ? byte_to_float<1>(neary) : j == 2 ? byte_to_float<2>(neary) : byte_to_float<3>(neary), ay, oy);
+            const float tnz = fmaf(j == 0 ? byte_to_float<0>(nearz) : j == 1 ? byte_to_float<1>(nearz) : j == 2 ? byte_to_float<2>(nearz) : byte_to_float<3>(nearz), az, oz);
+            const float tfx = fmaf(j == 0 ? byte_to_float<0>(farx) : j == 1 ? byte_to_float<1>(farx) : j == 2 ? byte_to_float<2>(farx) : byte_to_float<3>(farx), ax, ox);
+            const float tfy = fmaf(j == 0 ? byte_to_float<0>(fary) : j == 1 ? byte_to_float<1>(fary) : j == 2 ? byte_to_float<2>(fary) : byte_to_float<3>(fary), ay, oy);
+            const float tfz = fmaf(j == 0 ? byte_to_float<0>(farz) : j == 1 ? byte_to_float<1>(farz) : j == 2 ? byte_to_float<2>(farz) : byte_to_float<3>(farz), az, oz);
             const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
             const float tf = fminf(fminf(tfx, tfy), fminf(tfz, tlimit));
             if (tn <= tf) {
@@ -174,68 +181,93 @@ __device__ __forceinline__ uint32_t bvh8_child_hits(const float4* __restrict__ n
     return hitmask;
 }
 
-// Traversal state of one ray; `sm_stack` is this thread's column of a [FF_SM_STACK][stride] shared array.
+// Traversal state of one ray.  `sm` is this thread's column of a [FF_SM_STACK + FF_TRI_QUEUE][stride] shared array:
+// rows [0, FF_SM_STACK) are the top of the traversal stack, the rest is a ring of pending triangle groups.
 struct Trav {
-    uint2 ngroup, tgroup;
+    uint2 ngroup, tgroup;   // node group being expanded; triangle group being tested
     int sp;
+    int qhead, qcount;      // ring of triangle groups waiting behind `tgroup`
     float tlimit;
     uint2 lstack[FF_LOCAL_STACK];
     __device__ __forceinline__ void start(float best_key) {
         ngroup = make_uint2(0u, 0x80000000u);
         tgroup = make_uint2(0u, 0u);
-        sp = 0;
+        sp = 0; qhead = 0; qcount = 0;
         tlimit = best_key * FF_SLACK;
     }
-    __device__ __forceinline__ void push(uint2 v, uint2* sm_stack, int stride) {
-        if (sp < FF_SM_STACK) sm_stack[sp * stride] = v;
+    __device__ __forceinline__ void push(uint2 v, uint2* sm, int stride) {
+        if (sp < FF_SM_STACK) sm[sp * stride] = v;
         else lstack[sp - FF_SM_STACK] = v;
         ++sp;
     }
-    __device__ __forceinline__ uint2 pop(uint2* sm_stack, int stride) {
+    __device__ __forceinline__ uint2 pop(uint2* sm, int stride) {
         --sp;
-        return (sp < FF_SM_STACK) ? sm_stack[sp * stride] : lstack[sp - FF_SM_STACK];
+        return (sp < FF_SM_STACK) ? sm[sp * stride] : lstack[sp - FF_SM_STACK];
+    }
+    __device__ __forceinline__ void enqueue(uint2 v, uint2* sm, int stride) {
+        sm[(FF_SM_STACK + ((qhead + qcount) & (FF_TRI_QUEUE - 1))) * stride] = v;
+        ++qcount;
+    }
+    __device__ __forceinline__ uint2 dequeue(uint2* sm, int stride) {
+        const uint2 v = sm[(FF_SM_STACK + qhead) * stride];
+        qhead = (qhead + 1) & (FF_TRI_QUEUE - 1);
+        --qcount;
+        return v;
     }
 };
 
-// One traversal iteration: visit one node (or take over a popped triangle group), test pending triangles (postponing
-// them when few lanes have any, Ylitie et al. 2017 section 4.4), pop.  Returns false when the ray is finished.
 template <bool ANY, bool COUNT>
-__device__ __forceinline__ bool bvh8_step(const DevScene& sc, const RayCtx& r, Trav& tv, Best& best, uint2* sm_stack, int stride,
+__device__ __forceinline__ bool bvh8_test_one(const DevScene& sc, const RayCtx& r, Trav& tv, Best& best, unsigned& n_tris) {
+    const uint32_t ti = 31u - __clz(tv.tgroup.y);
+    tv.tgroup.y &= ~(1u << ti);
+    if (COUNT) ++n_tris;
+    if (test_slot<ANY>(sc.tris, (int)(tv.tgroup.x + ti), r.o, r.dn, best)) {
+        if (ANY) return true;
+        tv.tlimit = best.key * FF_SLACK;
+    }
+    return false;
+}
+
+// One traversal iteration = at most ONE node visit followed by at most ONE triangle test.  The triangles a node visit
+// finds are queued (in traversal order) instead of being tested in an inner loop: with incoherent rays the lanes of a
+// warp find very different numbers of triangles per node, and the inner loop ran at ~14 % lane occupancy for ~70 % of the
+// kernel's issue slots (profiles/r01b).  Decoupled, both halves of the iteration keep most lanes busy.  The accept rule
+// is order independent, so the result is unchanged.  Returns false when the ray is finished.
+template <bool ANY, bool COUNT>
+__device__ __forceinline__ bool bvh8_step(const DevScene& sc, const RayCtx& r, Trav& tv, Best& best, uint2* sm, int stride,
                                           unsigned& n_nodes, unsigned& n_tris) {
     if (tv.ngroup.y & 0xff000000u) {
         const uint32_t hits_imask = tv.ngroup.y;
         const uint32_t bit = 31u - __clz(hits_imask);
         const uint32_t base = tv.ngroup.x;
         tv.ngroup.y &= ~(1u << bit);
-        if (tv.ngroup.y & 0xff000000u) tv.push(tv.ngroup, sm_stack, stride);
+        if (tv.ngroup.y & 0xff000000u) tv.push(tv.ngroup, sm, stride);
         const uint32_t slot_index = (bit - 24u) ^ r.octinv;
         const uint32_t rel = __popc(hits_imask & ~(0xffffffffu << slot_index) & 0xffu);
-        uint32_t imask;
-        const uint32_t hitmask = bvh8_child_hits(sc.nodes, base + rel, r, tv.tlimit, tv.ngroup.x, tv.tgroup.x, imask);
+        uint32_t imask, tri_base;
+        const uint32_t hitmask = bvh8_child_hits(sc.nodes, base + rel, r, tv.tlimit, tv.ngroup.x, tri_base, imask);
         if (COUNT) ++n_nodes;
         tv.ngroup.y = (hitmask & 0xff000000u) | imask;
-        tv.tgroup.y = hitmask & 0x00ffffffu;
-    } else {
-        tv.tgroup = tv.ngroup;
-        tv.ngroup = make_uint2(0u, 0u);
+        const uint32_t tmask = hitmask & 0x00ffffffu;
+        if (tmask) {
+            if (tv.tgroup.y == 0u) tv.tgroup = make_uint2(tri_base, tmask);
+            else {
+                while (tv.qcount == FF_TRI_QUEUE) {  // ring full (rare): drain the group in hand
+                    while (tv.tgroup.y != 0u)
+                        if (bvh8_test_one<ANY, COUNT>(sc, r, tv, best, n_tris)) return false;
+                    tv.tgroup = tv.dequeue(sm, stride);
+                }
+                tv.enqueue(make_uint2(tri_base, tmask), sm, stride);
+            }
+        }
     }
-    const unsigned live = __popc(__activemask());
-    while (tv.tgroup.y != 0u) {
-        if (!ANY && (tv.ngroup.y & 0xff000000u) != 0u && __popc(__activemask()) * sc.postpone_div < live && tv.sp < FF_MAX_WIDE_DEPTH - 1) {
-            tv.push(tv.tgroup, sm_stack, stride);
-            break;
-        }
-        const uint32_t ti = 31u - __clz(tv.tgroup.y);
-        tv.tgroup.y &= ~(1u << ti);
-        if (COUNT) ++n_tris;
-        if (test_slot<ANY>(sc.tris, (int)(tv.tgroup.x + ti), r.o, r.dn, best)) {
-            if (ANY) return false;
-            tv.tlimit = best.key * FF_SLACK;
-        }
+    if (tv.tgroup.y != 0u) {
+        if (bvh8_test_one<ANY, COUNT>(sc, r, tv, best, n_tris)) return false;
+        if (tv.tgroup.y == 0u && tv.qcount > 0) tv.tgroup = tv.dequeue(sm, stride);
     }
     if ((tv.ngroup.y & 0xff000000u) == 0u) {
-        if (tv.sp == 0) return false;
-        tv.ngroup = tv.pop(sm_stack, stride);
+        if (tv.sp > 0) tv.ngroup = tv.pop(sm, stride);
+        else if (tv.tgroup.y == 0u) return false;
     }
     return true;
 }

@@ -76,6 +76,8 @@ _vp, _sz = C.c_void_p, C.c_size_t
 lib.ff_context_create.argtypes = [C.POINTER(_vp), C.c_int]
 lib.ff_context_destroy.argtypes = [_vp]
 lib.ff_context_synchronize.argtypes = [_vp]
+lib.ff_timer_begin.argtypes = [_vp]
+lib.ff_timer_end.argtypes = [_vp, C.POINTER(C.c_double)]
 lib.ff_scene_create.argtypes = [_vp, C.POINTER(_vp)]
 lib.ff_scene_destroy.argtypes = [_vp]
 lib.ff_scene_add_obj.argtypes = [_vp, C.c_char_p, _vp, _vp, _vp, _vp, C.c_int, C.POINTER(C.c_int)]
@@ -278,6 +280,15 @@ class Context:
 
     def flush_l2(self):
         _check(lib.ff_flush_l2(self.h))
+
+    def timer_begin(self):
+        """CUDA-event bracket on the context's stream (device clock); pair with timer_end() -> milliseconds."""
+        _check(lib.ff_timer_begin(self.h))
+
+    def timer_end(self):
+        ms = C.c_double()
+        _check(lib.ff_timer_end(self.h, C.byref(ms)))
+        return ms.value
 
     def make_soup(self, n, s=None):
         s = float(n) ** (-1.0 / 3.0) if s is None else float(s)

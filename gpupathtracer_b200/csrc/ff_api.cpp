@@ -43,6 +43,8 @@ struct ff_context {
     std::vector<cudaEvent_t> trace_events;
     float4* flush_buf = nullptr;
     size_t flush_n = 0;
+    cudaEvent_t timer_ev[2] = {nullptr, nullptr};  // ff_timer_begin / ff_timer_end
+    bool timer_open = false;
 };
 
 struct HostGeom {
@@ -133,6 +135,7 @@ int ff_context_create(ff_context** out, int device_id) {
     c->device = device_id;
     FF_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     for (int k = 0; k < 4; ++k) FF_CUDA(cudaEventCreate(&c->ev[k]));
+    for (int k = 0; k < 2; ++k) FF_CUDA(cudaEventCreate(&c->timer_ev[k]));
     *out = c;
     return FF_OK;
 }
@@ -142,6 +145,7 @@ void ff_context_destroy(ff_context* ctx) {
     cudaStreamSynchronize(ctx->stream);
     for (auto e : ctx->trace_events) cudaEventDestroy(e);
     for (int k = 0; k < 4; ++k) cudaEventDestroy(ctx->ev[k]);
+    for (int k = 0; k < 2; ++k) cudaEventDestroy(ctx->timer_ev[k]);
     cudaFree(ctx->flush_buf);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -150,6 +154,26 @@ int ff_context_device(const ff_context* ctx) { return ctx ? ctx->device : -1; }
 int ff_context_synchronize(ff_context* ctx) {
     FF_REQUIRE(ctx, "ff_context_synchronize: NULL context");
     FF_CUDA(cudaStreamSynchronize(ctx->stream));
+    return FF_OK;
+}
+
+int ff_timer_begin(ff_context* ctx) {
+    FF_REQUIRE(ctx, "ff_timer_begin: NULL context");
+    FF_CUDA(cudaSetDevice(ctx->device));
+    FF_CUDA(cudaEventRecord(ctx->timer_ev[0], ctx->stream));
+    ctx->timer_open = true;
+    return FF_OK;
+}
+int ff_timer_end(ff_context* ctx, double* out_ms) {
+    FF_REQUIRE(ctx && out_ms, "ff_timer_end: NULL argument");
+    FF_REQUIRE(ctx->timer_open, "ff_timer_end: no ff_timer_begin on this context");
+    FF_CUDA(cudaSetDevice(ctx->device));
+    FF_CUDA(cudaEventRecord(ctx->timer_ev[1], ctx->stream));
+    FF_CUDA(cudaEventSynchronize(ctx->timer_ev[1]));
+    float ms = 0.f;
+    FF_CUDA(cudaEventElapsedTime(&ms, ctx->timer_ev[0], ctx->timer_ev[1]));
+    ctx->timer_open = false;
+    *out_ms = (double)ms;
     return FF_OK;
 }
 

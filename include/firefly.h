@@ -108,6 +108,11 @@ int ff_context_create(ff_context** out, int device_id);
 void ff_context_destroy(ff_context* ctx);
 int ff_context_device(const ff_context* ctx);
 int ff_context_synchronize(ff_context* ctx);
+/* CUDA-event bracket on the context's stream: device-clock time of everything issued between the two calls
+ * (kernels, copies and any gap while another stream or library, e.g. an NCCL reduce, is working).  The
+ * reference has no timing of its own; this is what bench.py reports. */
+int ff_timer_begin(ff_context* ctx);
+int ff_timer_end(ff_context* ctx, double* out_ms);
 
 /* -- scene building.  LoadMesh (utilities.h:781-840) + Geometry ctor (utilities.h:176-213) + the
  *    m_bxdf assignment (kernel.cu:246-250).  model = T * Rx * Ry * Rz * S, rotations in degrees.

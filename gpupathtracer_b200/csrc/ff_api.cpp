@@ -45,6 +45,7 @@ struct ff_context {
     size_t flush_n = 0;
     cudaEvent_t timer_ev[2] = {nullptr, nullptr};  // ff_timer_begin / ff_timer_end
     bool timer_open = false;
+    std::vector<ff_scene*> scenes;  // live scenes: orphaned (device memory released) if the context goes first
 };
 
 struct HostGeom {
@@ -66,6 +67,7 @@ struct ff_scene {
     int* d_ord_tri = nullptr;
     float4* d_materials = nullptr;
     DevPlane* d_planes = nullptr;
+    uint32_t* d_lights = nullptr;
     int2* d_bvh2_children = nullptr;
     float4* d_bvh2_lo = nullptr;
     float4* d_bvh2_hi = nullptr;
@@ -76,6 +78,7 @@ struct ff_scene {
     WaveBuffers wb;
     size_t wb_capacity = 0;
     int wb_counts = 0;
+    bool wb_shadow = false;
     float4* d_accum = nullptr;
     float4* d_out = nullptr;
     size_t fb_pixels = 0;
@@ -87,15 +90,16 @@ struct ff_scene {
 static void free_scene_device(ff_scene* s) {
     cudaFree(s->d_flat); cudaFree(s->d_tris); cudaFree(s->d_nodes); cudaFree(s->d_ord_geom); cudaFree(s->d_ord_tri);
     cudaFree(s->d_materials); cudaFree(s->d_planes); cudaFree(s->d_bvh2_children); cudaFree(s->d_bvh2_lo);
-    cudaFree(s->d_bvh2_hi); cudaFree(s->d_leaf_slot);
+    cudaFree(s->d_bvh2_hi); cudaFree(s->d_leaf_slot); cudaFree(s->d_lights); s->d_lights = nullptr;
     s->d_flat = s->d_tris = s->d_nodes = nullptr; s->d_ord_geom = s->d_ord_tri = nullptr; s->d_materials = nullptr;
     s->d_planes = nullptr; s->d_bvh2_children = nullptr; s->d_bvh2_lo = s->d_bvh2_hi = nullptr; s->d_leaf_slot = nullptr;
     s->committed = false;
 }
 static void free_render_scratch(ff_scene* s) {
     for (int k = 0; k < 2; ++k) { cudaFree(s->wb.ray_o[k]); cudaFree(s->wb.ray_d[k]); cudaFree(s->wb.beta[k]); s->wb.ray_o[k] = s->wb.ray_d[k] = s->wb.beta[k] = nullptr; }
-    cudaFree(s->wb.hits); cudaFree(s->wb.radiance); cudaFree(s->wb.counts);
-    s->wb.hits = nullptr; s->wb.radiance = nullptr; s->wb.counts = nullptr; s->wb_capacity = 0; s->wb_counts = 0;
+    cudaFree(s->wb.hits); cudaFree(s->wb.radiance); cudaFree(s->wb.counts); cudaFree(s->wb.sh_o); cudaFree(s->wb.sh_d); cudaFree(s->wb.sh_c);
+    s->wb.hits = nullptr; s->wb.radiance = nullptr; s->wb.counts = nullptr; s->wb.sh_o = s->wb.sh_d = s->wb.sh_c = nullptr;
+    s->wb_capacity = 0; s->wb_counts = 0; s->wb_shadow = false;
     cudaFree(s->d_accum); cudaFree(s->d_out); s->d_accum = s->d_out = nullptr; s->fb_pixels = 0;
 }
 
@@ -139,10 +143,13 @@ int ff_context_create(ff_context** out, int device_id) {
     *out = c;
     return FF_OK;
 }
+static void release_scene(ff_scene* scene);
 void ff_context_destroy(ff_context* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    for (ff_scene* s : ctx->scenes) release_scene(s);  // a scene destroyed later only frees its host object
+    ctx->scenes.clear();
     for (auto e : ctx->trace_events) cudaEventDestroy(e);
     for (int k = 0; k < 4; ++k) cudaEventDestroy(ctx->ev[k]);
     for (int k = 0; k < 2; ++k) cudaEventDestroy(ctx->timer_ev[k]);
@@ -185,16 +192,26 @@ int ff_scene_create(ff_context* ctx, ff_scene** out) {
     memset(&s->dev, 0, sizeof(s->dev));
     memset(&s->info, 0, sizeof(s->info));
     memset(&s->wb, 0, sizeof(s->wb));
+    ctx->scenes.push_back(s);
     *out = s;
     return FF_OK;
 }
-void ff_scene_destroy(ff_scene* scene) {
-    if (!scene) return;
-    cudaSetDevice(scene->ctx->device);
-    cudaStreamSynchronize(scene->ctx->stream);
+static void release_scene(ff_scene* scene) {  // device side only; the context must still be alive
     free_scene_device(scene);
     free_render_scratch(scene);
     cudaFree(scene->d_work_counter); cudaFree(scene->d_ray_counter); cudaFree(scene->d_trace_counters);
+    scene->d_work_counter = nullptr; scene->d_ray_counter = nullptr; scene->d_trace_counters = nullptr;
+    scene->ctx = nullptr;
+}
+void ff_scene_destroy(ff_scene* scene) {
+    if (!scene) return;
+    if (scene->ctx) {
+        ff_context* ctx = scene->ctx;
+        cudaSetDevice(ctx->device);
+        cudaStreamSynchronize(ctx->stream);
+        ctx->scenes.erase(std::remove(ctx->scenes.begin(), ctx->scenes.end(), scene), ctx->scenes.end());
+        release_scene(scene);
+    }
     delete scene;
 }
 static ff_material default_material() {
@@ -250,6 +267,7 @@ int ff_scene_add_plane(ff_scene* scene, const float pos[3], const float rot_deg[
 
 int ff_scene_commit(ff_scene* scene, int builder, double* out_build_ms) {
     FF_REQUIRE(scene, "ff_scene_commit: NULL scene");
+    FF_REQUIRE(scene->ctx, "ff_scene_commit: the scene's context was destroyed");
     FF_REQUIRE(builder == FF_BUILDER_LBVH || builder == FF_BUILDER_SAH, "ff_scene_commit: unknown builder");
     ff_context* ctx = scene->ctx;
     FF_CUDA(cudaSetDevice(ctx->device));
@@ -267,6 +285,7 @@ int ff_scene_commit(ff_scene* scene, int builder, double* out_build_ms) {
     std::vector<M4> models(scene->geoms.size());
     std::vector<float4> materials(2 * scene->geoms.size());
     std::vector<DevPlane> planes;
+    std::vector<uint32_t> lights;  // flat indices of emitter-mesh triangles (next-event estimation samples these)
     float maxabs = 0.f;
     size_t flat = 0;
     for (size_t gi = 0; gi < scene->geoms.size(); ++gi) {
@@ -279,6 +298,7 @@ int ff_scene_commit(ff_scene* scene, int builder, double* out_build_ms) {
             const size_t nt = g.xyz9.size() / 9;
             for (size_t t = 0; t < nt; ++t, ++flat) {
                 geom_of[flat] = (uint32_t)gi; ord_of[flat] = (uint32_t)ord_geom.size();
+                if (g.mat.type == FF_MAT_EMITTER) lights.push_back((uint32_t)flat);
                 ord_geom.push_back((int)gi); ord_tri.push_back((int)t);
             }
         } else {
@@ -296,6 +316,7 @@ int ff_scene_commit(ff_scene* scene, int builder, double* out_build_ms) {
     FF_CUDA(upload(&scene->d_ord_tri, ord_tri, st));
     FF_CUDA(upload(&scene->d_materials, materials, st));
     FF_CUDA(upload(&scene->d_planes, planes, st));
+    FF_CUDA(upload(&scene->d_lights, lights, st));
 
     BuildOut bo; bo.n_nodes = 0; bo.depth = 0; bo.sah_cost = 0;
     float blo[3] = {0, 0, 0}, bhi[3] = {0, 0, 0};
@@ -355,7 +376,8 @@ int ff_scene_commit(ff_scene* scene, int builder, double* out_build_ms) {
 
     DevScene& d = scene->dev;
     d.tris = scene->d_tris; d.nodes = scene->d_nodes; d.ord_geom = scene->d_ord_geom; d.ord_tri = scene->d_ord_tri;
-    d.materials = scene->d_materials; d.planes = scene->d_planes; d.bvh2_children = scene->d_bvh2_children;
+    d.materials = scene->d_materials; d.planes = scene->d_planes; d.flat = scene->d_flat; d.lights = scene->d_lights;
+    d.n_lights = (uint32_t)lights.size(); d.bvh2_children = scene->d_bvh2_children;
     d.bvh2_lo = scene->d_bvh2_lo; d.bvh2_hi = scene->d_bvh2_hi; d.bvh2_leaf_slot = scene->d_leaf_slot;
     d.n_tris = (uint32_t)n_tris; d.n_nodes = bo.n_nodes; d.n_planes = (uint32_t)n_planes; d.n_geoms = (uint32_t)scene->geoms.size();
     d.wide_depth = bo.depth;
@@ -421,6 +443,7 @@ struct ScopedTimer {  // CUDA-event bracket on the context's stream
 };
 int check_scene(ff_scene* scene, const char* who) {
     if (!scene) { set_error(std::string(who) + ": NULL scene"); return FF_ERR_INVALID; }
+    if (!scene->ctx) { set_error(std::string(who) + ": the scene's context was destroyed"); return FF_ERR_INVALID; }
     if (!scene->committed) { set_error(std::string(who) + ": scene not committed"); return FF_ERR_INVALID; }
     cudaError_t e = cudaSetDevice(scene->ctx->device);
     if (e != cudaSuccess) { set_error(cudaGetErrorString(e)); return FF_ERR_CUDA; }
@@ -430,7 +453,7 @@ int ensure_counters(ff_scene* s) {
     if (!s->d_trace_counters) {
         FF_CUDA(cudaMalloc((void**)&s->d_trace_counters, sizeof(TraceCounters)));
         FF_CUDA(cudaMalloc((void**)&s->d_work_counter, sizeof(uint32_t)));
-        FF_CUDA(cudaMalloc((void**)&s->d_ray_counter, sizeof(unsigned long long)));
+        FF_CUDA(cudaMalloc((void**)&s->d_ray_counter, 2 * sizeof(unsigned long long)));  // closest-hit rays, shadow rays
     }
     return FF_OK;
 }
@@ -539,8 +562,10 @@ int ff_trace_any(ff_scene* scene, const float* rays6, const float* tmax, size_t 
     if (tmax) { FF_CUDA(cudaMalloc((void**)&dtm, sizeof(float) * n)); FF_CUDA(cudaMemcpyAsync(dtm, tmax, sizeof(float) * n, cudaMemcpyHostToDevice, st)); }
     FF_CUDA(cudaMemcpyAsync(d6, rays6, sizeof(float) * 6 * n, cudaMemcpyHostToDevice, st));
     k_pack_rays(d6, n, dr, dr + n, st);
+    if ((rc = ensure_counters(scene))) return rc;
+    FF_CUDA(cudaMemsetAsync(scene->d_work_counter, 0, sizeof(uint32_t), st));
     ScopedTimer t(c, 0, 1);
-    k_trace_any(scene->dev, dr, dr + n, dtm, (uint32_t)n, mode, docc, st);
+    k_trace_any(scene->dev, dr, dr + n, dtm, (uint32_t)n, mode, docc, scene->d_work_counter, st);
     const double ms = t.stop();
     FF_CUDA(cudaMemcpy(out_occluded, docc, n, cudaMemcpyDeviceToHost));
     if (stats) { stats->gpu_ms = ms; stats->trace_ms = ms; stats->shadow_rays = n; stats->kernel_launches = 2; }
@@ -617,11 +642,11 @@ int ff_camera_rays(ff_context* ctx, const ff_camera* cam, float* rays6_host, voi
 
 // ================================================================================================ render
 namespace {
-int ensure_wave(ff_scene* s, size_t capacity, int n_counts) {
+int ensure_wave(ff_scene* s, size_t capacity, int n_counts, bool want_shadow) {
     if (s->wb_capacity < capacity) {
         for (int k = 0; k < 2; ++k) { cudaFree(s->wb.ray_o[k]); cudaFree(s->wb.ray_d[k]); cudaFree(s->wb.beta[k]); s->wb.ray_o[k] = s->wb.ray_d[k] = s->wb.beta[k] = nullptr; }
-        cudaFree(s->wb.hits); cudaFree(s->wb.radiance);
-        s->wb.hits = nullptr; s->wb.radiance = nullptr; s->wb_capacity = 0;
+        cudaFree(s->wb.hits); cudaFree(s->wb.radiance); cudaFree(s->wb.sh_o); cudaFree(s->wb.sh_d); cudaFree(s->wb.sh_c);
+        s->wb.hits = nullptr; s->wb.radiance = nullptr; s->wb.sh_o = s->wb.sh_d = s->wb.sh_c = nullptr; s->wb_capacity = 0; s->wb_shadow = false;
         for (int k = 0; k < 2; ++k) {
             FF_CUDA(cudaMalloc((void**)&s->wb.ray_o[k], sizeof(float4) * capacity));
             FF_CUDA(cudaMalloc((void**)&s->wb.ray_d[k], sizeof(float4) * capacity));
@@ -632,9 +657,15 @@ int ensure_wave(ff_scene* s, size_t capacity, int n_counts) {
         s->wb_capacity = capacity;
         s->wb.capacity = (uint32_t)capacity;
     }
+    if (want_shadow && !s->wb_shadow) {  // shadow queue of the next-event-estimation stage, only when asked for
+        FF_CUDA(cudaMalloc((void**)&s->wb.sh_o, sizeof(float4) * s->wb_capacity));
+        FF_CUDA(cudaMalloc((void**)&s->wb.sh_d, sizeof(float4) * s->wb_capacity));
+        FF_CUDA(cudaMalloc((void**)&s->wb.sh_c, sizeof(float4) * s->wb_capacity));
+        s->wb_shadow = true;
+    }
     if (s->wb_counts < n_counts) {
         cudaFree(s->wb.counts); s->wb.counts = nullptr;
-        FF_CUDA(cudaMalloc((void**)&s->wb.counts, sizeof(uint32_t) * 2 * n_counts));
+        FF_CUDA(cudaMalloc((void**)&s->wb.counts, sizeof(uint32_t) * 4 * n_counts));
         s->wb_counts = n_counts;
     }
     return FF_OK;
@@ -656,7 +687,7 @@ int check_params(const ff_render_params* p, const char* who) {
     if ((p->integrator & 0xff) != FF_INTEGRATOR_WAVEFRONT && (p->integrator & 0xff) != FF_INTEGRATOR_MEGAKERNEL) {
         set_error(std::string(who) + ": integrator must be wavefront or megakernel here"); return FF_ERR_INVALID;
     }
-    if (p->nee) { set_error(std::string(who) + ": next-event estimation is not available in this build"); return FF_ERR_UNSUPPORTED; }
+    if (p->nee != 0 && p->nee != 1) { set_error(std::string(who) + ": nee must be 0 or 1"); return FF_ERR_INVALID; }
     return FF_OK;
 }
 // Adds params->spp samples (as sums, in sample-index order) into d_accum.
@@ -669,7 +700,7 @@ int accumulate_samples(ff_scene* scene, const ff_camera* cam, const ff_render_pa
     spb = std::min<size_t>(spb, (size_t)p->spp);
     while (spb > 1 && spb * npix > (32u << 20)) --spb;
     FF_REQUIRE(spb * npix < 0xffffffffull, "render: too many paths per pass");
-    int rc = ensure_wave(scene, spb * npix, p->max_bounces + 2);
+    int rc = ensure_wave(scene, spb * npix, p->max_bounces + 2, p->nee != 0);
     if (rc) return rc;
     rc = ensure_counters(scene);
     if (rc) return rc;
@@ -684,14 +715,15 @@ int accumulate_samples(ff_scene* scene, const ff_camera* cam, const ff_render_pa
     const bool count = wave && (p->integrator & FF_TRACE_COUNT) != 0;  // instrumented extend kernels
     if (count) FF_CUDA(cudaMemsetAsync(scene->d_trace_counters, 0, sizeof(TraceCounters), st));
     // one event pair per extend stage, so trace_ms can be reported separately from the bookkeeping
-    const size_t need_events = wave ? (size_t)2 * n_pass * (p->max_bounces + 1) : 0;
+    const size_t need_events = wave ? (size_t)(p->nee ? 4 : 2) * n_pass * (p->max_bounces + 1) : 0;
     const bool time_trace = stats && need_events <= 8192;
     if (time_trace) while (c->trace_events.size() < need_events) { cudaEvent_t e; FF_CUDA(cudaEventCreate(&e)); c->trace_events.push_back(e); }
     int n_ev = 0;
     uint32_t launches = 0;
-    uint64_t rays = 0;
-    std::vector<uint32_t> h_counts((size_t)n_pass * (p->max_bounces + 2));
-    FF_CUDA(cudaMemsetAsync(scene->d_ray_counter, 0, sizeof(unsigned long long), st));
+    uint64_t rays = 0, shadow_rays = 0;
+    const size_t nc = (size_t)p->max_bounces + 2;  // counts block: 4 x nc (paths | work | shadow rays | shadow work)
+    std::vector<uint32_t> h_counts((size_t)n_pass * 4 * nc);
+    FF_CUDA(cudaMemsetAsync(scene->d_ray_counter, 0, 2 * sizeof(unsigned long long), st));
     ScopedTimer t(c, 0, 1);
     for (int pass = 0; pass < n_pass; ++pass) {
         const size_t s0 = (size_t)pass * spb;
@@ -699,8 +731,8 @@ int accumulate_samples(ff_scene* scene, const ff_camera* cam, const ff_render_pa
         rd.samples = (uint32_t)std::min<size_t>(spb, p->spp - s0);
         if (wave) {
             k_wavefront_pass(scene->dev, cd, rd, scene->wb, FF_TRACE_BVH8 | (count ? FF_TRACE_COUNT : 0), scene->d_trace_counters, &launches, time_trace ? c->trace_events.data() : nullptr, &n_ev, st);
-            FF_CUDA(cudaMemcpyAsync(h_counts.data() + (size_t)pass * (p->max_bounces + 2), scene->wb.counts,
-                                    sizeof(uint32_t) * (p->max_bounces + 2), cudaMemcpyDeviceToHost, st));
+            FF_CUDA(cudaMemcpyAsync(h_counts.data() + (size_t)pass * 4 * nc, scene->wb.counts, sizeof(uint32_t) * 4 * nc,
+                                    cudaMemcpyDeviceToHost, st));
         } else {
             k_megakernel_pass(scene->dev, cd, rd, scene->wb.radiance, scene->d_work_counter, scene->d_ray_counter, &launches, st);
         }
@@ -711,11 +743,14 @@ int accumulate_samples(ff_scene* scene, const ff_camera* cam, const ff_render_pa
     FF_CUDA(cudaGetLastError());
     if (wave) {
         for (int pass = 0; pass < n_pass; ++pass)
-            for (int b = 0; b <= p->max_bounces; ++b) rays += h_counts[(size_t)pass * (p->max_bounces + 2) + b];
+            for (int b = 0; b <= p->max_bounces; ++b) {
+                rays += h_counts[(size_t)pass * 4 * nc + b];
+                if (p->nee && scene->dev.n_lights && b < p->max_bounces) shadow_rays += h_counts[(size_t)pass * 4 * nc + 2 * nc + b];
+            }
     } else {
-        unsigned long long r = 0;
-        FF_CUDA(cudaMemcpy(&r, scene->d_ray_counter, sizeof(r), cudaMemcpyDeviceToHost));
-        rays = r;
+        unsigned long long r[2] = {0, 0};
+        FF_CUDA(cudaMemcpy(r, scene->d_ray_counter, sizeof(r), cudaMemcpyDeviceToHost));
+        rays = r[0]; shadow_rays = r[1];
     }
     if (stats && count) {
         TraceCounters h;
@@ -723,7 +758,7 @@ int accumulate_samples(ff_scene* scene, const ff_camera* cam, const ff_render_pa
         stats->nodes_visited += h.nodes; stats->tris_tested += h.tris;
     }
     if (stats) {
-        stats->gpu_ms += ms; stats->rays += rays; stats->paths += (uint64_t)p->spp * npix; stats->kernel_launches += launches;
+        stats->gpu_ms += ms; stats->rays += rays; stats->shadow_rays += shadow_rays; stats->paths += (uint64_t)p->spp * npix; stats->kernel_launches += launches;
         if (time_trace) {
             double tr = 0;
             for (int k = 0; k + 1 < n_ev; k += 2) { float m = 0; cudaEventElapsedTime(&m, c->trace_events[k], c->trace_events[k + 1]); tr += m; }

@@ -501,11 +501,14 @@ __global__ void collapse_kernel(const uint2* __restrict__ queue_in, uint32_t n_i
 
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return e_; } while (0)
 
+cudaError_t sah_build_hierarchy(const float4* d_flat_tris, const uint32_t* d_sorted_idx, uint32_t n, const float centre_lo[3],
+                                const float centre_hi[3], int2* d_children, uint32_t* d_parent, uint32_t* d_order_out,
+                                uint32_t* launches, uint32_t* out_levels, cudaStream_t st);  // ff_sah.cu
+
 cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float pad, float4* d_tris_out, float4* d_nodes_out,
                       uint32_t node_capacity, int2* d_bvh2_children, float4* d_bvh2_lo, float4* d_bvh2_hi,
                       uint32_t* d_bvh2_leaf_slot, float bounds_lo[3], float bounds_hi[3], BuildOut* out, uint32_t* launches,
                       cudaStream_t st) {
-    (void)builder;
     out->n_nodes = 0; out->depth = 0; out->sah_cost = 0;
     for (int k = 0; k < 3; ++k) { bounds_lo[k] = 0; bounds_hi[k] = 0; }
     if (n == 0) return cudaSuccess;
@@ -532,16 +535,24 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
     morton_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(d_flat_tris, n, d_bounds, d_keys_a, d_vals_a);
     *launches += 3;
     radix_sort_pairs(d_keys_a, d_vals_a, d_keys_b, d_vals_b, n, d_hist, launches, st);
-    if (n > 1) {
+    int h_bounds[12];
+    CK(cudaMemcpyAsync(h_bounds, d_bounds, sizeof(h_bounds), cudaMemcpyDeviceToHost, st));
+    uint32_t* d_order = d_vals_a;  // position in the binary tree's leaf order -> flat triangle index
+    if (n > 1 && builder == FF_BUILDER_SAH) {
+        // top-down binned SAH over the Morton-sorted triangles (ff_sah.cu); leaves the order in d_vals_b
+        CK(cudaStreamSynchronize(st));
+        float clo[3], chi[3];
+        for (int k = 0; k < 3; ++k) { clo[k] = ordered_to_float(h_bounds[6 + k]); chi[k] = ordered_to_float(h_bounds[9 + k]); }
+        CK(sah_build_hierarchy(d_flat_tris, d_vals_a, n, clo, chi, d_bvh2_children, d_parent, d_vals_b, launches, nullptr, st));
+        d_order = d_vals_b;
+    } else if (n > 1) {
         hierarchy_kernel<<<grid_for(n - 1, 256, 148 * 16), 256, 0, st>>>(d_keys_a, (int)n, d_bvh2_children, d_parent);
         ++*launches;
     }
-    refit_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(d_flat_tris, d_vals_a, (int)n, pad, d_bvh2_children, d_parent, d_flags,
+    refit_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(d_flat_tris, d_order, (int)n, pad, d_bvh2_children, d_parent, d_flags,
                                                             d_bvh2_lo, d_bvh2_hi, d_cost);
     ++*launches;
 
-    int h_bounds[12];
-    CK(cudaMemcpyAsync(h_bounds, d_bounds, sizeof(h_bounds), cudaMemcpyDeviceToHost, st));
     float4 root_lo, root_hi;
     const uint32_t root = (n == 1) ? 0u : 0u;  // internal node 0, or the single leaf (id n-1+0 = 0)
     CK(cudaMemcpyAsync(&root_lo, d_bvh2_lo + root, sizeof(float4), cudaMemcpyDeviceToHost, st));
@@ -562,7 +573,7 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
     while (n_in > 0) {
         ++depth;
         collapse_kernel<<<grid_for(n_in, 128, 1 << 30), 128, 0, st>>>(qin, n_in, qout, (int)n, d_bvh2_children, d_bvh2_lo, d_bvh2_hi,
-                                                                     d_flat_tris, d_vals_a, d_nodes_out, d_tris_out, d_bvh2_leaf_slot,
+                                                                     d_flat_tris, d_order, d_nodes_out, d_tris_out, d_bvh2_leaf_slot,
                                                                      d_ctr, root_area);
         ++*launches;
         CK(cudaMemcpyAsync(&h_ctr, d_ctr, sizeof(h_ctr), cudaMemcpyDeviceToHost, st));

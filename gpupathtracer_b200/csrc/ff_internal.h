@@ -42,12 +42,14 @@ struct DevScene {
     const int* ord_tri;
     const float4* materials;
     const DevPlane* planes;
+    const float4* flat;          // the same 48-B records in flat (geometry, triangle) order; light sampling reads these
+    const uint32_t* lights;      // flat indices of the triangles of emitter meshes, in flat order (next-event estimation)
     // binary LBVH kept for the BVH2 comparison kernel
     const int2* bvh2_children;   // internal node i: {left, right}; id >= n_internal is leaf (id - n_internal = slot2)
     const float4* bvh2_lo;       // per node id (internal then leaves): box min, w unused
     const float4* bvh2_hi;
     const uint32_t* bvh2_leaf_slot;  // sorted position -> slot in tris
-    uint32_t n_tris, n_nodes, n_planes, n_geoms;
+    uint32_t n_tris, n_nodes, n_planes, n_geoms, n_lights;
     uint32_t wide_depth;
     float pad;                   // absolute inflation applied to every leaf box (conservative culling)
     uint32_t postpone_div;       // triangle groups are postponed when fewer than live/postpone_div lanes have any
@@ -99,7 +101,11 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
 void k_trace_closest(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const uint32_t* d_count,
                      uint32_t n_max, int mode, HitRec* d_hits, TraceCounters* d_counters, uint32_t* d_work_counter, cudaStream_t st);
 void k_trace_any(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const float* d_tmax, uint32_t n, int mode,
-                 unsigned char* d_occluded, cudaStream_t st);
+                 unsigned char* d_occluded, uint32_t* d_work_counter, cudaStream_t st);
+// Shadow stage of the wavefront: queue entries {o.xyz, path id}, {d.xyz, tmax}, {contribution.rgb}; unoccluded entries
+// add their contribution to radiance[path].  *d_work_counter must be zero.
+void k_trace_shadow(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const float4* d_contrib,
+                    const uint32_t* d_count, uint32_t n_max, float4* d_radiance, uint32_t* d_work_counter, cudaStream_t st);
 
 void k_camera_rays(const CamDev& cam, float4* d_ray_o, float4* d_ray_d, cudaStream_t st);
 void k_pack_rays(const float* d_rays6, size_t n, float4* d_ray_o, float4* d_ray_d, cudaStream_t st);
@@ -119,7 +125,10 @@ struct WaveBuffers {
     float4* beta[2];       // {throughput.rgb, 0}
     HitRec* hits;
     float4* radiance;      // per path of the pass: L.rgb, indexed by path id = sample_in_pass * npix + pixel
-    uint32_t* counts;      // [max_bounces + 2] active paths entering bounce b, then [max_bounces + 2] work counters
+    float4* sh_o;          // shadow queue (next-event estimation): {origin.xyz, path id}
+    float4* sh_d;          //   {unnormalised direction.xyz, tmax}
+    float4* sh_c;          //   {radiance to add when unoccluded, 0}
+    uint32_t* counts;      // 4 x [max_bounces + 2]: paths entering bounce b | extend work counters | shadow rays of bounce b | shadow work counters
     uint32_t capacity;     // paths per pass
 };
 void k_wavefront_pass(const DevScene& sc, const CamDev& cam, const RenderDev& rp, const WaveBuffers& wb, int trace_mode,

@@ -56,10 +56,53 @@ __device__ __forceinline__ void hit_surface(const DevScene& sc, const HitRec& h,
     }
 }
 
-// One shading event of the written-down algorithm.  Returns true when the path continues (o, d, beta updated);
-// otherwise L has received the path's terminal contribution.
+// Next-event estimation, one light sample per diffuse shading event (CPU twin: sample_light in
+// oracle/firefly_oracle.cpp, same operations in the same order).  Lights are the triangles of emitter meshes; one is
+// picked uniformly, a point uniformly on it; it radiates from its front side only (the side closest-hit can see).
+struct ShadowReq {
+    bool valid;
+    V3 o, d;       // shadow ray: origin, unnormalised direction to the light sample
+    float tmax;    // occluded <=> any front-facing hit with key < tmax
+    V3 contrib;    // radiance added to the path when unoccluded
+};
+__device__ __forceinline__ void sample_light(const DevScene& sc, const RenderDev& rp, uint32_t pixel, uint32_t sample, int bounce,
+                                             V3 so, V3 n, V3 beta, ShadowReq& sr) {
+    sr.valid = false;
+    const uint32_t nl = sc.n_lights;
+    if (nl == 0) return;
+    const U4 r = philox4x32_10(U4{pixel, sample, (uint32_t)bounce, 2u}, rp.seed_lo, rp.seed_hi);
+    uint32_t k = (uint32_t)fmul(u01(r.x), (float)nl);
+    if (k > nl - 1) k = nl - 1;
+    const uint32_t fi = __ldg(sc.lights + k);
+    const float4 a4 = __ldg(sc.flat + 3 * (size_t)fi), b4 = __ldg(sc.flat + 3 * (size_t)fi + 1), c4 = __ldg(sc.flat + 3 * (size_t)fi + 2);
+    const V3 v0 = ld3(a4), v1 = ld3(b4), v2 = ld3(c4);
+    const float su = fsqrt(u01(r.y));
+    const float b0 = fsub(1.0f, su), b1 = fmul(u01(r.z), su);
+    const float b2 = fsub(fsub(1.0f, b0), b1);
+    const V3 y = add(add(mul(v0, b0), mul(v1, b1)), mul(v2, b2));
+    const V3 N = cross(sub(v1, v0), sub(v2, v0));
+    const float len = length(N);
+    const V3 sd = sub(y, so);
+    const float dist2 = dot(sd, sd);
+    const float dist = fsqrt(dist2);
+    const float cosx = fdiv(dot(n, sd), dist);
+    const float cosl = fdiv(fdiv(-dot(N, sd), dist), len);
+    if (!(cosx > 0.0f && cosl > 0.0f && dist2 > 0.0f)) return;
+    const float w = fmul(fmul(fdiv(fmul(cosx, cosl), dist2), fmul(0.5f, len)), fmul((float)nl, 0.318309886183790672f));
+    const int geom = __float_as_int(b4.w);
+    const float4 m1 = __ldg(sc.materials + 2 * geom + 1);
+    sr.contrib = mul(mul3(beta, mul(v3(m1.x, m1.y, m1.z), m1.w)), w);
+    sr.o = so; sr.d = sd;
+    sr.tmax = fmul(dist, 0.999f);
+    sr.valid = true;
+}
+
+// One shading event of the written-down algorithm.  Returns true when the path continues (o, d, beta updated, and with
+// next-event estimation `sr` describes the shadow ray of this event); otherwise L has received the path's terminal
+// contribution.
 __device__ __forceinline__ bool shade_event(const DevScene& sc, const RenderDev& rp, const HitRec& h, uint32_t pixel, uint32_t sample,
-                                            int bounce, V3& o, V3& d, V3& beta, V3& L) {
+                                            int bounce, V3& o, V3& d, V3& beta, V3& L, ShadowReq& sr) {
+    sr.valid = false;
     if (h.slot < 0) {
         L = add(L, mul3(beta, v3(rp.background[0], rp.background[1], rp.background[2])));
         return false;
@@ -69,7 +112,10 @@ __device__ __forceinline__ bool shade_event(const DevScene& sc, const RenderDev&
     hit_surface(sc, h, o, d, P, nrm, geom);
     const float4 m0 = __ldg(sc.materials + 2 * geom), m1 = __ldg(sc.materials + 2 * geom + 1);
     if (__float_as_int(m0.x) == FF_MAT_EMITTER) {
-        L = add(L, mul3(beta, mul(v3(m1.x, m1.y, m1.z), m1.w)));
+        // with NEE the direct light of mesh emitters arrives through the shadow rays; a BSDF-sampled hit on one
+        // counts only for the camera ray
+        const bool sampled = rp.nee && !(h.slot & 0x40000000) && sc.n_lights != 0;
+        if (!sampled || bounce == 0) L = add(L, mul3(beta, mul(v3(m1.x, m1.y, m1.z), m1.w)));
         return false;
     }
     if (bounce == rp.max_bounces) return false;
@@ -82,6 +128,7 @@ __device__ __forceinline__ bool shade_event(const DevScene& sc, const RenderDev&
     onb(n, t, bt);
     d = add(add(mul(t, w.x), mul(bt, w.y)), mul(n, w.z));
     o = add(P, mul(n, rp.ray_eps));
+    if (rp.nee) sample_light(sc, rp, pixel, sample, bounce, o, n, beta, sr);
     return true;
 }
 
@@ -89,7 +136,8 @@ __device__ __forceinline__ bool shade_event(const DevScene& sc, const RenderDev&
 __global__ void wf_raygen_kernel(CamDev cam, RenderDev rp, float4* __restrict__ ray_o, float4* __restrict__ ray_d,
                                  float4* __restrict__ beta, float4* __restrict__ radiance, uint32_t* __restrict__ counts, int n_counts) {
     const uint32_t n = rp.samples * rp.npix;
-    if (blockIdx.x == 0 && threadIdx.x < 2 * n_counts) counts[threadIdx.x] = threadIdx.x == 0 ? n : 0u;  // + work counters
+    if (blockIdx.x == 0)  // paths per bounce | extend work counters | shadow rays per bounce | shadow work counters
+        for (int k = threadIdx.x; k < 4 * n_counts; k += blockDim.x) counts[k] = k == 0 ? n : 0u;
     for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
         const uint32_t s = p / rp.npix, pixel = p - s * rp.npix;
         V3 o, d;
@@ -108,7 +156,9 @@ __global__ void __launch_bounds__(256) wf_shade_kernel(DevScene sc, RenderDev rp
                                                         const float4* __restrict__ ray_o_in, const float4* __restrict__ ray_d_in,
                                                         const float4* __restrict__ beta_in, float4* __restrict__ ray_o_out,
                                                         float4* __restrict__ ray_d_out, float4* __restrict__ beta_out,
-                                                        float4* __restrict__ radiance, uint32_t* __restrict__ count_out) {
+                                                        float4* __restrict__ radiance, uint32_t* __restrict__ count_out,
+                                                        float4* __restrict__ sh_o, float4* __restrict__ sh_d, float4* __restrict__ sh_c,
+                                                        uint32_t* __restrict__ shadow_count) {
     const uint32_t n = min(*count_in, cap);
     const uint32_t total = ((n + 31u) / 32u) * 32u;
     const int lane = threadIdx.x & 31;
@@ -116,6 +166,8 @@ __global__ void __launch_bounds__(256) wf_shade_kernel(DevScene sc, RenderDev rp
         bool alive = false;
         V3 o, d, beta;
         uint32_t path = 0;
+        ShadowReq sr;
+        sr.valid = false;
         if (k < n) {
             const float4 o4 = ray_o_in[k], d4 = ray_d_in[k], b4 = beta_in[k];
             const HitRec h = hits[k];
@@ -123,8 +175,14 @@ __global__ void __launch_bounds__(256) wf_shade_kernel(DevScene sc, RenderDev rp
             const uint32_t s = path / rp.npix, pixel = path - s * rp.npix;
             o = ld3(o4); d = ld3(d4); beta = ld3(b4);
             V3 L = v3(0.f, 0.f, 0.f);
-            alive = shade_event(sc, rp, h, pixel, rp.first_sample + s, bounce, o, d, beta, L);
-            if (!alive) radiance[path] = make_float4(L.x, L.y, L.z, 0.f);
+            alive = shade_event(sc, rp, h, pixel, rp.first_sample + s, bounce, o, d, beta, L, sr);
+            if (!alive) {
+                if (rp.nee) {  // the shadow stages of earlier bounces have already added to this path
+                    const float4 a = radiance[path];
+                    L = add(ld3(a), L);
+                }
+                radiance[path] = make_float4(L.x, L.y, L.z, 0.f);
+            }
         }
         const unsigned m = __ballot_sync(0xffffffffu, alive);
         if (m) {
@@ -137,6 +195,21 @@ __global__ void __launch_bounds__(256) wf_shade_kernel(DevScene sc, RenderDev rp
                 ray_o_out[q] = make_float4(o.x, o.y, o.z, __uint_as_float(path));
                 ray_d_out[q] = make_float4(d.x, d.y, d.z, 0.f);
                 beta_out[q] = make_float4(beta.x, beta.y, beta.z, 0.f);
+            }
+        }
+        if (rp.nee) {  // shadow-ray queue of this bounce, compacted the same way
+            const unsigned ms = __ballot_sync(0xffffffffu, sr.valid);
+            if (ms) {
+                const int leader = __ffs(ms) - 1;
+                uint32_t base = 0;
+                if (lane == leader) base = atomicAdd(shadow_count, (uint32_t)__popc(ms));
+                base = __shfl_sync(0xffffffffu, base, leader);
+                if (sr.valid) {
+                    const uint32_t q = base + __popc(ms & ((1u << lane) - 1u));
+                    sh_o[q] = make_float4(sr.o.x, sr.o.y, sr.o.z, __uint_as_float(path));
+                    sh_d[q] = make_float4(sr.d.x, sr.d.y, sr.d.z, sr.tmax);
+                    sh_c[q] = make_float4(sr.contrib.x, sr.contrib.y, sr.contrib.z, 0.f);
+                }
             }
         }
     }
@@ -157,8 +230,15 @@ void k_wavefront_pass(const DevScene& sc, const CamDev& cam, const RenderDev& rp
         if (trace_events) cudaEventRecord(trace_events[(*n_trace_events)++], st);
         wf_shade_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(sc, rp, b, wb.counts + b, n, wb.hits, wb.ray_o[in], wb.ray_d[in],
                                                                    wb.beta[in], wb.ray_o[out], wb.ray_d[out], wb.beta[out],
-                                                                   wb.radiance, wb.counts + b + 1);
+                                                                   wb.radiance, wb.counts + b + 1, wb.sh_o, wb.sh_d, wb.sh_c,
+                                                                   wb.counts + 2 * n_counts + b);
         *launches += 2;
+        if (rp.nee && sc.n_lights != 0 && b < rp.max_bounces) {  // shadow stage: any-hit over this bounce's light samples
+            if (trace_events) cudaEventRecord(trace_events[(*n_trace_events)++], st);
+            k_trace_shadow(sc, wb.sh_o, wb.sh_d, wb.sh_c, wb.counts + 2 * n_counts + b, n, wb.radiance, wb.counts + 3 * n_counts + b, st);
+            if (trace_events) cudaEventRecord(trace_events[(*n_trace_events)++], st);
+            ++*launches;
+        }
     }
 }
 
@@ -173,13 +253,23 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) megakernel(DevScene sc, CamDev
     const int lane = threadIdx.x & 31;
     uint2* my = sm_stack + threadIdx.x;
     bool has = false, exhausted = false;
+    bool shadow = false;  // the traversal in flight is this bounce's shadow ray; (o, d) already hold the next segment
     uint32_t path = 0, pixel = 0, sample = 0;
     int bounce = 0;
-    V3 o = v3(0, 0, 0), d = v3(0, 0, 1), beta = v3(1, 1, 1), L = v3(0, 0, 0);
+    V3 o = v3(0, 0, 0), d = v3(0, 0, 1), beta = v3(1, 1, 1), L = v3(0, 0, 0), pending = v3(0, 0, 0);
     RayCtx r;
     Trav tv;
     Best best;
-    unsigned rays = 0, cn = 0, ct = 0;
+    unsigned rays = 0, shadow_rays = 0, cn = 0, ct = 0;
+    // (re)starts the closest-hit traversal of the segment (o, d)
+    auto start_segment = [&]() {
+        best_init(best, INFINITY);
+        test_planes<false>(sc, o, d, best);
+        r = make_ray_ctx(o, normalize(d));
+        tv.start(best.key);
+        if (sc.n_nodes == 0) tv.ngroup.y = 0u;
+        shadow = false;
+    };
     for (;;) {
         const unsigned need = __ballot_sync(0xffffffffu, !has);
         if (need && !exhausted) {
@@ -198,11 +288,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) megakernel(DevScene sc, CamDev
                     beta = v3(1.f, 1.f, 1.f); L = v3(0.f, 0.f, 0.f);
                     bounce = 0;
                     primary_ray(cam, rp, pixel, sample, o, d);
-                    best_init(best, INFINITY);
-                    test_planes<false>(sc, o, d, best);
-                    r = make_ray_ctx(o, normalize(d));
-                    tv.start(best.key);
-                    if (sc.n_nodes == 0) tv.ngroup.y = 0u;
+                    start_segment();
                     has = true;
                 }
             }
@@ -210,17 +296,39 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) megakernel(DevScene sc, CamDev
         if (!__any_sync(0xffffffffu, has)) break;
         if (has) {
             for (;;) {
-                if (!bvh8_step<false, false>(sc, r, tv, best, my, FF_TRACE_BLOCK, cn, ct)) {
+                // A shadow ray runs through the same closest-hit step (no second copy of the traversal in the loop, no
+                // divergence between lanes in different phases): its search interval starts at tmax and the first accepted
+                // hit ends it, which is the any-hit answer "some front-facing hit with key < tmax".
+                const bool more = bvh8_step<false, false>(sc, r, tv, best, my, FF_TRACE_BLOCK, cn, ct);
+                if (shadow) {
+                    if (!more || best.slot >= 0) {
+                        if (best.slot < 0) L = add(L, pending);
+                        start_segment();
+                    }
+                } else if (!more) {
                     ++rays;
                     HitRec h;
                     h.key = best.key; h.t = best.t; h.slot = best.slot; h.ord = best.slot < 0 ? -1 : best.ord;
-                    if (shade_event(sc, rp, h, pixel, sample, bounce, o, d, beta, L)) {
+                    ShadowReq sr;
+                    if (shade_event(sc, rp, h, pixel, sample, bounce, o, d, beta, L, sr)) {
                         ++bounce;
-                        best_init(best, INFINITY);
-                        test_planes<false>(sc, o, d, best);
-                        r = make_ray_ctx(o, normalize(d));
-                        tv.start(best.key);
-                        if (sc.n_nodes == 0) tv.ngroup.y = 0u;
+                        if (sr.valid) {
+                            ++shadow_rays;
+                            pending = sr.contrib;
+                            best_init(best, sr.tmax);
+                            best.ord = -1;  // strict '<' against tmax: nothing ties with the limit
+                            test_planes<false>(sc, sr.o, sr.d, best);
+                            if (best.slot >= 0 || sc.n_nodes == 0) {  // a plane already blocks it / nothing else to test
+                                if (best.slot < 0) L = add(L, pending);
+                                start_segment();
+                            } else {
+                                r = make_ray_ctx(sr.o, normalize(sr.d));
+                                tv.start(best.key);
+                                shadow = true;
+                            }
+                        } else {
+                            start_segment();
+                        }
                     } else {
                         radiance[path] = make_float4(L.x, L.y, L.z, 0.f);
                         has = false;
@@ -232,8 +340,14 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) megakernel(DevScene sc, CamDev
         }
         __syncwarp();
     }
-    for (int off = 16; off; off >>= 1) rays += __shfl_xor_sync(0xffffffffu, rays, off);
-    if (lane == 0) atomicAdd(ray_counter, (unsigned long long)rays);
+    for (int off = 16; off; off >>= 1) {
+        rays += __shfl_xor_sync(0xffffffffu, rays, off);
+        shadow_rays += __shfl_xor_sync(0xffffffffu, shadow_rays, off);
+    }
+    if (lane == 0) {
+        atomicAdd(ray_counter, (unsigned long long)rays);
+        if (shadow_rays) atomicAdd(ray_counter + 1, (unsigned long long)shadow_rays);
+    }
 }
 void k_megakernel_pass(const DevScene& sc, const CamDev& cam, const RenderDev& rp, float4* d_radiance, uint32_t* d_work_counter,
                        unsigned long long* d_ray_counter, uint32_t* launches, cudaStream_t st) {

@@ -1,0 +1,427 @@
+// ff_sah.cu -- GPU binned-SAH builder (FF_BUILDER_SAH): a top-down binary hierarchy over the Morton-sorted triangles,
+// built level by level on the device, in the same arrays the LBVH path produces (children / parent / sorted order),
+// so the refit + leaf-or-open DP + collapse to the 8-wide compressed layout in ff_bvh.cu run unchanged after it.
+//
+// The reference has no acceleration structure at all (kernel.cu:133-155 scans every triangle for every ray); the north
+// star asks for "a GPU LBVH/binned-SAH builder".  LBVH (ff_bvh.cu) is the fast builder, this is the quality builder.
+//
+// Layout of the work:
+//   * a "segment" is a node's contiguous range [b, e) of the current triangle order.  Each level one kernel runs one
+//     CTA per segment of more than 32 triangles: 16 bins x 3 axes in shared memory (centroid binning, shared atomics),
+//     45 candidate planes evaluated by 45 threads, then a stable two-way partition of the segment into the other
+//     order buffer (ballot/popc ranks), which also reduces the two children's centroid bounds for the next level.
+//   * a segment of <= 32 triangles is finished by ONE WARP in registers: lane k holds triangle k's box; every lane
+//     evaluates the sweep-SAH candidate "everything not after my centroid goes left" for the three axes (an exact
+//     sweep without sorting), the warp takes the minimum, partitions by shuffle, and repeats on the sub-ranges from a
+//     small stack until every leaf is one triangle.
+//   * node numbering follows Karras 2012 (what hierarchy_kernel emits): the children of a node split after position
+//     g are internal nodes g (left: its LAST position) and g+1 (right: its FIRST position), a one-triangle child at
+//     position p is leaf n-1+p, the root is 0.  The numbering depends only on positions, so the tree is deterministic
+//     although segments are appended to the next level's list with atomics.
+//   * splits always go down to single triangles; whether <= 3 of them become one leaf child is decided afterwards by
+//     the expected-cost DP in refit_kernel, exactly as for the LBVH tree.
+#include <cfloat>
+#include "ff_internal.h"
+
+namespace ff {
+
+#define SAH_BINS 16
+#define SAH_SMALL 32          // segments up to this size are finished by one warp
+#define SAH_BLOCK 256
+#define SAH_MAX_LEVELS 96     // beyond this depth segments are halved by position (never reached on sane input)
+
+struct SahSeg {
+    uint32_t b, e, id, level;
+    float clo[3], chi[3];     // bounds of the triangle-box centres (x2: lo+hi, never halved) of the segment
+    uint32_t pad0, pad1;
+};
+
+static inline int sah_grid_for(size_t n, int block, int max_blocks) {
+    size_t g = (n + block - 1) / block;
+    if (g < 1) g = 1;
+    if (g > (size_t)max_blocks) g = max_blocks;
+    return (int)g;
+}
+
+// Triangle boxes in the Morton-sorted order k (so a spatially compact segment gathers from a compact address range).
+__global__ void sah_boxes_kernel(const float4* __restrict__ flat_tris, const uint32_t* __restrict__ sorted_idx, uint32_t n,
+                                 float4* __restrict__ box_lo, float4* __restrict__ box_hi, uint32_t* __restrict__ order) {
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+        const uint32_t src = sorted_idx[k];
+        const float4 a = flat_tris[3 * (size_t)src], b = flat_tris[3 * (size_t)src + 1], c = flat_tris[3 * (size_t)src + 2];
+        box_lo[k] = make_float4(fminf(fminf(a.x, b.x), c.x), fminf(fminf(a.y, b.y), c.y), fminf(fminf(a.z, b.z), c.z), 0.f);
+        box_hi[k] = make_float4(fmaxf(fmaxf(a.x, b.x), c.x), fmaxf(fmaxf(a.y, b.y), c.y), fmaxf(fmaxf(a.z, b.z), c.z), 0.f);
+        order[k] = k;
+    }
+}
+
+__device__ __forceinline__ int sah_f2o(float f) { int i = __float_as_int(f); return i >= 0 ? i : i ^ 0x7fffffff; }
+__device__ __forceinline__ float sah_o2f(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); }
+__device__ __forceinline__ float sah_half_area(float lx, float ly, float lz, float hx, float hy, float hz) {
+    const float dx = hx - lx, dy = hy - ly, dz = hz - lz;
+    return dx * dy + dy * dz + dz * dx;
+}
+
+// Emits the two children of node `id` = segment [b, e) split at m (absolute positions) and returns their node ids.
+__device__ __forceinline__ void sah_link(uint32_t n, uint32_t id, uint32_t b, uint32_t m, uint32_t e, int2* children, uint32_t* parent,
+                                         uint32_t& lid, uint32_t& rid) {
+    lid = (m - b == 1u) ? (n - 1u + b) : (m - 1u);
+    rid = (e - m == 1u) ? (n - 1u + m) : m;
+    children[id] = make_int2((int)lid, (int)rid);
+    parent[lid] = id;
+    parent[rid] = id;
+}
+
+// ------------------------------------------------------------------ one CTA per segment of more than SAH_SMALL triangles
+struct SahLists {
+    SahSeg* next;          // segments of the next level (> SAH_SMALL triangles)
+    SahSeg* small;         // segments handed to the warp kernel
+    uint32_t* counters;    // [0] = entries in next, [1] = entries in small, [2] = deepest level seen
+};
+
+__device__ __forceinline__ int sah_bin_of(float c2, float lo2, float scale) {
+    const int b = (int)((c2 - lo2) * scale);
+    return min(max(b, 0), SAH_BINS - 1);
+}
+
+__global__ void __launch_bounds__(SAH_BLOCK) sah_level_kernel(const SahSeg* __restrict__ segs, const uint32_t* __restrict__ idx_in,
+                                                               uint32_t* __restrict__ idx_out, const float4* __restrict__ box_lo,
+                                                               const float4* __restrict__ box_hi, SahLists lists, int2* children,
+                                                               uint32_t* parent, uint32_t* __restrict__ final_order, uint32_t n) {
+    __shared__ int s_bins[3][SAH_BINS][7];      // lo.xyz, hi.xyz (ordered ints), count
+    __shared__ float s_cost[3 * (SAH_BINS - 1)];
+    __shared__ uint32_t s_nleft[3 * (SAH_BINS - 1)];
+    __shared__ int s_axis, s_plane;
+    __shared__ uint32_t s_nl;
+    __shared__ uint32_t s_warp_l[SAH_BLOCK / 32], s_warp_r[SAH_BLOCK / 32];
+    __shared__ uint32_t s_base_l, s_base_r;
+    __shared__ int s_cb[2][6];                  // children's centre bounds (ordered ints): [side][lo.xyz, hi.xyz]
+
+    const SahSeg s = segs[blockIdx.x];
+    const uint32_t b = s.b, e = s.e, cnt = e - b;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    for (int k = tid; k < 3 * SAH_BINS * 7; k += SAH_BLOCK) {
+        const int f = k % 7;
+        (&s_bins[0][0][0])[k] = f < 3 ? sah_f2o(FLT_MAX) : (f < 6 ? sah_f2o(-FLT_MAX) : 0);
+    }
+    if (tid < 12) (&s_cb[0][0])[tid] = (tid % 6) < 3 ? sah_f2o(FLT_MAX) : sah_f2o(-FLT_MAX);
+    float scale[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const float ext = s.chi[a] - s.clo[a];
+        scale[a] = ext > 0.f ? (float)SAH_BINS / ext : 0.f;
+    }
+    __syncthreads();
+
+    // pass A: bin the triangle boxes by centre
+    const bool forced = s.level >= SAH_MAX_LEVELS;
+    if (!forced) {
+        for (uint32_t i = b + tid; i < e; i += SAH_BLOCK) {
+            const uint32_t p = idx_in[i];
+            const float4 lo = __ldg(box_lo + p), hi = __ldg(box_hi + p);
+            const float c2[3] = {lo.x + hi.x, lo.y + hi.y, lo.z + hi.z};
+            const int ol[3] = {sah_f2o(lo.x), sah_f2o(lo.y), sah_f2o(lo.z)}, oh[3] = {sah_f2o(hi.x), sah_f2o(hi.y), sah_f2o(hi.z)};
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                int* bin = s_bins[a][sah_bin_of(c2[a], s.clo[a], scale[a])];
+                atomicMin(bin + 0, ol[0]); atomicMin(bin + 1, ol[1]); atomicMin(bin + 2, ol[2]);
+                atomicMax(bin + 3, oh[0]); atomicMax(bin + 4, oh[1]); atomicMax(bin + 5, oh[2]);
+                atomicAdd(bin + 6, 1);
+            }
+        }
+    }
+    __syncthreads();
+
+    // 45 candidate planes: thread t -> axis t / 15, left = bins [0, plane]
+    if (tid < 3 * (SAH_BINS - 1)) {
+        const int a = tid / (SAH_BINS - 1), plane = tid % (SAH_BINS - 1);
+        float l[6] = {FLT_MAX, FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX}, r[6] = {FLT_MAX, FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX};
+        uint32_t nl = 0, nr = 0;
+        for (int k = 0; k < SAH_BINS; ++k) {
+            const int* bin = s_bins[a][k];
+            if (bin[6] == 0) continue;
+            float* d = k <= plane ? l : r;
+            d[0] = fminf(d[0], sah_o2f(bin[0])); d[1] = fminf(d[1], sah_o2f(bin[1])); d[2] = fminf(d[2], sah_o2f(bin[2]));
+            d[3] = fmaxf(d[3], sah_o2f(bin[3])); d[4] = fmaxf(d[4], sah_o2f(bin[4])); d[5] = fmaxf(d[5], sah_o2f(bin[5]));
+            if (k <= plane) nl += (uint32_t)bin[6]; else nr += (uint32_t)bin[6];
+        }
+        float cost = FLT_MAX;
+        if (nl && nr && !forced)
+            cost = sah_half_area(l[0], l[1], l[2], l[3], l[4], l[5]) * (float)nl + sah_half_area(r[0], r[1], r[2], r[3], r[4], r[5]) * (float)nr;
+        if (!(cost < FLT_MAX)) cost = FLT_MAX;  // NaN boxes never win
+        s_cost[tid] = cost;
+        s_nleft[tid] = nl;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int best = -1;
+        float bc = FLT_MAX;
+        for (int k = 0; k < 3 * (SAH_BINS - 1); ++k)
+            if (s_cost[k] < bc) { bc = s_cost[k]; best = k; }   // first minimum: deterministic
+        if (best >= 0) { s_axis = best / (SAH_BINS - 1); s_plane = best % (SAH_BINS - 1); s_nl = s_nleft[best]; }
+        else { s_axis = -1; s_plane = 0; s_nl = cnt / 2; }      // no plane separates the centres: halve by position
+        s_base_l = b;
+        s_base_r = b + s_nl;
+    }
+    __syncthreads();
+    const int axis = s_axis, plane = s_plane;
+    const uint32_t nl = s_nl;
+
+    // pass B: stable partition into idx_out, and the centre bounds of the two sides
+    float cl[6] = {FLT_MAX, FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX}, cr[6] = {FLT_MAX, FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX};
+    for (uint32_t base = b; base < e; base += SAH_BLOCK) {
+        const uint32_t i = base + tid;
+        const bool live = i < e;
+        uint32_t p = 0;
+        bool left = false;
+        if (live) {
+            p = idx_in[i];
+            const float4 lo = __ldg(box_lo + p), hi = __ldg(box_hi + p);
+            const float c2[3] = {lo.x + hi.x, lo.y + hi.y, lo.z + hi.z};
+            left = axis < 0 ? (i - b) < nl : sah_bin_of(c2[axis], s.clo[axis], scale[axis]) <= plane;
+            float* d = left ? cl : cr;
+            d[0] = fminf(d[0], c2[0]); d[1] = fminf(d[1], c2[1]); d[2] = fminf(d[2], c2[2]);
+            d[3] = fmaxf(d[3], c2[0]); d[4] = fmaxf(d[4], c2[1]); d[5] = fmaxf(d[5], c2[2]);
+        }
+        const unsigned ml = __ballot_sync(0xffffffffu, live && left), mr = __ballot_sync(0xffffffffu, live && !left);
+        if (lane == 0) { s_warp_l[warp] = __popc(ml); s_warp_r[warp] = __popc(mr); }
+        __syncthreads();
+        uint32_t off_l = 0, off_r = 0, tot_l = 0, tot_r = 0;
+#pragma unroll
+        for (int w = 0; w < SAH_BLOCK / 32; ++w) {
+            if (w < warp) { off_l += s_warp_l[w]; off_r += s_warp_r[w]; }
+            tot_l += s_warp_l[w]; tot_r += s_warp_r[w];
+        }
+        if (live) {
+            const unsigned lt = (1u << lane) - 1u;
+            const uint32_t dst = left ? s_base_l + off_l + __popc(ml & lt) : s_base_r + off_r + __popc(mr & lt);
+            idx_out[dst] = p;
+        }
+        __syncthreads();
+        if (tid == 0) { s_base_l += tot_l; s_base_r += tot_r; }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        float vl = cl[k], vr = cr[k];
+        for (int off = 16; off; off >>= 1) {
+            const float ol = __shfl_xor_sync(0xffffffffu, vl, off), orr = __shfl_xor_sync(0xffffffffu, vr, off);
+            vl = k < 3 ? fminf(vl, ol) : fmaxf(vl, ol);
+            vr = k < 3 ? fminf(vr, orr) : fmaxf(vr, orr);
+        }
+        if (lane == 0) {
+            if (k < 3) { atomicMin(&s_cb[0][k], sah_f2o(vl)); atomicMin(&s_cb[1][k], sah_f2o(vr)); }
+            else { atomicMax(&s_cb[0][k], sah_f2o(vl)); atomicMax(&s_cb[1][k], sah_f2o(vr)); }
+        }
+    }
+    __syncthreads();
+
+    if (tid < 2) {  // thread 0 emits the left child, thread 1 the right one
+        const uint32_t m = b + nl;
+        uint32_t lid, rid;
+        if (tid == 0) sah_link(n, s.id, b, m, e, children, parent, lid, rid);
+        else { lid = (m - b == 1u) ? (n - 1u + b) : (m - 1u); rid = (e - m == 1u) ? (n - 1u + m) : m; }
+        const uint32_t cb = tid == 0 ? b : m, ce = tid == 0 ? m : e, cid = tid == 0 ? lid : rid, cc = ce - cb;
+        if (cc == 1u) {
+            final_order[cb] = idx_out[cb];
+        } else {
+            SahSeg c;
+            c.b = cb; c.e = ce; c.id = cid; c.level = s.level + 1; c.pad0 = c.pad1 = 0;
+            for (int k = 0; k < 3; ++k) { c.clo[k] = sah_o2f(s_cb[tid][k]); c.chi[k] = sah_o2f(s_cb[tid][3 + k]); }
+            if (cc <= SAH_SMALL) lists.small[atomicAdd(lists.counters + 1, 1u)] = c;
+            else lists.next[atomicAdd(lists.counters + 0, 1u)] = c;
+            atomicMax(lists.counters + 2, c.level);
+        }
+    }
+}
+
+// ------------------------------------------------------------------ one warp per segment of <= SAH_SMALL triangles
+// Lane k holds the triangle at position b + k.  Exact sweep SAH without sorting: lane j's candidate sends every
+// triangle whose (centre, lane) is not after (centre_j, j) to the left, which enumerates the prefixes of the order
+// sorted by centre.  The cheapest (cost, axis, lane) wins; the sub-range is partitioned stably through shared memory.
+#define SAH_WARPS 4
+__global__ void __launch_bounds__(SAH_WARPS * 32) sah_small_kernel(const SahSeg* __restrict__ segs, uint32_t n_segs,
+                                                                   const uint32_t* __restrict__ idx_in, const float4* __restrict__ box_lo,
+                                                                   const float4* __restrict__ box_hi, int2* children, uint32_t* parent,
+                                                                   uint32_t* __restrict__ final_order, uint32_t n) {
+    __shared__ float s_box[SAH_WARPS][6][32];
+    __shared__ uint32_t s_prim[SAH_WARPS][32];
+    __shared__ uint32_t s_stack[SAH_WARPS][32][3];   // {first lane, end lane, node id}
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t si = blockIdx.x * SAH_WARPS + warp;
+    if (si >= n_segs) return;
+    const SahSeg s = segs[si];
+    const uint32_t cnt = s.e - s.b;
+    uint32_t prim = 0;
+    float lo[3] = {0.f, 0.f, 0.f}, hi[3] = {0.f, 0.f, 0.f};
+    if ((uint32_t)lane < cnt) {
+        prim = idx_in[s.b + lane];
+        const float4 l = __ldg(box_lo + prim), h = __ldg(box_hi + prim);
+        lo[0] = l.x; lo[1] = l.y; lo[2] = l.z; hi[0] = h.x; hi[1] = h.y; hi[2] = h.z;
+    }
+    int sp = 0;
+    if (lane == 0) { s_stack[warp][0][0] = 0; s_stack[warp][0][1] = cnt; s_stack[warp][0][2] = s.id; }
+    sp = 1;
+    __syncwarp();
+    while (sp > 0) {
+        --sp;
+        const uint32_t rb = s_stack[warp][sp][0], re = s_stack[warp][sp][1], id = s_stack[warp][sp][2];
+        __syncwarp();
+        const uint32_t rc = re - rb;
+        const bool in = (uint32_t)lane >= rb && (uint32_t)lane < re;
+        const float cj[3] = {lo[0] + hi[0], lo[1] + hi[1], lo[2] + hi[2]};
+        float L[3][6], R[3][6];
+        uint32_t nl[3] = {0, 0, 0};
+#pragma unroll
+        for (int a = 0; a < 3; ++a)
+#pragma unroll
+            for (int k = 0; k < 6; ++k) { L[a][k] = k < 3 ? FLT_MAX : -FLT_MAX; R[a][k] = k < 3 ? FLT_MAX : -FLT_MAX; }
+        for (uint32_t k = rb; k < re; ++k) {
+            float kl[3], kh[3];
+#pragma unroll
+            for (int a = 0; a < 3; ++a) { kl[a] = __shfl_sync(0xffffffffu, lo[a], (int)k); kh[a] = __shfl_sync(0xffffffffu, hi[a], (int)k); }
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                const float ck = kl[a] + kh[a];
+                const bool left = ck < cj[a] || (ck == cj[a] && k <= (uint32_t)lane);
+                if (left) {
+                    ++nl[a];
+#pragma unroll
+                    for (int q = 0; q < 3; ++q) { L[a][q] = fminf(L[a][q], kl[q]); L[a][3 + q] = fmaxf(L[a][3 + q], kh[q]); }
+                } else {
+#pragma unroll
+                    for (int q = 0; q < 3; ++q) { R[a][q] = fminf(R[a][q], kl[q]); R[a][3 + q] = fmaxf(R[a][3 + q], kh[q]); }
+                }
+            }
+        }
+        float best = FLT_MAX;
+        uint32_t code = 0xffffffffu;  // axis * 32 + lane of the winning candidate
+        if (in) {
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                if (nl[a] == 0 || nl[a] >= rc) continue;
+                const float c = sah_half_area(L[a][0], L[a][1], L[a][2], L[a][3], L[a][4], L[a][5]) * (float)nl[a] +
+                                sah_half_area(R[a][0], R[a][1], R[a][2], R[a][3], R[a][4], R[a][5]) * (float)(rc - nl[a]);
+                if (c < best) { best = c; code = (uint32_t)a * 32u + (uint32_t)lane; }
+            }
+        }
+        for (int off = 16; off; off >>= 1) {
+            const float ob = __shfl_xor_sync(0xffffffffu, best, off);
+            const uint32_t oc = __shfl_xor_sync(0xffffffffu, code, off);
+            if (ob < best || (ob == best && oc < code)) { best = ob; code = oc; }
+        }
+        bool left;
+        if (code != 0xffffffffu) {
+            const int a = (int)(code >> 5), j = (int)(code & 31u);
+            const float mine = a == 0 ? cj[0] : (a == 1 ? cj[1] : cj[2]);
+            const float cjw = __shfl_sync(0xffffffffu, mine, j);
+            left = mine < cjw || (mine == cjw && lane <= j);
+        } else {
+            left = (uint32_t)lane < rb + rc / 2;   // NaN boxes: halve by position
+        }
+        const unsigned ml = __ballot_sync(0xffffffffu, in && left), mr = __ballot_sync(0xffffffffu, in && !left);
+        const uint32_t nleft = __popc(ml);
+        const unsigned lt = (1u << lane) - 1u;
+        if (in) {
+            const uint32_t dst = left ? rb + __popc(ml & lt) : rb + nleft + __popc(mr & lt);
+#pragma unroll
+            for (int q = 0; q < 3; ++q) { s_box[warp][q][dst] = lo[q]; s_box[warp][3 + q][dst] = hi[q]; }
+            s_prim[warp][dst] = prim;
+        }
+        __syncwarp();
+        if (in) {
+#pragma unroll
+            for (int q = 0; q < 3; ++q) { lo[q] = s_box[warp][q][lane]; hi[q] = s_box[warp][3 + q][lane]; }
+            prim = s_prim[warp][lane];
+        }
+        const uint32_t rm = rb + nleft;
+        if (lane == 0) {
+            uint32_t lid, rid;
+            sah_link(n, id, s.b + rb, s.b + rm, s.b + re, children, parent, lid, rid);
+            int t = sp;
+            if (re - rm >= 2u) { s_stack[warp][t][0] = rm; s_stack[warp][t][1] = re; s_stack[warp][t][2] = rid; ++t; }
+            if (rm - rb >= 2u) { s_stack[warp][t][0] = rb; s_stack[warp][t][1] = rm; s_stack[warp][t][2] = lid; ++t; }
+        }
+        sp += (re - rm >= 2u ? 1 : 0) + (rm - rb >= 2u ? 1 : 0);
+        __syncwarp();
+    }
+    if ((uint32_t)lane < cnt) final_order[s.b + lane] = prim;
+}
+
+__global__ void sah_compose_kernel(const uint32_t* __restrict__ order_k, const uint32_t* __restrict__ sorted_idx, uint32_t n,
+                                   uint32_t* __restrict__ out) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) out[i] = sorted_idx[order_k[i]];
+}
+
+#define SCK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { cleanup(); return e_; } } while (0)
+
+// Builds the binary hierarchy over n >= 2 triangles.  d_sorted_idx: Morton order (position -> flat index).  Writes
+// children[0 .. n-1), parent[0 .. 2n-1) and d_order_out (position -> flat index in the SAH tree's leaf order).
+cudaError_t sah_build_hierarchy(const float4* d_flat_tris, const uint32_t* d_sorted_idx, uint32_t n, const float centre_lo[3],
+                                const float centre_hi[3], int2* d_children, uint32_t* d_parent, uint32_t* d_order_out,
+                                uint32_t* launches, uint32_t* out_levels, cudaStream_t st) {
+    float4 *d_lo = nullptr, *d_hi = nullptr;
+    uint32_t *d_idx0 = nullptr, *d_idx1 = nullptr, *d_order_k = nullptr, *d_counters = nullptr;
+    SahSeg *d_seg0 = nullptr, *d_seg1 = nullptr, *d_small = nullptr;
+    auto cleanup = [&]() {
+        cudaFree(d_lo); cudaFree(d_hi); cudaFree(d_idx0); cudaFree(d_idx1); cudaFree(d_order_k); cudaFree(d_counters);
+        cudaFree(d_seg0); cudaFree(d_seg1); cudaFree(d_small);
+    };
+    const size_t seg_cap = (size_t)n / (SAH_SMALL + 1) + 2, small_cap = (size_t)n / 2 + 2;
+    SCK(cudaMalloc(&d_lo, sizeof(float4) * n)); SCK(cudaMalloc(&d_hi, sizeof(float4) * n));
+    SCK(cudaMalloc(&d_idx0, sizeof(uint32_t) * n)); SCK(cudaMalloc(&d_idx1, sizeof(uint32_t) * n));
+    SCK(cudaMalloc(&d_order_k, sizeof(uint32_t) * n)); SCK(cudaMalloc(&d_counters, sizeof(uint32_t) * 4));
+    SCK(cudaMalloc(&d_seg0, sizeof(SahSeg) * seg_cap)); SCK(cudaMalloc(&d_seg1, sizeof(SahSeg) * seg_cap));
+    SCK(cudaMalloc(&d_small, sizeof(SahSeg) * small_cap));
+    sah_boxes_kernel<<<sah_grid_for(n, 256, 148 * 16), 256, 0, st>>>(d_flat_tris, d_sorted_idx, n, d_lo, d_hi, d_idx0);
+    ++*launches;
+
+    SahSeg root;
+    memset(&root, 0, sizeof(root));
+    root.b = 0; root.e = n; root.id = 0; root.level = 0;
+    for (int k = 0; k < 3; ++k) { root.clo[k] = 2.0f * centre_lo[k]; root.chi[k] = 2.0f * centre_hi[k]; }
+    const uint32_t none = 0xffffffffu;
+    SCK(cudaMemcpyAsync(d_parent, &none, sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+    SCK(cudaMemsetAsync(d_counters, 0, sizeof(uint32_t) * 4, st));
+    uint32_t n_seg = 0, levels = 0;
+    SahSeg *seg_in = d_seg0, *seg_out = d_seg1;
+    uint32_t *idx_in = d_idx0, *idx_out = d_idx1;
+    if (n <= SAH_SMALL) {
+        SCK(cudaMemcpyAsync(d_small, &root, sizeof(root), cudaMemcpyHostToDevice, st));
+        sah_small_kernel<<<1, SAH_WARPS * 32, 0, st>>>(d_small, 1, idx_in, d_lo, d_hi, d_children, d_parent, d_order_k, n);
+        ++*launches;
+    } else {
+        SCK(cudaMemcpyAsync(seg_in, &root, sizeof(root), cudaMemcpyHostToDevice, st));
+        n_seg = 1;
+    }
+    while (n_seg > 0) {
+        ++levels;
+        SahLists lists;
+        lists.next = seg_out; lists.small = d_small; lists.counters = d_counters;
+        sah_level_kernel<<<n_seg, SAH_BLOCK, 0, st>>>(seg_in, idx_in, idx_out, d_lo, d_hi, lists, d_children, d_parent, d_order_k, n);
+        ++*launches;
+        uint32_t h[4];
+        SCK(cudaMemcpyAsync(h, d_counters, sizeof(h), cudaMemcpyDeviceToHost, st));
+        SCK(cudaStreamSynchronize(st));
+        if (h[0] > seg_cap || h[1] > small_cap) { cleanup(); return cudaErrorMemoryAllocation; }
+        if (h[1]) {
+            sah_small_kernel<<<(h[1] + SAH_WARPS - 1) / SAH_WARPS, SAH_WARPS * 32, 0, st>>>(d_small, h[1], idx_out, d_lo, d_hi, d_children,
+                                                                                          d_parent, d_order_k, n);
+            ++*launches;
+        }
+        SCK(cudaMemsetAsync(d_counters, 0, sizeof(uint32_t) * 2, st));
+        n_seg = h[0];
+        SahSeg* ts = seg_in; seg_in = seg_out; seg_out = ts;
+        uint32_t* ti = idx_in; idx_in = idx_out; idx_out = ti;
+    }
+    sah_compose_kernel<<<sah_grid_for(n, 256, 148 * 16), 256, 0, st>>>(d_order_k, d_sorted_idx, n, d_order_out);
+    ++*launches;
+    SCK(cudaStreamSynchronize(st));
+    SCK(cudaGetLastError());
+    if (out_levels) *out_levels = levels;
+    cleanup();
+    return cudaSuccess;
+}
+
+}  // namespace ff

@@ -204,14 +204,96 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_any_kernel(DevScene sc, 
         occluded[i] = best.slot >= 0 ? 1 : 0;
     }
 }
+// Any-hit with persistent warps + dynamic fetch (same scheduling as the closest-hit kernel).  Serves ff_trace_any
+// (tmax from an array, result = occluded flags) and the wavefront's shadow stage (tmax in ray_d.w, path id in ray_o.w;
+// an unoccluded entry adds its contribution to radiance[path] -- one shadow ray per path per bounce, stages are
+// stream-ordered, so a plain read-modify-write is race free and the sum order matches the CPU restatement).
+__global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_any_persistent_kernel(DevScene sc, const float4* __restrict__ ray_o,
+                                                                               const float4* __restrict__ ray_d,
+                                                                               const float* __restrict__ tmax_array, int tmax_in_dw,
+                                                                               const uint32_t* __restrict__ count_ptr, uint32_t n_max,
+                                                                               unsigned char* __restrict__ occluded,
+                                                                               const float4* __restrict__ contrib,
+                                                                               float4* __restrict__ radiance, uint32_t* work_counter) {
+    __shared__ uint2 sm_stack[(FF_SM_STACK + FF_TRI_QUEUE) * FF_TRACE_BLOCK];
+    const uint32_t n = count_ptr ? min(*count_ptr, n_max) : n_max;
+    const int lane = threadIdx.x & 31;
+    uint2* my_stack = sm_stack + threadIdx.x;
+    bool has = false, exhausted = false;
+    uint32_t ray_index = 0, path = 0;
+    RayCtx r;
+    Trav tv;
+    Best best;
+    unsigned cn = 0, ct = 0;
+    auto finish = [&]() {
+        const bool occ = best.slot >= 0;
+        if (occluded) occluded[ray_index] = occ ? 1 : 0;
+        if (radiance && !occ) {
+            const float4 c = __ldg(contrib + ray_index);
+            float4 a = radiance[path];
+            a.x = fadd(a.x, c.x); a.y = fadd(a.y, c.y); a.z = fadd(a.z, c.z);
+            radiance[path] = a;
+        }
+    };
+    for (;;) {
+        const unsigned need = __ballot_sync(0xffffffffu, !has);
+        if (need && !exhausted) {
+            uint32_t base = 0;
+            const int leader = __ffs(need) - 1;
+            if (lane == leader) base = atomicAdd(work_counter, (uint32_t)__popc(need));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (base + (uint32_t)__popc(need) >= n) exhausted = true;
+            if (!has) {
+                const uint32_t i = base + __popc(need & ((1u << lane) - 1u));
+                if (i < n) {
+                    const float4 o4 = __ldg(ray_o + i), d4 = __ldg(ray_d + i);
+                    const V3 o = ld3(o4), draw = ld3(d4);
+                    const V3 dn = normalize(draw);
+                    best_init(best, tmax_in_dw ? d4.w : (tmax_array ? tmax_array[i] : INFINITY));
+                    test_planes<true>(sc, o, draw, best);
+                    r = make_ray_ctx(o, dn);
+                    tv.start(best.key);
+                    ray_index = i;
+                    path = __float_as_uint(o4.w);
+                    has = sc.n_nodes != 0 && best.slot < 0;
+                    if (!has) finish();
+                }
+            }
+        }
+        if (!__any_sync(0xffffffffu, has)) break;
+        if (has) {
+            for (;;) {
+                if (!bvh8_step<true, false>(sc, r, tv, best, my_stack, FF_TRACE_BLOCK, cn, ct)) {
+                    finish();
+                    has = false;
+                    break;
+                }
+                if (!exhausted && __popc(__activemask()) < sc.refill_lanes) break;
+            }
+        }
+        __syncwarp();
+    }
+}
+
 void k_trace_any(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const float* d_tmax, uint32_t n, int mode,
-                 unsigned char* d_occluded, cudaStream_t st) {
+                 unsigned char* d_occluded, uint32_t* d_work_counter, cudaStream_t st) {
     if (n == 0) return;
-    const int g = grid_for(n, FF_TRACE_BLOCK, 148 * 64);
     const int m = mode & 0xff;
+    if (m == FF_TRACE_BVH8 && d_work_counter && !(mode & FF_TRACE_STATIC)) {
+        const int g = grid_for(n, FF_TRACE_BLOCK, 148 * tuning().blocks_per_sm);
+        trace_any_persistent_kernel<<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_tmax, 0, nullptr, n, d_occluded, nullptr, nullptr, d_work_counter);
+        return;
+    }
+    const int g = grid_for(n, FF_TRACE_BLOCK, 148 * 64);
     if (m == FF_TRACE_BRUTE) trace_any_kernel<FF_TRACE_BRUTE><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_tmax, n, d_occluded);
     else if (m == FF_TRACE_BVH2) trace_any_kernel<FF_TRACE_BVH2><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_tmax, n, d_occluded);
     else trace_any_kernel<FF_TRACE_BVH8><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_tmax, n, d_occluded);
+}
+void k_trace_shadow(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const float4* d_contrib,
+                    const uint32_t* d_count, uint32_t n_max, float4* d_radiance, uint32_t* d_work_counter, cudaStream_t st) {
+    if (n_max == 0) return;
+    const int g = grid_for(n_max, FF_TRACE_BLOCK, 148 * tuning().blocks_per_sm);
+    trace_any_persistent_kernel<<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, nullptr, 1, d_count, n_max, nullptr, d_contrib, d_radiance, d_work_counter);
 }
 
 // ------------------------------------------------------------------ camera rays (kernel.cu:198-205)

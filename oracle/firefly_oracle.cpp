@@ -470,21 +470,79 @@ void parallel_for(size_t n, int nthreads, F f) {
 struct OScene {
     Scene sc;
     Flat flat;
+    std::vector<int> lights;  // flat indices of the triangles of emitter meshes, in flat order
     bool flat_valid = false;
     const Flat& get_flat() {
-        if (!flat_valid) { flat = Flat(); flatten(sc, flat); flat_valid = true; }
+        if (!flat_valid) {
+            flat = Flat(); flatten(sc, flat); flat_valid = true;
+            lights.clear();
+            for (size_t k = 0; k < flat.tris.size(); ++k) if (sc.mats[flat.geom[k]].type == 0) lights.push_back((int)k);
+        }
         return flat;
     }
+    const std::vector<int>& get_lights() { get_flat(); return lights; }
 };
+
+// Shadow-ray query: is any front-facing triangle (or plane) hit with closest-hit key < tmax?  Same test and
+// key as intersectFlat, existence instead of minimum, so the answer does not depend on the scan order.
+bool occludedFlat(const Ray& ray, float tmax, const Scene& sc, const Flat& f) {
+    Ray os{ray.o, normalize(ray.d)};
+    for (size_t k = 0; k < f.tris.size(); ++k) {
+        Hit local;
+        if (intersectTriangle(f.tris[k], os, local) && distance(local.point, ray.o) < tmax) return true;
+    }
+    for (const Geom& g : sc.geoms) {
+        if (g.type != PLANE) continue;
+        Ray ps{xyz(mulMV(g.inv, v4(ray.o, 1.f))), xyz(normalize4(mulMV(g.inv, v4(ray.d, 0.f))))};
+        Hit local;
+        if (intersectPlane(g, ps, local) && distance(xyz(mulMV(g.model, v4(local.point, 1.0f))), ray.o) < tmax) return true;
+    }
+    return false;
+}
 
 // The as-intended path tracer.  One path.
 struct RenderParams {
-    int spp, max_bounces; uint32_t seed_lo, seed_hi; int first_sample; int aa; float background[3]; float ray_eps;
+    int spp, max_bounces; uint32_t seed_lo, seed_hi; int first_sample; int aa; float background[3]; float ray_eps; int nee;
 };
 inline V3 mul3(V3 a, V3 b) { return V3{a.x * b.x, a.y * b.y, a.z * b.z}; }
+
+// Next-event estimation (the north star's shadow-ray stage): one light sample per diffuse
+// shading event.  Lights = the triangles of emitter meshes, in flat order.  A triangle is picked uniformly, a point
+// uniformly on it; the emitter radiates from its front side only, the side the closest-hit test can see.
+// Returns false when the sample carries nothing; otherwise the shadow ray (origin `so`, unnormalised direction
+// `sd`, limit `tmax`) and the radiance `contrib` to add when it is unoccluded.
+bool sample_light(const OScene& os, const Flat& f, const std::vector<int>& lights, uint32_t pixel, uint32_t sample, int b,
+                  const RenderParams& rp, V3 so, V3 n, V3 beta, V3& sd, float& tmax, V3& contrib) {
+    const uint32_t nl = (uint32_t)lights.size();
+    if (nl == 0) return false;
+    U4 r = philox4x32_10(U4{pixel, sample, (uint32_t)b, 2u}, rp.seed_lo, rp.seed_hi);
+    uint32_t k = (uint32_t)(u01(r.x) * (float)nl);
+    if (k > nl - 1) k = nl - 1;
+    const int fi = lights[k];
+    const Tri& t = f.tris[fi];
+    float su = std::sqrt(u01(r.y));
+    float b0 = 1.0f - su, b1 = u01(r.z) * su;
+    float b2 = (1.0f - b0) - b1;
+    V3 y = add(add(mul(t.v0, b0), mul(t.v1, b1)), mul(t.v2, b2));
+    V3 N = cross(sub(t.v1, t.v0), sub(t.v2, t.v0));
+    float len = length(N);
+    sd = sub(y, so);
+    float dist2 = dot(sd, sd);
+    float dist = std::sqrt(dist2);
+    float cosx = dot(n, sd) / dist;
+    float cosl = (-dot(N, sd) / dist) / len;
+    if (!(cosx > 0.0f && cosl > 0.0f && dist2 > 0.0f)) return false;
+    float w = (((cosx * cosl) / dist2) * (0.5f * len)) * ((float)nl * 0.318309886183790672f);
+    const Material& m = os.sc.mats[f.geom[fi]];
+    contrib = mul(mul3(beta, mul(m.emissive, m.intensity)), w);
+    tmax = dist * 0.999f;
+    return true;
+}
+
 V3 trace_path(OScene& os, const Camera& cam, const M4& invVP, int x, int y, uint32_t sample, const RenderParams& rp,
-              long* ray_count) {
+              long* ray_count, long* shadow_count = nullptr) {
     const Flat& f = os.get_flat();
+    const std::vector<int>& lights = os.get_lights();
     uint32_t pixel = (uint32_t)(y * (int)cam.width + x);
     float px = (float)x, py = (float)y;
     if (rp.aa) {
@@ -499,7 +557,13 @@ V3 trace_path(OScene& os, const Camera& cam, const M4& invVP, int x, int y, uint
         if (ray_count) ++*ray_count;
         if (!h.hit) { L = add(L, mul3(beta, bg)); break; }
         const Material& m = os.sc.mats[h.geom];
-        if (m.type == 0) { L = add(L, mul3(beta, mul(m.emissive, m.intensity))); break; }
+        if (m.type == 0) {
+            // with NEE the direct light of sampled emitters (mesh emitters) arrives through the shadow rays;
+            // a BSDF-sampled hit on one counts only for the camera ray
+            const bool sampled = rp.nee && h.tri >= 0 && !lights.empty();
+            if (!sampled || b == 0) L = add(L, mul3(beta, mul(m.emissive, m.intensity)));
+            break;
+        }
         if (b == rp.max_bounces) break;
         V3 n = normalize(h.normal);
         if (dot(n, ray.d) > 0.0f) n = neg(n);
@@ -511,6 +575,13 @@ V3 trace_path(OScene& os, const Camera& cam, const M4& invVP, int x, int y, uint
         V3 d = add(add(mul(t, w.x), mul(bt, w.y)), mul(n, w.z));
         ray.o = add(h.point, mul(n, rp.ray_eps));
         ray.d = d;
+        if (rp.nee) {
+            V3 sd, contrib; float tmax;
+            if (sample_light(os, f, lights, pixel, sample, b, rp, ray.o, n, beta, sd, tmax, contrib)) {
+                if (shadow_count) ++*shadow_count;
+                if (!occludedFlat(Ray{ray.o, sd}, tmax, os.sc, f)) L = add(L, contrib);
+            }
+        }
     }
     return L;
 }
@@ -717,24 +788,25 @@ void orc_make_rays_uniform(long first, long n, uint32_t salt, float* rays6) {
 // mat table comes from the scene.  Returns the number of closest-hit rays traced.
 long orc_render(void* s, const float pos[3], const float world_up[3], float yaw, float pitch, float fov, int width,
                 int height, float near_clip, float far_clip, int spp, int max_bounces, uint32_t seed_lo,
-                uint32_t seed_hi, int first_sample, int aa, const float background[3], float ray_eps, float* out_rgba,
-                int nthreads) {
+                uint32_t seed_hi, int first_sample, int aa, const float background[3], float ray_eps, int nee,
+                float* out_rgba, long* out_shadow_rays, int nthreads) {
     OScene* os = (OScene*)s;
     os->get_flat();
     Camera cam = make_camera(pos, world_up, yaw, pitch, fov, (float)width, (float)height, near_clip, far_clip);
     M4 invVP = mulMM(cam.invView(), cam.invProj());
-    RenderParams rp{spp, max_bounces, seed_lo, seed_hi, first_sample, aa, {background[0], background[1], background[2]}, ray_eps};
-    std::vector<long> counts((size_t)std::max(1, nthreads) + 1, 0);
+    RenderParams rp{spp, max_bounces, seed_lo, seed_hi, first_sample, aa, {background[0], background[1], background[2]}, ray_eps, nee};
+    std::vector<long> counts((size_t)std::max(1, nthreads) + 1, 0), scounts((size_t)std::max(1, nthreads) + 1, 0);
     long* cptr = counts.data();
+    long* sptr = scounts.data();
     int nt = std::max(1, nthreads);
     size_t chunk = ((size_t)height + nt - 1) / nt;
     parallel_for((size_t)height, nthreads, [=](size_t a, size_t b) {
-        long local = 0;
+        long local = 0, slocal = 0;
         for (size_t y = a; y < b; ++y)
             for (int x = 0; x < width; ++x) {
                 V3 sum{0, 0, 0};
                 for (int k = 0; k < spp; ++k) {  // samples accumulated in index order
-                    V3 L = trace_path(*os, cam, invVP, x, (int)y, (uint32_t)(first_sample + k), rp, &local);
+                    V3 L = trace_path(*os, cam, invVP, x, (int)y, (uint32_t)(first_sample + k), rp, &local, &slocal);
                     sum = add(sum, L);
                 }
                 float inv = 1.0f / (float)spp;
@@ -742,9 +814,12 @@ long orc_render(void* s, const float pos[3], const float world_up[3], float yaw,
                 px[0] = sum.x * inv; px[1] = sum.y * inv; px[2] = sum.z * inv; px[3] = 1.0f;
             }
         cptr[a / chunk] = local;
+        sptr[a / chunk] = slocal;
     });
-    long total = 0;
+    long total = 0, stotal = 0;
     for (long c : counts) total += c;
+    for (long c : scounts) stotal += c;
+    if (out_shadow_rays) *out_shadow_rays = stotal;
     return total;
 }
 

@@ -203,17 +203,20 @@ class OracleScene(_SceneBase):
         return rgb
 
     def render(self, cam, spp, max_bounces, seed=1234, first_sample=0, aa=0, background=(0, 0, 0), ray_eps=1e-4,
-               threads=None):
-        """As-intended path tracer. Returns (rgba[h,w,4] mean radiance, closest-hit rays traced)."""
+               threads=None, nee=0, want_shadow_rays=False):
+        """As-intended path tracer. Returns (rgba[h,w,4] mean radiance, closest-hit rays traced[, shadow rays])."""
         w, h = int(cam["width"]), int(cam["height"])
         out = np.empty((h, w, 4), np.float32)
         fn = self.o.f("render")
         fn.restype = C.c_long
+        shadow = C.c_long(0)
         n = fn(self.h, _vec3(cam["pos"]), _vec3(cam.get("world_up", (0, 1, 0))), C.c_float(cam["yaw"]),
                C.c_float(cam["pitch"]), C.c_float(cam["fov"]), w, h, C.c_float(cam["near"]), C.c_float(cam["far"]),
                int(spp), int(max_bounces), C.c_uint32(seed & 0xFFFFFFFF), C.c_uint32((seed >> 32) & 0xFFFFFFFF),
-               int(first_sample), int(aa), _vec3(background), C.c_float(ray_eps), _ptr(out),
+               int(first_sample), int(aa), _vec3(background), C.c_float(ray_eps), int(nee), _ptr(out), C.byref(shadow),
                int(threads or self.o.threads))
+        if want_shadow_rays:
+            return out, n, shadow.value
         return out, n
 
 

@@ -243,3 +243,60 @@ def test_instrumented_counts_and_device_entry(ff, ctx):
     out = d_out.download(np.float32, nb * 8).reshape(2, nb, 4)
     assert np.allclose(np.linalg.norm(out[1, :, :3], axis=1), 1, atol=1e-5)
     assert (out[0, :, :3] > -0.1).all() and (out[0, :, :3] < 1.1).all()
+
+
+# ----------------------------------------------------------------------------- binned-SAH builder (FF_BUILDER_SAH)
+@pytest.mark.parametrize("n_tris", [1, 2, 3, 31, 32, 33, 34, 100, 1000, 20000, 200000])
+def test_sah_builder_matches_brute_force(ff, ctx, n_tris):
+    """The quality builder produces a different tree, never different hits: every size around the warp-kernel /
+    CTA-kernel switch (32 | 33), BVH8 and BVH2 over the SAH tree against GPU brute force and against the LBVH tree."""
+    soup = ctx.make_soup(n_tris, s=0.2 if n_tris < 1000 else None)
+    sc = ctx.scene()
+    sc.add_triangles(soup)
+    sc.commit(ff.BUILDER_SAH)
+    info = sc.info()
+    assert info["n_triangles"] == n_tris and info["builder"] == ff.BUILDER_SAH and info["depth"] <= 32
+    nr = 1 << 15
+    rays = ctx.make_rays_uniform(0, nr, salt=9)
+    brute = sc.trace_closest(rays, ff.TRACE_BRUTE)
+    assert_hits_equal(sc.trace_closest(rays, ff.TRACE_BVH8), brute, "sah bvh8 vs brute")
+    assert_hits_equal(sc.trace_closest(rays, ff.TRACE_BVH2), brute, "sah bvh2 vs brute")
+    lb = ctx.scene()
+    lb.add_triangles(soup)
+    lb.commit(ff.BUILDER_LBVH)
+    assert_hits_equal(lb.trace_closest(rays, ff.TRACE_BVH8), brute, "lbvh vs brute")
+    if n_tris >= 20000:  # the point of the builder: a cheaper tree (fewer node visits per ray) on the soup
+        n = 1 << 16
+        d_rays, d_hits = ctx.alloc(n * 32), ctx.alloc(n * 16)
+        ctx.make_rays_uniform(0, n, device_buffer=d_rays, host=False)
+        a = sc.trace_closest_device(d_rays, n, d_hits, ff.TRACE_BVH8 | ff.TRACE_COUNT)
+        b = lb.trace_closest_device(d_rays, n, d_hits, ff.TRACE_BVH8 | ff.TRACE_COUNT)
+        assert a["nodes_visited"] < b["nodes_visited"], (a["nodes_visited"], b["nodes_visited"])
+        assert info["sah_cost"] < lb.info()["sah_cost"]
+
+
+def test_sah_builder_degenerate_inputs(ff, ctx):
+    """All centres identical (no plane separates them: segments are halved by position) and exact duplicates."""
+    tri = np.float32([[0, 0, 0, 1, 0, 0, 0, 1, 0]])
+    same = np.repeat(tri, 300, 0)
+    shifted = same.copy()
+    shifted[150:, 2::3] = 0.5  # two stacks of coincident triangles
+    rays = np.float32([[0.2, 0.2, 2, 0, 0, -1], [0.2, 0.2, 0.25, 0, 0, -1], [0.9, 0.9, 2, 0, 0, -1]])
+    for tris in (same, shifted):
+        sc = ctx.scene()
+        sc.add_triangles(tris)
+        sc.commit(ff.BUILDER_SAH)
+        got = sc.trace_closest(rays, ff.TRACE_BVH8)
+        assert_hits_equal(got, sc.trace_closest(rays, ff.TRACE_BRUTE), "degenerate sah")
+        assert got["tri"][0] == (150 if tris is shifted else 0)  # lowest index among coincident hits (kernel.cu:115)
+
+
+@pytest.mark.parametrize("cfg", ["C2", "C3"])
+def test_sah_builder_config_scenes_vs_oracle(ff, ctx, orc, meshes, cfg):
+    desc = S.config2(meshes, 64, 64) if cfg == "C2" else S.config3(meshes, 64, 36)
+    sc, cam = S.instantiate(desc, ctx, meshes, builder=ff.BUILDER_SAH)
+    osc = S.instantiate_on(desc, orc.scene(), meshes)
+    rays = ctx.camera_rays(cam)
+    assert_hits_equal(sc.trace_closest(rays), osc.intersect(rays, mode=1), "sah " + cfg)
+    want, _ = osc.render(desc["camera"], 2, 3, seed=3)
+    assert (bits(sc.render(cam, 2, 3, seed=3)) == bits(want)).all()

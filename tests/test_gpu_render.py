@@ -32,6 +32,25 @@ def test_wavefront_and_megakernel_bit_identical_to_oracle(ff, ctx, orc, meshes, 
     assert want[..., :3].max() > 0
 
 
+@pytest.mark.parametrize("cfg", ["C2", "C3"])
+def test_next_event_estimation_bit_identical_to_oracle(ff, ctx, orc, meshes, cfg):
+    """The shadow-ray stage (wavefront: shade -> shadow queue -> any-hit kernel; megakernel: shadow phase of the lane
+    state machine) against the oracle's NEE loop: same light samples, same visibility, sums in the same order."""
+    desc = descs(meshes)[cfg]
+    sc, cam = S.instantiate(desc, ctx, meshes)
+    osc = S.instantiate_on(desc, orc.scene(), meshes)
+    want, want_rays, want_shadow = osc.render(desc["camera"], desc["spp"], desc["max_bounces"], seed=77, aa=1, nee=1, want_shadow_rays=True)
+    assert want_shadow > 0
+    for integ in (ff.INTEGRATOR_WAVEFRONT, ff.INTEGRATOR_MEGAKERNEL):
+        got, st = sc.render(cam, desc["spp"], desc["max_bounces"], want_stats=True, integrator=integ, seed=77, aa=1, nee=1)
+        assert (bits(got) == bits(want)).all(), "%s integrator %d: max abs diff %g" % (cfg, integ, np.abs(got - want).max())
+        assert st["rays"] == want_rays and st["shadow_rays"] == want_shadow
+    off = sc.render(cam, desc["spp"], desc["max_bounces"], seed=77, aa=1, nee=0)
+    assert (off != want).any()
+    # passes of different size give the same image (the shadow queue is per pass)
+    assert (bits(sc.render(cam, desc["spp"], desc["max_bounces"], seed=77, aa=1, nee=1, samples_per_pass=2)) == bits(want)).all()
+
+
 def test_samples_per_pass_and_seed(ff, ctx, orc, meshes):
     desc = descs(meshes)["C2"]
     sc, cam = S.instantiate(desc, ctx, meshes)
@@ -109,8 +128,25 @@ def test_errors(ff, ctx, meshes):
     with pytest.raises(ff.FireflyError):
         sc.render(cam, 0, 1)
     with pytest.raises(ff.FireflyError):
-        sc.render(cam, 1, 1, nee=1)
+        sc.render(cam, 1, 1, nee=2)
+    assert sc.render(cam, 1, 1, nee=1).shape == (8, 8, 4)  # no emitter in the scene: NEE has nothing to sample
     with pytest.raises(ff.FireflyError):
         sc.trace_closest(np.zeros((4, 6), np.float32), mode=77)
     with pytest.raises(ff.FireflyError):
         ff.Context(10 ** 6)
+
+
+def test_scene_outlives_context(ff, meshes):
+    """Destroying a context releases its scenes' device memory; the orphaned handle fails cleanly and frees safely."""
+    if ff.device_count() == 0:
+        pytest.skip("no CUDA device")
+    c = ff.Context(0)
+    sc = c.scene()
+    sc.add_triangles(meshes["cube"])
+    sc.commit()
+    c.close()
+    with pytest.raises(ff.FireflyError):
+        sc.trace_closest(np.zeros((1, 6), np.float32))
+    with pytest.raises(ff.FireflyError):
+        sc.commit()
+    sc.close()

@@ -381,6 +381,7 @@ int ff_scene_commit(ff_scene* scene, int builder, double* out_build_ms) {
     d.bvh2_lo = scene->d_bvh2_lo; d.bvh2_hi = scene->d_bvh2_hi; d.bvh2_leaf_slot = scene->d_leaf_slot;
     d.n_tris = (uint32_t)n_tris; d.n_nodes = bo.n_nodes; d.n_planes = (uint32_t)n_planes; d.n_geoms = (uint32_t)scene->geoms.size();
     d.wide_depth = bo.depth;
+    d.prmt_magic = 0x4B000000u;
     d.postpone_div = (uint32_t)tuning().postpone_div; d.refill_lanes = (uint32_t)tuning().refill_lanes;
     for (int k = 0; k < 3; ++k) { d.bounds_lo[k] = blo[k]; d.bounds_hi[k] = bhi[k]; }
 

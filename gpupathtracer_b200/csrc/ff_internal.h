@@ -51,6 +51,7 @@ struct DevScene {
     const uint32_t* bvh2_leaf_slot;  // sorted position -> slot in tris
     uint32_t n_tris, n_nodes, n_planes, n_geoms, n_lights;
     uint32_t wide_depth;
+    uint32_t prmt_magic;         // 0x4B000000 (2^23 as float bits), see byte_to_float in ff_trace.cuh
     float pad;                   // absolute inflation applied to every leaf box (conservative culling)
     uint32_t postpone_div;       // triangle groups are postponed when fewer than live/postpone_div lanes have any
     uint32_t refill_lanes;       // persistent kernel: refill idle lanes when fewer than this many still traverse

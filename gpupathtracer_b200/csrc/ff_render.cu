@@ -100,6 +100,7 @@ __device__ __forceinline__ void sample_light(const DevScene& sc, const RenderDev
 // One shading event of the written-down algorithm.  Returns true when the path continues (o, d, beta updated, and with
 // next-event estimation `sr` describes the shadow ray of this event); otherwise L has received the path's terminal
 // contribution.
+template <bool NEE>
 __device__ __forceinline__ bool shade_event(const DevScene& sc, const RenderDev& rp, const HitRec& h, uint32_t pixel, uint32_t sample,
                                             int bounce, V3& o, V3& d, V3& beta, V3& L, ShadowReq& sr) {
     sr.valid = false;
@@ -114,7 +115,7 @@ __device__ __forceinline__ bool shade_event(const DevScene& sc, const RenderDev&
     if (__float_as_int(m0.x) == FF_MAT_EMITTER) {
         // with NEE the direct light of mesh emitters arrives through the shadow rays; a BSDF-sampled hit on one
         // counts only for the camera ray
-        const bool sampled = rp.nee && !(h.slot & 0x40000000) && sc.n_lights != 0;
+        const bool sampled = NEE && rp.nee && !(h.slot & 0x40000000) && sc.n_lights != 0;
         if (!sampled || bounce == 0) L = add(L, mul3(beta, mul(v3(m1.x, m1.y, m1.z), m1.w)));
         return false;
     }
@@ -128,7 +129,7 @@ __device__ __forceinline__ bool shade_event(const DevScene& sc, const RenderDev&
     onb(n, t, bt);
     d = add(add(mul(t, w.x), mul(bt, w.y)), mul(n, w.z));
     o = add(P, mul(n, rp.ray_eps));
-    if (rp.nee) sample_light(sc, rp, pixel, sample, bounce, o, n, beta, sr);
+    if (NEE && rp.nee) sample_light(sc, rp, pixel, sample, bounce, o, n, beta, sr);
     return true;
 }
 
@@ -151,6 +152,7 @@ __global__ void wf_raygen_kernel(CamDev cam, RenderDev rp, float4* __restrict__ 
 
 // shade + BSDF sampling + warp-aggregated queue compaction: survivors are appended to the next bounce's queue
 // with one atomicAdd per warp (ballot + popc), so the next extend stage reads a dense, coalesced ray array.
+template <bool NEE>
 __global__ void __launch_bounds__(256) wf_shade_kernel(DevScene sc, RenderDev rp, int bounce, const uint32_t* __restrict__ count_in,
                                                         uint32_t cap, const HitRec* __restrict__ hits,
                                                         const float4* __restrict__ ray_o_in, const float4* __restrict__ ray_d_in,
@@ -175,9 +177,9 @@ __global__ void __launch_bounds__(256) wf_shade_kernel(DevScene sc, RenderDev rp
             const uint32_t s = path / rp.npix, pixel = path - s * rp.npix;
             o = ld3(o4); d = ld3(d4); beta = ld3(b4);
             V3 L = v3(0.f, 0.f, 0.f);
-            alive = shade_event(sc, rp, h, pixel, rp.first_sample + s, bounce, o, d, beta, L, sr);
+            alive = shade_event<NEE>(sc, rp, h, pixel, rp.first_sample + s, bounce, o, d, beta, L, sr);
             if (!alive) {
-                if (rp.nee) {  // the shadow stages of earlier bounces have already added to this path
+                if (NEE) {  // the shadow stages of earlier bounces have already added to this path
                     const float4 a = radiance[path];
                     L = add(ld3(a), L);
                 }
@@ -197,7 +199,7 @@ __global__ void __launch_bounds__(256) wf_shade_kernel(DevScene sc, RenderDev rp
                 beta_out[q] = make_float4(beta.x, beta.y, beta.z, 0.f);
             }
         }
-        if (rp.nee) {  // shadow-ray queue of this bounce, compacted the same way
+        if (NEE) {  // shadow-ray queue of this bounce, compacted the same way
             const unsigned ms = __ballot_sync(0xffffffffu, sr.valid);
             if (ms) {
                 const int leader = __ffs(ms) - 1;
@@ -228,12 +230,17 @@ void k_wavefront_pass(const DevScene& sc, const CamDev& cam, const RenderDev& rp
         if (trace_events) cudaEventRecord(trace_events[(*n_trace_events)++], st);
         k_trace_closest(sc, wb.ray_o[in], wb.ray_d[in], wb.counts + b, n, trace_mode, wb.hits, d_counters, wb.counts + n_counts + b, st);
         if (trace_events) cudaEventRecord(trace_events[(*n_trace_events)++], st);
-        wf_shade_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(sc, rp, b, wb.counts + b, n, wb.hits, wb.ray_o[in], wb.ray_d[in],
+        const bool nee = rp.nee && sc.n_lights != 0;
+        if (nee) wf_shade_kernel<true><<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(sc, rp, b, wb.counts + b, n, wb.hits, wb.ray_o[in], wb.ray_d[in],
+                                                                   wb.beta[in], wb.ray_o[out], wb.ray_d[out], wb.beta[out],
+                                                                   wb.radiance, wb.counts + b + 1, wb.sh_o, wb.sh_d, wb.sh_c,
+                                                                   wb.counts + 2 * n_counts + b);
+        else wf_shade_kernel<false><<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(sc, rp, b, wb.counts + b, n, wb.hits, wb.ray_o[in], wb.ray_d[in],
                                                                    wb.beta[in], wb.ray_o[out], wb.ray_d[out], wb.beta[out],
                                                                    wb.radiance, wb.counts + b + 1, wb.sh_o, wb.sh_d, wb.sh_c,
                                                                    wb.counts + 2 * n_counts + b);
         *launches += 2;
-        if (rp.nee && sc.n_lights != 0 && b < rp.max_bounces) {  // shadow stage: any-hit over this bounce's light samples
+        if (nee && b < rp.max_bounces) {  // shadow stage: any-hit over this bounce's light samples
             if (trace_events) cudaEventRecord(trace_events[(*n_trace_events)++], st);
             k_trace_shadow(sc, wb.sh_o, wb.sh_d, wb.sh_c, wb.counts + 2 * n_counts + b, n, wb.radiance, wb.counts + 3 * n_counts + b, st);
             if (trace_events) cudaEventRecord(trace_events[(*n_trace_events)++], st);
@@ -246,6 +253,8 @@ void k_wavefront_pass(const DevScene& sc, const CamDev& cam, const RenderDev& rp
 // One thread owns one path from camera to termination (the shape of the reference's launchPathTrace, kernel.cu:186-221,
 // with the bounce loop it intends).  Warps are persistent: a lane whose path has terminated pulls the next path id from
 // a global counter as soon as a few lanes are idle, so a warp never waits for its longest path.
+// NEE is a template parameter so that the plain loop does not carry the shadow phase's registers.
+template <bool NEE>
 __global__ void __launch_bounds__(FF_TRACE_BLOCK) megakernel(DevScene sc, CamDev cam, RenderDev rp, float4* __restrict__ radiance,
                                                               uint32_t* work_counter, unsigned long long* ray_counter) {
     __shared__ uint2 sm_stack[(FF_SM_STACK + FF_TRI_QUEUE) * FF_TRACE_BLOCK];
@@ -259,6 +268,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) megakernel(DevScene sc, CamDev
     V3 o = v3(0, 0, 0), d = v3(0, 0, 1), beta = v3(1, 1, 1), L = v3(0, 0, 0), pending = v3(0, 0, 0);
     RayCtx r;
     Trav tv;
+    uint2 lstack[FF_LOCAL_STACK];
     Best best;
     unsigned rays = 0, shadow_rays = 0, cn = 0, ct = 0;
     // (re)starts the closest-hit traversal of the segment (o, d)
@@ -299,8 +309,8 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) megakernel(DevScene sc, CamDev
                 // A shadow ray runs through the same closest-hit step (no second copy of the traversal in the loop, no
                 // divergence between lanes in different phases): its search interval starts at tmax and the first accepted
                 // hit ends it, which is the any-hit answer "some front-facing hit with key < tmax".
-                const bool more = bvh8_step<false, false>(sc, r, tv, best, my, FF_TRACE_BLOCK, cn, ct);
-                if (shadow) {
+                const bool more = bvh8_step<false, false>(sc, r, tv, best, my, FF_TRACE_BLOCK, lstack, cn, ct);
+                if (NEE && shadow) {
                     if (!more || best.slot >= 0) {
                         if (best.slot < 0) L = add(L, pending);
                         start_segment();
@@ -310,9 +320,9 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) megakernel(DevScene sc, CamDev
                     HitRec h;
                     h.key = best.key; h.t = best.t; h.slot = best.slot; h.ord = best.slot < 0 ? -1 : best.ord;
                     ShadowReq sr;
-                    if (shade_event(sc, rp, h, pixel, sample, bounce, o, d, beta, L, sr)) {
+                    if (shade_event<NEE>(sc, rp, h, pixel, sample, bounce, o, d, beta, L, sr)) {
                         ++bounce;
-                        if (sr.valid) {
+                        if (NEE && sr.valid) {
                             ++shadow_rays;
                             pending = sr.contrib;
                             best_init(best, sr.tmax);
@@ -353,7 +363,9 @@ void k_megakernel_pass(const DevScene& sc, const CamDev& cam, const RenderDev& r
                        unsigned long long* d_ray_counter, uint32_t* launches, cudaStream_t st) {
     cudaMemsetAsync(d_work_counter, 0, sizeof(uint32_t), st);
     const uint32_t n = rp.samples * rp.npix;
-    megakernel<<<grid_for(n, FF_TRACE_BLOCK, 148 * tuning().blocks_per_sm), FF_TRACE_BLOCK, 0, st>>>(sc, cam, rp, d_radiance, d_work_counter, d_ray_counter);
+    const int g = grid_for(n, FF_TRACE_BLOCK, 148 * tuning().blocks_per_sm);
+    if (rp.nee && sc.n_lights != 0) megakernel<true><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, cam, rp, d_radiance, d_work_counter, d_ray_counter);
+    else megakernel<false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, cam, rp, d_radiance, d_work_counter, d_ray_counter);
     ++*launches;
 }
 

@@ -68,6 +68,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_closest_persistent_kerne
     uint32_t ray_index = 0;
     RayCtx r;
     Trav tv;
+    uint2 lstack[FF_LOCAL_STACK];
     Best best;
     unsigned cn = 0, ct = 0;
     for (;;) {
@@ -96,7 +97,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_closest_persistent_kerne
         if (!__any_sync(0xffffffffu, has)) break;
         if (has) {
             for (;;) {
-                if (!bvh8_step<false, false>(sc, r, tv, best, my_stack, FF_TRACE_BLOCK, cn, ct)) {
+                if (!bvh8_step<false, false>(sc, r, tv, best, my_stack, FF_TRACE_BLOCK, lstack, cn, ct)) {
                     store_hit(hits, ray_index, best);
                     has = false;
                     break;
@@ -223,6 +224,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_any_persistent_kernel(De
     uint32_t ray_index = 0, path = 0;
     RayCtx r;
     Trav tv;
+    uint2 lstack[FF_LOCAL_STACK];
     Best best;
     unsigned cn = 0, ct = 0;
     auto finish = [&]() {
@@ -263,7 +265,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_any_persistent_kernel(De
         if (!__any_sync(0xffffffffu, has)) break;
         if (has) {
             for (;;) {
-                if (!bvh8_step<true, false>(sc, r, tv, best, my_stack, FF_TRACE_BLOCK, cn, ct)) {
+                if (!bvh8_step<true, false>(sc, r, tv, best, my_stack, FF_TRACE_BLOCK, lstack, cn, ct)) {
                     finish();
                     has = false;
                     break;

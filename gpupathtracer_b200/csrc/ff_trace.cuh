@@ -125,15 +125,17 @@ __device__ __forceinline__ RayCtx make_ray_ctx(V3 o, V3 dn) {
 
 // Byte j of q as a float WITHOUT the int->float converter (I2F runs on the quarter-rate XU pipe, and 48 of them per
 // node saturated it: profiles/r01b): PRMT builds the bits of 2^23 + byte, one exact FADD removes the 2^23.
+// `magic` = 0x4B000000 read from the kernel parameters (DevScene::prmt_magic): as a compile-time constant it would
+// occupy PRMT's only immediate slot and push the byte selector into a register, which cost ~40 MOVs per node visit.
 template <int J>
-__device__ __forceinline__ float byte_to_float(uint32_t q) {
-    return __uint_as_float(__byte_perm(q, 0x4B000000u, 0x7540u + J)) - 8388608.0f;
+__device__ __forceinline__ float byte_to_float(uint32_t q, uint32_t magic) {
+    return __uint_as_float(__byte_perm(q, magic, 0x7540u + J)) - 8388608.0f;
 }
 
 // Fetches one node (5 x LDG.128), tests its 8 quantised child boxes against the ray and returns the hit mask:
 // bits 24..31 = inner children in traversal order, bits 0..23 = triangles of the leaf children.
 __device__ __forceinline__ uint32_t bvh8_child_hits(const float4* __restrict__ nodes, uint32_t node_index, const RayCtx& r, float tlimit,
-                                                    uint32_t& child_base, uint32_t& tri_base, uint32_t& imask) {
+                                                    uint32_t magic, uint32_t& child_base, uint32_t& tri_base, uint32_t& imask) {
     const size_t ni = (size_t)node_index * 5;
     const float4 n0 = __ldg(nodes + ni), n1 = __ldg(nodes + ni + 1), n2 = __ldg(nodes + ni + 2), n3 = __ldg(nodes + ni + 3),
                  n4 = __ldg(nodes + ni + 4);
@@ -163,12 +165,12 @@ __device__ __forceinline__ uint32_t bvh8_child_hits(const float4* __restrict__ n
         const uint32_t nearz = nz ? qhiz : qloz, farz = nz ? qloz : qhiz;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            const float tnx = fmaf(j == 0 ? byte_to_float<0>(nearx) : j == 1 ? byte_to_float<1>(nearx) : j == 2 ? byte_to_float<2>(nearx) : byte_to_float<3>(nearx), ax, ox);
-            const float tny = fmaf(j == 0 ? byte_to_float<0>(neary) : j == 1 ? byte_to_float<1>(neary) : j == 2 ? byte_to_float<2>(neary) : byte_to_float<3>(neary), ay, oy);
-            const float tnz = fmaf(j == 0 ? byte_to_float<0>(nearz) : j == 1 ? byte_to_float<1>(nearz) : j == 2 ? byte_to_float<2>(nearz) : byte_to_float<3>(nearz), az, oz);
-            const float tfx = fmaf(j == 0 ? byte_to_float<0>(farx) : j == 1 ? byte_to_float<1>(farx) : j == 2 ? byte_to_float<2>(farx) : byte_to_float<3>(farx), ax, ox);
-            const float tfy = fmaf(j == 0 ? byte_to_float<0>(fary) : j == 1 ? byte_to_float<1>(fary) : j == 2 ? byte_to_float<2>(fary) : byte_to_float<3>(fary), ay, oy);
-            const float tfz = fmaf(j == 0 ? byte_to_float<0>(farz) : j == 1 ? byte_to_float<1>(farz) : j == 2 ? byte_to_float<2>(farz) : byte_to_float<3>(farz), az, oz);
+            const float tnx = fmaf(j == 0 ? byte_to_float<0>(nearx, magic) : j == 1 ? byte_to_float<1>(nearx, magic) : j == 2 ? byte_to_float<2>(nearx, magic) : byte_to_float<3>(nearx, magic), ax, ox);
+            const float tny = fmaf(j == 0 ? byte_to_float<0>(neary, magic) : j == 1 ? byte_to_float<1>(neary, magic) : j == 2 ? byte_to_float<2>(neary, magic) : byte_to_float<3>(neary, magic), ay, oy);
+            const float tnz = fmaf(j == 0 ? byte_to_float<0>(nearz, magic) : j == 1 ? byte_to_float<1>(nearz, magic) : j == 2 ? byte_to_float<2>(nearz, magic) : byte_to_float<3>(nearz, magic), az, oz);
+            const float tfx = fmaf(j == 0 ? byte_to_float<0>(farx, magic) : j == 1 ? byte_to_float<1>(farx, magic) : j == 2 ? byte_to_float<2>(farx, magic) : byte_to_float<3>(farx, magic), ax, ox);
+            const float tfy = fmaf(j == 0 ? byte_to_float<0>(fary, magic) : j == 1 ? byte_to_float<1>(fary, magic) : j == 2 ? byte_to_float<2>(fary, magic) : byte_to_float<3>(fary, magic), ay, oy);
+            const float tfz = fmaf(j == 0 ? byte_to_float<0>(farz, magic) : j == 1 ? byte_to_float<1>(farz, magic) : j == 2 ? byte_to_float<2>(farz, magic) : byte_to_float<3>(farz, magic), az, oz);
             const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
             const float tf = fminf(fminf(tfx, tfy), fminf(tfz, tlimit));
             if (tn <= tf) {
@@ -188,19 +190,21 @@ struct Trav {
     int sp;
     int qhead, qcount;      // ring of triangle groups waiting behind `tgroup`
     float tlimit;
-    uint2 lstack[FF_LOCAL_STACK];
+    // The spill part of the stack is NOT a member: a dynamically indexed array inside the struct would pin every field of
+    // the struct to local memory (the compiler then shadows each register update with an STL: ~40 wasted store sectors
+    // per ray in profiles/r01c).  Callers own `uint2 lstack[FF_LOCAL_STACK]` and pass it to push/pop.
     __device__ __forceinline__ void start(float best_key) {
         ngroup = make_uint2(0u, 0x80000000u);
         tgroup = make_uint2(0u, 0u);
         sp = 0; qhead = 0; qcount = 0;
         tlimit = best_key * FF_SLACK;
     }
-    __device__ __forceinline__ void push(uint2 v, uint2* sm, int stride) {
+    __device__ __forceinline__ void push(uint2 v, uint2* sm, int stride, uint2* lstack) {
         if (sp < FF_SM_STACK) sm[sp * stride] = v;
         else lstack[sp - FF_SM_STACK] = v;
         ++sp;
     }
-    __device__ __forceinline__ uint2 pop(uint2* sm, int stride) {
+    __device__ __forceinline__ uint2 pop(uint2* sm, int stride, const uint2* lstack) {
         --sp;
         return (sp < FF_SM_STACK) ? sm[sp * stride] : lstack[sp - FF_SM_STACK];
     }
@@ -235,17 +239,17 @@ __device__ __forceinline__ bool bvh8_test_one(const DevScene& sc, const RayCtx& 
 // is order independent, so the result is unchanged.  Returns false when the ray is finished.
 template <bool ANY, bool COUNT>
 __device__ __forceinline__ bool bvh8_step(const DevScene& sc, const RayCtx& r, Trav& tv, Best& best, uint2* sm, int stride,
-                                          unsigned& n_nodes, unsigned& n_tris) {
+                                          uint2* lstack, unsigned& n_nodes, unsigned& n_tris) {
     if (tv.ngroup.y & 0xff000000u) {
         const uint32_t hits_imask = tv.ngroup.y;
         const uint32_t bit = 31u - __clz(hits_imask);
         const uint32_t base = tv.ngroup.x;
         tv.ngroup.y &= ~(1u << bit);
-        if (tv.ngroup.y & 0xff000000u) tv.push(tv.ngroup, sm, stride);
+        if (tv.ngroup.y & 0xff000000u) tv.push(tv.ngroup, sm, stride, lstack);
         const uint32_t slot_index = (bit - 24u) ^ r.octinv;
         const uint32_t rel = __popc(hits_imask & ~(0xffffffffu << slot_index) & 0xffu);
         uint32_t imask, tri_base;
-        const uint32_t hitmask = bvh8_child_hits(sc.nodes, base + rel, r, tv.tlimit, tv.ngroup.x, tri_base, imask);
+        const uint32_t hitmask = bvh8_child_hits(sc.nodes, base + rel, r, tv.tlimit, sc.prmt_magic, tv.ngroup.x, tri_base, imask);
         if (COUNT) ++n_nodes;
         tv.ngroup.y = (hitmask & 0xff000000u) | imask;
         const uint32_t tmask = hitmask & 0x00ffffffu;
@@ -266,7 +270,7 @@ __device__ __forceinline__ bool bvh8_step(const DevScene& sc, const RayCtx& r, T
         if (tv.tgroup.y == 0u && tv.qcount > 0) tv.tgroup = tv.dequeue(sm, stride);
     }
     if ((tv.ngroup.y & 0xff000000u) == 0u) {
-        if (tv.sp > 0) tv.ngroup = tv.pop(sm, stride);
+        if (tv.sp > 0) tv.ngroup = tv.pop(sm, stride, lstack);
         else if (tv.tgroup.y == 0u) return false;
     }
     return true;
@@ -278,8 +282,9 @@ __device__ __forceinline__ void trace_bvh8(const DevScene& sc, V3 o, V3 dn, Best
     if (sc.n_nodes == 0) return;
     const RayCtx r = make_ray_ctx(o, dn);
     Trav tv;
+    uint2 lstack[FF_LOCAL_STACK];
     tv.start(best.key);
-    while (bvh8_step<ANY, COUNT>(sc, r, tv, best, sm_stack, sm_stride, n_nodes, n_tris)) {}
+    while (bvh8_step<ANY, COUNT>(sc, r, tv, best, sm_stack, sm_stride, lstack, n_nodes, n_tris)) {}
 }
 
 // Binary LBVH traversal (comparison / bridge variant).

@@ -71,6 +71,25 @@ def main():
             ctx.make_rays_uniform(0, n, device_buffer=d_rays, host=False)
             for m in a.modes.split(","):
                 print(json.dumps(dict(case="soupA_uniform_incoherent", mode=m, tris=a.tris, rays=n, **time_trace(ctx, sc, d_rays, n, d_hits, modes[m], a.reps))), flush=True)
+        if "soupA_sorted" in cases:
+            # experiment: the same batch with the rays regrouped on the host by (origin cell, direction octant); tells whether
+            # a device-side coherence sort in front of the extend stage would pay for itself
+            host = ctx.make_rays_uniform(0, n)
+            for bits in (3, 4, 5, 6):
+                q = np.minimum((host[:, :3] * (1 << bits)).astype(np.uint32), (1 << bits) - 1)
+                key = np.zeros(n, np.uint64)
+                for b in range(bits):
+                    for ax in range(3):
+                        key |= ((q[:, ax] >> b) & 1).astype(np.uint64) << np.uint64(3 * b + ax)
+                octant = ((host[:, 3] < 0).astype(np.uint64) << np.uint64(2)) | ((host[:, 4] < 0).astype(np.uint64) << np.uint64(1)) | (host[:, 5] < 0).astype(np.uint64)
+                for name, k in (("cell", key), ("cell+octant", (key << np.uint64(3)) | octant), ("octant+cell", (octant << np.uint64(3 * bits)) | key)):
+                    order = np.argsort(k, kind="stable")
+                    hs = host[order]
+                    packed = np.zeros((2 * n, 4), np.float32)
+                    packed[:n, :3] = hs[:, :3]
+                    packed[n:, :3] = hs[:, 3:]
+                    d_rays.upload(packed)
+                    print(json.dumps(dict(case="soupA_sorted", key=name, bits=bits, **time_trace(ctx, sc, d_rays, n, d_hits, modes["bvh8"], a.reps))), flush=True)
         if "soupB" in cases:
             cam = ff.Camera.from_dict(S.config4_camera())
             npr = cam.width * cam.height

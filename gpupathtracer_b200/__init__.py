@@ -77,6 +77,7 @@ lib.ff_context_create.argtypes = [C.POINTER(_vp), C.c_int]
 lib.ff_context_destroy.argtypes = [_vp]
 lib.ff_context_synchronize.argtypes = [_vp]
 lib.ff_timer_begin.argtypes = [_vp]
+lib.ff_context_release_scratch.argtypes = [_vp]
 lib.ff_timer_end.argtypes = [_vp, C.POINTER(C.c_double)]
 lib.ff_scene_create.argtypes = [_vp, C.POINTER(_vp)]
 lib.ff_scene_destroy.argtypes = [_vp]
@@ -280,6 +281,9 @@ class Context:
 
     def flush_l2(self):
         _check(lib.ff_flush_l2(self.h))
+
+    def release_scratch(self):
+        _check(lib.ff_context_release_scratch(self.h))
 
     def timer_begin(self):
         """CUDA-event bracket on the context's stream (device clock); pair with timer_end() -> milliseconds."""

@@ -45,6 +45,7 @@ struct ff_context {
     size_t flush_n = 0;
     cudaEvent_t timer_ev[2] = {nullptr, nullptr};  // ff_timer_begin / ff_timer_end
     bool timer_open = false;
+    Arena arena;                    // builder scratch, reused by every commit on this context
     std::vector<ff_scene*> scenes;  // live scenes: orphaned (device memory released) if the context goes first
 };
 
@@ -154,6 +155,7 @@ void ff_context_destroy(ff_context* ctx) {
     for (int k = 0; k < 4; ++k) cudaEventDestroy(ctx->ev[k]);
     for (int k = 0; k < 2; ++k) cudaEventDestroy(ctx->timer_ev[k]);
     cudaFree(ctx->flush_buf);
+    ctx->arena.release();
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -164,6 +166,13 @@ int ff_context_synchronize(ff_context* ctx) {
     return FF_OK;
 }
 
+int ff_context_release_scratch(ff_context* ctx) {
+    FF_REQUIRE(ctx, "ff_context_release_scratch: NULL context");
+    FF_CUDA(cudaSetDevice(ctx->device));
+    FF_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->arena.release();
+    return FF_OK;
+}
 int ff_timer_begin(ff_context* ctx) {
     FF_REQUIRE(ctx, "ff_timer_begin: NULL context");
     FF_CUDA(cudaSetDevice(ctx->device));
@@ -363,7 +372,7 @@ int ff_scene_commit(ff_scene* scene, int builder, double* out_build_ms) {
         FF_CUDA(cudaEventRecord(ctx->ev[0], st));
         cudaError_t be = bvh_build(scene->d_flat, (uint32_t)n_tris, builder, pad, scene->d_tris, scene->d_nodes, node_cap,
                                    scene->d_bvh2_children, scene->d_bvh2_lo, scene->d_bvh2_hi, scene->d_leaf_slot, blo, bhi, &bo,
-                                   &launches, st);
+                                   &launches, ctx->arena, st);
         if (be != cudaSuccess) { set_error(std::string("bvh_build: ") + cudaGetErrorString(be)); cudaGetLastError(); return FF_ERR_CUDA; }
         FF_CUDA(cudaEventRecord(ctx->ev[1], st));
         FF_CUDA(cudaEventSynchronize(ctx->ev[1]));

@@ -13,6 +13,9 @@
 //   meta: empty 0; inner child in slot s: 0x20 | (24 + s); leaf: (unary triangle count 1/3/7)<<5 | offset from tri_base
 //   child box (decoded) = p + q * 2^(e-127), always a superset of the exact child box.
 #include <cfloat>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include "ff_internal.h"
 
 namespace ff {
@@ -503,15 +506,26 @@ __global__ void collapse_kernel(const uint2* __restrict__ queue_in, uint32_t n_i
 
 cudaError_t sah_build_hierarchy(const float4* d_flat_tris, const uint32_t* d_sorted_idx, uint32_t n, const float centre_lo[3],
                                 const float centre_hi[3], int2* d_children, uint32_t* d_parent, uint32_t* d_order_out,
-                                uint32_t* launches, uint32_t* out_levels, cudaStream_t st);  // ff_sah.cu
+                                uint32_t* launches, uint32_t* out_levels, Arena& arena, cudaStream_t st);  // ff_sah.cu
+size_t sah_scratch_bytes(uint32_t n);
 
 cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float pad, float4* d_tris_out, float4* d_nodes_out,
                       uint32_t node_capacity, int2* d_bvh2_children, float4* d_bvh2_lo, float4* d_bvh2_hi,
                       uint32_t* d_bvh2_leaf_slot, float bounds_lo[3], float bounds_hi[3], BuildOut* out, uint32_t* launches,
-                      cudaStream_t st) {
+                      Arena& arena, cudaStream_t st) {
     out->n_nodes = 0; out->depth = 0; out->sah_cost = 0;
     for (int k = 0; k < 3; ++k) { bounds_lo[k] = 0; bounds_hi[k] = 0; }
     if (n == 0) return cudaSuccess;
+    // FF_BUILD_TRACE=1: per-stage wall times on stderr (synchronises after every stage; development aid)
+    const bool trace = getenv("FF_BUILD_TRACE") != nullptr;
+    auto t_last = std::chrono::steady_clock::now();
+    auto mark = [&](const char* what) {
+        if (!trace) return;
+        cudaStreamSynchronize(st);
+        const auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "[ff build] %-28s %9.3f ms\n", what, std::chrono::duration<double, std::milli>(now - t_last).count());
+        t_last = now;
+    };
     const uint32_t n_tiles = (n + RS_TILE - 1) / RS_TILE;
     int* d_bounds = nullptr;
     uint32_t *d_keys_a = nullptr, *d_keys_b = nullptr, *d_vals_a = nullptr, *d_vals_b = nullptr, *d_hist = nullptr;
@@ -519,22 +533,33 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
     float* d_cost = nullptr;
     uint2 *d_q0 = nullptr, *d_q1 = nullptr;
     CollapseCounters* d_ctr = nullptr;
-    CK(cudaMalloc(&d_bounds, 12 * sizeof(int)));
-    CK(cudaMalloc(&d_keys_a, sizeof(uint32_t) * n)); CK(cudaMalloc(&d_keys_b, sizeof(uint32_t) * n));
-    CK(cudaMalloc(&d_vals_a, sizeof(uint32_t) * n)); CK(cudaMalloc(&d_vals_b, sizeof(uint32_t) * n));
-    CK(cudaMalloc(&d_hist, sizeof(uint32_t) * 256 * (size_t)n_tiles));
-    CK(cudaMalloc(&d_parent, sizeof(uint32_t) * (2 * (size_t)n)));
-    CK(cudaMalloc(&d_flags, sizeof(uint32_t) * n));
-    CK(cudaMalloc(&d_cost, sizeof(float) * (2 * (size_t)n)));
-    CK(cudaMalloc(&d_q0, sizeof(uint2) * (size_t)node_capacity)); CK(cudaMalloc(&d_q1, sizeof(uint2) * (size_t)node_capacity));
-    CK(cudaMalloc(&d_ctr, sizeof(CollapseCounters)));
+    {
+        size_t need = Arena::padded(12 * sizeof(int)) + 4 * Arena::padded(sizeof(uint32_t) * n) + Arena::padded(sizeof(uint32_t) * 256 * (size_t)n_tiles) +
+                      Arena::padded(sizeof(uint32_t) * 2 * (size_t)n) + Arena::padded(sizeof(uint32_t) * n) + Arena::padded(sizeof(float) * 2 * (size_t)n) +
+                      2 * Arena::padded(sizeof(uint2) * (size_t)node_capacity) + Arena::padded(sizeof(CollapseCounters));
+        if (builder == FF_BUILDER_SAH) need += sah_scratch_bytes(n);
+        CK(arena.reserve(need));
+    }
+    d_bounds = arena.take<int>(12);
+    d_keys_a = arena.take<uint32_t>(n); d_keys_b = arena.take<uint32_t>(n);
+    d_vals_a = arena.take<uint32_t>(n); d_vals_b = arena.take<uint32_t>(n);
+    d_hist = arena.take<uint32_t>(256 * (size_t)n_tiles);
+    d_parent = arena.take<uint32_t>(2 * (size_t)n);
+    d_flags = arena.take<uint32_t>(n);
+    d_cost = arena.take<float>(2 * (size_t)n);
+    d_q0 = arena.take<uint2>(node_capacity); d_q1 = arena.take<uint2>(node_capacity);
+    d_ctr = arena.take<CollapseCounters>(1);
+    if (!d_ctr) return cudaErrorMemoryAllocation;
     CK(cudaMemsetAsync(d_flags, 0, sizeof(uint32_t) * n, st));
+    mark("reserve scratch");
 
     bounds_init_kernel<<<1, 32, 0, st>>>(d_bounds);
     bounds_kernel<<<grid_for(n, 256, 148 * 8), 256, 0, st>>>(d_flat_tris, n, d_bounds);
     morton_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(d_flat_tris, n, d_bounds, d_keys_a, d_vals_a);
     *launches += 3;
+    mark("bounds + morton");
     radix_sort_pairs(d_keys_a, d_vals_a, d_keys_b, d_vals_b, n, d_hist, launches, st);
+    mark("radix sort");
     int h_bounds[12];
     CK(cudaMemcpyAsync(h_bounds, d_bounds, sizeof(h_bounds), cudaMemcpyDeviceToHost, st));
     uint32_t* d_order = d_vals_a;  // position in the binary tree's leaf order -> flat triangle index
@@ -543,15 +568,18 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
         CK(cudaStreamSynchronize(st));
         float clo[3], chi[3];
         for (int k = 0; k < 3; ++k) { clo[k] = ordered_to_float(h_bounds[6 + k]); chi[k] = ordered_to_float(h_bounds[9 + k]); }
-        CK(sah_build_hierarchy(d_flat_tris, d_vals_a, n, clo, chi, d_bvh2_children, d_parent, d_vals_b, launches, nullptr, st));
+        CK(sah_build_hierarchy(d_flat_tris, d_vals_a, n, clo, chi, d_bvh2_children, d_parent, d_vals_b, launches, nullptr, arena, st));
         d_order = d_vals_b;
+        mark("binned-SAH hierarchy");
     } else if (n > 1) {
         hierarchy_kernel<<<grid_for(n - 1, 256, 148 * 16), 256, 0, st>>>(d_keys_a, (int)n, d_bvh2_children, d_parent);
         ++*launches;
+        mark("karras hierarchy");
     }
     refit_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(d_flat_tris, d_order, (int)n, pad, d_bvh2_children, d_parent, d_flags,
                                                             d_bvh2_lo, d_bvh2_hi, d_cost);
     ++*launches;
+    mark("refit + leaf/open DP");
 
     float4 root_lo, root_hi;
     const uint32_t root = (n == 1) ? 0u : 0u;  // internal node 0, or the single leaf (id n-1+0 = 0)
@@ -584,11 +612,10 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
         CK(cudaMemcpyAsync(&d_ctr->queue_count, &zero, sizeof(uint32_t), cudaMemcpyHostToDevice, st));
         uint2* t = qin; qin = qout; qout = t;
     }
+    mark("collapse to 8-wide");
     out->n_nodes = h_ctr.node_count;
     out->depth = depth;
     out->sah_cost = h_ctr.sah;
-    cudaFree(d_bounds); cudaFree(d_keys_a); cudaFree(d_keys_b); cudaFree(d_vals_a); cudaFree(d_vals_b); cudaFree(d_hist);
-    cudaFree(d_parent); cudaFree(d_flags); cudaFree(d_cost); cudaFree(d_q0); cudaFree(d_q1); cudaFree(d_ctr);
     return h_ctr.tri_count == n ? cudaSuccess : cudaErrorUnknown;
 }
 

@@ -89,6 +89,32 @@ struct TraceCounters { unsigned long long nodes, tris; };
 void k_bake_triangles(const float* d_xyz9_obj, const ffm::M4* d_model_per_geom, const uint32_t* d_geom_of_flat,
                       const uint32_t* d_ord_of_flat, uint32_t n, float4* d_flat_tris, cudaStream_t st);
 
+// Grow-only device scratch of a context, carved by a bump pointer: the builders take all their temporaries from it, so
+// a rebuild (the interactive case, and every build after the first) allocates nothing -- cudaMalloc/cudaFree of a dozen
+// arrays cost 10-30 ms per build, an order of magnitude more than the build kernels themselves.
+struct Arena {
+    char* base = nullptr;
+    size_t cap = 0, off = 0;
+    cudaError_t reserve(size_t bytes) {
+        off = 0;
+        if (bytes <= cap) return cudaSuccess;
+        if (base) cudaFree(base);
+        base = nullptr; cap = 0;
+        cudaError_t e = cudaMalloc((void**)&base, bytes);
+        if (e == cudaSuccess) cap = bytes;
+        return e;
+    }
+    template <class T>
+    T* take(size_t count) {
+        off = (off + 255) & ~(size_t)255;
+        T* p = (T*)(base + off);
+        off += sizeof(T) * count;
+        return off <= cap ? p : nullptr;
+    }
+    static size_t padded(size_t bytes) { return ((bytes + 255) & ~(size_t)255) + 256; }
+    void release() { if (base) cudaFree(base); base = nullptr; cap = off = 0; }
+};
+
 struct BuildOut {
     uint32_t n_nodes, depth;
     double sah_cost;
@@ -97,7 +123,7 @@ struct BuildOut {
 cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float pad, float4* d_tris_out,
                       float4* d_nodes_out, uint32_t node_capacity, int2* d_bvh2_children, float4* d_bvh2_lo,
                       float4* d_bvh2_hi, uint32_t* d_bvh2_leaf_slot, float bounds_lo[3], float bounds_hi[3],
-                      BuildOut* out, uint32_t* launches, cudaStream_t st);
+                      BuildOut* out, uint32_t* launches, Arena& arena, cudaStream_t st);
 
 void k_trace_closest(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const uint32_t* d_count,
                      uint32_t n_max, int mode, HitRec* d_hits, TraceCounters* d_counters, uint32_t* d_work_counter, cudaStream_t st);

@@ -73,15 +73,56 @@ __device__ __forceinline__ void sah_link(uint32_t n, uint32_t id, uint32_t b, ui
 }
 
 // ------------------------------------------------------------------ one CTA per segment of more than SAH_SMALL triangles
+#define SAH_BIG 8192           // segments above this are processed by many CTAs (see the big-segment kernels below)
+#define SAH_CHUNK 2048
 struct SahLists {
-    SahSeg* next;          // segments of the next level (> SAH_SMALL triangles)
+    SahSeg* next;          // segments of the next level with SAH_SMALL < size <= SAH_BIG (one CTA each)
     SahSeg* small;         // segments handed to the warp kernel
-    uint32_t* counters;    // [0] = entries in next, [1] = entries in small, [2] = deepest level seen
+    SahSeg* big;           // segments of the next level with more than SAH_BIG triangles
+    uint32_t* counters;    // [0] entries in next, [1] entries in small, [2] deepest level seen, [3] entries in big, [4] chunks of big
 };
+// Child [cb, ce) of a split goes to the list that fits its size; a single triangle is final.
+__device__ __forceinline__ void sah_append_child(const SahLists& lists, uint32_t cb, uint32_t ce, uint32_t cid, uint32_t level,
+                                                 const int* cbounds /*[6] ordered*/, const uint32_t* idx_out, uint32_t* final_order) {
+    const uint32_t cc = ce - cb;
+    if (cc == 1u) { final_order[cb] = idx_out[cb]; return; }
+    SahSeg c;
+    c.b = cb; c.e = ce; c.id = cid; c.level = level; c.pad0 = c.pad1 = 0;
+    for (int k = 0; k < 3; ++k) { c.clo[k] = sah_o2f(cbounds[k]); c.chi[k] = sah_o2f(cbounds[3 + k]); }
+    if (cc <= SAH_SMALL) lists.small[atomicAdd(lists.counters + 1, 1u)] = c;
+    else if (cc <= SAH_BIG) lists.next[atomicAdd(lists.counters + 0, 1u)] = c;
+    else {
+        c.pad1 = (cc + SAH_CHUNK - 1) / SAH_CHUNK;
+        c.pad0 = atomicAdd(lists.counters + 4, c.pad1);
+        lists.big[atomicAdd(lists.counters + 3, 1u)] = c;
+    }
+    atomicMax(lists.counters + 2, level);
+}
 
 __device__ __forceinline__ int sah_bin_of(float c2, float lo2, float scale) {
     const int b = (int)((c2 - lo2) * scale);
     return min(max(b, 0), SAH_BINS - 1);
+}
+
+// Candidate plane t (axis t / 15, left = bins [0, t % 15]) of a [3][SAH_BINS][7] bin table: SAH cost and left count.
+__device__ __forceinline__ void sah_eval_plane(const int* bins, int t, bool forced, float& cost_out, uint32_t& nl_out) {
+    const int a = t / (SAH_BINS - 1), plane = t % (SAH_BINS - 1);
+    float l[6] = {FLT_MAX, FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX}, r[6] = {FLT_MAX, FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX};
+    uint32_t nl = 0, nr = 0;
+    for (int k = 0; k < SAH_BINS; ++k) {
+        const int* bin = bins + (a * SAH_BINS + k) * 7;
+        if (bin[6] == 0) continue;
+        float* d = k <= plane ? l : r;
+        d[0] = fminf(d[0], sah_o2f(bin[0])); d[1] = fminf(d[1], sah_o2f(bin[1])); d[2] = fminf(d[2], sah_o2f(bin[2]));
+        d[3] = fmaxf(d[3], sah_o2f(bin[3])); d[4] = fmaxf(d[4], sah_o2f(bin[4])); d[5] = fmaxf(d[5], sah_o2f(bin[5]));
+        if (k <= plane) nl += (uint32_t)bin[6]; else nr += (uint32_t)bin[6];
+    }
+    float cost = FLT_MAX;
+    if (nl && nr && !forced)
+        cost = sah_half_area(l[0], l[1], l[2], l[3], l[4], l[5]) * (float)nl + sah_half_area(r[0], r[1], r[2], r[3], r[4], r[5]) * (float)nr;
+    if (!(cost < FLT_MAX)) cost = FLT_MAX;  // NaN boxes never win
+    cost_out = cost;
+    nl_out = nl;
 }
 
 __global__ void __launch_bounds__(SAH_BLOCK) sah_level_kernel(const SahSeg* __restrict__ segs, const uint32_t* __restrict__ idx_in,
@@ -134,25 +175,7 @@ __global__ void __launch_bounds__(SAH_BLOCK) sah_level_kernel(const SahSeg* __re
     __syncthreads();
 
     // 45 candidate planes: thread t -> axis t / 15, left = bins [0, plane]
-    if (tid < 3 * (SAH_BINS - 1)) {
-        const int a = tid / (SAH_BINS - 1), plane = tid % (SAH_BINS - 1);
-        float l[6] = {FLT_MAX, FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX}, r[6] = {FLT_MAX, FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX};
-        uint32_t nl = 0, nr = 0;
-        for (int k = 0; k < SAH_BINS; ++k) {
-            const int* bin = s_bins[a][k];
-            if (bin[6] == 0) continue;
-            float* d = k <= plane ? l : r;
-            d[0] = fminf(d[0], sah_o2f(bin[0])); d[1] = fminf(d[1], sah_o2f(bin[1])); d[2] = fminf(d[2], sah_o2f(bin[2]));
-            d[3] = fmaxf(d[3], sah_o2f(bin[3])); d[4] = fmaxf(d[4], sah_o2f(bin[4])); d[5] = fmaxf(d[5], sah_o2f(bin[5]));
-            if (k <= plane) nl += (uint32_t)bin[6]; else nr += (uint32_t)bin[6];
-        }
-        float cost = FLT_MAX;
-        if (nl && nr && !forced)
-            cost = sah_half_area(l[0], l[1], l[2], l[3], l[4], l[5]) * (float)nl + sah_half_area(r[0], r[1], r[2], r[3], r[4], r[5]) * (float)nr;
-        if (!(cost < FLT_MAX)) cost = FLT_MAX;  // NaN boxes never win
-        s_cost[tid] = cost;
-        s_nleft[tid] = nl;
-    }
+    if (tid < 3 * (SAH_BINS - 1)) sah_eval_plane(&s_bins[0][0][0], tid, forced, s_cost[tid], s_nleft[tid]);
     __syncthreads();
     if (tid == 0) {
         int best = -1;
@@ -222,18 +245,225 @@ __global__ void __launch_bounds__(SAH_BLOCK) sah_level_kernel(const SahSeg* __re
         uint32_t lid, rid;
         if (tid == 0) sah_link(n, s.id, b, m, e, children, parent, lid, rid);
         else { lid = (m - b == 1u) ? (n - 1u + b) : (m - 1u); rid = (e - m == 1u) ? (n - 1u + m) : m; }
-        const uint32_t cb = tid == 0 ? b : m, ce = tid == 0 ? m : e, cid = tid == 0 ? lid : rid, cc = ce - cb;
-        if (cc == 1u) {
-            final_order[cb] = idx_out[cb];
-        } else {
-            SahSeg c;
-            c.b = cb; c.e = ce; c.id = cid; c.level = s.level + 1; c.pad0 = c.pad1 = 0;
-            for (int k = 0; k < 3; ++k) { c.clo[k] = sah_o2f(s_cb[tid][k]); c.chi[k] = sah_o2f(s_cb[tid][3 + k]); }
-            if (cc <= SAH_SMALL) lists.small[atomicAdd(lists.counters + 1, 1u)] = c;
-            else lists.next[atomicAdd(lists.counters + 0, 1u)] = c;
-            atomicMax(lists.counters + 2, c.level);
+        sah_append_child(lists, tid == 0 ? b : m, tid == 0 ? m : e, tid == 0 ? lid : rid, s.level + 1, s_cb[tid], idx_out, final_order);
+    }
+}
+
+// ------------------------------------------------------------------ segments of more than SAH_BIG triangles: many CTAs each
+// One CTA per segment would leave the top levels (one segment of N triangles, then two of N/2, ...) on a handful of
+// SMs.  A big segment is cut into chunks of SAH_CHUNK triangles (SahSeg::pad0 = first chunk, pad1 = chunk count) and a
+// level takes five launches over all big segments of the level:
+//   prepare  clears the segment's global bin table, maps its chunks to it
+//   bin      one CTA per chunk: shared-memory bins, flushed to the segment's global table with atomics, and the
+//            chunk's own per-axis bin counts kept (they give the chunk's left count for ANY plane, so no third pass)
+//   split    one CTA per segment: the 45 planes, then an exclusive scan of the chunks' left counts -> every chunk knows
+//            where its left and right triangles go (stable, deterministic)
+//   scatter  one CTA per chunk: stable partition into the other order buffer; children's centre bounds by atomics
+//   emit     one thread per segment: links the node, appends the children to the big / CTA / warp lists
+struct SahBigSplit {
+    int axis, plane;
+    uint32_t nl, pad;
+    int cb[2][6];          // children's centre bounds (ordered ints)
+};
+struct SahBig {
+    const SahSeg* segs;        // big segments of this level
+    uint32_t n_segs;
+    uint32_t* chunk_seg;       // chunk -> index into segs
+    int* gbins;                // [n_segs][3][SAH_BINS][7]
+    uint32_t* chunk_hist;      // [chunks][3][SAH_BINS]
+    uint2* chunk_off;          // [chunks] {lefts before this chunk, rights before this chunk} within the segment
+    SahBigSplit* split;        // [n_segs]
+};
+
+__global__ void __launch_bounds__(SAH_BLOCK) sah_big_prepare_kernel(SahBig B) {
+    const SahSeg s = B.segs[blockIdx.x];
+    int* g = B.gbins + (size_t)blockIdx.x * 3 * SAH_BINS * 7;
+    for (int k = threadIdx.x; k < 3 * SAH_BINS * 7; k += SAH_BLOCK) {
+        const int f = k % 7;
+        g[k] = f < 3 ? sah_f2o(FLT_MAX) : (f < 6 ? sah_f2o(-FLT_MAX) : 0);
+    }
+    for (uint32_t c = threadIdx.x; c < s.pad1; c += SAH_BLOCK) B.chunk_seg[s.pad0 + c] = blockIdx.x;
+    if (threadIdx.x < 12) (&B.split[blockIdx.x].cb[0][0])[threadIdx.x] = (threadIdx.x % 6) < 3 ? sah_f2o(FLT_MAX) : sah_f2o(-FLT_MAX);
+}
+
+__global__ void __launch_bounds__(SAH_BLOCK) sah_big_bin_kernel(SahBig B, const uint32_t* __restrict__ idx_in,
+                                                                 const float4* __restrict__ box_lo, const float4* __restrict__ box_hi) {
+    __shared__ int s_bins[3][SAH_BINS][7];
+    const uint32_t si = B.chunk_seg[blockIdx.x];
+    const SahSeg s = B.segs[si];
+    const uint32_t cb = s.b + (blockIdx.x - s.pad0) * SAH_CHUNK, ce = min(cb + SAH_CHUNK, s.e);
+    const int tid = threadIdx.x;
+    for (int k = tid; k < 3 * SAH_BINS * 7; k += SAH_BLOCK) {
+        const int f = k % 7;
+        (&s_bins[0][0][0])[k] = f < 3 ? sah_f2o(FLT_MAX) : (f < 6 ? sah_f2o(-FLT_MAX) : 0);
+    }
+    float scale[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const float ext = s.chi[a] - s.clo[a];
+        scale[a] = ext > 0.f ? (float)SAH_BINS / ext : 0.f;
+    }
+    __syncthreads();
+    for (uint32_t i = cb + tid; i < ce; i += SAH_BLOCK) {
+        const uint32_t p = idx_in[i];
+        const float4 lo = __ldg(box_lo + p), hi = __ldg(box_hi + p);
+        const float c2[3] = {lo.x + hi.x, lo.y + hi.y, lo.z + hi.z};
+        const int ol[3] = {sah_f2o(lo.x), sah_f2o(lo.y), sah_f2o(lo.z)}, oh[3] = {sah_f2o(hi.x), sah_f2o(hi.y), sah_f2o(hi.z)};
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            int* bin = s_bins[a][sah_bin_of(c2[a], s.clo[a], scale[a])];
+            atomicMin(bin + 0, ol[0]); atomicMin(bin + 1, ol[1]); atomicMin(bin + 2, ol[2]);
+            atomicMax(bin + 3, oh[0]); atomicMax(bin + 4, oh[1]); atomicMax(bin + 5, oh[2]);
+            atomicAdd(bin + 6, 1);
         }
     }
+    __syncthreads();
+    int* g = B.gbins + (size_t)si * 3 * SAH_BINS * 7;
+    for (int k = tid; k < 3 * SAH_BINS; k += SAH_BLOCK) {
+        const int* bin = &s_bins[0][0][0] + k * 7;
+        B.chunk_hist[(size_t)blockIdx.x * 3 * SAH_BINS + k] = (uint32_t)bin[6];
+        if (bin[6]) {
+            int* d = g + k * 7;
+            atomicMin(d + 0, bin[0]); atomicMin(d + 1, bin[1]); atomicMin(d + 2, bin[2]);
+            atomicMax(d + 3, bin[3]); atomicMax(d + 4, bin[4]); atomicMax(d + 5, bin[5]);
+            atomicAdd(d + 6, bin[6]);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(SAH_BLOCK) sah_big_split_kernel(SahBig B) {
+    __shared__ float s_cost[3 * (SAH_BINS - 1)];
+    __shared__ uint32_t s_nleft[3 * (SAH_BINS - 1)];
+    __shared__ int s_axis, s_plane;
+    __shared__ uint32_t s_nl, s_carry;
+    __shared__ uint32_t s_warp[SAH_BLOCK / 32];
+    const SahSeg s = B.segs[blockIdx.x];
+    const uint32_t cnt = s.e - s.b;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const bool forced = s.level >= SAH_MAX_LEVELS;
+    if (tid < 3 * (SAH_BINS - 1)) sah_eval_plane(B.gbins + (size_t)blockIdx.x * 3 * SAH_BINS * 7, tid, forced, s_cost[tid], s_nleft[tid]);
+    __syncthreads();
+    if (tid == 0) {
+        int best = -1;
+        float bc = FLT_MAX;
+        for (int k = 0; k < 3 * (SAH_BINS - 1); ++k)
+            if (s_cost[k] < bc) { bc = s_cost[k]; best = k; }
+        if (best >= 0) { s_axis = best / (SAH_BINS - 1); s_plane = best % (SAH_BINS - 1); s_nl = s_nleft[best]; }
+        else { s_axis = -1; s_plane = 0; s_nl = cnt / 2; }
+        s_carry = 0;
+        SahBigSplit& sp = B.split[blockIdx.x];
+        sp.axis = s_axis; sp.plane = s_plane; sp.nl = s_nl; sp.pad = 0;
+    }
+    __syncthreads();
+    const int axis = s_axis, plane = s_plane;
+    const uint32_t nl = s_nl;
+    // exclusive scan of the chunks' left counts, SAH_BLOCK chunks per round
+    for (uint32_t c0 = 0; c0 < s.pad1; c0 += SAH_BLOCK) {
+        const uint32_t c = c0 + tid;
+        uint32_t mine = 0;
+        if (c < s.pad1) {
+            const uint32_t first = c * SAH_CHUNK, size = min((uint32_t)SAH_CHUNK, cnt - first);
+            if (axis < 0) mine = first >= nl ? 0u : min(size, nl - first);
+            else {
+                const uint32_t* h = B.chunk_hist + (size_t)(s.pad0 + c) * 3 * SAH_BINS + axis * SAH_BINS;
+                for (int k = 0; k <= plane; ++k) mine += h[k];
+            }
+        }
+        uint32_t incl = mine;
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, off);
+            if (lane >= off) incl += t;
+        }
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        uint32_t before = s_carry;
+        for (int w = 0; w < warp; ++w) before += s_warp[w];
+        const uint32_t left_before = before + incl - mine;
+        if (c < s.pad1) B.chunk_off[s.pad0 + c] = make_uint2(left_before, c * SAH_CHUNK - left_before);
+        __syncthreads();
+        if (tid == SAH_BLOCK - 1) s_carry = left_before + mine;
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(SAH_BLOCK) sah_big_scatter_kernel(SahBig B, const uint32_t* __restrict__ idx_in, uint32_t* __restrict__ idx_out,
+                                                                     const float4* __restrict__ box_lo, const float4* __restrict__ box_hi) {
+    __shared__ uint32_t s_warp_l[SAH_BLOCK / 32], s_warp_r[SAH_BLOCK / 32];
+    __shared__ uint32_t s_base_l, s_base_r;
+    const uint32_t si = B.chunk_seg[blockIdx.x];
+    const SahSeg s = B.segs[si];
+    const SahBigSplit sp = B.split[si];
+    const uint32_t cb = s.b + (blockIdx.x - s.pad0) * SAH_CHUNK, ce = min(cb + SAH_CHUNK, s.e);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int axis = sp.axis, plane = sp.plane;
+    const uint32_t nl = sp.nl;
+    const float ext = axis >= 0 ? s.chi[axis] - s.clo[axis] : 0.f;
+    const float scale = ext > 0.f ? (float)SAH_BINS / ext : 0.f;
+    if (tid == 0) {
+        const uint2 off = B.chunk_off[blockIdx.x];
+        s_base_l = s.b + off.x;
+        s_base_r = s.b + nl + off.y;
+    }
+    __syncthreads();
+    float cl[6] = {FLT_MAX, FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX}, cr[6] = {FLT_MAX, FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX};
+    for (uint32_t base = cb; base < ce; base += SAH_BLOCK) {
+        const uint32_t i = base + tid;
+        const bool live = i < ce;
+        uint32_t p = 0;
+        bool left = false;
+        if (live) {
+            p = idx_in[i];
+            const float4 lo = __ldg(box_lo + p), hi = __ldg(box_hi + p);
+            const float c2[3] = {lo.x + hi.x, lo.y + hi.y, lo.z + hi.z};
+            left = axis < 0 ? (i - s.b) < nl : sah_bin_of(axis == 0 ? c2[0] : (axis == 1 ? c2[1] : c2[2]), s.clo[axis], scale) <= plane;
+            float* d = left ? cl : cr;
+            d[0] = fminf(d[0], c2[0]); d[1] = fminf(d[1], c2[1]); d[2] = fminf(d[2], c2[2]);
+            d[3] = fmaxf(d[3], c2[0]); d[4] = fmaxf(d[4], c2[1]); d[5] = fmaxf(d[5], c2[2]);
+        }
+        const unsigned ml = __ballot_sync(0xffffffffu, live && left), mr = __ballot_sync(0xffffffffu, live && !left);
+        if (lane == 0) { s_warp_l[warp] = __popc(ml); s_warp_r[warp] = __popc(mr); }
+        __syncthreads();
+        uint32_t off_l = 0, off_r = 0, tot_l = 0, tot_r = 0;
+#pragma unroll
+        for (int w = 0; w < SAH_BLOCK / 32; ++w) {
+            if (w < warp) { off_l += s_warp_l[w]; off_r += s_warp_r[w]; }
+            tot_l += s_warp_l[w]; tot_r += s_warp_r[w];
+        }
+        if (live) {
+            const unsigned lt = (1u << lane) - 1u;
+            idx_out[left ? s_base_l + off_l + __popc(ml & lt) : s_base_r + off_r + __popc(mr & lt)] = p;
+        }
+        __syncthreads();
+        if (tid == 0) { s_base_l += tot_l; s_base_r += tot_r; }
+        __syncthreads();
+    }
+    int* gcb = &B.split[si].cb[0][0];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        float vl = cl[k], vr = cr[k];
+        for (int off = 16; off; off >>= 1) {
+            const float ol = __shfl_xor_sync(0xffffffffu, vl, off), orr = __shfl_xor_sync(0xffffffffu, vr, off);
+            vl = k < 3 ? fminf(vl, ol) : fmaxf(vl, ol);
+            vr = k < 3 ? fminf(vr, orr) : fmaxf(vr, orr);
+        }
+        if (lane == 0) {
+            if (k < 3) { atomicMin(gcb + k, sah_f2o(vl)); atomicMin(gcb + 6 + k, sah_f2o(vr)); }
+            else { atomicMax(gcb + k, sah_f2o(vl)); atomicMax(gcb + 6 + k, sah_f2o(vr)); }
+        }
+    }
+}
+
+__global__ void sah_big_emit_kernel(SahBig B, SahLists lists, const uint32_t* __restrict__ idx_out, int2* children, uint32_t* parent,
+                                    uint32_t* __restrict__ final_order, uint32_t n) {
+    const uint32_t si = blockIdx.x * blockDim.x + threadIdx.x;
+    if (si >= B.n_segs) return;
+    const SahSeg s = B.segs[si];
+    const SahBigSplit sp = B.split[si];
+    const uint32_t m = s.b + sp.nl;
+    uint32_t lid, rid;
+    sah_link(n, s.id, s.b, m, s.e, children, parent, lid, rid);
+    sah_append_child(lists, s.b, m, lid, s.level + 1, sp.cb[0], idx_out, final_order);
+    sah_append_child(lists, m, s.e, rid, s.level + 1, sp.cb[1], idx_out, final_order);
 }
 
 // ------------------------------------------------------------------ one warp per segment of <= SAH_SMALL triangles
@@ -354,26 +584,40 @@ __global__ void sah_compose_kernel(const uint32_t* __restrict__ order_k, const u
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) out[i] = sorted_idx[order_k[i]];
 }
 
-#define SCK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { cleanup(); return e_; } } while (0)
+#define SCK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return e_; } while (0)
+
+static inline size_t sah_seg_cap(uint32_t n) { return (size_t)n / (SAH_SMALL + 1) + 2; }
+static inline size_t sah_small_cap(uint32_t n) { return (size_t)n / 2 + 2; }
+static inline size_t sah_big_cap(uint32_t n) { return (size_t)n / (SAH_BIG + 1) + 2; }
+static inline size_t sah_chunk_cap(uint32_t n) { return (size_t)n / SAH_CHUNK + sah_big_cap(n) + 2; }
+// Bytes sah_build_hierarchy takes from the arena (on top of what bvh_build has taken).
+size_t sah_scratch_bytes(uint32_t n) {
+    return 2 * Arena::padded(sizeof(float4) * n) + 3 * Arena::padded(sizeof(uint32_t) * n) + Arena::padded(sizeof(uint32_t) * 8) +
+           2 * Arena::padded(sizeof(SahSeg) * sah_seg_cap(n)) + Arena::padded(sizeof(SahSeg) * sah_small_cap(n)) +
+           2 * Arena::padded(sizeof(SahSeg) * sah_big_cap(n)) + Arena::padded(sizeof(uint32_t) * sah_chunk_cap(n)) +
+           Arena::padded(sizeof(int) * 3 * SAH_BINS * 7 * sah_big_cap(n)) + Arena::padded(sizeof(uint32_t) * 3 * SAH_BINS * sah_chunk_cap(n)) +
+           Arena::padded(sizeof(uint2) * sah_chunk_cap(n)) + Arena::padded(sizeof(SahBigSplit) * sah_big_cap(n));
+}
 
 // Builds the binary hierarchy over n >= 2 triangles.  d_sorted_idx: Morton order (position -> flat index).  Writes
 // children[0 .. n-1), parent[0 .. 2n-1) and d_order_out (position -> flat index in the SAH tree's leaf order).
 cudaError_t sah_build_hierarchy(const float4* d_flat_tris, const uint32_t* d_sorted_idx, uint32_t n, const float centre_lo[3],
                                 const float centre_hi[3], int2* d_children, uint32_t* d_parent, uint32_t* d_order_out,
-                                uint32_t* launches, uint32_t* out_levels, cudaStream_t st) {
-    float4 *d_lo = nullptr, *d_hi = nullptr;
-    uint32_t *d_idx0 = nullptr, *d_idx1 = nullptr, *d_order_k = nullptr, *d_counters = nullptr;
-    SahSeg *d_seg0 = nullptr, *d_seg1 = nullptr, *d_small = nullptr;
-    auto cleanup = [&]() {
-        cudaFree(d_lo); cudaFree(d_hi); cudaFree(d_idx0); cudaFree(d_idx1); cudaFree(d_order_k); cudaFree(d_counters);
-        cudaFree(d_seg0); cudaFree(d_seg1); cudaFree(d_small);
-    };
-    const size_t seg_cap = (size_t)n / (SAH_SMALL + 1) + 2, small_cap = (size_t)n / 2 + 2;
-    SCK(cudaMalloc(&d_lo, sizeof(float4) * n)); SCK(cudaMalloc(&d_hi, sizeof(float4) * n));
-    SCK(cudaMalloc(&d_idx0, sizeof(uint32_t) * n)); SCK(cudaMalloc(&d_idx1, sizeof(uint32_t) * n));
-    SCK(cudaMalloc(&d_order_k, sizeof(uint32_t) * n)); SCK(cudaMalloc(&d_counters, sizeof(uint32_t) * 4));
-    SCK(cudaMalloc(&d_seg0, sizeof(SahSeg) * seg_cap)); SCK(cudaMalloc(&d_seg1, sizeof(SahSeg) * seg_cap));
-    SCK(cudaMalloc(&d_small, sizeof(SahSeg) * small_cap));
+                                uint32_t* launches, uint32_t* out_levels, Arena& arena, cudaStream_t st) {
+    const size_t seg_cap = sah_seg_cap(n), small_cap = sah_small_cap(n), big_cap = sah_big_cap(n), chunk_cap = sah_chunk_cap(n);
+    float4 *d_lo = arena.take<float4>(n), *d_hi = arena.take<float4>(n);
+    uint32_t *d_idx0 = arena.take<uint32_t>(n), *d_idx1 = arena.take<uint32_t>(n), *d_order_k = arena.take<uint32_t>(n);
+    uint32_t* d_counters = arena.take<uint32_t>(8);
+    SahSeg *d_seg0 = arena.take<SahSeg>(seg_cap), *d_seg1 = arena.take<SahSeg>(seg_cap), *d_small = arena.take<SahSeg>(small_cap);
+    SahSeg *d_big0 = arena.take<SahSeg>(big_cap), *d_big1 = arena.take<SahSeg>(big_cap);
+    SahBig B;
+    B.segs = nullptr; B.n_segs = 0;
+    B.chunk_seg = arena.take<uint32_t>(chunk_cap);
+    B.gbins = arena.take<int>(3 * SAH_BINS * 7 * big_cap);
+    B.chunk_hist = arena.take<uint32_t>(3 * SAH_BINS * chunk_cap);
+    B.chunk_off = arena.take<uint2>(chunk_cap);
+    B.split = arena.take<SahBigSplit>(big_cap);
+    if (!B.split) return cudaErrorMemoryAllocation;
     sah_boxes_kernel<<<sah_grid_for(n, 256, 148 * 16), 256, 0, st>>>(d_flat_tris, d_sorted_idx, n, d_lo, d_hi, d_idx0);
     ++*launches;
 
@@ -383,36 +627,52 @@ cudaError_t sah_build_hierarchy(const float4* d_flat_tris, const uint32_t* d_sor
     for (int k = 0; k < 3; ++k) { root.clo[k] = 2.0f * centre_lo[k]; root.chi[k] = 2.0f * centre_hi[k]; }
     const uint32_t none = 0xffffffffu;
     SCK(cudaMemcpyAsync(d_parent, &none, sizeof(uint32_t), cudaMemcpyHostToDevice, st));
-    SCK(cudaMemsetAsync(d_counters, 0, sizeof(uint32_t) * 4, st));
-    uint32_t n_seg = 0, levels = 0;
-    SahSeg *seg_in = d_seg0, *seg_out = d_seg1;
+    SCK(cudaMemsetAsync(d_counters, 0, sizeof(uint32_t) * 8, st));
+    uint32_t n_mid = 0, n_big = 0, n_chunks = 0, levels = 0;
+    SahSeg *seg_in = d_seg0, *seg_out = d_seg1, *big_in = d_big0, *big_out = d_big1;
     uint32_t *idx_in = d_idx0, *idx_out = d_idx1;
     if (n <= SAH_SMALL) {
         SCK(cudaMemcpyAsync(d_small, &root, sizeof(root), cudaMemcpyHostToDevice, st));
         sah_small_kernel<<<1, SAH_WARPS * 32, 0, st>>>(d_small, 1, idx_in, d_lo, d_hi, d_children, d_parent, d_order_k, n);
         ++*launches;
-    } else {
+    } else if (n <= SAH_BIG) {
         SCK(cudaMemcpyAsync(seg_in, &root, sizeof(root), cudaMemcpyHostToDevice, st));
-        n_seg = 1;
+        n_mid = 1;
+    } else {
+        root.pad0 = 0; root.pad1 = (n + SAH_CHUNK - 1) / SAH_CHUNK;
+        SCK(cudaMemcpyAsync(big_in, &root, sizeof(root), cudaMemcpyHostToDevice, st));
+        n_big = 1; n_chunks = root.pad1;
     }
-    while (n_seg > 0) {
+    while (n_mid > 0 || n_big > 0) {
         ++levels;
         SahLists lists;
-        lists.next = seg_out; lists.small = d_small; lists.counters = d_counters;
-        sah_level_kernel<<<n_seg, SAH_BLOCK, 0, st>>>(seg_in, idx_in, idx_out, d_lo, d_hi, lists, d_children, d_parent, d_order_k, n);
-        ++*launches;
-        uint32_t h[4];
+        lists.next = seg_out; lists.small = d_small; lists.big = big_out; lists.counters = d_counters;
+        if (n_big) {
+            B.segs = big_in; B.n_segs = n_big;
+            sah_big_prepare_kernel<<<n_big, SAH_BLOCK, 0, st>>>(B);
+            sah_big_bin_kernel<<<n_chunks, SAH_BLOCK, 0, st>>>(B, idx_in, d_lo, d_hi);
+            sah_big_split_kernel<<<n_big, SAH_BLOCK, 0, st>>>(B);
+            sah_big_scatter_kernel<<<n_chunks, SAH_BLOCK, 0, st>>>(B, idx_in, idx_out, d_lo, d_hi);
+            sah_big_emit_kernel<<<(n_big + 127) / 128, 128, 0, st>>>(B, lists, idx_out, d_children, d_parent, d_order_k, n);
+            *launches += 5;
+        }
+        if (n_mid) {
+            sah_level_kernel<<<n_mid, SAH_BLOCK, 0, st>>>(seg_in, idx_in, idx_out, d_lo, d_hi, lists, d_children, d_parent, d_order_k, n);
+            ++*launches;
+        }
+        uint32_t h[8];
         SCK(cudaMemcpyAsync(h, d_counters, sizeof(h), cudaMemcpyDeviceToHost, st));
         SCK(cudaStreamSynchronize(st));
-        if (h[0] > seg_cap || h[1] > small_cap) { cleanup(); return cudaErrorMemoryAllocation; }
+        if (h[0] > seg_cap || h[1] > small_cap || h[3] > big_cap || h[4] > chunk_cap) return cudaErrorMemoryAllocation;
         if (h[1]) {
             sah_small_kernel<<<(h[1] + SAH_WARPS - 1) / SAH_WARPS, SAH_WARPS * 32, 0, st>>>(d_small, h[1], idx_out, d_lo, d_hi, d_children,
                                                                                           d_parent, d_order_k, n);
             ++*launches;
         }
-        SCK(cudaMemsetAsync(d_counters, 0, sizeof(uint32_t) * 2, st));
-        n_seg = h[0];
+        SCK(cudaMemsetAsync(d_counters, 0, sizeof(uint32_t) * 8, st));
+        n_mid = h[0]; n_big = h[3]; n_chunks = h[4];
         SahSeg* ts = seg_in; seg_in = seg_out; seg_out = ts;
+        ts = big_in; big_in = big_out; big_out = ts;
         uint32_t* ti = idx_in; idx_in = idx_out; idx_out = ti;
     }
     sah_compose_kernel<<<sah_grid_for(n, 256, 148 * 16), 256, 0, st>>>(d_order_k, d_sorted_idx, n, d_order_out);
@@ -420,7 +680,6 @@ cudaError_t sah_build_hierarchy(const float4* d_flat_tris, const uint32_t* d_sor
     SCK(cudaStreamSynchronize(st));
     SCK(cudaGetLastError());
     if (out_levels) *out_levels = levels;
-    cleanup();
     return cudaSuccess;
 }
 

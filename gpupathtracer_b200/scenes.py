@@ -98,6 +98,18 @@ def config4_camera(width=3840, height=2160):
     return camera((0.5, 0.5, -1.5), yaw=90.0, fov=40.0, width=width, height=height)
 
 
+def config5_light():
+    """The one emitter of config 5: a two-triangle quad above the unit cube, facing down (front side towards the soup)."""
+    y = 1.25
+    quad = np.array([[-0.5, y, -0.5, 1.5, y, -0.5, 1.5, y, 1.5], [-0.5, y, -0.5, 1.5, y, 1.5, -0.5, y, 1.5]], np.float32)
+    return geom(quad, material=dict(type=0, emissive=(1, 1, 1), intensity=4.0))
+
+
+def config5(soup, width=7680, height=4320, spp=1024, max_bounces=4):
+    """Synthetic N-triangle soup (20M in BASELINE.json) + one emissive quad, 8K, 1024 spp split across GPUs."""
+    return dict(name="C5", geoms=[geom(soup), config5_light()], camera=config4_camera(width, height), spp=spp, max_bounces=max_bounces)
+
+
 def resolve_mesh(g, meshes):
     m = g["mesh"]
     if isinstance(m, str):

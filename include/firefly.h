@@ -108,6 +108,9 @@ int ff_context_create(ff_context** out, int device_id);
 void ff_context_destroy(ff_context* ctx);
 int ff_context_device(const ff_context* ctx);
 int ff_context_synchronize(ff_context* ctx);
+/* The builders keep their temporaries (~45 B/triangle LBVH, ~120 B/triangle SAH) in a grow-only scratch owned by
+ * the context so that rebuilds allocate nothing; this returns it to the driver. */
+int ff_context_release_scratch(ff_context* ctx);
 /* CUDA-event bracket on the context's stream: device-clock time of everything issued between the two calls
  * (kernels, copies and any gap while another stream or library, e.g. an NCCL reduce, is working).  The
  * reference has no timing of its own; this is what bench.py reports. */

@@ -246,10 +246,10 @@ def test_instrumented_counts_and_device_entry(ff, ctx):
 
 
 # ----------------------------------------------------------------------------- binned-SAH builder (FF_BUILDER_SAH)
-@pytest.mark.parametrize("n_tris", [1, 2, 3, 31, 32, 33, 34, 100, 1000, 20000, 200000])
+@pytest.mark.parametrize("n_tris", [1, 2, 3, 31, 32, 33, 34, 100, 1000, 8192, 8193, 12289, 20000, 200000])
 def test_sah_builder_matches_brute_force(ff, ctx, n_tris):
     """The quality builder produces a different tree, never different hits: every size around the warp-kernel /
-    CTA-kernel switch (32 | 33), BVH8 and BVH2 over the SAH tree against GPU brute force and against the LBVH tree."""
+    CTA-kernel switch (32 | 33) and the one-CTA / many-CTA switch (8192 | 8193, chunk edges), BVH8 and BVH2 over the SAH tree against GPU brute force and against the LBVH tree."""
     soup = ctx.make_soup(n_tris, s=0.2 if n_tris < 1000 else None)
     sc = ctx.scene()
     sc.add_triangles(soup)

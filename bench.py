@@ -184,6 +184,7 @@ def run_gpu_arm(args):
     sc, cam = S.instantiate(desc, ctx, meshes)
     info = sc.info()
     npix = W * H
+    sc_spb = max(1, (4 << 20) // npix)  # samples per wavefront pass the library picks for this image (ff_api.cpp accumulate_samples)
     first = rank * SPP  # weak scaling: every rank renders its own 64 global sample indices
     total_spp = SPP * world
     d_out = ctx.alloc(npix * 16)
@@ -269,6 +270,7 @@ def run_gpu_arm(args):
         peak, peak_src = measured_peak()
         bytes_per_ray = 32 + 16 + 80 * n_node + 48 * n_tri  # ray in, hit out, 80 B nodes, 48 B triangles
         rays_rank0 = rays / world
+        n_extend = ((SPP + sc_spb - 1) // sc_spb) * (BOUNCES + 1)  # extend launches per frame: passes x (bounces + 1)
         achieved = bytes_per_ray * rays_rank0 / (trace_ms * 1e-3) / 1e9 if trace_ms > 0 else 0.0
         traffic = None
         tp = os.path.join(ROOT, "profiles", "traffic.json")
@@ -294,9 +296,13 @@ def run_gpu_arm(args):
                         l2="flushed with a 256 MiB write between timed steps"),
             samples_per_sec_per_gpu=SPP * npix * steps / secs,
             rays_per_step=rays / steps, device_ms_per_step=gpu_ms / steps, trace_ms_per_step=trace_ms / steps,
-            roofline=dict(bound="hbm", kernel="trace_closest_kernel<BVH8> (extend stage, all bounces)", achieved=achieved, peak=peak, unit="GB/s",
+            roofline=dict(bound="hbm", kernel="trace_closest_persistent_kernel (extend stage, all bounces of all passes)", achieved=achieved, peak=peak, unit="GB/s",
                           frac=achieved / peak, traffic=traffic, peak_source=peak_src, bytes_per_ray=bytes_per_ray, nodes_per_ray=n_node,
-                          tris_per_ray=n_tri, share_of_step=trace_ms / gpu_ms if gpu_ms else None),
+                          tris_per_ray=n_tri, share_of_step=trace_ms / gpu_ms if gpu_ms else None,
+                          launches_per_step=n_extend, algorithmic_bytes_per_launch=bytes_per_ray * rays_rank0 / steps / n_extend,
+                          note="achieved = algorithmic bytes (SURVEY 8d: 48 B ray+hit, 80 B per node visited, 48 B per triangle tested) / CUDA-event time "
+                               "of the extend launches; traffic = measured DRAM bytes per launch (ncu, profiles/traffic.json): the scene is "
+                               "L2-resident, so DRAM carries only rays in / hits out"),
             cpu_baseline=cpu,
             e2e=dict(value=e_rays / e_secs / 1e6, unit=UNIT, h2d_bytes_per_step=ctypes_sizeof_inputs(ff), d2h_bytes_per_step=npix * 16,
                      ms_per_step=1e3 * e_secs / steps),

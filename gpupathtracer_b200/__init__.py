@@ -39,7 +39,8 @@ class CCamera(C.Structure):
 
 
 class CMaterial(C.Structure):
-    _fields_ = [("type", C.c_int), ("albedo", C.c_float * 3), ("emissive", C.c_float * 3), ("intensity", C.c_float)]
+    _fields_ = [("type", C.c_int), ("albedo", C.c_float * 3), ("emissive", C.c_float * 3), ("intensity", C.c_float),
+                ("specular", C.c_float * 3), ("ior", C.c_float), ("transmittance", C.c_float * 3)]
 
 
 class CRenderParams(C.Structure):
@@ -84,6 +85,7 @@ lib.ff_scene_destroy.argtypes = [_vp]
 lib.ff_scene_add_obj.argtypes = [_vp, C.c_char_p, _vp, _vp, _vp, _vp, C.c_int, C.POINTER(C.c_int)]
 lib.ff_scene_add_triangles.argtypes = [_vp, _vp, _sz, _vp, _vp, _vp, _vp, C.POINTER(C.c_int)]
 lib.ff_scene_add_plane.argtypes = [_vp, _vp, _vp, _vp, _vp, C.POINTER(C.c_int)]
+lib.ff_scene_add_sphere.argtypes = [_vp, C.c_float, _vp, _vp, _vp, _vp, C.POINTER(C.c_int)]
 lib.ff_scene_commit.argtypes = [_vp, C.c_int, C.POINTER(C.c_double)]
 lib.ff_scene_get_info.argtypes = [_vp, C.POINTER(CSceneInfo)]
 lib.ff_scene_get_flat.argtypes = [_vp, _vp, _vp, _vp, _sz]
@@ -158,12 +160,17 @@ def philox4x32_10(ctr, key):
     return o
 
 
-def material(type=MAT_DIFFUSE, albedo=(0.8, 0.8, 0.8), emissive=(0, 0, 0), intensity=0.0):
+def material(type=MAT_DIFFUSE, albedo=(0.8, 0.8, 0.8), emissive=(0, 0, 0), intensity=0.0, specular=(1, 1, 1), ior=1.5,
+             transmittance=(1, 1, 1)):
+    """BXDF fields (utilities.h:77-88)."""
     m = CMaterial()
     m.type = int(type)
     m.albedo[:] = [float(x) for x in albedo]
     m.emissive[:] = [float(x) for x in emissive]
     m.intensity = float(intensity)
+    m.specular[:] = [float(x) for x in specular]
+    m.ior = float(ior)
+    m.transmittance[:] = [float(x) for x in transmittance]
     return m
 
 
@@ -171,7 +178,7 @@ def _material_from(obj):
     if obj is None or isinstance(obj, CMaterial):
         return obj
     return material(obj.get("type", MAT_DIFFUSE), obj.get("albedo", (0.8, 0.8, 0.8)), obj.get("emissive", (0, 0, 0)),
-                    obj.get("intensity", 0.0))
+                    obj.get("intensity", 0.0), obj.get("specular", (1, 1, 1)), obj.get("ior", 1.5), obj.get("transmittance", (1, 1, 1)))
 
 
 class Camera:
@@ -366,6 +373,14 @@ class Scene:
         m = _material_from(material)
         _check(lib.ff_scene_add_plane(self.h, _p(_f3(pos)), _p(_f3(rot)), _p(_f3(scale)),
                                       C.byref(m) if m is not None else None, C.byref(idx)))
+        return idx.value
+
+    def add_sphere(self, radius=1.0, pos=(0, 0, 0), rot=(0, 0, 0), scale=(1, 1, 1), material=None):
+        """GeometryType::SPHERE (utilities.h:143,227): analytic sphere, front side only."""
+        idx = C.c_int(-1)
+        m = _material_from(material)
+        _check(lib.ff_scene_add_sphere(self.h, C.c_float(radius), _p(_f3(pos)), _p(_f3(rot)), _p(_f3(scale)),
+                                       C.byref(m) if m is not None else None, C.byref(idx)))
         return idx.value
 
     def commit(self, builder=BUILDER_LBVH):

@@ -50,7 +50,8 @@ struct ff_context {
 };
 
 struct HostGeom {
-    int type;  // 1 plane, 2 triangle mesh (GeometryType, utilities.h:141-146)
+    int type;  // 0 sphere, 1 plane, 2 triangle mesh (GeometryType, utilities.h:141-146)
+    float radius = 1.0f;
     M4 model, inv;
     ff_material mat;
     std::vector<float> xyz9;  // object space
@@ -229,6 +230,9 @@ static ff_material default_material() {
     m.albedo[0] = m.albedo[1] = m.albedo[2] = 0.8f;
     m.emissive[0] = m.emissive[1] = m.emissive[2] = 0.f;
     m.intensity = 0.f;
+    m.specular[0] = m.specular[1] = m.specular[2] = 1.f;
+    m.ior = 1.5f;
+    m.transmittance[0] = m.transmittance[1] = m.transmittance[2] = 1.f;
     return m;
 }
 static int add_geom(ff_scene* scene, int type, std::vector<float>&& xyz9, const float pos[3], const float rot[3], const float scl[3],
@@ -274,6 +278,19 @@ int ff_scene_add_plane(ff_scene* scene, const float pos[3], const float rot_deg[
     return add_geom(scene, 1, std::vector<float>(), pos, rot_deg, scale, material, out_geometry_index);
 }
 
+int ff_scene_add_sphere(ff_scene* scene, float radius, const float pos[3], const float rot_deg[3], const float scale[3],
+                        const ff_material* material, int* out_geometry_index) {
+    FF_REQUIRE(scene, "ff_scene_add_sphere: NULL scene");
+    FF_REQUIRE(radius > 0.f, "ff_scene_add_sphere: radius must be positive");
+    int idx = -1;
+    const int rc = add_geom(scene, 0, std::vector<float>(), pos, rot_deg, scale, material, &idx);
+    if (rc == FF_OK) {
+        scene->geoms[(size_t)idx].radius = radius;
+        if (out_geometry_index) *out_geometry_index = idx;
+    }
+    return rc;
+}
+
 int ff_scene_commit(ff_scene* scene, int builder, double* out_build_ms) {
     FF_REQUIRE(scene, "ff_scene_commit: NULL scene");
     FF_REQUIRE(scene->ctx, "ff_scene_commit: the scene's context was destroyed");
@@ -292,7 +309,7 @@ int ff_scene_commit(ff_scene* scene, int builder, double* out_build_ms) {
     ord_geom.reserve(n_tris + n_planes); ord_tri.reserve(n_tris + n_planes);
     std::vector<uint32_t> geom_of(n_tris), ord_of(n_tris);
     std::vector<M4> models(scene->geoms.size());
-    std::vector<float4> materials(2 * scene->geoms.size());
+    std::vector<float4> materials(4 * scene->geoms.size());
     std::vector<DevPlane> planes;
     std::vector<uint32_t> lights;  // flat indices of emitter-mesh triangles (next-event estimation samples these)
     float maxabs = 0.f;
@@ -301,8 +318,10 @@ int ff_scene_commit(ff_scene* scene, int builder, double* out_build_ms) {
         const HostGeom& g = scene->geoms[gi];
         models[gi] = g.model;
         float type_bits; int ty = g.mat.type; memcpy(&type_bits, &ty, 4);
-        materials[2 * gi] = make_float4(type_bits, g.mat.albedo[0], g.mat.albedo[1], g.mat.albedo[2]);
-        materials[2 * gi + 1] = make_float4(g.mat.emissive[0], g.mat.emissive[1], g.mat.emissive[2], g.mat.intensity);
+        materials[4 * gi] = make_float4(type_bits, g.mat.albedo[0], g.mat.albedo[1], g.mat.albedo[2]);
+        materials[4 * gi + 1] = make_float4(g.mat.emissive[0], g.mat.emissive[1], g.mat.emissive[2], g.mat.intensity);
+        materials[4 * gi + 2] = make_float4(g.mat.specular[0], g.mat.specular[1], g.mat.specular[2], g.mat.ior > 0.f ? g.mat.ior : 1.5f);
+        materials[4 * gi + 3] = make_float4(g.mat.transmittance[0], g.mat.transmittance[1], g.mat.transmittance[2], 0.f);
         if (g.type == 2) {
             const size_t nt = g.xyz9.size() / 9;
             for (size_t t = 0; t < nt; ++t, ++flat) {
@@ -315,7 +334,8 @@ int ff_scene_commit(ff_scene* scene, int builder, double* out_build_ms) {
             p.model = g.model; p.inv = g.inv;
             const ffm::V4 nw = ffh::matvec(ffh::inverted(ffh::transposed(g.model)), ffh::v4(0, 0, 1, 0));
             p.normal_world[0] = nw.x; p.normal_world[1] = nw.y; p.normal_world[2] = nw.z; p.normal_world[3] = 0;
-            p.ord = (int)ord_geom.size(); p.geom = (int)gi; p.pad0 = p.pad1 = 0;
+            p.nrm = ffh::inverted(ffh::transposed(g.model));
+            p.ord = (int)ord_geom.size(); p.geom = (int)gi; p.kind = g.type; p.radius = g.radius;
             planes.push_back(p);
             ord_geom.push_back((int)gi); ord_tri.push_back(-1);
         }

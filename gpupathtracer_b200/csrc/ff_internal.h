@@ -29,11 +29,15 @@ namespace ff {
 //             tie-break order of intersectRays (kernel.cu:133,145).
 //   nodes     5 float4 (80 B) per 8-wide compressed node, see ff_bvh.cu for the field layout.
 //   ord_geom / ord_tri   ord -> (geometryIndex, triangleIndex) in the reference's numbering.
-//   materials 2 float4 per geometry: {type, albedo.rgb}, {emissive.rgb * intensity, intensity}
+//   materials 4 float4 per geometry: {type, albedo.rgb}, {emissive.rgb, intensity}, {specular.rgb, ior}, {transmittance.rgb, 0}
+// Analytic primitive of the reference's Geometry: GeometryType::PLANE (unit square, intersectPlane kernel.cu:8-32) or
+// GeometryType::SPHERE (utilities.h:143,227; the reference leaves its branch empty, kernel.cu:166-169).
 struct DevPlane {
     ffm::M4 model, inv;   // Geometry::m_modelMatrix / m_invModelMatrix (utilities.h:188-189)
-    float normal_world[4];  // inverse(transpose(model)) * (0,0,1,0), not normalised (kernel.cu:117)
-    int ord, geom, pad0, pad1;
+    ffm::M4 nrm;          // inverse(transpose(model)): object normal -> world normal, not normalised (kernel.cu:117)
+    float normal_world[4];  // nrm * (0,0,1,0) for a plane
+    int ord, geom, kind;  // kind: 1 plane, 0 sphere (GeometryType values)
+    float radius;
 };
 struct DevScene {
     const float4* tris;

@@ -43,8 +43,10 @@ __device__ __forceinline__ void hit_surface(const DevScene& sc, const HitRec& h,
     if (h.slot & 0x40000000) {
         const DevPlane& pl = sc.planes[h.slot & 0x3fffffff];
         float key, tl;
-        plane_hit(pl, o, d_raw, key, tl, point);
-        normal = v3(pl.normal_world[0], pl.normal_world[1], pl.normal_world[2]);
+        V3 lp;
+        plane_hit(pl, o, d_raw, key, tl, point, lp);
+        if (pl.kind == 1) normal = v3(pl.normal_world[0], pl.normal_world[1], pl.normal_world[2]);
+        else { const V4 nw = mul_mv(pl.nrm, lp.x, lp.y, lp.z, 0.0f); normal = v3(nw.x, nw.y, nw.z); }
         geom = pl.geom;
     } else {
         const float4 a = __ldg(sc.tris + 3 * (size_t)h.slot), b = __ldg(sc.tris + 3 * (size_t)h.slot + 1),
@@ -90,7 +92,7 @@ __device__ __forceinline__ void sample_light(const DevScene& sc, const RenderDev
     if (!(cosx > 0.0f && cosl > 0.0f && dist2 > 0.0f)) return;
     const float w = fmul(fmul(fdiv(fmul(cosx, cosl), dist2), fmul(0.5f, len)), fmul((float)nl, 0.318309886183790672f));
     const int geom = __float_as_int(b4.w);
-    const float4 m1 = __ldg(sc.materials + 2 * geom + 1);
+    const float4 m1 = __ldg(sc.materials + 4 * geom + 1);
     sr.contrib = mul(mul3(beta, mul(v3(m1.x, m1.y, m1.z), m1.w)), w);
     sr.o = so; sr.d = sd;
     sr.tmax = fmul(dist, 0.999f);
@@ -102,7 +104,7 @@ __device__ __forceinline__ void sample_light(const DevScene& sc, const RenderDev
 // contribution.
 template <bool NEE>
 __device__ __forceinline__ bool shade_event(const DevScene& sc, const RenderDev& rp, const HitRec& h, uint32_t pixel, uint32_t sample,
-                                            int bounce, V3& o, V3& d, V3& beta, V3& L, ShadowReq& sr) {
+                                            int bounce, V3& o, V3& d, V3& beta, V3& L, bool& specular, ShadowReq& sr) {
     sr.valid = false;
     if (h.slot < 0) {
         L = add(L, mul3(beta, v3(rp.background[0], rp.background[1], rp.background[2])));
@@ -111,19 +113,53 @@ __device__ __forceinline__ bool shade_event(const DevScene& sc, const RenderDev&
     V3 P, nrm;
     int geom;
     hit_surface(sc, h, o, d, P, nrm, geom);
-    const float4 m0 = __ldg(sc.materials + 2 * geom), m1 = __ldg(sc.materials + 2 * geom + 1);
-    if (__float_as_int(m0.x) == FF_MAT_EMITTER) {
-        // with NEE the direct light of mesh emitters arrives through the shadow rays; a BSDF-sampled hit on one
-        // counts only for the camera ray
+    const float4 m0 = __ldg(sc.materials + 4 * geom), m1 = __ldg(sc.materials + 4 * geom + 1);
+    const int type = __float_as_int(m0.x);
+    if (type == FF_MAT_EMITTER) {
+        // with NEE the direct light of mesh emitters arrives through the shadow rays; a hit found by sampling the BSDF
+        // counts only for the camera ray and after a specular event (which has no light sample)
         const bool sampled = NEE && rp.nee && !(h.slot & 0x40000000) && sc.n_lights != 0;
-        if (!sampled || bounce == 0) L = add(L, mul3(beta, mul(v3(m1.x, m1.y, m1.z), m1.w)));
+        if (!sampled || bounce == 0 || specular) L = add(L, mul3(beta, mul(v3(m1.x, m1.y, m1.z), m1.w)));
         return false;
     }
     if (bounce == rp.max_bounces) return false;
     V3 n = normalize(nrm);
     if (dot(n, d) > 0.0f) n = neg(n);
-    beta = mul3(beta, v3(m0.y, m0.z, m0.w));
     const U4 r = philox4x32_10(U4{pixel, sample, (uint32_t)bounce, 0u}, rp.seed_lo, rp.seed_hi);
+    if (type == FF_MAT_MIRROR || type == FF_MAT_GLASS) {
+        // BXDFTyp MIRROR / GLASS (utilities.h:72-73, fields utilities.h:84-88; no code in the reference).  CPU twin:
+        // trace_path in oracle/firefly_oracle.cpp, same operations in the same order.  Only front faces are ever hit,
+        // so glass is one refracting interface air -> ior; Schlick's Fresnel picks reflection with probability F.
+        const float4 m2 = __ldg(sc.materials + 4 * geom + 2);
+        const V3 dn = normalize(d);
+        const float cosi = -dot(dn, n);
+        bool reflect = true;
+        if (type == FF_MAT_GLASS) {
+            const float ior = m2.w;
+            const float eta = fdiv(1.0f, ior);
+            float r0 = fdiv(fsub(1.0f, ior), fadd(1.0f, ior));
+            r0 = fmul(r0, r0);
+            const float c1 = fsub(1.0f, cosi);
+            const float F = fadd(r0, fmul(fsub(1.0f, r0), fmul(fmul(fmul(c1, c1), fmul(c1, c1)), c1)));
+            const float sin2t = fmul(fmul(eta, eta), fsub(1.0f, fmul(cosi, cosi)));
+            if (!(sin2t > 1.0f) && !(u01(r.z) < F)) {
+                reflect = false;
+                const float4 m3 = __ldg(sc.materials + 4 * geom + 3);
+                d = add(mul(dn, eta), mul(n, fsub(fmul(eta, cosi), fsqrt(fsub(1.0f, sin2t)))));
+                beta = mul3(beta, v3(m3.x, m3.y, m3.z));
+                o = sub(P, mul(n, rp.ray_eps));
+            }
+        }
+        if (reflect) {
+            d = add(dn, mul(n, fmul(2.0f, cosi)));
+            beta = mul3(beta, v3(m2.x, m2.y, m2.z));
+            o = add(P, mul(n, rp.ray_eps));
+        }
+        specular = true;
+        return true;
+    }
+    specular = false;
+    beta = mul3(beta, v3(m0.y, m0.z, m0.w));
     const V3 w = cosine_sample_hemisphere(u01(r.x), u01(r.y));
     V3 t, bt;
     onb(n, t, bt);
@@ -170,14 +206,16 @@ __global__ void __launch_bounds__(256) wf_shade_kernel(DevScene sc, RenderDev rp
         uint32_t path = 0;
         ShadowReq sr;
         sr.valid = false;
+        bool specular = false;  // the path's previous event was a mirror / glass bounce (carried in beta.w)
         if (k < n) {
             const float4 o4 = ray_o_in[k], d4 = ray_d_in[k], b4 = beta_in[k];
             const HitRec h = hits[k];
             path = __float_as_uint(o4.w);
             const uint32_t s = path / rp.npix, pixel = path - s * rp.npix;
             o = ld3(o4); d = ld3(d4); beta = ld3(b4);
+            specular = b4.w != 0.0f;
             V3 L = v3(0.f, 0.f, 0.f);
-            alive = shade_event<NEE>(sc, rp, h, pixel, rp.first_sample + s, bounce, o, d, beta, L, sr);
+            alive = shade_event<NEE>(sc, rp, h, pixel, rp.first_sample + s, bounce, o, d, beta, L, specular, sr);
             if (!alive) {
                 if (NEE) {  // the shadow stages of earlier bounces have already added to this path
                     const float4 a = radiance[path];
@@ -196,7 +234,7 @@ __global__ void __launch_bounds__(256) wf_shade_kernel(DevScene sc, RenderDev rp
                 const uint32_t q = base + __popc(m & ((1u << lane) - 1u));
                 ray_o_out[q] = make_float4(o.x, o.y, o.z, __uint_as_float(path));
                 ray_d_out[q] = make_float4(d.x, d.y, d.z, 0.f);
-                beta_out[q] = make_float4(beta.x, beta.y, beta.z, 0.f);
+                beta_out[q] = make_float4(beta.x, beta.y, beta.z, specular ? 1.0f : 0.0f);
             }
         }
         if (NEE) {  // shadow-ray queue of this bounce, compacted the same way
@@ -262,6 +300,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) megakernel(DevScene sc, CamDev
     const int lane = threadIdx.x & 31;
     uint2* my = sm_stack + threadIdx.x;
     bool has = false, exhausted = false;
+    bool specular = false;  // the previous event was a mirror / glass bounce
     bool shadow = false;  // the traversal in flight is this bounce's shadow ray; (o, d) already hold the next segment
     uint32_t path = 0, pixel = 0, sample = 0;
     int bounce = 0;
@@ -297,6 +336,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) megakernel(DevScene sc, CamDev
                     sample = rp.first_sample + s;
                     beta = v3(1.f, 1.f, 1.f); L = v3(0.f, 0.f, 0.f);
                     bounce = 0;
+                    specular = false;
                     primary_ray(cam, rp, pixel, sample, o, d);
                     start_segment();
                     has = true;
@@ -320,7 +360,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) megakernel(DevScene sc, CamDev
                     HitRec h;
                     h.key = best.key; h.t = best.t; h.slot = best.slot; h.ord = best.slot < 0 ? -1 : best.ord;
                     ShadowReq sr;
-                    if (shade_event<NEE>(sc, rp, h, pixel, sample, bounce, o, d, beta, L, sr)) {
+                    if (shade_event<NEE>(sc, rp, h, pixel, sample, bounce, o, d, beta, L, specular, sr)) {
                         ++bounce;
                         if (NEE && sr.valid) {
                             ++shadow_rays;

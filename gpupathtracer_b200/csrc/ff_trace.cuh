@@ -62,9 +62,10 @@ __device__ __forceinline__ ffm::V4 mul_mv(const ffm::M4& m, float x, float y, fl
     return r;
 }
 
-// intersectPlane (kernel.cu:8-32) + setIntersection (kernel.cu:110-125) for one analytic plane.
-// `d_raw` is the ray direction as given (the reference normalises it in object space, kernel.cu:138).
-__device__ __forceinline__ bool plane_hit(const DevPlane& pl, V3 o, V3 d_raw, float& key, float& t_local, V3& world_point) {
+// intersectPlane (kernel.cu:8-32) / the sphere routine (CPU twin: intersectSphere in oracle/firefly_oracle.cpp) +
+// setIntersection (kernel.cu:110-125) for one analytic primitive.  `d_raw` is the ray direction as given (the reference
+// normalises it in object space, kernel.cu:138).  `local_point` is the object-space hit point (the sphere's normal).
+__device__ __forceinline__ bool plane_hit(const DevPlane& pl, V3 o, V3 d_raw, float& key, float& t_local, V3& world_point, V3& local_point) {
     using namespace ffm;
     V4 o4 = mul_mv(pl.inv, o.x, o.y, o.z, 1.0f);
     V4 d4 = mul_mv(pl.inv, d_raw.x, d_raw.y, d_raw.z, 0.0f);
@@ -72,15 +73,28 @@ __device__ __forceinline__ bool plane_hit(const DevPlane& pl, V3 o, V3 d_raw, fl
     float inv = inversesqrt(dd);
     V3 od = v3(fmul(d4.x, inv), fmul(d4.y, inv), fmul(d4.z, inv));
     V3 oo = v3(o4.x, o4.y, o4.z);
-    V3 n = v3(0.f, 0.f, 1.f);
-    float denom = dot(n, od);
-    if (!((double)fabsf(denom) > 1e-7)) return false;
-    float t = fdiv(dot(neg(oo), n), denom);
-    V3 P = add(oo, mul(od, t));
-    if (!(P.x >= -0.5f && P.x <= 0.5f && P.y >= -0.5f && P.y <= 0.5f)) return false;
-    if (!(t > 0.0f)) return false;
+    float t;
+    V3 P;
+    if (pl.kind == 1) {
+        V3 n = v3(0.f, 0.f, 1.f);
+        float denom = dot(n, od);
+        if (!((double)fabsf(denom) > 1e-7)) return false;
+        t = fdiv(dot(neg(oo), n), denom);
+        P = add(oo, mul(od, t));
+        if (!(P.x >= -0.5f && P.x <= 0.5f && P.y >= -0.5f && P.y <= 0.5f)) return false;
+        if (!(t > 0.0f)) return false;
+    } else {
+        float b = dot(oo, od);
+        float c = fsub(dot(oo, oo), fmul(pl.radius, pl.radius));
+        float disc = fsub(fmul(b, b), c);
+        if (!(disc > 0.0f)) return false;
+        t = fsub(-b, fsqrt(disc));
+        if (!(t > 0.0f)) return false;
+        P = add(oo, mul(od, t));
+    }
     V4 w = mul_mv(pl.model, P.x, P.y, P.z, 1.0f);
     world_point = v3(w.x, w.y, w.z);
+    local_point = P;
     key = distance(world_point, o);
     t_local = t;
     return true;
@@ -90,8 +104,8 @@ template <bool ANY>
 __device__ __forceinline__ void test_planes(const DevScene& sc, V3 o, V3 d_raw, Best& best) {
     for (uint32_t i = 0; i < sc.n_planes; ++i) {
         float key, tl;
-        V3 wp;
-        if (plane_hit(sc.planes[i], o, d_raw, key, tl, wp)) {
+        V3 wp, lp;
+        if (plane_hit(sc.planes[i], o, d_raw, key, tl, wp, lp)) {
             int ord = sc.planes[i].ord;
             if (ANY ? (key < best.key) : best_accepts(best, key, ord)) {
                 if (!ANY) best.key = key;

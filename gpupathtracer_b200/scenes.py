@@ -36,8 +36,9 @@ def camera(pos, yaw=-90.0, pitch=0.0, fov=70.0, width=256, height=256, near=0.1,
     return dict(pos=tuple(pos), world_up=(0, 1, 0), yaw=yaw, pitch=pitch, fov=fov, width=width, height=height, near=near, far=far)
 
 
-def geom(mesh, pos=(0, 0, 0), rot=(0, 0, 0), scale=(1, 1, 1), material=None, flip=False, plane=False):
-    return dict(mesh=mesh, pos=pos, rot=rot, scale=scale, material=material or DIFFUSE_GREY, flip=flip, plane=plane)
+def geom(mesh, pos=(0, 0, 0), rot=(0, 0, 0), scale=(1, 1, 1), material=None, flip=False, plane=False, sphere=None):
+    """mesh: name | [n,9] array | None; plane=True: GeometryType::PLANE; sphere=r: GeometryType::SPHERE of radius r."""
+    return dict(mesh=mesh, pos=pos, rot=rot, scale=scale, material=material or DIFFUSE_GREY, flip=flip, plane=plane, sphere=sphere)
 
 
 def flip_winding(xyz9):
@@ -90,6 +91,22 @@ def reference_main(width=800, height=800):
                 camera=camera((0, 0, 15), fov=70.0, width=width, height=height), spp=1, max_bounces=0)
 
 
+def showcase(meshes, width=512, height=512, spp=16, max_bounces=6):
+    """Every declared BXDFTyp and GeometryType in one frame: the config-2 box with a glass
+    rocketman, an analytic mirror sphere, an analytic emissive sphere and an analytic plane."""
+    top, rest = _cube_faces(meshes["cube"])
+    return dict(name="showcase",
+                geoms=[geom(rest, scale=(5, 5, 5), flip=True),
+                       geom(top, scale=(5, 5, 5), flip=True, material=EMITTER_WHITE2),
+                       geom("rocketman", rot=(0, 90, 180), scale=(0.6, 0.6, 0.6), pos=(-0.9, 0, 0),
+                            material=dict(type=3, ior=1.5, specular=(1, 1, 1), transmittance=(0.9, 1.0, 0.9))),
+                       geom(None, sphere=0.8, pos=(1.1, -1.6, -0.6), scale=(1, 1.2, 1), rot=(0, 0, 20),
+                            material=dict(type=2, specular=(0.9, 0.9, 0.95))),
+                       geom(None, sphere=0.25, pos=(0.2, 1.2, 0.8), material=dict(type=0, emissive=(1.0, 0.6, 0.2), intensity=6.0)),
+                       geom(None, plane=True, pos=(0, -2.2, 0), rot=(-90, 0, 0), scale=(3, 3, 3), material=dict(type=1, albedo=(0.2, 0.4, 0.8)))],
+                camera=camera((0, 0, 2.4), fov=70.0, width=width, height=height), spp=spp, max_bounces=max_bounces)
+
+
 def soup_scale(n):
     return float(np.float32(float(n) ** (-1.0 / 3.0)))
 
@@ -123,7 +140,9 @@ def instantiate(desc, ctx, meshes=None, builder=0, commit=True):
     import gpupathtracer_b200 as ff
     sc = ctx.scene()
     for g in desc["geoms"]:
-        if g["plane"]:
+        if g.get("sphere") is not None:
+            sc.add_sphere(g["sphere"], g["pos"], g["rot"], g["scale"], g["material"])
+        elif g["plane"]:
             sc.add_plane(g["pos"], g["rot"], g["scale"], g["material"])
         else:
             sc.add_triangles(resolve_mesh(g, meshes), g["pos"], g["rot"], g["scale"], g["material"])
@@ -135,7 +154,9 @@ def instantiate(desc, ctx, meshes=None, builder=0, commit=True):
 def instantiate_on(desc, scene, meshes=None):
     """Same on any object with add_mesh/add_plane (the test oracle's scene classes)."""
     for g in desc["geoms"]:
-        if g["plane"]:
+        if g.get("sphere") is not None:
+            scene.add_sphere(g["sphere"], g["pos"], g["rot"], g["scale"], g["material"])
+        elif g["plane"]:
             scene.add_plane(g["pos"], g["rot"], g["scale"], g["material"])
         else:
             scene.add_mesh(resolve_mesh(g, meshes), g["pos"], g["rot"], g["scale"], g["material"])

@@ -54,6 +54,9 @@ typedef struct ff_material {
     float albedo[3];
     float emissive[3];
     float intensity;
+    float specular[3];       /* m_specularColor: mirror reflectance, and the reflected lobe of glass */
+    float ior;               /* m_refractiveIndex (glass); 0 is read as 1.5 */
+    float transmittance[3];  /* m_transmittanceColor: the refracted lobe of glass */
 } ff_material;
 
 enum { FF_INTEGRATOR_WAVEFRONT = 0, FF_INTEGRATOR_MEGAKERNEL = 1, FF_INTEGRATOR_AS_CODED = 2 };
@@ -131,6 +134,11 @@ int ff_scene_add_triangles(ff_scene* scene, const float* xyz9, size_t n_tris, co
 /* GeometryType::PLANE (utilities.h:141-146, intersectPlane kernel.cu:8-32): unit square at object z=0. */
 int ff_scene_add_plane(ff_scene* scene, const float pos[3], const float rot_deg[3], const float scale[3],
                        const ff_material* material, int* out_geometry_index);
+/* GeometryType::SPHERE (utilities.h:143, m_sphereRadius utilities.h:227; the reference leaves its intersection branch
+ * empty, kernel.cu:166-169): analytic sphere of `radius` at the object-space origin, front side only like every
+ * triangle (a ray that starts inside sees nothing). */
+int ff_scene_add_sphere(ff_scene* scene, float radius, const float pos[3], const float rot_deg[3], const float scale[3],
+                        const ff_material* material, int* out_geometry_index);
 /* OBJ -> xyz9 triangle list without a scene (the LoadMesh half on its own).  Call with xyz9 = NULL
  * to get the count. Returns the triangle count or a negative ff_status. */
 long ff_load_obj(const char* obj_path, float* xyz9, size_t capacity_tris);

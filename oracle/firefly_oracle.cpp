@@ -219,9 +219,14 @@ struct Geom {
     int type;
     M4 model, inv;
     V3 normal{0, 0, 1};  // utilities.h:230
+    float radius = 1.0f;  // Geometry::m_sphereRadius (utilities.h:227), used by intersectSphere
     std::vector<Tri> tris;
 };
-struct Material { int type; V3 albedo, emissive; float intensity; };  // BXDF utilities.h:77-88 (0 EMITTER, 1 DIFFUSE)
+// BXDF utilities.h:77-88; type = BXDFTyp utilities.h:68-75 (0 EMITTER, 1 DIFFUSE, 2 MIRROR, 3 GLASS)
+struct Material {
+    int type; V3 albedo, emissive; float intensity;
+    V3 specular{1, 1, 1}; float ior = 1.5f; V3 transmittance{1, 1, 1};   // m_specularColor, m_refractiveIndex, m_transmittanceColor
+};
 struct Scene {
     std::vector<Geom> geoms;
     std::vector<Material> mats;
@@ -239,6 +244,20 @@ bool intersectPlane(const Geom& plane, const Ray& ray, Hit& out) {
         if (t > 0.0f) { out.t = t; out.point = P; out.normal = plane.normal; return true; }
         return false;
     }
+    return false;
+}
+// GeometryType::SPHERE: the reference declares it (utilities.h:143, m_sphereRadius utilities.h:227) and leaves the
+// branch empty (kernel.cu:166-169).  New text in the style of intersectPlane: object-space sphere of radius r at the
+// origin, ENTERING root only (front faces only, like intersectTriangle's culling: a ray that starts inside sees
+// nothing), accepted when t > 0; the normal returned is the object-space point (not normalised, like setIntersection
+// leaves normals).
+bool intersectSphere(const Geom& sph, const Ray& ray, Hit& out) {
+    float b = dot(ray.o, ray.d);
+    float c = dot(ray.o, ray.o) - sph.radius * sph.radius;
+    float disc = b * b - c;
+    if (!(disc > 0.0f)) return false;
+    float t = -b - std::sqrt(disc);
+    if (t > 0.0f) { out.t = t; out.point = add(ray.o, mul(ray.d, t)); out.normal = out.point; return true; }
     return false;
 }
 // kernel.cu:35-108
@@ -295,6 +314,9 @@ Hit intersectRays(const Ray& ray, const Scene& sc) {
                     if (setIntersection(tMax, out, local, g.model, ray)) { out.geom = i; out.tri = j; }
         } else if (g.type == PLANE) {
             if (intersectPlane(g, os, local))
+                if (setIntersection(tMax, out, local, g.model, ray)) { out.geom = i; out.tri = -1; }
+        } else if (g.type == SPHERE) {  // an empty branch in the reference (kernel.cu:166-169); see intersectSphere
+            if (intersectSphere(g, os, local))
                 if (setIntersection(tMax, out, local, g.model, ray)) { out.geom = i; out.tri = -1; }
         }
     }
@@ -449,6 +471,17 @@ FlatHit intersectFlat(const Ray& ray, const Scene& sc, const Flat& f) {
                     out.normal = xyz(mulMV(inverse(transpose(g.model)), v4(local.normal, 0.f)));
                 }
             }
+        } else if (g.type == SPHERE) {
+            Ray ps{xyz(mulMV(g.inv, v4(ray.o, 1.f))), xyz(normalize4(mulMV(g.inv, v4(ray.d, 0.f))))};
+            Hit local;
+            if (intersectSphere(g, ps, local)) {
+                V3 worldPOI = xyz(mulMV(g.model, v4(local.point, 1.0f)));
+                float d = distance(worldPOI, ray.o);
+                if (d < tMax) {
+                    tMax = d; out.hit = true; out.geom = i; out.tri = -1; out.flat = -1; out.t = d; out.point = worldPOI;
+                    out.normal = xyz(mulMV(inverse(transpose(g.model)), v4(local.normal, 0.f)));
+                }
+            }
         }
     }
     return out;
@@ -492,10 +525,11 @@ bool occludedFlat(const Ray& ray, float tmax, const Scene& sc, const Flat& f) {
         if (intersectTriangle(f.tris[k], os, local) && distance(local.point, ray.o) < tmax) return true;
     }
     for (const Geom& g : sc.geoms) {
-        if (g.type != PLANE) continue;
+        if (g.type == TRIANGLEMESH) continue;
         Ray ps{xyz(mulMV(g.inv, v4(ray.o, 1.f))), xyz(normalize4(mulMV(g.inv, v4(ray.d, 0.f))))};
         Hit local;
-        if (intersectPlane(g, ps, local) && distance(xyz(mulMV(g.model, v4(local.point, 1.0f))), ray.o) < tmax) return true;
+        const bool hit = g.type == PLANE ? intersectPlane(g, ps, local) : intersectSphere(g, ps, local);
+        if (hit && distance(xyz(mulMV(g.model, v4(local.point, 1.0f))), ray.o) < tmax) return true;
     }
     return false;
 }
@@ -551,6 +585,7 @@ V3 trace_path(OScene& os, const Camera& cam, const M4& invVP, int x, int y, uint
     }
     Ray ray = gen_ray(cam, invVP, px, py);
     V3 beta{1, 1, 1}, L{0, 0, 0};
+    bool specular = false;  // the previous event was a mirror / glass bounce
     V3 bg{rp.background[0], rp.background[1], rp.background[2]};
     for (int b = 0; b <= rp.max_bounces; ++b) {
         FlatHit h = intersectFlat(ray, os.sc, f);
@@ -558,17 +593,49 @@ V3 trace_path(OScene& os, const Camera& cam, const M4& invVP, int x, int y, uint
         if (!h.hit) { L = add(L, mul3(beta, bg)); break; }
         const Material& m = os.sc.mats[h.geom];
         if (m.type == 0) {
-            // with NEE the direct light of sampled emitters (mesh emitters) arrives through the shadow rays;
-            // a BSDF-sampled hit on one counts only for the camera ray
+            // with NEE the direct light of sampled emitters (mesh emitters) arrives through the shadow rays; a hit found
+            // by sampling the BSDF counts only for the camera ray and after a specular event (which has no light sample)
             const bool sampled = rp.nee && h.tri >= 0 && !lights.empty();
-            if (!sampled || b == 0) L = add(L, mul3(beta, mul(m.emissive, m.intensity)));
+            if (!sampled || b == 0 || specular) L = add(L, mul3(beta, mul(m.emissive, m.intensity)));
             break;
         }
         if (b == rp.max_bounces) break;
         V3 n = normalize(h.normal);
         if (dot(n, ray.d) > 0.0f) n = neg(n);
-        beta = mul3(beta, m.albedo);
         U4 r = philox4x32_10(U4{pixel, sample, (uint32_t)b, 0u}, rp.seed_lo, rp.seed_hi);
+        if (m.type == 2 || m.type == 3) {
+            // MIRROR / GLASS (BXDFTyp utilities.h:72-73; the reference declares the fields, utilities.h:84-88, and no
+            // code).  Only front faces are ever hit (kernel.cu:48-51), so a ray meets a glass surface from outside only:
+            // one refracting interface, air -> ior; Schlick's Fresnel picks reflection with probability F.
+            V3 dn = normalize(ray.d);
+            float cosi = -dot(dn, n);
+            bool reflect = true;
+            V3 d;
+            if (m.type == 3) {
+                float eta = 1.0f / m.ior;
+                float r0 = (1.0f - m.ior) / (1.0f + m.ior);
+                r0 = r0 * r0;
+                float c1 = 1.0f - cosi;
+                float F = r0 + (1.0f - r0) * ((c1 * c1) * (c1 * c1) * c1);
+                float sin2t = (eta * eta) * (1.0f - cosi * cosi);
+                if (!(sin2t > 1.0f) && !(u01(r.z) < F)) {
+                    reflect = false;
+                    d = add(mul(dn, eta), mul(n, eta * cosi - std::sqrt(1.0f - sin2t)));
+                    beta = mul3(beta, m.transmittance);
+                    ray.o = sub(h.point, mul(n, rp.ray_eps));
+                }
+            }
+            if (reflect) {
+                d = add(dn, mul(n, 2.0f * cosi));
+                beta = mul3(beta, m.specular);
+                ray.o = add(h.point, mul(n, rp.ray_eps));
+            }
+            ray.d = d;
+            specular = true;
+            continue;
+        }
+        specular = false;
+        beta = mul3(beta, m.albedo);
         V3 w = cosineSampleHemisphere(u01(r.x), u01(r.y));
         V3 t, bt;
         onb(n, t, bt);
@@ -595,12 +662,17 @@ int orc_hardware_threads() { return (int)std::thread::hardware_concurrency(); }
 void* orc_scene_new() { return new OScene(); }
 void orc_scene_free(void* s) { delete (OScene*)s; }
 
-static void push_material(OScene* os, const float* mat8) {
-    Material m{1, v3(0.8f, 0.8f, 0.8f), v3(0, 0, 0), 0.f};
-    if (mat8) { m.type = (int)mat8[0]; m.albedo = v3(mat8[1], mat8[2], mat8[3]); m.emissive = v3(mat8[4], mat8[5], mat8[6]); m.intensity = mat8[7]; }
+// mat15 = {type (BXDFTyp: 0 emitter, 1 diffuse, 2 mirror, 3 glass), albedo rgb, emissive rgb, intensity, specular rgb, ior,
+//          transmittance rgb} or NULL
+static void push_material(OScene* os, const float* m15) {
+    Material m;
+    m.type = 1; m.albedo = v3(0.8f, 0.8f, 0.8f); m.emissive = v3(0, 0, 0); m.intensity = 0.f;
+    if (m15) {
+        m.type = (int)m15[0]; m.albedo = v3(m15[1], m15[2], m15[3]); m.emissive = v3(m15[4], m15[5], m15[6]); m.intensity = m15[7];
+        m.specular = v3(m15[8], m15[9], m15[10]); m.ior = m15[11]; m.transmittance = v3(m15[12], m15[13], m15[14]);
+    }
     os->sc.mats.push_back(m);
 }
-// mat8 = {type(0 emitter,1 diffuse), albedo rgb, emissive rgb, intensity} or NULL
 int orc_scene_add_mesh(void* s, const float* xyz9, long n_tris, const float pos[3], const float rot[3],
                        const float scale[3], const float* mat8) {
     OScene* os = (OScene*)s;
@@ -621,6 +693,17 @@ int orc_scene_add_plane(void* s, const float pos[3], const float rot[3], const f
     OScene* os = (OScene*)s;
     Geom g;
     g.type = PLANE;
+    model_matrices(v3(pos[0], pos[1], pos[2]), v3(rot[0], rot[1], rot[2]), v3(scale[0], scale[1], scale[2]), g.model, g.inv);
+    os->sc.geoms.push_back(std::move(g));
+    push_material(os, mat8);
+    os->flat_valid = false;
+    return (int)os->sc.geoms.size() - 1;
+}
+int orc_scene_add_sphere(void* s, float radius, const float pos[3], const float rot[3], const float scale[3], const float* mat8) {
+    OScene* os = (OScene*)s;
+    Geom g;
+    g.type = SPHERE;
+    g.radius = radius;
     model_matrices(v3(pos[0], pos[1], pos[2]), v3(rot[0], rot[1], rot[2]), v3(scale[0], scale[1], scale[2]), g.model, g.inv);
     os->sc.geoms.push_back(std::move(g));
     push_material(os, mat8);

@@ -36,11 +36,14 @@ def _vec3(v):
 
 
 def mat8(material):
-    """material: None | dict(type=0|1, albedo, emissive, intensity) -> float32[8]."""
+    """material: None | dict(type=0..3, albedo, emissive, intensity, specular, ior, transmittance) -> float32[15]
+    (BXDF fields, utilities.h:77-88; type = BXDFTyp: 0 emitter, 1 diffuse, 2 mirror, 3 glass)."""
     if material is None:
         return None
     return np.array([material.get("type", 1), *material.get("albedo", (0.8, 0.8, 0.8)),
-                     *material.get("emissive", (0, 0, 0)), material.get("intensity", 0.0)], np.float32)
+                     *material.get("emissive", (0, 0, 0)), material.get("intensity", 0.0),
+                     *material.get("specular", (1, 1, 1)), material.get("ior", 1.5),
+                     *material.get("transmittance", (1, 1, 1))], np.float32)
 
 
 class _Base:
@@ -167,6 +170,10 @@ class OracleScene(_SceneBase):
     def add_plane(self, pos=(0, 0, 0), rot=(0, 0, 0), scale=(1, 1, 1), material=None):
         self.n_geoms += 1
         return self.o.f("scene_add_plane")(self.h, _vec3(pos), _vec3(rot), _vec3(scale), _ptr(mat8(material)))
+
+    def add_sphere(self, radius=1.0, pos=(0, 0, 0), rot=(0, 0, 0), scale=(1, 1, 1), material=None):
+        self.n_geoms += 1
+        return self.o.f("scene_add_sphere")(self.h, C.c_float(radius), _vec3(pos), _vec3(rot), _vec3(scale), _ptr(mat8(material)))
 
     def flat(self):
         self.o.f("flat_count").restype = C.c_long

@@ -150,3 +150,24 @@ def test_scene_outlives_context(ff, meshes):
     with pytest.raises(ff.FireflyError):
         sc.commit()
     sc.close()
+
+
+@pytest.mark.parametrize("nee", [0, 1])
+def test_showcase_all_material_and_geometry_types(ff, ctx, orc, meshes, nee):
+    """Every BXDFTyp (emitter, diffuse, mirror, glass) and GeometryType (sphere, plane, mesh) in one frame: both
+    integrators bit-identical to the oracle, closest-hit ids and any-hit answers included."""
+    desc = S.showcase(meshes, 80, 64, 4, 6)
+    sc, cam = S.instantiate(desc, ctx, meshes)
+    osc = S.instantiate_on(desc, orc.scene(), meshes)
+    rays = ctx.camera_rays(cam)
+    got, want = sc.trace_closest(rays), osc.intersect(rays, mode=1)
+    assert (got["geom"] == want["geom"]).all() and (got["tri"] == want["tri"]).all() and (bits(got["t"]) == bits(want["t"])).all()
+    assert set(np.unique(want["geom"])) >= {0, 2, 3, 5}  # walls, glass mesh, mirror sphere, plane are all visible
+    assert (sc.trace_closest(rays, ff.TRACE_BRUTE)["geom"] == want["geom"]).all()
+    assert (sc.trace_any(rays, None) == (want["geom"] >= 0)).all()
+    img, rays_o, shadow_o = osc.render(desc["camera"], desc["spp"], desc["max_bounces"], seed=11, aa=1, nee=nee, want_shadow_rays=True)
+    for integ in (ff.INTEGRATOR_WAVEFRONT, ff.INTEGRATOR_MEGAKERNEL):
+        out, st = sc.render(cam, desc["spp"], desc["max_bounces"], want_stats=True, integrator=integ, seed=11, aa=1, nee=nee)
+        assert (bits(out) == bits(img)).all(), "integrator %d nee %d: max abs diff %g" % (integ, nee, np.abs(out - img).max())
+        assert st["rays"] == rays_o and st["shadow_rays"] == shadow_o
+    assert img[..., :3].max() > 0

@@ -191,3 +191,49 @@ def test_next_event_estimation_agrees_with_plain_loop(orc, meshes):
     p0, _ = s1.render(d1["camera"], 2, 2, background=(0.2, 0.3, 0.4))
     p1, _ = s1.render(d1["camera"], 2, 2, background=(0.2, 0.3, 0.4), nee=1)
     assert (p0.view(np.uint32) == p1.view(np.uint32)).all()
+
+
+def test_sphere_primitive_known_answers(orc):
+    """GeometryType::SPHERE (declared by the reference, branch left empty: kernel.cu:166-169): analytic known answers of
+    the restatement, and the object-space path (mode 0) against the baked path (mode 1)."""
+    sc = orc.scene()
+    sc.add_sphere(1.0)
+    rays = np.float32([[0, 0, 5, 0, 0, -1],      # head on: enters at z = 1, t = 4
+                       [0, 0, 0, 0, 0, -1],      # starts inside: front side only -> miss
+                       [1, 0, 5, 0, 0, -1],      # tangent: discriminant 0 -> miss
+                       [0.6, 0, 5, 0, 0, -2],    # un-normalised direction; enters at z = 0.8
+                       [0, 0, -5, 0, 0, -1]])    # pointing away
+    for mode in (0, 1):
+        h = sc.intersect(rays, mode=mode)
+        assert h["hit"].tolist() == [1, 0, 0, 1, 0]
+        assert h["t"][0] == 4.0 and np.allclose(h["point"][0], [0, 0, 1]) and np.allclose(h["normal"][0], [0, 0, 1])
+        assert np.isclose(h["t"][3], 4.2, atol=1e-6) and h["geom"][0] == 0 and h["tri"][0] == -1
+    # transformed: radius 0.5, scaled (2, 1, 1), moved to x = 3 -> world semi-axes (1, .5, .5)
+    sc2 = orc.scene()
+    sc2.add_sphere(0.5, pos=(3, 0, 0), scale=(2, 1, 1))
+    r2 = np.float32([[3, 0, 5, 0, 0, -1], [10, 0, 0, -1, 0, 0], [3, 0.6, 5, 0, 0, -1]])
+    a, b = sc2.intersect(r2, mode=0), sc2.intersect(r2, mode=1)
+    assert a["hit"].tolist() == [1, 1, 0] and (a["t"].view(np.uint32) == b["t"].view(np.uint32)).all()
+    assert np.isclose(a["t"][0], 4.5) and np.isclose(a["t"][1], 6.0)
+    assert np.allclose(a["normal"][1] / np.linalg.norm(a["normal"][1]), [1, 0, 0])
+
+
+def test_mirror_and_glass_events(orc, meshes):
+    """MIRROR / GLASS (BXDFTyp utilities.h:72-73): a mirror sphere under a uniform sky returns the sky tinted by its
+    specular colour after one bounce; glass splits between the two lobes with Schlick's Fresnel."""
+    sky = (0.5, 0.75, 1.0)
+    cam = S.camera((0, 0, 4), fov=10, width=6, height=6)
+    m = orc.scene()
+    m.add_sphere(1.0, material=dict(type=2, specular=(0.5, 1.0, 0.25)))
+    img, n = m.render(cam, 3, 2, background=sky)
+    assert np.allclose(img[..., :3], np.float32(sky) * np.float32([0.5, 1.0, 0.25]), atol=1e-6) and n == 6 * 6 * 3 * 2
+    g = orc.scene()
+    g.add_sphere(1.0, material=dict(type=3, ior=1.5, specular=(1, 0, 0), transmittance=(0, 0, 1)))
+    big = S.camera((0, 0, 4), fov=2, width=32, height=32)  # near-normal incidence: F = r0 = 0.04
+    img, _ = g.render(big, 64, 1, background=(1, 1, 1), aa=1)
+    red, blue = img[..., 0].mean(), img[..., 2].mean()
+    assert abs(red - 0.04) < 0.01 and abs(blue - 0.96) < 0.01 and np.allclose(img[..., 1], 0)
+    # refraction bends towards the normal: a ray entering off-axis leaves the front interface closer to -n
+    off = S.camera((0.9, 0, 4), yaw=-90, fov=0.01, width=1, height=1)
+    o = g.render(off, 1, 0, background=(0, 0, 0))  # max_bounces 0: nothing to add, just must not crash
+    assert o[0].shape == (1, 1, 4)

@@ -70,6 +70,10 @@ class CSceneInfo(C.Structure):
         return d
 
 
+class CSceneFile(C.Structure):
+    _fields_ = [("camera", CCamera), ("params", CRenderParams), ("builder", C.c_int), ("n_geometries", C.c_int)]
+
+
 lib.ff_last_error.restype = C.c_char_p
 lib.ff_load_obj.restype = C.c_long
 lib.ff_load_obj.argtypes = [C.c_char_p, C.c_void_p, C.c_size_t]
@@ -78,6 +82,8 @@ lib.ff_context_create.argtypes = [C.POINTER(_vp), C.c_int]
 lib.ff_context_destroy.argtypes = [_vp]
 lib.ff_context_synchronize.argtypes = [_vp]
 lib.ff_timer_begin.argtypes = [_vp]
+lib.ff_scene_load_file.argtypes = [_vp, C.c_char_p, C.c_char_p, C.POINTER(_vp), C.POINTER(CSceneFile)]
+lib.ff_scene_file_validate.argtypes = [C.c_char_p, C.POINTER(CSceneFile)]
 lib.ff_context_release_scratch.argtypes = [_vp]
 lib.ff_timer_end.argtypes = [_vp, C.POINTER(C.c_double)]
 lib.ff_scene_create.argtypes = [_vp, C.POINTER(_vp)]
@@ -460,6 +466,24 @@ class Scene:
         ptr = d_accum.ptr if isinstance(d_accum, DeviceBuffer) else C.c_void_p(int(d_accum))
         _check(lib.ff_render_accumulate(self.h, C.byref(cam.c), C.byref(p), ptr, C.byref(st)))
         return st.as_dict()
+
+
+def validate_scene_file(path):
+    """Parses a scene description file without touching a device; returns the CSceneFile (camera, params, builder)."""
+    d = CSceneFile()
+    _check(lib.ff_scene_file_validate(os.fsencode(path), C.byref(d)))
+    return d
+
+
+def load_scene_file(ctx, path, asset_dir=None):
+    """Scene description file -> (Scene (not committed), Camera, CSceneFile)."""
+    d = CSceneFile()
+    sc = Scene.__new__(Scene)
+    sc.ctx, sc.h = ctx, C.c_void_p()
+    _check(lib.ff_scene_load_file(ctx.h, os.fsencode(path), os.fsencode(asset_dir) if asset_dir else None, C.byref(sc.h), C.byref(d)))
+    cam = Camera(pos=tuple(d.camera.pos), yaw=d.camera.yaw_deg, pitch=d.camera.pitch_deg, fov=d.camera.fov_deg, width=d.camera.width,
+                 height=d.camera.height, near=d.camera.near_clip, far=d.camera.far_clip, world_up=tuple(d.camera.world_up))
+    return sc, cam, d
 
 
 def write_image(path, rgba):

@@ -11,7 +11,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libfirefly_b200.so")
-SOURCES = ["ff_trace.cu", "ff_bvh.cu", "ff_sah.cu", "ff_render.cu", "ff_api.cpp", "ff_io.cpp"]
+SOURCES = ["ff_trace.cu", "ff_bvh.cu", "ff_sah.cu", "ff_render.cu", "ff_api.cpp", "ff_io.cpp", "ff_scenefile.cpp"]
+CLI = os.path.join(HERE, "firefly_cli")   # headless front end, links against the C ABI only
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-ffp-contract=off,-fno-fast-math,-Wall",
@@ -24,7 +25,7 @@ def _deps():
 
 
 def needs_build():
-    if not os.path.exists(LIB):
+    if not os.path.exists(LIB) or not os.path.exists(CLI):
         return True
     t = os.path.getmtime(LIB)
     return any(os.path.getmtime(d) > t for d in _deps())
@@ -49,8 +50,14 @@ def build(force=False, verbose=False):
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n%s\n%s" % (r.stdout, r.stderr))
+    # the CLI is plain C++ over include/firefly.h; rpath $ORIGIN so it finds the library next to it
+    cmd = [os.environ.get("CXX", "g++"), "-O2", "-std=c++17", "-Wall", os.path.join(CSRC, "firefly_cli.cpp"), "-o", CLI,
+           "-L" + HERE, "-lfirefly_b200", "-Wl,-rpath,$ORIGIN"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("CLI link failed:\n%s\n%s" % (r.stdout, r.stderr))
     if verbose:
-        print("built", LIB)
+        print("built", LIB, "and", CLI)
     return LIB
 
 

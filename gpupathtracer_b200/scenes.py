@@ -161,3 +161,66 @@ def instantiate_on(desc, scene, meshes=None):
         else:
             scene.add_mesh(resolve_mesh(g, meshes), g["pos"], g["rot"], g["scale"], g["material"])
     return scene
+
+
+# --------------------------------------------------------------------------------------------- scene files
+_TYPE_NAMES = {0: "emitter", 1: "diffuse", 2: "mirror", 3: "glass"}
+
+
+def _f(v):
+    return " ".join("%.9g" % float(np.float32(x)) for x in v)
+
+
+def write_obj(path, xyz9):
+    """Triangle positions -> a minimal OBJ (one 'v' per corner, one 'f' per triangle); float32 values round-trip exactly."""
+    xyz9 = np.ascontiguousarray(xyz9, np.float32).reshape(-1, 9)
+    with open(path, "w") as f:
+        for t in xyz9:
+            for k in range(3):
+                f.write("v %s\n" % _f(t[3 * k:3 * k + 3]))
+        for i in range(len(xyz9)):
+            f.write("f %d %d %d\n" % (3 * i + 1, 3 * i + 2, 3 * i + 3))
+
+
+def write_scene_file(desc, path, meshes=None, mesh_dir=None, render=None, inline_limit=64):
+    """Writes a description as a scene file (format: csrc/ff_scenefile.cpp).  Named meshes and arrays of more than
+    `inline_limit` triangles become OBJ files in `mesh_dir` (default: next to the scene file); small arrays become inline
+    `triangles` blocks.  `render` overrides/extends the render line (dict: spp, bounces, seed, nee, aa, integrator, builder...)."""
+    mesh_dir = mesh_dir or os.path.dirname(os.path.abspath(path))
+    os.makedirs(mesh_dir, exist_ok=True)
+    c = desc["camera"]
+    lines = ["# %s -- written by gpupathtracer_b200.scenes.write_scene_file" % desc.get("name", "scene"),
+             "camera pos %s up %s yaw %.9g pitch %.9g fov %.9g size %d %d near %.9g far %.9g" % (
+                 _f(c["pos"]), _f(c.get("world_up", (0, 1, 0))), c["yaw"], c["pitch"], c["fov"], c["width"], c["height"], c["near"], c["far"])]
+    mats = {}
+    for gi, g in enumerate(desc["geoms"]):
+        m = g["material"]
+        key = repr(sorted((k, tuple(np.atleast_1d(v).tolist())) for k, v in m.items()))
+        if key not in mats:
+            mats[key] = "m%d" % len(mats)
+            lines.append("material %s %s albedo %s emissive %s intensity %.9g specular %s ior %.9g transmittance %s" % (
+                mats[key], _TYPE_NAMES[int(m.get("type", 1))], _f(m.get("albedo", (0.8, 0.8, 0.8))), _f(m.get("emissive", (0, 0, 0))),
+                m.get("intensity", 0.0), _f(m.get("specular", (1, 1, 1))), m.get("ior", 1.5), _f(m.get("transmittance", (1, 1, 1)))))
+        place = "pos %s rot %s scale %s material %s" % (_f(g["pos"]), _f(g["rot"]), _f(g["scale"]), mats[key])
+        if g.get("sphere") is not None:
+            lines.append("sphere %.9g %s" % (g["sphere"], place))
+        elif g["plane"]:
+            lines.append("plane %s" % place)
+        else:
+            tri = np.ascontiguousarray(meshes[g["mesh"]] if isinstance(g["mesh"], str) else g["mesh"], np.float32).reshape(-1, 9)
+            flip = " flip" if g["flip"] else ""
+            if isinstance(g["mesh"], str) or len(tri) > inline_limit:
+                name = (g["mesh"] if isinstance(g["mesh"], str) else "geom%d" % gi) + ".obj"
+                if not os.path.exists(os.path.join(mesh_dir, name)):
+                    write_obj(os.path.join(mesh_dir, name), tri)
+                lines.append("mesh %s %s%s" % (name, place, flip))
+            else:
+                lines.append("triangles %s%s" % (place, flip))
+                lines += ["tri %s" % _f(t) for t in tri]
+                lines.append("end")
+    r = dict(spp=desc.get("spp", 1), bounces=desc.get("max_bounces", 4))
+    r.update(render or {})
+    lines.append("render " + " ".join("%s %s" % (k, _f(v) if isinstance(v, (tuple, list)) else v) for k, v in r.items()))
+    with open(path, "w") as f:
+        f.write("\n".join(lines) + "\n")
+    return path

@@ -218,6 +218,21 @@ int ff_ipc_close_handle(ff_context* ctx, void* d_ptr);
 /* Writes > L2-size scratch so the next timed launch starts cold. */
 int ff_flush_l2(ff_context* ctx);
 
+/* -- scene description file: replaces the scene and camera literals of main() (kernel.cu:227-259, 311-322; its
+ *    "TODO: Load scene from file", kernel.cu:261).  The format is documented at the top of csrc/ff_scenefile.cpp and
+ *    in INTEGRATION.md: camera / material / mesh / plane / sphere / triangles / soup / render directives, one per line.
+ *    ff_scene_load_file creates the scene (NOT committed: call ff_scene_commit(scene, desc.builder, ..)) and returns
+ *    the camera and render parameters the file asks for.  Relative mesh paths resolve against asset_dir, or the
+ *    scene file's own directory when asset_dir is NULL.  ff_scene_file_validate only parses (no device needed). */
+typedef struct ff_scene_file {
+    ff_camera camera;
+    ff_render_params params;
+    int builder;
+    int n_geometries;
+} ff_scene_file;
+int ff_scene_load_file(ff_context* ctx, const char* path, const char* asset_dir, ff_scene** out_scene, ff_scene_file* out_desc);
+int ff_scene_file_validate(const char* path, ff_scene_file* out_desc);
+
 /* -- headless output.  Replaces saveToPPM (utilities.h:842-856).  Format by extension:
  *    .ppm (binary P6), .png (8-bit sRGB), .exr (fp32 scanline, uncompressed), .pfm. */
 int ff_write_image(const char* path, const float* rgba, int width, int height);

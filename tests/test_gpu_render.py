@@ -1,6 +1,8 @@
 """GPU: the integrators against the CPU oracle's as-intended path tracer (same Philox stream, same operation order,
 samples summed in index order) -- the images are required to be BIT-IDENTICAL on one GPU, which is far inside the
 per-pixel RMSE <= 1e-3 the north star asks for -- plus the as-coded normal frame, sample splitting and u8 output."""
+import os
+
 import numpy as np
 import pytest
 
@@ -171,3 +173,34 @@ def test_showcase_all_material_and_geometry_types(ff, ctx, orc, meshes, nee):
         assert (bits(out) == bits(img)).all(), "integrator %d nee %d: max abs diff %g" % (integ, nee, np.abs(out - img).max())
         assert st["rays"] == rays_o and st["shadow_rays"] == shadow_o
     assert img[..., :3].max() > 0
+
+
+def test_scene_file_and_headless_cli(ff, ctx, orc, meshes, tmp_path):
+    """Scene file -> library (ff_scene_load_file) and -> firefly_cli (C++ over the C ABI only) -> PFM: both give the frame
+    the Python-built description gives, which is the oracle's frame."""
+    import json
+    import subprocess
+    desc = S.showcase(meshes, 64, 48, 3, 5)
+    path = S.write_scene_file(desc, str(tmp_path / "show.ffscene"), meshes, render=dict(seed=21, aa=1, nee=1))
+    osc = S.instantiate_on(desc, orc.scene(), meshes)
+    want, _ = osc.render(desc["camera"], 3, 5, seed=21, aa=1, nee=1)
+    sc, cam, d = ff.load_scene_file(ctx, path)
+    sc.commit(d.builder)
+    got = sc.render(cam, d.params.spp, d.params.max_bounces, seed=d.params.seed, aa=d.params.aa, nee=d.params.nee)
+    assert (bits(got) == bits(want)).all()
+    cli = os.path.join(os.path.dirname(ff.__file__), "firefly_cli")
+    out = str(tmp_path / "show.pfm")
+    r = subprocess.run([cli, path, "--out", out, "--integrator", "megakernel"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    st = json.loads(r.stdout.strip().splitlines()[-1])
+    assert st["geometries"] == 6 and st["spp"] == 3 and st["nee"] == 1 and st["rays"] > 0 and st["shadow_rays"] > 0
+    raw = open(out, "rb").read()
+    hdr, dims, scale, body = raw.split(b"\n", 3)
+    assert hdr == b"PF" and dims.split() == [b"64", b"48"] and float(scale) < 0
+    img = np.frombuffer(body, "<f4").reshape(48, 64, 3)[::-1]  # PFM rows run bottom to top
+    assert (bits(img) == bits(want[..., :3])).all()
+    png = str(tmp_path / "show.png")
+    r = subprocess.run([cli, path, "--out", png, "--spp", "1", "--size", "32", "24", "--builder", "sah"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and open(png, "rb").read(8) == b"\x89PNG\r\n\x1a\n"
+    r = subprocess.run([cli, str(tmp_path / "nope.ffscene")], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 1 and "cannot read scene file" in r.stderr

@@ -181,3 +181,27 @@ def test_scene_descriptions(meshes):
     assert sum(len(S.resolve_mesh(g, meshes)) for g in d3["geoms"]) == 5172 + 320 + 2
     f = S.flip_winding(meshes["triangle"])
     assert (f[0] == [0, 0, 0, 0, 1, 0, 1, 0, 0]).all()
+
+
+def test_scene_file_parser(ff, meshes, tmp_path):
+    """The scene description format (replaces the literals of main(), kernel.cu:227-259): parse without a device."""
+    p = S.write_scene_file(S.showcase(meshes, 96, 64, 3, 5), str(tmp_path / "show.ffscene"), meshes,
+                           render=dict(seed=7, nee=1, aa=1, integrator="megakernel", builder="sah", background=(0.1, 0.2, 0.3)))
+    d = ff.validate_scene_file(p)
+    assert d.n_geometries == 6 and d.builder == ff.BUILDER_SAH
+    assert (d.camera.width, d.camera.height, d.camera.fov_deg, d.camera.yaw_deg) == (96, 64, 70.0, -90.0)
+    assert (d.params.spp, d.params.max_bounces, d.params.seed, d.params.nee, d.params.aa) == (3, 5, 7, 1, 1)
+    assert d.params.integrator == ff.INTEGRATOR_MEGAKERNEL and np.allclose(list(d.params.background), [0.1, 0.2, 0.3])
+    assert os.path.exists(tmp_path / "rocketman.obj")
+    assert (ff.load_obj(str(tmp_path / "rocketman.obj")).view(np.uint32) == meshes["rocketman"].view(np.uint32)).all()
+    bad = {"camera pos 1 2": "pos needs 3", "mesh": "needs a path", "sphere -1": "positive radius", "frobnicate 1": "unknown directive",
+           "plane material nope": "unknown material", "triangles\ntri 1 2 3": "exactly 9", "triangles\ntri 0 0 0 1 0 0 0 1 0": "without 'end'",
+           "render spp 0": "positive integer", "camera size 10 10": "no geometry", "material a shiny": "unknown material type"}
+    for text, msg in bad.items():
+        q = tmp_path / "bad.ffscene"
+        q.write_text(text + "\n")
+        with pytest.raises(ff.FireflyError) as e:
+            ff.validate_scene_file(str(q))
+        assert msg in str(e.value), (text, str(e.value))
+    with pytest.raises(ff.FireflyError):
+        ff.validate_scene_file(str(tmp_path / "missing.ffscene"))

@@ -210,13 +210,13 @@ def run_gpu_arm(args):
         return 1e-3 * ctx.timer_end(), st
 
     def step_e2e():
-        """The user-facing call with HOST buffers: camera/params in, framebuffer out to host memory."""
+        """The user-facing call with HOST buffers: camera/params in (by value), framebuffer out to page-locked host memory."""
         barrier()
         ctx.timer_begin()
         if world == 1:
-            _, st = sc.render(cam, SPP, BOUNCES, want_stats=True, first_sample=first)
+            _, st = sc.render(cam, SPP, BOUNCES, want_stats=True, first_sample=first, pinned=True)
         else:
-            _, st = M.render_distributed_weak(sc, cam, SPP, BOUNCES, dist, mode=args.reduce, to_host=True)
+            _, st = M.render_distributed_weak(sc, cam, SPP, BOUNCES, dist, mode=args.reduce, to_host=True, pinned=True)
         barrier()
         return 1e-3 * ctx.timer_end(), st
 
@@ -250,6 +250,7 @@ def run_gpu_arm(args):
     for _ in range(args.steps):
         ctx.flush_l2()
         dt, st = step_device()
+        log("rank %d device step: %.3f ms (device clock), library kernels %.3f ms" % (rank, 1e3 * dt, st["gpu_ms"]))
         secs += maxreduce(dt)
         trace_ms += st["trace_ms"]
         gpu_ms += st["gpu_ms"]
@@ -260,6 +261,7 @@ def run_gpu_arm(args):
     for _ in range(args.steps):
         ctx.flush_l2()
         dt, st = step_e2e()
+        log("rank %d e2e step: %.3f ms (device clock), library kernels %.3f ms" % (rank, 1e3 * dt, st["gpu_ms"]))
         e_secs += maxreduce(dt)
         e_rays += int(sumreduce(st["rays"]))
     clocks = sampler.stop() if rank == 0 else None

@@ -274,6 +274,8 @@ class Context:
 
     def close(self):
         if self.h:
+            for _, p in self.__dict__.pop("_pinned", {}).values():
+                lib.ff_host_free_pinned(p)
             lib.ff_context_destroy(self.h)
             self.h = C.c_void_p()
 
@@ -285,6 +287,19 @@ class Context:
 
     def scene(self):
         return Scene(self)
+
+    def pinned_array(self, shape, dtype=np.float32):
+        """A numpy array over page-locked host memory (cudaHostAlloc), cached per (shape, dtype) for the life of the
+        context: device<->host copies to it are true DMA transfers.  Reused by later calls with the same shape."""
+        key = (tuple(shape), np.dtype(dtype).str)
+        cache = self.__dict__.setdefault("_pinned", {})
+        if key not in cache:
+            nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+            p = C.c_void_p()
+            _check(lib.ff_host_alloc_pinned(nbytes, C.byref(p)))
+            buf = (C.c_char * nbytes).from_address(p.value)
+            cache[key] = (np.frombuffer(buf, dtype=dtype).reshape(shape), p)
+        return cache[key][0]
 
     def alloc(self, nbytes):
         return DeviceBuffer(self, nbytes)
@@ -325,15 +340,15 @@ class Context:
         _check(lib.ff_camera_rays(self.h, C.byref(cam.c), _p(out), device_buffer.ptr if device_buffer is not None else None))
         return out
 
-    def resolve(self, accum, width, height, total_spp, host=True, device_out=None):
-        out = np.empty((height, width, 4), np.float32) if host else None
+    def resolve(self, accum, width, height, total_spp, host=True, device_out=None, pinned=False):
+        out = (self.pinned_array((height, width, 4)) if pinned else np.empty((height, width, 4), np.float32)) if host else None
         _check(lib.ff_resolve(self.h, accum.ptr if isinstance(accum, DeviceBuffer) else C.c_void_p(accum), width, height,
                               int(total_spp), C.c_void_p(device_out) if device_out is not None else None, _p(out)))
         return out
 
-    def reduce_resolve_peers(self, ptrs, width, height, total_spp, host=True, device_out=None):
+    def reduce_resolve_peers(self, ptrs, width, height, total_spp, host=True, device_out=None, pinned=False):
         arr = (C.c_void_p * len(ptrs))(*[C.c_void_p(int(p)) for p in ptrs])
-        out = np.empty((height, width, 4), np.float32) if host else None
+        out = (self.pinned_array((height, width, 4)) if pinned else np.empty((height, width, 4), np.float32)) if host else None
         _check(lib.ff_reduce_resolve_peers(self.h, arr, len(ptrs), width, height, int(total_spp),
                                            C.c_void_p(device_out) if device_out is not None else None, _p(out)))
         return out
@@ -445,9 +460,13 @@ class Scene:
         return out_n.value
 
     # ---- render (launchPathTrace, kernel.cu:218-221,342)
-    def render(self, cam, spp=1, max_bounces=4, want_stats=False, host=True, device_out=None, **kw):
+    def render(self, cam, spp=1, max_bounces=4, want_stats=False, host=True, device_out=None, pinned=False, **kw):
+        """ff_render.  pinned=True returns the frame in the context's cached page-locked array (overwritten by the next
+        such call) instead of a fresh pageable one."""
         p = render_params(spp, max_bounces, **kw)
-        out = np.empty((cam.height, cam.width, 4), np.float32) if host else None
+        out = None
+        if host:
+            out = self.ctx.pinned_array((cam.height, cam.width, 4)) if pinned else np.empty((cam.height, cam.width, 4), np.float32)
         st = CStats()
         _check(lib.ff_render(self.h, C.byref(cam.c), C.byref(p), _p(out), device_out.ptr if device_out is not None else None,
                              C.byref(st)))

@@ -45,6 +45,8 @@ struct ff_context {
     size_t flush_n = 0;
     cudaEvent_t timer_ev[2] = {nullptr, nullptr};  // ff_timer_begin / ff_timer_end
     bool timer_open = false;
+    float4* resolve_buf = nullptr;  // device staging of ff_resolve / ff_reduce_resolve_peers when the caller gives no device output
+    size_t resolve_pixels = 0;
     Arena arena;                    // builder scratch, reused by every commit on this context
     std::vector<ff_scene*> scenes;  // live scenes: orphaned (device memory released) if the context goes first
 };
@@ -156,6 +158,7 @@ void ff_context_destroy(ff_context* ctx) {
     for (int k = 0; k < 4; ++k) cudaEventDestroy(ctx->ev[k]);
     for (int k = 0; k < 2; ++k) cudaEventDestroy(ctx->timer_ev[k]);
     cudaFree(ctx->flush_buf);
+    cudaFree(ctx->resolve_buf);
     ctx->arena.release();
     cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -823,13 +826,19 @@ int ff_reduce_resolve_peers(ff_context* ctx, const void* const* d_accum_peers, i
     FF_CUDA(cudaSetDevice(ctx->device));
     const size_t npix = (size_t)width * height;
     float4* d_out = (float4*)d_out_rgba;
-    if (!d_out) FF_CUDA(cudaMalloc((void**)&d_out, sizeof(float4) * npix));
+    if (!d_out) {
+        if (ctx->resolve_pixels < npix) {
+            cudaFree(ctx->resolve_buf); ctx->resolve_buf = nullptr; ctx->resolve_pixels = 0;
+            FF_CUDA(cudaMalloc((void**)&ctx->resolve_buf, sizeof(float4) * npix));
+            ctx->resolve_pixels = npix;
+        }
+        d_out = ctx->resolve_buf;
+    }
     const float inv = 1.0f / (float)total_spp;
     k_resolve((const float4* const*)d_accum_peers, n_peers, (uint32_t)npix, inv, d_out, ctx->stream);
     if (out_rgba_host) FF_CUDA(cudaMemcpyAsync(out_rgba_host, d_out, sizeof(float4) * npix, cudaMemcpyDeviceToHost, ctx->stream));
     FF_CUDA(cudaStreamSynchronize(ctx->stream));
     FF_CUDA(cudaGetLastError());
-    if (!d_out_rgba) cudaFree(d_out);
     return FF_OK;
 }
 

@@ -48,7 +48,7 @@ def reduce_sums(local_sum, dist, dst=0):
     return local_sum
 
 
-def render_distributed(scene, cam, spp, max_bounces, dist=None, mode="nccl", split="strong", to_host=True, **kw):
+def render_distributed(scene, cam, spp, max_bounces, dist=None, mode="nccl", split="strong", to_host=True, pinned=False, **kw):
     """Renders one frame over dist's world; returns (image on rank 0 or None, this rank's ff stats dict).
 
     split="strong": `spp` is the frame's total, rank k renders sample_range(k, G, spp).
@@ -87,7 +87,7 @@ def render_distributed(scene, cam, spp, max_bounces, dist=None, mode="nccl", spl
             reduce_sums(accum, dist, 0)
             torch.cuda.synchronize(dev)
         if rank == 0:
-            img = scene.ctx.resolve(accum_ptr, w, h, total, host=to_host, device_out=d_out.data_ptr() if d_out is not None else None)
+            img = scene.ctx.resolve(accum_ptr, w, h, total, host=to_host, device_out=d_out.data_ptr() if d_out is not None else None, pinned=pinned)
         return img, stats
     if mode == "peer":
         handle = np.zeros(64, np.uint8)
@@ -106,7 +106,7 @@ def render_distributed(scene, cam, spp, max_bounces, dist=None, mode="nccl", spl
                 ff._check(ff.lib.ff_ipc_open_handle(scene.ctx.h, hb.ctypes.data_as(C.c_void_p), C.byref(p)))
                 ptrs.append(p.value)
                 opened.append(p)
-            img = scene.ctx.reduce_resolve_peers(ptrs, w, h, total, host=to_host, device_out=d_out.data_ptr() if d_out is not None else None)
+            img = scene.ctx.reduce_resolve_peers(ptrs, w, h, total, host=to_host, device_out=d_out.data_ptr() if d_out is not None else None, pinned=pinned)
             for p in opened:
                 ff.lib.ff_ipc_close_handle(scene.ctx.h, p)
         dist.barrier()  # peers keep their accumulators alive until rank 0 has read them
@@ -115,5 +115,5 @@ def render_distributed(scene, cam, spp, max_bounces, dist=None, mode="nccl", spl
     raise ValueError("mode must be 'nccl' or 'peer'")
 
 
-def render_distributed_weak(scene, cam, spp, max_bounces, dist, mode="nccl", to_host=True, **kw):
-    return render_distributed(scene, cam, spp, max_bounces, dist, mode, "weak", to_host, **kw)
+def render_distributed_weak(scene, cam, spp, max_bounces, dist, mode="nccl", to_host=True, pinned=False, **kw):
+    return render_distributed(scene, cam, spp, max_bounces, dist, mode, "weak", to_host, pinned, **kw)

@@ -11,7 +11,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libfirefly_b200.so")
+LIB_PATH = os.environ.get("FF_LIB_OVERRIDE") or os.path.join(_HERE, "libfirefly_b200.so")  # override: kernel-variant experiments
 
 if not os.path.exists(LIB_PATH):
     raise ImportError("%s is missing: run `python gpupathtracer_b200/build.py` (or __graft_entry__.build()); "

@@ -16,7 +16,7 @@ CLI = os.path.join(HERE, "firefly_cli")   # headless front end, links against th
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-ffp-contract=off,-fno-fast-math,-Wall",
-         "-Wno-deprecated-gpu-targets"]
+         "-Wno-deprecated-gpu-targets"] + os.environ.get("FF_EXTRA_NVCC_FLAGS", "").split()  # extra -D... for experiments
 
 
 def _deps():

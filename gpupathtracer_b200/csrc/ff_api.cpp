@@ -1046,7 +1046,7 @@ int ff_flush_l2(ff_context* ctx) {
 
 int ff_debug_set_tuning(int postpone_div, int refill_lanes, int blocks_per_sm) {
     if (postpone_div > 0) tuning().postpone_div = postpone_div;
-    if (refill_lanes >= 0) tuning().refill_lanes = refill_lanes;
+    if (refill_lanes > 0) tuning().refill_lanes = refill_lanes;
     if (blocks_per_sm > 0) tuning().blocks_per_sm = blocks_per_sm;
     return FF_OK;
 }

@@ -293,7 +293,7 @@ __device__ __forceinline__ float box_area_lohi(const float4& lo, const float4& h
 // lo.w = triangle count (int bits), hi.w = first sorted position (int bits)
 __global__ void refit_kernel(const float4* __restrict__ flat_tris, const uint32_t* __restrict__ sorted_idx, int n, float pad,
                              const int2* __restrict__ children, const uint32_t* __restrict__ parent, uint32_t* __restrict__ flags,
-                             float4* __restrict__ box_lo, float4* __restrict__ box_hi, float* __restrict__ cost) {
+                             float4* __restrict__ box_lo, float4* __restrict__ box_hi, float* __restrict__ cost, float slot_cost) {
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
         const uint32_t src = sorted_idx[k];
         const float4 a = flat_tris[3 * (size_t)src], b = flat_tris[3 * (size_t)src + 1], c = flat_tris[3 * (size_t)src + 2];
@@ -302,7 +302,7 @@ __global__ void refit_kernel(const float4* __restrict__ flat_tris, const uint32_
         uint32_t node = (uint32_t)(n - 1 + k);
         box_lo[node] = lo;
         box_hi[node] = hi;
-        cost[node] = box_area_lohi(lo, hi) * (FF_SLOT_COST + 1.0f);
+        cost[node] = box_area_lohi(lo, hi) * (slot_cost + 1.0f);
         if (n == 1) return;
         for (;;) {
             const uint32_t p = parent[node];
@@ -328,7 +328,7 @@ __global__ void refit_kernel(const float4* __restrict__ flat_tris, const uint32_
             int flag = 0;
             float best = split;
             if (cnt <= 3) {
-                const float leaf = box_area_lohi(lo, hi) * (FF_SLOT_COST + (float)cnt);
+                const float leaf = box_area_lohi(lo, hi) * (slot_cost + (float)cnt);
                 if (split < leaf) flag = FF_PREFER_OPEN; else best = leaf;
             }
             cost[p] = best;
@@ -576,8 +576,10 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
         ++*launches;
         mark("karras hierarchy");
     }
+    const char* sc_env = getenv("FF_SLOT_COST");  // development knob: leaf-or-open trade-off of the refit DP
+    const float slot_cost = sc_env ? (float)atof(sc_env) : FF_SLOT_COST;
     refit_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(d_flat_tris, d_order, (int)n, pad, d_bvh2_children, d_parent, d_flags,
-                                                            d_bvh2_lo, d_bvh2_hi, d_cost);
+                                                            d_bvh2_lo, d_bvh2_hi, d_cost, slot_cost);
     ++*launches;
     mark("refit + leaf/open DP");
 

@@ -19,6 +19,8 @@ if not os.path.exists(LIB_PATH):
 lib = C.CDLL(LIB_PATH)
 
 INTEGRATOR_WAVEFRONT, INTEGRATOR_MEGAKERNEL, INTEGRATOR_AS_CODED = 0, 1, 2
+AOV_NORMAL, AOV_UV, AOV_BARY, AOV_ALBEDO = 3, 4, 5, 6  # primary-ray feature buffers through render(integrator=...)
+OBJ_FLIP_WINDING, OBJ_NORMALS, OBJ_UVS, OBJ_MATERIALS = 1, 2, 4, 8
 BUILDER_LBVH, BUILDER_SAH = 0, 1
 TRACE_BVH8, TRACE_BRUTE, TRACE_BVH2 = 0, 1, 2
 TRACE_COUNT = 0x100
@@ -92,6 +94,14 @@ lib.ff_scene_add_obj.argtypes = [_vp, C.c_char_p, _vp, _vp, _vp, _vp, C.c_int, C
 lib.ff_scene_add_triangles.argtypes = [_vp, _vp, _sz, _vp, _vp, _vp, _vp, C.POINTER(C.c_int)]
 lib.ff_scene_add_plane.argtypes = [_vp, _vp, _vp, _vp, _vp, C.POINTER(C.c_int)]
 lib.ff_scene_add_sphere.argtypes = [_vp, C.c_float, _vp, _vp, _vp, _vp, C.POINTER(C.c_int)]
+lib.ff_scene_set_normals.argtypes = [_vp, C.c_int, _vp]
+lib.ff_scene_set_uvs.argtypes = [_vp, C.c_int, _vp]
+lib.ff_scene_set_face_materials.argtypes = [_vp, C.c_int, _vp, _vp, C.c_int]
+lib.ff_scene_add_obj_ex.argtypes = [_vp, C.c_char_p, _vp, _vp, _vp, _vp, C.c_int, C.POINTER(C.c_int)]
+lib.ff_load_obj_ex.restype = C.c_long
+lib.ff_load_obj_ex.argtypes = [C.c_char_p, _vp, _vp, _vp, _vp, _sz, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int),
+                               C.POINTER(C.c_int), C.POINTER(C.c_double)]
+lib.ff_trace_closest_uv.argtypes = [_vp, _vp, _sz, C.c_int, _vp, _vp, _vp, _vp, _vp, C.POINTER(CStats)]
 lib.ff_scene_commit.argtypes = [_vp, C.c_int, C.POINTER(C.c_double)]
 lib.ff_scene_get_info.argtypes = [_vp, C.POINTER(CSceneInfo)]
 lib.ff_scene_get_flat.argtypes = [_vp, _vp, _vp, _vp, _sz]
@@ -156,6 +166,23 @@ def load_obj(path):
     if n:
         lib.ff_load_obj(os.fsencode(path), _p(out), n)
     return out
+
+
+def load_obj_ex(path, threads=0):
+    """OBJ file with every attribute LoadMesh keeps (utilities.h:806-837), parsed on `threads` host threads (0 = all):
+    dict(xyz9[n,9], normals9[n,9], uvs6[n,6], face_material[n] (index in order of first `usemtl`, -1 none),
+    has_normals, has_uvs, n_materials, seconds)."""
+    hn, hu, nm, sec = C.c_int(0), C.c_int(0), C.c_int(0), C.c_double(0)
+    n = lib.ff_load_obj_ex(os.fsencode(path), None, None, None, None, 0, int(threads), None, None, None, None)
+    if n < 0:
+        _check(int(n))
+    xyz9, n9, uv6, fm = np.zeros((n, 9), np.float32), np.zeros((n, 9), np.float32), np.zeros((n, 6), np.float32), np.zeros(n, np.int32)
+    n2 = lib.ff_load_obj_ex(os.fsencode(path), _p(xyz9), _p(n9), _p(uv6), _p(fm), n, int(threads), C.byref(hn), C.byref(hu),
+                            C.byref(nm), C.byref(sec))
+    if n2 < 0:
+        _check(int(n2))
+    return dict(xyz9=xyz9, normals9=n9, uvs6=uv6, face_material=fm, has_normals=bool(hn.value), has_uvs=bool(hu.value),
+                n_materials=nm.value, seconds=sec.value)
 
 
 def philox4x32_10(ctr, key):
@@ -379,6 +406,31 @@ class Scene:
                                     C.byref(m) if m is not None else None, int(flip_winding), C.byref(idx)))
         return idx.value
 
+    def add_obj_ex(self, path, pos=(0, 0, 0), rot=(0, 0, 0), scale=(1, 1, 1), material=None, flags=0):
+        """add_obj keeping the file's attributes: flags = OBJ_FLIP_WINDING | OBJ_NORMALS | OBJ_UVS | OBJ_MATERIALS."""
+        idx = C.c_int(-1)
+        m = _material_from(material)
+        _check(lib.ff_scene_add_obj_ex(self.h, os.fsencode(path), _p(_f3(pos)), _p(_f3(rot)), _p(_f3(scale)),
+                                       C.byref(m) if m is not None else None, int(flags), C.byref(idx)))
+        return idx.value
+
+    # ---- shading attributes (Triangle::m_n0..2 / m_uv0..2 utilities.h:163-170, material_ids utilities.h:837); None clears
+    def set_normals(self, gi, normals9):
+        a = None if normals9 is None else np.ascontiguousarray(normals9, np.float32).reshape(-1, 9)
+        _check(lib.ff_scene_set_normals(self.h, int(gi), _p(a)))
+
+    def set_uvs(self, gi, uvs6):
+        a = None if uvs6 is None else np.ascontiguousarray(uvs6, np.float32).reshape(-1, 6)
+        _check(lib.ff_scene_set_uvs(self.h, int(gi), _p(a)))
+
+    def set_face_materials(self, gi, face_material, materials=()):
+        if face_material is None:
+            _check(lib.ff_scene_set_face_materials(self.h, int(gi), None, None, 0))
+            return
+        fm = np.ascontiguousarray(face_material, np.int32)
+        arr = (CMaterial * max(1, len(materials)))(*[_material_from(m) for m in materials])
+        _check(lib.ff_scene_set_face_materials(self.h, int(gi), _p(fm), C.cast(arr, C.c_void_p), len(materials)))
+
     def add_triangles(self, xyz9, pos=(0, 0, 0), rot=(0, 0, 0), scale=(1, 1, 1), material=None):
         xyz9 = np.ascontiguousarray(xyz9, np.float32).reshape(-1, 9)
         idx = C.c_int(-1)
@@ -434,6 +486,15 @@ class Scene:
         _check(lib.ff_trace_closest(self.h, _p(rays), n, int(mode), _p(geom), _p(tri), _p(t), C.byref(st)))
         out = dict(hit=(geom >= 0).astype(np.uint8), geom=geom, tri=tri, t=t)
         return (out, st.as_dict()) if want_stats else out
+
+    def trace_closest_uv(self, rays, mode=TRACE_BVH8):
+        """trace_closest + the barycentrics of each hit (u, v weight v1, v2; kernel.cu:80-81)."""
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
+        n = len(rays)
+        geom, tri, t = np.empty(n, np.int32), np.empty(n, np.int32), np.empty(n, np.float32)
+        u, v = np.empty(n, np.float32), np.empty(n, np.float32)
+        _check(lib.ff_trace_closest_uv(self.h, _p(rays), n, int(mode), _p(geom), _p(tri), _p(t), _p(u), _p(v), None))
+        return dict(hit=(geom >= 0).astype(np.uint8), geom=geom, tri=tri, t=t, u=u, v=v)
 
     def trace_closest_device(self, d_rays, n, d_hits, mode=TRACE_BVH8):
         st = CStats()

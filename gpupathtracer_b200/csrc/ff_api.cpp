@@ -1,6 +1,7 @@
 // ff_api.cpp -- the C ABI of include/firefly.h: context, scene building / commit, trace and render entry points.
 // Host counterpart of the reference's main() set-up code (kernel.cu:223-329) and per-frame launch (kernel.cu:331-344).
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -57,6 +58,10 @@ struct HostGeom {
     M4 model, inv;
     ff_material mat;
     std::vector<float> xyz9;  // object space
+    // optional shading attributes, empty when absent
+    std::vector<float> n9, uv6;              // per-corner object-space normals / uvs
+    std::vector<int> face_mat;               // per triangle: index into face_materials, -1 = mat
+    std::vector<ff_material> face_materials;
 };
 
 struct ff_scene {
@@ -72,6 +77,10 @@ struct ff_scene {
     float4* d_materials = nullptr;
     DevPlane* d_planes = nullptr;
     uint32_t* d_lights = nullptr;
+    int4* d_geom_attr = nullptr;
+    float4* d_attr_normals = nullptr;
+    float2* d_attr_uvs = nullptr;
+    uint32_t* d_attr_facemat = nullptr;
     int2* d_bvh2_children = nullptr;
     float4* d_bvh2_lo = nullptr;
     float4* d_bvh2_hi = nullptr;
@@ -95,6 +104,8 @@ static void free_scene_device(ff_scene* s) {
     cudaFree(s->d_flat); cudaFree(s->d_tris); cudaFree(s->d_nodes); cudaFree(s->d_ord_geom); cudaFree(s->d_ord_tri);
     cudaFree(s->d_materials); cudaFree(s->d_planes); cudaFree(s->d_bvh2_children); cudaFree(s->d_bvh2_lo);
     cudaFree(s->d_bvh2_hi); cudaFree(s->d_leaf_slot); cudaFree(s->d_lights); s->d_lights = nullptr;
+    cudaFree(s->d_geom_attr); cudaFree(s->d_attr_normals); cudaFree(s->d_attr_uvs); cudaFree(s->d_attr_facemat);
+    s->d_geom_attr = nullptr; s->d_attr_normals = nullptr; s->d_attr_uvs = nullptr; s->d_attr_facemat = nullptr;
     s->d_flat = s->d_tris = s->d_nodes = nullptr; s->d_ord_geom = s->d_ord_tri = nullptr; s->d_materials = nullptr;
     s->d_planes = nullptr; s->d_bvh2_children = nullptr; s->d_bvh2_lo = s->d_bvh2_hi = nullptr; s->d_leaf_slot = nullptr;
     s->committed = false;
@@ -294,6 +305,105 @@ int ff_scene_add_sphere(ff_scene* scene, float radius, const float pos[3], const
     return rc;
 }
 
+static int mesh_geom(ff_scene* scene, int gi, const char* who, HostGeom** out) {
+    if (!scene) { set_error(std::string(who) + ": NULL scene"); return FF_ERR_INVALID; }
+    if (gi < 0 || (size_t)gi >= scene->geoms.size() || scene->geoms[(size_t)gi].type != 2) {
+        set_error(std::string(who) + ": geometry index does not name a triangle mesh"); return FF_ERR_INVALID;
+    }
+    *out = &scene->geoms[(size_t)gi];
+    return FF_OK;
+}
+int ff_scene_set_normals(ff_scene* scene, int geometry_index, const float* normals9) {
+    HostGeom* g;
+    int rc = mesh_geom(scene, geometry_index, "ff_scene_set_normals", &g);
+    if (rc) return rc;
+    if (normals9) g->n9.assign(normals9, normals9 + g->xyz9.size()); else g->n9.clear();
+    scene->committed = false;
+    return FF_OK;
+}
+int ff_scene_set_uvs(ff_scene* scene, int geometry_index, const float* uvs6) {
+    HostGeom* g;
+    int rc = mesh_geom(scene, geometry_index, "ff_scene_set_uvs", &g);
+    if (rc) return rc;
+    if (uvs6) g->uv6.assign(uvs6, uvs6 + g->xyz9.size() / 9 * 6); else g->uv6.clear();
+    scene->committed = false;
+    return FF_OK;
+}
+int ff_scene_set_face_materials(ff_scene* scene, int geometry_index, const int* face_material, const ff_material* materials, int n_materials) {
+    HostGeom* g;
+    int rc = mesh_geom(scene, geometry_index, "ff_scene_set_face_materials", &g);
+    if (rc) return rc;
+    scene->committed = false;
+    if (!face_material) { g->face_mat.clear(); g->face_materials.clear(); return FF_OK; }
+    FF_REQUIRE(n_materials >= 0 && (materials || n_materials == 0), "ff_scene_set_face_materials: NULL materials");
+    const size_t nt = g->xyz9.size() / 9;
+    for (size_t t = 0; t < nt; ++t)
+        FF_REQUIRE(face_material[t] >= -1 && face_material[t] < n_materials, "ff_scene_set_face_materials: material index out of range");
+    for (int k = 0; k < n_materials; ++k)
+        FF_REQUIRE(materials[k].type >= FF_MAT_EMITTER && materials[k].type <= FF_MAT_GLASS, "ff_scene_set_face_materials: unknown material type");
+    g->face_mat.assign(face_material, face_material + nt);
+    g->face_materials.assign(materials, materials + n_materials);
+    return FF_OK;
+}
+static std::string dir_of(const std::string& path) {
+    const size_t k = path.find_last_of('/');
+    return k == std::string::npos ? std::string() : path.substr(0, k + 1);
+}
+int ff_scene_add_obj_ex(ff_scene* scene, const char* obj_path, const float pos[3], const float rot_deg[3], const float scale[3],
+                        const ff_material* material, int flags, int* out_geometry_index) {
+    FF_REQUIRE(scene && obj_path, "ff_scene_add_obj_ex: NULL argument");
+    FF_REQUIRE((flags & ~15) == 0, "ff_scene_add_obj_ex: unknown flag");
+    ObjMesh m;
+    if (!load_obj_mesh(obj_path, m, 0)) return FF_ERR_IO;
+    const size_t nt = m.xyz9.size() / 9;
+    if (flags & FF_OBJ_FLIP_WINDING)
+        for (size_t t = 0; t < nt; ++t) {
+            for (int a = 0; a < 3; ++a) { std::swap(m.xyz9[9 * t + 3 + a], m.xyz9[9 * t + 6 + a]); std::swap(m.n9[9 * t + 3 + a], m.n9[9 * t + 6 + a]); }
+            for (int a = 0; a < 2; ++a) std::swap(m.uv6[6 * t + 2 + a], m.uv6[6 * t + 4 + a]);
+        }
+    std::vector<ff_material> mats;
+    std::vector<int> face_mat;
+    if ((flags & FF_OBJ_MATERIALS) && !m.material_names.empty() && !m.mtllib.empty()) {
+        std::vector<std::string> lib_names;
+        std::vector<ff_material> lib_mats;
+        if (!load_mtl((dir_of(obj_path) + m.mtllib).c_str(), lib_names, lib_mats)) return FF_ERR_IO;
+        std::vector<int> remap(m.material_names.size(), -1);
+        for (size_t k = 0; k < m.material_names.size(); ++k) {
+            auto it = std::find(lib_names.begin(), lib_names.end(), m.material_names[k]);
+            if (it != lib_names.end()) { remap[k] = (int)mats.size(); mats.push_back(lib_mats[(size_t)(it - lib_names.begin())]); }
+        }
+        face_mat.resize(nt);
+        for (size_t t = 0; t < nt; ++t) face_mat[t] = m.face_material[t] >= 0 ? remap[(size_t)m.face_material[t]] : -1;
+    }
+    int idx = -1;
+    int rc = add_geom(scene, 2, std::move(m.xyz9), pos, rot_deg, scale, material, &idx);
+    if (rc) return rc;
+    HostGeom& g = scene->geoms[(size_t)idx];
+    if ((flags & FF_OBJ_NORMALS) && m.has_normals) g.n9 = std::move(m.n9);
+    if ((flags & FF_OBJ_UVS) && m.has_uvs) g.uv6 = std::move(m.uv6);
+    if (!mats.empty()) { g.face_mat = std::move(face_mat); g.face_materials = std::move(mats); }
+    if (out_geometry_index) *out_geometry_index = idx;
+    return FF_OK;
+}
+long ff_load_obj_ex(const char* obj_path, float* xyz9, float* normals9, float* uvs6, int* face_material, size_t capacity_tris,
+                    int threads, int* out_has_normals, int* out_has_uvs, int* out_n_materials, double* out_seconds) {
+    if (!obj_path) { set_error("ff_load_obj_ex: NULL path"); return FF_ERR_INVALID; }
+    ObjMesh m;
+    const auto t0 = std::chrono::steady_clock::now();
+    if (!load_obj_mesh(obj_path, m, threads)) return FF_ERR_IO;
+    const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    const size_t n = m.xyz9.size() / 9, k = std::min(n, capacity_tris);
+    if (xyz9) memcpy(xyz9, m.xyz9.data(), sizeof(float) * 9 * k);
+    if (normals9) memcpy(normals9, m.n9.data(), sizeof(float) * 9 * k);
+    if (uvs6) memcpy(uvs6, m.uv6.data(), sizeof(float) * 6 * k);
+    if (face_material) memcpy(face_material, m.face_material.data(), sizeof(int) * k);
+    if (out_has_normals) *out_has_normals = m.has_normals;
+    if (out_has_uvs) *out_has_uvs = m.has_uvs;
+    if (out_n_materials) *out_n_materials = (int)m.material_names.size();
+    if (out_seconds) *out_seconds = sec;
+    return (long)n;
+}
+
 int ff_scene_commit(ff_scene* scene, int builder, double* out_build_ms) {
     FF_REQUIRE(scene, "ff_scene_commit: NULL scene");
     FF_REQUIRE(scene->ctx, "ff_scene_commit: the scene's context was destroyed");
@@ -312,7 +422,22 @@ int ff_scene_commit(ff_scene* scene, int builder, double* out_build_ms) {
     ord_geom.reserve(n_tris + n_planes); ord_tri.reserve(n_tris + n_planes);
     std::vector<uint32_t> geom_of(n_tris), ord_of(n_tris);
     std::vector<M4> models(scene->geoms.size());
-    std::vector<float4> materials(4 * scene->geoms.size());
+    size_t n_rows = scene->geoms.size();
+    for (auto& g : scene->geoms) n_rows += g.face_materials.size();
+    std::vector<float4> materials(4 * n_rows);
+    auto put_material = [&](size_t row, const ff_material& m) {
+        float type_bits; int ty = m.type; memcpy(&type_bits, &ty, 4);
+        materials[4 * row] = make_float4(type_bits, m.albedo[0], m.albedo[1], m.albedo[2]);
+        materials[4 * row + 1] = make_float4(m.emissive[0], m.emissive[1], m.emissive[2], m.intensity);
+        materials[4 * row + 2] = make_float4(m.specular[0], m.specular[1], m.specular[2], m.ior > 0.f ? m.ior : 1.5f);
+        materials[4 * row + 3] = make_float4(m.transmittance[0], m.transmittance[1], m.transmittance[2], 0.f);
+    };
+    std::vector<int4> geom_attr(scene->geoms.size(), make_int4(0, -1, -1, -1));
+    std::vector<float4> attr_normals;
+    std::vector<float2> attr_uvs;
+    std::vector<uint32_t> attr_facemat;
+    size_t next_row = scene->geoms.size();
+    bool has_attr = false;
     std::vector<DevPlane> planes;
     std::vector<uint32_t> lights;  // flat indices of emitter-mesh triangles (next-event estimation samples these)
     float maxabs = 0.f;
@@ -320,16 +445,40 @@ int ff_scene_commit(ff_scene* scene, int builder, double* out_build_ms) {
     for (size_t gi = 0; gi < scene->geoms.size(); ++gi) {
         const HostGeom& g = scene->geoms[gi];
         models[gi] = g.model;
-        float type_bits; int ty = g.mat.type; memcpy(&type_bits, &ty, 4);
-        materials[4 * gi] = make_float4(type_bits, g.mat.albedo[0], g.mat.albedo[1], g.mat.albedo[2]);
-        materials[4 * gi + 1] = make_float4(g.mat.emissive[0], g.mat.emissive[1], g.mat.emissive[2], g.mat.intensity);
-        materials[4 * gi + 2] = make_float4(g.mat.specular[0], g.mat.specular[1], g.mat.specular[2], g.mat.ior > 0.f ? g.mat.ior : 1.5f);
-        materials[4 * gi + 3] = make_float4(g.mat.transmittance[0], g.mat.transmittance[1], g.mat.transmittance[2], 0.f);
+        put_material(gi, g.mat);
         if (g.type == 2) {
             const size_t nt = g.xyz9.size() / 9;
+            int4& ga = geom_attr[gi];
+            ga.x = (int)flat;
+            const size_t first_row = next_row;
+            for (const ff_material& fm : g.face_materials) put_material(next_row++, fm);
+            FF_REQUIRE(g.n9.empty() || g.n9.size() == g.xyz9.size(), "ff_scene_commit: normals do not match the triangle count");
+            FF_REQUIRE(g.uv6.empty() || g.uv6.size() == nt * 6, "ff_scene_commit: uvs do not match the triangle count");
+            FF_REQUIRE(g.face_mat.empty() || g.face_mat.size() == nt, "ff_scene_commit: face materials do not match the triangle count");
+            if (!g.n9.empty() && nt) {
+                // world-space corner normals: inverse(transpose(M)) * (n, 0), left un-normalised like kernel.cu:117
+                has_attr = true;
+                ga.y = (int)attr_normals.size();
+                const M4 nm = ffh::inverted(ffh::transposed(g.model));
+                for (size_t c = 0; c < 3 * nt; ++c) {
+                    const ffm::V4 nw = ffh::matvec(nm, ffh::v4(g.n9[3 * c], g.n9[3 * c + 1], g.n9[3 * c + 2], 0));
+                    attr_normals.push_back(make_float4(nw.x, nw.y, nw.z, 0.f));
+                }
+            }
+            if (!g.uv6.empty() && nt) {
+                has_attr = true;
+                ga.z = (int)attr_uvs.size();
+                for (size_t c = 0; c < 3 * nt; ++c) attr_uvs.push_back(make_float2(g.uv6[2 * c], g.uv6[2 * c + 1]));
+            }
+            if (!g.face_mat.empty() && nt) {
+                has_attr = true;
+                ga.w = (int)attr_facemat.size();
+                for (size_t t = 0; t < nt; ++t) attr_facemat.push_back(g.face_mat[t] < 0 ? (uint32_t)gi : (uint32_t)(first_row + (size_t)g.face_mat[t]));
+            }
             for (size_t t = 0; t < nt; ++t, ++flat) {
                 geom_of[flat] = (uint32_t)gi; ord_of[flat] = (uint32_t)ord_geom.size();
-                if (g.mat.type == FF_MAT_EMITTER) lights.push_back((uint32_t)flat);
+                const int mt = g.face_mat.empty() || g.face_mat[t] < 0 ? g.mat.type : g.face_materials[(size_t)g.face_mat[t]].type;
+                if (mt == FF_MAT_EMITTER) lights.push_back((uint32_t)flat);
                 ord_geom.push_back((int)gi); ord_tri.push_back((int)t);
             }
         } else {
@@ -349,6 +498,11 @@ int ff_scene_commit(ff_scene* scene, int builder, double* out_build_ms) {
     FF_CUDA(upload(&scene->d_materials, materials, st));
     FF_CUDA(upload(&scene->d_planes, planes, st));
     FF_CUDA(upload(&scene->d_lights, lights, st));
+    FF_REQUIRE(attr_normals.size() < 0x7fffffffu && attr_uvs.size() < 0x7fffffffu, "ff_scene_commit: too many attribute corners");
+    FF_CUDA(upload(&scene->d_geom_attr, geom_attr, st));
+    FF_CUDA(upload(&scene->d_attr_normals, attr_normals, st));
+    FF_CUDA(upload(&scene->d_attr_uvs, attr_uvs, st));
+    FF_CUDA(upload(&scene->d_attr_facemat, attr_facemat, st));
 
     BuildOut bo; bo.n_nodes = 0; bo.depth = 0; bo.sah_cost = 0;
     float blo[3] = {0, 0, 0}, bhi[3] = {0, 0, 0};
@@ -409,6 +563,8 @@ int ff_scene_commit(ff_scene* scene, int builder, double* out_build_ms) {
     DevScene& d = scene->dev;
     d.tris = scene->d_tris; d.nodes = scene->d_nodes; d.ord_geom = scene->d_ord_geom; d.ord_tri = scene->d_ord_tri;
     d.materials = scene->d_materials; d.planes = scene->d_planes; d.flat = scene->d_flat; d.lights = scene->d_lights;
+    d.geom_attr = scene->d_geom_attr; d.attr_normals = scene->d_attr_normals; d.attr_uvs = scene->d_attr_uvs;
+    d.attr_facemat = scene->d_attr_facemat; d.has_attr = has_attr ? 1u : 0u;
     d.n_lights = (uint32_t)lights.size(); d.bvh2_children = scene->d_bvh2_children;
     d.bvh2_lo = scene->d_bvh2_lo; d.bvh2_hi = scene->d_bvh2_hi; d.bvh2_leaf_slot = scene->d_leaf_slot;
     d.n_tris = (uint32_t)n_tris; d.n_nodes = bo.n_nodes; d.n_planes = (uint32_t)n_planes; d.n_geoms = (uint32_t)scene->geoms.size();
@@ -541,6 +697,10 @@ int ff_hits_unpack(ff_scene* scene, const void* d_hits, size_t n, int* out_geom,
 }
 
 int ff_trace_closest(ff_scene* scene, const float* rays6, size_t n, int mode, int* out_geom, int* out_tri, float* out_t, ff_stats* stats) {
+    return ff_trace_closest_uv(scene, rays6, n, mode, out_geom, out_tri, out_t, nullptr, nullptr, stats);
+}
+int ff_trace_closest_uv(ff_scene* scene, const float* rays6, size_t n, int mode, int* out_geom, int* out_tri, float* out_t,
+                        float* out_u, float* out_v, ff_stats* stats) {
     int rc = check_scene(scene, "ff_trace_closest");
     if (rc) return rc;
     FF_REQUIRE(valid_mode(mode), "ff_trace_closest: unknown mode");
@@ -550,11 +710,12 @@ int ff_trace_closest(ff_scene* scene, const float* rays6, size_t n, int mode, in
     ff_context* c = scene->ctx;
     cudaStream_t st = c->stream;
     float* d6 = nullptr; float4* dr = nullptr; HitRec* dh = nullptr;
-    int *dg = nullptr, *dt = nullptr; float* dk = nullptr;
+    int *dg = nullptr, *dt = nullptr; float* dk = nullptr; float* duv = nullptr;
     FF_CUDA(cudaMalloc((void**)&d6, sizeof(float) * 6 * n));
     FF_CUDA(cudaMalloc((void**)&dr, sizeof(float4) * 2 * n));
     FF_CUDA(cudaMalloc((void**)&dh, sizeof(HitRec) * n));
     FF_CUDA(cudaMalloc((void**)&dg, sizeof(int) * n)); FF_CUDA(cudaMalloc((void**)&dt, sizeof(int) * n)); FF_CUDA(cudaMalloc((void**)&dk, sizeof(float) * n));
+    if (out_u || out_v) FF_CUDA(cudaMalloc((void**)&duv, sizeof(float) * 2 * n));
     double h2d, d2h;
     {
         ScopedTimer t(c, 2, 3);
@@ -570,12 +731,17 @@ int ff_trace_closest(ff_scene* scene, const float* rays6, size_t n, int mode, in
         if (out_geom) cudaMemcpyAsync(out_geom, dg, sizeof(int) * n, cudaMemcpyDeviceToHost, st);
         if (out_tri) cudaMemcpyAsync(out_tri, dt, sizeof(int) * n, cudaMemcpyDeviceToHost, st);
         if (out_t) cudaMemcpyAsync(out_t, dk, sizeof(float) * n, cudaMemcpyDeviceToHost, st);
+        if (duv) {
+            k_hit_barycentrics(scene->dev, dr, dr + n, dh, n, duv, duv + n, st);
+            if (out_u) cudaMemcpyAsync(out_u, duv, sizeof(float) * n, cudaMemcpyDeviceToHost, st);
+            if (out_v) cudaMemcpyAsync(out_v, duv + n, sizeof(float) * n, cudaMemcpyDeviceToHost, st);
+        }
         d2h = t.stop();
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) { set_error(cudaGetErrorString(e)); rc = FF_ERR_CUDA; }
         if (stats) { *stats = inner; stats->h2d_ms = h2d; stats->d2h_ms = d2h; stats->gpu_ms += h2d + d2h; stats->kernel_launches += 2; }
     }
-    cudaFree(d6); cudaFree(dr); cudaFree(dh); cudaFree(dg); cudaFree(dt); cudaFree(dk);
+    cudaFree(d6); cudaFree(dr); cudaFree(dh); cudaFree(dg); cudaFree(dt); cudaFree(dk); cudaFree(duv);
     return rc;
 }
 
@@ -865,6 +1031,17 @@ int ff_render(ff_scene* scene, const ff_camera* cam, const ff_render_params* par
         for (size_t i = 0; i < npix; ++i) { for (int k = 0; k < 3; ++k) f[4 * i + k] = h[3 * i + k] / 255.0f; f[4 * i + 3] = 1.0f; }
         if (out_rgba_host) memcpy(out_rgba_host, f.data(), sizeof(float) * 4 * npix);
         if (out_rgba_device) FF_CUDA(cudaMemcpy(out_rgba_device, f.data(), sizeof(float) * 4 * npix, cudaMemcpyHostToDevice));
+        return FF_OK;
+    }
+    const int integ = params->integrator & 0xff;
+    if (integ >= FF_INTEGRATOR_AOV_NORMAL && integ <= FF_INTEGRATOR_AOV_ALBEDO) {
+        float4* d_out = out_rgba_device ? (float4*)out_rgba_device : scene->d_out;
+        ScopedTimer t(c, 0, 1);
+        k_aov(scene->dev, make_cam(cam), integ, d_out, c->stream);
+        if (out_rgba_host) FF_CUDA(cudaMemcpyAsync(out_rgba_host, d_out, sizeof(float4) * npix, cudaMemcpyDeviceToHost, c->stream));
+        const double ms = t.stop();
+        FF_CUDA(cudaGetLastError());
+        if (stats) { stats->gpu_ms = ms; stats->trace_ms = ms; stats->rays = npix; stats->paths = npix; stats->kernel_launches = 1; }
         return FF_OK;
     }
     if ((rc = check_params(params, "ff_render"))) return rc;

@@ -29,7 +29,7 @@ namespace ff {
 //             tie-break order of intersectRays (kernel.cu:133,145).
 //   nodes     5 float4 (80 B) per 8-wide compressed node, see ff_bvh.cu for the field layout.
 //   ord_geom / ord_tri   ord -> (geometryIndex, triangleIndex) in the reference's numbering.
-//   materials 4 float4 per geometry: {type, albedo.rgb}, {emissive.rgb, intensity}, {specular.rgb, ior}, {transmittance.rgb, 0}
+//   materials 4 float4 per row; rows [0, n_geoms) are the geometries' own, per-face materials follow: {type, albedo.rgb}, {emissive.rgb, intensity}, {specular.rgb, ior}, {transmittance.rgb, 0}
 // Analytic primitive of the reference's Geometry: GeometryType::PLANE (unit square, intersectPlane kernel.cu:8-32) or
 // GeometryType::SPHERE (utilities.h:143,227; the reference leaves its branch empty, kernel.cu:166-169).
 struct DevPlane {
@@ -48,6 +48,14 @@ struct DevScene {
     const DevPlane* planes;
     const float4* flat;          // the same 48-B records in flat (geometry, triangle) order; light sampling reads these
     const uint32_t* lights;      // flat indices of the triangles of emitter meshes, in flat order (next-event estimation)
+    // shading attributes, all optional and cold: read once per shading event, never by traversal.
+    //   geom_attr[g] = {first flat index of g, base into attr_normals (float4 units) or -1, base into attr_uvs (float2
+    //   units) or -1, base into attr_facemat or -1}; corner k of triangle t of g lives at base + 3 t + k, t = flat - first.
+    const int4* geom_attr;
+    const float4* attr_normals;  // world-space corner normals inverse(transpose(M)) * n, not normalised (Triangle::m_n0..2, utilities.h:168-170)
+    const float2* attr_uvs;      // corner uvs (Triangle::m_uv0..2, utilities.h:163-166)
+    const uint32_t* attr_facemat;  // per triangle: row of `materials` (per-face OBJ material, utilities.h:837)
+    uint32_t has_attr;           // 0: no geometry of the scene carries any of the above (shading skips the lookup)
     // binary LBVH kept for the BVH2 comparison kernel
     const int2* bvh2_children;   // internal node i: {left, right}; id >= n_internal is leaf (id - n_internal = slot2)
     const float4* bvh2_lo;       // per node id (internal then leaves): box min, w unused
@@ -170,8 +178,28 @@ void k_megakernel_pass(const DevScene& sc, const CamDev& cam, const RenderDev& r
 void k_accumulate_pass(const float4* d_radiance, uint32_t npix, uint32_t samples, float4* d_accum, cudaStream_t st);
 void k_resolve(const float4* const* accums, int n_accums, uint32_t npix, float inv_spp, float4* d_out, cudaStream_t st);
 void k_as_coded(const DevScene& sc, const CamDev& cam, unsigned char* d_rgb, cudaStream_t st);
+// Primary-ray feature buffers (FF_INTEGRATOR_AOV_*): shading normal, uv, barycentrics, albedo of the first hit.
+void k_aov(const DevScene& sc, const CamDev& cam, int kind, float4* d_rgba, cudaStream_t st);
+// Barycentrics of closest hits (u, v as in kernel.cu:80-81); misses and analytic primitives give 0.
+void k_hit_barycentrics(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const HitRec* d_hits, size_t n,
+                        float* d_u, float* d_v, cudaStream_t st);
 void k_rgba_to_u8(const float4* d_rgba, uint32_t npix, unsigned char* d_rgb, cudaStream_t st);
 void k_flush(float4* d_buf, size_t n_float4, cudaStream_t st);
+
+// OBJ ingest (ff_obj.cpp): per-corner attributes in file order, 9 / 9 / 6 floats per triangle; face_material indexes
+// material_names (-1: no usemtl in force).
+struct ObjMesh {
+    std::vector<float> xyz9, n9, uv6;
+    std::vector<int> face_material;
+    std::vector<std::string> material_names;
+    std::string mtllib;
+    bool has_normals = false, has_uvs = false;
+    size_t bytes = 0;
+};
+bool load_obj_mesh(const char* path, ObjMesh& out, int threads);
+bool load_obj_positions(const char* path, std::vector<float>& xyz9);
+bool load_mtl(const char* path, std::vector<std::string>& names, std::vector<ff_material>& mats);
+int obj_default_threads();
 
 struct Tuning { int postpone_div, refill_lanes, blocks_per_sm; };
 Tuning& tuning();

@@ -1,11 +1,5 @@
-// ff_io.cpp -- host I/O: OBJ mesh reader and headless image writers (PPM / PNG / EXR / PFM).
+// ff_io.cpp -- headless image writers (PPM / PNG / EXR / PFM).  The OBJ / MTL reader lives in ff_obj.cpp.
 //
-// Reader: replaces LoadMesh (reference utilities.h:781-840), which goes through tinyobjloader and keeps, per face
-// corner, position / normal / uv.  The tracer only ever reads positions (intersectTriangle, kernel.cu:35-108), so
-// this reader gathers positions only; `vn` / `vt` indices are parsed and skipped, which also removes the
-// out-of-range read LoadMesh has on files without normals (utilities.h:823-824, sceneResources/triangle.obj).
-// Faces with more than three corners are fan-triangulated (the shipped meshes are all triangles already);
-// negative (relative) indices are supported (triangle.obj uses them).
 // Writers: replace saveToPPM (utilities.h:842-856).  Row 0 is the top of the image (kernel orientation).
 #include <cmath>
 #include <cstdio>
@@ -19,72 +13,6 @@
 namespace ff {
 
 void set_error(const std::string& msg);
-
-static bool read_file(const char* path, std::string& out) {
-    FILE* f = fopen(path, "rb");
-    if (!f) return false;
-    fseek(f, 0, SEEK_END);
-    long n = ftell(f);
-    fseek(f, 0, SEEK_SET);
-    out.resize(n > 0 ? (size_t)n : 0);
-    size_t got = n > 0 ? fread(&out[0], 1, (size_t)n, f) : 0;
-    fclose(f);
-    return got == out.size();
-}
-
-// Parses "v", "f"; everything else is ignored.  Returns false on I/O or index errors.
-bool load_obj_positions(const char* path, std::vector<float>& xyz9) {
-    std::string text;
-    if (!read_file(path, text)) { set_error(std::string("cannot read OBJ file: ") + path); return false; }
-    std::vector<float> pos;
-    std::vector<long> corner;
-    const char* p = text.c_str();
-    const char* end = p + text.size();
-    size_t line_no = 0;
-    while (p < end) {
-        ++line_no;
-        const char* eol = (const char*)memchr(p, '\n', (size_t)(end - p));
-        if (!eol) eol = end;
-        const char* q = p;
-        while (q < eol && (*q == ' ' || *q == '\t')) ++q;
-        if (q + 1 < eol && q[0] == 'v' && (q[1] == ' ' || q[1] == '\t')) {
-            char* e;
-            q += 2;
-            for (int k = 0; k < 3; ++k) {
-                float v = strtof(q, &e);
-                if (e == q) { set_error(std::string(path) + ": malformed vertex at line " + std::to_string(line_no)); return false; }
-                pos.push_back(v);
-                q = e;
-            }
-        } else if (q + 1 < eol && q[0] == 'f' && (q[1] == ' ' || q[1] == '\t')) {
-            q += 2;
-            corner.clear();
-            const long nv = (long)(pos.size() / 3);
-            while (q < eol) {
-                while (q < eol && (*q == ' ' || *q == '\t' || *q == '\r')) ++q;
-                if (q >= eol) break;
-                char* e;
-                long idx = strtol(q, &e, 10);
-                if (e == q) break;
-                q = e;
-                while (q < eol && *q != ' ' && *q != '\t' && *q != '\r') ++q;  // skip /vt/vn
-                long v = idx > 0 ? idx - 1 : nv + idx;
-                if (idx == 0 || v < 0 || v >= nv) {
-                    set_error(std::string(path) + ": face index out of range at line " + std::to_string(line_no));
-                    return false;
-                }
-                corner.push_back(v);
-            }
-            for (size_t k = 2; k < corner.size(); ++k) {
-                const long tri[3] = {corner[0], corner[k - 1], corner[k]};
-                for (int c = 0; c < 3; ++c)
-                    for (int a = 0; a < 3; ++a) xyz9.push_back(pos[3 * (size_t)tri[c] + a]);
-            }
-        }
-        p = eol + 1;
-    }
-    return true;
-}
 
 // ---------------------------------------------------------------------------------------------- writers
 static unsigned char to_srgb8(float v) {

@@ -78,6 +78,20 @@ FF_HD bool intersect_triangle(V3 v0, V3 v1, V3 v2, V3 o, V3 d, float& t_out) {
     t_out = t;
     return !back && !flat && !out_u && !out_v && t > EPSILON;  // kernel.cu:97
 }
+// The barycentrics intersectTriangle computes and then drops (u *= invDet; v *= invDet, kernel.cu:80-81), same operations
+// in the same order as above; (u, v) weight v1 and v2, 1 - u - v weights v0.
+FF_HD void triangle_barycentrics(V3 v0, V3 v1, V3 v2, V3 o, V3 d, float& u_out, float& v_out) {
+    V3 edge1 = sub(v1, v0), edge2 = sub(v2, v0);
+    V3 pvec = cross(d, edge2);
+    float det = dot(edge1, pvec);
+    V3 tvec = sub(o, v0);
+    float u = dot(tvec, pvec);
+    V3 qvec = cross(tvec, edge1);
+    float v = dot(d, qvec);
+    float invDet = fdiv(1.0f, det);
+    u_out = fmul(u, invDet);
+    v_out = fmul(v, invDet);
+}
 // Closest-hit key of setIntersection (kernel.cu:113-115) for a baked (M = I) triangle.
 FF_HD float hit_key(V3 o, V3 d, float t, V3& point) {
     point = add(o, mul(d, t));

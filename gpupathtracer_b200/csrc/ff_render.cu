@@ -58,6 +58,49 @@ __device__ __forceinline__ void hit_surface(const DevScene& sc, const HitRec& h,
     }
 }
 
+// Shading attributes of a triangle hit: the per-corner normals and uvs LoadMesh keeps and the tracer never
+// reads (Triangle::m_n0..2, m_uv0..2, utilities.h:163-170), interpolated with the barycentrics intersectTriangle computes
+// and drops (kernel.cu:80-81), and the per-face material id LoadMesh reads and drops (utilities.h:837).  CPU twin:
+// surface_attributes in oracle/firefly_oracle.cpp, same operations in the same order.
+struct SurfAttr {
+    int mat;        // row of sc.materials
+    bool smooth;    // ns holds a usable interpolated normal
+    V3 ns;          // normalised interpolated world normal (not yet face-forwarded)
+    float u, v;     // barycentrics (weights of v1, v2)
+    float tu, tv;   // interpolated uv
+};
+__device__ __forceinline__ int material_row(const DevScene& sc, int geom, int flat) {
+    if (!sc.has_attr) return geom;
+    const int4 ga = __ldg(sc.geom_attr + geom);
+    return ga.w >= 0 ? (int)__ldg(sc.attr_facemat + ga.w + (flat - ga.x)) : geom;
+}
+__device__ __forceinline__ void surface_attributes(const DevScene& sc, const HitRec& h, V3 o, V3 d_raw, int geom, bool want_bary, SurfAttr& a) {
+    a.mat = geom; a.smooth = false; a.ns = v3(0.f, 0.f, 0.f); a.u = a.v = a.tu = a.tv = 0.f;
+    if (h.slot < 0 || (h.slot & 0x40000000)) return;
+    int4 ga = make_int4(0, -1, -1, -1);
+    if (sc.has_attr) ga = __ldg(sc.geom_attr + geom);
+    if (!want_bary && ga.y < 0 && ga.z < 0 && ga.w < 0) return;
+    const float4 a4 = __ldg(sc.tris + 3 * (size_t)h.slot), b4 = __ldg(sc.tris + 3 * (size_t)h.slot + 1),
+                 c4 = __ldg(sc.tris + 3 * (size_t)h.slot + 2);
+    const int tri = __float_as_int(c4.w) - ga.x;
+    if (ga.w >= 0) a.mat = (int)__ldg(sc.attr_facemat + ga.w + tri);
+    if (!want_bary && ga.y < 0 && ga.z < 0) return;
+    triangle_barycentrics(ld3(a4), ld3(b4), ld3(c4), o, normalize(d_raw), a.u, a.v);
+    const float w0 = fsub(fsub(1.0f, a.u), a.v);
+    if (ga.y >= 0) {
+        const float4 n0 = __ldg(sc.attr_normals + ga.y + 3 * (size_t)tri), n1 = __ldg(sc.attr_normals + ga.y + 3 * (size_t)tri + 1),
+                     n2 = __ldg(sc.attr_normals + ga.y + 3 * (size_t)tri + 2);
+        const V3 ns = add(add(mul(ld3(n0), w0), mul(ld3(n1), a.u)), mul(ld3(n2), a.v));
+        if (dot(ns, ns) > 0.0f) { a.smooth = true; a.ns = normalize(ns); }
+    }
+    if (ga.z >= 0) {
+        const float2 t0 = __ldg(sc.attr_uvs + ga.z + 3 * (size_t)tri), t1 = __ldg(sc.attr_uvs + ga.z + 3 * (size_t)tri + 1),
+                     t2 = __ldg(sc.attr_uvs + ga.z + 3 * (size_t)tri + 2);
+        a.tu = fadd(fadd(fmul(t0.x, w0), fmul(t1.x, a.u)), fmul(t2.x, a.v));
+        a.tv = fadd(fadd(fmul(t0.y, w0), fmul(t1.y, a.u)), fmul(t2.y, a.v));
+    }
+}
+
 // Next-event estimation, one light sample per diffuse shading event (CPU twin: sample_light in
 // oracle/firefly_oracle.cpp, same operations in the same order).  Lights are the triangles of emitter meshes; one is
 // picked uniformly, a point uniformly on it; it radiates from its front side only (the side closest-hit can see).
@@ -68,7 +111,7 @@ struct ShadowReq {
     V3 contrib;    // radiance added to the path when unoccluded
 };
 __device__ __forceinline__ void sample_light(const DevScene& sc, const RenderDev& rp, uint32_t pixel, uint32_t sample, int bounce,
-                                             V3 so, V3 n, V3 beta, ShadowReq& sr) {
+                                             V3 so, V3 n, V3 ng, bool smooth, V3 beta, ShadowReq& sr) {
     sr.valid = false;
     const uint32_t nl = sc.n_lights;
     if (nl == 0) return;
@@ -90,9 +133,10 @@ __device__ __forceinline__ void sample_light(const DevScene& sc, const RenderDev
     const float cosx = fdiv(dot(n, sd), dist);
     const float cosl = fdiv(fdiv(-dot(N, sd), dist), len);
     if (!(cosx > 0.0f && cosl > 0.0f && dist2 > 0.0f)) return;
+    if (smooth && !(dot(ng, sd) > 0.0f)) return;  // below the real surface: the shadow ray would leave through culled back faces
     const float w = fmul(fmul(fdiv(fmul(cosx, cosl), dist2), fmul(0.5f, len)), fmul((float)nl, 0.318309886183790672f));
-    const int geom = __float_as_int(b4.w);
-    const float4 m1 = __ldg(sc.materials + 4 * geom + 1);
+    const int mat = material_row(sc, __float_as_int(b4.w), (int)fi);
+    const float4 m1 = __ldg(sc.materials + 4 * mat + 1);
     sr.contrib = mul(mul3(beta, mul(v3(m1.x, m1.y, m1.z), m1.w)), w);
     sr.o = so; sr.d = sd;
     sr.tmax = fmul(dist, 0.999f);
@@ -113,7 +157,10 @@ __device__ __forceinline__ bool shade_event(const DevScene& sc, const RenderDev&
     V3 P, nrm;
     int geom;
     hit_surface(sc, h, o, d, P, nrm, geom);
-    const float4 m0 = __ldg(sc.materials + 4 * geom), m1 = __ldg(sc.materials + 4 * geom + 1);
+    SurfAttr sa;
+    surface_attributes(sc, h, o, d, geom, false, sa);
+    const int mat = sa.mat;
+    const float4 m0 = __ldg(sc.materials + 4 * mat), m1 = __ldg(sc.materials + 4 * mat + 1);
     const int type = __float_as_int(m0.x);
     if (type == FF_MAT_EMITTER) {
         // with NEE the direct light of mesh emitters arrives through the shadow rays; a hit found by sampling the BSDF
@@ -125,14 +172,19 @@ __device__ __forceinline__ bool shade_event(const DevScene& sc, const RenderDev&
     if (bounce == rp.max_bounces) return false;
     V3 n = normalize(nrm);
     if (dot(n, d) > 0.0f) n = neg(n);
+    // shading normal: the interpolated corner normal when the geometry carries normals, turned to the side of n; every
+    // ray offset and every "which side" decision stays with the geometric normal n
+    V3 ns = n;
+    if (sa.smooth) { ns = sa.ns; if (dot(ns, n) < 0.0f) ns = neg(ns); }
     const U4 r = philox4x32_10(U4{pixel, sample, (uint32_t)bounce, 0u}, rp.seed_lo, rp.seed_hi);
     if (type == FF_MAT_MIRROR || type == FF_MAT_GLASS) {
         // BXDFTyp MIRROR / GLASS (utilities.h:72-73, fields utilities.h:84-88; no code in the reference).  CPU twin:
         // trace_path in oracle/firefly_oracle.cpp, same operations in the same order.  Only front faces are ever hit,
         // so glass is one refracting interface air -> ior; Schlick's Fresnel picks reflection with probability F.
-        const float4 m2 = __ldg(sc.materials + 4 * geom + 2);
+        const float4 m2 = __ldg(sc.materials + 4 * mat + 2);
         const V3 dn = normalize(d);
-        const float cosi = -dot(dn, n);
+        float cosi = -dot(dn, ns);
+        if (sa.smooth && !(cosi > 0.0f)) { ns = n; cosi = -dot(dn, n); }  // seen from behind the shading hemisphere
         bool reflect = true;
         if (type == FF_MAT_GLASS) {
             const float ior = m2.w;
@@ -144,14 +196,15 @@ __device__ __forceinline__ bool shade_event(const DevScene& sc, const RenderDev&
             const float sin2t = fmul(fmul(eta, eta), fsub(1.0f, fmul(cosi, cosi)));
             if (!(sin2t > 1.0f) && !(u01(r.z) < F)) {
                 reflect = false;
-                const float4 m3 = __ldg(sc.materials + 4 * geom + 3);
-                d = add(mul(dn, eta), mul(n, fsub(fmul(eta, cosi), fsqrt(fsub(1.0f, sin2t)))));
+                const float4 m3 = __ldg(sc.materials + 4 * mat + 3);
+                d = add(mul(dn, eta), mul(ns, fsub(fmul(eta, cosi), fsqrt(fsub(1.0f, sin2t)))));
                 beta = mul3(beta, v3(m3.x, m3.y, m3.z));
                 o = sub(P, mul(n, rp.ray_eps));
             }
         }
         if (reflect) {
-            d = add(dn, mul(n, fmul(2.0f, cosi)));
+            d = add(dn, mul(ns, fmul(2.0f, cosi)));
+            if (sa.smooth) { const float c = dot(d, n); if (!(c > 0.0f)) d = sub(d, mul(n, fmul(2.0f, c))); }
             beta = mul3(beta, v3(m2.x, m2.y, m2.z));
             o = add(P, mul(n, rp.ray_eps));
         }
@@ -162,10 +215,13 @@ __device__ __forceinline__ bool shade_event(const DevScene& sc, const RenderDev&
     beta = mul3(beta, v3(m0.y, m0.z, m0.w));
     const V3 w = cosine_sample_hemisphere(u01(r.x), u01(r.y));
     V3 t, bt;
-    onb(n, t, bt);
-    d = add(add(mul(t, w.x), mul(bt, w.y)), mul(n, w.z));
+    onb(ns, t, bt);
+    d = add(add(mul(t, w.x), mul(bt, w.y)), mul(ns, w.z));
+    // a direction sampled about the shading normal can point below the real surface, where it would leave a closed
+    // mesh through culled back faces: mirror it back above the geometric plane
+    if (sa.smooth) { const float c = dot(d, n); if (!(c > 0.0f)) d = sub(d, mul(n, fmul(2.0f, c))); }
     o = add(P, mul(n, rp.ray_eps));
-    if (NEE && rp.nee) sample_light(sc, rp, pixel, sample, bounce, o, n, beta, sr);
+    if (NEE && rp.nee) sample_light(sc, rp, pixel, sample, bounce, o, ns, n, sa.smooth, beta, sr);
     return true;
 }
 
@@ -441,6 +497,71 @@ void k_resolve(const float4* const* accums, int n_accums, uint32_t npix, float i
     PeerPtrs pp;
     for (int i = 0; i < 8; ++i) pp.p[i] = i < n_accums ? accums[i] : nullptr;
     resolve_kernel<<<grid_for(npix, 256, 148 * 16), 256, 0, st>>>(pp, n_accums, npix, inv_spp, d_out);
+}
+
+// ------------------------------------------------------------------ primary-ray feature buffers
+// One ray per pixel through the integer pixel corner (kernel.cu:200-201), first hit only.  kind: 3 shading normal
+// (interpolated when the geometry has normals, else geometric; face-forwarded, world space), 4 uv, 5 barycentrics
+// (1-u-v, u, v), 6 albedo of the hit's material row.  Alpha = 1 on a hit, 0 on a miss (rgb 0).
+__global__ void __launch_bounds__(FF_TRACE_BLOCK) aov_kernel(DevScene sc, CamDev cam, int kind, float4* __restrict__ out) {
+    __shared__ uint2 sm_stack[(FF_SM_STACK + FF_TRI_QUEUE) * FF_TRACE_BLOCK];
+    const uint32_t npix = (uint32_t)cam.w * cam.h;
+    unsigned cn = 0, ct = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += gridDim.x * blockDim.x) {
+        V3 o, d;
+        camera_ray_dev(cam, (float)(i % cam.w), (float)(i / cam.w), o, d);
+        const V3 dn = normalize(d);
+        Best best;
+        best_init(best, INFINITY);
+        test_planes<false>(sc, o, d, best);
+        trace_bvh8<false, false>(sc, o, dn, best, sm_stack + threadIdx.x, FF_TRACE_BLOCK, cn, ct);
+        float4 px = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (best.slot >= 0) {
+            HitRec h;
+            h.key = best.key; h.t = best.t; h.slot = best.slot; h.ord = best.ord;
+            V3 P, nrm;
+            int geom;
+            hit_surface(sc, h, o, d, P, nrm, geom);
+            SurfAttr sa;
+            surface_attributes(sc, h, o, d, geom, true, sa);
+            if (kind == FF_INTEGRATOR_AOV_NORMAL) {
+                V3 n = normalize(nrm);
+                if (dot(n, d) > 0.0f) n = neg(n);
+                V3 ns = n;
+                if (sa.smooth) { ns = sa.ns; if (dot(ns, n) < 0.0f) ns = neg(ns); }
+                px = make_float4(ns.x, ns.y, ns.z, 1.f);
+            } else if (kind == FF_INTEGRATOR_AOV_UV) {
+                px = make_float4(sa.tu, sa.tv, 0.f, 1.f);
+            } else if (kind == FF_INTEGRATOR_AOV_BARY) {
+                px = (h.slot & 0x40000000) ? make_float4(0.f, 0.f, 0.f, 1.f) : make_float4(fsub(fsub(1.0f, sa.u), sa.v), sa.u, sa.v, 1.f);
+            } else {
+                const float4 m0 = __ldg(sc.materials + 4 * sa.mat);
+                px = make_float4(m0.y, m0.z, m0.w, 1.f);
+            }
+        }
+        out[i] = px;
+    }
+}
+void k_aov(const DevScene& sc, const CamDev& cam, int kind, float4* d_rgba, cudaStream_t st) {
+    const size_t n = (size_t)cam.w * cam.h;
+    aov_kernel<<<grid_for(n, FF_TRACE_BLOCK, 148 * 16), FF_TRACE_BLOCK, 0, st>>>(sc, cam, kind, d_rgba);
+}
+__global__ void hit_barycentrics_kernel(DevScene sc, const float4* __restrict__ ray_o, const float4* __restrict__ ray_d,
+                                        const HitRec* __restrict__ hits, size_t n, float* __restrict__ out_u, float* __restrict__ out_v) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const HitRec h = hits[i];
+        float u = 0.f, v = 0.f;
+        if (h.slot >= 0 && !(h.slot & 0x40000000)) {
+            const float4 a4 = __ldg(sc.tris + 3 * (size_t)h.slot), b4 = __ldg(sc.tris + 3 * (size_t)h.slot + 1),
+                         c4 = __ldg(sc.tris + 3 * (size_t)h.slot + 2);
+            triangle_barycentrics(ld3(a4), ld3(b4), ld3(c4), ld3(ray_o[i]), normalize(ld3(ray_d[i])), u, v);
+        }
+        out_u[i] = u; out_v[i] = v;
+    }
+}
+void k_hit_barycentrics(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const HitRec* d_hits, size_t n,
+                        float* d_u, float* d_v, cudaStream_t st) {
+    hit_barycentrics_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(sc, d_ray_o, d_ray_d, d_hits, n, d_u, d_v);
 }
 
 // ------------------------------------------------------------------ as-coded frame (kernel.cu:186-216)

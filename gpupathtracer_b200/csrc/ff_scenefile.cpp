@@ -5,7 +5,8 @@
 //   camera    pos X Y Z [up X Y Z] [yaw D] [pitch D] [fov D] [size W H] [near N] [far F]
 //   material  NAME emitter|diffuse|mirror|glass [albedo R G B] [emissive R G B] [intensity I] [specular R G B] [ior N]
 //             [transmittance R G B]
-//   mesh      PATH.obj [pos X Y Z] [rot X Y Z] [scale X Y Z] [material NAME] [flip]
+//   mesh      PATH.obj [pos X Y Z] [rot X Y Z] [scale X Y Z] [material NAME] [flip] [normals] [uvs] [materials]
+//             normals / uvs / materials keep the file's `vn` / `vt` / `usemtl` + `mtllib` (ff_scene_add_obj_ex flags)
 //   plane     [pos ..] [rot ..] [scale ..] [material NAME]
 //   sphere    RADIUS [pos ..] [rot ..] [scale ..] [material NAME]
 //   triangles [pos ..] [rot ..] [scale ..] [material NAME] [flip]     then lines "tri x0 y0 z0 x1 y1 z1 x2 y2 z2", then "end"
@@ -38,6 +39,7 @@ struct ParsedGeom {
     float radius = 1.f, soup_size = 0.f;
     size_t soup_n = 0;
     bool flip = false;
+    int obj_flags = 0;  // FF_OBJ_NORMALS | FF_OBJ_UVS | FF_OBJ_MATERIALS, mesh files only
     ff_material mat;
     std::vector<float> xyz9;
 };
@@ -98,6 +100,9 @@ bool parse_placement(Cursor& c, ParsedGeom& g, const std::map<std::string, ff_ma
             if (it == mats.end()) return fail(c, "unknown material '" + name + "'");
             g.mat = it->second;
         } else if (k == "flip" && allow_flip) g.flip = true;
+        else if (k == "normals" && g.kind == 3) g.obj_flags |= FF_OBJ_NORMALS;
+        else if (k == "uvs" && g.kind == 3) g.obj_flags |= FF_OBJ_UVS;
+        else if (k == "materials" && g.kind == 3) g.obj_flags |= FF_OBJ_MATERIALS;
         else if (k == "size" && g.kind == 4) { if (!c.floats(&g.soup_size, 1)) return fail(c, "size needs a number"); }
         else return fail(c, "unexpected '" + k + "'");
     }
@@ -284,7 +289,7 @@ int ff_scene_load_file(ff_context* ctx, const char* path, const char* asset_dir,
                 break;
             case 3: {
                 const std::string full = (!g.path.empty() && g.path[0] == '/') ? g.path : base + "/" + g.path;
-                rc = ff_scene_add_obj(sc, full.c_str(), g.pos, g.rot, g.scale, &g.mat, g.flip ? 1 : 0, nullptr);
+                rc = ff_scene_add_obj_ex(sc, full.c_str(), g.pos, g.rot, g.scale, &g.mat, g.obj_flags | (g.flip ? FF_OBJ_FLIP_WINDING : 0), nullptr);
                 break;
             }
             default: {

@@ -15,6 +15,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 MESH_FIXTURE = os.path.join(_HERE, "..", "tests", "golden", "meshes.npz")
 REFERENCE_OBJ_DIR = "/root/reference/sceneResources"
+ATTR_FIXTURE = os.path.join(_HERE, "..", "tests", "golden", "mesh_attrs.npz")   # per-corner normals / uvs of the same meshes
 MESH_NAMES = ["cube", "triangle", "rocketman", "sphere", "sphereBlender", "wahoo"]
 
 DIFFUSE_GREY = dict(type=1, albedo=(0.8, 0.8, 0.8))
@@ -32,13 +33,33 @@ def load_meshes():
     raise FileNotFoundError("no mesh fixture (%s) and no reference tree" % MESH_FIXTURE)
 
 
+def load_mesh_attrs():
+    """{name + "_n": [n,9] corner normals, name + "_uv": [n,6] corner uvs} as the reference's LoadMesh gathers them
+    (utilities.h:822-824; zeros where the file has none).  Fixture made by tools/make_golden_attrs.py."""
+    if os.path.exists(ATTR_FIXTURE):
+        z = np.load(ATTR_FIXTURE)
+        return {k: z[k] for k in z.files}
+    if os.path.isdir(REFERENCE_OBJ_DIR):
+        import gpupathtracer_b200 as ff
+        out = {}
+        for k in MESH_NAMES:
+            m = ff.load_obj_ex(os.path.join(REFERENCE_OBJ_DIR, k + ".obj"))
+            out[k + "_n"], out[k + "_uv"] = m["normals9"], m["uvs6"]
+        return out
+    raise FileNotFoundError("no attribute fixture (%s) and no reference tree" % ATTR_FIXTURE)
+
+
 def camera(pos, yaw=-90.0, pitch=0.0, fov=70.0, width=256, height=256, near=0.1, far=1000.0):
     return dict(pos=tuple(pos), world_up=(0, 1, 0), yaw=yaw, pitch=pitch, fov=fov, width=width, height=height, near=near, far=far)
 
 
-def geom(mesh, pos=(0, 0, 0), rot=(0, 0, 0), scale=(1, 1, 1), material=None, flip=False, plane=False, sphere=None):
-    """mesh: name | [n,9] array | None; plane=True: GeometryType::PLANE; sphere=r: GeometryType::SPHERE of radius r."""
-    return dict(mesh=mesh, pos=pos, rot=rot, scale=scale, material=material or DIFFUSE_GREY, flip=flip, plane=plane, sphere=sphere)
+def geom(mesh, pos=(0, 0, 0), rot=(0, 0, 0), scale=(1, 1, 1), material=None, flip=False, plane=False, sphere=None,
+         normals=None, uvs=None, face_materials=None):
+    """mesh: name | [n,9] array | None; plane=True: GeometryType::PLANE; sphere=r: GeometryType::SPHERE of radius r.
+    Shading attributes: normals / uvs = True (the named mesh's own, from the attribute fixture) or an
+    [n,9] / [n,6] array; face_materials = (int[n] indices, [material dicts]), -1 = `material`."""
+    return dict(mesh=mesh, pos=pos, rot=rot, scale=scale, material=material or DIFFUSE_GREY, flip=flip, plane=plane, sphere=sphere,
+                normals=normals, uvs=uvs, face_materials=face_materials)
 
 
 def flip_winding(xyz9):
@@ -107,6 +128,32 @@ def showcase(meshes, width=512, height=512, spp=16, max_bounces=6):
                 camera=camera((0, 0, 2.4), fov=70.0, width=width, height=height), spp=spp, max_bounces=max_bounces)
 
 
+def shaded(meshes, width=256, height=256, spp=8, max_bounces=5):
+    """The shading inputs LoadMesh carries and the reference's tracer ignores, all in one frame:
+    interpolated corner normals on diffuse, mirror and glass meshes (one under a non-uniform scale, so the normal matrix
+    matters), uvs, and per-face materials on wahoo including emissive faces (they join the light list of NEE)."""
+    top, rest = _cube_faces(meshes["cube"])
+    nw = len(meshes["wahoo"])
+    fm = ((np.arange(nw) // 97) % 4 - 1).astype(np.int32)
+    face_mats = [dict(type=1, albedo=(0.2, 0.3, 0.9)), dict(type=2, specular=(0.9, 0.8, 0.6)),
+                 dict(type=0, emissive=(1.0, 0.5, 0.1), intensity=3.0)]
+    return dict(name="shaded",
+                geoms=[geom(rest, scale=(5, 5, 5), flip=True),
+                       geom(top, scale=(5, 5, 5), flip=True, material=EMITTER_WHITE2),
+                       geom("wahoo", pos=(-0.8, -2.4, 0.0), scale=(0.2, 0.2, 0.2), normals=True, uvs=True,
+                            material=dict(type=1, albedo=(0.8, 0.7, 0.6)), face_materials=(fm, face_mats)),
+                       # sphere.obj carries per-corner (smooth) normals; sphereBlender.obj is faceted (one `vn` per face)
+                       geom("sphere", pos=(1.2, -1.6, -0.3), scale=(0.35, 0.35, 0.35), normals=True,
+                            material=dict(type=2, specular=(0.95, 0.95, 0.95))),
+                       geom("sphere", pos=(1.0, 0.8, -1.0), scale=(0.24, 0.24, 0.24), normals=True,
+                            material=dict(type=3, ior=1.45, transmittance=(1.0, 0.9, 0.9))),
+                       geom("sphere", pos=(-1.3, 1.0, -1.0), rot=(20, 30, 0), scale=(0.24, 0.36, 0.2), normals=True,
+                            material=dict(type=1, albedo=(0.2, 0.8, 0.3))),
+                       geom("sphereBlender", pos=(0.0, 1.6, -1.5), scale=(0.4, 0.4, 0.4), normals=True, uvs=True,
+                            material=dict(type=1, albedo=(0.7, 0.7, 0.2)))],
+                camera=camera((0, 0, 2.4), fov=70.0, width=width, height=height), spp=spp, max_bounces=max_bounces)
+
+
 def soup_scale(n):
     return float(np.float32(float(n) ** (-1.0 / 3.0)))
 
@@ -135,7 +182,34 @@ def resolve_mesh(g, meshes):
     return flip_winding(m) if g["flip"] else m
 
 
-def instantiate(desc, ctx, meshes=None, builder=0, commit=True):
+def resolve_attrs(g, attrs=None):
+    """(normals9 | None, uvs6 | None, (face_mat, materials) | None) of a mesh geometry, winding flip applied."""
+    def pick(v, suffix, width):
+        if v is None or v is False:
+            return None
+        if v is True:
+            a = (attrs if attrs is not None else load_mesh_attrs())[g["mesh"] + suffix]
+        else:
+            a = v
+        a = np.ascontiguousarray(a, np.float32).reshape(-1, 3 * width).copy()
+        if g["flip"]:
+            a[:, width:2 * width], a[:, 2 * width:] = a[:, 2 * width:].copy(), a[:, width:2 * width].copy()
+        return a
+    fm = g.get("face_materials")
+    return pick(g.get("normals"), "_n", 3), pick(g.get("uvs"), "_uv", 2), (None if fm is None else (np.asarray(fm[0], np.int32), list(fm[1])))
+
+
+def _apply_attrs(scene, gi, g, attrs):
+    n9, uv6, fm = resolve_attrs(g, attrs)
+    if n9 is not None:
+        scene.set_normals(gi, n9)
+    if uv6 is not None:
+        scene.set_uvs(gi, uv6)
+    if fm is not None:
+        scene.set_face_materials(gi, fm[0], fm[1])
+
+
+def instantiate(desc, ctx, meshes=None, builder=0, commit=True, attrs=None):
     """Builds the description on the GPU library; returns (Scene, Camera)."""
     import gpupathtracer_b200 as ff
     sc = ctx.scene()
@@ -145,13 +219,14 @@ def instantiate(desc, ctx, meshes=None, builder=0, commit=True):
         elif g["plane"]:
             sc.add_plane(g["pos"], g["rot"], g["scale"], g["material"])
         else:
-            sc.add_triangles(resolve_mesh(g, meshes), g["pos"], g["rot"], g["scale"], g["material"])
+            gi = sc.add_triangles(resolve_mesh(g, meshes), g["pos"], g["rot"], g["scale"], g["material"])
+            _apply_attrs(sc, gi, g, attrs)
     if commit:
         sc.commit(builder)
     return sc, ff.Camera.from_dict(desc["camera"])
 
 
-def instantiate_on(desc, scene, meshes=None):
+def instantiate_on(desc, scene, meshes=None, attrs=None):
     """Same on any object with add_mesh/add_plane (the test oracle's scene classes)."""
     for g in desc["geoms"]:
         if g.get("sphere") is not None:
@@ -159,7 +234,8 @@ def instantiate_on(desc, scene, meshes=None):
         elif g["plane"]:
             scene.add_plane(g["pos"], g["rot"], g["scale"], g["material"])
         else:
-            scene.add_mesh(resolve_mesh(g, meshes), g["pos"], g["rot"], g["scale"], g["material"])
+            gi = scene.add_mesh(resolve_mesh(g, meshes), g["pos"], g["rot"], g["scale"], g["material"])
+            _apply_attrs(scene, gi, g, attrs)
     return scene
 
 

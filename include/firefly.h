@@ -59,7 +59,12 @@ typedef struct ff_material {
     float transmittance[3];  /* m_transmittanceColor: the refracted lobe of glass */
 } ff_material;
 
-enum { FF_INTEGRATOR_WAVEFRONT = 0, FF_INTEGRATOR_MEGAKERNEL = 1, FF_INTEGRATOR_AS_CODED = 2 };
+enum { FF_INTEGRATOR_WAVEFRONT = 0, FF_INTEGRATOR_MEGAKERNEL = 1, FF_INTEGRATOR_AS_CODED = 2,
+       /* primary-ray feature buffers through ff_render (one ray per pixel, spp / bounces ignored): */
+       FF_INTEGRATOR_AOV_NORMAL = 3, /* face-forwarded world shading normal (interpolated if the geometry has normals) */
+       FF_INTEGRATOR_AOV_UV = 4,     /* interpolated Triangle::m_uv (utilities.h:163-166) */
+       FF_INTEGRATOR_AOV_BARY = 5,   /* (1-u-v, u, v), the barycentrics of kernel.cu:80-81 */
+       FF_INTEGRATOR_AOV_ALBEDO = 6  /* albedo of the hit's (per-face) material */ };
 enum { FF_BUILDER_LBVH = 0, FF_BUILDER_SAH = 1 };
 enum { FF_TRACE_BVH8 = 0, FF_TRACE_BRUTE = 1, FF_TRACE_BVH2 = 2 };
 
@@ -139,6 +144,32 @@ int ff_scene_add_plane(ff_scene* scene, const float pos[3], const float rot_deg[
  * triangle (a ray that starts inside sees nothing). */
 int ff_scene_add_sphere(ff_scene* scene, float radius, const float pos[3], const float rot_deg[3], const float scale[3],
                         const ff_material* material, int* out_geometry_index);
+/* -- shading attributes the reference's loader carries and its tracer ignores: per-corner normals and
+ *    uvs (Triangle::m_n0..2 / m_uv0..2, utilities.h:163-170) and per-face materials (material_ids, read and dropped at
+ *    utilities.h:837).  All are optional, per triangle-mesh geometry, set between add and commit, and never touched by
+ *    traversal: hit ids and t are unaffected.
+ *    normals9: n_tris x 3 corners x xyz, object space.  A geometry with normals is shaded with the interpolated normal
+ *    (BSDF frame, cosines); ray offsets and sidedness keep the geometric normal; triangles whose interpolated normal is
+ *    zero fall back to the geometric one.  uvs6: n_tris x 3 corners x uv.  face_material: n_tris indices into
+ *    `materials` (-1 = the geometry's own material).  NULL clears the attribute. */
+int ff_scene_set_normals(ff_scene* scene, int geometry_index, const float* normals9);
+int ff_scene_set_uvs(ff_scene* scene, int geometry_index, const float* uvs6);
+int ff_scene_set_face_materials(ff_scene* scene, int geometry_index, const int* face_material, const ff_material* materials,
+                                int n_materials);
+/* ff_scene_add_obj with the attributes of the file.  flags: */
+enum { FF_OBJ_FLIP_WINDING = 1, /* swap v1/v2 (and their normals / uvs) of every face */
+       FF_OBJ_NORMALS = 2,      /* keep `vn`: smooth shading */
+       FF_OBJ_UVS = 4,          /* keep `vt` */
+       FF_OBJ_MATERIALS = 8     /* per-face `usemtl`, materials from the file's `mtllib` (searched next to the OBJ); a name
+                                 * the library does not define, or a missing library, keeps the geometry's material */ };
+int ff_scene_add_obj_ex(ff_scene* scene, const char* obj_path, const float pos[3], const float rot_deg[3],
+                        const float scale[3], const ff_material* material, int flags, int* out_geometry_index);
+/* The LoadMesh half on its own, all attributes, parsed on `threads` host threads (0 = all).  Any output may be NULL;
+ * capacity_tris bounds what is written.  Returns the triangle count or a negative ff_status.  out_seconds: wall time
+ * of read + parse (the ingest figure of SURVEY 8f f4). */
+long ff_load_obj_ex(const char* obj_path, float* xyz9, float* normals9, float* uvs6, int* face_material,
+                    size_t capacity_tris, int threads, int* out_has_normals, int* out_has_uvs, int* out_n_materials,
+                    double* out_seconds);
 /* OBJ -> xyz9 triangle list without a scene (the LoadMesh half on its own).  Call with xyz9 = NULL
  * to get the count. Returns the triangle count or a negative ff_status. */
 long ff_load_obj(const char* obj_path, float* xyz9, size_t capacity_tris);
@@ -167,6 +198,10 @@ int ff_trace_closest_device(ff_scene* scene, const void* d_rays, size_t n, int m
 int ff_trace_any(ff_scene* scene, const float* rays6, const float* tmax, size_t n, int mode,
                  unsigned char* out_occluded, ff_stats* stats);
 /* Unpack device hit records into the reference's numbering (host arrays, may be NULL). */
+/* ff_trace_closest that also returns the barycentrics of the hit (u, v weight v1, v2; kernel.cu:80-81, which the
+ * reference computes and drops): what a caller needs to interpolate its own per-corner data.  0 on misses / planes. */
+int ff_trace_closest_uv(ff_scene* scene, const float* rays6, size_t n, int mode, int* out_geom, int* out_tri,
+                        float* out_t, float* out_u, float* out_v, ff_stats* stats);
 int ff_hits_unpack(ff_scene* scene, const void* d_hits, size_t n, int* out_geom, int* out_tri, float* out_t);
 
 /* -- camera rays exactly as generateRays builds them (kernel.cu:198-205), host or device output. */

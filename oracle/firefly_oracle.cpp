@@ -215,17 +215,22 @@ struct Hit {  // utilities.h:57-66
     int geom = -1, tri = -1;
 };
 enum GType { SPHERE = 0, PLANE = 1, TRIANGLEMESH = 2 };  // utilities.h:141-146
+// BXDF utilities.h:77-88; type = BXDFTyp utilities.h:68-75 (0 EMITTER, 1 DIFFUSE, 2 MIRROR, 3 GLASS)
+struct Material {
+    int type; V3 albedo, emissive; float intensity;
+    V3 specular{1, 1, 1}; float ior = 1.5f; V3 transmittance{1, 1, 1};   // m_specularColor, m_refractiveIndex, m_transmittanceColor
+};
 struct Geom {
     int type;
     M4 model, inv;
     V3 normal{0, 0, 1};  // utilities.h:230
     float radius = 1.0f;  // Geometry::m_sphereRadius (utilities.h:227), used by intersectSphere
     std::vector<Tri> tris;
-};
-// BXDF utilities.h:77-88; type = BXDFTyp utilities.h:68-75 (0 EMITTER, 1 DIFFUSE, 2 MIRROR, 3 GLASS)
-struct Material {
-    int type; V3 albedo, emissive; float intensity;
-    V3 specular{1, 1, 1}; float ior = 1.5f; V3 transmittance{1, 1, 1};   // m_specularColor, m_refractiveIndex, m_transmittanceColor
+    // shading attributes the reference's loader keeps and its tracer never reads; empty when absent
+    std::vector<V3> normals;          // 3 per triangle, object space (Triangle::m_n0..2, utilities.h:168-170)
+    std::vector<float> uvs;           // 6 per triangle (Triangle::m_uv0..2, utilities.h:163-166)
+    std::vector<int> face_mat;        // per triangle: index into face_mats, -1 = the geometry's material (utilities.h:837)
+    std::vector<Material> face_mats;
 };
 struct Scene {
     std::vector<Geom> geoms;
@@ -424,6 +429,7 @@ inline void onb(V3 n, V3& t, V3& b) {
 struct Flat {
     std::vector<Tri> tris;
     std::vector<int> geom, tri;  // source numbering (geometryIndex, triangleIndex)
+    std::vector<V3> wnormal;     // 3 per flat triangle: inverse(transpose(M)) * (n, 0), not normalised; zero when the geometry has none
 };
 void flatten(const Scene& sc, Flat& f) {
     for (int i = 0; i < (int)sc.geoms.size(); ++i) {
@@ -435,8 +441,53 @@ void flatten(const Scene& sc, Flat& f) {
             w.v1 = xyz(mulMV(g.model, v4(g.tris[j].v1, 1.f)));
             w.v2 = xyz(mulMV(g.model, v4(g.tris[j].v2, 1.f)));
             f.tris.push_back(w); f.geom.push_back(i); f.tri.push_back(j);
+            for (int c = 0; c < 3; ++c) {
+                V3 n{0, 0, 0};
+                if (!g.normals.empty()) n = xyz(mulMV(inverse(transpose(g.model)), v4(g.normals[3 * (size_t)j + c], 0.f)));
+                f.wnormal.push_back(n);
+            }
         }
     }
+}
+// Material of triangle `tri` of geometry `geom` (tri < 0: analytic primitive).
+inline const Material& material_of(const Scene& sc, int geom, int tri) {
+    const Geom& g = sc.geoms[geom];
+    if (tri >= 0 && !g.face_mat.empty() && g.face_mat[tri] >= 0) return g.face_mats[g.face_mat[tri]];
+    return sc.mats[geom];
+}
+// The barycentrics intersectTriangle computes and drops (kernel.cu:53-81): u weights v1, v weights v2.
+inline void barycentrics(const Tri& tri, const Ray& ray, float& u, float& v) {
+    V3 edge1 = sub(tri.v1, tri.v0), edge2 = sub(tri.v2, tri.v0);
+    V3 pvec = cross(ray.d, edge2);
+    float det = dot(edge1, pvec);
+    V3 tvec = sub(ray.o, tri.v0);
+    u = dot(tvec, pvec);
+    V3 qvec = cross(tvec, edge1);
+    v = dot(ray.d, qvec);
+    float invDet = (float)(1.0 / (double)det);
+    u *= invDet;
+    v *= invDet;
+}
+// Shading attributes of a triangle hit; GPU twin: surface_attributes in ff_render.cu.
+struct SurfAttr { bool smooth = false; V3 ns{0, 0, 0}; float u = 0, v = 0, tu = 0, tv = 0; };
+inline SurfAttr surface_attributes(const Scene& sc, const Flat& f, int flat, const Ray& ray) {
+    SurfAttr a;
+    if (flat < 0) return a;
+    const Geom& g = sc.geoms[f.geom[flat]];
+    Ray os{ray.o, normalize(ray.d)};
+    barycentrics(f.tris[flat], os, a.u, a.v);
+    float w0 = (1.0f - a.u) - a.v;
+    if (!g.normals.empty()) {
+        const V3* n = &f.wnormal[3 * (size_t)flat];
+        V3 ns = add(add(mul(n[0], w0), mul(n[1], a.u)), mul(n[2], a.v));
+        if (dot(ns, ns) > 0.0f) { a.smooth = true; a.ns = normalize(ns); }
+    }
+    if (!g.uvs.empty()) {
+        const float* t = &g.uvs[6 * (size_t)f.tri[flat]];
+        a.tu = (t[0] * w0 + t[2] * a.u) + t[4] * a.v;
+        a.tv = (t[1] * w0 + t[3] * a.u) + t[5] * a.v;
+    }
+    return a;
 }
 // intersectRays on the baked scene: every geometry has M = I, so the object-space ray is
 // (o, normalize(d)) and the closest-hit key is distance(o + d'*t, o)  (kernel.cu:113-115,138).
@@ -509,7 +560,7 @@ struct OScene {
         if (!flat_valid) {
             flat = Flat(); flatten(sc, flat); flat_valid = true;
             lights.clear();
-            for (size_t k = 0; k < flat.tris.size(); ++k) if (sc.mats[flat.geom[k]].type == 0) lights.push_back((int)k);
+            for (size_t k = 0; k < flat.tris.size(); ++k) if (material_of(sc, flat.geom[k], flat.tri[k]).type == 0) lights.push_back((int)k);
         }
         return flat;
     }
@@ -546,7 +597,7 @@ inline V3 mul3(V3 a, V3 b) { return V3{a.x * b.x, a.y * b.y, a.z * b.z}; }
 // Returns false when the sample carries nothing; otherwise the shadow ray (origin `so`, unnormalised direction
 // `sd`, limit `tmax`) and the radiance `contrib` to add when it is unoccluded.
 bool sample_light(const OScene& os, const Flat& f, const std::vector<int>& lights, uint32_t pixel, uint32_t sample, int b,
-                  const RenderParams& rp, V3 so, V3 n, V3 beta, V3& sd, float& tmax, V3& contrib) {
+                  const RenderParams& rp, V3 so, V3 n, V3 ng, bool smooth, V3 beta, V3& sd, float& tmax, V3& contrib) {
     const uint32_t nl = (uint32_t)lights.size();
     if (nl == 0) return false;
     U4 r = philox4x32_10(U4{pixel, sample, (uint32_t)b, 2u}, rp.seed_lo, rp.seed_hi);
@@ -566,8 +617,9 @@ bool sample_light(const OScene& os, const Flat& f, const std::vector<int>& light
     float cosx = dot(n, sd) / dist;
     float cosl = (-dot(N, sd) / dist) / len;
     if (!(cosx > 0.0f && cosl > 0.0f && dist2 > 0.0f)) return false;
+    if (smooth && !(dot(ng, sd) > 0.0f)) return false;  // below the real surface: the shadow ray would leave through culled back faces
     float w = (((cosx * cosl) / dist2) * (0.5f * len)) * ((float)nl * 0.318309886183790672f);
-    const Material& m = os.sc.mats[f.geom[fi]];
+    const Material& m = material_of(os.sc, f.geom[fi], f.tri[fi]);
     contrib = mul(mul3(beta, mul(m.emissive, m.intensity)), w);
     tmax = dist * 0.999f;
     return true;
@@ -591,7 +643,8 @@ V3 trace_path(OScene& os, const Camera& cam, const M4& invVP, int x, int y, uint
         FlatHit h = intersectFlat(ray, os.sc, f);
         if (ray_count) ++*ray_count;
         if (!h.hit) { L = add(L, mul3(beta, bg)); break; }
-        const Material& m = os.sc.mats[h.geom];
+        const Material& m = material_of(os.sc, h.geom, h.tri);
+        const SurfAttr sa = surface_attributes(os.sc, f, h.flat, ray);
         if (m.type == 0) {
             // with NEE the direct light of sampled emitters (mesh emitters) arrives through the shadow rays; a hit found
             // by sampling the BSDF counts only for the camera ray and after a specular event (which has no light sample)
@@ -602,13 +655,18 @@ V3 trace_path(OScene& os, const Camera& cam, const M4& invVP, int x, int y, uint
         if (b == rp.max_bounces) break;
         V3 n = normalize(h.normal);
         if (dot(n, ray.d) > 0.0f) n = neg(n);
+        // shading normal: interpolated corner normal when the geometry carries normals, turned to the side of n; ray
+        // offsets and sidedness stay with the geometric normal n
+        V3 ns = n;
+        if (sa.smooth) { ns = sa.ns; if (dot(ns, n) < 0.0f) ns = neg(ns); }
         U4 r = philox4x32_10(U4{pixel, sample, (uint32_t)b, 0u}, rp.seed_lo, rp.seed_hi);
         if (m.type == 2 || m.type == 3) {
             // MIRROR / GLASS (BXDFTyp utilities.h:72-73; the reference declares the fields, utilities.h:84-88, and no
             // code).  Only front faces are ever hit (kernel.cu:48-51), so a ray meets a glass surface from outside only:
             // one refracting interface, air -> ior; Schlick's Fresnel picks reflection with probability F.
             V3 dn = normalize(ray.d);
-            float cosi = -dot(dn, n);
+            float cosi = -dot(dn, ns);
+            if (sa.smooth && !(cosi > 0.0f)) { ns = n; cosi = -dot(dn, n); }
             bool reflect = true;
             V3 d;
             if (m.type == 3) {
@@ -620,13 +678,14 @@ V3 trace_path(OScene& os, const Camera& cam, const M4& invVP, int x, int y, uint
                 float sin2t = (eta * eta) * (1.0f - cosi * cosi);
                 if (!(sin2t > 1.0f) && !(u01(r.z) < F)) {
                     reflect = false;
-                    d = add(mul(dn, eta), mul(n, eta * cosi - std::sqrt(1.0f - sin2t)));
+                    d = add(mul(dn, eta), mul(ns, eta * cosi - std::sqrt(1.0f - sin2t)));
                     beta = mul3(beta, m.transmittance);
                     ray.o = sub(h.point, mul(n, rp.ray_eps));
                 }
             }
             if (reflect) {
-                d = add(dn, mul(n, 2.0f * cosi));
+                d = add(dn, mul(ns, 2.0f * cosi));
+                if (sa.smooth) { float c = dot(d, n); if (!(c > 0.0f)) d = sub(d, mul(n, 2.0f * c)); }
                 beta = mul3(beta, m.specular);
                 ray.o = add(h.point, mul(n, rp.ray_eps));
             }
@@ -638,13 +697,14 @@ V3 trace_path(OScene& os, const Camera& cam, const M4& invVP, int x, int y, uint
         beta = mul3(beta, m.albedo);
         V3 w = cosineSampleHemisphere(u01(r.x), u01(r.y));
         V3 t, bt;
-        onb(n, t, bt);
-        V3 d = add(add(mul(t, w.x), mul(bt, w.y)), mul(n, w.z));
+        onb(ns, t, bt);
+        V3 d = add(add(mul(t, w.x), mul(bt, w.y)), mul(ns, w.z));
+        if (sa.smooth) { float c = dot(d, n); if (!(c > 0.0f)) d = sub(d, mul(n, 2.0f * c)); }
         ray.o = add(h.point, mul(n, rp.ray_eps));
         ray.d = d;
         if (rp.nee) {
             V3 sd, contrib; float tmax;
-            if (sample_light(os, f, lights, pixel, sample, b, rp, ray.o, n, beta, sd, tmax, contrib)) {
+            if (sample_light(os, f, lights, pixel, sample, b, rp, ray.o, ns, n, sa.smooth, beta, sd, tmax, contrib)) {
                 if (shadow_count) ++*shadow_count;
                 if (!occludedFlat(Ray{ray.o, sd}, tmax, os.sc, f)) L = add(L, contrib);
             }
@@ -709,6 +769,37 @@ int orc_scene_add_sphere(void* s, float radius, const float pos[3], const float 
     push_material(os, mat8);
     os->flat_valid = false;
     return (int)os->sc.geoms.size() - 1;
+}
+static Material material_from15(const float* m15) {
+    Material m;
+    m.type = (int)m15[0]; m.albedo = v3(m15[1], m15[2], m15[3]); m.emissive = v3(m15[4], m15[5], m15[6]); m.intensity = m15[7];
+    m.specular = v3(m15[8], m15[9], m15[10]); m.ior = m15[11]; m.transmittance = v3(m15[12], m15[13], m15[14]);
+    return m;
+}
+// shading attributes of a mesh geometry (NULL clears): normals9 / uvs6 per triangle; face_mat indexes mats15 rows, -1 = own
+void orc_scene_set_normals(void* s, int gi, const float* n9) {
+    OScene* os = (OScene*)s;
+    Geom& g = os->sc.geoms[gi];
+    g.normals.clear();
+    if (n9) for (size_t c = 0; c < 3 * g.tris.size(); ++c) g.normals.push_back(v3(n9[3 * c], n9[3 * c + 1], n9[3 * c + 2]));
+    os->flat_valid = false;
+}
+void orc_scene_set_uvs(void* s, int gi, const float* uv6) {
+    OScene* os = (OScene*)s;
+    Geom& g = os->sc.geoms[gi];
+    g.uvs.clear();
+    if (uv6) g.uvs.assign(uv6, uv6 + 6 * g.tris.size());
+    os->flat_valid = false;
+}
+void orc_scene_set_face_materials(void* s, int gi, const int* face_mat, const float* mats15, int n_mats) {
+    OScene* os = (OScene*)s;
+    Geom& g = os->sc.geoms[gi];
+    g.face_mat.clear(); g.face_mats.clear();
+    if (face_mat) {
+        g.face_mat.assign(face_mat, face_mat + g.tris.size());
+        for (int k = 0; k < n_mats; ++k) g.face_mats.push_back(material_from15(mats15 + 15 * k));
+    }
+    os->flat_valid = false;
 }
 void orc_geometry_matrices(void* s, int gi, float* model16, float* inv16) {
     OScene* os = (OScene*)s;
@@ -818,6 +909,51 @@ void orc_render_as_coded(void* s, int mode, const float pos[3], const float worl
                     for (int k = 0; k < 3; ++k) px[k] = (unsigned char)(c[k] > 255.f ? 255.f : c[k]);
                 }
             }
+    });
+}
+
+// Primary-ray feature buffers on the baked scene; kind as FF_INTEGRATOR_AOV_*: 3 shading normal, 4 uv, 5 barycentrics,
+// 6 albedo.  rgba = W*H*4 floats, alpha 1 on a hit, everything 0 on a miss.
+void orc_render_aov(void* s, int kind, const float pos[3], const float world_up[3], float yaw, float pitch, float fov, int width,
+                    int height, float near_clip, float far_clip, float* rgba, int nthreads) {
+    OScene* os = (OScene*)s;
+    Camera cam = make_camera(pos, world_up, yaw, pitch, fov, (float)width, (float)height, near_clip, far_clip);
+    M4 invVP = mulMM(cam.invView(), cam.invProj());
+    std::memset(rgba, 0, sizeof(float) * 4 * (size_t)width * height);
+    os->get_flat();
+    parallel_for((size_t)height, nthreads, [=](size_t a, size_t b) {
+        for (size_t y = a; y < b; ++y)
+            for (int x = 0; x < width; ++x) {
+                Ray ray = gen_ray(cam, invVP, (float)x, (float)y);
+                FlatHit h = intersectFlat(ray, os->sc, os->flat);
+                if (!h.hit) continue;
+                float* px = rgba + 4 * (y * width + x);
+                SurfAttr sa = surface_attributes(os->sc, os->flat, h.flat, ray);
+                px[3] = 1.0f;
+                if (kind == 3) {
+                    V3 n = normalize(h.normal);
+                    if (dot(n, ray.d) > 0.0f) n = neg(n);
+                    V3 ns = n;
+                    if (sa.smooth) { ns = sa.ns; if (dot(ns, n) < 0.0f) ns = neg(ns); }
+                    px[0] = ns.x; px[1] = ns.y; px[2] = ns.z;
+                } else if (kind == 4) { px[0] = sa.tu; px[1] = sa.tv; }
+                else if (kind == 5) { if (h.flat >= 0) { px[0] = (1.0f - sa.u) - sa.v; px[1] = sa.u; px[2] = sa.v; } }
+                else { const Material& m = material_of(os->sc, h.geom, h.tri); px[0] = m.albedo.x; px[1] = m.albedo.y; px[2] = m.albedo.z; }
+            }
+    });
+}
+// closest hit on the baked scene + the barycentrics of the hit (0 on misses and analytic primitives)
+void orc_intersect_uv(void* s, const float* rays6, long n, int* out_geom, int* out_tri, float* out_u, float* out_v, int nthreads) {
+    OScene* os = (OScene*)s;
+    os->get_flat();
+    parallel_for((size_t)n, nthreads, [=](size_t a, size_t b) {
+        for (size_t i = a; i < b; ++i) {
+            Ray ray{v3(rays6[6 * i], rays6[6 * i + 1], rays6[6 * i + 2]), v3(rays6[6 * i + 3], rays6[6 * i + 4], rays6[6 * i + 5])};
+            FlatHit h = intersectFlat(ray, os->sc, os->flat);
+            SurfAttr sa = surface_attributes(os->sc, os->flat, h.hit ? h.flat : -1, ray);
+            out_geom[i] = h.hit ? h.geom : -1; out_tri[i] = h.hit ? h.tri : -1;
+            out_u[i] = sa.u; out_v[i] = sa.v;
+        }
     });
 }
 

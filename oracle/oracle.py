@@ -175,6 +175,41 @@ class OracleScene(_SceneBase):
         self.n_geoms += 1
         return self.o.f("scene_add_sphere")(self.h, C.c_float(radius), _vec3(pos), _vec3(rot), _vec3(scale), _ptr(mat8(material)))
 
+    # shading attributes; None clears
+    def set_normals(self, gi, normals9):
+        a = None if normals9 is None else np.ascontiguousarray(normals9, np.float32).reshape(-1, 9)
+        self.o.f("scene_set_normals")(self.h, int(gi), _ptr(a))
+
+    def set_uvs(self, gi, uvs6):
+        a = None if uvs6 is None else np.ascontiguousarray(uvs6, np.float32).reshape(-1, 6)
+        self.o.f("scene_set_uvs")(self.h, int(gi), _ptr(a))
+
+    def set_face_materials(self, gi, face_material, materials):
+        if face_material is None:
+            self.o.f("scene_set_face_materials")(self.h, int(gi), None, None, 0)
+            return
+        fm = np.ascontiguousarray(face_material, np.int32)
+        m = np.ascontiguousarray(np.stack([mat8(x) for x in materials]) if len(materials) else np.zeros((0, 15)), np.float32)
+        self.o.f("scene_set_face_materials")(self.h, int(gi), _ptr(fm), _ptr(m), int(len(materials)))
+
+    def intersect_uv(self, rays, threads=None):
+        """Closest hit on the baked scene + the barycentrics of kernel.cu:80-81 (0 on misses / analytic primitives)."""
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
+        n = len(rays)
+        out = dict(geom=np.empty(n, np.int32), tri=np.empty(n, np.int32), u=np.empty(n, np.float32), v=np.empty(n, np.float32))
+        self.o.f("intersect_uv")(self.h, _ptr(rays), C.c_long(n), _ptr(out["geom"]), _ptr(out["tri"]), _ptr(out["u"]),
+                                 _ptr(out["v"]), int(threads or self.o.threads))
+        return out
+
+    def render_aov(self, cam, kind, threads=None):
+        """Primary-ray feature buffer; kind 3 shading normal, 4 uv, 5 barycentrics, 6 albedo -> rgba[h,w,4]."""
+        w, h = int(cam["width"]), int(cam["height"])
+        out = np.empty((h, w, 4), np.float32)
+        self.o.f("render_aov")(self.h, int(kind), _vec3(cam["pos"]), _vec3(cam.get("world_up", (0, 1, 0))),
+                               C.c_float(cam["yaw"]), C.c_float(cam["pitch"]), C.c_float(cam["fov"]), w, h,
+                               C.c_float(cam["near"]), C.c_float(cam["far"]), _ptr(out), int(threads or self.o.threads))
+        return out
+
     def flat(self):
         self.o.f("flat_count").restype = C.c_long
         n = self.o.f("flat_count")(self.h)

@@ -264,6 +264,59 @@ long ref_load_obj(const char* path, float* xyz9, long cap_tris) {
     return n;
 }
 
+// LoadMesh (utilities.h:806-837) with every attribute it gathers: per-corner position, normal, uv and the per-face
+// material id it reads and drops (utilities.h:837); normal / uv reads guarded for files without `vn` / `vt`
+// (index -1 -> zeros).  Any output may be null.
+long ref_load_obj_attrs(const char* path, float* xyz9, float* n9, float* uv6, int* material_id, long cap_tris) {
+    tinyobj::attrib_t attrib;
+    std::vector<tinyobj::shape_t> shapes;
+    std::vector<tinyobj::material_t> materials;
+    std::string warn, err;
+    bool ret = tinyobj::LoadObj(&attrib, &shapes, &materials, &warn, &err, path);
+    if (!ret) return -1;
+    long n = 0;
+    for (size_t s = 0; s < shapes.size(); s++) {
+        size_t index_offset = 0;
+        for (size_t f = 0; f < shapes[s].mesh.num_face_vertices.size(); f++) {
+            int fv = shapes[s].mesh.num_face_vertices[f];
+            if (n < cap_tris) {
+                for (int v = 0; v < 3; v++) {
+                    tinyobj::index_t idx = shapes[s].mesh.indices[index_offset + v];
+                    for (int k = 0; k < 3; ++k) {
+                        if (xyz9) xyz9[9 * n + 3 * v + k] = attrib.vertices[3 * idx.vertex_index + k];
+                        if (n9) n9[9 * n + 3 * v + k] = idx.normal_index >= 0 ? attrib.normals[3 * idx.normal_index + k] : 0.f;
+                    }
+                    for (int k = 0; k < 2; ++k)
+                        if (uv6) uv6[6 * n + 2 * v + k] = idx.texcoord_index >= 0 ? attrib.texcoords[2 * idx.texcoord_index + k] : 0.f;
+                }
+                if (material_id) material_id[n] = shapes[s].mesh.material_ids[f];
+            }
+            index_offset += fv;
+            ++n;
+        }
+    }
+    return n;
+}
+
+// Camera::ProcessKeyboard / ProcessMouseMovement / resetCamera (utilities.h:343-427) driven through the reference's own
+// struct.  state = {pos xyz, yaw, pitch}; ops = n x {kind, a, b}: kind 0 = ProcessKeyboard((int)a); kind 1 =
+// SetClickPosition(a, b) (absolute deltas) then ProcessMouseMovement(true).  Outputs the final state and basis.
+void ref_camera_walk(const float world_up[3], float* state5, const float* ops3, long n_ops, float* basis9) {
+    Camera cam;
+    cam.m_position = glm::vec3(state5[0], state5[1], state5[2]);
+    cam.m_worldUp = glm::vec3(world_up[0], world_up[1], world_up[2]);
+    cam.m_yaw = state5[3]; cam.m_pitch = state5[4];
+    cam.UpdateBasisAxis();
+    for (long i = 0; i < n_ops; ++i) {
+        const float* op = ops3 + 3 * i;
+        if ((int)op[0] == 0) cam.ProcessKeyboard((int)op[1]);
+        else { cam.SetClickPosition(op[1], op[2]); cam.ProcessMouseMovement(true); }
+    }
+    state5[0] = cam.m_position.x; state5[1] = cam.m_position.y; state5[2] = cam.m_position.z; state5[3] = cam.m_yaw; state5[4] = cam.m_pitch;
+    const glm::vec3 b[3] = {cam.m_forward, cam.m_right, cam.m_up};
+    for (int k = 0; k < 3; ++k) { basis9[3 * k] = b[k].x; basis9[3 * k + 1] = b[k].y; basis9[3 * k + 2] = b[k].z; }
+}
+
 // Timed brute-force batch for the CPU baseline: returns best-of-`reps` seconds.
 double ref_time_intersect(void* s, const float* rays6, long n, int nthreads, int reps, int* out_geom, int* out_tri,
                           float* out_t) {

@@ -204,3 +204,113 @@ def test_scene_file_and_headless_cli(ff, ctx, orc, meshes, tmp_path):
     assert r.returncode == 0 and open(png, "rb").read(8) == b"\x89PNG\r\n\x1a\n"
     r = subprocess.run([cli, str(tmp_path / "nope.ffscene")], capture_output=True, text=True, timeout=60)
     assert r.returncode == 1 and "cannot read scene file" in r.stderr
+
+
+@pytest.fixture(scope="module")
+def attrs():
+    return S.load_mesh_attrs()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nee", [0, 1])
+def test_shading_attributes_bit_identical_to_oracle(ff, ctx, orc, meshes, attrs, nee):
+    """interpolated corner normals (diffuse, mirror, glass; one mesh under a non-uniform scale), uvs and
+    per-face materials (emissive faces join the NEE light list): both integrators bit-identical to the oracle, ray and
+    shadow-ray counts included; every feature buffer bit-identical; hit ids unaffected by the attributes."""
+    desc = S.shaded(meshes, 72, 56, 4, 5)
+    sc, cam = S.instantiate(desc, ctx, meshes, attrs=attrs)
+    osc = S.instantiate_on(desc, orc.scene(), meshes, attrs)
+    rays = ctx.camera_rays(cam)
+    got, want = sc.trace_closest_uv(rays), osc.intersect_uv(rays)
+    assert (got["geom"] == want["geom"]).all() and (got["tri"] == want["tri"]).all()
+    assert (bits(got["u"]) == bits(want["u"])).all() and (bits(got["v"]) == bits(want["v"])).all()
+    assert set(np.unique(want["geom"])) >= {0, 2, 3, 4, 5, 6}
+    if nee == 0:
+        for kind in (ff.AOV_NORMAL, ff.AOV_UV, ff.AOV_BARY, ff.AOV_ALBEDO):
+            a, b = sc.render(cam, integrator=kind), osc.render_aov(desc["camera"], kind)
+            assert (bits(a) == bits(b)).all(), "feature buffer %d: max abs diff %g" % (kind, np.abs(a - b).max())
+        assert len(np.unique(sc.render(cam, integrator=ff.AOV_ALBEDO).reshape(-1, 4), axis=0)) >= 8  # per-face materials visible
+    img, rays_o, shadow_o = osc.render(desc["camera"], desc["spp"], desc["max_bounces"], seed=17, aa=1, nee=nee, want_shadow_rays=True)
+    for integ in (ff.INTEGRATOR_WAVEFRONT, ff.INTEGRATOR_MEGAKERNEL):
+        out, st = sc.render(cam, desc["spp"], desc["max_bounces"], want_stats=True, integrator=integ, seed=17, aa=1, nee=nee)
+        assert (bits(out) == bits(img)).all(), "integrator %d nee %d: max abs diff %g" % (integ, nee, np.abs(out - img).max())
+        assert st["rays"] == rays_o and st["shadow_rays"] == shadow_o
+    assert img[..., :3].max() > 0
+    # the SAH tree shades identically (attributes are addressed by flat index, not by leaf slot)
+    sc.commit(ff.BUILDER_SAH)
+    out = sc.render(cam, desc["spp"], desc["max_bounces"], seed=17, aa=1, nee=nee)
+    assert (bits(out) == bits(img)).all()
+
+
+@pytest.mark.gpu
+def test_obj_attributes_through_the_scene(ff, ctx, orc, meshes, attrs, tmp_path):
+    """ff_scene_add_obj_ex: the attributes of an OBJ + MTL pair reach shading (flags pick which), a missing library or an
+    unknown material name keeps the geometry's material, flip swaps normals and uvs with the corners; setter errors."""
+    from test_host import _write_obj_full
+    name = "sphere"
+    xyz9, n9 = meshes[name], attrs[name + "_n"]
+    n = len(xyz9)
+    uv6 = np.stack([xyz9[:, 0], xyz9[:, 1], xyz9[:, 3], xyz9[:, 4], xyz9[:, 6], xyz9[:, 7]], 1).astype(np.float32) * np.float32(0.25)
+    face_mat = ((np.arange(n) // 40) % 3).astype(np.int32)
+    (tmp_path / "lib.mtl").write_text("newmtl red\nKd 0.9 0.1 0.1\n\nnewmtl mirror\nKs 0.8 0.8 0.9\nillum 3\n\nnewmtl lamp\nKe 2 1.5 1\n")
+    mats = [dict(type=1, albedo=(0.9, 0.1, 0.1), specular=(1, 1, 1)), dict(type=2, albedo=(0.8, 0.8, 0.8), specular=(0.8, 0.8, 0.9)),
+            dict(type=0, albedo=(0.8, 0.8, 0.8), emissive=(2, 1.5, 1), intensity=1.0)]
+    p = str(tmp_path / "ball.obj")
+    _write_obj_full(p, xyz9, n9, uv6, face_mat, ["red", "mirror", "unknown"], mtl="lib.mtl")
+    face_mat_known = np.where(face_mat == 2, -1, face_mat).astype(np.int32)   # "unknown" is not in the library
+    own = dict(type=1, albedo=(0.3, 0.6, 0.9))
+    cam_d = S.camera((0, 0.5, 9), fov=40.0, width=48, height=40)
+    cam = ff.Camera.from_dict(cam_d)
+    box = S.flip_winding(meshes["cube"])
+
+    def build(flags, flip=False):
+        sc = ctx.scene()
+        sc.add_triangles(box, scale=(12, 12, 24), material=S.EMITTER_WHITE2)
+        sc.add_obj_ex(p, material=own, flags=flags | (ff.OBJ_FLIP_WINDING if flip else 0))
+        sc.commit()
+        return sc
+
+    def oracle(normals, uvs, fm, flip=False):
+        sc = orc.scene()
+        sc.add_mesh(box, scale=(12, 12, 24), material=S.EMITTER_WHITE2)
+        g = S.geom(xyz9, material=own, flip=flip, normals=n9 if normals else None, uvs=uv6 if uvs else None,
+                   face_materials=(face_mat_known, mats[:2]) if fm else None)
+        gi = sc.add_mesh(S.resolve_mesh(g, None), material=own)
+        S._apply_attrs(sc, gi, g, None)
+        return sc
+
+    for flags, flip in ((0, False), (ff.OBJ_NORMALS, False), (ff.OBJ_NORMALS | ff.OBJ_UVS | ff.OBJ_MATERIALS, False),
+                        (ff.OBJ_NORMALS | ff.OBJ_UVS | ff.OBJ_MATERIALS, True)):
+        sc = build(flags, flip)
+        osc = oracle(flags & ff.OBJ_NORMALS, flags & ff.OBJ_UVS, flags & ff.OBJ_MATERIALS, flip)
+        for kind in (ff.AOV_NORMAL, ff.AOV_UV, ff.AOV_ALBEDO):
+            assert (bits(sc.render(cam, integrator=kind)) == bits(osc.render_aov(cam_d, kind))).all(), (flags, flip, kind)
+        want, _ = osc.render(cam_d, 2, 3, seed=4, aa=1)
+        assert (bits(sc.render(cam, 2, 3, seed=4, aa=1)) == bits(want)).all(), (flags, flip)
+    # the same through a scene file: `mesh ... normals uvs materials`
+    sf = tmp_path / "ball.ffscene"
+    sf.write_text("camera pos 0 0.5 9 yaw -90 fov 40 size 48 40 near 0.1 far 1000\n"
+                  "material own diffuse albedo 0.3 0.6 0.9\nmaterial lamp emitter emissive 1 1 1 intensity 2\n"
+                  "triangles scale 12 12 24 material lamp flip\n" + "".join("tri %s\n" % " ".join("%.9g" % v for v in t) for t in meshes["cube"]) +
+                  "end\nmesh ball.obj material own normals uvs materials\nrender spp 2 bounces 3 seed 4 aa 1\n")
+    fsc, fcam, d = ff.load_scene_file(ctx, str(sf))
+    fsc.commit(d.builder)
+    osc = oracle(True, True, True)
+    for kind in (ff.AOV_NORMAL, ff.AOV_UV, ff.AOV_ALBEDO):
+        assert (bits(fsc.render(fcam, integrator=kind)) == bits(osc.render_aov(cam_d, kind))).all(), kind
+    # a missing material library is an I/O error only when materials were asked for
+    q = str(tmp_path / "nolib.obj")
+    _write_obj_full(q, xyz9, n9, uv6, face_mat, ["red", "mirror", "lamp"], mtl="absent.mtl")
+    sc = ctx.scene()
+    sc.add_obj_ex(q, flags=ff.OBJ_NORMALS)
+    with pytest.raises(ff.FireflyError):
+        sc.add_obj_ex(q, flags=ff.OBJ_MATERIALS)
+    with pytest.raises(ff.FireflyError):
+        sc.add_obj_ex(q, flags=64)
+    gi = sc.add_plane()
+    with pytest.raises(ff.FireflyError):
+        sc.set_normals(gi, n9)
+    with pytest.raises(ff.FireflyError):
+        sc.set_face_materials(0, np.full(n, 3, np.int32), mats)   # index 3 of 3 materials
+    with pytest.raises(ff.FireflyError):
+        sc.set_uvs(7, uv6)

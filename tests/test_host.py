@@ -91,6 +91,95 @@ def test_obj_reader_on_reference_assets(ff, meshes):
         assert (bits(got) == bits(meshes[name])).all(), name
 
 
+@pytest.fixture(scope="module")
+def attrs():
+    return S.load_mesh_attrs()
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/sceneResources"), reason="reference tree not mounted")
+def test_obj_attributes_on_reference_assets(ff, meshes, attrs):
+    """Normals / uvs of the shipped meshes equal what the reference's own loader (tinyobjloader through LoadMesh's gather
+    loop, oracle/ref_shim.cpp) produced for the committed fixture, bit for bit, for 1 and many parser threads."""
+    for name in S.MESH_NAMES:
+        for threads in (1, 0):
+            m = ff.load_obj_ex("/root/reference/sceneResources/%s.obj" % name, threads=threads)
+            assert (bits(m["xyz9"]) == bits(meshes[name])).all(), name
+            assert (bits(m["normals9"]) == bits(attrs[name + "_n"])).all(), name
+            assert (bits(m["uvs6"]) == bits(attrs[name + "_uv"])).all(), name
+            assert m["has_normals"] == (name != "triangle") and m["has_uvs"] == (name != "triangle")   # sphere.obj: `vt` all zero
+
+
+def _write_obj_full(path, xyz9, n9, uv6, face_mat, names, relative_every=0, mtl=None):
+    """Indexed OBJ with v/vt/vn pools, `usemtl` runs, optional relative indices on every k-th face."""
+    n = len(xyz9)
+    with open(path, "w") as f:
+        if mtl:
+            f.write("mtllib %s\n" % mtl)
+        nv = nt = nn = 0
+        current = None
+        for i in range(n):
+            for k in range(3):
+                f.write("v %.9g %.9g %.9g\n" % tuple(xyz9[i, 3 * k:3 * k + 3]))
+                f.write("vn %.9g %.9g %.9g\n" % tuple(n9[i, 3 * k:3 * k + 3]))
+                f.write("vt %.9g %.9g\n" % tuple(uv6[i, 2 * k:2 * k + 2]))
+            nv += 3; nt += 3; nn += 3
+            if face_mat[i] != current:
+                current = face_mat[i]
+                if current >= 0:
+                    f.write("usemtl %s\n" % names[current])
+            if relative_every and i % relative_every == 0:
+                f.write("f -3/-3/-3 -2/-2/-2 -1/-1/-1\n")
+            else:
+                f.write("f %d/%d/%d %d/%d/%d %d/%d/%d\n" % (nv - 2, nt - 2, nn - 2, nv - 1, nt - 1, nn - 1, nv, nt, nn))
+
+
+def test_obj_parallel_parse_and_materials(ff, meshes, attrs, tmp_path, monkeypatch):
+    """The chunked parser gives the same arrays for any chunking (relative indices and `usemtl` runs cross chunk
+    borders), and agrees with the reference's loader (tinyobjloader) on positions, normals, uvs and material ids."""
+    name = "sphereBlender"
+    xyz9, n9, uv6 = meshes[name], attrs[name + "_n"], attrs[name + "_uv"]
+    n = len(xyz9)
+    face_mat = ((np.arange(n) // 37) % 3).astype(np.int32)   # first use in order 0, 1, 2 = MTL order
+    names = ["red", "mirror", "lamp"]
+    (tmp_path / "lib.mtl").write_text(
+        "newmtl red\nKd 0.9 0.1 0.1\nillum 2\n\nnewmtl mirror\nKd 0 0 0\nKs 0.8 0.8 0.9\nillum 3\n\n"
+        "newmtl lamp\nKe 2 1.5 1\nKd 0 0 0\n")
+    p = str(tmp_path / "full.obj")
+    _write_obj_full(p, xyz9, n9, uv6, face_mat, names, relative_every=5, mtl="lib.mtl")
+    base = ff.load_obj_ex(p, threads=1)
+    assert (bits(base["xyz9"]) == bits(xyz9)).all() and (bits(base["normals9"]) == bits(n9)).all()
+    assert (bits(base["uvs6"]) == bits(uv6)).all() and (base["face_material"] == face_mat).all()
+    assert base["n_materials"] == 3 and base["has_normals"] and base["has_uvs"]
+    monkeypatch.setenv("FF_OBJ_CHUNK_BYTES", "4096")   # ~100 chunks' worth of file, cut into up to `threads` chunks
+    for threads in (2, 3, 7, 16):
+        m = ff.load_obj_ex(p, threads=threads)
+        for k in ("xyz9", "normals9", "uvs6", "face_material"):
+            assert np.array_equal(m[k], base[k]), (threads, k)
+    monkeypatch.delenv("FF_OBJ_CHUNK_BYTES")
+    from oracle import oracle as O
+    if O.Ref.available():
+        import ctypes as C
+        lib = C.CDLL(O.REF_SO)
+        fn = lib.ref_load_obj_attrs
+        fn.restype = C.c_long
+        fn.argtypes = [C.c_char_p] + [C.c_void_p] * 4 + [C.c_long]
+        r = [np.zeros((n, 9), np.float32), np.zeros((n, 9), np.float32), np.zeros((n, 6), np.float32), np.zeros(n, np.int32)]
+        cwd = os.getcwd()
+        os.chdir(tmp_path)   # tinyobjloader resolves mtllib against the working directory
+        try:
+            assert fn(b"full.obj", *[a.ctypes.data for a in r], n) == n
+        finally:
+            os.chdir(cwd)
+        assert (bits(r[0]) == bits(base["xyz9"])).all() and (bits(r[1]) == bits(base["normals9"])).all()
+        assert (bits(r[2]) == bits(base["uvs6"])).all() and (r[3] == base["face_material"]).all()
+    # malformed input is reported with the file's line number, also from a later chunk
+    bad = tmp_path / "bad2.obj"
+    bad.write_text("v 0 0 0\n" * 2000 + "f 1 2 x\n")
+    monkeypatch.setenv("FF_OBJ_CHUNK_BYTES", "1024")
+    with pytest.raises(ff.FireflyError, match="line 2001"):
+        ff.load_obj_ex(str(bad), threads=8)
+
+
 def test_camera_matches_oracle_bit_exact(ff, orc, golden):
     g = golden("ref_camera.npz")
     for i in range(3):

@@ -237,3 +237,78 @@ def test_mirror_and_glass_events(orc, meshes):
     off = S.camera((0.9, 0, 4), yaw=-90, fov=0.01, width=1, height=1)
     o = g.render(off, 1, 0, background=(0, 0, 0))  # max_bounces 0: nothing to add, just must not crash
     assert o[0].shape == (1, 1, 4)
+
+
+def test_shading_attribute_known_answers(orc):
+    """Barycentrics (kernel.cu:80-81), interpolated normal and uv on one triangle, against hand-computed values."""
+    sc = orc.scene()
+    tri = np.array([[0, 0, 0, 1, 0, 0, 0, 1, 0]], np.float32)
+    gi = sc.add_mesh(tri)
+    sc.set_normals(gi, np.array([[0, 0, 1, 1, 0, 1, 0, 1, 1]], np.float32))
+    sc.set_uvs(gi, np.array([[0, 0, 1, 0, 0, 1]], np.float32))
+    rays = np.array([[0.25, 0.5, 1, 0, 0, -1], [0.125, 0.125, 2, 0, 0, -3], [2, 2, 1, 0, 0, -1]], np.float32)
+    h = sc.intersect_uv(rays)
+    assert h["geom"].tolist() == [0, 0, -1] and h["tri"].tolist() == [0, 0, -1]
+    assert h["u"].tolist() == [0.25, 0.125, 0.0] and h["v"].tolist() == [0.5, 0.125, 0.0]
+    cam = dict(pos=(0.25, 0.5, 1.0), world_up=(0, 1, 0), yaw=-90.0, pitch=0.0, fov=40.0, width=2, height=2, near=0.1, far=100.0)
+    # pixel (1,1) of a 2x2 frame is the image centre (integer pixel corners, kernel.cu:200-201): the ray straight down -z
+    n = sc.render_aov(cam, 3)[1, 1]
+    want = np.array([0.25, 0.5, 1.0]) / np.linalg.norm([0.25, 0.5, 1.0])
+    assert np.allclose(n[:3], want, atol=1e-6) and n[3] == 1.0
+    assert np.allclose(sc.render_aov(cam, 4)[1, 1], [0.25, 0.5, 0, 1], atol=1e-6)
+    assert np.allclose(sc.render_aov(cam, 5)[1, 1], [0.25, 0.25, 0.5, 1], atol=1e-6)
+    assert np.allclose(sc.render_aov(cam, 6)[1, 1], [0.8, 0.8, 0.8, 1])
+    sc.set_normals(gi, None)
+    assert np.allclose(sc.render_aov(cam, 3)[1, 1], [0, 0, 1, 1])   # geometric normal, facing the camera
+
+
+def test_shading_attribute_properties(orc, meshes):
+    """All-zero normals and all -1 face materials change nothing; per-face materials equal the same triangles split into
+    one geometry per material (same flat order, so the same light list and the same tie-breaks); smooth normals change
+    shading but not what is hit."""
+    attrs = S.load_mesh_attrs()
+    desc = S.shaded(meshes, 40, 32, 3, 4)
+    cam = desc["camera"]
+    base = S.instantiate_on(desc, orc.scene(), meshes, attrs)
+    img, rays = base.render(cam, 3, 4, seed=5, aa=1, nee=1)
+    assert img[..., :3].max() > 0 and np.isfinite(img).all()
+    # (1) no-op attributes
+    plain_desc = S.config2(meshes, 40, 32, 3, 4)
+    plain = S.instantiate_on(plain_desc, orc.scene(), meshes)
+    want, _ = plain.render(cam, 3, 4, seed=5, aa=1, nee=1)
+    noop = S.instantiate_on(plain_desc, orc.scene(), meshes)
+    nr = len(meshes["rocketman"])
+    noop.set_normals(2, np.zeros((nr, 9), np.float32))
+    noop.set_face_materials(2, np.full(nr, -1, np.int32), [dict(type=0, emissive=(9, 9, 9), intensity=9.0)])
+    got, _ = noop.render(cam, 3, 4, seed=5, aa=1, nee=1)
+    assert (bits(got) == bits(want)).all()
+    # (2) per-face materials == split geometries
+    mats = [dict(type=1, albedo=(0.9, 0.2, 0.2)), dict(type=0, emissive=(1, 0.8, 0.6), intensity=4.0), dict(type=2, specular=(0.9, 0.9, 0.9))]
+    w = meshes["wahoo"]
+    cut = [0, 1700, 3400, len(w)]
+    a, b = orc.scene(), orc.scene()
+    for s in (a, b):
+        s.add_mesh(S.flip_winding(meshes["cube"]), scale=(5, 5, 5))
+    gi = a.add_mesh(w, pos=(0, -2.4, 0), scale=(0.2, 0.2, 0.2))
+    fm = np.concatenate([np.full(cut[k + 1] - cut[k], k, np.int32) for k in range(3)])
+    a.set_face_materials(gi, fm, mats)
+    for k in range(3):
+        b.add_mesh(w[cut[k]:cut[k + 1]], pos=(0, -2.4, 0), scale=(0.2, 0.2, 0.2), material=mats[k])
+    for nee in (0, 1):
+        ia, ra, sa = a.render(cam, 3, 4, seed=9, aa=1, nee=nee, want_shadow_rays=True)
+        ib, rb, sb = b.render(cam, 3, 4, seed=9, aa=1, nee=nee, want_shadow_rays=True)
+        assert (bits(ia) == bits(ib)).all() and ra == rb and sa == sb and ia[..., :3].max() > 0
+    # (3) smooth normals: same primary hits, different shading normals on the curved meshes
+    flat_desc = dict(desc, geoms=[dict(g, normals=None) for g in desc["geoms"]])
+    flat = S.instantiate_on(flat_desc, orc.scene(), meshes, attrs)
+    rays6, _ = orc.camera_rays(cam)
+    h1, h2 = base.intersect(rays6, mode=1), flat.intersect(rays6, mode=1)
+    assert (h1["geom"] == h2["geom"]).all() and (h1["tri"] == h2["tri"]).all() and (bits(h1["t"]) == bits(h2["t"])).all()
+    n1, n2 = base.render_aov(cam, 3), flat.render_aov(cam, 3)
+    on_sphere = np.isin(h1["geom"].reshape(32, 40), [2, 3, 4, 5])   # wahoo.obj and sphere.obj have smooth normals
+    assert on_sphere.sum() > 50
+    diff = np.abs(n1 - n2)[..., :3].max(-1)
+    assert (diff[on_sphere] > 1e-3).mean() > 0.8 and (diff[~on_sphere & (h1["geom"].reshape(32, 40) < 2)] == 0).all()
+    assert np.allclose(np.linalg.norm(n1[..., :3], axis=-1)[h1["geom"].reshape(32, 40) >= 0], 1.0, atol=1e-5)
+    img_flat, _ = flat.render(cam, 3, 4, seed=5, aa=1, nee=1)
+    assert not (bits(img_flat) == bits(img)).all()

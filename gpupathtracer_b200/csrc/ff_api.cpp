@@ -85,6 +85,7 @@ struct ff_scene {
     float4* d_bvh2_lo = nullptr;
     float4* d_bvh2_hi = nullptr;
     uint32_t* d_leaf_slot = nullptr;
+    cudaTextureObject_t nodes_tex = 0, tris_tex = 0;  // kernel variants FF_NODE_TEX / FF_TRI_TEX only
     DevScene dev;
     ff_scene_info info;
     // render scratch (grown on demand)
@@ -101,6 +102,9 @@ struct ff_scene {
 };
 
 static void free_scene_device(ff_scene* s) {
+    if (s->nodes_tex) cudaDestroyTextureObject(s->nodes_tex);
+    if (s->tris_tex) cudaDestroyTextureObject(s->tris_tex);
+    s->nodes_tex = s->tris_tex = 0;
     cudaFree(s->d_flat); cudaFree(s->d_tris); cudaFree(s->d_nodes); cudaFree(s->d_ord_geom); cudaFree(s->d_ord_tri);
     cudaFree(s->d_materials); cudaFree(s->d_planes); cudaFree(s->d_bvh2_children); cudaFree(s->d_bvh2_lo);
     cudaFree(s->d_bvh2_hi); cudaFree(s->d_leaf_slot); cudaFree(s->d_lights); s->d_lights = nullptr;
@@ -524,7 +528,7 @@ int ff_scene_commit(ff_scene* scene, int builder, double* out_build_ms) {
         FF_CUDA(cudaMalloc((void**)&scene->d_flat, sizeof(float4) * 3 * n_tris));
         FF_CUDA(cudaMalloc((void**)&scene->d_tris, sizeof(float4) * 3 * n_tris));
         const uint32_t node_cap = (uint32_t)(n_tris / 2 + 64);
-        FF_CUDA(cudaMalloc((void**)&scene->d_nodes, sizeof(float4) * 5 * (size_t)node_cap));
+        FF_CUDA(cudaMalloc((void**)&scene->d_nodes, sizeof(float4) * FF_NODE_F4 * (size_t)node_cap));
         FF_CUDA(cudaMalloc((void**)&scene->d_bvh2_children, sizeof(int2) * std::max<size_t>(1, n_tris)));
         FF_CUDA(cudaMalloc((void**)&scene->d_bvh2_lo, sizeof(float4) * 2 * n_tris));
         FF_CUDA(cudaMalloc((void**)&scene->d_bvh2_hi, sizeof(float4) * 2 * n_tris));
@@ -569,14 +573,29 @@ int ff_scene_commit(ff_scene* scene, int builder, double* out_build_ms) {
     d.bvh2_lo = scene->d_bvh2_lo; d.bvh2_hi = scene->d_bvh2_hi; d.bvh2_leaf_slot = scene->d_leaf_slot;
     d.n_tris = (uint32_t)n_tris; d.n_nodes = bo.n_nodes; d.n_planes = (uint32_t)n_planes; d.n_geoms = (uint32_t)scene->geoms.size();
     d.wide_depth = bo.depth;
-    d.prmt_magic = 0x4B000000u;
+    d.prmt_magic = 0x3F800000u;
+    d.nodes_tex = d.tris_tex = 0;
+#if FF_NODE_TEX || FF_TRI_TEX
+    {   // linear float4 texture views for the texture-path kernel variants
+        auto make_tex = [](const void* p, size_t bytes, cudaTextureObject_t* out) -> cudaError_t {
+            cudaResourceDesc rd; memset(&rd, 0, sizeof(rd));
+            rd.resType = cudaResourceTypeLinear; rd.res.linear.devPtr = const_cast<void*>(p);
+            rd.res.linear.desc = cudaCreateChannelDesc<float4>(); rd.res.linear.sizeInBytes = bytes;
+            cudaTextureDesc td; memset(&td, 0, sizeof(td)); td.readMode = cudaReadModeElementType;
+            return cudaCreateTextureObject(out, &rd, &td, nullptr);
+        };
+        if (bo.n_nodes) FF_CUDA(make_tex(scene->d_nodes, sizeof(float4) * FF_NODE_F4 * (size_t)bo.n_nodes, &scene->nodes_tex));
+        if (n_tris) FF_CUDA(make_tex(scene->d_tris, sizeof(float4) * 3 * n_tris, &scene->tris_tex));
+        d.nodes_tex = scene->nodes_tex; d.tris_tex = scene->tris_tex;
+    }
+#endif
     d.postpone_div = (uint32_t)tuning().postpone_div; d.refill_lanes = (uint32_t)tuning().refill_lanes;
     for (int k = 0; k < 3; ++k) { d.bounds_lo[k] = blo[k]; d.bounds_hi[k] = bhi[k]; }
 
     ff_scene_info& in = scene->info;
     memset(&in, 0, sizeof(in));
     in.n_triangles = n_tris; in.n_geometries = scene->geoms.size(); in.n_planes = n_planes; in.n_nodes = bo.n_nodes;
-    in.node_bytes = 80ull * bo.n_nodes; in.triangle_bytes = 48ull * n_tris; in.depth = bo.depth; in.builder = (uint32_t)builder;
+    in.node_bytes = 16ull * FF_NODE_F4 * bo.n_nodes; in.triangle_bytes = 48ull * n_tris; in.depth = bo.depth; in.builder = (uint32_t)builder;
     for (int k = 0; k < 3; ++k) { in.bounds_lo[k] = blo[k]; in.bounds_hi[k] = bhi[k]; }
     in.build_ms = build_ms; in.sah_cost = bo.sah_cost;
     scene->committed = true;

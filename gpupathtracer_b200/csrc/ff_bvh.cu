@@ -5,7 +5,7 @@
 // geometry and every triangle) and its pointer-laden upload (kernel.cu:268-298).
 //
 // 8-wide node, 80 B = 5 x float4 (one LDG.128 each):
-//   n0 = { p.x, p.y, p.z, ex | ey<<8 | ez<<16 | imask<<24 }     p = node box min, e* = biased IEEE exponents
+//   n0 = { p.x, p.y, p.z, ex | ey<<8 | ez<<16 | imask<<24 }     p = frame origin, e* = biased IEEE exponents of 2^15 * scale
 //   n1 = { child_base, tri_base, meta[0..3], meta[4..7] }        u32 each
 //   n2 = { qlo_x[0..3], qlo_x[4..7], qlo_y[0..3], qlo_y[4..7] }  8-bit quantised child planes
 //   n3 = { qlo_z[0..3], qlo_z[4..7], qhi_x[0..3], qhi_x[4..7] }
@@ -359,9 +359,9 @@ __device__ __forceinline__ uint32_t exponent_for(float extent) {
     frexpf(extent / 255.0f, &ex);  // extent/255 = m * 2^ex, m in [0.5, 1)  =>  2^ex >= extent/255
     int eb = ex + 127;
     if (eb < 1) eb = 1;
-    if (eb > 254) eb = 254;
+    if (eb > 254 - FF_NODE_EXP_BIAS) eb = 254 - FF_NODE_EXP_BIAS;
     float sc = __uint_as_float((uint32_t)eb << 23);
-    while (sc * 255.0f < extent && eb < 254) { ++eb; sc = __uint_as_float((uint32_t)eb << 23); }
+    while (sc * 255.0f < extent && eb < 254 - FF_NODE_EXP_BIAS) { ++eb; sc = __uint_as_float((uint32_t)eb << 23); }
     return (uint32_t)eb;
 }
 __device__ __forceinline__ uint32_t quant_lo(float c, float p, float sc) {
@@ -390,7 +390,7 @@ __global__ void collapse_kernel(const uint2* __restrict__ queue_in, uint32_t n_i
 
     uint32_t ch[8];
     int nch = 0;
-    const float4 plo = box_lo[bnode], phi = box_hi[bnode];
+    float4 plo = box_lo[bnode], phi = box_hi[bnode];
     if (bnode >= n_internal || (__float_as_int(plo.w) & FF_COUNT_MASK) <= 3) {
         ch[nch++] = bnode;  // tiny scene: the whole tree is one leaf child
     } else {
@@ -457,6 +457,14 @@ __global__ void collapse_kernel(const uint2* __restrict__ queue_in, uint32_t n_i
     if (n_inner) { child_base = atomicAdd(&ctr->node_count, n_inner); q_base = atomicAdd(&ctr->queue_count, n_inner); }
     if (n_leaf_tris) tri_base = atomicAdd(&ctr->tri_count, n_leaf_tris);
 
+    // Quantisation frame: the node box pushed out by 2^-13 of its extent per side.  The traversal evaluates a plane as
+    // u*A + B with A = 2^15 * scale / d (byte_unit in ff_trace.cuh); the rounding of B moves a plane by at most 2^-16 of
+    // the extent, and floor/ceil against the wider frame keeps every child box inside its quantised box by 8x that.
+    {
+        const float gx = (phi.x - plo.x) * 0x1p-13f, gy = (phi.y - plo.y) * 0x1p-13f, gz = (phi.z - plo.z) * 0x1p-13f;
+        plo.x -= gx; plo.y -= gy; plo.z -= gz;
+        phi.x += gx; phi.y += gy; phi.z += gz;
+    }
     const uint32_t ebx = exponent_for(phi.x - plo.x), eby = exponent_for(phi.y - plo.y), ebz = exponent_for(phi.z - plo.z);
     const float sx = __uint_as_float(ebx << 23), sy = __uint_as_float(eby << 23), sz = __uint_as_float(ebz << 23);
     uint32_t meta[2] = {0, 0}, qlx[2] = {0, 0}, qly[2] = {0, 0}, qlz[2] = {0, 0}, qhx[2] = {0, 0}, qhy[2] = {0, 0}, qhz[2] = {0, 0};
@@ -489,15 +497,25 @@ __global__ void collapse_kernel(const uint2* __restrict__ queue_in, uint32_t n_i
         }
         const int w = s >> 2, sh = 8 * (s & 3);
         meta[w] |= m << sh;
-        qlx[w] |= quant_lo(l.x, plo.x, sx) << sh; qly[w] |= quant_lo(l.y, plo.y, sy) << sh; qlz[w] |= quant_lo(l.z, plo.z, sz) << sh;
-        qhx[w] |= quant_hi(h.x, plo.x, sx) << sh; qhy[w] |= quant_hi(h.y, plo.y, sy) << sh; qhz[w] |= quant_hi(h.z, plo.z, sz) << sh;
+        const float gx = (h.x - l.x) * 0x1p-13f + (phi.x - plo.x) * 0x1p-15f, gy = (h.y - l.y) * 0x1p-13f + (phi.y - plo.y) * 0x1p-15f,
+                    gz = (h.z - l.z) * 0x1p-13f + (phi.z - plo.z) * 0x1p-15f;
+        qlx[w] |= quant_lo(l.x - gx, plo.x, sx) << sh; qly[w] |= quant_lo(l.y - gy, plo.y, sy) << sh; qlz[w] |= quant_lo(l.z - gz, plo.z, sz) << sh;
+        qhx[w] |= quant_hi(h.x + gx, plo.x, sx) << sh; qhy[w] |= quant_hi(h.y + gy, plo.y, sy) << sh; qhz[w] |= quant_hi(h.z + gz, plo.z, sz) << sh;
     }
-    float4* out = nodes + 5 * (size_t)wnode;
-    out[0] = make_float4(plo.x, plo.y, plo.z, __uint_as_float(ebx | (eby << 8) | (ebz << 16) | (imask << 24)));
+    float4* out = nodes + FF_NODE_F4 * (size_t)wnode;
+    const uint32_t xb = FF_NODE_EXP_BIAS;  // the node stores the exponents of 2^15 * scale
+    out[0] = make_float4(plo.x, plo.y, plo.z, __uint_as_float((ebx + xb) | ((eby + xb) << 8) | ((ebz + xb) << 16) | (imask << 24)));
     out[1] = make_float4(__uint_as_float(child_base), __uint_as_float(tri_base), __uint_as_float(meta[0]), __uint_as_float(meta[1]));
+#if FF_NODE_256
+    out[2] = make_float4(__uint_as_float(qlx[0]), __uint_as_float(qlx[1]), __uint_as_float(qly[0]), __uint_as_float(qly[1]));
+    out[3] = make_float4(__uint_as_float(qlz[0]), __uint_as_float(qlz[1]), 0.f, 0.f);
+    out[4] = make_float4(__uint_as_float(qhx[0]), __uint_as_float(qhx[1]), __uint_as_float(qhy[0]), __uint_as_float(qhy[1]));
+    out[5] = make_float4(__uint_as_float(qhz[0]), __uint_as_float(qhz[1]), 0.f, 0.f);
+#else
     out[2] = make_float4(__uint_as_float(qlx[0]), __uint_as_float(qlx[1]), __uint_as_float(qly[0]), __uint_as_float(qly[1]));
     out[3] = make_float4(__uint_as_float(qlz[0]), __uint_as_float(qlz[1]), __uint_as_float(qhx[0]), __uint_as_float(qhx[1]));
     out[4] = make_float4(__uint_as_float(qhy[0]), __uint_as_float(qhy[1]), __uint_as_float(qhz[0]), __uint_as_float(qhz[1]));
+#endif
     // SAH cost of the wide tree: C_node * area(node) + C_tri * sum(leaf area * count), normalised by the root area
     if (root_area > 0.f) atomicAdd(&ctr->sah, ((double)box_area(plo, phi) * 1.0 + sah * 1.0) / (double)root_area);
 }

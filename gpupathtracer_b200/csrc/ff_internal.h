@@ -19,6 +19,20 @@
 #define FF_TRACE_STATIC 0x200          // OR into a trace mode: one-thread-per-ray kernel instead of the persistent one
 #define FF_POSTPONE_DIV 1000000  // postpone triangle tests when fewer than live/DIV lanes have any (off by default: dynamic fetch does better)
 
+// Kernel-variant switches (tools/probes): FF_NODE_256 = 96-byte nodes fetched with three LDG.E.256; FF_NODE_TEX / FF_TRI_TEX =
+// nodes / triangles fetched through the texture path (tex1Dfetch) instead of the LSU.
+#ifndef FF_NODE_256
+#define FF_NODE_256 0
+#endif
+#ifndef FF_NODE_TEX
+#define FF_NODE_TEX 0
+#endif
+#ifndef FF_TRI_TEX
+#define FF_TRI_TEX 0
+#endif
+#define FF_NODE_F4 (FF_NODE_256 ? 6 : 5)  // float4s per node
+#define FF_NODE_EXP_BIAS 15  // node exponents are stored as exponent(scale) + 15 (byte_unit in ff_trace.cuh)
+
 namespace ff {
 
 // ---------------------------------------------------------------- device-side scene (HBM layout)
@@ -61,9 +75,10 @@ struct DevScene {
     const float4* bvh2_lo;       // per node id (internal then leaves): box min, w unused
     const float4* bvh2_hi;
     const uint32_t* bvh2_leaf_slot;  // sorted position -> slot in tris
+    cudaTextureObject_t nodes_tex, tris_tex;   // linear float4 views of nodes / tris (kernel variants FF_NODE_TEX / FF_TRI_TEX)
     uint32_t n_tris, n_nodes, n_planes, n_geoms, n_lights;
     uint32_t wide_depth;
-    uint32_t prmt_magic;         // 0x4B000000 (2^23 as float bits), see byte_to_float in ff_trace.cuh
+    uint32_t prmt_magic;         // 0x3F800000 (1.0f as float bits), see byte_unit in ff_trace.cuh
     float pad;                   // absolute inflation applied to every leaf box (conservative culling)
     uint32_t postpone_div;       // triangle groups are postponed when fewer than live/postpone_div lanes have any
     uint32_t refill_lanes;       // persistent kernel: refill idle lanes when fewer than this many still traverse

@@ -198,7 +198,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_any_kernel(DevScene sc, 
         test_planes<true>(sc, o, draw, best);
         if (best.slot < 0) {
             if (MODE == FF_TRACE_BRUTE) {
-                for (uint32_t k = 0; k < sc.n_tris && best.slot < 0; ++k) test_slot<true>(sc.tris, (int)k, o, dn, best);
+                for (uint32_t k = 0; k < sc.n_tris && best.slot < 0; ++k) test_slot<true>(sc, (int)k, o, dn, best);
             } else if (MODE == FF_TRACE_BVH2) trace_bvh2<true, false>(sc, o, dn, best, cn, ct);
             else trace_bvh8<true, false>(sc, o, dn, best, sm_stack + threadIdx.x, FF_TRACE_BLOCK, cn, ct);
         }

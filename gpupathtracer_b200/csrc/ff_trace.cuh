@@ -31,10 +31,17 @@ __device__ __forceinline__ V3 ld3(const float4& v) { return ffm::v3(v.x, v.y, v.
 
 // One triangle slot against the ray: the reference's test + key + tie-break.
 template <bool ANY>
-__device__ __forceinline__ bool test_slot(const float4* __restrict__ tris, int slot, V3 o, V3 dn, Best& best) {
+__device__ __forceinline__ bool test_slot(const DevScene& sc, int slot, V3 o, V3 dn, Best& best) {
+#if FF_TRI_TEX
+    const float4 a = tex1Dfetch<float4>(sc.tris_tex, 3 * slot);
+    const float4 b = tex1Dfetch<float4>(sc.tris_tex, 3 * slot + 1);
+    const float4 c = tex1Dfetch<float4>(sc.tris_tex, 3 * slot + 2);
+#else
+    const float4* __restrict__ tris = sc.tris;
     const float4 a = __ldg(tris + 3 * (size_t)slot);
     const float4 b = __ldg(tris + 3 * (size_t)slot + 1);
     const float4 c = __ldg(tris + 3 * (size_t)slot + 2);
+#endif
     float t;
     if (!ffm::intersect_triangle(ld3(a), ld3(b), ld3(c), o, dn, t)) return false;
     V3 p;
@@ -138,26 +145,50 @@ __device__ __forceinline__ RayCtx make_ray_ctx(V3 o, V3 dn) {
 #define FF_SLACK 1.000030517578125f  // 1 + 2^-15: a node is culled only beyond best * FF_SLACK
 
 // Byte j of q as a float WITHOUT the int->float converter (I2F runs on the quarter-rate XU pipe, and 48 of them per
-// node saturated it: profiles/r01b): PRMT builds the bits of 2^23 + byte, one exact FADD removes the 2^23.
-// `magic` = 0x4B000000 read from the kernel parameters (DevScene::prmt_magic): as a compile-time constant it would
-// occupy PRMT's only immediate slot and push the byte selector into a register, which cost ~40 MOVs per node visit.
+// node saturated it: profiles/r01b) and without a subtraction: PRMT drops the byte into mantissa bits 8..15 of 1.0f, so
+// the result is u = 1 + byte * 2^-15 exactly, and the plane distance is ONE FMA,
+//     t = (p + byte*s - o) * id  =  u * A + B,   A = 2^15 * s * id,   B = (p - o) * id - A.
+// B carries one extra rounding of relative size 2^-24 at the magnitude of A = 128 node extents, i.e. <= 2^-16 of the
+// node extent in world units; the builder pushes the quantisation frame out by 2^-13 of the extent (collapse_kernel), so
+// culling stays conservative.  The node stores the exponent of 2^15 * s.  `magic` = 0x3F800000 read from the kernel
+// parameters (DevScene::prmt_magic): as a compile-time constant it would occupy PRMT's only immediate slot and push the
+// byte selector into a register, which cost ~40 MOVs per node visit.
 template <int J>
-__device__ __forceinline__ float byte_to_float(uint32_t q, uint32_t magic) {
-    return __uint_as_float(__byte_perm(q, magic, 0x7540u + J)) - 8388608.0f;
+__device__ __forceinline__ float byte_unit(uint32_t q, uint32_t magic) {
+    return __uint_as_float(__byte_perm(q, magic, 0x7604u + (J << 4)));
+}
+template <int J>
+__device__ __forceinline__ float plane_t(uint32_t q, uint32_t magic, float a, float b) {
+    return fmaf(byte_unit<J>(q, magic), a, b);
 }
 
 // Fetches one node (5 x LDG.128), tests its 8 quantised child boxes against the ray and returns the hit mask:
 // bits 24..31 = inner children in traversal order, bits 0..23 = triangles of the leaf children.
-__device__ __forceinline__ uint32_t bvh8_child_hits(const float4* __restrict__ nodes, uint32_t node_index, const RayCtx& r, float tlimit,
+__device__ __forceinline__ uint32_t bvh8_child_hits(const DevScene& sc, uint32_t node_index, const RayCtx& r, float tlimit,
                                                     uint32_t magic, uint32_t& child_base, uint32_t& tri_base, uint32_t& imask) {
-    const size_t ni = (size_t)node_index * 5;
+#if FF_NODE_256
+    // 96-byte node, three 32-byte loads (LDG.E.256): {n0, n1}, {qlo x,y,z + 8 spare bytes}, {qhi x,y,z + 8 spare bytes}
+    const char* np = (const char*)sc.nodes + (size_t)node_index * 96;
+    float4 n0, n1, n2, n3, n4;
+    float s0, s1, s2, s3;
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];" : "=f"(n0.x), "=f"(n0.y), "=f"(n0.z), "=f"(n0.w), "=f"(n1.x), "=f"(n1.y), "=f"(n1.z), "=f"(n1.w) : "l"(np));
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];" : "=f"(n2.x), "=f"(n2.y), "=f"(n2.z), "=f"(n2.w), "=f"(n3.x), "=f"(n3.y), "=f"(s0), "=f"(s1) : "l"(np + 32));
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];" : "=f"(n3.z), "=f"(n3.w), "=f"(n4.x), "=f"(n4.y), "=f"(n4.z), "=f"(n4.w), "=f"(s2), "=f"(s3) : "l"(np + 64));
+#elif FF_NODE_TEX
+    const int ni = (int)node_index * 5;
+    const float4 n0 = tex1Dfetch<float4>(sc.nodes_tex, ni), n1 = tex1Dfetch<float4>(sc.nodes_tex, ni + 1), n2 = tex1Dfetch<float4>(sc.nodes_tex, ni + 2),
+                 n3 = tex1Dfetch<float4>(sc.nodes_tex, ni + 3), n4 = tex1Dfetch<float4>(sc.nodes_tex, ni + 4);
+#else
+    const float4* __restrict__ nodes = sc.nodes;
+    const size_t ni = (size_t)node_index * FF_NODE_F4;
     const float4 n0 = __ldg(nodes + ni), n1 = __ldg(nodes + ni + 1), n2 = __ldg(nodes + ni + 2), n3 = __ldg(nodes + ni + 3),
                  n4 = __ldg(nodes + ni + 4);
+#endif
     const uint32_t eb = __float_as_uint(n0.w);
-    const float ax = __uint_as_float((eb & 0xffu) << 23) * r.idx;
+    const float ax = __uint_as_float((eb & 0xffu) << 23) * r.idx;   // 2^15 * scale * 1/d (exponent stored pre-biased)
     const float ay = __uint_as_float(((eb >> 8) & 0xffu) << 23) * r.idy;
     const float az = __uint_as_float(((eb >> 16) & 0xffu) << 23) * r.idz;
-    const float ox = (n0.x - r.o.x) * r.idx, oy = (n0.y - r.o.y) * r.idy, oz = (n0.z - r.o.z) * r.idz;
+    const float ox = fmaf(n0.x - r.o.x, r.idx, -ax), oy = fmaf(n0.y - r.o.y, r.idy, -ay), oz = fmaf(n0.z - r.o.z, r.idz, -az);
     child_base = __float_as_uint(n1.x);
     tri_base = __float_as_uint(n1.y);
     imask = eb >> 24;
@@ -179,12 +210,12 @@ __device__ __forceinline__ uint32_t bvh8_child_hits(const float4* __restrict__ n
         const uint32_t nearz = nz ? qhiz : qloz, farz = nz ? qloz : qhiz;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            const float tnx = fmaf(j == 0 ? byte_to_float<0>(nearx, magic) : j == 1 ? byte_to_float<1>(nearx, magic) : j == 2 ? byte_to_float<2>(nearx, magic) : byte_to_float<3>(nearx, magic), ax, ox);
-            const float tny = fmaf(j == 0 ? byte_to_float<0>(neary, magic) : j == 1 ? byte_to_float<1>(neary, magic) : j == 2 ? byte_to_float<2>(neary, magic) : byte_to_float<3>(neary, magic), ay, oy);
-            const float tnz = fmaf(j == 0 ? byte_to_float<0>(nearz, magic) : j == 1 ? byte_to_float<1>(nearz, magic) : j == 2 ? byte_to_float<2>(nearz, magic) : byte_to_float<3>(nearz, magic), az, oz);
-            const float tfx = fmaf(j == 0 ? byte_to_float<0>(farx, magic) : j == 1 ? byte_to_float<1>(farx, magic) : j == 2 ? byte_to_float<2>(farx, magic) : byte_to_float<3>(farx, magic), ax, ox);
-            const float tfy = fmaf(j == 0 ? byte_to_float<0>(fary, magic) : j == 1 ? byte_to_float<1>(fary, magic) : j == 2 ? byte_to_float<2>(fary, magic) : byte_to_float<3>(fary, magic), ay, oy);
-            const float tfz = fmaf(j == 0 ? byte_to_float<0>(farz, magic) : j == 1 ? byte_to_float<1>(farz, magic) : j == 2 ? byte_to_float<2>(farz, magic) : byte_to_float<3>(farz, magic), az, oz);
+            const float tnx = (j == 0 ? plane_t<0>(nearx, magic, ax, ox) : j == 1 ? plane_t<1>(nearx, magic, ax, ox) : j == 2 ? plane_t<2>(nearx, magic, ax, ox) : plane_t<3>(nearx, magic, ax, ox));
+            const float tny = (j == 0 ? plane_t<0>(neary, magic, ay, oy) : j == 1 ? plane_t<1>(neary, magic, ay, oy) : j == 2 ? plane_t<2>(neary, magic, ay, oy) : plane_t<3>(neary, magic, ay, oy));
+            const float tnz = (j == 0 ? plane_t<0>(nearz, magic, az, oz) : j == 1 ? plane_t<1>(nearz, magic, az, oz) : j == 2 ? plane_t<2>(nearz, magic, az, oz) : plane_t<3>(nearz, magic, az, oz));
+            const float tfx = (j == 0 ? plane_t<0>(farx, magic, ax, ox) : j == 1 ? plane_t<1>(farx, magic, ax, ox) : j == 2 ? plane_t<2>(farx, magic, ax, ox) : plane_t<3>(farx, magic, ax, ox));
+            const float tfy = (j == 0 ? plane_t<0>(fary, magic, ay, oy) : j == 1 ? plane_t<1>(fary, magic, ay, oy) : j == 2 ? plane_t<2>(fary, magic, ay, oy) : plane_t<3>(fary, magic, ay, oy));
+            const float tfz = (j == 0 ? plane_t<0>(farz, magic, az, oz) : j == 1 ? plane_t<1>(farz, magic, az, oz) : j == 2 ? plane_t<2>(farz, magic, az, oz) : plane_t<3>(farz, magic, az, oz));
             const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
             const float tf = fminf(fminf(tfx, tfy), fminf(tfz, tlimit));
             if (tn <= tf) {
@@ -239,7 +270,7 @@ __device__ __forceinline__ bool bvh8_test_one(const DevScene& sc, const RayCtx& 
     const uint32_t ti = 31u - __clz(tv.tgroup.y);
     tv.tgroup.y &= ~(1u << ti);
     if (COUNT) ++n_tris;
-    if (test_slot<ANY>(sc.tris, (int)(tv.tgroup.x + ti), r.o, r.dn, best)) {
+    if (test_slot<ANY>(sc, (int)(tv.tgroup.x + ti), r.o, r.dn, best)) {
         if (ANY) return true;
         tv.tlimit = best.key * FF_SLACK;
     }
@@ -263,7 +294,7 @@ __device__ __forceinline__ bool bvh8_step(const DevScene& sc, const RayCtx& r, T
         const uint32_t slot_index = (bit - 24u) ^ r.octinv;
         const uint32_t rel = __popc(hits_imask & ~(0xffffffffu << slot_index) & 0xffu);
         uint32_t imask, tri_base;
-        const uint32_t hitmask = bvh8_child_hits(sc.nodes, base + rel, r, tv.tlimit, sc.prmt_magic, tv.ngroup.x, tri_base, imask);
+        const uint32_t hitmask = bvh8_child_hits(sc, base + rel, r, tv.tlimit, sc.prmt_magic, tv.ngroup.x, tri_base, imask);
         if (COUNT) ++n_nodes;
         tv.ngroup.y = (hitmask & 0xff000000u) | imask;
         const uint32_t tmask = hitmask & 0x00ffffffu;
@@ -313,13 +344,13 @@ __device__ __forceinline__ void trace_bvh2(const DevScene& sc, V3 o, V3 dn, Best
     uint32_t node = 0;
     if (n_internal == 0) {
         if (COUNT) ++n_tris;
-        test_slot<ANY>(sc.tris, (int)sc.bvh2_leaf_slot[0], o, dn, best);
+        test_slot<ANY>(sc, (int)sc.bvh2_leaf_slot[0], o, dn, best);
         return;
     }
     for (;;) {
         if (node >= n_internal) {
             if (COUNT) ++n_tris;
-            if (test_slot<ANY>(sc.tris, (int)sc.bvh2_leaf_slot[node - n_internal], o, dn, best) && ANY) return;
+            if (test_slot<ANY>(sc, (int)sc.bvh2_leaf_slot[node - n_internal], o, dn, best) && ANY) return;
         } else {
             if (COUNT) ++n_nodes;
             const int2 ch = sc.bvh2_children[node];

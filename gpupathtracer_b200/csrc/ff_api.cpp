@@ -1246,6 +1246,31 @@ int ff_debug_set_tuning(int postpone_div, int refill_lanes, int blocks_per_sm) {
     if (blocks_per_sm > 0) tuning().blocks_per_sm = blocks_per_sm;
     return FF_OK;
 }
+int ff_debug_node_stats(const ff_scene* scene, unsigned long long child_hist[9], unsigned long long leaf_tri_hist[4]) {
+    FF_REQUIRE(scene && scene->committed && child_hist && leaf_tri_hist, "ff_debug_node_stats: committed scene and outputs required");
+    for (int k = 0; k < 9; ++k) child_hist[k] = 0;
+    for (int k = 0; k < 4; ++k) leaf_tri_hist[k] = 0;
+    const size_t nn = scene->dev.n_nodes;
+    if (nn == 0) return FF_OK;
+    std::vector<float4> h(nn * FF_NODE_F4);
+    FF_CUDA(cudaMemcpy(h.data(), scene->d_nodes, sizeof(float4) * h.size(), cudaMemcpyDeviceToHost));
+    for (size_t i = 0; i < nn; ++i) {
+        uint32_t meta[2];
+        memcpy(&meta[0], &h[i * FF_NODE_F4 + 1].z, 4);
+        memcpy(&meta[1], &h[i * FF_NODE_F4 + 1].w, 4);
+        int nch = 0;
+        for (int s = 0; s < 8; ++s) {
+            const uint32_t m = (meta[s >> 2] >> (8 * (s & 3))) & 0xffu;
+            if (m == 0) continue;
+            ++nch;
+            if ((m & 0xe0u) == 0x20u && (m & 0x1fu) >= 24u) continue;  // inner child
+            const uint32_t unary = m >> 5;
+            leaf_tri_hist[unary == 1 ? 1 : unary == 3 ? 2 : 3]++;
+        }
+        child_hist[nch]++;
+    }
+    return FF_OK;
+}
 int ff_write_image(const char* path, const float* rgba, int width, int height) { return write_image_float(path, rgba, width, height); }
 int ff_write_image_u8(const char* path, const unsigned char* rgb, int width, int height) { return write_image_u8(path, rgb, width, height); }
 void ff_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) {

@@ -283,17 +283,28 @@ __global__ void hierarchy_kernel(const uint32_t* __restrict__ keys, int n, int2*
 }
 
 #define FF_COUNT_MASK 0x3fffffff
-#define FF_PREFER_OPEN 0x40000000
-#define FF_SLOT_COST 0.25f   // cost of one more child slot (box test + share of the node fetch) in triangle tests
+#define FF_SLOT_COST 0.25f   // cost of one hit child (mask assembly, queueing), in triangle tests
+#define FF_NODE_COST 1.5f    // cost of one wide-node visit (fetch + 8 box tests) in triangle tests (~240 vs ~150 instructions)
 __device__ __forceinline__ float box_area_lohi(const float4& lo, const float4& hi) {
     const float dx = hi.x - lo.x, dy = hi.y - lo.y, dz = hi.z - lo.z;
     return 2.0f * (dx * dy + dy * dz + dz * dx);
 }
-// ------------------------------------------------------------------ bottom-up refit
+// ------------------------------------------------------------------ bottom-up refit + collapse DP
 // lo.w = triangle count (int bits), hi.w = first sorted position (int bits)
+//
+// The same pass runs the dynamic programme that decides how the binary tree is cut into 8-wide nodes (after Ylitie,
+// Karras & Laine 2017, section 3.1, with this kernel's costs).  For a binary node v and a budget of j parent slots,
+//     F(v, j) = cheapest way to hang the subtree of v under a wide node using at most j of its child slots
+//     F(v, 1) = area(v) * (slot + count(v))                 count(v) <= 3: one leaf child
+//             = area(v) * (slot + node) + min_k F(l, k) + F(r, 8 - k)       otherwise: one inner child, a wide node of its own
+//     F(v, j) = min( F(v, 1), min_k F(l, k) + F(r, j - k) )                 j = 2..7
+// in units of one triangle test.  dp[2v] = {F1..F4}, dp[2v+1] = {F5, F6, F7, decisions}: decisions bits 3(j-2).. = the
+// left child's share k for budget j (0 = take a single slot), bits 21.. = k of the node's own 8 slots.  The greedy
+// "open the largest child" collapse this replaces left 40 % of C2's nodes with two children (profiles/r01g_node_stats).
 __global__ void refit_kernel(const float4* __restrict__ flat_tris, const uint32_t* __restrict__ sorted_idx, int n, float pad,
                              const int2* __restrict__ children, const uint32_t* __restrict__ parent, uint32_t* __restrict__ flags,
-                             float4* __restrict__ box_lo, float4* __restrict__ box_hi, float* __restrict__ cost, float slot_cost) {
+                             float4* __restrict__ box_lo, float4* __restrict__ box_hi, float4* __restrict__ dp, float slot_cost,
+                             float node_cost) {
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
         const uint32_t src = sorted_idx[k];
         const float4 a = flat_tris[3 * (size_t)src], b = flat_tris[3 * (size_t)src + 1], c = flat_tris[3 * (size_t)src + 2];
@@ -302,7 +313,9 @@ __global__ void refit_kernel(const float4* __restrict__ flat_tris, const uint32_
         uint32_t node = (uint32_t)(n - 1 + k);
         box_lo[node] = lo;
         box_hi[node] = hi;
-        cost[node] = box_area_lohi(lo, hi) * (slot_cost + 1.0f);
+        const float f1 = box_area_lohi(lo, hi) * (slot_cost + 1.0f);
+        dp[2 * (size_t)node] = make_float4(f1, f1, f1, f1);
+        dp[2 * (size_t)node + 1] = make_float4(f1, f1, f1, 0.f);
         if (n == 1) return;
         for (;;) {
             const uint32_t p = parent[node];
@@ -321,18 +334,36 @@ __global__ void refit_kernel(const float4* __restrict__ flat_tris, const uint32_
             const int cnt = (__float_as_int(l0.w) & FF_COUNT_MASK) + (__float_as_int(l1.w) & FF_COUNT_MASK);
             lo = make_float4(fminf(l0.x, l1.x), fminf(l0.y, l1.y), fminf(l0.z, l1.z), 0.f);
             hi = make_float4(fmaxf(h0.x, h1.x), fmaxf(h0.y, h1.y), fmaxf(h0.z, h1.z), h0.w);
-            // leaf-or-open decision by expected cost: a <=3-triangle subtree becomes ONE leaf child only when
-            // testing all its triangles under the merged box is cheaper than keeping the children apart
-            const volatile float* vc = cost;
-            const float split = vc[ch.x] + vc[ch.y];
-            int flag = 0;
-            float best = split;
-            if (cnt <= 3) {
-                const float leaf = box_area_lohi(lo, hi) * (slot_cost + (float)cnt);
-                if (split < leaf) flag = FF_PREFER_OPEN; else best = leaf;
+            // F(left, 1..7), F(right, 1..7)
+            const volatile float4* vdp = dp;
+            float fl[8], fr[8];
+            fl[1] = vdp[2 * (size_t)ch.x].x; fl[2] = vdp[2 * (size_t)ch.x].y; fl[3] = vdp[2 * (size_t)ch.x].z; fl[4] = vdp[2 * (size_t)ch.x].w;
+            fl[5] = vdp[2 * (size_t)ch.x + 1].x; fl[6] = vdp[2 * (size_t)ch.x + 1].y; fl[7] = vdp[2 * (size_t)ch.x + 1].z;
+            fr[1] = vdp[2 * (size_t)ch.y].x; fr[2] = vdp[2 * (size_t)ch.y].y; fr[3] = vdp[2 * (size_t)ch.y].z; fr[4] = vdp[2 * (size_t)ch.y].w;
+            fr[5] = vdp[2 * (size_t)ch.y + 1].x; fr[6] = vdp[2 * (size_t)ch.y + 1].y; fr[7] = vdp[2 * (size_t)ch.y + 1].z;
+            const float area = box_area_lohi(lo, hi);
+            float f[8];
+            uint32_t dec = 0;
+            {
+                float g = FLT_MAX;
+                uint32_t k8 = 1;
+#pragma unroll
+                for (int q = 1; q <= 7; ++q) { const float v = fl[q] + fr[8 - q]; if (v < g) { g = v; k8 = (uint32_t)q; } }
+                dec |= k8 << 21;
+                f[1] = (cnt <= 3) ? area * (slot_cost + (float)cnt) : area * (slot_cost + node_cost) + g;
             }
-            cost[p] = best;
-            lo.w = __int_as_float(cnt | flag);
+#pragma unroll
+            for (int j = 2; j <= 7; ++j) {
+                float g = f[1];
+                uint32_t kj = 0;
+#pragma unroll
+                for (int q = 1; q < j; ++q) { const float v = fl[q] + fr[j - q]; if (v < g) { g = v; kj = (uint32_t)q; } }
+                f[j] = g;
+                dec |= kj << (3 * (j - 2));
+            }
+            dp[2 * (size_t)p] = make_float4(f[1], f[2], f[3], f[4]);
+            dp[2 * (size_t)p + 1] = make_float4(f[5], f[6], f[7], __uint_as_float(dec));
+            lo.w = __int_as_float(cnt);
             box_lo[p] = lo;
             box_hi[p] = hi;
             node = p;
@@ -382,7 +413,7 @@ __global__ void collapse_kernel(const uint2* __restrict__ queue_in, uint32_t n_i
                                 const int2* __restrict__ children, const float4* __restrict__ box_lo, const float4* __restrict__ box_hi,
                                 const float4* __restrict__ flat_tris, const uint32_t* __restrict__ sorted_idx,
                                 float4* __restrict__ nodes, float4* __restrict__ tris_out, uint32_t* __restrict__ leaf_slot,
-                                CollapseCounters* ctr, float root_area) {
+                                CollapseCounters* ctr, float root_area, const float4* __restrict__ dp) {
     const uint32_t qi = blockIdx.x * blockDim.x + threadIdx.x;
     if (qi >= n_in) return;
     const uint32_t bnode = queue_in[qi].x, wnode = queue_in[qi].y;
@@ -394,23 +425,23 @@ __global__ void collapse_kernel(const uint2* __restrict__ queue_in, uint32_t n_i
     if (bnode >= n_internal || (__float_as_int(plo.w) & FF_COUNT_MASK) <= 3) {
         ch[nch++] = bnode;  // tiny scene: the whole tree is one leaf child
     } else {
-        ch[0] = (uint32_t)children[bnode].x;
-        ch[1] = (uint32_t)children[bnode].y;
-        nch = 2;
-        while (nch < 8) {
-            int pick = -1;
-            float best = -1.f;
-            for (int k = 0; k < nch; ++k) {
-                const int cw = __float_as_int(box_lo[ch[k]].w);
-                if (ch[k] < n_internal && ((cw & FF_COUNT_MASK) > 3 || (cw & FF_PREFER_OPEN))) {
-                    const float a = box_area(box_lo[ch[k]], box_hi[ch[k]]);
-                    if (a > best) { best = a; pick = k; }
-                }
-            }
-            if (pick < 0) break;
-            const int2 c2 = children[ch[pick]];
-            ch[pick] = (uint32_t)c2.x;
-            ch[nch++] = (uint32_t)c2.y;
+        // follow the decisions of the refit DP: (binary node, slot budget) pairs, at most 8 slots in flight
+        uint32_t st_node[8];
+        uint32_t st_bud[8];
+        int sp = 0;
+        {
+            const uint32_t k8 = (__float_as_uint(dp[2 * (size_t)bnode + 1].w) >> 21) & 7u;
+            st_node[sp] = (uint32_t)children[bnode].y; st_bud[sp++] = 8u - k8;
+            st_node[sp] = (uint32_t)children[bnode].x; st_bud[sp++] = k8;
+        }
+        while (sp > 0 && nch < 8) {
+            const uint32_t m = st_node[--sp], j = st_bud[sp];
+            uint32_t d = 0;
+            if (m < n_internal && j >= 2u) d = (__float_as_uint(dp[2 * (size_t)m + 1].w) >> (3u * (j - 2u))) & 7u;
+            if (d == 0u || d >= j || sp + 2 > 8) { ch[nch++] = m; continue; }   // one slot: a leaf (<= 3 triangles) or an inner child
+            const int2 c2 = children[m];
+            st_node[sp] = (uint32_t)c2.y; st_bud[sp++] = j - d;
+            st_node[sp] = (uint32_t)c2.x; st_bud[sp++] = d;
         }
     }
 
@@ -548,12 +579,12 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
     int* d_bounds = nullptr;
     uint32_t *d_keys_a = nullptr, *d_keys_b = nullptr, *d_vals_a = nullptr, *d_vals_b = nullptr, *d_hist = nullptr;
     uint32_t *d_parent = nullptr, *d_flags = nullptr;
-    float* d_cost = nullptr;
+    float4* d_dp = nullptr;
     uint2 *d_q0 = nullptr, *d_q1 = nullptr;
     CollapseCounters* d_ctr = nullptr;
     {
         size_t need = Arena::padded(12 * sizeof(int)) + 4 * Arena::padded(sizeof(uint32_t) * n) + Arena::padded(sizeof(uint32_t) * 256 * (size_t)n_tiles) +
-                      Arena::padded(sizeof(uint32_t) * 2 * (size_t)n) + Arena::padded(sizeof(uint32_t) * n) + Arena::padded(sizeof(float) * 2 * (size_t)n) +
+                      Arena::padded(sizeof(uint32_t) * 2 * (size_t)n) + Arena::padded(sizeof(uint32_t) * n) + Arena::padded(sizeof(float4) * 4 * (size_t)n) +
                       2 * Arena::padded(sizeof(uint2) * (size_t)node_capacity) + Arena::padded(sizeof(CollapseCounters));
         if (builder == FF_BUILDER_SAH) need += sah_scratch_bytes(n);
         CK(arena.reserve(need));
@@ -564,7 +595,7 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
     d_hist = arena.take<uint32_t>(256 * (size_t)n_tiles);
     d_parent = arena.take<uint32_t>(2 * (size_t)n);
     d_flags = arena.take<uint32_t>(n);
-    d_cost = arena.take<float>(2 * (size_t)n);
+    d_dp = arena.take<float4>(4 * (size_t)n);
     d_q0 = arena.take<uint2>(node_capacity); d_q1 = arena.take<uint2>(node_capacity);
     d_ctr = arena.take<CollapseCounters>(1);
     if (!d_ctr) return cudaErrorMemoryAllocation;
@@ -596,10 +627,12 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
     }
     const char* sc_env = getenv("FF_SLOT_COST");  // development knob: leaf-or-open trade-off of the refit DP
     const float slot_cost = sc_env ? (float)atof(sc_env) : FF_SLOT_COST;
+    const char* nc_env = getenv("FF_NODE_COST");
+    const float node_cost = nc_env ? (float)atof(nc_env) : FF_NODE_COST;
     refit_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(d_flat_tris, d_order, (int)n, pad, d_bvh2_children, d_parent, d_flags,
-                                                            d_bvh2_lo, d_bvh2_hi, d_cost, slot_cost);
+                                                            d_bvh2_lo, d_bvh2_hi, d_dp, slot_cost, node_cost);
     ++*launches;
-    mark("refit + leaf/open DP");
+    mark("refit + collapse DP");
 
     float4 root_lo, root_hi;
     const uint32_t root = (n == 1) ? 0u : 0u;  // internal node 0, or the single leaf (id n-1+0 = 0)
@@ -622,7 +655,7 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
         ++depth;
         collapse_kernel<<<grid_for(n_in, 128, 1 << 30), 128, 0, st>>>(qin, n_in, qout, (int)n, d_bvh2_children, d_bvh2_lo, d_bvh2_hi,
                                                                      d_flat_tris, d_order, d_nodes_out, d_tris_out, d_bvh2_leaf_slot,
-                                                                     d_ctr, root_area);
+                                                                     d_ctr, root_area, d_dp);
         ++*launches;
         CK(cudaMemcpyAsync(&h_ctr, d_ctr, sizeof(h_ctr), cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));

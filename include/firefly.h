@@ -275,6 +275,9 @@ int ff_write_image_u8(const char* path, const unsigned char* rgb, int width, int
 
 /* -- development knobs of the traversal scheduler (take effect at the next ff_scene_commit); <= 0 keeps a value. */
 int ff_debug_set_tuning(int postpone_div, int refill_lanes, int blocks_per_sm);
+/* -- development statistics of the committed 8-wide hierarchy: child_hist[k] = nodes with k children (k = 0..8),
+ *    leaf_tri_hist[k] = leaf children holding k triangles (k = 1..3). */
+int ff_debug_node_stats(const ff_scene* scene, unsigned long long child_hist[9], unsigned long long leaf_tri_hist[4]);
 
 /* -- Philox4x32-10 on the host (the generator all kernels use), for cross-checks. */
 void ff_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]);

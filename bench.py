@@ -181,7 +181,7 @@ def run_gpu_arm(args):
     ctx = ff.Context(local_rank)
     meshes = S.load_meshes()
     desc = S.config2(meshes, W, H, SPP, BOUNCES)
-    sc, cam = S.instantiate(desc, ctx, meshes)
+    sc, cam = S.instantiate(desc, ctx, meshes, builder=args.builder)
     info = sc.info()
     npix = W * H
     sc_spb = max(1, (4 << 20) // npix)  # samples per wavefront pass the library picks for this image (ff_api.cpp accumulate_samples)
@@ -294,7 +294,7 @@ def run_gpu_arm(args):
             metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=max(3, args.warmup),
             ms_per_step=1e3 * secs / steps, higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32", data="synthetic",
             config=dict(workload=WORKLOAD, image=[W, H], spp_per_gpu=SPP, total_spp=total_spp, max_bounces=BOUNCES, triangles=info["n_triangles"],
-                        bvh_nodes=info["n_nodes"], build_ms=info["build_ms"], parallelism="sample-split x%d, 1 framebuffer reduce (%s)" % (world, args.reduce),
+                        bvh_nodes=info["n_nodes"], builder=("lbvh", "binned-sah")[args.builder], build_ms=info["build_ms"], parallelism="sample-split x%d, 1 framebuffer reduce (%s)" % (world, args.reduce),
                         l2="flushed with a 256 MiB write between timed steps"),
             samples_per_sec_per_gpu=SPP * npix * steps / secs,
             rays_per_step=rays / steps, device_ms_per_step=gpu_ms / steps, trace_ms_per_step=trace_ms / steps,
@@ -328,6 +328,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="firefly_b200", choices=["firefly_b200", "reference"])
     ap.add_argument("--reduce", default="nccl", choices=["nccl", "peer"])
+    ap.add_argument("--builder", type=int, default=1, choices=[0, 1], help="0 = LBVH, 1 = binned SAH (build time is reported in config.build_ms, outside the timed region)")
     args = ap.parse_args()
     claim_stdout()
     if args.impl == "reference":

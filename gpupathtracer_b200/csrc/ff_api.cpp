@@ -589,7 +589,11 @@ int ff_scene_commit(ff_scene* scene, int builder, double* out_build_ms) {
         d.nodes_tex = scene->nodes_tex; d.tris_tex = scene->tris_tex;
     }
 #endif
-    d.postpone_div = (uint32_t)tuning().postpone_div; d.refill_lanes = (uint32_t)tuning().refill_lanes;
+    d.postpone_div = (uint32_t)tuning().postpone_div;
+    // refill threshold of the persistent kernels: short rays (small hierarchies: C2 visits 5 nodes per ray) finish so often
+    // that refilling at 28 live lanes spends 10 % of the issue slots in the fetch path at 11 active lanes; measured optimum
+    // 16-20 lanes on C2 (+4 %), 28 on the 1M-triangle soup (profiles/r01g_tune_refill.txt).  ff_debug_set_tuning overrides.
+    d.refill_lanes = tuning().refill_lanes > 0 ? (uint32_t)tuning().refill_lanes : (bo.n_nodes <= 4096u ? 20u : 28u);
     for (int k = 0; k < 3; ++k) { d.bounds_lo[k] = blo[k]; d.bounds_hi[k] = bhi[k]; }
 
     ff_scene_info& in = scene->info;

@@ -8,7 +8,7 @@ namespace ff {
 using namespace ffm;
 
 Tuning& tuning() {
-    static Tuning t = {FF_POSTPONE_DIV, FF_REFILL_LANES, FF_PERSISTENT_BLOCKS_PER_SM};
+    static Tuning t = {FF_POSTPONE_DIV, 0 /* refill_lanes: chosen per scene at commit */, FF_PERSISTENT_BLOCKS_PER_SM};
     return t;
 }
 

@@ -18,6 +18,7 @@ if not os.path.exists(LIB_PATH):
                       "there is no fallback implementation" % LIB_PATH)
 lib = C.CDLL(LIB_PATH)
 
+CAM_FORWARD, CAM_BACKWARD, CAM_LEFT, CAM_RIGHT, CAM_UP, CAM_DOWN, CAM_YAW_LEFT, CAM_YAW_RIGHT, CAM_PITCH_UP, CAM_PITCH_DOWN, CAM_RESET = range(11)
 INTEGRATOR_WAVEFRONT, INTEGRATOR_MEGAKERNEL, INTEGRATOR_AS_CODED = 0, 1, 2
 AOV_NORMAL, AOV_UV, AOV_BARY, AOV_ALBEDO = 3, 4, 5, 6  # primary-ray feature buffers through render(integrator=...)
 OBJ_FLIP_WINDING, OBJ_NORMALS, OBJ_UVS, OBJ_MATERIALS = 1, 2, 4, 8
@@ -135,6 +136,15 @@ lib.ff_flush_l2.argtypes = [_vp]
 lib.ff_write_image.argtypes = [C.c_char_p, _vp, C.c_int, C.c_int]
 lib.ff_write_image_u8.argtypes = [C.c_char_p, _vp, C.c_int, C.c_int]
 lib.ff_philox4x32_10.argtypes = [_vp, _vp, _vp]
+lib.ff_camera_process_keyboard.argtypes = [C.POINTER(CCamera), C.c_int]
+lib.ff_camera_process_mouse.argtypes = [C.POINTER(CCamera), C.c_float, C.c_float, C.c_int]
+lib.ff_progressive_create.argtypes = [_vp, C.POINTER(_vp)]
+lib.ff_progressive_destroy.argtypes = [_vp]
+lib.ff_progressive_destroy.restype = None
+lib.ff_progressive_reset.argtypes = [_vp]
+lib.ff_progressive_frame.argtypes = [_vp, C.POINTER(CCamera), C.POINTER(CRenderParams), _vp, _vp, _vp, C.c_int, C.POINTER(C.c_int),
+                                     C.POINTER(CStats)]
+lib.ff_debug_node_stats.argtypes = [_vp, _vp, _vp]
 lib.ff_philox4x32_10.restype = None
 lib.ff_context_destroy.restype = None
 lib.ff_scene_destroy.restype = None
@@ -248,6 +258,19 @@ class Camera:
         iv, ip = np.zeros(16, np.float32), np.zeros(16, np.float32)
         _check(lib.ff_camera_inverse_matrices(C.byref(self.c), _p(iv), _p(ip)))
         return iv, ip
+
+    # Camera::ProcessKeyboard / ProcessMouseMovement (utilities.h:343-404): direction = CAM_* (the reference's codes)
+    def process_keyboard(self, direction):
+        _check(lib.ff_camera_process_keyboard(C.byref(self.c), int(direction)))
+        return self
+
+    def process_mouse(self, x_delta, y_delta, constrain_pitch=True):
+        _check(lib.ff_camera_process_mouse(C.byref(self.c), float(x_delta), float(y_delta), int(bool(constrain_pitch))))
+        return self
+
+    def state(self):
+        """(pos xyz, yaw, pitch) as float32, the part of the camera the controls change."""
+        return np.array([*self.c.pos, self.c.yaw_deg, self.c.pitch_deg], np.float32)
 
 
 def render_params(spp=1, max_bounces=4, seed=1234, integrator=INTEGRATOR_WAVEFRONT, nee=0, first_sample=0, aa=0,
@@ -546,6 +569,46 @@ class Scene:
         ptr = d_accum.ptr if isinstance(d_accum, DeviceBuffer) else C.c_void_p(int(d_accum))
         _check(lib.ff_render_accumulate(self.h, C.byref(cam.c), C.byref(p), ptr, C.byref(st)))
         return st.as_dict()
+
+
+class Progressive:
+    """ff_progressive: accumulation across frames that restarts when the camera or an image-changing parameter moves
+    (the state the viewer loop, kernel.cu:331-359, carries once the tracer accumulates).  Close it before its scene."""
+
+    def __init__(self, scene):
+        self.scene = scene
+        self.h = C.c_void_p()
+        _check(lib.ff_progressive_create(scene.h, C.byref(self.h)))
+
+    def close(self):
+        if self.h:
+            lib.ff_progressive_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def reset(self):
+        _check(lib.ff_progressive_reset(self.h))
+
+    def frame(self, cam, spp=1, max_bounces=4, want_u8=False, want_stats=False, **kw):
+        """Adds `spp` samples; returns (float RGBA mean so far, total spp[, 8-bit RGB][, stats])."""
+        p = render_params(spp, max_bounces, **kw)
+        out = np.empty((cam.height, cam.width, 4), np.float32)
+        u8 = np.empty((cam.height, cam.width, 3), np.uint8) if want_u8 else None
+        total = C.c_int(0)
+        st = CStats()
+        _check(lib.ff_progressive_frame(self.h, C.byref(cam.c), C.byref(p), _p(out), None, _p(u8) if want_u8 else None, 0,
+                                        C.byref(total), C.byref(st)))
+        r = [out, total.value]
+        if want_u8:
+            r.append(u8)
+        if want_stats:
+            r.append(st.as_dict())
+        return tuple(r)
 
 
 def validate_scene_file(path):

@@ -917,8 +917,10 @@ int accumulate_samples(ff_scene* scene, const ff_camera* cam, const ff_render_pa
     ff_context* c = scene->ctx;
     cudaStream_t st = c->stream;
     const size_t npix = (size_t)cam->width * cam->height;
-    // samples per pass: fill the machine (>= ~2M paths in flight) without exceeding ~16M paths of state
-    size_t spb = p->samples_per_pass > 0 ? (size_t)p->samples_per_pass : std::max<size_t>(1, (4u << 20) / npix);
+    // samples per pass: ~16M paths in flight.  Late bounces of a pass carry few rays (C3: 8 bounces, most paths escape
+    // early), and a persistent kernel over a short queue is all tail: C3 wavefront 19.3 ms at 4M paths per pass, 12.7 ms at
+    // 32M; C2 is flat from 4M to 32M (profiles/r01g_pass_size.txt).  State is ~150 B per path.
+    size_t spb = p->samples_per_pass > 0 ? (size_t)p->samples_per_pass : std::max<size_t>(1, (16u << 20) / npix);
     spb = std::min<size_t>(spb, (size_t)p->spp);
     while (spb > 1 && spb * npix > (32u << 20)) --spb;
     FF_REQUIRE(spb * npix < 0xffffffffull, "render: too many paths per pass");
@@ -1241,6 +1243,128 @@ int ff_flush_l2(ff_context* ctx) {
     }
     k_flush(ctx->flush_buf, ctx->flush_n, ctx->stream);
     FF_CUDA(cudaStreamSynchronize(ctx->stream));
+    return FF_OK;
+}
+
+// ---------------------------------------------------------------- camera controls (utilities.h:343-427)
+int ff_camera_process_keyboard(ff_camera* cam, int direction) {
+    FF_REQUIRE(cam, "ff_camera_process_keyboard: NULL camera");
+    FF_REQUIRE(direction >= 0 && direction <= FF_CAM_RESET, "ff_camera_process_keyboard: direction must be 0..10");
+    const float velocity = 0.2f;  // m_cameraMouseSensitivity (utilities.h:288,345)
+    V3 f, r, u;
+    ffh::camera_basis(cam->world_up, cam->yaw_deg, cam->pitch_deg, f, r, u);
+    auto move = [&](const V3& axis, bool plus) {   // m_position +/-= axis * velocity: one rounded multiply, one rounded add
+        const V3 step = ffm::mul(axis, velocity);
+        const V3 p = ffm::v3(cam->pos[0], cam->pos[1], cam->pos[2]);
+        const V3 q = plus ? ffm::add(p, step) : ffm::sub(p, step);
+        cam->pos[0] = q.x; cam->pos[1] = q.y; cam->pos[2] = q.z;
+    };
+    switch (direction) {
+        case FF_CAM_FORWARD: move(f, true); break;
+        case FF_CAM_BACKWARD: move(f, false); break;
+        case FF_CAM_LEFT: move(r, false); break;
+        case FF_CAM_RIGHT: move(r, true); break;
+        case FF_CAM_UP: move(u, true); break;
+        case FF_CAM_DOWN: move(u, false); break;
+        case FF_CAM_YAW_LEFT: cam->yaw_deg = ffm::fsub(cam->yaw_deg, 0.5f); break;
+        case FF_CAM_YAW_RIGHT: cam->yaw_deg = ffm::fadd(cam->yaw_deg, 0.5f); break;
+        case FF_CAM_PITCH_UP: cam->pitch_deg = ffm::fadd(cam->pitch_deg, 0.5f); break;
+        case FF_CAM_PITCH_DOWN: cam->pitch_deg = ffm::fsub(cam->pitch_deg, 0.5f); break;
+        default:  // resetCamera (utilities.h:420-426)
+            cam->pos[0] = 0.f; cam->pos[1] = 0.f; cam->pos[2] = 15.f; cam->pitch_deg = 0.f; cam->yaw_deg = -90.f;
+            break;
+    }
+    return FF_OK;
+}
+int ff_camera_process_mouse(ff_camera* cam, float x_delta, float y_delta, int constrain_pitch) {
+    FF_REQUIRE(cam, "ff_camera_process_mouse: NULL camera");
+    const float sens = 0.2f;  // m_cameraMouseSensitivity
+    cam->yaw_deg = ffm::fadd(cam->yaw_deg, ffm::fmul(x_delta, sens));
+    cam->pitch_deg = ffm::fadd(cam->pitch_deg, ffm::fmul(y_delta, sens));
+    if (constrain_pitch) {
+        if (cam->pitch_deg > 89.0f) cam->pitch_deg = 89.0f;
+        if (cam->pitch_deg < -89.0f) cam->pitch_deg = -89.0f;
+    }
+    return FF_OK;
+}
+
+// ---------------------------------------------------------------- progressive accumulation (viewer loop state, kernel.cu:331-359)
+struct ff_progressive {
+    ff_scene* scene = nullptr;
+    float4* d_accum = nullptr;
+    float4* d_out = nullptr;
+    unsigned char* d_u8 = nullptr;
+    size_t pixels = 0;
+    int accumulated = 0;
+    bool valid = false;
+    ff_camera cam;
+    ff_render_params params;
+};
+int ff_progressive_create(ff_scene* scene, ff_progressive** out) {
+    FF_REQUIRE(scene && out, "ff_progressive_create: NULL argument");
+    *out = new ff_progressive();
+    (*out)->scene = scene;
+    return FF_OK;
+}
+void ff_progressive_destroy(ff_progressive* p) {
+    if (!p) return;
+    if (p->scene && p->scene->ctx) cudaSetDevice(p->scene->ctx->device);
+    cudaFree(p->d_accum); cudaFree(p->d_out); cudaFree(p->d_u8);
+    delete p;
+}
+int ff_progressive_reset(ff_progressive* p) {
+    FF_REQUIRE(p, "ff_progressive_reset: NULL session");
+    p->valid = false; p->accumulated = 0;
+    return FF_OK;
+}
+int ff_progressive_frame(ff_progressive* p, const ff_camera* cam, const ff_render_params* params, float* out_rgba_host,
+                         void* out_rgba_device, unsigned char* out_rgb_u8, int u8_is_device, int* out_total_spp, ff_stats* stats) {
+    FF_REQUIRE(p, "ff_progressive_frame: NULL session");
+    int rc = check_scene(p->scene, "ff_progressive_frame");
+    if (rc) return rc;
+    if ((rc = check_cam(cam, "ff_progressive_frame"))) return rc;
+    if ((rc = check_params(params, "ff_progressive_frame"))) return rc;
+    if (stats) memset(stats, 0, sizeof(*stats));
+    ff_context* c = p->scene->ctx;
+    FF_CUDA(cudaSetDevice(c->device));
+    const size_t npix = (size_t)cam->width * cam->height;
+    if (p->pixels != npix) {
+        cudaFree(p->d_accum); cudaFree(p->d_out); cudaFree(p->d_u8);
+        p->d_accum = p->d_out = nullptr; p->d_u8 = nullptr; p->pixels = 0; p->valid = false;
+        FF_CUDA(cudaMalloc((void**)&p->d_accum, sizeof(float4) * npix));
+        FF_CUDA(cudaMalloc((void**)&p->d_out, sizeof(float4) * npix));
+        FF_CUDA(cudaMalloc((void**)&p->d_u8, npix * 3));
+        p->pixels = npix;
+    }
+    auto same_image = [&]() {
+        const ff_render_params& a = p->params;
+        return memcmp(&p->cam, cam, sizeof(ff_camera)) == 0 && a.max_bounces == params->max_bounces && a.seed == params->seed &&
+               (a.integrator & 0xff) == (params->integrator & 0xff) && a.nee == params->nee && a.aa == params->aa &&
+               memcmp(a.background, params->background, sizeof(a.background)) == 0 && a.ray_eps == params->ray_eps;
+    };
+    if (!p->valid || !same_image() || (long long)p->accumulated + params->spp > 0x7fffffffll) {
+        FF_CUDA(cudaMemsetAsync(p->d_accum, 0, sizeof(float4) * npix, c->stream));
+        p->accumulated = 0;
+        p->cam = *cam; p->params = *params; p->valid = true;
+    }
+    ff_render_params q = *params;
+    q.first_sample = p->accumulated;   // the Philox stream continues where the previous frame stopped
+    if ((rc = accumulate_samples(p->scene, cam, &q, p->d_accum, stats))) { p->valid = false; return rc; }
+    p->accumulated += params->spp;
+    float4* d_out = out_rgba_device ? (float4*)out_rgba_device : p->d_out;
+    const float4* one[1] = {p->d_accum};
+    ScopedTimer t(c, 2, 3);
+    k_resolve(one, 1, (uint32_t)npix, 1.0f / (float)p->accumulated, d_out, c->stream);
+    if (out_rgb_u8) {
+        unsigned char* d8 = u8_is_device ? out_rgb_u8 : p->d_u8;
+        k_rgba_to_u8(d_out, (uint32_t)npix, d8, c->stream);
+        if (!u8_is_device) FF_CUDA(cudaMemcpyAsync(out_rgb_u8, d8, npix * 3, cudaMemcpyDeviceToHost, c->stream));
+    }
+    if (out_rgba_host) FF_CUDA(cudaMemcpyAsync(out_rgba_host, d_out, sizeof(float4) * npix, cudaMemcpyDeviceToHost, c->stream));
+    const double ms = t.stop();
+    FF_CUDA(cudaGetLastError());
+    if (stats) { stats->gpu_ms += ms; stats->d2h_ms = (out_rgba_host || (out_rgb_u8 && !u8_is_device)) ? ms : 0; stats->kernel_launches += out_rgb_u8 ? 2 : 1; }
+    if (out_total_spp) *out_total_spp = p->accumulated;
     return FF_OK;
 }
 

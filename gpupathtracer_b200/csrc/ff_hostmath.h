@@ -138,9 +138,14 @@ inline M4 perspective_fov_rh_no(float fov, float width, float height, float z_ne
 // Camera::UpdateBasisAxis, utilities.h:407-418
 inline void camera_basis(const float world_up[3], float yaw_deg, float pitch_deg, V3& forward, V3& right, V3& up) {
     V3 front;
-    front.x = std::cos(to_radians(yaw_deg)) * std::cos(to_radians(pitch_deg));
-    front.y = std::sin(to_radians(pitch_deg));
-    front.z = std::sin(to_radians(yaw_deg)) * std::cos(to_radians(pitch_deg));
+    // The reference writes unqualified cos / sin on floats at global scope (utilities.h:411-413).  Re-hosted with g++ (the
+    // pin: oracle/_ref), those are the C library's double functions: float arguments are widened, the PRODUCT is formed in
+    // double and rounded to float once.  std::cos(float) * std::cos(float) differs from that in the last bit for about one
+    // direction in five (tests/golden/ref_camera_walk.npz).
+    const double ry = (double)to_radians(yaw_deg), rp = (double)to_radians(pitch_deg);
+    front.x = (float)(::cos(ry) * ::cos(rp));
+    front.y = (float)::sin(rp);
+    front.z = (float)(::sin(ry) * ::cos(rp));
     forward = ffm::normalize(front);
     right = ffm::normalize(ffm::cross(forward, ffm::v3(world_up[0], world_up[1], world_up[2])));
     up = ffm::normalize(ffm::cross(right, forward));

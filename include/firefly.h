@@ -268,6 +268,30 @@ typedef struct ff_scene_file {
 int ff_scene_load_file(ff_context* ctx, const char* path, const char* asset_dir, ff_scene** out_scene, ff_scene_file* out_desc);
 int ff_scene_file_validate(const char* path, ff_scene_file* out_desc);
 
+/* -- camera controls: Camera::ProcessKeyboard / ProcessMouseMovement / resetCamera (utilities.h:343-427) applied to an
+ *    ff_camera, so a front end without the GLFW callbacks (utilities.h:858-893) moves the camera exactly like the viewer.
+ *    direction = the reference's codes; a step is m_cameraMouseSensitivity = 0.2 (utilities.h:345: the reference steps by
+ *    the mouse sensitivity, not by m_cameraMovementSpeed), a turn is 0.5 degrees. */
+enum { FF_CAM_FORWARD = 0, FF_CAM_BACKWARD = 1, FF_CAM_LEFT = 2, FF_CAM_RIGHT = 3, FF_CAM_UP = 4, FF_CAM_DOWN = 5,
+       FF_CAM_YAW_LEFT = 6, FF_CAM_YAW_RIGHT = 7, FF_CAM_PITCH_UP = 8, FF_CAM_PITCH_DOWN = 9, FF_CAM_RESET = 10 };
+int ff_camera_process_keyboard(ff_camera* cam, int direction);
+/*    SetClickPosition(x_delta, y_delta) followed by ProcessMouseMovement(constrain_pitch) (utilities.h:385-404). */
+int ff_camera_process_mouse(ff_camera* cam, float x_delta, float y_delta, int constrain_pitch);
+
+/* -- progressive accumulation: the state the viewer loop (kernel.cu:331-359) would carry from frame to frame once the
+ *    tracer accumulates.  Each ff_progressive_frame adds params->spp samples (global sample indices continue from the
+ *    frames before, so k frames of s samples are bit-identical to one ff_render of k*s samples) and resolves the mean;
+ *    the accumulation restarts by itself when the camera, the image size or a parameter that changes the image
+ *    (max_bounces, seed, integrator, nee, aa, background, ray_eps) differs from the previous frame, and after
+ *    ff_progressive_reset (call it after re-committing the scene).  Outputs as ff_render (float RGBA, host and/or
+ *    device) plus an optional 8-bit frame with the PBO layout of ff_render_u8 (kernel.cu:214). */
+typedef struct ff_progressive ff_progressive;
+int ff_progressive_create(ff_scene* scene, ff_progressive** out);
+void ff_progressive_destroy(ff_progressive* prog);
+int ff_progressive_reset(ff_progressive* prog);
+int ff_progressive_frame(ff_progressive* prog, const ff_camera* cam, const ff_render_params* params, float* out_rgba_host,
+                         void* out_rgba_device, unsigned char* out_rgb_u8, int u8_is_device, int* out_total_spp, ff_stats* stats);
+
 /* -- headless output.  Replaces saveToPPM (utilities.h:842-856).  Format by extension:
  *    .ppm (binary P6), .png (8-bit sRGB), .exr (fp32 scanline, uncompressed), .pfm. */
 int ff_write_image(const char* path, const float* rgba, int width, int height);

@@ -334,9 +334,11 @@ struct Camera {
     float yaw, pitch, width, height, fov, nearClip, farClip;
     void updateBasis() {
         V3 front;
-        front.x = std::cos(radians(yaw)) * std::cos(radians(pitch));
-        front.y = std::sin(radians(pitch));
-        front.z = std::sin(radians(yaw)) * std::cos(radians(pitch));
+        // utilities.h:411-413 call the global (double) cos / sin on floats: products in double, one rounding to float
+        const double ry = (double)radians(yaw), rp = (double)radians(pitch);
+        front.x = (float)(::cos(ry) * ::cos(rp));
+        front.y = (float)::sin(rp);
+        front.z = (float)(::sin(ry) * ::cos(rp));
         forward = normalize(front);
         right = normalize(cross(forward, worldUp));
         up = normalize(cross(right, forward));

@@ -120,6 +120,41 @@ def test_render_u8_and_device_output(ff, ctx, meshes):
     assert (bits(d_out.download(np.float32, cam.width * cam.height * 4)) == bits(img).ravel()).all()
 
 
+@pytest.mark.parametrize("integ", ["wavefront", "megakernel"])
+def test_progressive_accumulation_with_camera_moves(ff, ctx, meshes, integ):
+    """ff_progressive (the viewer loop's frame-to-frame state, kernel.cu:331-359): k frames of s samples are bit-identical
+    to one render of k*s samples; a camera control (Camera::ProcessKeyboard, utilities.h:343-382) restarts the
+    accumulation at the new pose; an unchanged camera keeps accumulating; the 8-bit frame follows the PBO contract."""
+    integrator = ff.INTEGRATOR_WAVEFRONT if integ == "wavefront" else ff.INTEGRATOR_MEGAKERNEL
+    desc = descs(meshes)["C2"]
+    sc, cam = S.instantiate(desc, ctx, meshes)
+    prog = ff.Progressive(sc)
+    kw = dict(integrator=integrator, seed=5, aa=1)
+    for k in range(1, 4):
+        img, total, u8 = prog.frame(cam, 2, 4, want_u8=True, **kw)
+        assert total == 2 * k
+        want = sc.render(cam, 2 * k, 4, **kw)
+        assert (bits(img) == bits(want)).all(), "frame %d" % k
+        assert (u8 == (np.clip(want[..., :3], 0, 1) * np.float32(255)).astype(np.uint8)).all()
+    # move: the accumulation restarts at the new pose
+    cam.process_keyboard(ff.CAM_FORWARD).process_keyboard(ff.CAM_YAW_LEFT).process_mouse(12.0, -7.0)
+    img, total = prog.frame(cam, 3, 4, **kw)
+    assert total == 3 and (bits(img) == bits(sc.render(cam, 3, 4, **kw))).all()
+    img, total = prog.frame(cam, 1, 4, **kw)
+    assert total == 4 and (bits(img) == bits(sc.render(cam, 4, 4, **kw))).all()
+    # an image-changing parameter restarts it too; an explicit reset as well
+    img, total = prog.frame(cam, 2, 3, **kw)
+    assert total == 2 and (bits(img) == bits(sc.render(cam, 2, 3, **kw))).all()
+    prog.reset()
+    img, total = prog.frame(cam, 2, 3, **kw)
+    assert total == 2 and (bits(img) == bits(sc.render(cam, 2, 3, **kw))).all()
+    # a different image size reallocates
+    small = ff.Camera.from_dict(dict(desc["camera"], width=40, height=24))
+    img, total = prog.frame(small, 2, 3, **kw)
+    assert img.shape == (24, 40, 4) and total == 2 and (bits(img) == bits(sc.render(small, 2, 3, **kw))).all()
+    prog.close()
+
+
 def test_errors(ff, ctx, meshes):
     sc = ctx.scene()
     sc.add_triangles(meshes["cube"])

@@ -198,6 +198,29 @@ def test_camera_matches_oracle_bit_exact(ff, orc, golden):
         assert (bits(iv) == bits(oiv)).all() and (bits(ip) == bits(oip)).all()
 
 
+def test_camera_controls_match_reference_bit_exact(ff, golden):
+    """ff_camera_process_keyboard / _mouse against the reference's own Camera::ProcessKeyboard / ProcessMouseMovement /
+    resetCamera (utilities.h:343-427), state and basis after every one of 6 x 64 operations (tools/make_golden_camera.py)."""
+    g = golden("ref_camera_walk.npz")
+    for k in range(6):
+        ops, states, bases, up = g["ops%d" % k], g["states%d" % k], g["bases%d" % k], g["up%d" % k]
+        cam = ff.Camera(states[0][:3], states[0][3], states[0][4], world_up=up)
+        for i, op in enumerate(ops):
+            if int(op[0]) == 0:
+                cam.process_keyboard(int(op[1]))
+            else:
+                cam.process_mouse(op[1], op[2], True)
+            assert (bits(cam.state()) == bits(states[i + 1])).all(), (k, i, op, cam.state(), states[i + 1])
+            assert (bits(np.concatenate(cam.basis())) == bits(bases[i + 1])).all(), (k, i, op)
+    cam = ff.Camera()
+    with pytest.raises(ff.FireflyError):
+        cam.process_keyboard(11)
+    # unconstrained pitch is allowed to pass 89 degrees, constrained is clamped (utilities.h:393-399)
+    assert ff.Camera(pitch=88.0).process_mouse(0, 100, False).state()[4] > 89.0
+    assert ff.Camera(pitch=88.0).process_mouse(0, 100, True).state()[4] == np.float32(89.0)
+    assert ff.Camera(pitch=-88.0).process_mouse(0, -100, True).state()[4] == np.float32(-89.0)
+
+
 def test_philox_host(ff, orc):
     rng = np.random.default_rng(11)
     for _ in range(100):

@@ -49,7 +49,8 @@ class CMaterial(C.Structure):
 class CRenderParams(C.Structure):
     _fields_ = [("spp", C.c_int), ("max_bounces", C.c_int), ("seed", C.c_uint64), ("integrator", C.c_int), ("nee", C.c_int),
                 ("first_sample", C.c_int), ("aa", C.c_int), ("background", C.c_float * 3), ("ray_eps", C.c_float),
-                ("samples_per_pass", C.c_int), ("total_spp", C.c_int)]
+                ("samples_per_pass", C.c_int), ("total_spp", C.c_int), ("tile_size", C.c_int), ("tile_rank", C.c_int),
+                ("tile_world", C.c_int)]
 
 
 class CStats(C.Structure):
@@ -136,6 +137,8 @@ lib.ff_flush_l2.argtypes = [_vp]
 lib.ff_write_image.argtypes = [C.c_char_p, _vp, C.c_int, C.c_int]
 lib.ff_write_image_u8.argtypes = [C.c_char_p, _vp, C.c_int, C.c_int]
 lib.ff_philox4x32_10.argtypes = [_vp, _vp, _vp]
+lib.ff_tile_owned_pixels.restype = C.c_long
+lib.ff_tile_owned_pixels.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _vp, _sz]
 lib.ff_camera_process_keyboard.argtypes = [C.POINTER(CCamera), C.c_int]
 lib.ff_camera_process_mouse.argtypes = [C.POINTER(CCamera), C.c_float, C.c_float, C.c_int]
 lib.ff_progressive_create.argtypes = [_vp, C.POINTER(_vp)]
@@ -274,13 +277,14 @@ class Camera:
 
 
 def render_params(spp=1, max_bounces=4, seed=1234, integrator=INTEGRATOR_WAVEFRONT, nee=0, first_sample=0, aa=0,
-                  background=(0, 0, 0), ray_eps=1e-4, samples_per_pass=0, total_spp=0):
+                  background=(0, 0, 0), ray_eps=1e-4, samples_per_pass=0, total_spp=0, tile_size=0, tile_rank=0, tile_world=0):
     p = CRenderParams()
     p.spp, p.max_bounces, p.seed, p.integrator, p.nee = int(spp), int(max_bounces), int(seed), int(integrator), int(nee)
     p.first_sample, p.aa = int(first_sample), int(aa)
     p.background[:] = [float(x) for x in background]
     p.ray_eps = float(ray_eps)
     p.samples_per_pass, p.total_spp = int(samples_per_pass), int(total_spp)
+    p.tile_size, p.tile_rank, p.tile_world = int(tile_size), int(tile_rank), int(tile_world)
     return p
 
 
@@ -609,6 +613,17 @@ class Progressive:
         if want_stats:
             r.append(st.as_dict())
         return tuple(r)
+
+
+def tile_owned_pixels(width, height, rank, world, tile_size=0):
+    """Pixel ids rank `rank` of `world` renders under the interleaved-tile split (ff_tile_owned_pixels)."""
+    n = lib.ff_tile_owned_pixels(int(width), int(height), int(tile_size), int(rank), int(world), None, 0)
+    if n < 0:
+        _check(int(n))
+    out = np.empty(n, np.uint32)
+    if n:
+        lib.ff_tile_owned_pixels(int(width), int(height), int(tile_size), int(rank), int(world), _p(out), n)
+    return out
 
 
 def validate_scene_file(path):

@@ -96,6 +96,10 @@ struct ff_scene {
     float4* d_accum = nullptr;
     float4* d_out = nullptr;
     size_t fb_pixels = 0;
+    // tile split: owned-pixel list of the last (width, height, tile, rank, world) rendered
+    uint32_t* d_pixel_map = nullptr;
+    size_t pixel_map_count = 0;
+    int pixel_map_key[5] = {0, 0, 0, 0, 0};
     uint32_t* d_work_counter = nullptr;
     unsigned long long* d_ray_counter = nullptr;
     TraceCounters* d_trace_counters = nullptr;
@@ -120,6 +124,7 @@ static void free_render_scratch(ff_scene* s) {
     s->wb.hits = nullptr; s->wb.radiance = nullptr; s->wb.counts = nullptr; s->wb.sh_o = s->wb.sh_d = s->wb.sh_c = nullptr;
     s->wb_capacity = 0; s->wb_counts = 0; s->wb_shadow = false;
     cudaFree(s->d_accum); cudaFree(s->d_out); s->d_accum = s->d_out = nullptr; s->fb_pixels = 0;
+    cudaFree(s->d_pixel_map); s->d_pixel_map = nullptr; s->pixel_map_count = 0;
 }
 
 template <class T>
@@ -910,13 +915,43 @@ int check_params(const ff_render_params* p, const char* who) {
         set_error(std::string(who) + ": integrator must be wavefront or megakernel here"); return FF_ERR_INVALID;
     }
     if (p->nee != 0 && p->nee != 1) { set_error(std::string(who) + ": nee must be 0 or 1"); return FF_ERR_INVALID; }
+    if (p->tile_world > 1 && (p->tile_rank < 0 || p->tile_rank >= p->tile_world || p->tile_size < 0 || p->tile_size > 4096)) {
+        set_error(std::string(who) + ": bad tile_rank / tile_world / tile_size"); return FF_ERR_INVALID;
+    }
     return FF_OK;
+}
+// The pixels a rank owns under the interleaved-tile split, ascending inside each tile, tiles in row-major order.
+void tile_owned_pixels(int width, int height, int tile, int rank, int world, std::vector<uint32_t>& out) {
+    out.clear();
+    if (tile <= 0) tile = 32;
+    const int tx = (width + tile - 1) / tile, ty = (height + tile - 1) / tile;
+    for (long t = rank; t < (long)tx * ty; t += world) {
+        const int x0 = (int)(t % tx) * tile, y0 = (int)(t / tx) * tile;
+        for (int y = y0; y < std::min(height, y0 + tile); ++y)
+            for (int x = x0; x < std::min(width, x0 + tile); ++x) out.push_back((uint32_t)y * (uint32_t)width + (uint32_t)x);
+    }
 }
 // Adds params->spp samples (as sums, in sample-index order) into d_accum.
 int accumulate_samples(ff_scene* scene, const ff_camera* cam, const ff_render_params* p, float4* d_accum, ff_stats* stats) {
     ff_context* c = scene->ctx;
     cudaStream_t st = c->stream;
-    const size_t npix = (size_t)cam->width * cam->height;
+    size_t npix = (size_t)cam->width * cam->height;
+    const uint32_t* d_map = nullptr;
+    if (p->tile_world > 1) {  // this call renders the rank's tiles only
+        const int key[5] = {cam->width, cam->height, p->tile_size, p->tile_rank, p->tile_world};
+        if (!scene->d_pixel_map || memcmp(key, scene->pixel_map_key, sizeof(key)) != 0) {
+            std::vector<uint32_t> own;
+            tile_owned_pixels(cam->width, cam->height, p->tile_size, p->tile_rank, p->tile_world, own);
+            cudaFree(scene->d_pixel_map); scene->d_pixel_map = nullptr; scene->pixel_map_count = 0;
+            FF_CUDA(cudaMalloc((void**)&scene->d_pixel_map, sizeof(uint32_t) * std::max<size_t>(1, own.size())));
+            FF_CUDA(cudaMemcpy(scene->d_pixel_map, own.data(), sizeof(uint32_t) * own.size(), cudaMemcpyHostToDevice));
+            scene->pixel_map_count = own.size();
+            memcpy(scene->pixel_map_key, key, sizeof(key));
+        }
+        npix = scene->pixel_map_count;
+        d_map = scene->d_pixel_map;
+        if (npix == 0) return FF_OK;  // more ranks than tiles: nothing to render here
+    }
     // samples per pass: ~16M paths in flight.  Late bounces of a pass carry few rays (C3: 8 bounces, most paths escape
     // early), and a persistent kernel over a short queue is all tail: C3 wavefront 19.3 ms at 4M paths per pass, 12.7 ms at
     // 32M; C2 is flat from 4M to 32M (profiles/r01g_pass_size.txt).  State is ~150 B per path.
@@ -931,7 +966,7 @@ int accumulate_samples(ff_scene* scene, const ff_camera* cam, const ff_render_pa
     const CamDev cd = make_cam(cam);
     RenderDev rd;
     rd.seed_lo = (uint32_t)(p->seed & 0xffffffffull); rd.seed_hi = (uint32_t)(p->seed >> 32);
-    rd.max_bounces = p->max_bounces; rd.aa = p->aa; rd.nee = p->nee; rd.npix = (uint32_t)npix;
+    rd.max_bounces = p->max_bounces; rd.aa = p->aa; rd.nee = p->nee; rd.npix = (uint32_t)npix; rd.pixel_map = d_map;
     rd.background[0] = p->background[0]; rd.background[1] = p->background[1]; rd.background[2] = p->background[2];
     rd.ray_eps = p->ray_eps;
     const int n_pass = (int)((p->spp + spb - 1) / spb);
@@ -960,7 +995,7 @@ int accumulate_samples(ff_scene* scene, const ff_camera* cam, const ff_render_pa
         } else {
             k_megakernel_pass(scene->dev, cd, rd, scene->wb.radiance, scene->d_work_counter, scene->d_ray_counter, &launches, st);
         }
-        k_accumulate_pass(scene->wb.radiance, (uint32_t)npix, rd.samples, d_accum, st);
+        k_accumulate_pass(scene->wb.radiance, (uint32_t)npix, rd.samples, d_map, d_accum, st);
         ++launches;
     }
     const double ms = t.stop();
@@ -1244,6 +1279,19 @@ int ff_flush_l2(ff_context* ctx) {
     k_flush(ctx->flush_buf, ctx->flush_n, ctx->stream);
     FF_CUDA(cudaStreamSynchronize(ctx->stream));
     return FF_OK;
+}
+
+long ff_tile_owned_pixels(int width, int height, int tile_size, int tile_rank, int tile_world, uint32_t* out, size_t capacity) {
+    if (width <= 0 || height <= 0 || tile_size < 0 || tile_world < 1 || tile_rank < 0 || tile_rank >= tile_world) {
+        set_error("ff_tile_owned_pixels: bad argument"); return FF_ERR_INVALID;
+    }
+    std::vector<uint32_t> own;
+    tile_owned_pixels(width, height, tile_size, tile_rank, tile_world, own);
+    if (out) {
+        if (capacity < own.size()) { set_error("ff_tile_owned_pixels: capacity too small"); return FF_ERR_INVALID; }
+        memcpy(out, own.data(), sizeof(uint32_t) * own.size());
+    }
+    return (long)own.size();
 }
 
 // ---------------------------------------------------------------- camera controls (utilities.h:343-427)

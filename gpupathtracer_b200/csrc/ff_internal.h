@@ -104,7 +104,8 @@ struct RenderDev {
     int max_bounces, aa, nee;
     uint32_t first_sample;   // global sample index of local sample 0 of this pass
     uint32_t samples;        // samples in this pass
-    uint32_t npix;
+    uint32_t npix;           // pixels THIS call renders (the owned pixels under a tile split, else width * height)
+    const uint32_t* pixel_map;  // tile split: rendered pixel ordinal -> pixel id of the frame; nullptr = identity
     float background[3];
     float ray_eps;
 };
@@ -190,7 +191,7 @@ void k_wavefront_pass(const DevScene& sc, const CamDev& cam, const RenderDev& rp
                       cudaStream_t st);
 void k_megakernel_pass(const DevScene& sc, const CamDev& cam, const RenderDev& rp, float4* d_radiance,
                        uint32_t* d_work_counter, unsigned long long* d_ray_counter, uint32_t* launches, cudaStream_t st);
-void k_accumulate_pass(const float4* d_radiance, uint32_t npix, uint32_t samples, float4* d_accum, cudaStream_t st);
+void k_accumulate_pass(const float4* d_radiance, uint32_t npix, uint32_t samples, const uint32_t* d_pixel_map, float4* d_accum, cudaStream_t st);
 void k_resolve(const float4* const* accums, int n_accums, uint32_t npix, float inv_spp, float4* d_out, cudaStream_t st);
 void k_as_coded(const DevScene& sc, const CamDev& cam, unsigned char* d_rgb, cudaStream_t st);
 // Primary-ray feature buffers (FF_INTEGRATOR_AOV_*): shading normal, uv, barycentrics, albedo of the first hit.

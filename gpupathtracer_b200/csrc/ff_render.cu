@@ -28,6 +28,9 @@ __device__ __forceinline__ void camera_ray_dev(const CamDev& cam, float px, floa
     d = normalize(sub(v3(look.x, look.y, look.z), o));
 }
 // primary ray of path (pixel, sample): integer pixel corner (kernel.cu:200-201) or Philox-jittered
+// Pixel of the frame behind ordinal q of this call's pixels (identity unless the call renders a tile split).
+__device__ __forceinline__ uint32_t frame_pixel(const RenderDev& rp, uint32_t q) { return rp.pixel_map ? __ldg(rp.pixel_map + q) : q; }
+
 __device__ __forceinline__ void primary_ray(const CamDev& cam, const RenderDev& rp, uint32_t pixel, uint32_t sample, V3& o, V3& d) {
     float px = (float)(pixel % (uint32_t)cam.w), py = (float)(pixel / (uint32_t)cam.w);
     if (rp.aa) {
@@ -232,7 +235,7 @@ __global__ void wf_raygen_kernel(CamDev cam, RenderDev rp, float4* __restrict__ 
     if (blockIdx.x == 0)  // paths per bounce | extend work counters | shadow rays per bounce | shadow work counters
         for (int k = threadIdx.x; k < 4 * n_counts; k += blockDim.x) counts[k] = k == 0 ? n : 0u;
     for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
-        const uint32_t s = p / rp.npix, pixel = p - s * rp.npix;
+        const uint32_t s = p / rp.npix, pixel = frame_pixel(rp, p - s * rp.npix);
         V3 o, d;
         primary_ray(cam, rp, pixel, rp.first_sample + s, o, d);
         ray_o[p] = make_float4(o.x, o.y, o.z, __uint_as_float(p));
@@ -267,7 +270,7 @@ __global__ void __launch_bounds__(256) wf_shade_kernel(DevScene sc, RenderDev rp
             const float4 o4 = ray_o_in[k], d4 = ray_d_in[k], b4 = beta_in[k];
             const HitRec h = hits[k];
             path = __float_as_uint(o4.w);
-            const uint32_t s = path / rp.npix, pixel = path - s * rp.npix;
+            const uint32_t s = path / rp.npix, pixel = frame_pixel(rp, path - s * rp.npix);
             o = ld3(o4); d = ld3(d4); beta = ld3(b4);
             specular = b4.w != 0.0f;
             V3 L = v3(0.f, 0.f, 0.f);
@@ -388,7 +391,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) megakernel(DevScene sc, CamDev
                 if (p < n) {
                     path = p;
                     const uint32_t s = p / rp.npix;
-                    pixel = p - s * rp.npix;
+                    pixel = frame_pixel(rp, p - s * rp.npix);
                     sample = rp.first_sample + s;
                     beta = v3(1.f, 1.f, 1.f); L = v3(0.f, 0.f, 0.f);
                     bounce = 0;
@@ -467,18 +470,20 @@ void k_megakernel_pass(const DevScene& sc, const CamDev& cam, const RenderDev& r
 
 // ------------------------------------------------------------------ accumulate / resolve
 // accum[pixel] = (((accum + L[0]) + L[1]) + ...): samples in index order, like the oracle's per-pixel loop.
-__global__ void accumulate_kernel(const float4* __restrict__ radiance, uint32_t npix, uint32_t samples, float4* __restrict__ accum) {
+__global__ void accumulate_kernel(const float4* __restrict__ radiance, uint32_t npix, uint32_t samples,
+                                  const uint32_t* __restrict__ pixel_map, float4* __restrict__ accum) {
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += gridDim.x * blockDim.x) {
-        float4 a = accum[i];
+        const uint32_t px = pixel_map ? pixel_map[i] : i;
+        float4 a = accum[px];
         for (uint32_t s = 0; s < samples; ++s) {
             const float4 l = radiance[(size_t)s * npix + i];
             a.x = fadd(a.x, l.x); a.y = fadd(a.y, l.y); a.z = fadd(a.z, l.z);
         }
-        accum[i] = a;
+        accum[px] = a;
     }
 }
-void k_accumulate_pass(const float4* d_radiance, uint32_t npix, uint32_t samples, float4* d_accum, cudaStream_t st) {
-    accumulate_kernel<<<grid_for(npix, 256, 148 * 16), 256, 0, st>>>(d_radiance, npix, samples, d_accum);
+void k_accumulate_pass(const float4* d_radiance, uint32_t npix, uint32_t samples, const uint32_t* d_pixel_map, float4* d_accum, cudaStream_t st) {
+    accumulate_kernel<<<grid_for(npix, 256, 148 * 16), 256, 0, st>>>(d_radiance, npix, samples, d_pixel_map, d_accum);
 }
 // out = (sum over accumulators in rank order) * (1 / total_spp); alpha = 1.  With n_accums > 1 the pointers may be
 // peer-GPU memory (CUDA IPC over NVLink): the framebuffer reduce and the resolve are one kernel.

@@ -53,6 +53,9 @@ def render_distributed(scene, cam, spp, max_bounces, dist=None, mode="nccl", spl
 
     split="strong": `spp` is the frame's total, rank k renders sample_range(k, G, spp).
     split="weak":   every rank renders `spp` samples, rank k the global indices [k*spp, (k+1)*spp); total = G*spp.
+    split="tiles":  every rank renders ALL `spp` samples of the pixels of its interleaved 32x32 tiles (tile_owner); the other
+                    pixels of its accumulator stay zero, so the same SUM reduce assembles the frame -- bit-identical to a
+                    single-GPU render for every world size (x + 0 = x), the split for low-spp / interactive frames.
     `scene` must already be committed on this rank's GPU (scene + BVH are replicated).  With to_host=False the resolved
     frame stays in device memory on rank 0 (returned image is None everywhere)."""
     import ctypes as C
@@ -60,7 +63,11 @@ def render_distributed(scene, cam, spp, max_bounces, dist=None, mode="nccl", spl
     import gpupathtracer_b200 as ff
     rank = dist.get_rank() if dist is not None else 0
     world = dist.get_world_size() if dist is not None else 1
-    if split == "weak":
+    if split == "tiles":
+        first, count, total = 0, spp, spp
+        if world > 1:
+            kw = dict(kw, tile_rank=rank, tile_world=world, tile_size=kw.get("tile_size", 32))
+    elif split == "weak":
         first, count, total = rank * spp, spp, spp * world
     else:
         (first, count), total = sample_range(rank, world, spp), spp

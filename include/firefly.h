@@ -80,6 +80,11 @@ typedef struct ff_render_params {
     float ray_eps;           /* offset of spawned rays along the normal */
     int samples_per_pass;    /* samples in flight per wavefront pass; 0 = pick from image size */
     int total_spp;           /* divisor of the final mean; 0 = spp (single GPU) */
+    /* interleaved screen tiles (multi-GPU split for low-spp / interactive frames): with tile_world > 1 this call
+     * renders only the pixels of the tile_size x tile_size tiles t (row-major) with t % tile_world == tile_rank and leaves
+     * every other pixel of the accumulator untouched, so the SUM of the ranks' accumulators is the full frame and is
+     * bit-identical to a single-GPU render whatever tile_world is.  tile_size 0 = 32.  tile_world <= 1: the whole image. */
+    int tile_size, tile_rank, tile_world;
 } ff_render_params;
 
 /* Per-call measurements, all taken with CUDA events on the context's stream. */
@@ -267,6 +272,10 @@ typedef struct ff_scene_file {
 } ff_scene_file;
 int ff_scene_load_file(ff_context* ctx, const char* path, const char* asset_dir, ff_scene** out_scene, ff_scene_file* out_desc);
 int ff_scene_file_validate(const char* path, ff_scene_file* out_desc);
+
+/* -- the pixels rank `tile_rank` of `tile_world` owns under the interleaved-tile split above, ascending (row-major inside
+ *    each tile, tiles in row-major order); returns the count (out may be NULL to query it), negative on bad arguments. */
+long ff_tile_owned_pixels(int width, int height, int tile_size, int tile_rank, int tile_world, uint32_t* out, size_t capacity);
 
 /* -- camera controls: Camera::ProcessKeyboard / ProcessMouseMovement / resetCamera (utilities.h:343-427) applied to an
  *    ff_camera, so a front end without the GLFW callbacks (utilities.h:858-893) moves the camera exactly like the viewer.

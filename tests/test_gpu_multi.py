@@ -32,3 +32,4 @@ def test_sample_split_over_nccl_and_peer_memory(ff, ctx):
     line = [l for l in r.stdout.splitlines() if l.startswith("{")][-1]
     out = json.loads(line)
     assert out["ok"] and out["peer_bit_identical_to_rank_order_sum"], out
+    assert out["nccl_tiles_bit_identical"] and out["peer_tiles_bit_identical"], out

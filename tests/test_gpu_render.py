@@ -121,6 +121,42 @@ def test_render_u8_and_device_output(ff, ctx, meshes):
 
 
 @pytest.mark.parametrize("integ", ["wavefront", "megakernel"])
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_tile_split_sums_to_the_full_frame_bit_exactly(ff, ctx, meshes, integ, world):
+    """Interleaved-tile split (SURVEY 8e ii): rank k renders only its tiles' pixels; the SUM of the ranks' accumulators is
+    bit-identical to the single-GPU accumulator, for a frame that is not a multiple of the tile size, both integrators,
+    NEE on (the shadow queue indexes paths, not pixels)."""
+    integrator = ff.INTEGRATOR_WAVEFRONT if integ == "wavefront" else ff.INTEGRATOR_MEGAKERNEL
+    desc = S.config2(meshes, 75, 52, 5, 4)
+    sc, cam = S.instantiate(desc, ctx, meshes)
+    npix = cam.width * cam.height
+    kw = dict(integrator=integrator, seed=9, aa=1, nee=1)
+    whole = ctx.alloc(npix * 16)
+    whole.zero()
+    st_full = sc.render_accumulate(cam, whole, 5, 4, **kw)
+    want = whole.download(np.float32, npix * 4)
+    total = np.zeros(npix * 4, np.float32)
+    paths = rays = 0
+    for r in range(world):
+        part = ctx.alloc(npix * 16)
+        part.zero()
+        st = sc.render_accumulate(cam, part, 5, 4, tile_rank=r, tile_world=world, tile_size=16, **kw)
+        got = part.download(np.float32, npix * 4).reshape(npix, 4)
+        own = ff.tile_owned_pixels(cam.width, cam.height, r, world, 16)
+        mask = np.ones(npix, bool)
+        mask[own] = False
+        assert (got[mask] == 0).all()   # pixels of other ranks are untouched
+        assert st["paths"] == 5 * len(own)
+        total = total + got.ravel()
+        paths += st["paths"]
+        rays += st["rays"]
+        part.free()
+    assert (bits(total) == bits(want)).all()
+    assert paths == st_full["paths"] and rays == st_full["rays"]
+    whole.free()
+
+
+@pytest.mark.parametrize("integ", ["wavefront", "megakernel"])
 def test_progressive_accumulation_with_camera_moves(ff, ctx, meshes, integ):
     """ff_progressive (the viewer loop's frame-to-frame state, kernel.cu:331-359): k frames of s samples are bit-identical
     to one render of k*s samples; a camera control (Camera::ProcessKeyboard, utilities.h:343-382) restarts the

@@ -32,6 +32,25 @@ def test_tile_owner_interleave():
     assert M.tile_owner(0, 0, 4, 32, 8) == 0 and M.tile_owner(33, 0, 4, 32, 8) == 1 and M.tile_owner(0, 32, 4, 32, 8) == 0
 
 
+def test_tile_owned_pixels_partition_the_frame():
+    """ff_tile_owned_pixels (the host side of the tile split): ranks' pixel lists are disjoint, cover the frame, agree with
+    tile_owner, and are ragged-size safe (frames that are not a multiple of the tile, more ranks than tiles)."""
+    import gpupathtracer_b200 as ff
+    for (w, h, tile) in ((64, 64, 32), (100, 37, 32), (33, 65, 16), (7, 5, 32), (256, 128, 0)):
+        for world in (1, 2, 3, 4, 8):
+            seen = np.zeros(w * h, np.int32)
+            t = tile or 32
+            tiles_x = (w + t - 1) // t
+            for r in range(world):
+                own = ff.tile_owned_pixels(w, h, r, world, tile)
+                seen[own] += 1
+                xs, ys = own % w, own // w
+                assert all(M.tile_owner(int(x), int(y), world, t, tiles_x) == r for x, y in zip(xs[::17], ys[::17]))
+            assert (seen == 1).all(), (w, h, tile, world)
+    with pytest.raises(ff.FireflyError):
+        ff.tile_owned_pixels(8, 8, 2, 2)
+
+
 def test_combine_sums_matches_sequential():
     rng = np.random.default_rng(0)
     parts = [rng.uniform(0, 3, (5, 7, 4)).astype(np.float32) for _ in range(4)]
@@ -69,6 +88,17 @@ def _worker(rank, world, port, out_dir):
     MM.reduce_sums(local_sum, dist, 0)
     if rank == 0:
         np.save(os.path.join(out_dir, "reduced.npy"), local_sum.numpy())
+    # tile split: every rank keeps only the pixels of its interleaved tiles (all samples), zeros elsewhere; same reduce
+    import gpupathtracer_b200 as ff
+    full, _ = sc.render(desc["camera"], spp, desc["max_bounces"], threads=2)
+    cam = desc["camera"]
+    own = ff.tile_owned_pixels(cam["width"], cam["height"], rank, world, 8)
+    part = np.zeros_like(full).reshape(-1, full.shape[-1])
+    part[own] = full.reshape(-1, full.shape[-1])[own]
+    tile_sum = torch.from_numpy(part.reshape(full.shape).copy())
+    MM.reduce_sums(tile_sum, dist, 0)
+    if rank == 0:
+        np.save(os.path.join(out_dir, "tiles.npy"), tile_sum.numpy())
     dist.barrier()
     dist.destroy_process_group()
 
@@ -86,3 +116,6 @@ def test_two_rank_sample_split_over_gloo(orc, meshes, tmp_path):
     # same set of paths; only the fp32 summation order differs (per-rank partial sums, then rank order)
     assert np.abs(got[..., :3] - full[..., :3]).max() <= 1e-5 * max(1.0, float(full[..., :3].max()))
     assert full[..., :3].max() > 0
+    # tile split: disjoint pixels, so the reduce reproduces the single-process image bit for bit
+    tiles = np.load(tmp_path / "tiles.npy")
+    assert (tiles[..., :3].view(np.uint32) == full[..., :3].view(np.uint32)).all()

@@ -43,6 +43,13 @@ def main():
                 err = float(np.abs(img - full).max())
                 out["%s_%s_max_abs_err" % (mode, split)] = err
                 ok = ok and err <= 1e-5 and bool((img[..., 3] == 1.0).all())
+    # interleaved-tile split: disjoint pixels per rank, so both reduce paths must reproduce the single-GPU frame bit for bit
+    for mode in ("nccl", "peer"):
+        img, st = M.render_distributed(sc, cam, spp, bounces, dist, mode=mode, split="tiles")
+        if rank == 0:
+            same = bool((img[..., :3].view(np.uint32) == full[..., :3].view(np.uint32)).all())
+            out["%s_tiles_bit_identical" % mode] = same
+            ok = ok and same
     # the peer kernel against its host statement: partial sums gathered through NCCL, added in rank order
     first, count = M.sample_range(rank, world, spp)
     acc = torch.zeros((h, w, 4), dtype=torch.float32, device="cuda")

@@ -313,10 +313,7 @@ __global__ void refit_kernel(const float4* __restrict__ flat_tris, const uint32_
         uint32_t node = (uint32_t)(n - 1 + k);
         box_lo[node] = lo;
         box_hi[node] = hi;
-        const float f1 = box_area_lohi(lo, hi) * (slot_cost + 1.0f);
-        dp[2 * (size_t)node] = make_float4(f1, f1, f1, f1);
-        dp[2 * (size_t)node + 1] = make_float4(f1, f1, f1, 0.f);
-        if (n == 1) return;
+        if (n == 1) return;   // (a single triangle has no F table: F(leaf, j) = area * (slot + 1) is formed by its parent)
         for (;;) {
             const uint32_t p = parent[node];
             if (p == 0xffffffffu) break;
@@ -337,10 +334,22 @@ __global__ void refit_kernel(const float4* __restrict__ flat_tris, const uint32_
             // F(left, 1..7), F(right, 1..7)
             const volatile float4* vdp = dp;
             float fl[8], fr[8];
-            fl[1] = vdp[2 * (size_t)ch.x].x; fl[2] = vdp[2 * (size_t)ch.x].y; fl[3] = vdp[2 * (size_t)ch.x].z; fl[4] = vdp[2 * (size_t)ch.x].w;
-            fl[5] = vdp[2 * (size_t)ch.x + 1].x; fl[6] = vdp[2 * (size_t)ch.x + 1].y; fl[7] = vdp[2 * (size_t)ch.x + 1].z;
-            fr[1] = vdp[2 * (size_t)ch.y].x; fr[2] = vdp[2 * (size_t)ch.y].y; fr[3] = vdp[2 * (size_t)ch.y].z; fr[4] = vdp[2 * (size_t)ch.y].w;
-            fr[5] = vdp[2 * (size_t)ch.y + 1].x; fr[6] = vdp[2 * (size_t)ch.y + 1].y; fr[7] = vdp[2 * (size_t)ch.y + 1].z;
+            if ((uint32_t)ch.x < (uint32_t)(n - 1)) {
+                fl[1] = vdp[2 * (size_t)ch.x].x; fl[2] = vdp[2 * (size_t)ch.x].y; fl[3] = vdp[2 * (size_t)ch.x].z; fl[4] = vdp[2 * (size_t)ch.x].w;
+                fl[5] = vdp[2 * (size_t)ch.x + 1].x; fl[6] = vdp[2 * (size_t)ch.x + 1].y; fl[7] = vdp[2 * (size_t)ch.x + 1].z;
+            } else {  // a triangle: one leaf child whatever the budget (only internal nodes have a table)
+                const float f1 = box_area_lohi(l0, h0) * (slot_cost + 1.0f);
+#pragma unroll
+                for (int q = 1; q <= 7; ++q) fl[q] = f1;
+            }
+            if ((uint32_t)ch.y < (uint32_t)(n - 1)) {
+                fr[1] = vdp[2 * (size_t)ch.y].x; fr[2] = vdp[2 * (size_t)ch.y].y; fr[3] = vdp[2 * (size_t)ch.y].z; fr[4] = vdp[2 * (size_t)ch.y].w;
+                fr[5] = vdp[2 * (size_t)ch.y + 1].x; fr[6] = vdp[2 * (size_t)ch.y + 1].y; fr[7] = vdp[2 * (size_t)ch.y + 1].z;
+            } else {
+                const float f1 = box_area_lohi(l1, h1) * (slot_cost + 1.0f);
+#pragma unroll
+                for (int q = 1; q <= 7; ++q) fr[q] = f1;
+            }
             const float area = box_area_lohi(lo, hi);
             float f[8];
             uint32_t dec = 0;
@@ -375,8 +384,9 @@ __global__ void refit_kernel(const float4* __restrict__ flat_tris, const uint32_
 struct CollapseCounters {
     uint32_t node_count;   // wide nodes allocated so far
     uint32_t tri_count;    // triangle slots allocated so far
-    uint32_t queue_count;  // entries appended to the next level's queue
-    uint32_t pad;
+    uint32_t level_begin, level_end;  // wide nodes [begin, end) form the level being collapsed (indices are allocated in level order)
+    uint32_t levels;       // non-empty levels processed so far
+    uint32_t overflow;     // a node allocation ran past the capacity of the node arrays
     double sah;            // sum over wide nodes of area(node) * (1 + sum_leaf area_ratio...) -- see below
 };
 __device__ __forceinline__ float box_area(const float4& lo, const float4& hi) {
@@ -408,15 +418,14 @@ __device__ __forceinline__ uint32_t quant_hi(float c, float p, float sc) {
     return (uint32_t)q;
 }
 
-// One thread per wide node.  queue entries: {bvh2 node id, wide node index}.
-__global__ void collapse_kernel(const uint2* __restrict__ queue_in, uint32_t n_in, uint2* __restrict__ queue_out, int n,
+// One thread per wide node.  node_src[w] = the binary node wide node w is built from.  Wide-node indices are handed out
+// by one counter, so the nodes of a level are a contiguous index range and the levels need no host round trip: the kernel
+// reads its range from the counters block, collapse_advance_kernel moves the range to the nodes the level allocated.
+__device__ __forceinline__ void collapse_one(uint32_t bnode, uint32_t wnode, uint32_t* __restrict__ node_src, uint32_t node_capacity, int n,
                                 const int2* __restrict__ children, const float4* __restrict__ box_lo, const float4* __restrict__ box_hi,
                                 const float4* __restrict__ flat_tris, const uint32_t* __restrict__ sorted_idx,
                                 float4* __restrict__ nodes, float4* __restrict__ tris_out, uint32_t* __restrict__ leaf_slot,
                                 CollapseCounters* ctr, float root_area, const float4* __restrict__ dp) {
-    const uint32_t qi = blockIdx.x * blockDim.x + threadIdx.x;
-    if (qi >= n_in) return;
-    const uint32_t bnode = queue_in[qi].x, wnode = queue_in[qi].y;
     const uint32_t n_internal = (uint32_t)(n - 1);
 
     uint32_t ch[8];
@@ -484,8 +493,13 @@ __global__ void collapse_kernel(const uint2* __restrict__ queue_in, uint32_t n_i
         if (c < n_internal && cnt > 3) { imask |= 1u << s; ++n_inner; }
         else n_leaf_tris += (uint32_t)cnt;
     }
-    uint32_t child_base = 0, tri_base = 0, q_base = 0;
-    if (n_inner) { child_base = atomicAdd(&ctr->node_count, n_inner); q_base = atomicAdd(&ctr->queue_count, n_inner); }
+    uint32_t child_base = 0, tri_base = 0;
+    bool fits = true;
+    if (n_inner) {
+        child_base = atomicAdd(&ctr->node_count, n_inner);
+        fits = child_base + n_inner <= node_capacity;
+        if (!fits) atomicExch(&ctr->overflow, 1u);   // reported by bvh_build; the children are not queued, nothing is written out of bounds
+    }
     if (n_leaf_tris) tri_base = atomicAdd(&ctr->tri_count, n_leaf_tris);
 
     // Quantisation frame: the node box pushed out by 2^-13 of its extent per side.  The traversal evaluates a plane as
@@ -510,7 +524,7 @@ __global__ void collapse_kernel(const uint2* __restrict__ queue_in, uint32_t n_i
         uint32_t m;
         if (imask & (1u << s)) {
             m = 0x20u | (24u + (uint32_t)s);
-            queue_out[q_base + inner_rank] = make_uint2(c, child_base + inner_rank);
+            if (fits) node_src[child_base + inner_rank] = c;
             ++inner_rank;
         } else {
             const uint32_t first = (uint32_t)__float_as_int(h.w);
@@ -550,6 +564,22 @@ __global__ void collapse_kernel(const uint2* __restrict__ queue_in, uint32_t n_i
     // SAH cost of the wide tree: C_node * area(node) + C_tri * sum(leaf area * count), normalised by the root area
     if (root_area > 0.f) atomicAdd(&ctr->sah, ((double)box_area(plo, phi) * 1.0 + sah * 1.0) / (double)root_area);
 }
+__global__ void __launch_bounds__(128) collapse_kernel(uint32_t* __restrict__ node_src, uint32_t node_capacity, int n,
+                                const int2* __restrict__ children, const float4* __restrict__ box_lo, const float4* __restrict__ box_hi,
+                                const float4* __restrict__ flat_tris, const uint32_t* __restrict__ sorted_idx,
+                                float4* __restrict__ nodes, float4* __restrict__ tris_out, uint32_t* __restrict__ leaf_slot,
+                                CollapseCounters* ctr, float root_area, const float4* __restrict__ dp) {
+    const uint32_t begin = ctr->level_begin, end = ctr->level_end;   // constant during the level
+    for (uint32_t w = begin + blockIdx.x * blockDim.x + threadIdx.x; w < end; w += gridDim.x * blockDim.x)
+        collapse_one(node_src[w], w, node_src, node_capacity, n, children, box_lo, box_hi, flat_tris, sorted_idx, nodes, tris_out, leaf_slot,
+                     ctr, root_area, dp);
+}
+__global__ void collapse_advance_kernel(CollapseCounters* ctr, uint32_t node_capacity) {
+    const uint32_t end = ctr->level_end, allocated = min(ctr->node_count, node_capacity);
+    if (end > ctr->level_begin) ctr->levels += 1;
+    ctr->level_begin = end;
+    ctr->level_end = ctr->overflow ? end : allocated;
+}
 
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return e_; } while (0)
 
@@ -580,12 +610,12 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
     uint32_t *d_keys_a = nullptr, *d_keys_b = nullptr, *d_vals_a = nullptr, *d_vals_b = nullptr, *d_hist = nullptr;
     uint32_t *d_parent = nullptr, *d_flags = nullptr;
     float4* d_dp = nullptr;
-    uint2 *d_q0 = nullptr, *d_q1 = nullptr;
+    uint32_t* d_src = nullptr;
     CollapseCounters* d_ctr = nullptr;
     {
         size_t need = Arena::padded(12 * sizeof(int)) + 4 * Arena::padded(sizeof(uint32_t) * n) + Arena::padded(sizeof(uint32_t) * 256 * (size_t)n_tiles) +
-                      Arena::padded(sizeof(uint32_t) * 2 * (size_t)n) + Arena::padded(sizeof(uint32_t) * n) + Arena::padded(sizeof(float4) * 4 * (size_t)n) +
-                      2 * Arena::padded(sizeof(uint2) * (size_t)node_capacity) + Arena::padded(sizeof(CollapseCounters));
+                      Arena::padded(sizeof(uint32_t) * 2 * (size_t)n) + Arena::padded(sizeof(uint32_t) * n) + Arena::padded(sizeof(float4) * 2 * (size_t)n) +
+                      Arena::padded(sizeof(uint32_t) * (size_t)node_capacity) + Arena::padded(sizeof(CollapseCounters));
         if (builder == FF_BUILDER_SAH) need += sah_scratch_bytes(n);
         CK(arena.reserve(need));
     }
@@ -595,8 +625,8 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
     d_hist = arena.take<uint32_t>(256 * (size_t)n_tiles);
     d_parent = arena.take<uint32_t>(2 * (size_t)n);
     d_flags = arena.take<uint32_t>(n);
-    d_dp = arena.take<float4>(4 * (size_t)n);
-    d_q0 = arena.take<uint2>(node_capacity); d_q1 = arena.take<uint2>(node_capacity);
+    d_dp = arena.take<float4>(2 * (size_t)n);   // F table + decisions of the n - 1 internal binary nodes
+    d_src = arena.take<uint32_t>(node_capacity);
     d_ctr = arena.take<CollapseCounters>(1);
     if (!d_ctr) return cudaErrorMemoryAllocation;
     CK(cudaMemsetAsync(d_flags, 0, sizeof(uint32_t) * n, st));
@@ -645,26 +675,25 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
 
     CollapseCounters h_ctr;
     memset(&h_ctr, 0, sizeof(h_ctr));
-    h_ctr.node_count = 1;
+    h_ctr.node_count = 1; h_ctr.level_begin = 0; h_ctr.level_end = 1;
     CK(cudaMemcpyAsync(d_ctr, &h_ctr, sizeof(h_ctr), cudaMemcpyHostToDevice, st));
-    const uint2 root_entry = make_uint2(root, 0u);
-    CK(cudaMemcpyAsync(d_q0, &root_entry, sizeof(uint2), cudaMemcpyHostToDevice, st));
-    uint32_t n_in = 1, depth = 0;
-    uint2 *qin = d_q0, *qout = d_q1;
-    while (n_in > 0) {
-        ++depth;
-        collapse_kernel<<<grid_for(n_in, 128, 1 << 30), 128, 0, st>>>(qin, n_in, qout, (int)n, d_bvh2_children, d_bvh2_lo, d_bvh2_hi,
-                                                                     d_flat_tris, d_order, d_nodes_out, d_tris_out, d_bvh2_leaf_slot,
-                                                                     d_ctr, root_area, d_dp);
-        ++*launches;
+    CK(cudaMemcpyAsync(d_src, &root, sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+    // Levels in flights of 12 without host round trips (a hierarchy of 20 M triangles is 10 levels deep): fixed grid,
+    // grid-stride over the level's index range read from the device; an exhausted hierarchy costs empty launches.
+    for (int flight = 0; flight < 8; ++flight) {
+        for (int l = 0; l < 12; ++l) {
+            collapse_kernel<<<148 * 8, 128, 0, st>>>(d_src, node_capacity, (int)n, d_bvh2_children, d_bvh2_lo, d_bvh2_hi, d_flat_tris, d_order,
+                                                    d_nodes_out, d_tris_out, d_bvh2_leaf_slot, d_ctr, root_area, d_dp);
+            collapse_advance_kernel<<<1, 1, 0, st>>>(d_ctr, node_capacity);
+            *launches += 2;
+        }
         CK(cudaMemcpyAsync(&h_ctr, d_ctr, sizeof(h_ctr), cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
-        n_in = h_ctr.queue_count;
-        if (h_ctr.node_count > node_capacity) { CK(cudaErrorMemoryAllocation); }
-        const uint32_t zero = 0;
-        CK(cudaMemcpyAsync(&d_ctr->queue_count, &zero, sizeof(uint32_t), cudaMemcpyHostToDevice, st));
-        uint2* t = qin; qin = qout; qout = t;
+        if (h_ctr.overflow) { CK(cudaErrorMemoryAllocation); }
+        if (h_ctr.level_begin == h_ctr.level_end) break;
     }
+    if (h_ctr.level_begin != h_ctr.level_end) return cudaErrorUnknown;  // deeper than 96 levels: not a hierarchy this builder makes
+    const uint32_t depth = h_ctr.levels;
     mark("collapse to 8-wide");
     out->n_nodes = h_ctr.node_count;
     out->depth = depth;

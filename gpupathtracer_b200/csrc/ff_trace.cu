@@ -94,7 +94,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_closest_persistent_kerne
                 }
             }
         }
-        if (!__any_sync(0xffffffffu, has)) break;
+        if (!__any_sync(0xffffffffu, has)) { if (exhausted) break; continue; }  // (no hierarchy / occluded by an analytic primitive: rays finish in the fetch path)
         if (has) {
             for (;;) {
                 if (!bvh8_step<false, false>(sc, r, tv, best, my_stack, FF_TRACE_BLOCK, lstack, cn, ct)) {
@@ -262,7 +262,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_any_persistent_kernel(De
                 }
             }
         }
-        if (!__any_sync(0xffffffffu, has)) break;
+        if (!__any_sync(0xffffffffu, has)) { if (exhausted) break; continue; }  // (no hierarchy / occluded by an analytic primitive: rays finish in the fetch path)
         if (has) {
             for (;;) {
                 if (!bvh8_step<true, false>(sc, r, tv, best, my_stack, FF_TRACE_BLOCK, lstack, cn, ct)) {

@@ -221,6 +221,39 @@ def test_any_hit_consistent_with_closest(ff, ctx, meshes, mode):
     assert (occ == (closest["t"] < tmax)).all()
 
 
+def test_analytic_only_scene_and_plane_occluders_finish_every_ray(ff, ctx, orc, meshes):
+    """Rays that end in the fetch path of the persistent kernels (a scene without any triangle hierarchy; shadow rays
+    stopped by an analytic plane before traversal starts) must not end a warp's loop early: batches far larger than the
+    resident grid, every ray checked."""
+    n = 600000
+    rng = np.random.default_rng(12)
+    rays = np.empty((n, 6), np.float32)
+    rays[:, :3] = rng.uniform((-1.5, -1.5, 2.0), (1.5, 1.5, 6.0), (n, 3))
+    rays[:, 3:] = np.float32((0, 0, -1)) + rng.uniform(-0.05, 0.05, (n, 3)).astype(np.float32)
+    # planes only: no nodes at all
+    sc = ctx.scene()
+    sc.add_plane((0, 0, 0), (0, 0, 0), (4, 4, 4))
+    sc.add_plane((0, 0, -1), (0, 0, 0), (8, 8, 8))
+    sc.commit()
+    osc = orc.scene()
+    osc.add_plane((0, 0, 0), (0, 0, 0), (4, 4, 4))
+    osc.add_plane((0, 0, -1), (0, 0, 0), (8, 8, 8))
+    want = osc.intersect(rays[:50000])
+    got = sc.trace_closest(rays)
+    assert (got["geom"][:50000] == want["geom"]).all() and (bits(got["t"][:50000]) == bits(want["t"])).all()
+    assert (got["geom"] >= 0).mean() > 0.9 and (got["geom"] == sc.trace_closest(rays, ff.TRACE_BVH8 | ff.TRACE_STATIC)["geom"]).all()
+    assert (sc.trace_any(rays) == (got["geom"] >= 0)).all()
+    # a mesh hidden behind a plane: every any-hit query is decided by the plane, in the fetch path
+    sc2 = ctx.scene()
+    sc2.add_plane((0, 0, 1), (0, 0, 0), (20, 20, 20))
+    sc2.add_triangles(meshes["cube"])
+    sc2.commit()
+    occ = sc2.trace_any(rays)
+    assert occ.all()
+    c2 = sc2.trace_closest(rays)
+    assert (c2["geom"] == 0).all()
+
+
 def test_instrumented_counts_and_device_entry(ff, ctx):
     soup = ctx.make_soup(50000)
     sc = ctx.scene()

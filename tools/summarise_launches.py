@@ -63,10 +63,13 @@ def main():
                        dram_read_bytes_per_launch=t["dram_read_per_launch"], dram_write_bytes_per_launch=t["dram_write_per_launch"],
                        kernel="trace_closest_persistent_kernel", launches_averaged=t["launches"], mean_launch_ns_under_ncu=t["mean_us"] * 1e3,
                        share_of_captured_time=t["share"], command=a.command, source=os.path.relpath(a.csv, ROOT),
-                       note="DRAM traffic of the extend stage is the ray batch in and the hit records out (about 3.4 M rays x 48 B per launch); "
+                       note="DRAM traffic of the extend stage is the ray batch in and the hit records out (48 B per ray of the launch); "
                             "the scene stays in L2/L1, so DRAM bytes are a few per cent of the algorithmic traversal bytes.")
         json.dump(traffic, open(os.path.join(ROOT, "profiles", "traffic.json"), "w"), indent=1)
-        print("wrote profiles/traffic.json:", round(traffic["trace_closest_bytes_per_launch"] / 1e6, 1), "MB per launch, share", round(t["share"], 3))
+        try:
+            print("wrote profiles/traffic.json:", round(traffic["trace_closest_bytes_per_launch"] / 1e6, 1), "MB per launch, share", round(t["share"], 3))
+        except BrokenPipeError:
+            pass
 
 
 if __name__ == "__main__":

@@ -18,6 +18,12 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+#include <atomic>
+#include <chrono>
 #include <thread>
 #include <vector>
 
@@ -43,6 +49,35 @@ bool read_whole_file(const char* path, std::string& out) {
     fclose(f);
     return got == out.size();
 }
+
+// The file as one read-only byte range.  Mapped, not copied (a 200 MB file costs 0.2 s to fread into a zero-filled
+// string before the first thread can start; mapped, the page faults happen inside the parallel parse).  The parsers
+// (strtof / strtoll) stop at the first byte that cannot continue a number, so the range must END in a newline: a file
+// that does not is read into a string with one appended.
+struct FileText {
+    const char* data = nullptr;
+    size_t size = 0;
+    void* map = nullptr;
+    size_t map_size = 0;
+    std::string copy;
+    ~FileText() { if (map) munmap(map, map_size); }
+    bool open(const char* path) {
+        const int fd = ::open(path, O_RDONLY);
+        if (fd < 0) return false;
+        struct stat st;
+        if (fstat(fd, &st) != 0 || !S_ISREG(st.st_mode)) { ::close(fd); return false; }
+        const size_t n = (size_t)st.st_size;
+        if (n == 0) { ::close(fd); data = ""; size = 0; return true; }
+        void* m = mmap(nullptr, n, PROT_READ, MAP_PRIVATE, fd, 0);
+        ::close(fd);
+        if (m != MAP_FAILED && ((const char*)m)[n - 1] == '\n') { map = m; map_size = n; data = (const char*)m; size = n; return true; }
+        if (m != MAP_FAILED) munmap(m, n);
+        if (!read_whole_file(path, copy)) return false;
+        copy.push_back('\n');
+        data = copy.data(); size = copy.size();
+        return true;
+    }
+};
 
 struct Chunk {
     const char *begin = nullptr, *end = nullptr;
@@ -139,11 +174,17 @@ void parse_chunk(Chunk& c) {
     }
 }
 
+// n work items on at most `workers` threads, handed out by an atomic counter: the file is cut into several chunks per
+// thread because OBJ lines are not equally expensive (an `f` line is nine integer parses, and files keep all their `v`
+// lines first), so one static chunk per thread left most threads waiting for the slowest.
 template <class F>
-void run_threads(size_t n, F f) {
-    if (n <= 1) { if (n) f((size_t)0); return; }
+void run_threads(size_t n, size_t workers, F f) {
+    workers = std::min(workers, n);
+    if (workers <= 1) { for (size_t k = 0; k < n; ++k) f(k); return; }
+    std::atomic<size_t> next{0};
     std::vector<std::thread> th;
-    for (size_t t = 0; t < n; ++t) th.emplace_back([=] { f(t); });
+    for (size_t t = 0; t < workers; ++t)
+        th.emplace_back([&] { for (size_t k = next.fetch_add(1); k < n; k = next.fetch_add(1)) f(k); });
     for (auto& t : th) t.join();
 }
 
@@ -157,20 +198,30 @@ int obj_default_threads() {
 }
 
 bool load_obj_mesh(const char* path, ObjMesh& out, int threads) {
-    std::string text;
-    if (!read_whole_file(path, text)) { set_error(std::string("cannot read OBJ file: ") + path); return false; }
+    FileText text;
+    if (!text.open(path)) { set_error(std::string("cannot read OBJ file: ") + path); return false; }
     if (threads <= 0) threads = obj_default_threads();
-    // one chunk per thread, at least 1 MiB each (FF_OBJ_CHUNK_BYTES overrides: tests cut small files), cut after a newline
+    const bool trace = getenv("FF_OBJ_TRACE") != nullptr;
+    auto t_last = std::chrono::steady_clock::now();
+    auto mark = [&](const char* what) {
+        if (!trace) return;
+        const auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "[ff obj] %-28s %8.1f ms\n", what, std::chrono::duration<double, std::milli>(now - t_last).count());
+        t_last = now;
+    };
+    mark("read file");
+    // eight chunks per thread, at least 1 MiB each (FF_OBJ_CHUNK_BYTES overrides: tests cut small files), cut after a newline
     size_t min_chunk = 1u << 20;
     if (const char* e = getenv("FF_OBJ_CHUNK_BYTES")) if (atoll(e) > 0) min_chunk = (size_t)atoll(e);
-    size_t n_chunks = std::max<size_t>(1, std::min<size_t>((size_t)threads, text.size() / min_chunk));
+    const size_t workers = (size_t)threads;
+    size_t n_chunks = std::max<size_t>(1, std::min<size_t>(workers > 1 ? 8 * workers : 1, text.size / min_chunk));
     std::vector<Chunk> chunks(n_chunks);
-    const char* base = text.data();
-    const char* end = base + text.size();
+    const char* base = text.data;
+    const char* end = base + text.size;
     const char* cur = base;
     for (size_t k = 0; k < n_chunks; ++k) {
         chunks[k].begin = cur;
-        const char* stop = k + 1 == n_chunks ? end : base + (text.size() / n_chunks) * (k + 1);
+        const char* stop = k + 1 == n_chunks ? end : base + (text.size / n_chunks) * (k + 1);
         if (stop < cur) stop = cur;
         if (k + 1 < n_chunks) {
             const char* nl = (const char*)memchr(stop, '\n', (size_t)(end - stop));
@@ -179,7 +230,8 @@ bool load_obj_mesh(const char* path, ObjMesh& out, int threads) {
         chunks[k].end = stop;
         cur = stop;
     }
-    run_threads(n_chunks, [&](size_t k) { parse_chunk(chunks[k]); });
+    run_threads(n_chunks, workers, [&](size_t k) { parse_chunk(chunks[k]); });
+    mark("parse chunks");
     size_t nv = 0, nt = 0, nn = 0, ntri = 0, line = 0;
     for (auto& c : chunks) {
         c.first_line = line; line += c.lines;
@@ -195,7 +247,7 @@ bool load_obj_mesh(const char* path, ObjMesh& out, int threads) {
     }
     // concatenate the attribute pools
     std::vector<float> pos(3 * nv), tex(2 * nt), nrm(3 * nn);
-    run_threads(n_chunks, [&](size_t k) {
+    run_threads(n_chunks, workers, [&](size_t k) {
         const Chunk& c = chunks[k];
         if (!c.pos.empty()) memcpy(&pos[3 * c.base_v], c.pos.data(), sizeof(float) * c.pos.size());
         if (!c.tex.empty()) memcpy(&tex[2 * c.base_t], c.tex.data(), sizeof(float) * c.tex.size());
@@ -219,9 +271,11 @@ bool load_obj_mesh(const char* path, ObjMesh& out, int threads) {
     }
     std::vector<std::string> errors(n_chunks);
     std::vector<char> saw_n(n_chunks, 0), saw_t(n_chunks, 0);
-    run_threads(n_chunks, [&](size_t k) {
+    mark("pools + output allocation");
+    run_threads(n_chunks, workers, [&](size_t k) {
         const Chunk& c = chunks[k];
         const size_t n = c.corner.size() / 9;
+        char seen_n = 0, seen_t = 0;   // (not saw_n[k] / saw_t[k] directly: neighbouring bytes written per corner by different threads)
         const long long base[3] = {(long long)c.base_v, (long long)c.base_t, (long long)c.base_n};
         const long long limit[3] = {(long long)nv, (long long)nt, (long long)nn};
         size_t ev = 0;
@@ -241,15 +295,17 @@ bool load_obj_mesh(const char* path, ObjMesh& out, int threads) {
                     idx[j] = v;
                 }
                 memcpy(&out.xyz9[9 * g + 3 * a], &pos[3 * (size_t)idx[0]], 12);
-                if (idx[1] != NO_INDEX) { memcpy(&out.uv6[6 * g + 2 * a], &tex[2 * (size_t)idx[1]], 8); saw_t[k] = 1; }
-                if (idx[2] != NO_INDEX) { memcpy(&out.n9[9 * g + 3 * a], &nrm[3 * (size_t)idx[2]], 12); saw_n[k] = 1; }
+                if (idx[1] != NO_INDEX) { memcpy(&out.uv6[6 * g + 2 * a], &tex[2 * (size_t)idx[1]], 8); seen_t = 1; }
+                if (idx[2] != NO_INDEX) { memcpy(&out.n9[9 * g + 3 * a], &nrm[3 * (size_t)idx[2]], 12); seen_n = 1; }
             }
+            saw_n[k] = seen_n; saw_t[k] = seen_t;
         }
     });
+    mark("gather corners");
     for (auto& e : errors) if (!e.empty()) { set_error(std::string(path) + ": " + e); return false; }
     out.has_normals = std::find(saw_n.begin(), saw_n.end(), 1) != saw_n.end();
     out.has_uvs = std::find(saw_t.begin(), saw_t.end(), 1) != saw_t.end();
-    out.bytes = text.size();
+    out.bytes = text.size;
     return true;
 }
 

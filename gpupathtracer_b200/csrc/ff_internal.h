@@ -21,6 +21,12 @@
 
 // Kernel-variant switches (tools/probes): FF_NODE_256 = 96-byte nodes fetched with three LDG.E.256; FF_NODE_TEX / FF_TRI_TEX =
 // nodes / triangles fetched through the texture path (tex1Dfetch) instead of the LSU.
+#ifndef FF_NODE_MIN
+#define FF_NODE_MIN 0   // >0: hold a node visit back until this many lanes of the warp want one (see bvh8_step)
+#endif
+#ifndef FF_TRI_MIN
+#define FF_TRI_MIN 0    // >0: hold triangle tests back until this many lanes of the warp have one pending
+#endif
 #ifndef FF_NODE_256
 #define FF_NODE_256 0
 #endif

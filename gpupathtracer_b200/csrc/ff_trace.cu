@@ -95,6 +95,23 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_closest_persistent_kerne
             }
         }
         if (!__any_sync(0xffffffffu, has)) { if (exhausted) break; continue; }  // (no hierarchy / occluded by an analytic primitive: rays finish in the fetch path)
+#if FF_NODE_MIN || FF_TRI_MIN
+        // Experiment: every lane runs the loop (idle ones predicated off), so the warp votes with a full mask: a node visit
+        // is held back while fewer than FF_NODE_MIN lanes want one and some lane still has triangles to test.
+        for (;;) {
+            const unsigned nb = __ballot_sync(0xffffffffu, has && (tv.ngroup.y & 0xff000000u) != 0u);
+            const unsigned tb = __ballot_sync(0xffffffffu, has && tv.tgroup.y != 0u);
+            bool do_node = (__popc(nb) >= FF_NODE_MIN) || tb == 0u;
+            bool do_tri = (__popc(tb) >= FF_TRI_MIN) || nb == 0u;
+            if (!do_node && !do_tri) do_node = do_tri = true;
+            if (has && !bvh8_step<false, false>(sc, r, tv, best, my_stack, FF_TRACE_BLOCK, lstack, cn, ct, do_node, do_tri)) {
+                store_hit(hits, ray_index, best);
+                has = false;
+            }
+            const unsigned hb = __ballot_sync(0xffffffffu, has);
+            if (hb == 0u || (!exhausted && __popc(hb) < sc.refill_lanes)) break;
+        }
+#else
         if (has) {
             for (;;) {
                 if (!bvh8_step<false, false>(sc, r, tv, best, my_stack, FF_TRACE_BLOCK, lstack, cn, ct)) {
@@ -105,6 +122,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_closest_persistent_kerne
                 if (!exhausted && __popc(__activemask()) < sc.refill_lanes) break;
             }
         }
+#endif
         __syncwarp();
     }
 }

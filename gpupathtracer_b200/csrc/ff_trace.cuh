@@ -289,8 +289,8 @@ __device__ __forceinline__ bool bvh8_test_one(const DevScene& sc, const RayCtx& 
 // is order independent, so the result is unchanged.  Returns false when the ray is finished.
 template <bool ANY, bool COUNT>
 __device__ __forceinline__ bool bvh8_step(const DevScene& sc, const RayCtx& r, Trav& tv, Best& best, uint2* sm, int stride,
-                                          uint2* lstack, unsigned& n_nodes, unsigned& n_tris) {
-    if (tv.ngroup.y & 0xff000000u) {
+                                          uint2* lstack, unsigned& n_nodes, unsigned& n_tris, bool do_node = true, bool do_tri = true) {
+    if (do_node && (tv.ngroup.y & 0xff000000u)) {
         const uint32_t hits_imask = tv.ngroup.y;
         const uint32_t bit = 31u - __clz(hits_imask);
         const uint32_t base = tv.ngroup.x;
@@ -315,7 +315,7 @@ __device__ __forceinline__ bool bvh8_step(const DevScene& sc, const RayCtx& r, T
             }
         }
     }
-    if (tv.tgroup.y != 0u) {
+    if (do_tri && tv.tgroup.y != 0u) {
         if (bvh8_test_one<ANY, COUNT>(sc, r, tv, best, n_tris)) return false;
         if (tv.tgroup.y == 0u && tv.qcount > 0) tv.tgroup = tv.dequeue(sm, stride);
     }

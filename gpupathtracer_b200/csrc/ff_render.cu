@@ -245,10 +245,15 @@ __global__ void wf_raygen_kernel(CamDev cam, RenderDev rp, float4* __restrict__ 
     }
 }
 
-// shade + BSDF sampling + warp-aggregated queue compaction: survivors are appended to the next bounce's queue
-// with one atomicAdd per warp (ballot + popc), so the next extend stage reads a dense, coalesced ray array.
+// shade + BSDF sampling + queue compaction: survivors are appended to the next bounce's queue (ballot + popc inside a
+// warp, a shared-memory scan over the CTA's warps, one atomicAdd per CTA and iteration), so the next extend stage reads a
+// dense, coalesced ray array.
+#ifndef FF_SHADE_BLOCK
+#define FF_SHADE_BLOCK 256
+#endif
+static_assert(FF_SHADE_BLOCK >= 64 && FF_SHADE_BLOCK <= 512 && (FF_SHADE_BLOCK & (FF_SHADE_BLOCK - 1)) == 0, "two warp groups of warp 0 scan the CTA's warps");
 template <bool NEE>
-__global__ void __launch_bounds__(256) wf_shade_kernel(DevScene sc, RenderDev rp, int bounce, const uint32_t* __restrict__ count_in,
+__global__ void __launch_bounds__(FF_SHADE_BLOCK) wf_shade_kernel(DevScene sc, RenderDev rp, int bounce, const uint32_t* __restrict__ count_in,
                                                         uint32_t cap, const HitRec* __restrict__ hits,
                                                         const float4* __restrict__ ray_o_in, const float4* __restrict__ ray_d_in,
                                                         const float4* __restrict__ beta_in, float4* __restrict__ ray_o_out,
@@ -256,9 +261,14 @@ __global__ void __launch_bounds__(256) wf_shade_kernel(DevScene sc, RenderDev rp
                                                         float4* __restrict__ radiance, uint32_t* __restrict__ count_out,
                                                         float4* __restrict__ sh_o, float4* __restrict__ sh_d, float4* __restrict__ sh_c,
                                                         uint32_t* __restrict__ shadow_count) {
+    // Queue compaction is aggregated over the CTA: one atomicAdd per 256 paths (per queue) instead of one per warp.  With a
+    // warp-level atomic the 430 k same-address atomics of a 14 M-path launch were the kernel's top stall (53 % of the warp
+    // samples sat on the shuffle that broadcasts the returned base, profiles/r01i_shade_c2_before_details.txt).
+    __shared__ uint32_t s_cnt[2][FF_SHADE_BLOCK / 32], s_off[2][FF_SHADE_BLOCK / 32];
     const uint32_t n = min(*count_in, cap);
-    const uint32_t total = ((n + 31u) / 32u) * 32u;
-    const int lane = threadIdx.x & 31;
+    const uint32_t total = ((n + FF_SHADE_BLOCK - 1u) / FF_SHADE_BLOCK) * FF_SHADE_BLOCK;  // uniform trip count per CTA
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    constexpr int NW = FF_SHADE_BLOCK / 32;
     for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < total; k += gridDim.x * blockDim.x) {
         bool alive = false;
         V3 o, d, beta;
@@ -284,32 +294,39 @@ __global__ void __launch_bounds__(256) wf_shade_kernel(DevScene sc, RenderDev rp
             }
         }
         const unsigned m = __ballot_sync(0xffffffffu, alive);
-        if (m) {
-            const int leader = __ffs(m) - 1;
-            uint32_t base = 0;
-            if (lane == leader) base = atomicAdd(count_out, (uint32_t)__popc(m));
-            base = __shfl_sync(0xffffffffu, base, leader);
-            if (alive) {
-                const uint32_t q = base + __popc(m & ((1u << lane) - 1u));
-                ray_o_out[q] = make_float4(o.x, o.y, o.z, __uint_as_float(path));
-                ray_d_out[q] = make_float4(d.x, d.y, d.z, 0.f);
-                beta_out[q] = make_float4(beta.x, beta.y, beta.z, specular ? 1.0f : 0.0f);
-            }
+        const unsigned ms = NEE ? __ballot_sync(0xffffffffu, sr.valid) : 0u;
+        if (lane == 0) {
+            s_cnt[0][warp] = (uint32_t)__popc(m);
+            if (NEE) s_cnt[1][warp] = (uint32_t)__popc(ms);
         }
-        if (NEE) {  // shadow-ray queue of this bounce, compacted the same way
-            const unsigned ms = __ballot_sync(0xffffffffu, sr.valid);
-            if (ms) {
-                const int leader = __ffs(ms) - 1;
-                uint32_t base = 0;
-                if (lane == leader) base = atomicAdd(shadow_count, (uint32_t)__popc(ms));
-                base = __shfl_sync(0xffffffffu, base, leader);
-                if (sr.valid) {
-                    const uint32_t q = base + __popc(ms & ((1u << lane) - 1u));
-                    sh_o[q] = make_float4(sr.o.x, sr.o.y, sr.o.z, __uint_as_float(path));
-                    sh_d[q] = make_float4(sr.d.x, sr.d.y, sr.d.z, sr.tmax);
-                    sh_c[q] = make_float4(sr.contrib.x, sr.contrib.y, sr.contrib.z, 0.f);
-                }
+        __syncthreads();
+        if (warp == 0) {  // lanes [0, NW): the next bounce's queue; lanes [NW, 2 NW): the shadow queue
+            const int g = lane / NW, j = lane % NW;
+            const uint32_t c = (g == 0 || (NEE && g == 1)) ? s_cnt[g][j] : 0u;
+            uint32_t incl = c;
+#pragma unroll
+            for (int off = 1; off < NW; off <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xffffffffu, incl, off, NW);
+                if (j >= off) incl += t;
             }
+            const uint32_t sum = __shfl_sync(0xffffffffu, incl, NW - 1, NW);
+            uint32_t base = 0;
+            if (j == 0 && sum != 0u && g < 2) base = atomicAdd(g == 0 ? count_out : shadow_count, sum);
+            base = __shfl_sync(0xffffffffu, base, 0, NW);
+            if (g == 0 || (NEE && g == 1)) s_off[g][j] = base + incl - c;
+        }
+        __syncthreads();
+        if (alive) {
+            const uint32_t q = s_off[0][warp] + __popc(m & ((1u << lane) - 1u));
+            ray_o_out[q] = make_float4(o.x, o.y, o.z, __uint_as_float(path));
+            ray_d_out[q] = make_float4(d.x, d.y, d.z, 0.f);
+            beta_out[q] = make_float4(beta.x, beta.y, beta.z, specular ? 1.0f : 0.0f);
+        }
+        if (NEE && sr.valid) {  // shadow-ray queue of this bounce, compacted the same way
+            const uint32_t q = s_off[1][warp] + __popc(ms & ((1u << lane) - 1u));
+            sh_o[q] = make_float4(sr.o.x, sr.o.y, sr.o.z, __uint_as_float(path));
+            sh_d[q] = make_float4(sr.d.x, sr.d.y, sr.d.z, sr.tmax);
+            sh_c[q] = make_float4(sr.contrib.x, sr.contrib.y, sr.contrib.z, 0.f);
         }
     }
 }
@@ -328,11 +345,11 @@ void k_wavefront_pass(const DevScene& sc, const CamDev& cam, const RenderDev& rp
         k_trace_closest(sc, wb.ray_o[in], wb.ray_d[in], wb.counts + b, n, trace_mode, wb.hits, d_counters, wb.counts + n_counts + b, st);
         if (trace_events) cudaEventRecord(trace_events[(*n_trace_events)++], st);
         const bool nee = rp.nee && sc.n_lights != 0;
-        if (nee) wf_shade_kernel<true><<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(sc, rp, b, wb.counts + b, n, wb.hits, wb.ray_o[in], wb.ray_d[in],
+        if (nee) wf_shade_kernel<true><<<grid_for(n, FF_SHADE_BLOCK, 148 * 16 * 256 / FF_SHADE_BLOCK), FF_SHADE_BLOCK, 0, st>>>(sc, rp, b, wb.counts + b, n, wb.hits, wb.ray_o[in], wb.ray_d[in],
                                                                    wb.beta[in], wb.ray_o[out], wb.ray_d[out], wb.beta[out],
                                                                    wb.radiance, wb.counts + b + 1, wb.sh_o, wb.sh_d, wb.sh_c,
                                                                    wb.counts + 2 * n_counts + b);
-        else wf_shade_kernel<false><<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(sc, rp, b, wb.counts + b, n, wb.hits, wb.ray_o[in], wb.ray_d[in],
+        else wf_shade_kernel<false><<<grid_for(n, FF_SHADE_BLOCK, 148 * 16 * 256 / FF_SHADE_BLOCK), FF_SHADE_BLOCK, 0, st>>>(sc, rp, b, wb.counts + b, n, wb.hits, wb.ray_o[in], wb.ray_d[in],
                                                                    wb.beta[in], wb.ray_o[out], wb.ray_d[out], wb.beta[out],
                                                                    wb.radiance, wb.counts + b + 1, wb.sh_o, wb.sh_d, wb.sh_c,
                                                                    wb.counts + 2 * n_counts + b);

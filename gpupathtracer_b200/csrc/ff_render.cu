@@ -249,7 +249,10 @@ __global__ void wf_raygen_kernel(CamDev cam, RenderDev rp, float4* __restrict__ 
 // warp, a shared-memory scan over the CTA's warps, one atomicAdd per CTA and iteration), so the next extend stage reads a
 // dense, coalesced ray array.
 #ifndef FF_SHADE_BLOCK
-#define FF_SHADE_BLOCK 256
+#define FF_SHADE_BLOCK 128   // 64 / 128 / 256 within 1 %, 512 -2 % (profiles/r01i_variants_shade.txt)
+#endif
+#ifndef FF_SHADE_PREFETCH
+#define FF_SHADE_PREFETCH 1  // +0.5 .. 1 %
 #endif
 static_assert(FF_SHADE_BLOCK >= 64 && FF_SHADE_BLOCK <= 512 && (FF_SHADE_BLOCK & (FF_SHADE_BLOCK - 1)) == 0, "two warp groups of warp 0 scan the CTA's warps");
 template <bool NEE>
@@ -261,7 +264,7 @@ __global__ void __launch_bounds__(FF_SHADE_BLOCK) wf_shade_kernel(DevScene sc, R
                                                         float4* __restrict__ radiance, uint32_t* __restrict__ count_out,
                                                         float4* __restrict__ sh_o, float4* __restrict__ sh_d, float4* __restrict__ sh_c,
                                                         uint32_t* __restrict__ shadow_count) {
-    // Queue compaction is aggregated over the CTA: one atomicAdd per 256 paths (per queue) instead of one per warp.  With a
+    // Queue compaction is aggregated over the CTA: one atomicAdd per CTA and iteration (per queue) instead of one per warp.  With a
     // warp-level atomic the 430 k same-address atomics of a 14 M-path launch were the kernel's top stall (53 % of the warp
     // samples sat on the shuffle that broadcasts the returned base, profiles/r01i_shade_c2_before_details.txt).
     __shared__ uint32_t s_cnt[2][FF_SHADE_BLOCK / 32], s_off[2][FF_SHADE_BLOCK / 32];
@@ -276,6 +279,17 @@ __global__ void __launch_bounds__(FF_SHADE_BLOCK) wf_shade_kernel(DevScene sc, R
         ShadowReq sr;
         sr.valid = false;
         bool specular = false;  // the path's previous event was a mirror / glass bounce (carried in beta.w)
+#if FF_SHADE_PREFETCH
+        {   // pull the next iteration's four streams towards L2 while this one is shaded (one lane per 128-byte line)
+            const uint32_t k2 = k + gridDim.x * blockDim.x;
+            if ((lane & 7) == 0 && k2 < n) {
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(ray_o_in + k2));
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(ray_d_in + k2));
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(beta_in + k2));
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(hits + k2));
+            }
+        }
+#endif
         if (k < n) {
             const float4 o4 = ray_o_in[k], d4 = ray_d_in[k], b4 = beta_in[k];
             const HitRec h = hits[k];

@@ -24,6 +24,9 @@
 #ifndef FF_NODE_MIN
 #define FF_NODE_MIN 0   // >0: hold a node visit back until this many lanes of the warp want one (see bvh8_step)
 #endif
+#ifndef FF_TRACE_MINB
+#define FF_TRACE_MINB 8   // minimum resident CTAs per SM the persistent trace kernels are compiled for (register cap)
+#endif
 #ifndef FF_TRI_MIN
 #define FF_TRI_MIN 0    // >0: hold triangle tests back until this many lanes of the warp have one pending
 #endif

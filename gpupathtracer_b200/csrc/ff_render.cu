@@ -283,10 +283,15 @@ __global__ void __launch_bounds__(FF_SHADE_BLOCK) wf_shade_kernel(DevScene sc, R
         {   // pull the next iteration's four streams towards L2 while this one is shaded (one lane per 128-byte line)
             const uint32_t k2 = k + gridDim.x * blockDim.x;
             if ((lane & 7) == 0 && k2 < n) {
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(ray_o_in + k2));
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(ray_d_in + k2));
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(beta_in + k2));
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(hits + k2));
+#if FF_SHADE_PREFETCH == 2
+#define FF_PF "prefetch.global.L1 [%0];"
+#else
+#define FF_PF "prefetch.global.L2 [%0];"
+#endif
+                asm volatile(FF_PF ::"l"(ray_o_in + k2));
+                asm volatile(FF_PF ::"l"(ray_d_in + k2));
+                asm volatile(FF_PF ::"l"(beta_in + k2));
+                asm volatile(FF_PF ::"l"(hits + k2));
             }
         }
 #endif

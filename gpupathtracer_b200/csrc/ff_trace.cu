@@ -56,7 +56,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_closest_kernel(DevScene 
 // Warps pull rays from a global counter; when fewer than FF_REFILL_LANES lanes of a warp are still traversing, the
 // idle lanes fetch new rays instead of waiting for the slowest one (Aila & Laine 2009).  Results do not depend on
 // the schedule (the accept rule is order independent).
-__global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_closest_persistent_kernel(DevScene sc, const float4* __restrict__ ray_o,
+__global__ void __launch_bounds__(FF_TRACE_BLOCK, FF_TRACE_MINB) trace_closest_persistent_kernel(DevScene sc, const float4* __restrict__ ray_o,
                                                                                    const float4* __restrict__ ray_d,
                                                                                    const uint32_t* __restrict__ count_ptr, uint32_t n_max,
                                                                                    HitRec* __restrict__ hits, uint32_t* work_counter) {
@@ -227,7 +227,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_any_kernel(DevScene sc, 
 // (tmax from an array, result = occluded flags) and the wavefront's shadow stage (tmax in ray_d.w, path id in ray_o.w;
 // an unoccluded entry adds its contribution to radiance[path] -- one shadow ray per path per bounce, stages are
 // stream-ordered, so a plain read-modify-write is race free and the sum order matches the CPU restatement).
-__global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_any_persistent_kernel(DevScene sc, const float4* __restrict__ ray_o,
+__global__ void __launch_bounds__(FF_TRACE_BLOCK, FF_TRACE_MINB) trace_any_persistent_kernel(DevScene sc, const float4* __restrict__ ray_o,
                                                                                const float4* __restrict__ ray_d,
                                                                                const float* __restrict__ tmax_array, int tmax_in_dw,
                                                                                const uint32_t* __restrict__ count_ptr, uint32_t n_max,

@@ -12,12 +12,16 @@
 //   n4 = { qhi_y[0..3], qhi_y[4..7], qhi_z[0..3], qhi_z[4..7] }
 //   meta: empty 0; inner child in slot s: 0x20 | (24 + s); leaf: (unary triangle count 1/3/7)<<5 | offset from tri_base
 //   child box (decoded) = p + q * 2^(e-127), always a superset of the exact child box.
+#include <cooperative_groups.h>
+#include <cooperative_groups/reduce.h>
+#include <cooperative_groups/scan.h>
 #include <cfloat>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include "ff_internal.h"
 
+namespace cg = cooperative_groups;
 namespace ff {
 
 using namespace ffm;
@@ -301,6 +305,9 @@ __global__ void hierarchy_kernel(const uint32_t* __restrict__ keys, int n, int2*
 }
 
 #define FF_COUNT_MASK 0x3fffffff
+#ifndef FF_REFIT_FENCE
+#define FF_REFIT_FENCE 1   // 2 = the two __threadfence() per level of r01h
+#endif
 #define FF_SLOT_COST 0.25f   // cost of one hit child (mask assembly, queueing), in triangle tests
 #define FF_NODE_COST 1.5f    // cost of one wide-node visit (fetch + 8 box tests) in triangle tests (~240 vs ~150 instructions)
 __device__ __forceinline__ float box_area_lohi(const float4& lo, const float4& hi) {
@@ -335,10 +342,21 @@ __global__ void refit_kernel(const float4* __restrict__ flat_tris, const uint32_
         for (;;) {
             const uint32_t p = parent[node];
             if (p == 0xffffffffu) break;
+            // Release: this thread's box and table must be visible before its arrival is counted.  The second arrival reads
+            // them with volatile (L1-bypassing) loads that issue only after its own atomic has returned, so it needs no fence
+            // of its own; the fence.sc + L1 invalidate that __threadfence() costs twice per level was 39 % of the kernel's
+            // stall samples (profiles/r01i_refit_before_stalls.txt).
+#if FF_REFIT_FENCE == 2
             __threadfence();
             if (atomicAdd(&flags[p], 1u) == 0u) break;  // first arrival: the sibling's thread finishes this node
             __threadfence();
+#else
+            uint32_t arrived;
+            asm volatile("atom.global.add.release.gpu.u32 %0, [%1], 1;" : "=r"(arrived) : "l"(__cvta_generic_to_global(flags + p)) : "memory");
+            if (arrived == 0u) break;  // first arrival: the sibling's thread finishes this node
+#endif
             const int2 ch = children[p];
+#if FF_REFIT_FENCE == 2
             const volatile float4* vlo = box_lo;
             const volatile float4* vhi = box_hi;
             float4 l0, l1, h0, h1;
@@ -346,23 +364,26 @@ __global__ void refit_kernel(const float4* __restrict__ flat_tris, const uint32_
             l1.x = vlo[ch.y].x; l1.y = vlo[ch.y].y; l1.z = vlo[ch.y].z; l1.w = vlo[ch.y].w;
             h0.x = vhi[ch.x].x; h0.y = vhi[ch.x].y; h0.z = vhi[ch.x].z; h0.w = vhi[ch.x].w;
             h1.x = vhi[ch.y].x; h1.y = vhi[ch.y].y; h1.z = vhi[ch.y].z; h1.w = vhi[ch.y].w;
+#else
+            // ld.global.cg: 128-bit loads served by L2 (never a stale L1 line), ordered after the atomic by its "memory" clobber
+            const float4 l0 = __ldcg(box_lo + ch.x), l1 = __ldcg(box_lo + ch.y), h0 = __ldcg(box_hi + ch.x), h1 = __ldcg(box_hi + ch.y);
+#endif
             const int cnt = (__float_as_int(l0.w) & FF_COUNT_MASK) + (__float_as_int(l1.w) & FF_COUNT_MASK);
             lo = make_float4(fminf(l0.x, l1.x), fminf(l0.y, l1.y), fminf(l0.z, l1.z), 0.f);
             hi = make_float4(fmaxf(h0.x, h1.x), fmaxf(h0.y, h1.y), fmaxf(h0.z, h1.z), h0.w);
             // F(left, 1..7), F(right, 1..7)
-            const volatile float4* vdp = dp;
             float fl[8], fr[8];
             if ((uint32_t)ch.x < (uint32_t)(n - 1)) {
-                fl[1] = vdp[2 * (size_t)ch.x].x; fl[2] = vdp[2 * (size_t)ch.x].y; fl[3] = vdp[2 * (size_t)ch.x].z; fl[4] = vdp[2 * (size_t)ch.x].w;
-                fl[5] = vdp[2 * (size_t)ch.x + 1].x; fl[6] = vdp[2 * (size_t)ch.x + 1].y; fl[7] = vdp[2 * (size_t)ch.x + 1].z;
+                const float4 d0 = __ldcg(dp + 2 * (size_t)ch.x), d1 = __ldcg(dp + 2 * (size_t)ch.x + 1);
+                fl[1] = d0.x; fl[2] = d0.y; fl[3] = d0.z; fl[4] = d0.w; fl[5] = d1.x; fl[6] = d1.y; fl[7] = d1.z;
             } else {  // a triangle: one leaf child whatever the budget (only internal nodes have a table)
                 const float f1 = box_area_lohi(l0, h0) * (slot_cost + 1.0f);
 #pragma unroll
                 for (int q = 1; q <= 7; ++q) fl[q] = f1;
             }
             if ((uint32_t)ch.y < (uint32_t)(n - 1)) {
-                fr[1] = vdp[2 * (size_t)ch.y].x; fr[2] = vdp[2 * (size_t)ch.y].y; fr[3] = vdp[2 * (size_t)ch.y].z; fr[4] = vdp[2 * (size_t)ch.y].w;
-                fr[5] = vdp[2 * (size_t)ch.y + 1].x; fr[6] = vdp[2 * (size_t)ch.y + 1].y; fr[7] = vdp[2 * (size_t)ch.y + 1].z;
+                const float4 d0 = __ldcg(dp + 2 * (size_t)ch.y), d1 = __ldcg(dp + 2 * (size_t)ch.y + 1);
+                fr[1] = d0.x; fr[2] = d0.y; fr[3] = d0.z; fr[4] = d0.w; fr[5] = d1.x; fr[6] = d1.y; fr[7] = d1.z;
             } else {
                 const float f1 = box_area_lohi(l1, h1) * (slot_cost + 1.0f);
 #pragma unroll
@@ -511,14 +532,28 @@ __device__ __forceinline__ void collapse_one(uint32_t bnode, uint32_t wnode, uin
         if (c < n_internal && cnt > 3) { imask |= 1u << s; ++n_inner; }
         else n_leaf_tris += (uint32_t)cnt;
     }
+    // Allocation is aggregated over the lanes that arrive here together (one atomicAdd per counter and warp instead of one
+    // per wide node): the three counters of a 20 M-triangle build took 8.4 M same-address atomics, which the L2 serialises.
     uint32_t child_base = 0, tri_base = 0;
     bool fits = true;
+    {
+        cg::coalesced_group g = cg::coalesced_threads();
+        const uint32_t pre_n = cg::exclusive_scan(g, n_inner), pre_t = cg::exclusive_scan(g, n_leaf_tris);
+        const unsigned last = g.size() - 1;
+        const uint32_t tot_n = g.shfl(pre_n + n_inner, last), tot_t = g.shfl(pre_t + n_leaf_tris, last);
+        uint32_t bn = 0, bt = 0;
+        if (g.thread_rank() == 0) {
+            if (tot_n) bn = atomicAdd(&ctr->node_count, tot_n);
+            if (tot_t) bt = atomicAdd(&ctr->tri_count, tot_t);
+        }
+        bn = g.shfl(bn, 0); bt = g.shfl(bt, 0);
+        if (n_inner) child_base = bn + pre_n;
+        if (n_leaf_tris) tri_base = bt + pre_t;
+    }
     if (n_inner) {
-        child_base = atomicAdd(&ctr->node_count, n_inner);
         fits = child_base + n_inner <= node_capacity;
         if (!fits) atomicExch(&ctr->overflow, 1u);   // reported by bvh_build; the children are not queued, nothing is written out of bounds
     }
-    if (n_leaf_tris) tri_base = atomicAdd(&ctr->tri_count, n_leaf_tris);
 
     // Quantisation frame: the node box pushed out by 2^-13 of its extent per side.  The traversal evaluates a plane as
     // u*A + B with A = 2^15 * scale / d (byte_unit in ff_trace.cuh); the rounding of B moves a plane by at most 2^-16 of
@@ -580,7 +615,11 @@ __device__ __forceinline__ void collapse_one(uint32_t bnode, uint32_t wnode, uin
     out[4] = make_float4(__uint_as_float(qhy[0]), __uint_as_float(qhy[1]), __uint_as_float(qhz[0]), __uint_as_float(qhz[1]));
 #endif
     // SAH cost of the wide tree: C_node * area(node) + C_tri * sum(leaf area * count), normalised by the root area
-    if (root_area > 0.f) atomicAdd(&ctr->sah, ((double)box_area(plo, phi) * 1.0 + sah * 1.0) / (double)root_area);
+    if (root_area > 0.f) {
+        cg::coalesced_group g = cg::coalesced_threads();
+        const double sum = cg::reduce(g, ((double)box_area(plo, phi) * 1.0 + sah * 1.0) / (double)root_area, cg::plus<double>());
+        if (g.thread_rank() == 0) atomicAdd(&ctr->sah, sum);
+    }
 }
 __global__ void __launch_bounds__(128) collapse_kernel(uint32_t* __restrict__ node_src, uint32_t node_capacity, int n,
                                 const int2* __restrict__ children, const float4* __restrict__ box_lo, const float4* __restrict__ box_hi,

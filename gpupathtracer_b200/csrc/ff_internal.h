@@ -16,6 +16,7 @@
 #define FF_TRACE_BLOCK 128
 #define FF_REFILL_LANES 28            // persistent trace: refill idle lanes when fewer than this many still traverse
 #define FF_PERSISTENT_BLOCKS_PER_SM 12
+#define FF_TRACE_SELFSKIP 0x400        // OR into a trace mode (internal): rays carry the slot of the triangle they start on in ray_d.w
 #define FF_TRACE_STATIC 0x200          // OR into a trace mode: one-thread-per-ray kernel instead of the persistent one
 #define FF_POSTPONE_DIV 1000000  // postpone triangle tests when fewer than live/DIV lanes have any (off by default: dynamic fetch does better)
 
@@ -26,6 +27,9 @@
 #endif
 #ifndef FF_TRACE_MINB
 #define FF_TRACE_MINB 8   // minimum resident CTAs per SM the persistent trace kernels are compiled for (register cap)
+#endif
+#ifndef FF_SELF_SKIP
+#define FF_SELF_SKIP 1   // integrator rays never test the triangle they start on (make_ray_ctx in ff_trace.cuh)
 #endif
 #ifndef FF_TRI_MIN
 #define FF_TRI_MIN 0    // >0: hold triangle tests back until this many lanes of the warp have one pending

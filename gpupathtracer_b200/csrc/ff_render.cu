@@ -146,6 +146,19 @@ __device__ __forceinline__ void sample_light(const DevScene& sc, const RenderDev
     sr.valid = true;
 }
 
+// The self-skip of make_ray_ctx (ff_trace.cuh) rests on the spawned ray starting a clear distance off the plane of the triangle
+// it leaves: the reference's test returns t = -h / (d.n) for an origin h above the plane, computed with an absolute error of a few
+// 2^-24 * |o - v0| / (d.n), so it cannot come out above its 1e-6 acceptance threshold once h exceeds ~3e-7 of the scene size.
+// DevScene::pad is 2^-16 of the largest coordinate; the skip is used only when ray_eps > pad / 4 (3.8e-6 of the scene size, a
+// 10x margin; the default ray_eps of 1e-4 qualifies for scenes up to 26 units across), else every triangle is tested.
+__device__ __forceinline__ bool self_skip_safe(const DevScene& sc, const RenderDev& rp) {
+#ifdef FF_SELF_SKIP_UNGUARDED   // probe only: how far below the guard the skip stays invisible (profiles/r01i_selfskip_unguarded.txt)
+    return true;
+#else
+    return rp.ray_eps > 0.25f * sc.pad;
+#endif
+}
+
 // One shading event of the written-down algorithm.  Returns true when the path continues (o, d, beta updated, and with
 // next-event estimation `sr` describes the shadow ray of this event); otherwise L has received the path's terminal
 // contribution.
@@ -279,6 +292,7 @@ __global__ void __launch_bounds__(FF_SHADE_BLOCK) wf_shade_kernel(DevScene sc, R
         ShadowReq sr;
         sr.valid = false;
         bool specular = false;  // the path's previous event was a mirror / glass bounce (carried in beta.w)
+        uint32_t from = 0;      // slot + 1 of the triangle the continued ray starts on (0: a plane, a sphere, or no offset)
 #if FF_SHADE_PREFETCH
         {   // pull the next iteration's four streams towards L2 while this one is shaded (one lane per 128-byte line)
             const uint32_t k2 = k + gridDim.x * blockDim.x;
@@ -304,6 +318,7 @@ __global__ void __launch_bounds__(FF_SHADE_BLOCK) wf_shade_kernel(DevScene sc, R
             specular = b4.w != 0.0f;
             V3 L = v3(0.f, 0.f, 0.f);
             alive = shade_event<NEE>(sc, rp, h, pixel, rp.first_sample + s, bounce, o, d, beta, L, specular, sr);
+            if (FF_SELF_SKIP && h.slot >= 0 && !(h.slot & 0x40000000) && self_skip_safe(sc, rp)) from = (uint32_t)h.slot + 1u;
             if (!alive) {
                 if (NEE) {  // the shadow stages of earlier bounces have already added to this path
                     const float4 a = radiance[path];
@@ -338,7 +353,7 @@ __global__ void __launch_bounds__(FF_SHADE_BLOCK) wf_shade_kernel(DevScene sc, R
         if (alive) {
             const uint32_t q = s_off[0][warp] + __popc(m & ((1u << lane) - 1u));
             ray_o_out[q] = make_float4(o.x, o.y, o.z, __uint_as_float(path));
-            ray_d_out[q] = make_float4(d.x, d.y, d.z, 0.f);
+            ray_d_out[q] = make_float4(d.x, d.y, d.z, __uint_as_float(from));
             beta_out[q] = make_float4(beta.x, beta.y, beta.z, specular ? 1.0f : 0.0f);
         }
         if (NEE && sr.valid) {  // shadow-ray queue of this bounce, compacted the same way
@@ -361,7 +376,7 @@ void k_wavefront_pass(const DevScene& sc, const CamDev& cam, const RenderDev& rp
     for (int b = 0; b <= rp.max_bounces; ++b) {
         const int in = b & 1, out = in ^ 1;
         if (trace_events) cudaEventRecord(trace_events[(*n_trace_events)++], st);
-        k_trace_closest(sc, wb.ray_o[in], wb.ray_d[in], wb.counts + b, n, trace_mode, wb.hits, d_counters, wb.counts + n_counts + b, st);
+        k_trace_closest(sc, wb.ray_o[in], wb.ray_d[in], wb.counts + b, n, trace_mode | (FF_SELF_SKIP ? FF_TRACE_SELFSKIP : 0), wb.hits, d_counters, wb.counts + n_counts + b, st);
         if (trace_events) cudaEventRecord(trace_events[(*n_trace_events)++], st);
         const bool nee = rp.nee && sc.n_lights != 0;
         if (nee) wf_shade_kernel<true><<<grid_for(n, FF_SHADE_BLOCK, 148 * 16 * 256 / FF_SHADE_BLOCK), FF_SHADE_BLOCK, 0, st>>>(sc, rp, b, wb.counts + b, n, wb.hits, wb.ray_o[in], wb.ray_d[in],
@@ -406,10 +421,11 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) megakernel(DevScene sc, CamDev
     Best best;
     unsigned rays = 0, shadow_rays = 0, cn = 0, ct = 0;
     // (re)starts the closest-hit traversal of the segment (o, d)
+    uint32_t from = 0xffffffffu;  // slot of the triangle the segment starts on: never tested (make_ray_ctx in ff_trace.cuh)
     auto start_segment = [&]() {
         best_init(best, INFINITY);
         test_planes<false>(sc, o, d, best);
-        r = make_ray_ctx(o, normalize(d));
+        r = make_ray_ctx(o, normalize(d), from);
         tv.start(best.key);
         if (sc.n_nodes == 0) tv.ngroup.y = 0u;
         shadow = false;
@@ -433,6 +449,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) megakernel(DevScene sc, CamDev
                     bounce = 0;
                     specular = false;
                     primary_ray(cam, rp, pixel, sample, o, d);
+                    from = 0xffffffffu;
                     start_segment();
                     has = true;
                 }
@@ -444,7 +461,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) megakernel(DevScene sc, CamDev
                 // A shadow ray runs through the same closest-hit step (no second copy of the traversal in the loop, no
                 // divergence between lanes in different phases): its search interval starts at tmax and the first accepted
                 // hit ends it, which is the any-hit answer "some front-facing hit with key < tmax".
-                const bool more = bvh8_step<false, false>(sc, r, tv, best, my, FF_TRACE_BLOCK, lstack, cn, ct);
+                const bool more = bvh8_step<false, false, FF_SELF_SKIP != 0>(sc, r, tv, best, my, FF_TRACE_BLOCK, lstack, cn, ct);
                 if (NEE && shadow) {
                     if (!more || best.slot >= 0) {
                         if (best.slot < 0) L = add(L, pending);
@@ -457,6 +474,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) megakernel(DevScene sc, CamDev
                     ShadowReq sr;
                     if (shade_event<NEE>(sc, rp, h, pixel, sample, bounce, o, d, beta, L, specular, sr)) {
                         ++bounce;
+                        from = (h.slot >= 0 && !(h.slot & 0x40000000) && self_skip_safe(sc, rp)) ? (uint32_t)h.slot : 0xffffffffu;
                         if (NEE && sr.valid) {
                             ++shadow_rays;
                             pending = sr.contrib;
@@ -467,7 +485,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) megakernel(DevScene sc, CamDev
                                 if (best.slot < 0) L = add(L, pending);
                                 start_segment();
                             } else {
-                                r = make_ray_ctx(sr.o, normalize(sr.d));
+                                r = make_ray_ctx(sr.o, normalize(sr.d), from);
                                 tv.start(best.key);
                                 shadow = true;
                             }

@@ -27,7 +27,7 @@ __device__ __forceinline__ void store_hit(HitRec* hits, size_t i, const Best& b)
 }
 
 // ------------------------------------------------------------------ closest hit, one thread per ray
-template <int MODE, bool COUNT>
+template <int MODE, bool COUNT, bool SKIP>
 __global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_closest_kernel(DevScene sc, const float4* __restrict__ ray_o,
                                                                         const float4* __restrict__ ray_d,
                                                                         const uint32_t* __restrict__ count_ptr, uint32_t n_max,
@@ -42,7 +42,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_closest_kernel(DevScene 
         Best best;
         best_init(best, INFINITY);
         test_planes<false>(sc, o, draw, best);
-        if (MODE == FF_TRACE_BVH8) trace_bvh8<false, COUNT>(sc, o, dn, best, sm_stack + threadIdx.x, FF_TRACE_BLOCK, cn, ct);
+        if (MODE == FF_TRACE_BVH8) trace_bvh8<false, COUNT, SKIP>(sc, o, dn, best, sm_stack + threadIdx.x, FF_TRACE_BLOCK, cn, ct, SKIP ? skip_from_bits(d4.w) : 0xffffffffu);
         else trace_bvh2<false, COUNT>(sc, o, dn, best, cn, ct);
         store_hit(hits, i, best);
     }
@@ -56,6 +56,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_closest_kernel(DevScene 
 // Warps pull rays from a global counter; when fewer than FF_REFILL_LANES lanes of a warp are still traversing, the
 // idle lanes fetch new rays instead of waiting for the slowest one (Aila & Laine 2009).  Results do not depend on
 // the schedule (the accept rule is order independent).
+template <bool SKIP>
 __global__ void __launch_bounds__(FF_TRACE_BLOCK, FF_TRACE_MINB) trace_closest_persistent_kernel(DevScene sc, const float4* __restrict__ ray_o,
                                                                                    const float4* __restrict__ ray_d,
                                                                                    const uint32_t* __restrict__ count_ptr, uint32_t n_max,
@@ -82,11 +83,12 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK, FF_TRACE_MINB) trace_closest_p
             if (!has) {
                 const uint32_t i = base + __popc(need & ((1u << lane) - 1u));
                 if (i < n) {
-                    const V3 o = ld3(__ldg(ray_o + i)), draw = ld3(__ldg(ray_d + i));
+                    const float4 d4 = __ldg(ray_d + i);
+                    const V3 o = ld3(__ldg(ray_o + i)), draw = ld3(d4);
                     const V3 dn = normalize(draw);  // kernel.cu:138
                     best_init(best, INFINITY);
                     test_planes<false>(sc, o, draw, best);
-                    r = make_ray_ctx(o, dn);
+                    r = make_ray_ctx(o, dn, SKIP ? skip_from_bits(d4.w) : 0xffffffffu);
                     tv.start(best.key);
                     ray_index = i;
                     has = sc.n_nodes != 0;
@@ -104,7 +106,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK, FF_TRACE_MINB) trace_closest_p
             bool do_node = (__popc(nb) >= FF_NODE_MIN) || tb == 0u;
             bool do_tri = (__popc(tb) >= FF_TRI_MIN) || nb == 0u;
             if (!do_node && !do_tri) do_node = do_tri = true;
-            if (has && !bvh8_step<false, false>(sc, r, tv, best, my_stack, FF_TRACE_BLOCK, lstack, cn, ct, do_node, do_tri)) {
+            if (has && !bvh8_step<false, false, SKIP>(sc, r, tv, best, my_stack, FF_TRACE_BLOCK, lstack, cn, ct, do_node, do_tri)) {
                 store_hit(hits, ray_index, best);
                 has = false;
             }
@@ -114,7 +116,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK, FF_TRACE_MINB) trace_closest_p
 #else
         if (has) {
             for (;;) {
-                if (!bvh8_step<false, false>(sc, r, tv, best, my_stack, FF_TRACE_BLOCK, lstack, cn, ct)) {
+                if (!bvh8_step<false, false, SKIP>(sc, r, tv, best, my_stack, FF_TRACE_BLOCK, lstack, cn, ct)) {
                     store_hit(hits, ray_index, best);
                     has = false;
                     break;
@@ -181,7 +183,8 @@ void k_trace_closest(const DevScene& sc, const float4* d_ray_o, const float4* d_
         // persistent: enough warps to fill the machine, each pulling rays until the batch is drained.
         // *d_work_counter must be zero (the caller clears it on the same stream).
         const int g = grid_for(n_max, FF_TRACE_BLOCK, 148 * tuning().blocks_per_sm);
-        trace_closest_persistent_kernel<<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_work_counter);
+        if (mode & FF_TRACE_SELFSKIP) trace_closest_persistent_kernel<true><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_work_counter);
+        else trace_closest_persistent_kernel<false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_work_counter);
         return;
     }
     if (m == FF_TRACE_BRUTE) {
@@ -191,12 +194,16 @@ void k_trace_closest(const DevScene& sc, const float4* d_ray_o, const float4* d_
         return;
     }
     const int g = grid_for(n_max, FF_TRACE_BLOCK, 148 * 64);
+    const bool skip = (mode & FF_TRACE_SELFSKIP) != 0;
     if (m == FF_TRACE_BVH2) {
-        if (count) trace_closest_kernel<FF_TRACE_BVH2, true><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);
-        else trace_closest_kernel<FF_TRACE_BVH2, false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);
+        if (count) trace_closest_kernel<FF_TRACE_BVH2, true, false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);
+        else trace_closest_kernel<FF_TRACE_BVH2, false, false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);
+    } else if (skip) {
+        if (count) trace_closest_kernel<FF_TRACE_BVH8, true, true><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);
+        else trace_closest_kernel<FF_TRACE_BVH8, false, true><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);
     } else {
-        if (count) trace_closest_kernel<FF_TRACE_BVH8, true><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);
-        else trace_closest_kernel<FF_TRACE_BVH8, false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);
+        if (count) trace_closest_kernel<FF_TRACE_BVH8, true, false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);
+        else trace_closest_kernel<FF_TRACE_BVH8, false, false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);
     }
 }
 

@@ -68,6 +68,24 @@ def test_samples_per_pass_and_seed(ff, ctx, orc, meshes):
     assert (bits(sc.render(cam, 2, 4, seed=big_seed)) == bits(want)).all()
 
 
+def test_self_skip_of_the_origin_triangle_is_invisible(ff, ctx, orc, meshes):
+    """Integrator rays never test the triangle they start on (make_ray_ctx, ff_trace.cuh); the CPU restatement tests every
+    triangle.  Images must stay bit-identical for every ray offset: far above the guard (default 1e-4), just above it
+    (C2's threshold is pad/4 = 9.5e-6, C3's 6.9e-5), below it and at zero (skip off), with and without next-event
+    estimation, on flat (C2, C3), specular (showcase) and smooth-shaded (shaded) geometry."""
+    all_descs = dict(descs(meshes), showcase=S.showcase(meshes, 64, 48, 2, 5), shaded=S.shaded(meshes, 64, 64, 2, 5))
+    for name, spp, bounces in (("C2", 3, 4), ("C3", 2, 5), ("showcase", 2, 5), ("shaded", 2, 5)):
+        desc = all_descs[name]
+        sc, cam = S.instantiate(desc, ctx, meshes)
+        osc = S.instantiate_on(desc, orc.scene(), meshes)
+        for eps in (1e-4, 7e-5, 1e-5, 1e-6, 0.0):
+            for nee in (0, 1):
+                want, _ = osc.render(desc["camera"], spp, bounces, seed=5, ray_eps=eps, nee=nee)
+                for integ in (ff.INTEGRATOR_WAVEFRONT, ff.INTEGRATOR_MEGAKERNEL):
+                    got = sc.render(cam, spp, bounces, seed=5, ray_eps=eps, nee=nee, integrator=integ)
+                    assert (bits(got) == bits(want)).all(), (name, eps, nee, integ)
+
+
 def test_sample_split_matches_full_render(ff, ctx, meshes):
     """What the multi-GPU path does, on one GPU: disjoint sample ranges accumulated separately, reduced in rank order."""
     desc = descs(meshes)["C2"]

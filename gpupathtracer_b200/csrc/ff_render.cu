@@ -147,15 +147,28 @@ __device__ __forceinline__ void sample_light(const DevScene& sc, const RenderDev
 }
 
 // The self-skip of make_ray_ctx (ff_trace.cuh) rests on the spawned ray starting a clear distance off the plane of the triangle
-// it leaves: the reference's test returns t = -h / (d.n) for an origin h above the plane, computed with an absolute error of a few
-// 2^-24 * |o - v0| / (d.n), so it cannot come out above its 1e-6 acceptance threshold once h exceeds ~3e-7 of the scene size.
-// DevScene::pad is 2^-16 of the largest coordinate; the skip is used only when ray_eps > pad / 4 (3.8e-6 of the scene size, a
-// 10x margin; the default ray_eps of 1e-4 qualifies for scenes up to 26 units across), else every triangle is tested.
-__device__ __forceinline__ bool self_skip_safe(const DevScene& sc, const RenderDev& rp) {
-#ifdef FF_SELF_SKIP_UNGUARDED   // probe only: how far below the guard the skip stays invisible (profiles/r01i_selfskip_unguarded.txt)
+// it leaves.  For an origin at height h over that plane the reference's test computes t = (e2 . (tvec x e1)) / det, whose numerator
+// is -h |N| exactly and carries a rounding error of at most ~6 * 2^-24 * |tvec| |e1| |e2| (|tvec| <= the longer edge: the origin
+// lies over the triangle); the origin itself is known to ~2^-23 of the largest coordinate.  The skip is used only when ray_eps
+// clears both by a factor of ten:  ray_eps > pad/8 (pad = 2^-16 of the largest coordinate) and
+// ray_eps |N| > 4e-6 |e1| |e2| max(|e1|, |e2|) for the triangle in question -- a sliver, or a triangle as large as C3's 100-unit
+// floor under the default offset of 1e-4, keeps being tested like any other.
+__device__ __forceinline__ bool self_skip_enabled(const DevScene& sc, const RenderDev& rp) {
+#ifdef FF_SELF_SKIP_UNGUARDED   // probe only: how far below the guard the skip stays invisible (profiles/r01j_selfskip_unguarded.txt)
     return true;
 #else
-    return rp.ray_eps > 0.25f * sc.pad;
+    return FF_SELF_SKIP && rp.ray_eps > 0.125f * sc.pad;
+#endif
+}
+__device__ __forceinline__ bool self_skip_safe(const DevScene& sc, const RenderDev& rp, int slot) {
+    if (!self_skip_enabled(sc, rp) || slot < 0 || (slot & 0x40000000)) return false;
+#ifdef FF_SELF_SKIP_UNGUARDED
+    return true;
+#else
+    const float4 a = __ldg(sc.tris + 3 * (size_t)slot), b = __ldg(sc.tris + 3 * (size_t)slot + 1), c = __ldg(sc.tris + 3 * (size_t)slot + 2);
+    const V3 e1 = sub(ld3(b), ld3(a)), e2 = sub(ld3(c), ld3(a)), N = cross(e1, e2);
+    const float l1 = dot(e1, e1), l2 = dot(e2, e2), nn = dot(N, N);
+    return rp.ray_eps * rp.ray_eps * nn > 1.6e-11f * (l1 * l2) * fmaxf(l1, l2);
 #endif
 }
 
@@ -318,7 +331,7 @@ __global__ void __launch_bounds__(FF_SHADE_BLOCK) wf_shade_kernel(DevScene sc, R
             specular = b4.w != 0.0f;
             V3 L = v3(0.f, 0.f, 0.f);
             alive = shade_event<NEE>(sc, rp, h, pixel, rp.first_sample + s, bounce, o, d, beta, L, specular, sr);
-            if (FF_SELF_SKIP && h.slot >= 0 && !(h.slot & 0x40000000) && self_skip_safe(sc, rp)) from = (uint32_t)h.slot + 1u;
+            if (alive && self_skip_safe(sc, rp, h.slot)) from = (uint32_t)h.slot + 1u;
             if (!alive) {
                 if (NEE) {  // the shadow stages of earlier bounces have already added to this path
                     const float4 a = radiance[path];
@@ -376,7 +389,7 @@ void k_wavefront_pass(const DevScene& sc, const CamDev& cam, const RenderDev& rp
     for (int b = 0; b <= rp.max_bounces; ++b) {
         const int in = b & 1, out = in ^ 1;
         if (trace_events) cudaEventRecord(trace_events[(*n_trace_events)++], st);
-        k_trace_closest(sc, wb.ray_o[in], wb.ray_d[in], wb.counts + b, n, trace_mode | (FF_SELF_SKIP ? FF_TRACE_SELFSKIP : 0), wb.hits, d_counters, wb.counts + n_counts + b, st);
+        k_trace_closest(sc, wb.ray_o[in], wb.ray_d[in], wb.counts + b, n, trace_mode | ((FF_SELF_SKIP && rp.ray_eps > 0.125f * sc.pad) ? FF_TRACE_SELFSKIP : 0), wb.hits, d_counters, wb.counts + n_counts + b, st);
         if (trace_events) cudaEventRecord(trace_events[(*n_trace_events)++], st);
         const bool nee = rp.nee && sc.n_lights != 0;
         if (nee) wf_shade_kernel<true><<<grid_for(n, FF_SHADE_BLOCK, 148 * 16 * 256 / FF_SHADE_BLOCK), FF_SHADE_BLOCK, 0, st>>>(sc, rp, b, wb.counts + b, n, wb.hits, wb.ray_o[in], wb.ray_d[in],
@@ -421,11 +434,12 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) megakernel(DevScene sc, CamDev
     Best best;
     unsigned rays = 0, shadow_rays = 0, cn = 0, ct = 0;
     // (re)starts the closest-hit traversal of the segment (o, d)
-    uint32_t from = 0xffffffffu;  // slot of the triangle the segment starts on: never tested (make_ray_ctx in ff_trace.cuh)
+    // (no self-skip here: carrying the origin triangle's slot costs the megakernel 16 / 32 registers and, with next-event
+    // estimation, 17 % of its speed -- profiles/r01j_configs.jsonl)
     auto start_segment = [&]() {
         best_init(best, INFINITY);
         test_planes<false>(sc, o, d, best);
-        r = make_ray_ctx(o, normalize(d), from);
+        r = make_ray_ctx(o, normalize(d));
         tv.start(best.key);
         if (sc.n_nodes == 0) tv.ngroup.y = 0u;
         shadow = false;
@@ -449,7 +463,6 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) megakernel(DevScene sc, CamDev
                     bounce = 0;
                     specular = false;
                     primary_ray(cam, rp, pixel, sample, o, d);
-                    from = 0xffffffffu;
                     start_segment();
                     has = true;
                 }
@@ -461,7 +474,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) megakernel(DevScene sc, CamDev
                 // A shadow ray runs through the same closest-hit step (no second copy of the traversal in the loop, no
                 // divergence between lanes in different phases): its search interval starts at tmax and the first accepted
                 // hit ends it, which is the any-hit answer "some front-facing hit with key < tmax".
-                const bool more = bvh8_step<false, false, FF_SELF_SKIP != 0>(sc, r, tv, best, my, FF_TRACE_BLOCK, lstack, cn, ct);
+                const bool more = bvh8_step<false, false>(sc, r, tv, best, my, FF_TRACE_BLOCK, lstack, cn, ct);
                 if (NEE && shadow) {
                     if (!more || best.slot >= 0) {
                         if (best.slot < 0) L = add(L, pending);
@@ -474,7 +487,6 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) megakernel(DevScene sc, CamDev
                     ShadowReq sr;
                     if (shade_event<NEE>(sc, rp, h, pixel, sample, bounce, o, d, beta, L, specular, sr)) {
                         ++bounce;
-                        from = (h.slot >= 0 && !(h.slot & 0x40000000) && self_skip_safe(sc, rp)) ? (uint32_t)h.slot : 0xffffffffu;
                         if (NEE && sr.valid) {
                             ++shadow_rays;
                             pending = sr.contrib;
@@ -485,7 +497,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) megakernel(DevScene sc, CamDev
                                 if (best.slot < 0) L = add(L, pending);
                                 start_segment();
                             } else {
-                                r = make_ray_ctx(sr.o, normalize(sr.d), from);
+                                r = make_ray_ctx(sr.o, normalize(sr.d));
                                 tv.start(best.key);
                                 shadow = true;
                             }

@@ -70,8 +70,8 @@ def test_samples_per_pass_and_seed(ff, ctx, orc, meshes):
 
 def test_self_skip_of_the_origin_triangle_is_invisible(ff, ctx, orc, meshes):
     """Integrator rays never test the triangle they start on (make_ray_ctx, ff_trace.cuh); the CPU restatement tests every
-    triangle.  Images must stay bit-identical for every ray offset: far above the guard (default 1e-4), just above it
-    (C2's threshold is pad/4 = 9.5e-6, C3's 6.9e-5), below it and at zero (skip off), with and without next-event
+    triangle.  Images must stay bit-identical for every ray offset: far above the guard of self_skip_safe (default 1e-4 in
+    C2, whose global threshold pad/8 is 4.8e-6), just above it, below it and at zero (skip off), with and without next-event
     estimation, on flat (C2, C3), specular (showcase) and smooth-shaded (shaded) geometry."""
     all_descs = dict(descs(meshes), showcase=S.showcase(meshes, 64, 48, 2, 5), shaded=S.shaded(meshes, 64, 64, 2, 5))
     for name, spp, bounces in (("C2", 3, 4), ("C3", 2, 5), ("showcase", 2, 5), ("shaded", 2, 5)):

@@ -495,30 +495,39 @@ __device__ __forceinline__ void collapse_one(uint32_t bnode, uint32_t wnode, uin
 
     // slot assignment: greedy maximisation of dot(child centre - node centre, octant direction of the slot)
     const float pcx = 0.5f * (plo.x + phi.x), pcy = 0.5f * (plo.y + phi.y), pcz = 0.5f * (plo.z + phi.z);
-    float cost[8][8];
-    for (int k = 0; k < nch; ++k) {
-        const float4 l = box_lo[ch[k]], h = box_hi[ch[k]];
-        const float dx = 0.5f * (l.x + h.x) - pcx, dy = 0.5f * (l.y + h.y) - pcy, dz = 0.5f * (l.z + h.z) - pcz;
-        for (int s = 0; s < 8; ++s) cost[k][s] = ((s & 4) ? dx : -dx) + ((s & 2) ? dy : -dy) + ((s & 1) ? dz : -dz);
+    // (the 8 x 8 cost table used to live in local memory: 512 LDL per node, 80 % of this kernel's stall samples at the
+    // 2.4 M-node level of a 20 M-triangle build; the costs are now recomputed from 24 registers, same expression, same order)
+    float cdx[8], cdy[8], cdz[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        cdx[k] = cdy[k] = cdz[k] = 0.f;
+        if (k < nch) {
+            const float4 l = box_lo[ch[k]], h = box_hi[ch[k]];
+            cdx[k] = 0.5f * (l.x + h.x) - pcx; cdy[k] = 0.5f * (l.y + h.y) - pcy; cdz[k] = 0.5f * (l.z + h.z) - pcz;
+        }
     }
     int slot_child[8];
     for (int s = 0; s < 8; ++s) slot_child[s] = -1;
-    uint32_t assigned = 0;
+    uint32_t assigned = 0, used = 0;
     for (int it = 0; it < nch; ++it) {
         float bestc = -FLT_MAX;
         int bk = -1, bs = -1;
-        for (int k = 0; k < nch; ++k) {
-            if (assigned & (1u << k)) continue;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            if (k >= nch || (assigned & (1u << k))) continue;
+#pragma unroll
             for (int s = 0; s < 8; ++s) {
-                if (slot_child[s] >= 0) continue;
-                if (cost[k][s] > bestc) { bestc = cost[k][s]; bk = k; bs = s; }
+                if (used & (1u << s)) continue;
+                const float c = ((s & 4) ? cdx[k] : -cdx[k]) + ((s & 2) ? cdy[k] : -cdy[k]) + ((s & 1) ? cdz[k] : -cdz[k]);
+                if (c > bestc) { bestc = c; bk = k; bs = s; }
             }
         }
         if (bk < 0) {  // NaN costs: fall back to first free pairing
             for (int k = 0; k < nch && bk < 0; ++k) if (!(assigned & (1u << k))) bk = k;
-            for (int s = 0; s < 8 && bs < 0; ++s) if (slot_child[s] < 0) bs = s;
+            for (int s = 0; s < 8 && bs < 0; ++s) if (!(used & (1u << s))) bs = s;
         }
         slot_child[bs] = bk;
+        used |= 1u << bs;
         assigned |= 1u << bk;
     }
 
@@ -582,14 +591,9 @@ __device__ __forceinline__ void collapse_one(uint32_t bnode, uint32_t wnode, uin
         } else {
             const uint32_t first = (uint32_t)__float_as_int(h.w);
             m = (((1u << cnt) - 1u) << 5) | tri_off;
-            for (int t = 0; t < cnt; ++t) {
-                const uint32_t src = sorted_idx[first + t];
-                const uint32_t slot = tri_base + tri_off + (uint32_t)t;
-                tris_out[3 * (size_t)slot] = flat_tris[3 * (size_t)src];
-                tris_out[3 * (size_t)slot + 1] = flat_tris[3 * (size_t)src + 1];
-                tris_out[3 * (size_t)slot + 2] = flat_tris[3 * (size_t)src + 2];
-                leaf_slot[first + t] = slot;
-            }
+            // only the destination is recorded here; gather_tris_kernel moves the 48-byte records afterwards, one thread
+            // per triangle (the copies used to be 72 dependent-latency loads and stores in this one thread)
+            for (int t = 0; t < cnt; ++t) leaf_slot[first + t] = tri_base + tri_off + (uint32_t)t;
             tri_off += (uint32_t)cnt;
             sah += (double)box_area(l, h) * cnt;
         }
@@ -630,6 +634,15 @@ __global__ void __launch_bounds__(128) collapse_kernel(uint32_t* __restrict__ no
     for (uint32_t w = begin + blockIdx.x * blockDim.x + threadIdx.x; w < end; w += gridDim.x * blockDim.x)
         collapse_one(node_src[w], w, node_src, node_capacity, n, children, box_lo, box_hi, flat_tris, sorted_idx, nodes, tris_out, leaf_slot,
                      ctr, root_area, dp);
+}
+// Triangles into BVH-leaf order: sorted position p -> slot leaf_slot[p] (written by the collapse).
+__global__ void gather_tris_kernel(const float4* __restrict__ flat_tris, const uint32_t* __restrict__ sorted_idx,
+                                   const uint32_t* __restrict__ leaf_slot, uint32_t n, float4* __restrict__ tris_out) {
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
+        const size_t src = sorted_idx[p], slot = leaf_slot[p];
+        const float4 a = __ldg(flat_tris + 3 * src), b = __ldg(flat_tris + 3 * src + 1), c = __ldg(flat_tris + 3 * src + 2);
+        tris_out[3 * slot] = a; tris_out[3 * slot + 1] = b; tris_out[3 * slot + 2] = c;
+    }
 }
 __global__ void collapse_advance_kernel(CollapseCounters* ctr, uint32_t node_capacity) {
     const uint32_t end = ctr->level_end, allocated = min(ctr->node_count, node_capacity);
@@ -750,6 +763,10 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
         if (h_ctr.level_begin == h_ctr.level_end) break;
     }
     if (h_ctr.level_begin != h_ctr.level_end) return cudaErrorUnknown;  // deeper than 96 levels: not a hierarchy this builder makes
+    if (h_ctr.tri_count == n) {
+        gather_tris_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(d_flat_tris, d_order, d_bvh2_leaf_slot, n, d_tris_out);
+        ++*launches;
+    }
     const uint32_t depth = h_ctr.levels;
     mark("collapse to 8-wide");
     out->n_nodes = h_ctr.node_count;

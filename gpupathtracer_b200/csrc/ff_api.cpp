@@ -869,6 +869,10 @@ int ff_camera_rays(ff_context* ctx, const ff_camera* cam, float* rays6_host, voi
 
 // ================================================================================================ render
 namespace {
+#ifndef FF_PASS_PATHS
+#define FF_PASS_PATHS 32       // default paths in flight per wavefront pass, in Mi
+#define FF_PASS_PATHS_MAX 128  // upper bound for an explicit samples_per_pass, in Mi (state is ~150 B per path)
+#endif
 int ensure_wave(ff_scene* s, size_t capacity, int n_counts, bool want_shadow) {
     if (s->wb_capacity < capacity) {
         for (int k = 0; k < 2; ++k) { cudaFree(s->wb.ray_o[k]); cudaFree(s->wb.ray_d[k]); cudaFree(s->wb.beta[k]); s->wb.ray_o[k] = s->wb.ray_d[k] = s->wb.beta[k] = nullptr; }
@@ -952,12 +956,13 @@ int accumulate_samples(ff_scene* scene, const ff_camera* cam, const ff_render_pa
         d_map = scene->d_pixel_map;
         if (npix == 0) return FF_OK;  // more ranks than tiles: nothing to render here
     }
-    // samples per pass: ~16M paths in flight.  Late bounces of a pass carry few rays (C3: 8 bounces, most paths escape
-    // early), and a persistent kernel over a short queue is all tail: C3 wavefront 19.3 ms at 4M paths per pass, 12.7 ms at
-    // 32M; C2 is flat from 4M to 32M (profiles/r01g_pass_size.txt).  State is ~150 B per path.
-    size_t spb = p->samples_per_pass > 0 ? (size_t)p->samples_per_pass : std::max<size_t>(1, (16u << 20) / npix);
+    // samples per pass: ~32M paths in flight by default.  Late bounces of a pass carry few rays (C3: 8 bounces, most paths
+    // escape early), and a persistent kernel over a short queue is all tail: C3 (64 spp) 28.5 ms at 8M paths per pass, 23.7 at
+    // 16M, 21.3 at 32M, 19.8 at 64M; C2 47.1 / 46.4 / 46.0 ms at 16M / 32M / 64M (profiles/r01j_pass_size.txt).  State is
+    // ~150 B per path (4.8 GB at the default); an explicit samples_per_pass may go up to 128M paths.
+    size_t spb = p->samples_per_pass > 0 ? (size_t)p->samples_per_pass : std::max<size_t>(1, ((size_t)FF_PASS_PATHS << 20) / npix);
     spb = std::min<size_t>(spb, (size_t)p->spp);
-    while (spb > 1 && spb * npix > (32u << 20)) --spb;
+    while (spb > 1 && spb * npix > ((size_t)FF_PASS_PATHS_MAX << 20)) --spb;
     FF_REQUIRE(spb * npix < 0xffffffffull, "render: too many paths per pass");
     int rc = ensure_wave(scene, spb * npix, p->max_bounces + 2, p->nee != 0);
     if (rc) return rc;

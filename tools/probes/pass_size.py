@@ -6,9 +6,9 @@ import gpupathtracer_b200 as ff
 from gpupathtracer_b200 import scenes as S
 ctx = ff.Context(0)
 meshes = S.load_meshes()
-for name, desc in (("c2", S.config2(meshes)), ("c3", S.config3(meshes, spp=32))):
+for name, desc in (("c2", S.config2(meshes)), ("c3", S.config3(meshes, spp=64))):
     sc, cam = S.instantiate(desc, ctx, meshes, builder=1)
-    for spb in (1, 2, 4, 8, 16, 32):
+    for spb in (4, 8, 16, 32, 64):
         if spb > desc["spp"]:
             continue
         best = 1e30

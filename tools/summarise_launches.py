@@ -56,7 +56,7 @@ def main():
     for t in table[:12]:
         print("%-40s n=%5d  %8.3f ms  %5.1f %%  %9.1f us/launch  DRAM %.1f MB/launch" % (t["kernel"][:40], t["launches"], t["total_ms"], 100 * t["share"],
                                                                                      t["mean_us"], (t["dram_read_per_launch"] + t["dram_write_per_launch"]) / 1e6))
-    tr = [t for t in table if t["kernel"].startswith("trace_closest_persistent_kernel")]
+    tr = [t for t in table if "trace_closest_persistent_kernel" in t["kernel"]]
     if tr:
         t = tr[0]
         traffic = dict(trace_closest_bytes_per_launch=t["dram_read_per_launch"] + t["dram_write_per_launch"],

@@ -173,7 +173,7 @@ void k_trace_any(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_
 // Shadow stage of the wavefront: queue entries {o.xyz, path id}, {d.xyz, tmax}, {contribution.rgb}; unoccluded entries
 // add their contribution to radiance[path].  *d_work_counter must be zero.
 void k_trace_shadow(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const float4* d_contrib,
-                    const uint32_t* d_count, uint32_t n_max, float4* d_radiance, uint32_t* d_work_counter, cudaStream_t st);
+                    const uint32_t* d_count, uint32_t n_max, float4* d_radiance, uint32_t* d_work_counter, bool self_skip, cudaStream_t st);
 
 void k_camera_rays(const CamDev& cam, float4* d_ray_o, float4* d_ray_d, cudaStream_t st);
 void k_pack_rays(const float* d_rays6, size_t n, float4* d_ray_o, float4* d_ray_d, cudaStream_t st);

@@ -373,7 +373,7 @@ __global__ void __launch_bounds__(FF_SHADE_BLOCK) wf_shade_kernel(DevScene sc, R
             const uint32_t q = s_off[1][warp] + __popc(ms & ((1u << lane) - 1u));
             sh_o[q] = make_float4(sr.o.x, sr.o.y, sr.o.z, __uint_as_float(path));
             sh_d[q] = make_float4(sr.d.x, sr.d.y, sr.d.z, sr.tmax);
-            sh_c[q] = make_float4(sr.contrib.x, sr.contrib.y, sr.contrib.z, 0.f);
+            sh_c[q] = make_float4(sr.contrib.x, sr.contrib.y, sr.contrib.z, __uint_as_float(from));
         }
     }
 }
@@ -403,7 +403,8 @@ void k_wavefront_pass(const DevScene& sc, const CamDev& cam, const RenderDev& rp
         *launches += 2;
         if (nee && b < rp.max_bounces) {  // shadow stage: any-hit over this bounce's light samples
             if (trace_events) cudaEventRecord(trace_events[(*n_trace_events)++], st);
-            k_trace_shadow(sc, wb.sh_o, wb.sh_d, wb.sh_c, wb.counts + 2 * n_counts + b, n, wb.radiance, wb.counts + 3 * n_counts + b, st);
+            k_trace_shadow(sc, wb.sh_o, wb.sh_d, wb.sh_c, wb.counts + 2 * n_counts + b, n, wb.radiance, wb.counts + 3 * n_counts + b,
+                           FF_SELF_SKIP && rp.ray_eps > 0.125f * sc.pad, st);
             if (trace_events) cudaEventRecord(trace_events[(*n_trace_events)++], st);
             ++*launches;
         }

@@ -234,6 +234,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_any_kernel(DevScene sc, 
 // (tmax from an array, result = occluded flags) and the wavefront's shadow stage (tmax in ray_d.w, path id in ray_o.w;
 // an unoccluded entry adds its contribution to radiance[path] -- one shadow ray per path per bounce, stages are
 // stream-ordered, so a plain read-modify-write is race free and the sum order matches the CPU restatement).
+template <bool SKIP>
 __global__ void __launch_bounds__(FF_TRACE_BLOCK, FF_TRACE_MINB) trace_any_persistent_kernel(DevScene sc, const float4* __restrict__ ray_o,
                                                                                const float4* __restrict__ ray_d,
                                                                                const float* __restrict__ tmax_array, int tmax_in_dw,
@@ -278,7 +279,8 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK, FF_TRACE_MINB) trace_any_persi
                     const V3 dn = normalize(draw);
                     best_init(best, tmax_in_dw ? d4.w : (tmax_array ? tmax_array[i] : INFINITY));
                     test_planes<true>(sc, o, draw, best);
-                    r = make_ray_ctx(o, dn);
+                    // shadow stage: the slot of the triangle the light sample was taken from rides in contrib.w (make_ray_ctx)
+                    r = make_ray_ctx(o, dn, SKIP ? skip_from_bits(__ldg(&contrib[i].w)) : 0xffffffffu);
                     tv.start(best.key);
                     ray_index = i;
                     path = __float_as_uint(o4.w);
@@ -290,7 +292,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK, FF_TRACE_MINB) trace_any_persi
         if (!__any_sync(0xffffffffu, has)) { if (exhausted) break; continue; }  // (no hierarchy / occluded by an analytic primitive: rays finish in the fetch path)
         if (has) {
             for (;;) {
-                if (!bvh8_step<true, false>(sc, r, tv, best, my_stack, FF_TRACE_BLOCK, lstack, cn, ct)) {
+                if (!bvh8_step<true, false, SKIP>(sc, r, tv, best, my_stack, FF_TRACE_BLOCK, lstack, cn, ct)) {
                     finish();
                     has = false;
                     break;
@@ -308,7 +310,7 @@ void k_trace_any(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_
     const int m = mode & 0xff;
     if (m == FF_TRACE_BVH8 && d_work_counter && !(mode & FF_TRACE_STATIC)) {
         const int g = grid_for(n, FF_TRACE_BLOCK, 148 * tuning().blocks_per_sm);
-        trace_any_persistent_kernel<<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_tmax, 0, nullptr, n, d_occluded, nullptr, nullptr, d_work_counter);
+        trace_any_persistent_kernel<false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_tmax, 0, nullptr, n, d_occluded, nullptr, nullptr, d_work_counter);
         return;
     }
     const int g = grid_for(n, FF_TRACE_BLOCK, 148 * 64);
@@ -317,10 +319,11 @@ void k_trace_any(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_
     else trace_any_kernel<FF_TRACE_BVH8><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_tmax, n, d_occluded);
 }
 void k_trace_shadow(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const float4* d_contrib,
-                    const uint32_t* d_count, uint32_t n_max, float4* d_radiance, uint32_t* d_work_counter, cudaStream_t st) {
+                    const uint32_t* d_count, uint32_t n_max, float4* d_radiance, uint32_t* d_work_counter, bool self_skip, cudaStream_t st) {
     if (n_max == 0) return;
     const int g = grid_for(n_max, FF_TRACE_BLOCK, 148 * tuning().blocks_per_sm);
-    trace_any_persistent_kernel<<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, nullptr, 1, d_count, n_max, nullptr, d_contrib, d_radiance, d_work_counter);
+    if (self_skip) trace_any_persistent_kernel<true><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, nullptr, 1, d_count, n_max, nullptr, d_contrib, d_radiance, d_work_counter);
+    else trace_any_persistent_kernel<false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, nullptr, 1, d_count, n_max, nullptr, d_contrib, d_radiance, d_work_counter);
 }
 
 // ------------------------------------------------------------------ camera rays (kernel.cu:198-205)

@@ -184,7 +184,7 @@ def run_gpu_arm(args):
     sc, cam = S.instantiate(desc, ctx, meshes, builder=args.builder)
     info = sc.info()
     npix = W * H
-    sc_spb = max(1, (32 << 20) // npix)  # samples per wavefront pass the library picks for this image (ff_api.cpp accumulate_samples)
+    sc_spb = max(1, (64 << 20) // npix)  # samples per wavefront pass the library picks for this image (ff_api.cpp accumulate_samples)
     first = rank * SPP  # weak scaling: every rank renders its own 64 global sample indices
     total_spp = SPP * world
     d_out = ctx.alloc(npix * 16)

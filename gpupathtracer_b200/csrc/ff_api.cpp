@@ -870,7 +870,7 @@ int ff_camera_rays(ff_context* ctx, const ff_camera* cam, float* rays6_host, voi
 // ================================================================================================ render
 namespace {
 #ifndef FF_PASS_PATHS
-#define FF_PASS_PATHS 32       // default paths in flight per wavefront pass, in Mi
+#define FF_PASS_PATHS 64       // default paths in flight per wavefront pass, in Mi (9.6 GB of state on a 180 GB part)
 #define FF_PASS_PATHS_MAX 128  // upper bound for an explicit samples_per_pass, in Mi (state is ~150 B per path)
 #endif
 int ensure_wave(ff_scene* s, size_t capacity, int n_counts, bool want_shadow) {
@@ -956,10 +956,10 @@ int accumulate_samples(ff_scene* scene, const ff_camera* cam, const ff_render_pa
         d_map = scene->d_pixel_map;
         if (npix == 0) return FF_OK;  // more ranks than tiles: nothing to render here
     }
-    // samples per pass: ~32M paths in flight by default.  Late bounces of a pass carry few rays (C3: 8 bounces, most paths
+    // samples per pass: ~64M paths in flight by default.  Late bounces of a pass carry few rays (C3: 8 bounces, most paths
     // escape early), and a persistent kernel over a short queue is all tail: C3 (64 spp) 28.5 ms at 8M paths per pass, 23.7 at
     // 16M, 21.3 at 32M, 19.8 at 64M; C2 47.1 / 46.4 / 46.0 ms at 16M / 32M / 64M (profiles/r01j_pass_size.txt).  State is
-    // ~150 B per path (4.8 GB at the default); an explicit samples_per_pass may go up to 128M paths.
+    // ~150 B per path (9.6 GB at the default); an explicit samples_per_pass may go up to 128M paths.
     size_t spb = p->samples_per_pass > 0 ? (size_t)p->samples_per_pass : std::max<size_t>(1, ((size_t)FF_PASS_PATHS << 20) / npix);
     spb = std::min<size_t>(spb, (size_t)p->spp);
     while (spb > 1 && spb * npix > ((size_t)FF_PASS_PATHS_MAX << 20)) --spb;

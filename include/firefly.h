@@ -78,7 +78,7 @@ typedef struct ff_render_params {
     int aa;                  /* 0: integer pixel corner like kernel.cu:200-201; 1: Philox jitter */
     float background[3];     /* radiance of a miss; the reference leaves misses black (kernel.cu:340) */
     float ray_eps;           /* offset of spawned rays along the normal */
-    int samples_per_pass;    /* samples in flight per wavefront pass; 0 = about 32 Mi paths (~150 B of device state each), at most 128 Mi */
+    int samples_per_pass;    /* samples in flight per wavefront pass; 0 = about 64 Mi paths (~150 B of device state each), at most 128 Mi */
     int total_spp;           /* divisor of the final mean; 0 = spp (single GPU) */
     /* interleaved screen tiles (multi-GPU split for low-spp / interactive frames): with tile_world > 1 this call
      * renders only the pixels of the tile_size x tile_size tiles t (row-major) with t % tile_world == tile_rank and leaves

@@ -266,8 +266,9 @@ __global__ void wf_raygen_kernel(CamDev cam, RenderDev rp, float4* __restrict__ 
         primary_ray(cam, rp, pixel, rp.first_sample + s, o, d);
         ray_o[p] = make_float4(o.x, o.y, o.z, __uint_as_float(p));
         ray_d[p] = make_float4(d.x, d.y, d.z, 0.f);
-        beta[p] = make_float4(1.f, 1.f, 1.f, 0.f);
-        radiance[p] = make_float4(0.f, 0.f, 0.f, 0.f);
+        // beta is 1 on the camera segment: the shade stage of bounce 0 knows that and does not read it.  radiance[p] is written
+        // exactly once, when the path ends -- only the shadow stage of next-event estimation adds to it before that.
+        if (rp.nee) radiance[p] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
 }
 
@@ -317,13 +318,13 @@ __global__ void __launch_bounds__(FF_SHADE_BLOCK) wf_shade_kernel(DevScene sc, R
 #endif
                 asm volatile(FF_PF ::"l"(ray_o_in + k2));
                 asm volatile(FF_PF ::"l"(ray_d_in + k2));
-                asm volatile(FF_PF ::"l"(beta_in + k2));
+                if (bounce != 0) asm volatile(FF_PF ::"l"(beta_in + k2));
                 asm volatile(FF_PF ::"l"(hits + k2));
             }
         }
 #endif
         if (k < n) {
-            const float4 o4 = ray_o_in[k], d4 = ray_d_in[k], b4 = beta_in[k];
+            const float4 o4 = ray_o_in[k], d4 = ray_d_in[k], b4 = bounce == 0 ? make_float4(1.f, 1.f, 1.f, 0.f) : beta_in[k];
             const HitRec h = hits[k];
             path = __float_as_uint(o4.w);
             const uint32_t s = path / rp.npix, pixel = frame_pixel(rp, path - s * rp.npix);

@@ -64,11 +64,21 @@ def measured_peak():
 
 class ClockSampler:
     """nvidia-smi clocks/throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+    Q = ("timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
         self.index, self.proc, self.path = index, None, None
+        self.t0 = self.t1 = None
+
+    def mark_begin(self):
+        """The timed region starts here.  nvidia-smi itself is started BEFORE the warm-up: its start-up (NVML initialisation,
+        a few hundred ms of driver calls) used to land on the first timed steps and cost one of them 4.5 ms
+        (profiles/r01m_bench_c2_after_reference_arm.json); rows are filtered to the timed region by their timestamps."""
+        self.t0 = time.time()
+
+    def mark_end(self):
+        self.t1 = time.time()
 
     def start(self):
         try:
@@ -92,6 +102,17 @@ class ClockSampler:
         try:
             rows = [r.split(",") for r in open(self.path).read().strip().splitlines() if r.count(",") >= 8]
             os.unlink(self.path)
+            if self.t0 is not None and self.t1 is not None:
+                import datetime
+
+                def stamp(r):
+                    try:
+                        return datetime.datetime.strptime(r[0].strip(), "%Y/%m/%d %H:%M:%S.%f").timestamp()
+                    except Exception:
+                        return None
+                inside = [r for r in rows if stamp(r) is not None and self.t0 - 0.05 <= stamp(r) <= self.t1 + 0.05]
+                if inside:
+                    rows = inside
             sm = [float(r[1]) for r in rows]
             reasons = set()
             for r in rows:
@@ -236,6 +257,9 @@ def run_gpu_arm(args):
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
         return float(t.item())
 
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
     for _ in range(max(3, args.warmup)):
         step_device()
     # instrumented frame (untimed): mean nodes / triangles per ray for the algorithmic-bytes figure
@@ -243,9 +267,7 @@ def run_gpu_arm(args):
                        integrator=ff.INTEGRATOR_WAVEFRONT | ff.TRACE_COUNT)
     n_node, n_tri = stc["nodes_visited"] / stc["rays"], stc["tris_tested"] / stc["rays"]
 
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
+    sampler.mark_begin()
     secs, trace_ms, gpu_ms, rays, launches = 0.0, 0.0, 0.0, 0, 0
     for _ in range(args.steps):
         ctx.flush_l2()
@@ -264,6 +286,7 @@ def run_gpu_arm(args):
         log("rank %d e2e step: %.3f ms (device clock), library kernels %.3f ms" % (rank, 1e3 * dt, st["gpu_ms"]))
         e_secs += maxreduce(dt)
         e_rays += int(sumreduce(st["rays"]))
+    sampler.mark_end()
     clocks = sampler.stop() if rank == 0 else None
 
     if rank == 0:

@@ -965,6 +965,14 @@ int accumulate_samples(ff_scene* scene, const ff_camera* cam, const ff_render_pa
     while (spb > 1 && spb * npix > ((size_t)FF_PASS_PATHS_MAX << 20)) --spb;
     FF_REQUIRE(spb * npix < 0xffffffffull, "render: too many paths per pass");
     int rc = ensure_wave(scene, spb * npix, p->max_bounces + 2, p->nee != 0);
+    while (rc != FF_OK && p->samples_per_pass <= 0 && spb > 1) {
+        // the DEFAULT pass size did not fit beside what else lives on the device: give the partial allocation back and halve it
+        // (an explicit samples_per_pass is the caller's decision and fails as it did)
+        cudaGetLastError();
+        scene->wb_capacity = 0;
+        spb = (spb + 1) / 2;
+        rc = ensure_wave(scene, spb * npix, p->max_bounces + 2, p->nee != 0);
+    }
     if (rc) return rc;
     rc = ensure_counters(scene);
     if (rc) return rc;

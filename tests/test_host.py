@@ -317,3 +317,42 @@ def test_scene_file_parser(ff, meshes, tmp_path):
         assert msg in str(e.value), (text, str(e.value))
     with pytest.raises(ff.FireflyError):
         ff.validate_scene_file(str(tmp_path / "missing.ffscene"))
+
+
+def test_bench_clock_sampler_keeps_only_the_timed_region(tmp_path):
+    """bench.py starts nvidia-smi before the warm-up (its start-up used to perturb the first timed steps) and must then report
+    only the rows sampled inside the timed region, with throttle reasons taken from those rows alone."""
+    import datetime
+    import importlib.util
+    import time
+    spec = importlib.util.spec_from_file_location("ff_bench", os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+
+    class Done:
+        def terminate(self): pass
+        def wait(self, timeout=None): return 0
+        def kill(self): pass
+
+    now = time.time()
+
+    def row(t, sm, power, thermal):
+        ts = datetime.datetime.fromtimestamp(t).strftime("%Y/%m/%d %H:%M:%S.%f")[:-3]
+        return "%s, %d, 1965, %.2f, 0x0000000000000000, Not Active, Not Active, %s, Not Active" % (ts, sm, power, thermal)
+
+    path = tmp_path / "smi.csv"
+    path.write_text("\n".join([row(now - 3.0, 300, 150.0, "Active"),      # warm-up: idle clocks and a throttle flag that must not count
+                               row(now - 1.0, 1965, 480.0, "Not Active"), row(now - 0.5, 1950, 500.0, "Not Active"),
+                               row(now + 2.0, 210, 140.0, "Not Active")]) + "\n")
+    s = bench.ClockSampler(0)
+    s.proc, s.path = Done(), str(path)
+    s.t0, s.t1 = now - 1.5, now
+    out = s.stop()
+    assert out["samples"] == 2 and out["sm_mhz"] == 1957.5 and out["sm_max_mhz"] == 1965.0
+    assert out["reasons"] == [] and out["power_w_max"] == 500.0
+    # without marks (or unparsable timestamps) every row counts, as before
+    path.write_text(row(now, 1965, 480.0, "Active") + "\n")
+    s2 = bench.ClockSampler(0)
+    s2.proc, s2.path = Done(), str(path)
+    out2 = s2.stop()
+    assert out2["samples"] == 1 and out2["reasons"] == ["sw_thermal_slowdown"]

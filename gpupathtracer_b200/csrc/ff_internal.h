@@ -26,7 +26,7 @@
 #define FF_NODE_MIN 0   // >0: hold a node visit back until this many lanes of the warp want one (see bvh8_step)
 #endif
 #ifndef FF_TRACE_MINB
-#define FF_TRACE_MINB 8   // minimum resident CTAs per SM the persistent trace kernels are compiled for (register cap)
+#define FF_TRACE_MINB 7   // minimum resident CTAs per SM the persistent trace kernels are compiled for: 72-register cap (they use 71); 8 (64 registers) is 1 % slower on C2 / C3, 9 and more lose 2-50 % (profiles/r01i_variants_minb.txt, r01n_variants_minb7.txt)
 #endif
 #ifndef FF_SELF_SKIP
 #define FF_SELF_SKIP 1   // integrator rays never test the triangle they start on (make_ray_ctx in ff_trace.cuh)

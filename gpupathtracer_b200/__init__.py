@@ -16,7 +16,26 @@ LIB_PATH = os.environ.get("FF_LIB_OVERRIDE") or os.path.join(_HERE, "libfirefly_
 if not os.path.exists(LIB_PATH):
     raise ImportError("%s is missing: run `python gpupathtracer_b200/build.py` (or __graft_entry__.build()); "
                       "there is no fallback implementation" % LIB_PATH)
-lib = C.CDLL(LIB_PATH)
+
+
+class _LazyLibrary:
+    """The shared library is mapped on FIRST USE, not on import: `import gpupathtracer_b200.scenes` (pure-Python scene
+    descriptions, which bench.py's reference arm and the oracle tests share) must not pull the product library into a
+    process that is only supposed to run the CPU oracle.  Every attribute access goes through the real CDLL."""
+    _handle = None
+
+    def _load(self):
+        if _LazyLibrary._handle is None:
+            h = C.CDLL(LIB_PATH)
+            _bind(h)
+            _LazyLibrary._handle = h
+        return _LazyLibrary._handle
+
+    def __getattr__(self, name):
+        return getattr(self._load(), name)
+
+
+lib = _LazyLibrary()
 
 CAM_FORWARD, CAM_BACKWARD, CAM_LEFT, CAM_RIGHT, CAM_UP, CAM_DOWN, CAM_YAW_LEFT, CAM_YAW_RIGHT, CAM_PITCH_UP, CAM_PITCH_DOWN, CAM_RESET = range(11)
 INTEGRATOR_WAVEFRONT, INTEGRATOR_MEGAKERNEL, INTEGRATOR_AS_CODED = 0, 1, 2
@@ -78,79 +97,81 @@ class CSceneFile(C.Structure):
     _fields_ = [("camera", CCamera), ("params", CRenderParams), ("builder", C.c_int), ("n_geometries", C.c_int)]
 
 
-lib.ff_last_error.restype = C.c_char_p
-lib.ff_load_obj.restype = C.c_long
-lib.ff_load_obj.argtypes = [C.c_char_p, C.c_void_p, C.c_size_t]
-_vp, _sz = C.c_void_p, C.c_size_t
-lib.ff_context_create.argtypes = [C.POINTER(_vp), C.c_int]
-lib.ff_context_destroy.argtypes = [_vp]
-lib.ff_context_synchronize.argtypes = [_vp]
-lib.ff_timer_begin.argtypes = [_vp]
-lib.ff_scene_load_file.argtypes = [_vp, C.c_char_p, C.c_char_p, C.POINTER(_vp), C.POINTER(CSceneFile)]
-lib.ff_scene_file_validate.argtypes = [C.c_char_p, C.POINTER(CSceneFile)]
-lib.ff_context_release_scratch.argtypes = [_vp]
-lib.ff_timer_end.argtypes = [_vp, C.POINTER(C.c_double)]
-lib.ff_scene_create.argtypes = [_vp, C.POINTER(_vp)]
-lib.ff_scene_destroy.argtypes = [_vp]
-lib.ff_scene_add_obj.argtypes = [_vp, C.c_char_p, _vp, _vp, _vp, _vp, C.c_int, C.POINTER(C.c_int)]
-lib.ff_scene_add_triangles.argtypes = [_vp, _vp, _sz, _vp, _vp, _vp, _vp, C.POINTER(C.c_int)]
-lib.ff_scene_add_plane.argtypes = [_vp, _vp, _vp, _vp, _vp, C.POINTER(C.c_int)]
-lib.ff_scene_add_sphere.argtypes = [_vp, C.c_float, _vp, _vp, _vp, _vp, C.POINTER(C.c_int)]
-lib.ff_scene_set_normals.argtypes = [_vp, C.c_int, _vp]
-lib.ff_scene_set_uvs.argtypes = [_vp, C.c_int, _vp]
-lib.ff_scene_set_face_materials.argtypes = [_vp, C.c_int, _vp, _vp, C.c_int]
-lib.ff_scene_add_obj_ex.argtypes = [_vp, C.c_char_p, _vp, _vp, _vp, _vp, C.c_int, C.POINTER(C.c_int)]
-lib.ff_load_obj_ex.restype = C.c_long
-lib.ff_load_obj_ex.argtypes = [C.c_char_p, _vp, _vp, _vp, _vp, _sz, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int),
-                               C.POINTER(C.c_int), C.POINTER(C.c_double)]
-lib.ff_trace_closest_uv.argtypes = [_vp, _vp, _sz, C.c_int, _vp, _vp, _vp, _vp, _vp, C.POINTER(CStats)]
-lib.ff_scene_commit.argtypes = [_vp, C.c_int, C.POINTER(C.c_double)]
-lib.ff_scene_get_info.argtypes = [_vp, C.POINTER(CSceneInfo)]
-lib.ff_scene_get_flat.argtypes = [_vp, _vp, _vp, _vp, _sz]
-lib.ff_scene_get_matrices.argtypes = [_vp, C.c_int, _vp, _vp]
-lib.ff_trace_closest.argtypes = [_vp, _vp, _sz, C.c_int, _vp, _vp, _vp, C.POINTER(CStats)]
-lib.ff_trace_closest_device.argtypes = [_vp, _vp, _sz, C.c_int, _vp, C.POINTER(CStats)]
-lib.ff_trace_any.argtypes = [_vp, _vp, _vp, _sz, C.c_int, _vp, C.POINTER(CStats)]
-lib.ff_hits_unpack.argtypes = [_vp, _vp, _sz, _vp, _vp, _vp]
-lib.ff_camera_rays.argtypes = [_vp, C.POINTER(CCamera), _vp, _vp]
-lib.ff_camera_basis.argtypes = [C.POINTER(CCamera), _vp, _vp, _vp]
-lib.ff_camera_inverse_matrices.argtypes = [C.POINTER(CCamera), _vp, _vp]
-lib.ff_render.argtypes = [_vp, C.POINTER(CCamera), C.POINTER(CRenderParams), _vp, _vp, C.POINTER(CStats)]
-lib.ff_render_u8.argtypes = [_vp, C.POINTER(CCamera), C.POINTER(CRenderParams), _vp, C.c_int, C.POINTER(CStats)]
-lib.ff_render_accumulate.argtypes = [_vp, C.POINTER(CCamera), C.POINTER(CRenderParams), _vp, C.POINTER(CStats)]
-lib.ff_resolve.argtypes = [_vp, _vp, C.c_int, C.c_int, C.c_int, _vp, _vp]
-lib.ff_reduce_resolve_peers.argtypes = [_vp, C.POINTER(_vp), C.c_int, C.c_int, C.c_int, C.c_int, _vp, _vp]
-lib.ff_make_soup.argtypes = [_vp, _sz, C.c_float, _vp]
-lib.ff_make_rays_uniform.argtypes = [_vp, C.c_uint64, _sz, C.c_uint32, _vp, _vp]
-lib.ff_make_rays_bounce.argtypes = [_vp, _vp, _vp, _sz, C.c_uint64, _vp, C.POINTER(_sz)]
-lib.ff_device_malloc.argtypes = [_vp, _sz, C.POINTER(_vp)]
-lib.ff_device_free.argtypes = [_vp, _vp]
-lib.ff_device_memset.argtypes = [_vp, _vp, C.c_int, _sz]
-lib.ff_memcpy_h2d.argtypes = [_vp, _vp, _vp, _sz]
-lib.ff_memcpy_d2h.argtypes = [_vp, _vp, _vp, _sz]
-lib.ff_host_alloc_pinned.argtypes = [_sz, C.POINTER(_vp)]
-lib.ff_host_free_pinned.argtypes = [_vp]
-lib.ff_ipc_get_handle.argtypes = [_vp, _vp, _vp]
-lib.ff_ipc_open_handle.argtypes = [_vp, _vp, C.POINTER(_vp)]
-lib.ff_ipc_close_handle.argtypes = [_vp, _vp]
-lib.ff_flush_l2.argtypes = [_vp]
-lib.ff_write_image.argtypes = [C.c_char_p, _vp, C.c_int, C.c_int]
-lib.ff_write_image_u8.argtypes = [C.c_char_p, _vp, C.c_int, C.c_int]
-lib.ff_philox4x32_10.argtypes = [_vp, _vp, _vp]
-lib.ff_tile_owned_pixels.restype = C.c_long
-lib.ff_tile_owned_pixels.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _vp, _sz]
-lib.ff_camera_process_keyboard.argtypes = [C.POINTER(CCamera), C.c_int]
-lib.ff_camera_process_mouse.argtypes = [C.POINTER(CCamera), C.c_float, C.c_float, C.c_int]
-lib.ff_progressive_create.argtypes = [_vp, C.POINTER(_vp)]
-lib.ff_progressive_destroy.argtypes = [_vp]
-lib.ff_progressive_destroy.restype = None
-lib.ff_progressive_reset.argtypes = [_vp]
-lib.ff_progressive_frame.argtypes = [_vp, C.POINTER(CCamera), C.POINTER(CRenderParams), _vp, _vp, _vp, C.c_int, C.POINTER(C.c_int),
-                                     C.POINTER(CStats)]
-lib.ff_debug_node_stats.argtypes = [_vp, _vp, _vp]
-lib.ff_philox4x32_10.restype = None
-lib.ff_context_destroy.restype = None
-lib.ff_scene_destroy.restype = None
+def _bind(lib):
+    """argtypes / restypes of every entry point of include/firefly.h (run once, when the library is first used)."""
+    lib.ff_last_error.restype = C.c_char_p
+    lib.ff_load_obj.restype = C.c_long
+    lib.ff_load_obj.argtypes = [C.c_char_p, C.c_void_p, C.c_size_t]
+    _vp, _sz = C.c_void_p, C.c_size_t
+    lib.ff_context_create.argtypes = [C.POINTER(_vp), C.c_int]
+    lib.ff_context_destroy.argtypes = [_vp]
+    lib.ff_context_synchronize.argtypes = [_vp]
+    lib.ff_timer_begin.argtypes = [_vp]
+    lib.ff_scene_load_file.argtypes = [_vp, C.c_char_p, C.c_char_p, C.POINTER(_vp), C.POINTER(CSceneFile)]
+    lib.ff_scene_file_validate.argtypes = [C.c_char_p, C.POINTER(CSceneFile)]
+    lib.ff_context_release_scratch.argtypes = [_vp]
+    lib.ff_timer_end.argtypes = [_vp, C.POINTER(C.c_double)]
+    lib.ff_scene_create.argtypes = [_vp, C.POINTER(_vp)]
+    lib.ff_scene_destroy.argtypes = [_vp]
+    lib.ff_scene_add_obj.argtypes = [_vp, C.c_char_p, _vp, _vp, _vp, _vp, C.c_int, C.POINTER(C.c_int)]
+    lib.ff_scene_add_triangles.argtypes = [_vp, _vp, _sz, _vp, _vp, _vp, _vp, C.POINTER(C.c_int)]
+    lib.ff_scene_add_plane.argtypes = [_vp, _vp, _vp, _vp, _vp, C.POINTER(C.c_int)]
+    lib.ff_scene_add_sphere.argtypes = [_vp, C.c_float, _vp, _vp, _vp, _vp, C.POINTER(C.c_int)]
+    lib.ff_scene_set_normals.argtypes = [_vp, C.c_int, _vp]
+    lib.ff_scene_set_uvs.argtypes = [_vp, C.c_int, _vp]
+    lib.ff_scene_set_face_materials.argtypes = [_vp, C.c_int, _vp, _vp, C.c_int]
+    lib.ff_scene_add_obj_ex.argtypes = [_vp, C.c_char_p, _vp, _vp, _vp, _vp, C.c_int, C.POINTER(C.c_int)]
+    lib.ff_load_obj_ex.restype = C.c_long
+    lib.ff_load_obj_ex.argtypes = [C.c_char_p, _vp, _vp, _vp, _vp, _sz, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                   C.POINTER(C.c_int), C.POINTER(C.c_double)]
+    lib.ff_trace_closest_uv.argtypes = [_vp, _vp, _sz, C.c_int, _vp, _vp, _vp, _vp, _vp, C.POINTER(CStats)]
+    lib.ff_scene_commit.argtypes = [_vp, C.c_int, C.POINTER(C.c_double)]
+    lib.ff_scene_get_info.argtypes = [_vp, C.POINTER(CSceneInfo)]
+    lib.ff_scene_get_flat.argtypes = [_vp, _vp, _vp, _vp, _sz]
+    lib.ff_scene_get_matrices.argtypes = [_vp, C.c_int, _vp, _vp]
+    lib.ff_trace_closest.argtypes = [_vp, _vp, _sz, C.c_int, _vp, _vp, _vp, C.POINTER(CStats)]
+    lib.ff_trace_closest_device.argtypes = [_vp, _vp, _sz, C.c_int, _vp, C.POINTER(CStats)]
+    lib.ff_trace_any.argtypes = [_vp, _vp, _vp, _sz, C.c_int, _vp, C.POINTER(CStats)]
+    lib.ff_hits_unpack.argtypes = [_vp, _vp, _sz, _vp, _vp, _vp]
+    lib.ff_camera_rays.argtypes = [_vp, C.POINTER(CCamera), _vp, _vp]
+    lib.ff_camera_basis.argtypes = [C.POINTER(CCamera), _vp, _vp, _vp]
+    lib.ff_camera_inverse_matrices.argtypes = [C.POINTER(CCamera), _vp, _vp]
+    lib.ff_render.argtypes = [_vp, C.POINTER(CCamera), C.POINTER(CRenderParams), _vp, _vp, C.POINTER(CStats)]
+    lib.ff_render_u8.argtypes = [_vp, C.POINTER(CCamera), C.POINTER(CRenderParams), _vp, C.c_int, C.POINTER(CStats)]
+    lib.ff_render_accumulate.argtypes = [_vp, C.POINTER(CCamera), C.POINTER(CRenderParams), _vp, C.POINTER(CStats)]
+    lib.ff_resolve.argtypes = [_vp, _vp, C.c_int, C.c_int, C.c_int, _vp, _vp]
+    lib.ff_reduce_resolve_peers.argtypes = [_vp, C.POINTER(_vp), C.c_int, C.c_int, C.c_int, C.c_int, _vp, _vp]
+    lib.ff_make_soup.argtypes = [_vp, _sz, C.c_float, _vp]
+    lib.ff_make_rays_uniform.argtypes = [_vp, C.c_uint64, _sz, C.c_uint32, _vp, _vp]
+    lib.ff_make_rays_bounce.argtypes = [_vp, _vp, _vp, _sz, C.c_uint64, _vp, C.POINTER(_sz)]
+    lib.ff_device_malloc.argtypes = [_vp, _sz, C.POINTER(_vp)]
+    lib.ff_device_free.argtypes = [_vp, _vp]
+    lib.ff_device_memset.argtypes = [_vp, _vp, C.c_int, _sz]
+    lib.ff_memcpy_h2d.argtypes = [_vp, _vp, _vp, _sz]
+    lib.ff_memcpy_d2h.argtypes = [_vp, _vp, _vp, _sz]
+    lib.ff_host_alloc_pinned.argtypes = [_sz, C.POINTER(_vp)]
+    lib.ff_host_free_pinned.argtypes = [_vp]
+    lib.ff_ipc_get_handle.argtypes = [_vp, _vp, _vp]
+    lib.ff_ipc_open_handle.argtypes = [_vp, _vp, C.POINTER(_vp)]
+    lib.ff_ipc_close_handle.argtypes = [_vp, _vp]
+    lib.ff_flush_l2.argtypes = [_vp]
+    lib.ff_write_image.argtypes = [C.c_char_p, _vp, C.c_int, C.c_int]
+    lib.ff_write_image_u8.argtypes = [C.c_char_p, _vp, C.c_int, C.c_int]
+    lib.ff_philox4x32_10.argtypes = [_vp, _vp, _vp]
+    lib.ff_tile_owned_pixels.restype = C.c_long
+    lib.ff_tile_owned_pixels.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _vp, _sz]
+    lib.ff_camera_process_keyboard.argtypes = [C.POINTER(CCamera), C.c_int]
+    lib.ff_camera_process_mouse.argtypes = [C.POINTER(CCamera), C.c_float, C.c_float, C.c_int]
+    lib.ff_progressive_create.argtypes = [_vp, C.POINTER(_vp)]
+    lib.ff_progressive_destroy.argtypes = [_vp]
+    lib.ff_progressive_destroy.restype = None
+    lib.ff_progressive_reset.argtypes = [_vp]
+    lib.ff_progressive_frame.argtypes = [_vp, C.POINTER(CCamera), C.POINTER(CRenderParams), _vp, _vp, _vp, C.c_int, C.POINTER(C.c_int),
+                                         C.POINTER(CStats)]
+    lib.ff_debug_node_stats.argtypes = [_vp, _vp, _vp]
+    lib.ff_philox4x32_10.restype = None
+    lib.ff_context_destroy.restype = None
+    lib.ff_scene_destroy.restype = None
 
 
 def _check(rc):

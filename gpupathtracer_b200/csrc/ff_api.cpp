@@ -85,6 +85,7 @@ struct ff_scene {
     float4* d_bvh2_lo = nullptr;
     float4* d_bvh2_hi = nullptr;
     uint32_t* d_leaf_slot = nullptr;
+    float4* d_as_coded_normals = nullptr;  // per flat triangle, built by the first as-coded frame after a commit (ensure_as_coded_normals)
     cudaTextureObject_t nodes_tex = 0, tris_tex = 0;  // kernel variants FF_NODE_TEX / FF_TRI_TEX only
     DevScene dev;
     ff_scene_info info;
@@ -96,6 +97,8 @@ struct ff_scene {
     float4* d_accum = nullptr;
     float4* d_out = nullptr;
     size_t fb_pixels = 0;
+    unsigned char* d_u8 = nullptr;  // device staging of ff_render_u8 when the caller's buffer is host memory
+    size_t u8_bytes = 0;
     // tile split: owned-pixel list of the last (width, height, tile, rank, world) rendered
     uint32_t* d_pixel_map = nullptr;
     size_t pixel_map_count = 0;
@@ -112,6 +115,7 @@ static void free_scene_device(ff_scene* s) {
     cudaFree(s->d_flat); cudaFree(s->d_tris); cudaFree(s->d_nodes); cudaFree(s->d_ord_geom); cudaFree(s->d_ord_tri);
     cudaFree(s->d_materials); cudaFree(s->d_planes); cudaFree(s->d_bvh2_children); cudaFree(s->d_bvh2_lo);
     cudaFree(s->d_bvh2_hi); cudaFree(s->d_leaf_slot); cudaFree(s->d_lights); s->d_lights = nullptr;
+    cudaFree(s->d_as_coded_normals); s->d_as_coded_normals = nullptr;
     cudaFree(s->d_geom_attr); cudaFree(s->d_attr_normals); cudaFree(s->d_attr_uvs); cudaFree(s->d_attr_facemat);
     s->d_geom_attr = nullptr; s->d_attr_normals = nullptr; s->d_attr_uvs = nullptr; s->d_attr_facemat = nullptr;
     s->d_flat = s->d_tris = s->d_nodes = nullptr; s->d_ord_geom = s->d_ord_tri = nullptr; s->d_materials = nullptr;
@@ -125,7 +129,19 @@ static void free_render_scratch(ff_scene* s) {
     s->wb_capacity = 0; s->wb_counts = 0; s->wb_shadow = false;
     cudaFree(s->d_accum); cudaFree(s->d_out); s->d_accum = s->d_out = nullptr; s->fb_pixels = 0;
     cudaFree(s->d_pixel_map); s->d_pixel_map = nullptr; s->pixel_map_count = 0;
+    cudaFree(s->d_u8); s->d_u8 = nullptr; s->u8_bytes = 0;
 }
+
+// Device temporary that is released on every exit path (FF_CUDA / FF_REQUIRE return early).
+struct DevTmp {
+    void* p = nullptr;
+    DevTmp() = default;
+    DevTmp(const DevTmp&) = delete;
+    DevTmp& operator=(const DevTmp&) = delete;
+    ~DevTmp() { if (p) cudaFree(p); }
+    cudaError_t alloc(size_t bytes) { if (p) { cudaFree(p); p = nullptr; } return bytes ? cudaMalloc(&p, bytes) : cudaSuccess; }
+    template <class T> T* as() const { return (T*)p; }
+};
 
 template <class T>
 static cudaError_t upload(T** dptr, const std::vector<T>& h, cudaStream_t st) {
@@ -519,17 +535,21 @@ int ff_scene_commit(ff_scene* scene, int builder, double* out_build_ms) {
     uint32_t launches = 0;
     if (n_tris) {
         // stage object-space triangles, bake on the device (same single-rounding op order as the reference's M * v)
-        float* d_obj = nullptr; M4* d_models = nullptr; uint32_t *d_geom_of = nullptr, *d_ord_of = nullptr;
-        FF_CUDA(cudaMalloc((void**)&d_obj, sizeof(float) * 9 * n_tris));
+        DevTmp t_obj, t_models, t_geom_of, t_ord_of;  // released on every exit path
+        FF_CUDA(t_obj.alloc(sizeof(float) * 9 * n_tris));
+        FF_CUDA(t_models.alloc(sizeof(M4) * models.size()));
+        FF_CUDA(t_geom_of.alloc(sizeof(uint32_t) * n_tris));
+        FF_CUDA(t_ord_of.alloc(sizeof(uint32_t) * n_tris));
+        float* d_obj = t_obj.as<float>();
         size_t off = 0;
         for (auto& g : scene->geoms) {
             if (g.type != 2 || g.xyz9.empty()) continue;
             FF_CUDA(cudaMemcpyAsync(d_obj + off, g.xyz9.data(), sizeof(float) * g.xyz9.size(), cudaMemcpyHostToDevice, st));
             off += g.xyz9.size();
         }
-        FF_CUDA(upload(&d_models, models, st));
-        FF_CUDA(upload(&d_geom_of, geom_of, st));
-        FF_CUDA(upload(&d_ord_of, ord_of, st));
+        FF_CUDA(cudaMemcpyAsync(t_models.p, models.data(), sizeof(M4) * models.size(), cudaMemcpyHostToDevice, st));
+        FF_CUDA(cudaMemcpyAsync(t_geom_of.p, geom_of.data(), sizeof(uint32_t) * n_tris, cudaMemcpyHostToDevice, st));
+        FF_CUDA(cudaMemcpyAsync(t_ord_of.p, ord_of.data(), sizeof(uint32_t) * n_tris, cudaMemcpyHostToDevice, st));
         FF_CUDA(cudaMalloc((void**)&scene->d_flat, sizeof(float4) * 3 * n_tris));
         FF_CUDA(cudaMalloc((void**)&scene->d_tris, sizeof(float4) * 3 * n_tris));
         const uint32_t node_cap = (uint32_t)(n_tris / 2 + 64);
@@ -538,9 +558,9 @@ int ff_scene_commit(ff_scene* scene, int builder, double* out_build_ms) {
         FF_CUDA(cudaMalloc((void**)&scene->d_bvh2_lo, sizeof(float4) * 2 * n_tris));
         FF_CUDA(cudaMalloc((void**)&scene->d_bvh2_hi, sizeof(float4) * 2 * n_tris));
         FF_CUDA(cudaMalloc((void**)&scene->d_leaf_slot, sizeof(uint32_t) * n_tris));
-        k_bake_triangles(d_obj, d_models, d_geom_of, d_ord_of, (uint32_t)n_tris, scene->d_flat, st);
+        k_bake_triangles(d_obj, t_models.as<M4>(), t_geom_of.as<uint32_t>(), t_ord_of.as<uint32_t>(), (uint32_t)n_tris, scene->d_flat, st);
         FF_CUDA(cudaStreamSynchronize(st));
-        cudaFree(d_obj); cudaFree(d_models); cudaFree(d_geom_of); cudaFree(d_ord_of);
+        t_obj.alloc(0); t_models.alloc(0); t_geom_of.alloc(0); t_ord_of.alloc(0);  // give the staging back before the build
         // the conservative pad needs the scene's largest |coordinate|: take it from the host copies' model-space
         // bounds pushed through |M| (cheap upper bound), refined by the device bounds after the build
         for (auto& g : scene->geoms) {
@@ -713,14 +733,14 @@ int ff_hits_unpack(ff_scene* scene, const void* d_hits, size_t n, int* out_geom,
     if (rc) return rc;
     if (n == 0) return FF_OK;
     cudaStream_t st = scene->ctx->stream;
-    int *dg = nullptr, *dt = nullptr; float* dk = nullptr;
-    FF_CUDA(cudaMalloc((void**)&dg, sizeof(int) * n)); FF_CUDA(cudaMalloc((void**)&dt, sizeof(int) * n)); FF_CUDA(cudaMalloc((void**)&dk, sizeof(float) * n));
+    DevTmp tg, tt, tk;
+    FF_CUDA(tg.alloc(sizeof(int) * n)); FF_CUDA(tt.alloc(sizeof(int) * n)); FF_CUDA(tk.alloc(sizeof(float) * n));
+    int *dg = tg.as<int>(), *dt = tt.as<int>(); float* dk = tk.as<float>();
     k_unpack_hits(scene->dev, (const HitRec*)d_hits, n, dg, dt, dk, st);
     if (out_geom) FF_CUDA(cudaMemcpyAsync(out_geom, dg, sizeof(int) * n, cudaMemcpyDeviceToHost, st));
     if (out_tri) FF_CUDA(cudaMemcpyAsync(out_tri, dt, sizeof(int) * n, cudaMemcpyDeviceToHost, st));
     if (out_t) FF_CUDA(cudaMemcpyAsync(out_t, dk, sizeof(float) * n, cudaMemcpyDeviceToHost, st));
     FF_CUDA(cudaStreamSynchronize(st));
-    cudaFree(dg); cudaFree(dt); cudaFree(dk);
     return FF_OK;
 }
 
@@ -737,13 +757,15 @@ int ff_trace_closest_uv(ff_scene* scene, const float* rays6, size_t n, int mode,
     if (n == 0) return FF_OK;
     ff_context* c = scene->ctx;
     cudaStream_t st = c->stream;
-    float* d6 = nullptr; float4* dr = nullptr; HitRec* dh = nullptr;
-    int *dg = nullptr, *dt = nullptr; float* dk = nullptr; float* duv = nullptr;
-    FF_CUDA(cudaMalloc((void**)&d6, sizeof(float) * 6 * n));
-    FF_CUDA(cudaMalloc((void**)&dr, sizeof(float4) * 2 * n));
-    FF_CUDA(cudaMalloc((void**)&dh, sizeof(HitRec) * n));
-    FF_CUDA(cudaMalloc((void**)&dg, sizeof(int) * n)); FF_CUDA(cudaMalloc((void**)&dt, sizeof(int) * n)); FF_CUDA(cudaMalloc((void**)&dk, sizeof(float) * n));
-    if (out_u || out_v) FF_CUDA(cudaMalloc((void**)&duv, sizeof(float) * 2 * n));
+    FF_REQUIRE(n < 0xffffffffull, "ff_trace_closest: batch too large");
+    DevTmp t6, tr, th, tg, tt, tk, tuv;  // released on every exit path
+    FF_CUDA(t6.alloc(sizeof(float) * 6 * n));
+    FF_CUDA(tr.alloc(sizeof(float4) * 2 * n));
+    FF_CUDA(th.alloc(sizeof(HitRec) * n));
+    FF_CUDA(tg.alloc(sizeof(int) * n)); FF_CUDA(tt.alloc(sizeof(int) * n)); FF_CUDA(tk.alloc(sizeof(float) * n));
+    if (out_u || out_v) FF_CUDA(tuv.alloc(sizeof(float) * 2 * n));
+    float* d6 = t6.as<float>(); float4* dr = tr.as<float4>(); HitRec* dh = th.as<HitRec>();
+    int *dg = tg.as<int>(), *dt = tt.as<int>(); float* dk = tk.as<float>(); float* duv = tuv.as<float>();
     double h2d, d2h;
     {
         ScopedTimer t(c, 2, 3);
@@ -769,7 +791,6 @@ int ff_trace_closest_uv(ff_scene* scene, const float* rays6, size_t n, int mode,
         if (e != cudaSuccess) { set_error(cudaGetErrorString(e)); rc = FF_ERR_CUDA; }
         if (stats) { *stats = inner; stats->h2d_ms = h2d; stats->d2h_ms = d2h; stats->gpu_ms += h2d + d2h; stats->kernel_launches += 2; }
     }
-    cudaFree(d6); cudaFree(dr); cudaFree(dh); cudaFree(dg); cudaFree(dt); cudaFree(dk); cudaFree(duv);
     return rc;
 }
 
@@ -782,11 +803,14 @@ int ff_trace_any(ff_scene* scene, const float* rays6, const float* tmax, size_t 
     if (n == 0) return FF_OK;
     ff_context* c = scene->ctx;
     cudaStream_t st = c->stream;
-    float* d6 = nullptr; float4* dr = nullptr; float* dtm = nullptr; unsigned char* docc = nullptr;
-    FF_CUDA(cudaMalloc((void**)&d6, sizeof(float) * 6 * n));
-    FF_CUDA(cudaMalloc((void**)&dr, sizeof(float4) * 2 * n));
-    FF_CUDA(cudaMalloc((void**)&docc, n));
-    if (tmax) { FF_CUDA(cudaMalloc((void**)&dtm, sizeof(float) * n)); FF_CUDA(cudaMemcpyAsync(dtm, tmax, sizeof(float) * n, cudaMemcpyHostToDevice, st)); }
+    FF_REQUIRE(n < 0xffffffffull, "ff_trace_any: batch too large");
+    DevTmp t6, tr, ttm, tocc;  // released on every exit path
+    FF_CUDA(t6.alloc(sizeof(float) * 6 * n));
+    FF_CUDA(tr.alloc(sizeof(float4) * 2 * n));
+    FF_CUDA(tocc.alloc(n));
+    float* d6 = t6.as<float>(); float4* dr = tr.as<float4>(); unsigned char* docc = tocc.as<unsigned char>();
+    if (tmax) { FF_CUDA(ttm.alloc(sizeof(float) * n)); FF_CUDA(cudaMemcpyAsync(ttm.p, tmax, sizeof(float) * n, cudaMemcpyHostToDevice, st)); }
+    float* dtm = ttm.as<float>();
     FF_CUDA(cudaMemcpyAsync(d6, rays6, sizeof(float) * 6 * n, cudaMemcpyHostToDevice, st));
     k_pack_rays(d6, n, dr, dr + n, st);
     if ((rc = ensure_counters(scene))) return rc;
@@ -794,9 +818,9 @@ int ff_trace_any(ff_scene* scene, const float* rays6, const float* tmax, size_t 
     ScopedTimer t(c, 0, 1);
     k_trace_any(scene->dev, dr, dr + n, dtm, (uint32_t)n, mode, docc, scene->d_work_counter, st);
     const double ms = t.stop();
+    FF_CUDA(cudaGetLastError());
     FF_CUDA(cudaMemcpy(out_occluded, docc, n, cudaMemcpyDeviceToHost));
     if (stats) { stats->gpu_ms = ms; stats->trace_ms = ms; stats->shadow_rays = n; stats->kernel_launches = 2; }
-    cudaFree(d6); cudaFree(dr); cudaFree(dtm); cudaFree(docc);
     return FF_OK;
 }
 
@@ -849,19 +873,17 @@ int ff_camera_rays(ff_context* ctx, const ff_camera* cam, float* rays6_host, voi
     if (rc) return rc;
     FF_CUDA(cudaSetDevice(ctx->device));
     const size_t n = (size_t)cam->width * cam->height;
+    DevTmp tr, t6;
     float4* dr = (float4*)d_rays;
-    if (!dr) FF_CUDA(cudaMalloc((void**)&dr, sizeof(float4) * 2 * n));
+    if (!dr) { FF_CUDA(tr.alloc(sizeof(float4) * 2 * n)); dr = tr.as<float4>(); }
     k_camera_rays(make_cam(cam), dr, dr + n, ctx->stream);
     if (rays6_host) {
-        float* d6 = nullptr;
-        FF_CUDA(cudaMalloc((void**)&d6, sizeof(float) * 6 * n));
-        k_unpack_rays(dr, dr + n, n, d6, ctx->stream);
-        FF_CUDA(cudaMemcpyAsync(rays6_host, d6, sizeof(float) * 6 * n, cudaMemcpyDeviceToHost, ctx->stream));
-        FF_CUDA(cudaStreamSynchronize(ctx->stream));
-        cudaFree(d6);
+        FF_CUDA(t6.alloc(sizeof(float) * 6 * n));
+        k_unpack_rays(dr, dr + n, n, t6.as<float>(), ctx->stream);
+        FF_CUDA(cudaMemcpyAsync(rays6_host, t6.p, sizeof(float) * 6 * n, cudaMemcpyDeviceToHost, ctx->stream));
     }
     FF_CUDA(cudaStreamSynchronize(ctx->stream));
-    if (!d_rays) cudaFree(dr);
+    FF_CUDA(cudaGetLastError());
     return FF_OK;
 }
 
@@ -908,6 +930,50 @@ int ensure_fb(ff_scene* s, size_t npix) {
         FF_CUDA(cudaMalloc((void**)&s->d_out, sizeof(float4) * npix));
         s->fb_pixels = npix;
     }
+    return FF_OK;
+}
+int ensure_u8(ff_scene* s, size_t bytes) {
+    if (s->u8_bytes < bytes) {
+        cudaFree(s->d_u8); s->d_u8 = nullptr; s->u8_bytes = 0;
+        FF_CUDA(cudaMalloc((void**)&s->d_u8, bytes));
+        s->u8_bytes = bytes;
+    }
+    return FF_OK;
+}
+// The normal the reference's frame shows for a mesh hit is inverse(transpose(M)) * the OBJECT-space unit normal
+// (kernel.cu:101,117), which the baked world-space triangles cannot give back (a scale changes its length).  The first
+// as-coded frame after a commit builds it per flat triangle from the host copy of the object-space vertices (16 B per
+// triangle, only for scenes that are ever rendered as-coded).
+int ensure_as_coded_normals(ff_scene* scene) {
+    if (scene->d_as_coded_normals || scene->dev.n_tris == 0) return FF_OK;
+    cudaStream_t st = scene->ctx->stream;
+    const size_t n_tris = scene->dev.n_tris;
+    std::vector<M4> nrm(scene->geoms.size());
+    std::vector<uint32_t> geom_of(n_tris);
+    DevTmp t_obj, t_nrm, t_geom;
+    FF_CUDA(t_obj.alloc(sizeof(float) * 9 * n_tris));
+    size_t off = 0, flat = 0;
+    for (size_t gi = 0; gi < scene->geoms.size(); ++gi) {
+        const HostGeom& g = scene->geoms[gi];
+        nrm[gi] = ffh::inverted(ffh::transposed(g.model));
+        if (g.type != 2 || g.xyz9.empty()) continue;
+        FF_REQUIRE(off + g.xyz9.size() <= 9 * n_tris, "as-coded frame: geometry was edited after the commit");
+        FF_CUDA(cudaMemcpyAsync(t_obj.as<float>() + off, g.xyz9.data(), sizeof(float) * g.xyz9.size(), cudaMemcpyHostToDevice, st));
+        off += g.xyz9.size();
+        for (size_t t = 0; t < g.xyz9.size() / 9; ++t) geom_of[flat++] = (uint32_t)gi;
+    }
+    FF_REQUIRE(flat == n_tris, "as-coded frame: geometry was edited after the commit");
+    FF_CUDA(t_nrm.alloc(sizeof(M4) * nrm.size()));
+    FF_CUDA(t_geom.alloc(sizeof(uint32_t) * n_tris));
+    FF_CUDA(cudaMemcpyAsync(t_nrm.p, nrm.data(), sizeof(M4) * nrm.size(), cudaMemcpyHostToDevice, st));
+    FF_CUDA(cudaMemcpyAsync(t_geom.p, geom_of.data(), sizeof(uint32_t) * n_tris, cudaMemcpyHostToDevice, st));
+    float4* out = nullptr;
+    FF_CUDA(cudaMalloc((void**)&out, sizeof(float4) * n_tris));
+    k_as_coded_normals(t_obj.as<float>(), t_nrm.as<M4>(), t_geom.as<uint32_t>(), (uint32_t)n_tris, out, st);
+    cudaError_t e = cudaStreamSynchronize(st);
+    if (e == cudaSuccess) e = cudaGetLastError();
+    if (e != cudaSuccess) { cudaFree(out); set_error(std::string("as-coded normals: ") + cudaGetErrorString(e)); return FF_ERR_CUDA; }
+    scene->d_as_coded_normals = out;
     return FF_OK;
 }
 int check_params(const ff_render_params* p, const char* who) {
@@ -1092,18 +1158,15 @@ int ff_render(ff_scene* scene, const ff_camera* cam, const ff_render_params* par
     const size_t npix = (size_t)cam->width * cam->height;
     if ((rc = ensure_fb(scene, npix))) return rc;
     if ((params->integrator & 0xff) == FF_INTEGRATOR_AS_CODED) {
-        // 8-bit as-coded frame widened to float RGBA (value / 255), for callers that want one code path
-        unsigned char* d_rgb = nullptr;
-        FF_CUDA(cudaMalloc((void**)&d_rgb, npix * 3));
-        rc = ff_render_u8(scene, cam, params, d_rgb, 1, stats);
-        std::vector<unsigned char> h(npix * 3);
-        if (rc == FF_OK) FF_CUDA(cudaMemcpy(h.data(), d_rgb, npix * 3, cudaMemcpyDeviceToHost));
-        cudaFree(d_rgb);
-        if (rc) return rc;
-        std::vector<float> f(npix * 4);
-        for (size_t i = 0; i < npix; ++i) { for (int k = 0; k < 3; ++k) f[4 * i + k] = h[3 * i + k] / 255.0f; f[4 * i + 3] = 1.0f; }
-        if (out_rgba_host) memcpy(out_rgba_host, f.data(), sizeof(float) * 4 * npix);
-        if (out_rgba_device) FF_CUDA(cudaMemcpy(out_rgba_device, f.data(), sizeof(float) * 4 * npix, cudaMemcpyHostToDevice));
+        // 8-bit as-coded frame widened to float RGBA (value / 255) on the device, for callers that want one code path
+        if ((rc = ensure_u8(scene, npix * 3))) return rc;
+        if ((rc = ff_render_u8(scene, cam, params, scene->d_u8, 1, stats))) return rc;
+        float4* d_out = out_rgba_device ? (float4*)out_rgba_device : scene->d_out;
+        k_u8_to_rgba(scene->d_u8, (uint32_t)npix, d_out, c->stream);
+        if (out_rgba_host) FF_CUDA(cudaMemcpyAsync(out_rgba_host, d_out, sizeof(float4) * npix, cudaMemcpyDeviceToHost, c->stream));
+        FF_CUDA(cudaStreamSynchronize(c->stream));
+        FF_CUDA(cudaGetLastError());
+        if (stats) stats->kernel_launches += 1;
         return FF_OK;
     }
     const int integ = params->integrator & 0xff;
@@ -1141,26 +1204,26 @@ int ff_render_u8(ff_scene* scene, const ff_camera* cam, const ff_render_params* 
     ff_context* c = scene->ctx;
     const size_t npix = (size_t)cam->width * cam->height;
     unsigned char* d_rgb = out_is_device ? out_rgb : nullptr;
-    if (!d_rgb) FF_CUDA(cudaMalloc((void**)&d_rgb, npix * 3));
+    if (!d_rgb) {  // host output: staging owned by the scene, grown on demand (no allocation per frame)
+        if ((rc = ensure_u8(scene, npix * 3))) return rc;
+        d_rgb = scene->d_u8;
+    }
     if ((params->integrator & 0xff) == FF_INTEGRATOR_AS_CODED) {
         if (stats) memset(stats, 0, sizeof(*stats));
+        if ((rc = ensure_as_coded_normals(scene))) return rc;
         ScopedTimer t(c, 0, 1);
-        k_as_coded(scene->dev, make_cam(cam), d_rgb, c->stream);
+        k_as_coded(scene->dev, make_cam(cam), scene->d_as_coded_normals, d_rgb, c->stream);
         const double ms = t.stop();
         FF_CUDA(cudaGetLastError());
         if (stats) { stats->gpu_ms = ms; stats->trace_ms = ms; stats->rays = npix; stats->paths = npix; stats->kernel_launches = 1; }
     } else {
         if ((rc = ensure_fb(scene, npix))) return rc;
-        rc = ff_render(scene, cam, params, nullptr, scene->d_out, stats);
-        if (rc) { if (!out_is_device) cudaFree(d_rgb); return rc; }
+        if ((rc = ff_render(scene, cam, params, nullptr, scene->d_out, stats))) return rc;
         k_rgba_to_u8(scene->d_out, (uint32_t)npix, d_rgb, c->stream);
         FF_CUDA(cudaStreamSynchronize(c->stream));
         if (stats) stats->kernel_launches += 1;
     }
-    if (!out_is_device) {
-        FF_CUDA(cudaMemcpy(out_rgb, d_rgb, npix * 3, cudaMemcpyDeviceToHost));
-        cudaFree(d_rgb);
-    }
+    if (!out_is_device) FF_CUDA(cudaMemcpy(out_rgb, d_rgb, npix * 3, cudaMemcpyDeviceToHost));
     return FF_OK;
 }
 
@@ -1169,31 +1232,28 @@ int ff_make_soup(ff_context* ctx, size_t n_tris, float s, float* xyz9_host) {
     FF_REQUIRE(ctx && (xyz9_host || n_tris == 0), "ff_make_soup: NULL argument");
     if (!n_tris) return FF_OK;
     FF_CUDA(cudaSetDevice(ctx->device));
-    float* d = nullptr;
-    FF_CUDA(cudaMalloc((void**)&d, sizeof(float) * 9 * n_tris));
-    k_make_soup(n_tris, s, d, ctx->stream);
-    FF_CUDA(cudaMemcpyAsync(xyz9_host, d, sizeof(float) * 9 * n_tris, cudaMemcpyDeviceToHost, ctx->stream));
+    DevTmp td;
+    FF_CUDA(td.alloc(sizeof(float) * 9 * n_tris));
+    k_make_soup(n_tris, s, td.as<float>(), ctx->stream);
+    FF_CUDA(cudaMemcpyAsync(xyz9_host, td.p, sizeof(float) * 9 * n_tris, cudaMemcpyDeviceToHost, ctx->stream));
     FF_CUDA(cudaStreamSynchronize(ctx->stream));
-    cudaFree(d);
     return FF_OK;
 }
 int ff_make_rays_uniform(ff_context* ctx, uint64_t first, size_t n, uint32_t salt, float* rays6_host, void* d_rays) {
     FF_REQUIRE(ctx, "ff_make_rays_uniform: NULL context");
     if (!n) return FF_OK;
     FF_CUDA(cudaSetDevice(ctx->device));
+    DevTmp tr, t6;
     float4* dr = (float4*)d_rays;
-    if (!dr) FF_CUDA(cudaMalloc((void**)&dr, sizeof(float4) * 2 * n));
+    if (!dr) { FF_CUDA(tr.alloc(sizeof(float4) * 2 * n)); dr = tr.as<float4>(); }
     k_make_rays_uniform(first, n, salt, dr, dr + n, ctx->stream);
     if (rays6_host) {
-        float* d6 = nullptr;
-        FF_CUDA(cudaMalloc((void**)&d6, sizeof(float) * 6 * n));
-        k_unpack_rays(dr, dr + n, n, d6, ctx->stream);
-        FF_CUDA(cudaMemcpyAsync(rays6_host, d6, sizeof(float) * 6 * n, cudaMemcpyDeviceToHost, ctx->stream));
-        FF_CUDA(cudaStreamSynchronize(ctx->stream));
-        cudaFree(d6);
+        FF_CUDA(t6.alloc(sizeof(float) * 6 * n));
+        k_unpack_rays(dr, dr + n, n, t6.as<float>(), ctx->stream);
+        FF_CUDA(cudaMemcpyAsync(rays6_host, t6.p, sizeof(float) * 6 * n, cudaMemcpyDeviceToHost, ctx->stream));
     }
     FF_CUDA(cudaStreamSynchronize(ctx->stream));
-    if (!d_rays) cudaFree(dr);
+    FF_CUDA(cudaGetLastError());
     return FF_OK;
 }
 int ff_make_rays_bounce(ff_scene* scene, const void* d_rays_in, const void* d_hits_in, size_t n, uint64_t seed, void* d_rays_out, size_t* out_n) {
@@ -1401,7 +1461,10 @@ int ff_progressive_frame(ff_progressive* p, const ff_camera* cam, const ff_rende
         const ff_render_params& a = p->params;
         return memcmp(&p->cam, cam, sizeof(ff_camera)) == 0 && a.max_bounces == params->max_bounces && a.seed == params->seed &&
                (a.integrator & 0xff) == (params->integrator & 0xff) && a.nee == params->nee && a.aa == params->aa &&
-               memcmp(a.background, params->background, sizeof(a.background)) == 0 && a.ray_eps == params->ray_eps;
+               memcmp(a.background, params->background, sizeof(a.background)) == 0 && a.ray_eps == params->ray_eps &&
+               // the tile split decides WHICH pixels this rank accumulates: a changed split must not add to stale pixels
+               (a.tile_world > 1 ? a.tile_world : 1) == (params->tile_world > 1 ? params->tile_world : 1) &&
+               (params->tile_world <= 1 || (a.tile_rank == params->tile_rank && (a.tile_size > 0 ? a.tile_size : 32) == (params->tile_size > 0 ? params->tile_size : 32)));
     };
     if (!p->valid || !same_image() || (long long)p->accumulated + params->spp > 0x7fffffffll) {
         FF_CUDA(cudaMemsetAsync(p->d_accum, 0, sizeof(float4) * npix, c->stream));

@@ -57,7 +57,30 @@ __global__ void bake_kernel(const float* __restrict__ xyz9, const M4* __restrict
 }
 void k_bake_triangles(const float* d_xyz9_obj, const M4* d_model_per_geom, const uint32_t* d_geom_of_flat,
                       const uint32_t* d_ord_of_flat, uint32_t n, float4* d_flat_tris, cudaStream_t st) {
-    if (n) bake_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(d_xyz9_obj, d_model_per_geom, d_geom_of_flat, d_ord_of_flat, n, d_flat_tris);
+    if (n) bake_kernel<<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(d_xyz9_obj, d_model_per_geom, d_geom_of_flat, d_ord_of_flat, n, d_flat_tris);
+}
+
+// As-coded shading normal of every triangle, flat order: inverse(transpose(M)) * vec4(normalize(cross(e1, e2)), 0) with
+// OBJECT-space edges -- what intersectTriangle leaves in m_normal (kernel.cu:101) pushed through setIntersection
+// (kernel.cu:117), un-normalised, so a mesh scaled by s comes out 1/s as bright, exactly as in the reference's frame.
+__global__ void as_coded_normals_kernel(const float* __restrict__ xyz9, const M4* __restrict__ nrm_of_geom, const uint32_t* __restrict__ geom_of,
+                                        uint32_t n, float4* __restrict__ out) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const M4 m = nrm_of_geom[geom_of[i]];
+        const float* p = xyz9 + 9 * (size_t)i;
+        const V3 v0 = v3(p[0], p[1], p[2]), v1 = v3(p[3], p[4], p[5]), v2 = v3(p[6], p[7], p[8]);
+        const V3 no = normalize(cross(sub(v1, v0), sub(v2, v0)));
+        float4 w;  // glm mat4 * vec4(no, 0) (type_mat4x4.inl:536-575)
+        w.x = fadd(fadd(fmul(m.c[0].x, no.x), fmul(m.c[1].x, no.y)), fadd(fmul(m.c[2].x, no.z), fmul(m.c[3].x, 0.0f)));
+        w.y = fadd(fadd(fmul(m.c[0].y, no.x), fmul(m.c[1].y, no.y)), fadd(fmul(m.c[2].y, no.z), fmul(m.c[3].y, 0.0f)));
+        w.z = fadd(fadd(fmul(m.c[0].z, no.x), fmul(m.c[1].z, no.y)), fadd(fmul(m.c[2].z, no.z), fmul(m.c[3].z, 0.0f)));
+        w.w = 0.f;
+        out[i] = w;
+    }
+}
+void k_as_coded_normals(const float* d_xyz9_obj, const M4* d_nrm_per_geom, const uint32_t* d_geom_of_flat, uint32_t n,
+                        float4* d_out, cudaStream_t st) {
+    if (n) as_coded_normals_kernel<<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(d_xyz9_obj, d_nrm_per_geom, d_geom_of_flat, n, d_out);
 }
 
 // ------------------------------------------------------------------ bounds
@@ -342,17 +365,18 @@ __global__ void refit_kernel(const float4* __restrict__ flat_tris, const uint32_
         for (;;) {
             const uint32_t p = parent[node];
             if (p == 0xffffffffu) break;
-            // Release: this thread's box and table must be visible before its arrival is counted.  The second arrival reads
-            // them with volatile (L1-bypassing) loads that issue only after its own atomic has returned, so it needs no fence
-            // of its own; the fence.sc + L1 invalidate that __threadfence() costs twice per level was 39 % of the kernel's
-            // stall samples (profiles/r01i_refit_before_stalls.txt).
+            // acq_rel: RELEASE so this thread's box and table are visible before its arrival is counted; ACQUIRE so the second
+            // arrival's loads of its sibling's box and table are ordered after the atomic by the PTX memory model itself (a
+            // compiler barrier plus a control dependency is not an ordering there).  One atomic instead of the fence.sc + L1
+            // invalidate that __threadfence() cost twice per level (39 % of the kernel's stall samples,
+            // profiles/r01i_refit_before_stalls.txt); the loads below additionally bypass L1 (ld.global.cg).
 #if FF_REFIT_FENCE == 2
             __threadfence();
             if (atomicAdd(&flags[p], 1u) == 0u) break;  // first arrival: the sibling's thread finishes this node
             __threadfence();
 #else
             uint32_t arrived;
-            asm volatile("atom.global.add.release.gpu.u32 %0, [%1], 1;" : "=r"(arrived) : "l"(__cvta_generic_to_global(flags + p)) : "memory");
+            asm volatile("atom.global.add.acq_rel.gpu.u32 %0, [%1], 1;" : "=r"(arrived) : "l"(__cvta_generic_to_global(flags + p)) : "memory");
             if (arrived == 0u) break;  // first arrival: the sibling's thread finishes this node
 #endif
             const int2 ch = children[p];
@@ -703,8 +727,8 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
     mark("reserve scratch");
 
     bounds_init_kernel<<<1, 32, 0, st>>>(d_bounds);
-    bounds_kernel<<<grid_for(n, 256, 148 * 8), 256, 0, st>>>(d_flat_tris, n, d_bounds);
-    morton_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(d_flat_tris, n, d_bounds, d_keys_a, d_vals_a);
+    bounds_kernel<<<grid_for(n, 256, sm_count() * 8), 256, 0, st>>>(d_flat_tris, n, d_bounds);
+    morton_kernel<<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(d_flat_tris, n, d_bounds, d_keys_a, d_vals_a);
     *launches += 3;
     mark("bounds + morton");
     radix_sort_pairs(d_keys_a, d_vals_a, d_keys_b, d_vals_b, n, d_hist, launches, st);
@@ -721,7 +745,7 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
         d_order = d_vals_b;
         mark("binned-SAH hierarchy");
     } else if (n > 1) {
-        hierarchy_kernel<<<grid_for(n - 1, 256, 148 * 16), 256, 0, st>>>(d_keys_a, (int)n, d_bvh2_children, d_parent);
+        hierarchy_kernel<<<grid_for(n - 1, 256, sm_count() * 16), 256, 0, st>>>(d_keys_a, (int)n, d_bvh2_children, d_parent);
         ++*launches;
         mark("karras hierarchy");
     }
@@ -729,7 +753,7 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
     const float slot_cost = sc_env ? (float)atof(sc_env) : FF_SLOT_COST;
     const char* nc_env = getenv("FF_NODE_COST");
     const float node_cost = nc_env ? (float)atof(nc_env) : FF_NODE_COST;
-    refit_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(d_flat_tris, d_order, (int)n, pad, d_bvh2_children, d_parent, d_flags,
+    refit_kernel<<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(d_flat_tris, d_order, (int)n, pad, d_bvh2_children, d_parent, d_flags,
                                                             d_bvh2_lo, d_bvh2_hi, d_dp, slot_cost, node_cost);
     ++*launches;
     mark("refit + collapse DP");
@@ -752,7 +776,7 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
     // grid-stride over the level's index range read from the device; an exhausted hierarchy costs empty launches.
     for (int flight = 0; flight < 8; ++flight) {
         for (int l = 0; l < 12; ++l) {
-            collapse_kernel<<<148 * 8, 128, 0, st>>>(d_src, node_capacity, (int)n, d_bvh2_children, d_bvh2_lo, d_bvh2_hi, d_flat_tris, d_order,
+            collapse_kernel<<<sm_count() * 8, 128, 0, st>>>(d_src, node_capacity, (int)n, d_bvh2_children, d_bvh2_lo, d_bvh2_hi, d_flat_tris, d_order,
                                                     d_nodes_out, d_tris_out, d_bvh2_leaf_slot, d_ctr, root_area, d_dp);
             collapse_advance_kernel<<<1, 1, 0, st>>>(d_ctr, node_capacity);
             *launches += 2;
@@ -764,7 +788,7 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
     }
     if (h_ctr.level_begin != h_ctr.level_end) return cudaErrorUnknown;  // deeper than 96 levels: not a hierarchy this builder makes
     if (h_ctr.tri_count == n) {
-        gather_tris_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(d_flat_tris, d_order, d_bvh2_leaf_slot, n, d_tris_out);
+        gather_tris_kernel<<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(d_flat_tris, d_order, d_bvh2_leaf_slot, n, d_tris_out);
         ++*launches;
     }
     const uint32_t depth = h_ctr.levels;

@@ -130,6 +130,11 @@ struct TraceCounters { unsigned long long nodes, tris; };
 void k_bake_triangles(const float* d_xyz9_obj, const ffm::M4* d_model_per_geom, const uint32_t* d_geom_of_flat,
                       const uint32_t* d_ord_of_flat, uint32_t n, float4* d_flat_tris, cudaStream_t st);
 
+// Per flat triangle: inverse(transpose(M)) * (normalize(cross(e1, e2)), 0) from OBJECT-space vertices: the normal the
+// reference's frame shows (kernel.cu:101,117,183).  d_nrm_per_geom = inverse(transpose(model)) of every geometry.
+void k_as_coded_normals(const float* d_xyz9_obj, const ffm::M4* d_nrm_per_geom, const uint32_t* d_geom_of_flat, uint32_t n,
+                        float4* d_out, cudaStream_t st);
+
 // Grow-only device scratch of a context, carved by a bump pointer: the builders take all their temporaries from it, so
 // a rebuild (the interactive case, and every build after the first) allocates nothing -- cudaMalloc/cudaFree of a dozen
 // arrays cost 10-30 ms per build, an order of magnitude more than the build kernels themselves.
@@ -206,13 +211,14 @@ void k_megakernel_pass(const DevScene& sc, const CamDev& cam, const RenderDev& r
                        uint32_t* d_work_counter, unsigned long long* d_ray_counter, uint32_t* launches, cudaStream_t st);
 void k_accumulate_pass(const float4* d_radiance, uint32_t npix, uint32_t samples, const uint32_t* d_pixel_map, float4* d_accum, cudaStream_t st);
 void k_resolve(const float4* const* accums, int n_accums, uint32_t npix, float inv_spp, float4* d_out, cudaStream_t st);
-void k_as_coded(const DevScene& sc, const CamDev& cam, unsigned char* d_rgb, cudaStream_t st);
+void k_as_coded(const DevScene& sc, const CamDev& cam, const float4* d_as_coded_normals, unsigned char* d_rgb, cudaStream_t st);
 // Primary-ray feature buffers (FF_INTEGRATOR_AOV_*): shading normal, uv, barycentrics, albedo of the first hit.
 void k_aov(const DevScene& sc, const CamDev& cam, int kind, float4* d_rgba, cudaStream_t st);
 // Barycentrics of closest hits (u, v as in kernel.cu:80-81); misses and analytic primitives give 0.
 void k_hit_barycentrics(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const HitRec* d_hits, size_t n,
                         float* d_u, float* d_v, cudaStream_t st);
 void k_rgba_to_u8(const float4* d_rgba, uint32_t npix, unsigned char* d_rgb, cudaStream_t st);
+void k_u8_to_rgba(const unsigned char* d_rgb, uint32_t npix, float4* d_rgba, cudaStream_t st);  // value / 255, alpha 1
 void k_flush(float4* d_buf, size_t n_float4, cudaStream_t st);
 
 // OBJ ingest (ff_obj.cpp): per-corner attributes in file order, 9 / 9 / 6 floats per triangle; face_material indexes
@@ -232,5 +238,8 @@ int obj_default_threads();
 
 struct Tuning { int postpone_div, refill_lanes, blocks_per_sm; };
 Tuning& tuning();
+// Multiprocessors of the CURRENT device (cudaDevAttrMultiProcessorCount, cached per device): every grid is sized as a
+// multiple of it (148 on B200).
+int sm_count();
 
 }  // namespace ff

@@ -100,6 +100,36 @@ std::string token_rest(const char* q, const char* eol) {
     return std::string(q, e);
 }
 
+// Number parsers that never look past `eol`: strtof / strtoll skip leading white space INCLUDING new lines and stop only at a
+// non-numeric byte, so on the mmap'd file a short line (`vt u`, a two-coordinate `v`) would take its missing value from the
+// next line, and a number that ends the file on a page boundary would be read past the mapping.  The token is copied to a
+// small NUL-terminated buffer first.  Return false when no number starts before eol (the missing-value case).
+bool parse_float(const char*& q, const char* eol, float& out) {
+    while (q < eol && is_space(*q)) ++q;
+    char buf[64];
+    size_t n = 0;
+    while (q + n < eol && !is_space(q[n]) && n + 1 < sizeof(buf)) { buf[n] = q[n]; ++n; }
+    if (n == 0) return false;
+    buf[n] = 0;
+    char* e;
+    out = strtof(buf, &e);
+    if (e == buf) return false;
+    q += (size_t)(e - buf);
+    return true;
+}
+bool parse_index(const char*& q, const char* eol, long long& out) {
+    char buf[32];
+    size_t n = 0;
+    while (q + n < eol && (q[n] == '-' || q[n] == '+' || (q[n] >= '0' && q[n] <= '9')) && n + 1 < sizeof(buf)) { buf[n] = q[n]; ++n; }
+    if (n == 0) return false;
+    buf[n] = 0;
+    char* e;
+    out = strtoll(buf, &e, 10);
+    if (e == buf) return false;
+    q += (size_t)(e - buf);
+    return true;
+}
+
 void parse_chunk(Chunk& c) {
     const char* p = c.begin;
     std::vector<long long> poly;
@@ -113,29 +143,23 @@ void parse_chunk(Chunk& c) {
         if (left >= 2 && q[0] == 'v' && is_space(q[1])) {
             q += 2;
             for (int k = 0; k < 3; ++k) {
-                char* e;
-                const float v = strtof(q, &e);
-                if (e == q) { c.error = "malformed vertex at line " + std::to_string(c.lines); return; }
+                float v;
+                if (!parse_float(q, eol, v)) { c.error = "malformed vertex at line " + std::to_string(c.lines); return; }
                 c.pos.push_back(v);
-                q = e;
             }
         } else if (left >= 3 && q[0] == 'v' && q[1] == 'n' && is_space(q[2])) {
             q += 3;
             for (int k = 0; k < 3; ++k) {
-                char* e;
-                const float v = strtof(q, &e);
-                if (e == q) { c.error = "malformed normal at line " + std::to_string(c.lines); return; }
+                float v;
+                if (!parse_float(q, eol, v)) { c.error = "malformed normal at line " + std::to_string(c.lines); return; }
                 c.nrm.push_back(v);
-                q = e;
             }
         } else if (left >= 3 && q[0] == 'v' && q[1] == 't' && is_space(q[2])) {
             q += 3;
             for (int k = 0; k < 2; ++k) {
-                char* e;
-                float v = strtof(q, &e);
-                if (e == q) { if (k == 0) { c.error = "malformed texture coordinate at line " + std::to_string(c.lines); return; } v = 0.f; }
+                float v;
+                if (!parse_float(q, eol, v)) { if (k == 0) { c.error = "malformed texture coordinate at line " + std::to_string(c.lines); return; } v = 0.f; }
                 c.tex.push_back(v);
-                q = e;
             }
         } else if (left >= 2 && q[0] == 'f' && is_space(q[1])) {
             q += 2;
@@ -148,10 +172,8 @@ void parse_chunk(Chunk& c) {
                 bool bad = false;
                 for (int k = 0; k < 3; ++k) {
                     if (q < eol && *q != '/' && !is_space(*q)) {
-                        char* e;
-                        const long long v = strtoll(q, &e, 10);
-                        if (e == q || v == 0) { bad = true; break; }
-                        q = e;
+                        long long v;
+                        if (!parse_index(q, eol, v) || v == 0) { bad = true; break; }
                         idx[k] = v > 0 ? v - 1 : REL_BASE + cnt[k] + v;
                     }
                     if (q < eol && *q == '/') ++q; else break;

@@ -385,7 +385,7 @@ void k_wavefront_pass(const DevScene& sc, const CamDev& cam, const RenderDev& rp
                       cudaStream_t st) {
     const uint32_t n = rp.samples * rp.npix;
     const int n_counts = rp.max_bounces + 2;
-    wf_raygen_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(cam, rp, wb.ray_o[0], wb.ray_d[0], wb.beta[0], wb.radiance, wb.counts, n_counts);
+    wf_raygen_kernel<<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(cam, rp, wb.ray_o[0], wb.ray_d[0], wb.beta[0], wb.radiance, wb.counts, n_counts);
     ++*launches;
     for (int b = 0; b <= rp.max_bounces; ++b) {
         const int in = b & 1, out = in ^ 1;
@@ -393,11 +393,11 @@ void k_wavefront_pass(const DevScene& sc, const CamDev& cam, const RenderDev& rp
         k_trace_closest(sc, wb.ray_o[in], wb.ray_d[in], wb.counts + b, n, trace_mode | ((FF_SELF_SKIP && rp.ray_eps > 0.125f * sc.pad) ? FF_TRACE_SELFSKIP : 0), wb.hits, d_counters, wb.counts + n_counts + b, st);
         if (trace_events) cudaEventRecord(trace_events[(*n_trace_events)++], st);
         const bool nee = rp.nee && sc.n_lights != 0;
-        if (nee) wf_shade_kernel<true><<<grid_for(n, FF_SHADE_BLOCK, 148 * 16 * 256 / FF_SHADE_BLOCK), FF_SHADE_BLOCK, 0, st>>>(sc, rp, b, wb.counts + b, n, wb.hits, wb.ray_o[in], wb.ray_d[in],
+        if (nee) wf_shade_kernel<true><<<grid_for(n, FF_SHADE_BLOCK, sm_count() * 16 * 256 / FF_SHADE_BLOCK), FF_SHADE_BLOCK, 0, st>>>(sc, rp, b, wb.counts + b, n, wb.hits, wb.ray_o[in], wb.ray_d[in],
                                                                    wb.beta[in], wb.ray_o[out], wb.ray_d[out], wb.beta[out],
                                                                    wb.radiance, wb.counts + b + 1, wb.sh_o, wb.sh_d, wb.sh_c,
                                                                    wb.counts + 2 * n_counts + b);
-        else wf_shade_kernel<false><<<grid_for(n, FF_SHADE_BLOCK, 148 * 16 * 256 / FF_SHADE_BLOCK), FF_SHADE_BLOCK, 0, st>>>(sc, rp, b, wb.counts + b, n, wb.hits, wb.ray_o[in], wb.ray_d[in],
+        else wf_shade_kernel<false><<<grid_for(n, FF_SHADE_BLOCK, sm_count() * 16 * 256 / FF_SHADE_BLOCK), FF_SHADE_BLOCK, 0, st>>>(sc, rp, b, wb.counts + b, n, wb.hits, wb.ray_o[in], wb.ray_d[in],
                                                                    wb.beta[in], wb.ray_o[out], wb.ray_d[out], wb.beta[out],
                                                                    wb.radiance, wb.counts + b + 1, wb.sh_o, wb.sh_d, wb.sh_c,
                                                                    wb.counts + 2 * n_counts + b);
@@ -530,7 +530,7 @@ void k_megakernel_pass(const DevScene& sc, const CamDev& cam, const RenderDev& r
                        unsigned long long* d_ray_counter, uint32_t* launches, cudaStream_t st) {
     cudaMemsetAsync(d_work_counter, 0, sizeof(uint32_t), st);
     const uint32_t n = rp.samples * rp.npix;
-    const int g = grid_for(n, FF_TRACE_BLOCK, 148 * tuning().blocks_per_sm);
+    const int g = grid_for(n, FF_TRACE_BLOCK, sm_count() * tuning().blocks_per_sm);
     if (rp.nee && sc.n_lights != 0) megakernel<true><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, cam, rp, d_radiance, d_work_counter, d_ray_counter);
     else megakernel<false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, cam, rp, d_radiance, d_work_counter, d_ray_counter);
     ++*launches;
@@ -551,7 +551,7 @@ __global__ void accumulate_kernel(const float4* __restrict__ radiance, uint32_t 
     }
 }
 void k_accumulate_pass(const float4* d_radiance, uint32_t npix, uint32_t samples, const uint32_t* d_pixel_map, float4* d_accum, cudaStream_t st) {
-    accumulate_kernel<<<grid_for(npix, 256, 148 * 16), 256, 0, st>>>(d_radiance, npix, samples, d_pixel_map, d_accum);
+    accumulate_kernel<<<grid_for(npix, 256, sm_count() * 16), 256, 0, st>>>(d_radiance, npix, samples, d_pixel_map, d_accum);
 }
 // out = (sum over accumulators in rank order) * (1 / total_spp); alpha = 1.  With n_accums > 1 the pointers may be
 // peer-GPU memory (CUDA IPC over NVLink): the framebuffer reduce and the resolve are one kernel.
@@ -569,7 +569,7 @@ __global__ void resolve_kernel(PeerPtrs peers, int n_accums, uint32_t npix, floa
 void k_resolve(const float4* const* accums, int n_accums, uint32_t npix, float inv_spp, float4* d_out, cudaStream_t st) {
     PeerPtrs pp;
     for (int i = 0; i < 8; ++i) pp.p[i] = i < n_accums ? accums[i] : nullptr;
-    resolve_kernel<<<grid_for(npix, 256, 148 * 16), 256, 0, st>>>(pp, n_accums, npix, inv_spp, d_out);
+    resolve_kernel<<<grid_for(npix, 256, sm_count() * 16), 256, 0, st>>>(pp, n_accums, npix, inv_spp, d_out);
 }
 
 // ------------------------------------------------------------------ primary-ray feature buffers
@@ -617,7 +617,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) aov_kernel(DevScene sc, CamDev
 }
 void k_aov(const DevScene& sc, const CamDev& cam, int kind, float4* d_rgba, cudaStream_t st) {
     const size_t n = (size_t)cam.w * cam.h;
-    aov_kernel<<<grid_for(n, FF_TRACE_BLOCK, 148 * 16), FF_TRACE_BLOCK, 0, st>>>(sc, cam, kind, d_rgba);
+    aov_kernel<<<grid_for(n, FF_TRACE_BLOCK, sm_count() * 16), FF_TRACE_BLOCK, 0, st>>>(sc, cam, kind, d_rgba);
 }
 __global__ void hit_barycentrics_kernel(DevScene sc, const float4* __restrict__ ray_o, const float4* __restrict__ ray_d,
                                         const HitRec* __restrict__ hits, size_t n, float* __restrict__ out_u, float* __restrict__ out_v) {
@@ -634,12 +634,17 @@ __global__ void hit_barycentrics_kernel(DevScene sc, const float4* __restrict__ 
 }
 void k_hit_barycentrics(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const HitRec* d_hits, size_t n,
                         float* d_u, float* d_v, cudaStream_t st) {
-    hit_barycentrics_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(sc, d_ray_o, d_ray_d, d_hits, n, d_u, d_v);
+    hit_barycentrics_kernel<<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(sc, d_ray_o, d_ray_d, d_hits, n, d_u, d_v);
 }
 
 // ------------------------------------------------------------------ as-coded frame (kernel.cu:186-216)
-// colour = abs(normal) -> uchar3 (kernel.cu:183,214); misses keep the cleared pixel (kernel.cu:340).
-__global__ void __launch_bounds__(FF_TRACE_BLOCK) as_coded_kernel(DevScene sc, CamDev cam, unsigned char* __restrict__ rgb) {
+// colour = abs(normal) -> uchar3 (kernel.cu:183,214); misses keep the cleared pixel (kernel.cu:340).  `normal` is what
+// setIntersection leaves in the Intersect (kernel.cu:117): inverse(transpose(M)) * object-space unit normal, NOT
+// re-normalised -- `nref` holds it per flat triangle (k_as_coded_normals).  make_uchar3(float...) compiles to
+// cvt.rzi.u32.f32 followed by an 8-bit store, so a component above 255 wraps modulo 256 (|normal| > 1 under a scale < 1);
+// F2I saturates at 2^32 - 1 and turns NaN into 0.  CPU twin: u8_as_cuda in oracle/firefly_oracle.cpp.
+__device__ __forceinline__ unsigned char as_coded_u8(float c) { return (unsigned char)(__float2uint_rz(c) & 0xffu); }
+__global__ void __launch_bounds__(FF_TRACE_BLOCK) as_coded_kernel(DevScene sc, CamDev cam, const float4* __restrict__ nref, unsigned char* __restrict__ rgb) {
     __shared__ uint2 sm_stack[(FF_SM_STACK + FF_TRI_QUEUE) * FF_TRACE_BLOCK];
     const uint32_t npix = (uint32_t)cam.w * cam.h;
     unsigned cn = 0, ct = 0;
@@ -653,20 +658,25 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) as_coded_kernel(DevScene sc, C
         trace_bvh8<false, false>(sc, o, dn, best, sm_stack + threadIdx.x, FF_TRACE_BLOCK, cn, ct);
         unsigned char px[3] = {0, 0, 0};
         if (best.slot >= 0) {
-            HitRec h;
-            h.key = best.key; h.t = best.t; h.slot = best.slot; h.ord = best.ord;
-            V3 P, n;
-            int geom;
-            hit_surface(sc, h, o, d, P, n, geom);
-            const float c[3] = {fmul(fabsf(n.x), 255.f), fmul(fabsf(n.y), 255.f), fmul(fabsf(n.z), 255.f)};
-            for (int k = 0; k < 3; ++k) px[k] = (unsigned char)(c[k] > 255.f ? 255.f : c[k]);
+            V3 n;
+            if (best.slot & 0x40000000) {
+                HitRec h;
+                h.key = best.key; h.t = best.t; h.slot = best.slot; h.ord = best.ord;
+                V3 P;
+                int geom;
+                hit_surface(sc, h, o, d, P, n, geom);
+            } else {
+                const int flat = __float_as_int(__ldg(sc.tris + 3 * (size_t)best.slot + 2).w);
+                n = ld3(__ldg(nref + flat));
+            }
+            px[0] = as_coded_u8(fmul(fabsf(n.x), 255.f)); px[1] = as_coded_u8(fmul(fabsf(n.y), 255.f)); px[2] = as_coded_u8(fmul(fabsf(n.z), 255.f));
         }
         rgb[3 * (size_t)i] = px[0]; rgb[3 * (size_t)i + 1] = px[1]; rgb[3 * (size_t)i + 2] = px[2];
     }
 }
-void k_as_coded(const DevScene& sc, const CamDev& cam, unsigned char* d_rgb, cudaStream_t st) {
+void k_as_coded(const DevScene& sc, const CamDev& cam, const float4* d_as_coded_normals, unsigned char* d_rgb, cudaStream_t st) {
     const size_t n = (size_t)cam.w * cam.h;
-    as_coded_kernel<<<grid_for(n, FF_TRACE_BLOCK, 148 * 16), FF_TRACE_BLOCK, 0, st>>>(sc, cam, d_rgb);
+    as_coded_kernel<<<grid_for(n, FF_TRACE_BLOCK, sm_count() * 16), FF_TRACE_BLOCK, 0, st>>>(sc, cam, d_as_coded_normals, d_rgb);
 }
 // linear radiance -> 8-bit: clamp to [0,1], x255, truncate (the kernel.cu:214 conversion)
 __global__ void rgba_to_u8_kernel(const float4* __restrict__ rgba, uint32_t npix, unsigned char* __restrict__ rgb) {
@@ -677,8 +687,15 @@ __global__ void rgba_to_u8_kernel(const float4* __restrict__ rgba, uint32_t npix
         rgb[3 * (size_t)i + 2] = (unsigned char)(fminf(fmaxf(v.z, 0.f), 1.f) * 255.f);
     }
 }
+__global__ void u8_to_rgba_kernel(const unsigned char* __restrict__ rgb, uint32_t npix, float4* __restrict__ rgba) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += gridDim.x * blockDim.x)
+        rgba[i] = make_float4(fdiv((float)rgb[3 * (size_t)i], 255.0f), fdiv((float)rgb[3 * (size_t)i + 1], 255.0f), fdiv((float)rgb[3 * (size_t)i + 2], 255.0f), 1.0f);
+}
+void k_u8_to_rgba(const unsigned char* d_rgb, uint32_t npix, float4* d_rgba, cudaStream_t st) {
+    u8_to_rgba_kernel<<<grid_for(npix, 256, sm_count() * 16), 256, 0, st>>>(d_rgb, npix, d_rgba);
+}
 void k_rgba_to_u8(const float4* d_rgba, uint32_t npix, unsigned char* d_rgb, cudaStream_t st) {
-    rgba_to_u8_kernel<<<grid_for(npix, 256, 148 * 16), 256, 0, st>>>(d_rgba, npix, d_rgb);
+    rgba_to_u8_kernel<<<grid_for(npix, 256, sm_count() * 16), 256, 0, st>>>(d_rgba, npix, d_rgb);
 }
 
 }  // namespace ff

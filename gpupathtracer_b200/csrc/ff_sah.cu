@@ -618,7 +618,7 @@ cudaError_t sah_build_hierarchy(const float4* d_flat_tris, const uint32_t* d_sor
     B.chunk_off = arena.take<uint2>(chunk_cap);
     B.split = arena.take<SahBigSplit>(big_cap);
     if (!B.split) return cudaErrorMemoryAllocation;
-    sah_boxes_kernel<<<sah_grid_for(n, 256, 148 * 16), 256, 0, st>>>(d_flat_tris, d_sorted_idx, n, d_lo, d_hi, d_idx0);
+    sah_boxes_kernel<<<sah_grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(d_flat_tris, d_sorted_idx, n, d_lo, d_hi, d_idx0);
     ++*launches;
 
     SahSeg root;
@@ -675,7 +675,7 @@ cudaError_t sah_build_hierarchy(const float4* d_flat_tris, const uint32_t* d_sor
         ts = big_in; big_in = big_out; big_out = ts;
         uint32_t* ti = idx_in; idx_in = idx_out; idx_out = ti;
     }
-    sah_compose_kernel<<<sah_grid_for(n, 256, 148 * 16), 256, 0, st>>>(d_order_k, d_sorted_idx, n, d_order_out);
+    sah_compose_kernel<<<sah_grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(d_order_k, d_sorted_idx, n, d_order_out);
     ++*launches;
     SCK(cudaStreamSynchronize(st));
     SCK(cudaGetLastError());

@@ -12,6 +12,18 @@ Tuning& tuning() {
     return t;
 }
 
+int sm_count() {
+    static int cached[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (cached[dev] == 0) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cached[dev] = n;
+    }
+    return cached[dev];
+}
+
 static inline int grid_for(size_t n, int block, int max_blocks) {
     size_t g = (n + block - 1) / block;
     if (g < 1) g = 1;
@@ -182,18 +194,18 @@ void k_trace_closest(const DevScene& sc, const float4* d_ray_o, const float4* d_
     if (m == FF_TRACE_BVH8 && !count && d_work_counter && !(mode & FF_TRACE_STATIC)) {
         // persistent: enough warps to fill the machine, each pulling rays until the batch is drained.
         // *d_work_counter must be zero (the caller clears it on the same stream).
-        const int g = grid_for(n_max, FF_TRACE_BLOCK, 148 * tuning().blocks_per_sm);
+        const int g = grid_for(n_max, FF_TRACE_BLOCK, sm_count() * tuning().blocks_per_sm);
         if (mode & FF_TRACE_SELFSKIP) trace_closest_persistent_kernel<true><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_work_counter);
         else trace_closest_persistent_kernel<false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_work_counter);
         return;
     }
     if (m == FF_TRACE_BRUTE) {
-        const int g = grid_for(n_max, FF_BRUTE_TILE, 148 * 8);
+        const int g = grid_for(n_max, FF_BRUTE_TILE, sm_count() * 8);
         if (count) trace_brute_kernel<true><<<g, FF_BRUTE_TILE, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);
         else trace_brute_kernel<false><<<g, FF_BRUTE_TILE, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);
         return;
     }
-    const int g = grid_for(n_max, FF_TRACE_BLOCK, 148 * 64);
+    const int g = grid_for(n_max, FF_TRACE_BLOCK, sm_count() * 64);
     const bool skip = (mode & FF_TRACE_SELFSKIP) != 0;
     if (m == FF_TRACE_BVH2) {
         if (count) trace_closest_kernel<FF_TRACE_BVH2, true, false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);
@@ -309,11 +321,11 @@ void k_trace_any(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_
     if (n == 0) return;
     const int m = mode & 0xff;
     if (m == FF_TRACE_BVH8 && d_work_counter && !(mode & FF_TRACE_STATIC)) {
-        const int g = grid_for(n, FF_TRACE_BLOCK, 148 * tuning().blocks_per_sm);
+        const int g = grid_for(n, FF_TRACE_BLOCK, sm_count() * tuning().blocks_per_sm);
         trace_any_persistent_kernel<false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_tmax, 0, nullptr, n, d_occluded, nullptr, nullptr, d_work_counter);
         return;
     }
-    const int g = grid_for(n, FF_TRACE_BLOCK, 148 * 64);
+    const int g = grid_for(n, FF_TRACE_BLOCK, sm_count() * 64);
     if (m == FF_TRACE_BRUTE) trace_any_kernel<FF_TRACE_BRUTE><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_tmax, n, d_occluded);
     else if (m == FF_TRACE_BVH2) trace_any_kernel<FF_TRACE_BVH2><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_tmax, n, d_occluded);
     else trace_any_kernel<FF_TRACE_BVH8><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_tmax, n, d_occluded);
@@ -321,7 +333,7 @@ void k_trace_any(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_
 void k_trace_shadow(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const float4* d_contrib,
                     const uint32_t* d_count, uint32_t n_max, float4* d_radiance, uint32_t* d_work_counter, bool self_skip, cudaStream_t st) {
     if (n_max == 0) return;
-    const int g = grid_for(n_max, FF_TRACE_BLOCK, 148 * tuning().blocks_per_sm);
+    const int g = grid_for(n_max, FF_TRACE_BLOCK, sm_count() * tuning().blocks_per_sm);
     if (self_skip) trace_any_persistent_kernel<true><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, nullptr, 1, d_count, n_max, nullptr, d_contrib, d_radiance, d_work_counter);
     else trace_any_persistent_kernel<false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, nullptr, 1, d_count, n_max, nullptr, d_contrib, d_radiance, d_work_counter);
 }
@@ -347,7 +359,7 @@ __global__ void camera_rays_kernel(CamDev cam, float4* ray_o, float4* ray_d) {
 }
 void k_camera_rays(const CamDev& cam, float4* d_ray_o, float4* d_ray_d, cudaStream_t st) {
     const size_t n = (size_t)cam.w * cam.h;
-    camera_rays_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(cam, d_ray_o, d_ray_d);
+    camera_rays_kernel<<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(cam, d_ray_o, d_ray_d);
 }
 
 // ------------------------------------------------------------------ pack / unpack
@@ -358,7 +370,7 @@ __global__ void pack_rays_kernel(const float* __restrict__ r6, size_t n, float4*
     }
 }
 void k_pack_rays(const float* d_rays6, size_t n, float4* d_ray_o, float4* d_ray_d, cudaStream_t st) {
-    if (n) pack_rays_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(d_rays6, n, d_ray_o, d_ray_d);
+    if (n) pack_rays_kernel<<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(d_rays6, n, d_ray_o, d_ray_d);
 }
 __global__ void unpack_rays_kernel(const float4* __restrict__ ray_o, const float4* __restrict__ ray_d, size_t n, float* r6) {
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
@@ -368,7 +380,7 @@ __global__ void unpack_rays_kernel(const float4* __restrict__ ray_o, const float
     }
 }
 void k_unpack_rays(const float4* d_ray_o, const float4* d_ray_d, size_t n, float* d_rays6, cudaStream_t st) {
-    if (n) unpack_rays_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(d_ray_o, d_ray_d, n, d_rays6);
+    if (n) unpack_rays_kernel<<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(d_ray_o, d_ray_d, n, d_rays6);
 }
 __global__ void unpack_hits_kernel(DevScene sc, const HitRec* __restrict__ hits, size_t n, int* geom, int* tri, float* t) {
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
@@ -379,7 +391,7 @@ __global__ void unpack_hits_kernel(DevScene sc, const HitRec* __restrict__ hits,
     }
 }
 void k_unpack_hits(const DevScene& sc, const HitRec* d_hits, size_t n, int* d_geom, int* d_tri, float* d_t, cudaStream_t st) {
-    if (n) unpack_hits_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(sc, d_hits, n, d_geom, d_tri, d_t);
+    if (n) unpack_hits_kernel<<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(sc, d_hits, n, d_geom, d_tri, d_t);
 }
 
 // ------------------------------------------------------------------ synthetic workloads
@@ -398,7 +410,7 @@ __global__ void make_soup_kernel(size_t n, float s, float* xyz9) {
     }
 }
 void k_make_soup(size_t n, float s, float* d_xyz9, cudaStream_t st) {
-    if (n) make_soup_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(n, s, d_xyz9);
+    if (n) make_soup_kernel<<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(n, s, d_xyz9);
 }
 // Batch A: origin ~ U[0,1)^3, direction uniform on the sphere; key {0xF1EEF1E5, 1}, counter {i, 0|1, salt, 0}.
 __global__ void make_rays_uniform_kernel(uint64_t first, size_t n, uint32_t salt, float4* ray_o, float4* ray_d) {
@@ -415,7 +427,7 @@ __global__ void make_rays_uniform_kernel(uint64_t first, size_t n, uint32_t salt
     }
 }
 void k_make_rays_uniform(uint64_t first, size_t n, uint32_t salt, float4* d_ray_o, float4* d_ray_d, cudaStream_t st) {
-    if (n) make_rays_uniform_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(first, n, salt, d_ray_o, d_ray_d);
+    if (n) make_rays_uniform_kernel<<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(first, n, salt, d_ray_o, d_ray_d);
 }
 
 // Batch B: one cosine-hemisphere bounce off every hit of an input batch (compacted, warp-aggregated append).
@@ -460,7 +472,7 @@ __global__ void make_rays_bounce_kernel(DevScene sc, const float4* __restrict__ 
 }
 void k_make_rays_bounce(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const HitRec* d_hits, uint32_t n,
                         uint32_t seed_lo, uint32_t seed_hi, float4* d_out_o, float4* d_out_d, uint32_t* d_count, cudaStream_t st) {
-    if (n) make_rays_bounce_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(sc, d_ray_o, d_ray_d, d_hits, n, seed_lo, seed_hi,
+    if (n) make_rays_bounce_kernel<<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(sc, d_ray_o, d_ray_d, d_hits, n, seed_lo, seed_hi,
                                                                               d_out_o, d_out_d, d_count);
 }
 
@@ -469,7 +481,7 @@ __global__ void flush_kernel(float4* buf, size_t n) {
         buf[i] = make_float4((float)i, 0.f, 0.f, 0.f);
 }
 void k_flush(float4* d_buf, size_t n_float4, cudaStream_t st) {
-    if (n_float4) flush_kernel<<<148 * 8, 256, 0, st>>>(d_buf, n_float4);
+    if (n_float4) flush_kernel<<<sm_count() * 8, 256, 0, st>>>(d_buf, n_float4);
 }
 
 }  // namespace ff

@@ -112,6 +112,19 @@ def reference_main(width=800, height=800):
                 camera=camera((0, 0, 15), fov=70.0, width=width, height=height), spp=1, max_bounces=0)
 
 
+def scaled_meshes(width=160, height=160):
+    """Meshes under uniform and non-uniform scales below and above 1, plus a scaled plane.  The as-coded frame shows
+    inverse(transpose(M)) * n WITHOUT re-normalising it (kernel.cu:117,183), so a scale changes the brightness and a scale
+    below 1 pushes components past 255, where make_uchar3 wraps (kernel.cu:214): the scene that pins both."""
+    return dict(name="scaled",
+                geoms=[geom("rocketman", pos=(-1.6, 0, 0), rot=(0, 90, 180), scale=(0.5, 0.5, 0.5), material=DIFFUSE_RED),
+                       geom("cube", pos=(1.6, 0.5, -1.0), rot=(20, 30, 10), scale=(2.0, 1.0, 3.0)),
+                       geom("sphereBlender", pos=(0.2, -1.6, 1.0), rot=(0, 0, 35), scale=(0.7, 1.3, 0.7)),
+                       geom("triangle", pos=(-0.5, 1.2, 2.0), scale=(1.5, 1.5, 1.5)),
+                       geom(None, pos=(0, 0, -3.0), scale=(8, 8, 8), plane=True, material=DIFFUSE_RED)],
+                camera=camera((0, 0, 8), fov=50.0, width=width, height=height), spp=1, max_bounces=0)
+
+
 def showcase(meshes, width=512, height=512, spp=16, max_bounces=6):
     """Every declared BXDFTyp and GeometryType in one frame: the config-2 box with a glass
     rocketman, an analytic mirror sphere, an analytic emissive sphere and an analytic plane."""

@@ -20,7 +20,7 @@
 //       radians                              detail/func_trigonometric.inl:9-14
 //
 // Parity status: PINNED.  This restatement is checked bit-for-bit against the reference's own text
-// compiled from /root/reference (oracle/_ref, see oracle/ref_shim.cpp) by tests/test_oracle_vs_ref.py
+// compiled from /root/reference (oracle/_ref, see oracle/ref_shim.cpp) by tests/test_oracle_golden.py (the *_vs_ref tests)
 // when that library is present, and against the golden vectors under tests/golden/ that were
 // generated from it (tools/make_golden.py).  The reference itself ships no tests or vectors.
 //
@@ -889,7 +889,17 @@ void orc_camera_inverse_matrices(const float pos[3], const float world_up[3], fl
     std::memcpy(inv_view16, &iv, 64);
     std::memcpy(inv_proj16, &ip, 64);
 }
-// As-coded frame (kernel.cu:186-216, memset kernel.cu:340). mode as in orc_intersect.
+// make_uchar3(colour * 255.f) (kernel.cu:214) as the CUDA compiler builds it: cvt.rzi.u32.f32 followed by an 8-bit store
+// (checked with nvcc 12.9: F2I.U32.TRUNC + STG.U8).  The conversion saturates at 0 and 2^32 - 1 and maps NaN to 0; the
+// store keeps the low byte, so a component above 255 WRAPS modulo 256 (|normal| > 1 under a scale below 1).
+static inline unsigned char u8_as_cuda(float v) {
+    if (!(v > 0.0f)) return 0;                 // NaN, zero, negatives
+    if (v >= 4294967296.0f) return 0xff;       // saturates to 0xffffffff
+    return (unsigned char)((uint32_t)v & 0xffu);
+}
+// As-coded frame (kernel.cu:186-216, memset kernel.cu:340). mode as in orc_intersect: 0 = the reference's object-space
+// path; 1 = the GPU contract: the hit is found on the baked world-space triangles, the colour is still the normal the
+// reference shows, inverse(transpose(M)) * the OBJECT-space unit normal (kernel.cu:101,117), not re-normalised.
 void orc_render_as_coded(void* s, int mode, const float pos[3], const float world_up[3], float yaw, float pitch,
                          float fov, int width, int height, float near_clip, float far_clip, unsigned char* rgb,
                          int nthreads) {
@@ -904,11 +914,18 @@ void orc_render_as_coded(void* s, int mode, const float pos[3], const float worl
                 Ray ray = gen_ray(cam, invVP, (float)x, (float)y);
                 V3 n; bool hit;
                 if (mode == 0) { Hit h = intersectRays(ray, os->sc); hit = h.hit; n = h.normal; }
-                else { FlatHit h = intersectFlat(ray, os->sc, os->flat); hit = h.hit; n = h.normal; }
+                else {
+                    FlatHit h = intersectFlat(ray, os->sc, os->flat); hit = h.hit; n = h.normal;
+                    if (hit && h.tri >= 0) {
+                        const Geom& g = os->sc.geoms[h.geom];
+                        const Tri& t = g.tris[h.tri];
+                        V3 no = normalize(cross(sub(t.v1, t.v0), sub(t.v2, t.v0)));
+                        n = xyz(mulMV(inverse(transpose(g.model)), v4(no, 0.f)));
+                    }
+                }
                 if (hit) {
                     unsigned char* px = rgb + 3 * (y * width + x);
-                    float c[3] = {std::fabs(n.x) * 255.f, std::fabs(n.y) * 255.f, std::fabs(n.z) * 255.f};
-                    for (int k = 0; k < 3; ++k) px[k] = (unsigned char)(c[k] > 255.f ? 255.f : c[k]);
+                    px[0] = u8_as_cuda(std::fabs(n.x) * 255.f); px[1] = u8_as_cuda(std::fabs(n.y) * 255.f); px[2] = u8_as_cuda(std::fabs(n.z) * 255.f);
                 }
             }
     });

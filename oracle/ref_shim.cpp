@@ -221,10 +221,11 @@ void ref_render_as_coded(void* s, const float pos[3], const float world_up[3], f
                     glm::vec3 dir;
                     glm::vec3 c = shade(ray, it, dir, sc->geoms.data());
                     unsigned char* px = rgb + 3 * (y * width + x);
-                    // make_uchar3(c*255.f) (kernel.cu:214): float -> unsigned char, truncating
+                    // make_uchar3(c*255.f) (kernel.cu:214) as nvcc builds it: cvt.rzi.u32.f32 + an 8-bit store, i.e. the
+                    // value saturates to [0, 2^32 - 1] (NaN -> 0) and the low byte is kept (wraps above 255)
                     for (int k = 0; k < 3; ++k) {
                         float v = c[k] * 255.f;
-                        px[k] = (unsigned char)(v > 255.f ? 255.f : v);
+                        px[k] = !(v > 0.0f) ? 0 : v >= 4294967296.0f ? 0xff : (unsigned char)((uint32_t)v & 0xffu);
                     }
                 }
             }

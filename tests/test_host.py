@@ -85,6 +85,26 @@ def test_obj_reader(ff, meshes, tmp_path):
 
 
 @pytest.mark.skipif(not os.path.isdir("/root/reference/sceneResources"), reason="reference tree not mounted")
+def test_obj_reader_short_lines_never_borrow_from_the_next_line(ff, tmp_path):
+    """A number parse is bounded by its own line: a one-coordinate `vt` is legal (v = 0), a short `v` line is an error even
+    when the next line starts with a number, and a file whose last number ends exactly on a page boundary loads."""
+    p = tmp_path / "short_vt.obj"
+    p.write_text("v 0 0 0\nv 1 0 0\nv 0 1 0\nvt 0.25\n0.5 0.5\nvt 0.5 0.75\nvt 1 1\nf 1/1 2/2 3/3\n")
+    m = ff.load_obj_ex(str(p), threads=1)
+    assert m["xyz9"].shape == (1, 9) and m["uvs6"].tolist() == [[0.25, 0.0, 0.5, 0.75, 1.0, 1.0]]
+    bad = tmp_path / "short_v.obj"
+    bad.write_text("v 0 0 0\nv 1 2\n7 8 9\nv 0 1 0\nf 1 2 3\n")
+    with pytest.raises(ff.FireflyError):
+        ff.load_obj(str(bad))
+    body = "v 0 0 0\nv 1 0 0\nv 0 1 0\nf 1 2 3\n"
+    page = tmp_path / "page.obj"
+    page.write_text("#" + "x" * (4096 - len(body) - 2) + "\n" + body)
+    assert os.path.getsize(page) == 4096 and ff.load_obj(str(page)).shape == (1, 9)
+    tail = tmp_path / "no_newline.obj"
+    tail.write_text(body[:-1].replace("f 1 2 3", "f 1 2 -1"))
+    assert ff.load_obj(str(tail)).shape == (1, 9)
+
+
 def test_obj_reader_on_reference_assets(ff, meshes):
     for name in S.MESH_NAMES:
         got = ff.load_obj("/root/reference/sceneResources/%s.obj" % name)

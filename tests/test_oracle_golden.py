@@ -91,6 +91,26 @@ def test_main_scene_with_planes(orc, golden, meshes):
     assert np.allclose(got1["t"][h], g["t"][h], rtol=1e-5)
 
 
+def test_scaled_meshes_as_coded_frame(orc, golden, meshes):
+    """Meshes under scales below / above 1 (scenes.scaled_meshes): the reference's frame shows inverse(transpose(M)) * n
+    un-normalised (kernel.cu:117,183) and make_uchar3 wraps above 255 (kernel.cu:214).  Mode 0 is the reference's own path
+    (bit-exact, frame included); mode 1 -- the GPU contract: hit found on baked triangles, same colour rule -- must show the
+    same bytes wherever it finds the same primitive."""
+    g = golden("ref_scaled.npz")
+    desc = S.scaled_meshes(160, 160)
+    sc = S.instantiate_on(desc, orc.scene(), meshes)
+    got = sc.intersect(g["rays"], mode=0)
+    assert_hits_equal(got, g, "scaled scene mode 0")
+    frame = g["as_coded"]
+    assert (sc.render_as_coded(desc["camera"], mode=0) == frame).all()
+    assert frame.max() < 255 and (frame.reshape(-1, 3)[g["geom"] == 0].astype(int).sum(-1) > 300).any()  # |n| = 2 on the half-scale mesh wraps: no clamped 255s, sums a unit normal cannot reach
+    got1 = sc.intersect(g["rays"], mode=1)
+    same = (got1["geom"] == g["geom"]) & (got1["tri"] == g["tri"])
+    assert same.mean() > 0.999
+    f1 = sc.render_as_coded(desc["camera"], mode=1).reshape(-1, 3)
+    assert (f1[same] == frame.reshape(-1, 3)[same]).all()
+
+
 def test_camera_and_matrices(orc, golden):
     g = golden("ref_camera.npz")
     for i in range(3):

@@ -15,6 +15,8 @@ the GPU box except the produced .npz files.
                      bit-exact contract for hit ids AND t
   ref_c1.npz         config 1 (cube + translated triangle), 256x256 camera rays, reference results
   ref_main.npz       the main() scene (rocketman rot (0,90,180) + 4 planes x5): ids, t, and the as-coded 8-bit frame
+  ref_scaled.npz     meshes under scales below / above 1 (scenes.scaled_meshes): ids, t and the as-coded 8-bit frame, whose
+                     colour is the un-normalised inverse-transpose normal and wraps above 255 (kernel.cu:117,214)
   ref_camera.npz     camera basis, inverse matrices and rays for three cameras
   ref_matrices.npz   model / inverse matrices of Geometry for a set of TRS triples
 """
@@ -37,9 +39,16 @@ def main():
     O.build()
     ref = O.Ref()
     rng = np.random.default_rng(20261104)
+    only = set(sys.argv[1:])  # e.g. `python tools/make_golden.py ref_scaled.npz`: write just that file (everything is still computed)
+
+    def save(fname, **arrays):
+        if only and fname not in only:
+            print("not rewritten:", fname)
+            return
+        np.savez_compressed(os.path.join(OUT, fname), **arrays)
 
     meshes = {k: ref.load_obj(os.path.join(REF_OBJ, k + ".obj")) for k in S.MESH_NAMES}
-    np.savez_compressed(os.path.join(OUT, "meshes.npz"), **meshes)
+    save("meshes.npz", **meshes)
     print({k: v.shape for k, v in meshes.items()})
 
     # ---- single-triangle known answers
@@ -69,8 +78,7 @@ def main():
         d = (tgt - o).astype(np.float32)
         d = (d / np.linalg.norm(d)).astype(np.float32)
         add(v9, o, d)
-    np.savez_compressed(os.path.join(OUT, "kat_triangle.npz"),
-                        v9=np.stack([c[0] for c in cases]), o=np.stack([c[1] for c in cases]), d=np.stack([c[2] for c in cases]),
+    save("kat_triangle.npz", v9=np.stack([c[0] for c in cases]), o=np.stack([c[1] for c in cases]), d=np.stack([c[2] for c in cases]),
                         hit=np.array([c[3] for c in cases], np.uint8), t=np.array([c[4] for c in cases], np.float32),
                         point=np.stack([c[5] for c in cases]), normal=np.stack([c[6] for c in cases]))
     print("kat_triangle:", len(cases), "cases,", int(sum(c[3] for c in cases)), "hits")
@@ -100,16 +108,16 @@ def main():
         for k in ("hit", "geom", "tri", "t", "point", "normal"):
             ident[name + "_" + k] = r[k]
         print("identity", name, "rays", len(rays), "hits", int(r["hit"].sum()))
-    np.savez_compressed(os.path.join(OUT, "ref_identity.npz"), **ident)
+    save("ref_identity.npz", **ident)
 
     # ---- config 1 and the main() scene
-    for desc, fname in ((S.config1(), "ref_c1.npz"), (S.reference_main(160, 160), "ref_main.npz")):
+    for desc, fname in ((S.config1(), "ref_c1.npz"), (S.reference_main(160, 160), "ref_main.npz"), (S.scaled_meshes(160, 160), "ref_scaled.npz")):
         sc = S.instantiate_on(desc, ref.scene(), meshes)
         rays, _ = ref.camera_rays(desc["camera"])
         r = sc.intersect(rays)
         out = dict(rays=rays, **r)
         out["as_coded"] = sc.render_as_coded(desc["camera"])
-        np.savez_compressed(os.path.join(OUT, fname), **out)
+        save(fname, **out)
         print(desc["name"], "rays", len(rays), "hits", int(r["hit"].sum()), "geoms hit", np.unique(r["geom"]))
 
     # ---- camera and matrices
@@ -121,7 +129,7 @@ def main():
         cam_out["cam%d" % i] = np.array([*cam["pos"], cam["yaw"], cam["pitch"], cam["fov"], cam["width"], cam["height"],
                                          cam["near"], cam["far"]], np.float64)
         cam_out["rays%d" % i], cam_out["basis%d" % i], cam_out["iv%d" % i], cam_out["ip%d" % i] = rays, basis, iv, ip
-    np.savez_compressed(os.path.join(OUT, "ref_camera.npz"), **cam_out)
+    save("ref_camera.npz", **cam_out)
     trs = [((0, 0, 0), (0, 0, 0), (1, 1, 1)), ((0, 0, 0), (0, 90, 180), (1, 1, 1)), ((-0.5, -0.5, 1.0), (0, 0, 0), (1, 1, 1)),
            ((0, 2.5, 0), (90, 0, 0), (5, 5, 5)), ((1.5, -2, 0.25), (33, -71, 12.5), (0.5, 2, 3))]
     mats = []
@@ -130,7 +138,7 @@ def main():
         gi = sc.add_mesh(meshes["triangle"], pos, rot, scl)
         m, inv = sc.matrices(gi)
         mats.append(np.concatenate([m, inv]))
-    np.savez_compressed(os.path.join(OUT, "ref_matrices.npz"), trs=np.array(trs, np.float32), mats=np.stack(mats))
+    save("ref_matrices.npz", trs=np.array(trs, np.float32), mats=np.stack(mats))
     total = sum(os.path.getsize(os.path.join(OUT, f)) for f in os.listdir(OUT))
     print("golden bytes:", total)
 

@@ -46,6 +46,9 @@ TRACE_BVH8, TRACE_BRUTE, TRACE_BVH2 = 0, 1, 2
 TRACE_COUNT = 0x100
 TRACE_STATIC = 0x200  # one-thread-per-ray kernel instead of the persistent dynamic-fetch kernel
 MAT_EMITTER, MAT_DIFFUSE, MAT_MIRROR, MAT_GLASS = 0, 1, 2, 3
+SPLIT_SAMPLES, SPLIT_TILES = 0, 1
+REDUCE_NCCL, REDUCE_PEER = 0, 1
+GROUP_ID_BYTES = 128
 
 
 class FireflyError(RuntimeError):
@@ -75,10 +78,10 @@ class CRenderParams(C.Structure):
 class CStats(C.Structure):
     _fields_ = [("gpu_ms", C.c_double), ("trace_ms", C.c_double), ("h2d_ms", C.c_double), ("d2h_ms", C.c_double),
                 ("rays", C.c_uint64), ("shadow_rays", C.c_uint64), ("paths", C.c_uint64), ("nodes_visited", C.c_uint64),
-                ("tris_tested", C.c_uint64), ("kernel_launches", C.c_uint32), ("reserved", C.c_uint32)]
+                ("tris_tested", C.c_uint64), ("kernel_launches", C.c_uint32), ("passes", C.c_uint32)]
 
     def as_dict(self):
-        return {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}
+        return {k: getattr(self, k) for k, _ in self._fields_}
 
 
 class CSceneInfo(C.Structure):
@@ -172,6 +175,19 @@ def _bind(lib):
     lib.ff_philox4x32_10.restype = None
     lib.ff_context_destroy.restype = None
     lib.ff_scene_destroy.restype = None
+    lib.ff_group_create.argtypes = [_vp, C.c_int, C.POINTER(_vp)]
+    lib.ff_group_unique_id.argtypes = [_vp]
+    lib.ff_group_create_rank.argtypes = [_vp, _vp, C.c_int, C.c_int, C.POINTER(_vp)]
+    lib.ff_group_destroy.argtypes = [_vp]
+    lib.ff_group_destroy.restype = None
+    lib.ff_group_world.argtypes = [_vp]
+    lib.ff_group_local_count.argtypes = [_vp]
+    lib.ff_group_rank.argtypes = [_vp, C.c_int]
+    lib.ff_group_context.argtypes = [_vp, C.c_int]
+    lib.ff_group_context.restype = _vp
+    lib.ff_group_sample_range.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    lib.ff_group_render.argtypes = [_vp, C.POINTER(_vp), C.POINTER(CCamera), C.POINTER(CRenderParams), C.c_int, C.c_int, _vp, _vp,
+                                    C.POINTER(CStats), C.POINTER(C.c_double)]
 
 
 def _check(rc):
@@ -351,7 +367,8 @@ class Context:
         if self.h:
             for _, p in self.__dict__.pop("_pinned", {}).values():
                 lib.ff_host_free_pinned(p)
-            lib.ff_context_destroy(self.h)
+            if not getattr(self, "_borrowed", False):  # a context of multigpu.Group.local belongs to its ff_group
+                lib.ff_context_destroy(self.h)
             self.h = C.c_void_p()
 
     def __del__(self):
@@ -363,10 +380,10 @@ class Context:
     def scene(self):
         return Scene(self)
 
-    def pinned_array(self, shape, dtype=np.float32):
-        """A numpy array over page-locked host memory (cudaHostAlloc), cached per (shape, dtype) for the life of the
-        context: device<->host copies to it are true DMA transfers.  Reused by later calls with the same shape."""
-        key = (tuple(shape), np.dtype(dtype).str)
+    def pinned_array(self, shape, dtype=np.float32, key=None):
+        """A numpy array over page-locked host memory (cudaHostAlloc), cached per (shape, dtype, key) for the life of the
+        context: device<->host copies to it are true DMA transfers.  Reused by later calls with the same shape and key."""
+        key = (tuple(shape), np.dtype(dtype).str, key)
         cache = self.__dict__.setdefault("_pinned", {})
         if key not in cache:
             nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
@@ -534,6 +551,16 @@ class Scene:
         _check(lib.ff_trace_closest(self.h, _p(rays), n, int(mode), _p(geom), _p(tri), _p(t), C.byref(st)))
         out = dict(hit=(geom >= 0).astype(np.uint8), geom=geom, tri=tri, t=t)
         return (out, st.as_dict()) if want_stats else out
+
+    def trace_closest_into(self, rays, geom, tri, t, mode=TRACE_BVH8):
+        """ff_trace_closest with caller-owned host buffers (page-locked ones from Context.pinned_array make the copies DMA
+        transfers that overlap the traversal); returns the stats of the call."""
+        assert rays.dtype == np.float32 and rays.flags.c_contiguous and rays.ndim == 2 and rays.shape[1] == 6
+        n = len(rays)
+        assert geom.dtype == np.int32 and tri.dtype == np.int32 and t.dtype == np.float32 and len(geom) == len(tri) == len(t) == n
+        st = CStats()
+        _check(lib.ff_trace_closest(self.h, _p(rays), n, int(mode), _p(geom), _p(tri), _p(t), C.byref(st)))
+        return st.as_dict()
 
     def trace_closest_uv(self, rays, mode=TRACE_BVH8):
         """trace_closest + the barycentrics of each hit (u, v weight v1, v2; kernel.cu:80-81)."""

@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libfirefly_b200.so")
-SOURCES = ["ff_trace.cu", "ff_bvh.cu", "ff_sah.cu", "ff_render.cu", "ff_api.cpp", "ff_io.cpp", "ff_obj.cpp", "ff_scenefile.cpp"]
+SOURCES = ["ff_trace.cu", "ff_bvh.cu", "ff_sah.cu", "ff_render.cu", "ff_api.cpp", "ff_group.cpp", "ff_io.cpp", "ff_obj.cpp", "ff_scenefile.cpp"]
 CLI = os.path.join(HERE, "firefly_cli")   # headless front end, links against the C ABI only
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
@@ -46,7 +46,7 @@ def build(force=False, verbose=False):
     os.makedirs(OBJ, exist_ok=True)
     with ThreadPoolExecutor(max_workers=len(SOURCES)) as ex:
         objs = list(ex.map(_compile, SOURCES))
-    cmd = [NVCC] + ARCH + ["-shared", "-o", LIB] + objs + ["-Wno-deprecated-gpu-targets"]
+    cmd = [NVCC] + ARCH + ["-shared", "-o", LIB] + objs + ["-Wno-deprecated-gpu-targets", "-ldl", "-lpthread"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n%s\n%s" % (r.stdout, r.stderr))

@@ -9,104 +9,18 @@
 #include <string>
 #include <vector>
 
-#include "ff_hostmath.h"
-#include "ff_internal.h"
+#include "ff_host.h"
 
 namespace ff {
 static thread_local std::string g_error;
 void set_error(const std::string& msg) { g_error = msg; }
+const std::string& get_error() { return g_error; }
 bool load_obj_positions(const char* path, std::vector<float>& xyz9);
 int write_image_float(const char* path, const float* rgba, int w, int h);
 int write_image_u8(const char* path, const unsigned char* rgb, int w, int h);
 }  // namespace ff
 
 using namespace ff;
-using ffm::M4;
-using ffm::V3;
-
-#define FF_CUDA(call)                                                                               \
-    do {                                                                                            \
-        cudaError_t e_ = (call);                                                                    \
-        if (e_ != cudaSuccess) {                                                                    \
-            set_error(std::string(#call) + ": " + cudaGetErrorString(e_));                          \
-            return FF_ERR_CUDA;                                                                     \
-        }                                                                                           \
-    } while (0)
-#define FF_REQUIRE(cond, msg)                                                                       \
-    do {                                                                                            \
-        if (!(cond)) { set_error(msg); return FF_ERR_INVALID; }                                     \
-    } while (0)
-
-struct ff_context {
-    int device = 0;
-    cudaStream_t stream = nullptr;
-    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
-    std::vector<cudaEvent_t> trace_events;
-    float4* flush_buf = nullptr;
-    size_t flush_n = 0;
-    cudaEvent_t timer_ev[2] = {nullptr, nullptr};  // ff_timer_begin / ff_timer_end
-    bool timer_open = false;
-    float4* resolve_buf = nullptr;  // device staging of ff_resolve / ff_reduce_resolve_peers when the caller gives no device output
-    size_t resolve_pixels = 0;
-    Arena arena;                    // builder scratch, reused by every commit on this context
-    std::vector<ff_scene*> scenes;  // live scenes: orphaned (device memory released) if the context goes first
-};
-
-struct HostGeom {
-    int type;  // 0 sphere, 1 plane, 2 triangle mesh (GeometryType, utilities.h:141-146)
-    float radius = 1.0f;
-    M4 model, inv;
-    ff_material mat;
-    std::vector<float> xyz9;  // object space
-    // optional shading attributes, empty when absent
-    std::vector<float> n9, uv6;              // per-corner object-space normals / uvs
-    std::vector<int> face_mat;               // per triangle: index into face_materials, -1 = mat
-    std::vector<ff_material> face_materials;
-};
-
-struct ff_scene {
-    ff_context* ctx = nullptr;
-    std::vector<HostGeom> geoms;
-    bool committed = false;
-    // device
-    float4* d_flat = nullptr;  // baked triangles in flat order
-    float4* d_tris = nullptr;  // baked triangles in leaf order
-    float4* d_nodes = nullptr;
-    int* d_ord_geom = nullptr;
-    int* d_ord_tri = nullptr;
-    float4* d_materials = nullptr;
-    DevPlane* d_planes = nullptr;
-    uint32_t* d_lights = nullptr;
-    int4* d_geom_attr = nullptr;
-    float4* d_attr_normals = nullptr;
-    float2* d_attr_uvs = nullptr;
-    uint32_t* d_attr_facemat = nullptr;
-    int2* d_bvh2_children = nullptr;
-    float4* d_bvh2_lo = nullptr;
-    float4* d_bvh2_hi = nullptr;
-    uint32_t* d_leaf_slot = nullptr;
-    float4* d_as_coded_normals = nullptr;  // per flat triangle, built by the first as-coded frame after a commit (ensure_as_coded_normals)
-    cudaTextureObject_t nodes_tex = 0, tris_tex = 0;  // kernel variants FF_NODE_TEX / FF_TRI_TEX only
-    DevScene dev;
-    ff_scene_info info;
-    // render scratch (grown on demand)
-    WaveBuffers wb;
-    size_t wb_capacity = 0;
-    int wb_counts = 0;
-    bool wb_shadow = false;
-    float4* d_accum = nullptr;
-    float4* d_out = nullptr;
-    size_t fb_pixels = 0;
-    unsigned char* d_u8 = nullptr;  // device staging of ff_render_u8 when the caller's buffer is host memory
-    size_t u8_bytes = 0;
-    // tile split: owned-pixel list of the last (width, height, tile, rank, world) rendered
-    uint32_t* d_pixel_map = nullptr;
-    size_t pixel_map_count = 0;
-    int pixel_map_key[5] = {0, 0, 0, 0, 0};
-    uint32_t* d_work_counter = nullptr;
-    unsigned long long* d_ray_counter = nullptr;
-    TraceCounters* d_trace_counters = nullptr;
-};
 
 static void free_scene_device(ff_scene* s) {
     if (s->nodes_tex) cudaDestroyTextureObject(s->nodes_tex);
@@ -131,17 +45,6 @@ static void free_render_scratch(ff_scene* s) {
     cudaFree(s->d_pixel_map); s->d_pixel_map = nullptr; s->pixel_map_count = 0;
     cudaFree(s->d_u8); s->d_u8 = nullptr; s->u8_bytes = 0;
 }
-
-// Device temporary that is released on every exit path (FF_CUDA / FF_REQUIRE return early).
-struct DevTmp {
-    void* p = nullptr;
-    DevTmp() = default;
-    DevTmp(const DevTmp&) = delete;
-    DevTmp& operator=(const DevTmp&) = delete;
-    ~DevTmp() { if (p) cudaFree(p); }
-    cudaError_t alloc(size_t bytes) { if (p) { cudaFree(p); p = nullptr; } return bytes ? cudaMalloc(&p, bytes) : cudaSuccess; }
-    template <class T> T* as() const { return (T*)p; }
-};
 
 template <class T>
 static cudaError_t upload(T** dptr, const std::vector<T>& h, cudaStream_t st) {
@@ -195,6 +98,13 @@ void ff_context_destroy(ff_context* ctx) {
     for (int k = 0; k < 2; ++k) cudaEventDestroy(ctx->timer_ev[k]);
     cudaFree(ctx->flush_buf);
     cudaFree(ctx->resolve_buf);
+    if (ctx->pipe.ready) {
+        TracePipe& tp = ctx->pipe;
+        for (int k = 0; k < FF_PIPE_SLOTS; ++k) { cudaFree(tp.block[k]); cudaEventDestroy(tp.in_done[k]); cudaEventDestroy(tp.comp_done[k]); cudaEventDestroy(tp.out_done[k]); }
+        for (int k = 0; k < 5; ++k) cudaEventDestroy(tp.span[k]);
+        cudaFree(tp.work);
+        cudaStreamDestroy(tp.s_in); cudaStreamDestroy(tp.s_out);
+    }
     ctx->arena.release();
     cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -747,6 +657,31 @@ int ff_hits_unpack(ff_scene* scene, const void* d_hits, size_t n, int* out_geom,
 int ff_trace_closest(ff_scene* scene, const float* rays6, size_t n, int mode, int* out_geom, int* out_tri, float* out_t, ff_stats* stats) {
     return ff_trace_closest_uv(scene, rays6, n, mode, out_geom, out_tri, out_t, nullptr, nullptr, stats);
 }
+// Layout of one pipeline slot (bytes per ray): rays6 24 | packed o,d 32 | hit record 16 | geom 4 | tri 4 | t 4 | u,v 8.
+static const size_t kPipeBytesPerRay = 24 + 32 + 16 + 4 + 4 + 4 + 8;
+static int ensure_pipe(ff_context* c, size_t chunk) {
+    TracePipe& tp = c->pipe;
+    if (!tp.ready) {
+        FF_CUDA(cudaStreamCreateWithFlags(&tp.s_in, cudaStreamNonBlocking));
+        FF_CUDA(cudaStreamCreateWithFlags(&tp.s_out, cudaStreamNonBlocking));
+        for (int k = 0; k < FF_PIPE_SLOTS; ++k) {
+            FF_CUDA(cudaEventCreateWithFlags(&tp.in_done[k], cudaEventDisableTiming));
+            FF_CUDA(cudaEventCreateWithFlags(&tp.comp_done[k], cudaEventDisableTiming));
+            FF_CUDA(cudaEventCreateWithFlags(&tp.out_done[k], cudaEventDisableTiming));
+        }
+        for (int k = 0; k < 5; ++k) FF_CUDA(cudaEventCreate(&tp.span[k]));
+        FF_CUDA(cudaMalloc((void**)&tp.work, sizeof(uint32_t) * FF_PIPE_SLOTS));
+        tp.ready = true;
+    }
+    chunk = (chunk + 3) & ~(size_t)3;  // keeps every sub-array of a slot 16-byte aligned
+    if (tp.chunk < chunk) {
+        for (int k = 0; k < FF_PIPE_SLOTS; ++k) { cudaFree(tp.block[k]); tp.block[k] = nullptr; }
+        tp.chunk = 0;
+        for (int k = 0; k < FF_PIPE_SLOTS; ++k) FF_CUDA(cudaMalloc((void**)&tp.block[k], kPipeBytesPerRay * chunk + 1024));
+        tp.chunk = chunk;
+    }
+    return FF_OK;
+}
 int ff_trace_closest_uv(ff_scene* scene, const float* rays6, size_t n, int mode, int* out_geom, int* out_tri, float* out_t,
                         float* out_u, float* out_v, ff_stats* stats) {
     int rc = check_scene(scene, "ff_trace_closest");
@@ -755,43 +690,83 @@ int ff_trace_closest_uv(ff_scene* scene, const float* rays6, size_t n, int mode,
     FF_REQUIRE(rays6 || n == 0, "ff_trace_closest: NULL rays");
     if (stats) memset(stats, 0, sizeof(*stats));
     if (n == 0) return FF_OK;
-    ff_context* c = scene->ctx;
-    cudaStream_t st = c->stream;
     FF_REQUIRE(n < 0xffffffffull, "ff_trace_closest: batch too large");
-    DevTmp t6, tr, th, tg, tt, tk, tuv;  // released on every exit path
-    FF_CUDA(t6.alloc(sizeof(float) * 6 * n));
-    FF_CUDA(tr.alloc(sizeof(float4) * 2 * n));
-    FF_CUDA(th.alloc(sizeof(HitRec) * n));
-    FF_CUDA(tg.alloc(sizeof(int) * n)); FF_CUDA(tt.alloc(sizeof(int) * n)); FF_CUDA(tk.alloc(sizeof(float) * n));
-    if (out_u || out_v) FF_CUDA(tuv.alloc(sizeof(float) * 2 * n));
-    float* d6 = t6.as<float>(); float4* dr = tr.as<float4>(); HitRec* dh = th.as<HitRec>();
-    int *dg = tg.as<int>(), *dt = tt.as<int>(); float* dk = tk.as<float>(); float* duv = tuv.as<float>();
-    double h2d, d2h;
-    {
-        ScopedTimer t(c, 2, 3);
-        FF_CUDA(cudaMemcpyAsync(d6, rays6, sizeof(float) * 6 * n, cudaMemcpyHostToDevice, st));
-        k_pack_rays(d6, n, dr, dr + n, st);
-        h2d = t.stop();
+    ff_context* c = scene->ctx;
+    if ((rc = ensure_counters(scene))) return rc;
+    // ~1 Mi rays per chunk: large enough that the persistent kernel's tail is a few per cent of a chunk, small enough that
+    // the first copy-in and the last copy-out (the only transfers nothing overlaps) are a small part of the call
+    static const size_t chunk_pref = [] { const char* e = getenv("FF_TRACE_CHUNK"); const long v = e ? atol(e) : 0; return v > 0 ? (size_t)v : (size_t)1 << 20; }();
+    const size_t chunk = std::min(n, chunk_pref);
+    const size_t n_chunks = (n + chunk - 1) / chunk;
+    if ((rc = ensure_pipe(c, chunk))) return rc;
+    TracePipe& tp = c->pipe;
+    cudaStream_t st = c->stream;
+    const bool count = (mode & FF_TRACE_COUNT) != 0;
+    const bool want_uv = out_u || out_v;
+    if (count) FF_CUDA(cudaMemsetAsync(scene->d_trace_counters, 0, sizeof(TraceCounters), st));
+    while (c->trace_events.size() < 2 * n_chunks) { cudaEvent_t e; FF_CUDA(cudaEventCreate(&e)); c->trace_events.push_back(e); }
+    // everything below is ordered after what is already queued on the context's stream (so an ff_timer bracket sees it)
+    FF_CUDA(cudaEventRecord(tp.span[0], st));
+    FF_CUDA(cudaStreamWaitEvent(tp.s_in, tp.span[0], 0));
+    FF_CUDA(cudaStreamWaitEvent(tp.s_out, tp.span[0], 0));
+    for (size_t k = 0; k < n_chunks; ++k) {
+        const int slot = (int)(k % FF_PIPE_SLOTS);
+        const size_t first = k * chunk, m = std::min(chunk, n - first);
+        char* b = tp.block[slot];
+        float* d6 = (float*)b;
+        float4* dr = (float4*)(b + 24 * tp.chunk);
+        HitRec* dh = (HitRec*)(b + 56 * tp.chunk);
+        int* dg = (int*)(b + 72 * tp.chunk);
+        int* dt = dg + tp.chunk;
+        float* dk = (float*)(dt + tp.chunk);
+        float* duv = dk + tp.chunk;
+        // copy in (the slot's previous chunk must have been packed: its compute stage is done)
+        if (k >= FF_PIPE_SLOTS) FF_CUDA(cudaStreamWaitEvent(tp.s_in, tp.comp_done[slot], 0));
+        FF_CUDA(cudaMemcpyAsync(d6, rays6 + 6 * first, sizeof(float) * 6 * m, cudaMemcpyHostToDevice, tp.s_in));
+        FF_CUDA(cudaEventRecord(tp.in_done[slot], tp.s_in));
+        if (k + 1 == n_chunks) FF_CUDA(cudaEventRecord(tp.span[1], tp.s_in));
+        // pack + trace + unpack (the slot's previous outputs must have left the device)
+        FF_CUDA(cudaStreamWaitEvent(st, tp.in_done[slot], 0));
+        if (k >= FF_PIPE_SLOTS) FF_CUDA(cudaStreamWaitEvent(st, tp.out_done[slot], 0));
+        k_pack_rays(d6, m, dr, dr + m, st);
+        FF_CUDA(cudaMemsetAsync(tp.work + slot, 0, sizeof(uint32_t), st));
+        FF_CUDA(cudaEventRecord(c->trace_events[2 * k], st));
+        k_trace_closest(scene->dev, dr, dr + m, nullptr, (uint32_t)m, mode, dh, scene->d_trace_counters, tp.work + slot, st);
+        FF_CUDA(cudaEventRecord(c->trace_events[2 * k + 1], st));
+        k_unpack_hits(scene->dev, dh, m, dg, dt, dk, st);
+        if (want_uv) k_hit_barycentrics(scene->dev, dr, dr + m, dh, m, duv, duv + m, st);
+        FF_CUDA(cudaEventRecord(tp.comp_done[slot], st));
+        // copy out
+        FF_CUDA(cudaStreamWaitEvent(tp.s_out, tp.comp_done[slot], 0));
+        if (k == 0) FF_CUDA(cudaEventRecord(tp.span[2], tp.s_out));
+        if (out_geom) FF_CUDA(cudaMemcpyAsync(out_geom + first, dg, sizeof(int) * m, cudaMemcpyDeviceToHost, tp.s_out));
+        if (out_tri) FF_CUDA(cudaMemcpyAsync(out_tri + first, dt, sizeof(int) * m, cudaMemcpyDeviceToHost, tp.s_out));
+        if (out_t) FF_CUDA(cudaMemcpyAsync(out_t + first, dk, sizeof(float) * m, cudaMemcpyDeviceToHost, tp.s_out));
+        if (out_u) FF_CUDA(cudaMemcpyAsync(out_u + first, duv, sizeof(float) * m, cudaMemcpyDeviceToHost, tp.s_out));
+        if (out_v) FF_CUDA(cudaMemcpyAsync(out_v + first, duv + m, sizeof(float) * m, cudaMemcpyDeviceToHost, tp.s_out));
+        FF_CUDA(cudaEventRecord(tp.out_done[slot], tp.s_out));
     }
-    ff_stats inner;
-    rc = ff_trace_closest_device(scene, dr, n, mode, dh, &inner);
-    if (rc == FF_OK) {
-        ScopedTimer t(c, 2, 3);
-        k_unpack_hits(scene->dev, dh, n, dg, dt, dk, st);
-        if (out_geom) cudaMemcpyAsync(out_geom, dg, sizeof(int) * n, cudaMemcpyDeviceToHost, st);
-        if (out_tri) cudaMemcpyAsync(out_tri, dt, sizeof(int) * n, cudaMemcpyDeviceToHost, st);
-        if (out_t) cudaMemcpyAsync(out_t, dk, sizeof(float) * n, cudaMemcpyDeviceToHost, st);
-        if (duv) {
-            k_hit_barycentrics(scene->dev, dr, dr + n, dh, n, duv, duv + n, st);
-            if (out_u) cudaMemcpyAsync(out_u, duv, sizeof(float) * n, cudaMemcpyDeviceToHost, st);
-            if (out_v) cudaMemcpyAsync(out_v, duv + n, sizeof(float) * n, cudaMemcpyDeviceToHost, st);
+    FF_CUDA(cudaEventRecord(tp.span[3], tp.s_out));
+    FF_CUDA(cudaStreamWaitEvent(st, tp.span[3], 0));   // the context's stream (and an open ff_timer) ends after the last copy
+    FF_CUDA(cudaEventRecord(tp.span[4], st));
+    FF_CUDA(cudaEventSynchronize(tp.span[4]));
+    FF_CUDA(cudaGetLastError());
+    if (stats) {
+        float ms = 0;
+        cudaEventElapsedTime(&ms, tp.span[0], tp.span[4]); stats->gpu_ms = ms;
+        cudaEventElapsedTime(&ms, tp.span[0], tp.span[1]); stats->h2d_ms = ms;   // span of the copy-in stream's activity
+        cudaEventElapsedTime(&ms, tp.span[2], tp.span[3]); stats->d2h_ms = ms;   // span of the copy-out stream's activity
+        double tr = 0;
+        for (size_t k = 0; k < n_chunks; ++k) { cudaEventElapsedTime(&ms, c->trace_events[2 * k], c->trace_events[2 * k + 1]); tr += ms; }
+        stats->trace_ms = tr; stats->rays = n; stats->passes = (uint32_t)n_chunks;
+        stats->kernel_launches = (uint32_t)(n_chunks * (want_uv ? 4 : 3));
+        if (count) {
+            TraceCounters h;
+            FF_CUDA(cudaMemcpy(&h, scene->d_trace_counters, sizeof(h), cudaMemcpyDeviceToHost));
+            stats->nodes_visited = h.nodes; stats->tris_tested = h.tris;
         }
-        d2h = t.stop();
-        cudaError_t e = cudaGetLastError();
-        if (e != cudaSuccess) { set_error(cudaGetErrorString(e)); rc = FF_ERR_CUDA; }
-        if (stats) { *stats = inner; stats->h2d_ms = h2d; stats->d2h_ms = d2h; stats->gpu_ms += h2d + d2h; stats->kernel_launches += 2; }
     }
-    return rc;
+    return FF_OK;
 }
 
 int ff_trace_any(ff_scene* scene, const float* rays6, const float* tmax, size_t n, int mode, unsigned char* out_occluded, ff_stats* stats) {
@@ -1096,7 +1071,7 @@ int accumulate_samples(ff_scene* scene, const ff_camera* cam, const ff_render_pa
         stats->nodes_visited += h.nodes; stats->tris_tested += h.tris;
     }
     if (stats) {
-        stats->gpu_ms += ms; stats->rays += rays; stats->shadow_rays += shadow_rays; stats->paths += (uint64_t)p->spp * npix; stats->kernel_launches += launches;
+        stats->gpu_ms += ms; stats->rays += rays; stats->shadow_rays += shadow_rays; stats->paths += (uint64_t)p->spp * npix; stats->kernel_launches += launches; stats->passes += (uint32_t)n_pass;
         if (time_trace) {
             double tr = 0;
             for (int k = 0; k + 1 < n_ev; k += 2) { float m = 0; cudaEventElapsedTime(&m, c->trace_events[k], c->trace_events[k + 1]); tr += m; }
@@ -1106,6 +1081,18 @@ int accumulate_samples(ff_scene* scene, const ff_camera* cam, const ff_render_pa
     return FF_OK;
 }
 }  // namespace
+
+namespace ff {
+int host_check_render(ff_scene* scene, const ff_camera* cam, const ff_render_params* params, const char* who) {
+    int rc = check_scene(scene, who);
+    if (rc) return rc;
+    if ((rc = check_cam(cam, who))) return rc;
+    return check_params(params, who);
+}
+int host_accumulate_samples(ff_scene* scene, const ff_camera* cam, const ff_render_params* params, float4* d_accum, ff_stats* stats) {
+    return accumulate_samples(scene, cam, params, d_accum, stats);
+}
+}  // namespace ff
 
 extern "C" {
 

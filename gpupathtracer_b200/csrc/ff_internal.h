@@ -211,6 +211,9 @@ void k_megakernel_pass(const DevScene& sc, const CamDev& cam, const RenderDev& r
                        uint32_t* d_work_counter, unsigned long long* d_ray_counter, uint32_t* launches, cudaStream_t st);
 void k_accumulate_pass(const float4* d_radiance, uint32_t npix, uint32_t samples, const uint32_t* d_pixel_map, float4* d_accum, cudaStream_t st);
 void k_resolve(const float4* const* accums, int n_accums, uint32_t npix, float inv_spp, float4* d_out, cudaStream_t st);
+// FF_REDUCE_PEER: this GPU's slice [first, first + count) of the frame, summed over `world` accumulators in rank order
+// (pointers valid on this device: own memory or NVLink peers), resolved and stored into the root's frame.
+void k_reduce_scatter_resolve(const float4* const* accums, int world, uint32_t first, uint32_t count, float inv_spp, float4* d_out_root, cudaStream_t st);
 void k_as_coded(const DevScene& sc, const CamDev& cam, const float4* d_as_coded_normals, unsigned char* d_rgb, cudaStream_t st);
 // Primary-ray feature buffers (FF_INTEGRATOR_AOV_*): shading normal, uv, barycentrics, albedo of the first hit.
 void k_aov(const DevScene& sc, const CamDev& cam, int kind, float4* d_rgba, cudaStream_t st);

@@ -572,6 +572,47 @@ void k_resolve(const float4* const* accums, int n_accums, uint32_t npix, float i
     resolve_kernel<<<grid_for(npix, 256, sm_count() * 16), 256, 0, st>>>(pp, n_accums, npix, inv_spp, d_out);
 }
 
+// Fused framebuffer reduce-scatter + resolve + gather over peer memory (FF_REDUCE_PEER, ff_group.cpp): the GPU that runs this
+// sums pixels [first, first + count) of EVERY rank's accumulator -- its own from HBM, the peers' over NVLink -- in rank order,
+// scales by 1/spp and stores the finished pixels into the root's frame (a peer store unless this GPU is the root).  All GPUs
+// run it at once on their own slice, so each NVLink ingress carries (world-1)/world of one accumulator.  Peer loads bypass L1
+// (ld.global.cg): the lines belong to another GPU's memory and were rewritten since the last frame.  Four pixels per thread
+// and iteration keep 4 x world independent 16-byte loads in flight per thread, which is what hides the NVLink latency.
+#define FF_RS_UNROLL 4
+__global__ void __launch_bounds__(256) reduce_scatter_resolve_kernel(PeerPtrs peers, int world, uint32_t first, uint32_t count, float inv_spp,
+                                                                      float4* __restrict__ out) {
+    const uint32_t stride = gridDim.x * blockDim.x * FF_RS_UNROLL;
+    for (uint32_t base = blockIdx.x * blockDim.x * FF_RS_UNROLL + threadIdx.x; base < count; base += stride) {
+        float4 a[FF_RS_UNROLL];
+#pragma unroll
+        for (int u = 0; u < FF_RS_UNROLL; ++u) {
+            const uint32_t i = base + u * blockDim.x;
+            a[u] = i < count ? __ldcg(peers.p[0] + first + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        for (int r = 1; r < world; ++r) {
+            float4 b[FF_RS_UNROLL];
+#pragma unroll
+            for (int u = 0; u < FF_RS_UNROLL; ++u) {
+                const uint32_t i = base + u * blockDim.x;
+                b[u] = i < count ? __ldcg(peers.p[r] + first + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+#pragma unroll
+            for (int u = 0; u < FF_RS_UNROLL; ++u) { a[u].x = fadd(a[u].x, b[u].x); a[u].y = fadd(a[u].y, b[u].y); a[u].z = fadd(a[u].z, b[u].z); }
+        }
+#pragma unroll
+        for (int u = 0; u < FF_RS_UNROLL; ++u) {
+            const uint32_t i = base + u * blockDim.x;
+            if (i < count) out[first + i] = make_float4(fmul(a[u].x, inv_spp), fmul(a[u].y, inv_spp), fmul(a[u].z, inv_spp), 1.0f);
+        }
+    }
+}
+void k_reduce_scatter_resolve(const float4* const* accums, int world, uint32_t first, uint32_t count, float inv_spp, float4* d_out_root, cudaStream_t st) {
+    if (!count) return;
+    PeerPtrs pp;
+    for (int i = 0; i < 8; ++i) pp.p[i] = i < world ? accums[i] : nullptr;
+    reduce_scatter_resolve_kernel<<<grid_for((count + FF_RS_UNROLL - 1) / FF_RS_UNROLL, 256, sm_count() * 8), 256, 0, st>>>(pp, world, first, count, inv_spp, d_out_root);
+}
+
 // ------------------------------------------------------------------ primary-ray feature buffers
 // One ray per pixel through the integer pixel corner (kernel.cu:200-201), first hit only.  kind: 3 shading normal
 // (interpolated when the geometry has normals, else geometric; face-forwarded, world space), 4 uv, 5 barycentrics

@@ -98,7 +98,8 @@ typedef struct ff_stats {
     uint64_t nodes_visited;  /* instrumented runs only (ff_trace flag FF_TRACE_COUNT), else 0 */
     uint64_t tris_tested;    /* idem */
     uint32_t kernel_launches;
-    uint32_t reserved;
+    uint32_t passes;         /* render calls: wavefront / megakernel passes actually run (spp / the samples-per-pass the library chose,
+                              * which is smaller than the default when the path state did not fit); trace calls: pipeline chunks */
 } ff_stats;
 
 typedef struct ff_scene_info {
@@ -194,6 +195,10 @@ int ff_scene_get_matrices(const ff_scene* scene, int geometry_index, float model
 #define FF_TRACE_COUNT 0x100 /* OR into `mode`: instrumented kernel, fills nodes_visited / tris_tested */
 int ff_trace_closest(ff_scene* scene, const float* rays6, size_t n, int mode, int* out_geom, int* out_tri,
                      float* out_t, ff_stats* stats);
+/*    Host batches run as a three-stage pipeline over chunks of ~1 Mi rays (copy in | pack + trace + unpack | copy out on
+ *    three streams, device staging owned by the context and reused across calls), so with page-locked host buffers
+ *    (ff_host_alloc_pinned) the PCIe transfers of one chunk overlap the traversal of its neighbours.  Pageable buffers work
+ *    and are simply slower.  stats: gpu_ms = device time from the first copy to the last, trace_ms = traversal kernels only. */
 /* Same with device-resident buffers (no copies): d_rays = 2n float4, SoA: n origins {o.xyz, 0} followed by
  * n directions {d.xyz, 0}; d_hits = n 16-byte records {key t (f32), t along the ray (f32), triangle slot
  * (i32), scan-order id (i32)} -- see ff_hits_unpack. */
@@ -234,6 +239,43 @@ int ff_resolve(ff_context* ctx, const void* d_accum_rgba, int width, int height,
  * CUDA-IPC mapped peers over NVLink) in rank order and divides by total_spp in one kernel. */
 int ff_reduce_resolve_peers(ff_context* ctx, const void* const* d_accum_peers, int n_peers, int width,
                             int height, int total_spp, void* d_out_rgba, float* out_rgba_host);
+
+/* -- multi-GPU group (BASELINE.json north_star).  The reference is single-GPU: its `multi_gpu` flag is dead
+ *    (utilities.h:484-487).  The image is partitioned over the GPUs of one node by disjoint sample ranges or by interleaved
+ *    screen tiles, the scene + BVH are replicated (commit the same scene on every context), and the per-GPU accumulators are
+ *    combined by ONE framebuffer reduce per frame over NVLink, inside the library.  Philox is keyed by the GLOBAL sample
+ *    index, so the set of paths does not depend on the number of GPUs.
+ *      ff_group_create       one process drives n devices: one context (ff_group_context) and one host thread per device
+ *      ff_group_create_rank  one process per GPU (torchrun / MPI style): rank 0 makes an id with ff_group_unique_id and hands
+ *                            its FF_GROUP_ID_BYTES to the other ranks by any means; every rank passes its own context.
+ *                            Collective, like every ff_group_render of such a group.  world 1 needs no id (may be NULL).
+ *    NCCL (libnccl.so.2) is loaded at run time when a group of more than one GPU is formed; FF_ERR_UNSUPPORTED without it. */
+typedef struct ff_group ff_group;
+#define FF_GROUP_ID_BYTES 128
+enum { FF_SPLIT_SAMPLES = 0,  /* rank k renders samples [k*spp/G, (k+1)*spp/G) of every pixel (ff_group_sample_range) */
+       FF_SPLIT_TILES = 1 };  /* rank k renders all samples of the 32x32 tiles t with t % G == k (ff_render_params.tile_*):
+                               * bit-identical to one GPU for every G */
+enum { FF_REDUCE_NCCL = 0,    /* ncclReduce(SUM) of the accumulators to the root + resolve kernel */
+       FF_REDUCE_PEER = 1 };  /* one fused kernel per GPU: reduce-scatter + resolve + gather over NVLink peer memory (peer
+                               * access in one process, CUDA IPC between processes); summation in rank order, so the frame is
+                               * bit-reproducible for a given G.  FF_ERR_UNSUPPORTED when the GPUs have no peer path */
+int ff_group_create(const int* device_ids, int n, ff_group** out);
+int ff_group_unique_id(unsigned char id[FF_GROUP_ID_BYTES]);
+int ff_group_create_rank(ff_context* ctx, const unsigned char id[FF_GROUP_ID_BYTES], int rank, int world, ff_group** out);
+void ff_group_destroy(ff_group* group);   /* destroys the contexts of ff_group_create (destroy their scenes first); never the one passed to _create_rank */
+int ff_group_world(const ff_group* group);                    /* GPUs in the group */
+int ff_group_local_count(const ff_group* group);              /* contexts this process drives: n, or 1 */
+int ff_group_rank(const ff_group* group, int local_index);    /* global rank of a local context; rank 0 is the root */
+ff_context* ff_group_context(ff_group* group, int local_index);
+int ff_group_nccl_version(void);                              /* e.g. 22703, 0 when NCCL cannot be loaded */
+int ff_group_sample_range(int rank, int world, int spp, int* out_first, int* out_count);
+/* One frame.  scenes[i] = the committed scene on the group's i-th local context.  params->spp is the frame's TOTAL sample
+ * count (the mean divides by params->total_spp when that is set: accumulating frames), first_sample the global index of its
+ * first sample.  The resolved frame (mean radiance, RGBA fp32, as ff_render) arrives on the root: out_rgba_host and / or
+ * out_rgba_device (memory of the root's device); other ranks of a one-process-per-GPU group pass NULL.  stats = one ff_stats
+ * per local context (may be NULL); *out_reduce_ms = device time of reduce + resolve, max over the local contexts. */
+int ff_group_render(ff_group* group, ff_scene* const* scenes, const ff_camera* cam, const ff_render_params* params, int split,
+                    int reduce, float* out_rgba_host, void* out_rgba_device, ff_stats* stats, double* out_reduce_ms);
 
 /* -- synthetic workloads of BASELINE.json configs 4/5, generated on the device with the same
  *    Philox streams as the oracle (bit-identical to the host generators). */

@@ -1061,4 +1061,35 @@ long orc_render(void* s, const float pos[3], const float world_up[3], float yaw,
     return total;
 }
 
+// The same tracer over the pixel rectangle [x0, x0 + cw) x [y0, y0 + ch) of the width x height frame (paths are keyed by
+// the pixel's index in the FULL frame, so the crop equals those pixels of orc_render bit for bit): lets a tile of a
+// full-size benchmark frame be checked in seconds.  out_rgba = cw * ch * 4 floats, row-major inside the crop.
+long orc_render_crop(void* s, const float pos[3], const float world_up[3], float yaw, float pitch, float fov, int width,
+                     int height, float near_clip, float far_clip, int spp, int max_bounces, uint32_t seed_lo,
+                     uint32_t seed_hi, int first_sample, int aa, const float background[3], float ray_eps, int nee,
+                     int x0, int y0, int cw, int ch, float* out_rgba, int nthreads) {
+    OScene* os = (OScene*)s;
+    os->get_flat();
+    Camera cam = make_camera(pos, world_up, yaw, pitch, fov, (float)width, (float)height, near_clip, far_clip);
+    M4 invVP = mulMM(cam.invView(), cam.invProj());
+    RenderParams rp{spp, max_bounces, seed_lo, seed_hi, first_sample, aa, {background[0], background[1], background[2]}, ray_eps, nee};
+    std::vector<long> counts((size_t)cw * ch, 0);
+    long* cptr = counts.data();
+    parallel_for((size_t)cw * ch, nthreads, [=](size_t a, size_t b) {
+        for (size_t i = a; i < b; ++i) {
+            const int x = x0 + (int)(i % (size_t)cw), y = y0 + (int)(i / (size_t)cw);
+            long local = 0, slocal = 0;
+            V3 sum{0, 0, 0};
+            for (int k = 0; k < spp; ++k) sum = add(sum, trace_path(*os, cam, invVP, x, y, (uint32_t)(first_sample + k), rp, &local, &slocal));
+            float inv = 1.0f / (float)spp;
+            float* px = out_rgba + 4 * i;
+            px[0] = sum.x * inv; px[1] = sum.y * inv; px[2] = sum.z * inv; px[3] = 1.0f;
+            cptr[i] = local;
+        }
+    });
+    long total = 0;
+    for (long c : counts) total += c;
+    return total;
+}
+
 }  // extern "C"

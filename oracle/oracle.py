@@ -262,6 +262,22 @@ class OracleScene(_SceneBase):
         return out, n
 
 
+    def render_crop(self, cam, spp, max_bounces, x0, y0, cw, ch, seed=1234, first_sample=0, aa=0, background=(0, 0, 0),
+                    ray_eps=1e-4, threads=None, nee=0):
+        """Pixels [x0, x0+cw) x [y0, y0+ch) of render(cam, ...), bit for bit (paths are keyed by the full-frame pixel index)."""
+        w, h = int(cam["width"]), int(cam["height"])
+        assert 0 <= x0 and 0 <= y0 and x0 + cw <= w and y0 + ch <= h
+        out = np.empty((ch, cw, 4), np.float32)
+        fn = self.o.f("render_crop")
+        fn.restype = C.c_long
+        n = fn(self.h, _vec3(cam["pos"]), _vec3(cam.get("world_up", (0, 1, 0))), C.c_float(cam["yaw"]),
+               C.c_float(cam["pitch"]), C.c_float(cam["fov"]), w, h, C.c_float(cam["near"]), C.c_float(cam["far"]),
+               int(spp), int(max_bounces), C.c_uint32(seed & 0xFFFFFFFF), C.c_uint32((seed >> 32) & 0xFFFFFFFF),
+               int(first_sample), int(aa), _vec3(background), C.c_float(ray_eps), int(nee), int(x0), int(y0), int(cw), int(ch),
+               _ptr(out), int(threads or self.o.threads))
+        return out, n
+
+
 class Ref(_Base):
     prefix = "ref_"
     so = REF_SO

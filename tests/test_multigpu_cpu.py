@@ -26,6 +26,28 @@ def test_sample_range_partition():
         M.sample_range(2, 2, 4)
 
 
+def test_group_api_host_side():
+    """The parts of the ff_group API that need no device: the sample split equals its Python statement, and bad arguments
+    come back as status codes (never a crash)."""
+    import ctypes as C
+    import gpupathtracer_b200 as ff
+    for spp in (0, 1, 2, 7, 64, 1000):
+        for world in (1, 2, 3, 4, 8):
+            for r in range(world):
+                a, b = C.c_int(-1), C.c_int(-1)
+                assert ff.lib.ff_group_sample_range(r, world, spp, C.byref(a), C.byref(b)) == 0
+                assert (a.value, b.value) == M.sample_range(r, world, spp)
+    a, b = C.c_int(), C.c_int()
+    assert ff.lib.ff_group_sample_range(2, 2, 4, C.byref(a), C.byref(b)) < 0
+    h = C.c_void_p()
+    assert ff.lib.ff_group_create_rank(None, None, 0, 1, C.byref(h)) < 0 and not h.value
+    assert ff.lib.ff_group_create(None, 2, C.byref(h)) < 0 and not h.value
+    ids = (C.c_int * 2)(0, 0)
+    assert ff.lib.ff_group_create(ids, 2, C.byref(h)) < 0 and b"twice" in ff.lib.ff_last_error()
+    assert ff.lib.ff_group_world(None) == 0 and ff.lib.ff_group_rank(None, 0) == -1
+    ff.lib.ff_group_destroy(None)
+
+
 def test_tile_owner_interleave():
     owners = {M.tile_owner(x, y, 4, 32, tiles_x=8) for x in range(0, 256, 32) for y in range(0, 64, 32)}
     assert owners == {0, 1, 2, 3}

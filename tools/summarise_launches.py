@@ -20,7 +20,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("csv")
     ap.add_argument("--tag", default="")
-    ap.add_argument("--command", default="ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -c 1200 --csv python bench.py --steps 2 --warmup 1")
+    ap.add_argument("--command", default="ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -c 1500 --csv python bench.py --steps 2 --warmup 1 --skip c2,c3,c5,cpu")
     a = ap.parse_args()
     rows = []
     with open(a.csv) as f:
@@ -56,20 +56,36 @@ def main():
     for t in table[:12]:
         print("%-40s n=%5d  %8.3f ms  %5.1f %%  %9.1f us/launch  DRAM %.1f MB/launch" % (t["kernel"][:40], t["launches"], t["total_ms"], 100 * t["share"],
                                                                                      t["mean_us"], (t["dram_read_per_launch"] + t["dram_write_per_launch"]) / 1e6))
-    tr = [t for t in table if "trace_closest_persistent_kernel" in t["kernel"]]
-    if tr:
-        t = tr[0]
-        traffic = dict(trace_closest_bytes_per_launch=t["dram_read_per_launch"] + t["dram_write_per_launch"],
-                       dram_read_bytes_per_launch=t["dram_read_per_launch"], dram_write_bytes_per_launch=t["dram_write_per_launch"],
-                       kernel="trace_closest_persistent_kernel", launches_averaged=t["launches"], mean_launch_ns_under_ncu=t["mean_us"] * 1e3,
-                       share_of_captured_time=t["share"], command=a.command, source=os.path.relpath(a.csv, ROOT),
-                       note="DRAM traffic of the extend stage is the ray batch in and the hit records out (48 B per ray of the launch); "
-                            "the scene stays in L2/L1, so DRAM bytes are a few per cent of the algorithmic traversal bytes.")
+    # The headline kernel: the persistent closest-hit launches over the WHOLE batch (bench.py's timed C4 steps).  The same kernel
+    # also runs on the 1 Mi-ray chunks of the host-batch pipeline (e2e) and on batch B; those are told apart by their duration.
+    per_launch = defaultdict(lambda: defaultdict(float))
+    for r in rows:
+        if "trace_closest_persistent_kernel" not in r["Kernel Name"]:
+            continue
+        v = float(r["Metric Value"].replace(",", ""))
+        m, unit = r["Metric Name"], r["Metric Unit"]
+        if m == "gpu__time_duration.sum":
+            v *= {"ns": 1.0, "us": 1e3, "usecond": 1e3, "ms": 1e6, "msecond": 1e6, "nsecond": 1.0, "second": 1e9}.get(unit, 1.0)
+        else:
+            v *= {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(unit, 1.0)
+        per_launch[r["ID"]][m] = v
+    if per_launch:
+        longest = max(p["gpu__time_duration.sum"] for p in per_launch.values())
+        full = [p for p in per_launch.values() if p["gpu__time_duration.sum"] >= 0.7 * longest]
+        n = len(full)
+        rd = sum(p["dram__bytes_read.sum"] for p in full) / n
+        wr = sum(p["dram__bytes_write.sum"] for p in full) / n
+        ns = sum(p["gpu__time_duration.sum"] for p in full) / n
+        all_ns = sum(p["gpu__time_duration.sum"] for p in per_launch.values())
+        traffic = dict(c4_trace_closest_dram_bytes_per_launch=rd + wr, dram_read_bytes_per_launch=rd, dram_write_bytes_per_launch=wr,
+                       kernel="trace_closest_persistent_kernel<false>, launches over the whole 8 294 400-ray batch A of C4", launches_averaged=n,
+                       mean_launch_ns_under_ncu=ns, share_of_captured_time_all_launches_of_this_kernel=all_ns / total_ns, command=a.command,
+                       source=os.path.relpath(a.csv, ROOT),
+                       c4_trace_closest_limiter="L1/TEX wavefronts and instruction issue: the 62 MB scene (14 MB nodes + 48 MB triangles) is L2-resident, "
+                                                "DRAM carries the rays in, the hits out and the part of the scene a launch pulls in after the L2 flush",
+                       note="ncu times are cold-cache and serialised; bench.py times the same launch with CUDA events")
         json.dump(traffic, open(os.path.join(ROOT, "profiles", "traffic.json"), "w"), indent=1)
-        try:
-            print("wrote profiles/traffic.json:", round(traffic["trace_closest_bytes_per_launch"] / 1e6, 1), "MB per launch, share", round(t["share"], 3))
-        except BrokenPipeError:
-            pass
+        print("wrote profiles/traffic.json: %.1f MB per full-batch launch (%d launches, %.2f ms each under ncu)" % ((rd + wr) / 1e6, n, ns / 1e6))
 
 
 if __name__ == "__main__":

@@ -564,10 +564,11 @@ def run_gpu_multi(args):
         solo.render(sc, cam, 2, C5_BOUNCES, to_host=False)
         ctx.synchronize()
         ctx.timer_begin()
-        ref_img, st1 = solo.render(sc, cam, C5_SPP, C5_BOUNCES, to_host=True)
+        _, st1 = solo.render(sc, cam, C5_SPP, C5_BOUNCES, to_host=False)   # like the timed steps: the frame stays on the device
         t1 = 1e-3 * ctx.timer_end()
         base = dict(n_gpus=1, frame_ms=1e3 * t1, value=st1["rays"] / t1 / 1e6, unit=UNIT, msamples_s=C5_SPP * npix / t1 / 1e6,
-                    note="the same frame (all %d spp) rendered by rank 0 alone in this job, host framebuffer out" % C5_SPP)
+                    note="the same frame (all %d spp) rendered by rank 0 alone in this job, frame left on the device like the timed steps" % C5_SPP)
+        ref_img, _ = solo.render(sc, cam, C5_SPP, C5_BOUNCES, to_host=True)   # untimed: the one-GPU frame for the parity figure
         parity = dict(parity_vs_1gpu_max_abs=float(np.abs(img[..., :3] - ref_img[..., :3]).max()), frame_max=float(ref_img[..., :3].max()),
                       note="sample-split sums re-associate the per-pixel fp32 sum; tolerance 1e-5 x max(1, frame max)")
     barrier()

@@ -103,7 +103,7 @@ void ff_context_destroy(ff_context* ctx) {
         for (int k = 0; k < FF_PIPE_SLOTS; ++k) { cudaFree(tp.block[k]); cudaEventDestroy(tp.in_done[k]); cudaEventDestroy(tp.comp_done[k]); cudaEventDestroy(tp.out_done[k]); }
         for (int k = 0; k < 5; ++k) cudaEventDestroy(tp.span[k]);
         cudaFree(tp.work);
-        cudaStreamDestroy(tp.s_in); cudaStreamDestroy(tp.s_out);
+        cudaStreamDestroy(tp.s_in); cudaStreamDestroy(tp.s_out); cudaStreamDestroy(tp.s_comp);
     }
     ctx->arena.release();
     cudaStreamDestroy(ctx->stream);
@@ -664,6 +664,7 @@ static int ensure_pipe(ff_context* c, size_t chunk) {
     if (!tp.ready) {
         FF_CUDA(cudaStreamCreateWithFlags(&tp.s_in, cudaStreamNonBlocking));
         FF_CUDA(cudaStreamCreateWithFlags(&tp.s_out, cudaStreamNonBlocking));
+        FF_CUDA(cudaStreamCreateWithFlags(&tp.s_comp, cudaStreamNonBlocking));
         for (int k = 0; k < FF_PIPE_SLOTS; ++k) {
             FF_CUDA(cudaEventCreateWithFlags(&tp.in_done[k], cudaEventDisableTiming));
             FF_CUDA(cudaEventCreateWithFlags(&tp.comp_done[k], cudaEventDisableTiming));
@@ -709,7 +710,13 @@ int ff_trace_closest_uv(ff_scene* scene, const float* rays6, size_t n, int mode,
     FF_CUDA(cudaEventRecord(tp.span[0], st));
     FF_CUDA(cudaStreamWaitEvent(tp.s_in, tp.span[0], 0));
     FF_CUDA(cudaStreamWaitEvent(tp.s_out, tp.span[0], 0));
+    FF_CUDA(cudaStreamWaitEvent(tp.s_comp, tp.span[0], 0));
     for (size_t k = 0; k < n_chunks; ++k) {
+        // Chunks alternate between two compute streams: a persistent trace launch ends in a tail where a few warps finish
+        // their last rays on an otherwise idle machine; with the next chunk's launch already queued on the other stream its
+        // CTAs move in as the tail's retire, instead of waiting for the whole launch (a chunked batch cost 28 % more traversal
+        // time than one launch when the chunks were serialised on one stream, profiles/r02a_bench.json).
+        cudaStream_t cs = (k & 1) ? tp.s_comp : st;
         const int slot = (int)(k % FF_PIPE_SLOTS);
         const size_t first = k * chunk, m = std::min(chunk, n - first);
         char* b = tp.block[slot];
@@ -726,16 +733,16 @@ int ff_trace_closest_uv(ff_scene* scene, const float* rays6, size_t n, int mode,
         FF_CUDA(cudaEventRecord(tp.in_done[slot], tp.s_in));
         if (k + 1 == n_chunks) FF_CUDA(cudaEventRecord(tp.span[1], tp.s_in));
         // pack + trace + unpack (the slot's previous outputs must have left the device)
-        FF_CUDA(cudaStreamWaitEvent(st, tp.in_done[slot], 0));
-        if (k >= FF_PIPE_SLOTS) FF_CUDA(cudaStreamWaitEvent(st, tp.out_done[slot], 0));
-        k_pack_rays(d6, m, dr, dr + m, st);
-        FF_CUDA(cudaMemsetAsync(tp.work + slot, 0, sizeof(uint32_t), st));
-        FF_CUDA(cudaEventRecord(c->trace_events[2 * k], st));
-        k_trace_closest(scene->dev, dr, dr + m, nullptr, (uint32_t)m, mode, dh, scene->d_trace_counters, tp.work + slot, st);
-        FF_CUDA(cudaEventRecord(c->trace_events[2 * k + 1], st));
-        k_unpack_hits(scene->dev, dh, m, dg, dt, dk, st);
-        if (want_uv) k_hit_barycentrics(scene->dev, dr, dr + m, dh, m, duv, duv + m, st);
-        FF_CUDA(cudaEventRecord(tp.comp_done[slot], st));
+        FF_CUDA(cudaStreamWaitEvent(cs, tp.in_done[slot], 0));
+        if (k >= FF_PIPE_SLOTS) FF_CUDA(cudaStreamWaitEvent(cs, tp.out_done[slot], 0));
+        k_pack_rays(d6, m, dr, dr + m, cs);
+        FF_CUDA(cudaMemsetAsync(tp.work + slot, 0, sizeof(uint32_t), cs));
+        FF_CUDA(cudaEventRecord(c->trace_events[2 * k], cs));
+        k_trace_closest(scene->dev, dr, dr + m, nullptr, (uint32_t)m, mode, dh, scene->d_trace_counters, tp.work + slot, cs);
+        FF_CUDA(cudaEventRecord(c->trace_events[2 * k + 1], cs));
+        k_unpack_hits(scene->dev, dh, m, dg, dt, dk, cs);
+        if (want_uv) k_hit_barycentrics(scene->dev, dr, dr + m, dh, m, duv, duv + m, cs);
+        FF_CUDA(cudaEventRecord(tp.comp_done[slot], cs));
         // copy out
         FF_CUDA(cudaStreamWaitEvent(tp.s_out, tp.comp_done[slot], 0));
         if (k == 0) FF_CUDA(cudaEventRecord(tp.span[2], tp.s_out));
@@ -756,9 +763,10 @@ int ff_trace_closest_uv(ff_scene* scene, const float* rays6, size_t n, int mode,
         cudaEventElapsedTime(&ms, tp.span[0], tp.span[4]); stats->gpu_ms = ms;
         cudaEventElapsedTime(&ms, tp.span[0], tp.span[1]); stats->h2d_ms = ms;   // span of the copy-in stream's activity
         cudaEventElapsedTime(&ms, tp.span[2], tp.span[3]); stats->d2h_ms = ms;   // span of the copy-out stream's activity
-        double tr = 0;
-        for (size_t k = 0; k < n_chunks; ++k) { cudaEventElapsedTime(&ms, c->trace_events[2 * k], c->trace_events[2 * k + 1]); tr += ms; }
-        stats->trace_ms = tr; stats->rays = n; stats->passes = (uint32_t)n_chunks;
+        // chunks overlap on the two compute streams: the traversal time is the span from the first launch to the end of the last
+        cudaEventElapsedTime(&ms, c->trace_events[0], c->trace_events[2 * (n_chunks - 1) + 1]);
+        if (n_chunks > 1) { float m2 = 0; cudaEventElapsedTime(&m2, c->trace_events[0], c->trace_events[2 * (n_chunks - 2) + 1]); ms = std::max(ms, m2); }
+        stats->trace_ms = ms; stats->rays = n; stats->passes = (uint32_t)n_chunks;
         stats->kernel_launches = (uint32_t)(n_chunks * (want_uv ? 4 : 3));
         if (count) {
             TraceCounters h;
@@ -880,7 +888,7 @@ int ensure_wave(ff_scene* s, size_t capacity, int n_counts, bool want_shadow) {
             FF_CUDA(cudaMalloc((void**)&s->wb.ray_d[k], sizeof(float4) * capacity));
             FF_CUDA(cudaMalloc((void**)&s->wb.beta[k], sizeof(float4) * capacity));
         }
-        FF_CUDA(cudaMalloc((void**)&s->wb.hits, sizeof(HitRec) * capacity));
+        FF_CUDA(cudaMalloc((void**)&s->wb.hits, sizeof(HitLite) * capacity));
         FF_CUDA(cudaMalloc((void**)&s->wb.radiance, sizeof(float4) * capacity));
         s->wb_capacity = capacity;
         s->wb.capacity = (uint32_t)capacity;

@@ -35,7 +35,7 @@ struct TracePipe {
     size_t chunk = 0;   // rays per slot
     char* block[FF_PIPE_SLOTS] = {nullptr, nullptr, nullptr};
     uint32_t* work = nullptr;  // one work counter per slot
-    cudaStream_t s_in = nullptr, s_out = nullptr;
+    cudaStream_t s_in = nullptr, s_out = nullptr, s_comp = nullptr;  // copy-in, copy-out, second compute stream
     cudaEvent_t in_done[FF_PIPE_SLOTS], comp_done[FF_PIPE_SLOTS], out_done[FF_PIPE_SLOTS], span[5];
     bool ready = false;
 };

@@ -125,6 +125,13 @@ struct RenderDev {
 
 struct TraceCounters { unsigned long long nodes, tris; };
 
+// What the wavefront's extend stage leaves for its shade stage: 8 bytes instead of the 16-byte API record (the closest-hit
+// key and the scan-order id matter to callers of ff_trace_closest*, not to shading).
+struct HitLite { float t; int slot; };
+// Bounce 0 of a wavefront pass: the extend stage generates the camera ray of path p = (sample, pixel) itself instead of
+// reading 32 bytes a ray-generation kernel would have had to write (and the shade stage re-derives it the same way).
+struct WaveGen { CamDev cam; RenderDev rp; };
+
 // ---------------------------------------------------------------- kernel launch wrappers
 // (implemented in the .cu files; all asynchronous on `st`)
 void k_bake_triangles(const float* d_xyz9_obj, const ffm::M4* d_model_per_geom, const uint32_t* d_geom_of_flat,
@@ -173,6 +180,10 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
 
 void k_trace_closest(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const uint32_t* d_count,
                      uint32_t n_max, int mode, HitRec* d_hits, TraceCounters* d_counters, uint32_t* d_work_counter, cudaStream_t st);
+// Extend stage of the wavefront: as k_trace_closest, with 8-byte hit records, rays optionally generated from the path id
+// (gen != nullptr: bounce 0; d_ray_o / d_ray_d are not read) and the self-skip slot read from ray_d.w (FF_TRACE_SELFSKIP).
+void k_trace_extend(const DevScene& sc, const WaveGen* gen, const float4* d_ray_o, const float4* d_ray_d, const uint32_t* d_count,
+                    uint32_t n_max, int mode, HitLite* d_hits, TraceCounters* d_counters, uint32_t* d_work_counter, cudaStream_t st);
 void k_trace_any(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const float* d_tmax, uint32_t n, int mode,
                  unsigned char* d_occluded, uint32_t* d_work_counter, cudaStream_t st);
 // Shadow stage of the wavefront: queue entries {o.xyz, path id}, {d.xyz, tmax}, {contribution.rgb}; unoccluded entries
@@ -196,7 +207,7 @@ struct WaveBuffers {
     float4* ray_o[2];      // {o.xyz, path id}
     float4* ray_d[2];      // {d.xyz, 0}
     float4* beta[2];       // {throughput.rgb, 0}
-    HitRec* hits;
+    HitLite* hits;
     float4* radiance;      // per path of the pass: L.rgb, indexed by path id = sample_in_pass * npix + pixel
     float4* sh_o;          // shadow queue (next-event estimation): {origin.xyz, path id}
     float4* sh_d;          //   {unnormalised direction.xyz, tmax}

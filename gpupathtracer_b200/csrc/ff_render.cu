@@ -19,28 +19,6 @@ static inline int grid_for(size_t n, int block, int max_blocks) {
     return (int)g;
 }
 
-__device__ __forceinline__ void camera_ray_dev(const CamDev& cam, float px, float py, V3& o, V3& d) {
-    o = v3(cam.pos[0], cam.pos[1], cam.pos[2]);
-    const float Px = fsub(fmul(fdiv(px, cam.width), 2.f), 1.f);
-    const float Py = fsub(1.f, fmul(fdiv(py, cam.height), 2.f));
-    const V4 look = mul_mv(cam.inv_vp, fmul(Px, cam.far_clip), fmul(Py, cam.far_clip), fmul(1.f, cam.far_clip),
-                           fmul(1.f, cam.far_clip));
-    d = normalize(sub(v3(look.x, look.y, look.z), o));
-}
-// primary ray of path (pixel, sample): integer pixel corner (kernel.cu:200-201) or Philox-jittered
-// Pixel of the frame behind ordinal q of this call's pixels (identity unless the call renders a tile split).
-__device__ __forceinline__ uint32_t frame_pixel(const RenderDev& rp, uint32_t q) { return rp.pixel_map ? __ldg(rp.pixel_map + q) : q; }
-
-__device__ __forceinline__ void primary_ray(const CamDev& cam, const RenderDev& rp, uint32_t pixel, uint32_t sample, V3& o, V3& d) {
-    float px = (float)(pixel % (uint32_t)cam.w), py = (float)(pixel / (uint32_t)cam.w);
-    if (rp.aa) {
-        const U4 j = philox4x32_10(U4{pixel, sample, 0u, 1u}, rp.seed_lo, rp.seed_hi);
-        px = fadd(px, u01(j.z));
-        py = fadd(py, u01(j.w));
-    }
-    camera_ray_dev(cam, px, py, o, d);
-}
-
 // Surface data of a hit: world point, geometric normal as the reference returns it, geometry index.
 __device__ __forceinline__ void hit_surface(const DevScene& sc, const HitRec& h, V3 o, V3 d_raw, V3& point, V3& normal, int& geom) {
     if (h.slot & 0x40000000) {
@@ -255,21 +233,17 @@ __device__ __forceinline__ bool shade_event(const DevScene& sc, const RenderDev&
 }
 
 // ------------------------------------------------------------------ wavefront stages
-__global__ void wf_raygen_kernel(CamDev cam, RenderDev rp, float4* __restrict__ ray_o, float4* __restrict__ ray_d,
-                                 float4* __restrict__ beta, float4* __restrict__ radiance, uint32_t* __restrict__ counts, int n_counts) {
+// Start of a pass: the queue counters, and (next-event estimation only) radiance[p] = 0 for the shadow stages to add to.
+// There is no ray-generation kernel any more: bounce 0's extend stage makes the camera ray of path p from p itself
+// (FetchCamera in ff_trace.cu) and the shade stage of bounce 0 repeats the same arithmetic, so the 64 B per path that
+// wf_raygen_kernel wrote -- and the 32 B that each of the two stages read back -- are gone (C2: 4.2 GB + 4.2 GB per frame).
+__global__ void wf_reset_kernel(RenderDev rp, float4* __restrict__ radiance, uint32_t* __restrict__ counts, int n_counts) {
     const uint32_t n = rp.samples * rp.npix;
     if (blockIdx.x == 0)  // paths per bounce | extend work counters | shadow rays per bounce | shadow work counters
         for (int k = threadIdx.x; k < 4 * n_counts; k += blockDim.x) counts[k] = k == 0 ? n : 0u;
-    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
-        const uint32_t s = p / rp.npix, pixel = frame_pixel(rp, p - s * rp.npix);
-        V3 o, d;
-        primary_ray(cam, rp, pixel, rp.first_sample + s, o, d);
-        ray_o[p] = make_float4(o.x, o.y, o.z, __uint_as_float(p));
-        ray_d[p] = make_float4(d.x, d.y, d.z, 0.f);
-        // beta is 1 on the camera segment: the shade stage of bounce 0 knows that and does not read it.  radiance[p] is written
-        // exactly once, when the path ends -- only the shadow stage of next-event estimation adds to it before that.
-        if (rp.nee) radiance[p] = make_float4(0.f, 0.f, 0.f, 0.f);
-    }
+    // radiance[p] is written exactly once, when the path ends -- only the shadow stage of next-event estimation adds to it before that
+    if (rp.nee)
+        for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) radiance[p] = make_float4(0.f, 0.f, 0.f, 0.f);
 }
 
 // shade + BSDF sampling + queue compaction: survivors are appended to the next bounce's queue (ballot + popc inside a
@@ -282,9 +256,9 @@ __global__ void wf_raygen_kernel(CamDev cam, RenderDev rp, float4* __restrict__ 
 #define FF_SHADE_PREFETCH 1  // +0.5 .. 1 %
 #endif
 static_assert(FF_SHADE_BLOCK >= 64 && FF_SHADE_BLOCK <= 512 && (FF_SHADE_BLOCK & (FF_SHADE_BLOCK - 1)) == 0, "two warp groups of warp 0 scan the CTA's warps");
-template <bool NEE>
-__global__ void __launch_bounds__(FF_SHADE_BLOCK) wf_shade_kernel(DevScene sc, RenderDev rp, int bounce, const uint32_t* __restrict__ count_in,
-                                                        uint32_t cap, const HitRec* __restrict__ hits,
+template <bool NEE, bool FIRST>
+__global__ void __launch_bounds__(FF_SHADE_BLOCK) wf_shade_kernel(DevScene sc, CamDev cam, RenderDev rp, int bounce, const uint32_t* __restrict__ count_in,
+                                                        uint32_t cap, const HitLite* __restrict__ hits,
                                                         const float4* __restrict__ ray_o_in, const float4* __restrict__ ray_d_in,
                                                         const float4* __restrict__ beta_in, float4* __restrict__ ray_o_out,
                                                         float4* __restrict__ ray_d_out, float4* __restrict__ beta_out,
@@ -316,20 +290,32 @@ __global__ void __launch_bounds__(FF_SHADE_BLOCK) wf_shade_kernel(DevScene sc, R
 #else
 #define FF_PF "prefetch.global.L2 [%0];"
 #endif
-                asm volatile(FF_PF ::"l"(ray_o_in + k2));
-                asm volatile(FF_PF ::"l"(ray_d_in + k2));
-                if (bounce != 0) asm volatile(FF_PF ::"l"(beta_in + k2));
-                asm volatile(FF_PF ::"l"(hits + k2));
+                if (!FIRST) {
+                    asm volatile(FF_PF ::"l"(ray_o_in + k2));
+                    asm volatile(FF_PF ::"l"(ray_d_in + k2));
+                    asm volatile(FF_PF ::"l"(beta_in + k2));
+                }
+                if ((lane & 15) == 0) asm volatile(FF_PF ::"l"(hits + k2));
             }
         }
 #endif
         if (k < n) {
-            const float4 o4 = ray_o_in[k], d4 = ray_d_in[k], b4 = bounce == 0 ? make_float4(1.f, 1.f, 1.f, 0.f) : beta_in[k];
-            const HitRec h = hits[k];
-            path = __float_as_uint(o4.w);
-            const uint32_t s = path / rp.npix, pixel = frame_pixel(rp, path - s * rp.npix);
-            o = ld3(o4); d = ld3(d4); beta = ld3(b4);
-            specular = b4.w != 0.0f;
+            const HitLite hl = hits[k];
+            HitRec h;
+            h.key = 0.f; h.t = hl.t; h.slot = hl.slot; h.ord = 0;   // shading reads t and slot only
+            uint32_t s, pixel;
+            if (FIRST) {   // camera segment: path k is (sample, pixel) = (k / npix, k % npix); its ray is re-derived, beta = 1
+                path = k;
+                s = path / rp.npix; pixel = frame_pixel(rp, path - s * rp.npix);
+                primary_ray(cam, rp, pixel, rp.first_sample + s, o, d);
+                beta = v3(1.f, 1.f, 1.f);
+            } else {
+                const float4 o4 = ray_o_in[k], d4 = ray_d_in[k], b4 = beta_in[k];
+                path = __float_as_uint(o4.w);
+                s = path / rp.npix; pixel = frame_pixel(rp, path - s * rp.npix);
+                o = ld3(o4); d = ld3(d4); beta = ld3(b4);
+                specular = b4.w != 0.0f;
+            }
             V3 L = v3(0.f, 0.f, 0.f);
             alive = shade_event<NEE>(sc, rp, h, pixel, rp.first_sample + s, bounce, o, d, beta, L, specular, sr);
             if (alive && self_skip_safe(sc, rp, h.slot)) from = (uint32_t)h.slot + 1u;
@@ -385,22 +371,27 @@ void k_wavefront_pass(const DevScene& sc, const CamDev& cam, const RenderDev& rp
                       cudaStream_t st) {
     const uint32_t n = rp.samples * rp.npix;
     const int n_counts = rp.max_bounces + 2;
-    wf_raygen_kernel<<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(cam, rp, wb.ray_o[0], wb.ray_d[0], wb.beta[0], wb.radiance, wb.counts, n_counts);
+    wf_reset_kernel<<<rp.nee ? grid_for(n, 256, sm_count() * 16) : 1, 256, 0, st>>>(rp, wb.radiance, wb.counts, n_counts);
     ++*launches;
+    const WaveGen gen = {cam, rp};
+    const bool nee = rp.nee && sc.n_lights != 0;
+    const int shade_grid = grid_for(n, FF_SHADE_BLOCK, sm_count() * 16 * 256 / FF_SHADE_BLOCK);
     for (int b = 0; b <= rp.max_bounces; ++b) {
         const int in = b & 1, out = in ^ 1;
         if (trace_events) cudaEventRecord(trace_events[(*n_trace_events)++], st);
-        k_trace_closest(sc, wb.ray_o[in], wb.ray_d[in], wb.counts + b, n, trace_mode | ((FF_SELF_SKIP && rp.ray_eps > 0.125f * sc.pad) ? FF_TRACE_SELFSKIP : 0), wb.hits, d_counters, wb.counts + n_counts + b, st);
+        k_trace_extend(sc, b == 0 ? &gen : nullptr, wb.ray_o[in], wb.ray_d[in], wb.counts + b, n,
+                       trace_mode | ((FF_SELF_SKIP && rp.ray_eps > 0.125f * sc.pad) ? FF_TRACE_SELFSKIP : 0), wb.hits, d_counters, wb.counts + n_counts + b, st);
         if (trace_events) cudaEventRecord(trace_events[(*n_trace_events)++], st);
-        const bool nee = rp.nee && sc.n_lights != 0;
-        if (nee) wf_shade_kernel<true><<<grid_for(n, FF_SHADE_BLOCK, sm_count() * 16 * 256 / FF_SHADE_BLOCK), FF_SHADE_BLOCK, 0, st>>>(sc, rp, b, wb.counts + b, n, wb.hits, wb.ray_o[in], wb.ray_d[in],
-                                                                   wb.beta[in], wb.ray_o[out], wb.ray_d[out], wb.beta[out],
-                                                                   wb.radiance, wb.counts + b + 1, wb.sh_o, wb.sh_d, wb.sh_c,
-                                                                   wb.counts + 2 * n_counts + b);
-        else wf_shade_kernel<false><<<grid_for(n, FF_SHADE_BLOCK, sm_count() * 16 * 256 / FF_SHADE_BLOCK), FF_SHADE_BLOCK, 0, st>>>(sc, rp, b, wb.counts + b, n, wb.hits, wb.ray_o[in], wb.ray_d[in],
-                                                                   wb.beta[in], wb.ray_o[out], wb.ray_d[out], wb.beta[out],
-                                                                   wb.radiance, wb.counts + b + 1, wb.sh_o, wb.sh_d, wb.sh_c,
-                                                                   wb.counts + 2 * n_counts + b);
+#define FF_SHADE_ARGS sc, cam, rp, b, wb.counts + b, n, wb.hits, wb.ray_o[in], wb.ray_d[in], wb.beta[in], wb.ray_o[out], wb.ray_d[out], wb.beta[out], \
+                      wb.radiance, wb.counts + b + 1, wb.sh_o, wb.sh_d, wb.sh_c, wb.counts + 2 * n_counts + b
+        if (nee) {
+            if (b == 0) wf_shade_kernel<true, true><<<shade_grid, FF_SHADE_BLOCK, 0, st>>>(FF_SHADE_ARGS);
+            else wf_shade_kernel<true, false><<<shade_grid, FF_SHADE_BLOCK, 0, st>>>(FF_SHADE_ARGS);
+        } else {
+            if (b == 0) wf_shade_kernel<false, true><<<shade_grid, FF_SHADE_BLOCK, 0, st>>>(FF_SHADE_ARGS);
+            else wf_shade_kernel<false, false><<<shade_grid, FF_SHADE_BLOCK, 0, st>>>(FF_SHADE_ARGS);
+        }
+#undef FF_SHADE_ARGS
         *launches += 2;
         if (nee && b < rp.max_bounces) {  // shadow stage: any-hit over this bounce's light samples
             if (trace_events) cudaEventRecord(trace_events[(*n_trace_events)++], st);

@@ -38,25 +38,56 @@ __device__ __forceinline__ void store_hit(HitRec* hits, size_t i, const Best& b)
     reinterpret_cast<int4*>(hits)[i] = v;
 }
 
+// Where a closest-hit kernel takes its rays from and what it leaves behind.  The API entry points read ray arrays and write
+// the 16-byte record; the wavefront's extend stage writes 8-byte records and, on bounce 0, makes the camera ray of path i
+// itself (primary_ray: the same arithmetic the shade stage repeats), so no ray-generation kernel has to write 32 bytes per
+// path for this one to read back.  `skipbits` = slot + 1 of the triangle the ray starts on (0: none), see make_ray_ctx.
+struct FetchArrays {
+    const float4* __restrict__ ray_o;
+    const float4* __restrict__ ray_d;
+    __device__ __forceinline__ void operator()(uint32_t i, V3& o, V3& draw, uint32_t& skipbits) const {
+        const float4 d4 = __ldg(ray_d + i);
+        o = ld3(__ldg(ray_o + i)); draw = ld3(d4); skipbits = __float_as_uint(d4.w);
+    }
+};
+struct FetchCamera {
+    CamDev cam;
+    RenderDev rp;
+    __device__ __forceinline__ void operator()(uint32_t i, V3& o, V3& draw, uint32_t& skipbits) const {
+        const uint32_t s = i / rp.npix, pixel = frame_pixel(rp, i - s * rp.npix);
+        primary_ray(cam, rp, pixel, rp.first_sample + s, o, draw);
+        skipbits = 0u;
+    }
+};
+struct StoreRec {
+    HitRec* __restrict__ hits;
+    __device__ __forceinline__ void operator()(size_t i, const Best& b) const { store_hit(hits, i, b); }
+};
+struct StoreLite {
+    HitLite* __restrict__ hits;
+    __device__ __forceinline__ void operator()(size_t i, const Best& b) const {
+        reinterpret_cast<int2*>(hits)[i] = b.slot < 0 ? make_int2(0, -1) : make_int2(__float_as_int(b.t), b.slot);
+    }
+};
+
 // ------------------------------------------------------------------ closest hit, one thread per ray
-template <int MODE, bool COUNT, bool SKIP>
-__global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_closest_kernel(DevScene sc, const float4* __restrict__ ray_o,
-                                                                        const float4* __restrict__ ray_d,
-                                                                        const uint32_t* __restrict__ count_ptr, uint32_t n_max,
-                                                                        HitRec* __restrict__ hits, TraceCounters* ctr) {
+template <int MODE, bool COUNT, bool SKIP, class Fetch, class Store>
+__global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_closest_kernel(DevScene sc, Fetch fetch, Store store, const uint32_t* __restrict__ count_ptr,
+                                                                        uint32_t n_max, TraceCounters* ctr) {
     __shared__ uint2 sm_stack[(FF_SM_STACK + FF_TRI_QUEUE) * FF_TRACE_BLOCK];
     const uint32_t n = count_ptr ? min(*count_ptr, n_max) : n_max;
     unsigned cn = 0, ct = 0;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const float4 o4 = __ldg(ray_o + i), d4 = __ldg(ray_d + i);
-        const V3 o = ld3(o4), draw = ld3(d4);
+        V3 o, draw;
+        uint32_t skipbits;
+        fetch(i, o, draw, skipbits);
         const V3 dn = normalize(draw);  // kernel.cu:138
         Best best;
         best_init(best, INFINITY);
         test_planes<false>(sc, o, draw, best);
-        if (MODE == FF_TRACE_BVH8) trace_bvh8<false, COUNT, SKIP>(sc, o, dn, best, sm_stack + threadIdx.x, FF_TRACE_BLOCK, cn, ct, SKIP ? skip_from_bits(d4.w) : 0xffffffffu);
+        if (MODE == FF_TRACE_BVH8) trace_bvh8<false, COUNT, SKIP>(sc, o, dn, best, sm_stack + threadIdx.x, FF_TRACE_BLOCK, cn, ct, SKIP ? skipbits - 1u : 0xffffffffu);
         else trace_bvh2<false, COUNT>(sc, o, dn, best, cn, ct);
-        store_hit(hits, i, best);
+        store(i, best);
     }
     if (COUNT) {
         atomicAdd(&ctr->nodes, (unsigned long long)cn);
@@ -68,11 +99,10 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_closest_kernel(DevScene 
 // Warps pull rays from a global counter; when fewer than FF_REFILL_LANES lanes of a warp are still traversing, the
 // idle lanes fetch new rays instead of waiting for the slowest one (Aila & Laine 2009).  Results do not depend on
 // the schedule (the accept rule is order independent).
-template <bool SKIP>
-__global__ void __launch_bounds__(FF_TRACE_BLOCK, FF_TRACE_MINB) trace_closest_persistent_kernel(DevScene sc, const float4* __restrict__ ray_o,
-                                                                                   const float4* __restrict__ ray_d,
+template <bool SKIP, class Fetch, class Store>
+__global__ void __launch_bounds__(FF_TRACE_BLOCK, FF_TRACE_MINB) trace_closest_persistent_kernel(DevScene sc, Fetch fetch, Store store,
                                                                                    const uint32_t* __restrict__ count_ptr, uint32_t n_max,
-                                                                                   HitRec* __restrict__ hits, uint32_t* work_counter) {
+                                                                                   uint32_t* work_counter) {
     __shared__ uint2 sm_stack[(FF_SM_STACK + FF_TRI_QUEUE) * FF_TRACE_BLOCK];
     const uint32_t n = count_ptr ? min(*count_ptr, n_max) : n_max;
     const int lane = threadIdx.x & 31;
@@ -95,16 +125,17 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK, FF_TRACE_MINB) trace_closest_p
             if (!has) {
                 const uint32_t i = base + __popc(need & ((1u << lane) - 1u));
                 if (i < n) {
-                    const float4 d4 = __ldg(ray_d + i);
-                    const V3 o = ld3(__ldg(ray_o + i)), draw = ld3(d4);
+                    V3 o, draw;
+                    uint32_t skipbits;
+                    fetch(i, o, draw, skipbits);
                     const V3 dn = normalize(draw);  // kernel.cu:138
                     best_init(best, INFINITY);
                     test_planes<false>(sc, o, draw, best);
-                    r = make_ray_ctx(o, dn, SKIP ? skip_from_bits(d4.w) : 0xffffffffu);
+                    r = make_ray_ctx(o, dn, SKIP ? skipbits - 1u : 0xffffffffu);
                     tv.start(best.key);
                     ray_index = i;
                     has = sc.n_nodes != 0;
-                    if (!has) store_hit(hits, i, best);
+                    if (!has) store(i, best);
                 }
             }
         }
@@ -119,7 +150,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK, FF_TRACE_MINB) trace_closest_p
             bool do_tri = (__popc(tb) >= FF_TRI_MIN) || nb == 0u;
             if (!do_node && !do_tri) do_node = do_tri = true;
             if (has && !bvh8_step<false, false, SKIP>(sc, r, tv, best, my_stack, FF_TRACE_BLOCK, lstack, cn, ct, do_node, do_tri)) {
-                store_hit(hits, ray_index, best);
+                store(ray_index, best);
                 has = false;
             }
             const unsigned hb = __ballot_sync(0xffffffffu, has);
@@ -129,7 +160,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK, FF_TRACE_MINB) trace_closest_p
         if (has) {
             for (;;) {
                 if (!bvh8_step<false, false, SKIP>(sc, r, tv, best, my_stack, FF_TRACE_BLOCK, lstack, cn, ct)) {
-                    store_hit(hits, ray_index, best);
+                    store(ray_index, best);
                     has = false;
                     break;
                 }
@@ -186,37 +217,48 @@ __global__ void __launch_bounds__(FF_BRUTE_TILE) trace_brute_kernel(DevScene sc,
     if (COUNT) atomicAdd(&ctr->tris, ct);
 }
 
-void k_trace_closest(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const uint32_t* d_count,
-                     uint32_t n_max, int mode, HitRec* d_hits, TraceCounters* d_counters, uint32_t* d_work_counter, cudaStream_t st) {
-    if (n_max == 0) return;
+template <class Fetch, class Store>
+static void launch_closest(const DevScene& sc, const Fetch& fetch, const Store& store, const uint32_t* d_count, uint32_t n_max, int mode,
+                           TraceCounters* d_counters, uint32_t* d_work_counter, cudaStream_t st) {
     const bool count = (mode & FF_TRACE_COUNT) != 0;
     const int m = mode & 0xff;
+    const bool skip = (mode & FF_TRACE_SELFSKIP) != 0;
     if (m == FF_TRACE_BVH8 && !count && d_work_counter && !(mode & FF_TRACE_STATIC)) {
         // persistent: enough warps to fill the machine, each pulling rays until the batch is drained.
         // *d_work_counter must be zero (the caller clears it on the same stream).
         const int g = grid_for(n_max, FF_TRACE_BLOCK, sm_count() * tuning().blocks_per_sm);
-        if (mode & FF_TRACE_SELFSKIP) trace_closest_persistent_kernel<true><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_work_counter);
-        else trace_closest_persistent_kernel<false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_work_counter);
-        return;
-    }
-    if (m == FF_TRACE_BRUTE) {
-        const int g = grid_for(n_max, FF_BRUTE_TILE, sm_count() * 8);
-        if (count) trace_brute_kernel<true><<<g, FF_BRUTE_TILE, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);
-        else trace_brute_kernel<false><<<g, FF_BRUTE_TILE, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);
+        if (skip) trace_closest_persistent_kernel<true><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, fetch, store, d_count, n_max, d_work_counter);
+        else trace_closest_persistent_kernel<false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, fetch, store, d_count, n_max, d_work_counter);
         return;
     }
     const int g = grid_for(n_max, FF_TRACE_BLOCK, sm_count() * 64);
-    const bool skip = (mode & FF_TRACE_SELFSKIP) != 0;
     if (m == FF_TRACE_BVH2) {
-        if (count) trace_closest_kernel<FF_TRACE_BVH2, true, false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);
-        else trace_closest_kernel<FF_TRACE_BVH2, false, false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);
+        if (count) trace_closest_kernel<FF_TRACE_BVH2, true, false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, fetch, store, d_count, n_max, d_counters);
+        else trace_closest_kernel<FF_TRACE_BVH2, false, false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, fetch, store, d_count, n_max, d_counters);
     } else if (skip) {
-        if (count) trace_closest_kernel<FF_TRACE_BVH8, true, true><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);
-        else trace_closest_kernel<FF_TRACE_BVH8, false, true><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);
+        if (count) trace_closest_kernel<FF_TRACE_BVH8, true, true><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, fetch, store, d_count, n_max, d_counters);
+        else trace_closest_kernel<FF_TRACE_BVH8, false, true><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, fetch, store, d_count, n_max, d_counters);
     } else {
-        if (count) trace_closest_kernel<FF_TRACE_BVH8, true, false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);
-        else trace_closest_kernel<FF_TRACE_BVH8, false, false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);
+        if (count) trace_closest_kernel<FF_TRACE_BVH8, true, false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, fetch, store, d_count, n_max, d_counters);
+        else trace_closest_kernel<FF_TRACE_BVH8, false, false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, fetch, store, d_count, n_max, d_counters);
     }
+}
+void k_trace_closest(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const uint32_t* d_count,
+                     uint32_t n_max, int mode, HitRec* d_hits, TraceCounters* d_counters, uint32_t* d_work_counter, cudaStream_t st) {
+    if (n_max == 0) return;
+    if ((mode & 0xff) == FF_TRACE_BRUTE) {
+        const int g = grid_for(n_max, FF_BRUTE_TILE, sm_count() * 8);
+        if (mode & FF_TRACE_COUNT) trace_brute_kernel<true><<<g, FF_BRUTE_TILE, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);
+        else trace_brute_kernel<false><<<g, FF_BRUTE_TILE, 0, st>>>(sc, d_ray_o, d_ray_d, d_count, n_max, d_hits, d_counters);
+        return;
+    }
+    launch_closest(sc, FetchArrays{d_ray_o, d_ray_d}, StoreRec{d_hits}, d_count, n_max, mode, d_counters, d_work_counter, st);
+}
+void k_trace_extend(const DevScene& sc, const WaveGen* gen, const float4* d_ray_o, const float4* d_ray_d, const uint32_t* d_count,
+                    uint32_t n_max, int mode, HitLite* d_hits, TraceCounters* d_counters, uint32_t* d_work_counter, cudaStream_t st) {
+    if (n_max == 0) return;
+    if (gen) launch_closest(sc, FetchCamera{gen->cam, gen->rp}, StoreLite{d_hits}, d_count, n_max, mode & ~FF_TRACE_SELFSKIP, d_counters, d_work_counter, st);
+    else launch_closest(sc, FetchArrays{d_ray_o, d_ray_d}, StoreLite{d_hits}, d_count, n_max, mode, d_counters, d_work_counter, st);
 }
 
 // ------------------------------------------------------------------ any hit (occlusion)

@@ -123,6 +123,33 @@ __device__ __forceinline__ void test_planes(const DevScene& sc, V3 o, V3 d_raw, 
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Camera rays (kernel.cu:198-205), shared by the ray-batch kernels, the integrators and the wavefront's extend stage.
+__device__ __forceinline__ void camera_ray_dev(const CamDev& cam, float px, float py, V3& o, V3& d) {
+    using namespace ffm;
+    o = v3(cam.pos[0], cam.pos[1], cam.pos[2]);
+    const float Px = fsub(fmul(fdiv(px, cam.width), 2.f), 1.f);
+    const float Py = fsub(1.f, fmul(fdiv(py, cam.height), 2.f));
+    const V4 look = mul_mv(cam.inv_vp, fmul(Px, cam.far_clip), fmul(Py, cam.far_clip), fmul(1.f, cam.far_clip),
+                           fmul(1.f, cam.far_clip));
+    d = normalize(sub(v3(look.x, look.y, look.z), o));
+}
+// primary ray of path (pixel, sample): integer pixel corner (kernel.cu:200-201) or Philox-jittered
+// Pixel of the frame behind ordinal q of this call's pixels (identity unless the call renders a tile split).
+__device__ __forceinline__ uint32_t frame_pixel(const RenderDev& rp, uint32_t q) { return rp.pixel_map ? __ldg(rp.pixel_map + q) : q; }
+
+__device__ __forceinline__ void primary_ray(const CamDev& cam, const RenderDev& rp, uint32_t pixel, uint32_t sample, V3& o, V3& d) {
+    using namespace ffm;
+    float px = (float)(pixel % (uint32_t)cam.w), py = (float)(pixel / (uint32_t)cam.w);
+    if (rp.aa) {
+        const U4 j = philox4x32_10(U4{pixel, sample, 0u, 1u}, rp.seed_lo, rp.seed_hi);
+        px = fadd(px, u01(j.z));
+        py = fadd(py, u01(j.w));
+    }
+    camera_ray_dev(cam, px, py, o, d);
+}
+
+
 // Reciprocal direction for the slab tests only (never for the leaf test): MUFU.RCP, 1 ulp.  The culling margins
 // (FF_SLACK, DevScene::pad) are seven orders of magnitude wider, and the IEEE divide cost ~25 instructions per ray at the
 // low lane occupancy of the refill path.

@@ -15,6 +15,7 @@
 #include <cooperative_groups.h>
 #include <cooperative_groups/reduce.h>
 #include <cooperative_groups/scan.h>
+#include <algorithm>
 #include <cfloat>
 #include <chrono>
 #include <cstdio>
@@ -111,6 +112,10 @@ __global__ void bounds_kernel(const float4* __restrict__ tris, uint32_t n, int* 
             clo[k] = fminf(clo[k], ce); chi[k] = fmaxf(chi[k], ce);
         }
     }
+    // warp shuffle -> shared memory -> warp 0: 12 atomics per CTA.  (One set per WARP was 375 k same-address atomics at 1 M
+    // triangles, which the L2 serialises: 80 of the build's 930 us, profiles/r02a_launches_bench_summary.json.)
+    __shared__ float s_red[12][8];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         for (int off = 16; off; off >>= 1) {
@@ -119,16 +124,21 @@ __global__ void bounds_kernel(const float4* __restrict__ tris, uint32_t n, int* 
             clo[k] = fminf(clo[k], __shfl_xor_sync(0xffffffffu, clo[k], off));
             chi[k] = fmaxf(chi[k], __shfl_xor_sync(0xffffffffu, chi[k], off));
         }
-        if ((threadIdx.x & 31) == 0) {
-            atomicMin(bounds + k, float_to_ordered(lo[k]));
-            atomicMax(bounds + 3 + k, float_to_ordered(hi[k]));
-            atomicMin(bounds + 6 + k, float_to_ordered(clo[k]));
-            atomicMax(bounds + 9 + k, float_to_ordered(chi[k]));
-        }
+        if (lane == 0) { s_red[k][warp] = lo[k]; s_red[3 + k][warp] = hi[k]; s_red[6 + k][warp] = clo[k]; s_red[9 + k][warp] = chi[k]; }
+    }
+    __syncthreads();
+    if (threadIdx.x < 12) {
+        const int q = threadIdx.x;
+        const bool is_max = ((q / 3) & 1) != 0;
+        float v = s_red[q][0];
+        for (int w = 1; w < (int)(blockDim.x >> 5); ++w) v = is_max ? fmaxf(v, s_red[q][w]) : fminf(v, s_red[q][w]);
+        if (is_max) atomicMax(bounds + q, float_to_ordered(v)); else atomicMin(bounds + q, float_to_ordered(v));
     }
 }
 
-// ------------------------------------------------------------------ Morton codes (30 bit, centroid in centroid bounds)
+// ------------------------------------------------------------------ Morton codes of the box centres inside the centroid bounds
+// 30 bits (10 per axis, u32) for small scenes, 63 bits (21 per axis, u64) above 2^20 triangles: on a 1024^3 grid a large or
+// clustered scene puts many triangles into one cell, and inside a cell the hierarchy can only fall back to the input order.
 __device__ __forceinline__ uint32_t expand10(uint32_t v) {
     v = (v * 0x00010001u) & 0xFF0000FFu;
     v = (v * 0x00000101u) & 0x0F00F00Fu;
@@ -136,88 +146,90 @@ __device__ __forceinline__ uint32_t expand10(uint32_t v) {
     v = (v * 0x00000005u) & 0x49249249u;
     return v;
 }
-__global__ void morton_kernel(const float4* __restrict__ tris, uint32_t n, const int* __restrict__ bounds, uint32_t* keys, uint32_t* vals) {
+__device__ __forceinline__ uint64_t expand21(uint32_t a) {
+    uint64_t x = a & 0x1fffffu;
+    x = (x | x << 32) & 0x1f00000000ffffull;
+    x = (x | x << 16) & 0x1f0000ff0000ffull;
+    x = (x | x << 8) & 0x100f00f00f00f00full;
+    x = (x | x << 4) & 0x10c30c30c30c30c3ull;
+    x = (x | x << 2) & 0x1249249249249249ull;
+    return x;
+}
+template <class KeyT> struct Morton;
+template <> struct Morton<uint32_t> {
+    static constexpr float CELLS = 1024.0f;
+    static constexpr uint32_t MAXQ = 1023u;
+    static __device__ __forceinline__ uint32_t code(uint32_t x, uint32_t y, uint32_t z) { return (expand10(x) << 2) | (expand10(y) << 1) | expand10(z); }
+};
+template <> struct Morton<uint64_t> {
+    static constexpr float CELLS = 2097152.0f;
+    static constexpr uint32_t MAXQ = 2097151u;
+    static __device__ __forceinline__ uint64_t code(uint32_t x, uint32_t y, uint32_t z) { return (expand21(x) << 2) | (expand21(y) << 1) | expand21(z); }
+};
+template <class KeyT>
+__global__ void morton_kernel(const float4* __restrict__ tris, uint32_t n, const int* __restrict__ bounds, KeyT* keys, uint32_t* vals) {
     float clo[3], inv[3];
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         clo[k] = ordered_to_float(bounds[6 + k]);
         const float ext = ordered_to_float(bounds[9 + k]) - clo[k];
-        inv[k] = ext > 0.f ? 1024.0f / ext : 0.f;
+        inv[k] = ext > 0.f ? Morton<KeyT>::CELLS / ext : 0.f;
     }
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const float4 a = tris[3 * (size_t)i], b = tris[3 * (size_t)i + 1], c = tris[3 * (size_t)i + 2];
         const float cx = 0.5f * (fminf(fminf(a.x, b.x), c.x) + fmaxf(fmaxf(a.x, b.x), c.x));
         const float cy = 0.5f * (fminf(fminf(a.y, b.y), c.y) + fmaxf(fmaxf(a.y, b.y), c.y));
         const float cz = 0.5f * (fminf(fminf(a.z, b.z), c.z) + fmaxf(fmaxf(a.z, b.z), c.z));
-        const uint32_t x = min(1023u, (uint32_t)max(0.f, (cx - clo[0]) * inv[0]));
-        const uint32_t y = min(1023u, (uint32_t)max(0.f, (cy - clo[1]) * inv[1]));
-        const uint32_t z = min(1023u, (uint32_t)max(0.f, (cz - clo[2]) * inv[2]));
-        keys[i] = (expand10(x) << 2) | (expand10(y) << 1) | expand10(z);
+        const uint32_t x = min(Morton<KeyT>::MAXQ, (uint32_t)max(0.f, (cx - clo[0]) * inv[0]));
+        const uint32_t y = min(Morton<KeyT>::MAXQ, (uint32_t)max(0.f, (cy - clo[1]) * inv[1]));
+        const uint32_t z = min(Morton<KeyT>::MAXQ, (uint32_t)max(0.f, (cz - clo[2]) * inv[2]));
+        keys[i] = Morton<KeyT>::code(x, y, z);
         vals[i] = i;
     }
 }
 
-// ------------------------------------------------------------------ LSD radix sort, 8-bit digits, key/value u32
-// Three kernels per pass: per-tile digit histogram -> exclusive scan over (digit, tile) -> stable scatter.
-#define RS_THREADS 256
-#define RS_ITEMS 16
-#define RS_TILE (RS_THREADS * RS_ITEMS)
-__global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const uint32_t* __restrict__ keys, uint32_t n, int shift, uint32_t n_tiles,
-                                                              uint32_t* __restrict__ hist /*[256][n_tiles]*/) {
-    __shared__ uint32_t h[256];
-    h[threadIdx.x] = 0;
+// ------------------------------------------------------------------ LSD radix sort, 8-bit digits, ONE sweep per pass
+// Keys are 32-bit (30-bit Morton codes, 4 passes) or 64-bit (63-bit codes, 8 passes); values are the 32-bit triangle indices.
+//   os_hist_kernel   one read of the keys: the digit histograms of ALL passes (shared-memory atomics), added to global counters
+//   os_scan_kernel   exclusive scan of each pass's 256 counters
+//   os_pass_kernel   one launch per pass: a CTA takes the next tile (4096 keys) from a counter, ranks its keys by digit
+//                    (match_any inside each warp, prefix over the warps), publishes the tile's 256 digit counts, obtains the
+//                    counts of all earlier tiles by decoupled look-back (Merrill & Garland 2016: a tile publishes its local
+//                    counts, then its inclusive prefix, one flagged 32-bit word per digit; a successor sums local counts
+//                    backwards until it meets an inclusive one), reorders keys and values through shared memory and writes
+//                    them in digit runs.  One read and one write of the pairs per pass; the three-kernel pass it replaces
+//                    (histogram, two scans, scatter) read the keys twice and ran at 1.07 TB/s.
+#define OS_THREADS 256
+#define OS_ITEMS 16
+#define OS_TILE (OS_THREADS * OS_ITEMS)
+#define OS_FLAG_LOCAL 0x40000000u
+#define OS_FLAG_PREFIX 0x80000000u
+#define OS_VALUE_MASK 0x3fffffffu
+template <class KeyT> struct KeyTraits;
+template <> struct KeyTraits<uint32_t> { static constexpr int PASSES = 4; };
+template <> struct KeyTraits<uint64_t> { static constexpr int PASSES = 8; };
+
+template <class KeyT>
+__global__ void __launch_bounds__(256) os_hist_kernel(const KeyT* __restrict__ keys, uint32_t n, uint32_t* __restrict__ ghist /*[PASSES][256]*/) {
+    constexpr int P = KeyTraits<KeyT>::PASSES;
+    __shared__ uint32_t h[P][256];
+    for (int k = threadIdx.x; k < P * 256; k += blockDim.x) (&h[0][0])[k] = 0u;
     __syncthreads();
-    const uint32_t base = blockIdx.x * RS_TILE;
-    for (int r = 0; r < RS_ITEMS; ++r) {
-        const uint32_t i = base + r * RS_THREADS + threadIdx.x;
-        if (i < n) atomicAdd(&h[(keys[i] >> shift) & 0xffu], 1u);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const KeyT k = keys[i];
+#pragma unroll
+        for (int p = 0; p < P; ++p) atomicAdd(&h[p][(uint32_t)(k >> (8 * p)) & 0xffu], 1u);
     }
     __syncthreads();
-    hist[(size_t)threadIdx.x * n_tiles + blockIdx.x] = h[threadIdx.x];
-}
-// Exclusive scan of the (digit, tile) counters in two steps: block d scans row d (the tiles of digit d) in place and
-// leaves the row total; rs_scan_totals_kernel scans the 256 totals; the scatter adds the two.  (One block over all
-// 256 * n_tiles counters was 0.4 ms per pass at 20 M keys: 1.6 of the sort's 3.5 ms.)
-__global__ void __launch_bounds__(1024) rs_scan_kernel(uint32_t* hist, uint32_t m, uint32_t* __restrict__ totals) {
-    uint32_t* data = hist + (size_t)blockIdx.x * m;
-    __shared__ uint32_t warp_sums[32];
-    __shared__ uint32_t carry;
-    if (threadIdx.x == 0) carry = 0;
-    __syncthreads();
-    const uint32_t per = 4;
-    for (uint32_t base = 0; base < m; base += 1024 * per) {
-        uint32_t v[per], sum = 0;
-        const uint32_t i0 = base + threadIdx.x * per;
-#pragma unroll
-        for (uint32_t k = 0; k < per; ++k) { v[k] = (i0 + k < m) ? data[i0 + k] : 0u; sum += v[k]; }
-        uint32_t incl = sum;
-        for (int off = 1; off < 32; off <<= 1) {
-            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, off);
-            if ((threadIdx.x & 31) >= off) incl += t;
-        }
-        if ((threadIdx.x & 31) == 31) warp_sums[threadIdx.x >> 5] = incl;
-        __syncthreads();
-        if (threadIdx.x < 32) {
-            uint32_t w = warp_sums[threadIdx.x], wi = w;
-            for (int off = 1; off < 32; off <<= 1) {
-                const uint32_t t = __shfl_up_sync(0xffffffffu, wi, off);
-                if (threadIdx.x >= off) wi += t;
-            }
-            warp_sums[threadIdx.x] = wi - w;
-        }
-        __syncthreads();
-        uint32_t excl = carry + warp_sums[threadIdx.x >> 5] + incl - sum;
-#pragma unroll
-        for (uint32_t k = 0; k < per; ++k) { if (i0 + k < m) data[i0 + k] = excl; excl += v[k]; }
-        __syncthreads();
-        if (threadIdx.x == 1023) carry = excl;
-        __syncthreads();
+    for (int k = threadIdx.x; k < P * 256; k += blockDim.x) {
+        const uint32_t v = (&h[0][0])[k];
+        if (v) atomicAdd(ghist + k, v);
     }
-    if (threadIdx.x == 0) totals[blockIdx.x] = carry;
 }
-__global__ void __launch_bounds__(256) rs_scan_totals_kernel(uint32_t* totals) {
+__global__ void __launch_bounds__(256) os_scan_kernel(uint32_t* ghist) {   // block p: exclusive scan of pass p's 256 counters
     __shared__ uint32_t s[256];
-    const uint32_t v = totals[threadIdx.x];
+    uint32_t* g = ghist + 256 * blockIdx.x;
+    const uint32_t v = g[threadIdx.x];
     s[threadIdx.x] = v;
     __syncthreads();
     for (int off = 1; off < 256; off <<= 1) {
@@ -226,27 +238,43 @@ __global__ void __launch_bounds__(256) rs_scan_totals_kernel(uint32_t* totals) {
         s[threadIdx.x] += t;
         __syncthreads();
     }
-    totals[threadIdx.x] = s[threadIdx.x] - v;
+    g[threadIdx.x] = s[threadIdx.x] - v;
 }
-__global__ void __launch_bounds__(RS_THREADS) rs_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
-                                                                 uint32_t n, int shift, uint32_t n_tiles, const uint32_t* __restrict__ hist,
-                                                                 uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out) {
-    // warp w owns the contiguous chunk [w*512, (w+1)*512) of the tile, processed 32 keys per round, so ranks are stable
-    __shared__ uint32_t warp_hist[RS_THREADS / 32][256];
-    __shared__ uint32_t digit_base[256];
+template <class KeyT>
+__global__ void __launch_bounds__(OS_THREADS) os_pass_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                                                              KeyT* __restrict__ keys_out, uint32_t* __restrict__ vals_out, uint32_t n, int shift,
+                                                              const uint32_t* __restrict__ gbase /*[256], exclusive*/, uint32_t* desc /*[tiles][256], zero*/,
+                                                              uint32_t* tile_counter /*zero*/) {
+    __shared__ uint32_t s_tile;
+    __shared__ uint32_t warp_hist[OS_THREADS / 32][256];
+    __shared__ uint32_t digit_off[256];    // first local position of the digit inside the reordered tile
+    __shared__ uint32_t digit_dst[256];    // global position of that first element, minus digit_off
+    __shared__ uint32_t warp_sums[OS_THREADS / 32];
+    __shared__ KeyT s_buf[OS_TILE];        // keys, then (its first half, as u32) the values
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (int k = threadIdx.x; k < (RS_THREADS / 32) * 256; k += RS_THREADS) (&warp_hist[0][0])[k] = 0;
+    // tiles in launch order, not in blockIdx order: a tile only ever waits for tiles that already hold an SM
+    if (threadIdx.x == 0) s_tile = atomicAdd(tile_counter, 1u);
+    for (int k = threadIdx.x; k < (OS_THREADS / 32) * 256; k += OS_THREADS) (&warp_hist[0][0])[k] = 0u;
     __syncthreads();
-    const uint32_t base = blockIdx.x * RS_TILE + warp * (32 * RS_ITEMS);
-    uint32_t key[RS_ITEMS], val[RS_ITEMS], rank[RS_ITEMS];
+    const uint32_t tile = s_tile;
+    const uint32_t tile_base = tile * OS_TILE;
+    const uint32_t tile_count = min((uint32_t)OS_TILE, n - tile_base);
+    // warp w owns the contiguous chunk [w*512, (w+1)*512) of the tile, processed 32 keys per round, so ranks are stable
+    const uint32_t base = tile_base + warp * (32 * OS_ITEMS);
+    KeyT key[OS_ITEMS];
+    uint32_t val[OS_ITEMS], rank[OS_ITEMS];
 #pragma unroll
-    for (int r = 0; r < RS_ITEMS; ++r) {
+    for (int r = 0; r < OS_ITEMS; ++r) {
         const uint32_t i = base + r * 32 + lane;
         const bool live = i < n;
-        key[r] = live ? keys_in[i] : 0xffffffffu;
+        key[r] = live ? keys_in[i] : (KeyT)0;
         val[r] = live ? vals_in[i] : 0u;
-        const uint32_t d = (key[r] >> shift) & 0xffu;
-        const unsigned peers = __match_any_sync(0xffffffffu, live ? d : 0x100u + 0u);
+    }
+#pragma unroll
+    for (int r = 0; r < OS_ITEMS; ++r) {
+        const bool live = base + r * 32 + lane < n;
+        const uint32_t d = (uint32_t)(key[r] >> shift) & 0xffu;
+        const unsigned peers = __match_any_sync(0xffffffffu, live ? d : 0x100u);
         const int leader = __ffs(peers) - 1;
         uint32_t start = 0;
         if (live && lane == leader) { start = warp_hist[warp][d]; warp_hist[warp][d] = start + __popc(peers); }
@@ -255,52 +283,124 @@ __global__ void __launch_bounds__(RS_THREADS) rs_scatter_kernel(const uint32_t* 
         __syncwarp();
     }
     __syncthreads();
-    {   // per digit: exclusive prefix over warps, plus the tile's global base
+    {   // thread d owns digit d: counts over the warps, the tile's count, its position inside the tile, the look-back
         const uint32_t d = threadIdx.x;
-        uint32_t run = hist[(size_t)d * n_tiles + blockIdx.x] + hist[(size_t)256 * n_tiles + d];  // row prefix + prefix of the row totals
-        digit_base[d] = run;
-        uint32_t acc = 0;
-        for (int w = 0; w < RS_THREADS / 32; ++w) { const uint32_t c = warp_hist[w][d]; warp_hist[w][d] = acc; acc += c; }
+        uint32_t count = 0;
+#pragma unroll
+        for (int w = 0; w < OS_THREADS / 32; ++w) { const uint32_t c = warp_hist[w][d]; warp_hist[w][d] = count; count += c; }
+        uint32_t* my = desc + (size_t)tile * 256 + d;
+        if (tile == 0) atomicExch(my, count | OS_FLAG_PREFIX);
+        else atomicExch(my, count | OS_FLAG_LOCAL);
+        // exclusive scan of `count` over the 256 digits: where each digit starts in the reordered tile
+        uint32_t incl = count;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, off);
+            if (lane >= off) incl += t;
+        }
+        if (lane == 31) warp_sums[warp] = incl;
+        __syncthreads();
+        uint32_t wbase = 0;
+#pragma unroll
+        for (int w = 0; w < OS_THREADS / 32; ++w) wbase += w < warp ? warp_sums[w] : 0u;
+        const uint32_t off_d = wbase + incl - count;
+        digit_off[d] = off_d;
+        uint32_t prefix = 0;
+        if (tile != 0) {
+            for (int t = (int)tile - 1; t >= 0;) {
+                const uint32_t v = *(volatile uint32_t*)(desc + (size_t)t * 256 + d);
+                if ((v & (OS_FLAG_LOCAL | OS_FLAG_PREFIX)) == 0u) { __nanosleep(20); continue; }   // not published yet
+                prefix += v & OS_VALUE_MASK;
+                if (v & OS_FLAG_PREFIX) break;
+                --t;
+            }
+            atomicExch(my, (prefix + count) | OS_FLAG_PREFIX);
+        }
+        digit_dst[d] = __ldg(gbase + d) + prefix - off_d;
     }
     __syncthreads();
+    // reorder through shared memory so that a digit's keys leave as one contiguous run
+    uint32_t lp[OS_ITEMS];
 #pragma unroll
-    for (int r = 0; r < RS_ITEMS; ++r) {
-        const uint32_t i = base + r * 32 + lane;
-        if (i < n) {
-            const uint32_t d = (key[r] >> shift) & 0xffu;
-            const uint32_t pos = digit_base[d] + warp_hist[warp][d] + rank[r];
-            keys_out[pos] = key[r];
-            vals_out[pos] = val[r];
+    for (int r = 0; r < OS_ITEMS; ++r) {
+        const uint32_t d = (uint32_t)(key[r] >> shift) & 0xffu;
+        lp[r] = digit_off[d] + warp_hist[warp][d] + rank[r];
+        if (base + r * 32 + lane < n) s_buf[lp[r]] = key[r];
+    }
+    __syncthreads();
+    uint32_t dst[OS_ITEMS];
+#pragma unroll
+    for (int j = 0; j < OS_ITEMS; ++j) {
+        const uint32_t idx = j * OS_THREADS + threadIdx.x;
+        dst[j] = 0xffffffffu;
+        if (idx < tile_count) {
+            const KeyT k = s_buf[idx];
+            dst[j] = digit_dst[(uint32_t)(k >> shift) & 0xffu] + idx;
+            keys_out[dst[j]] = k;
         }
     }
+    __syncthreads();
+    uint32_t* s_val = reinterpret_cast<uint32_t*>(s_buf);
+#pragma unroll
+    for (int r = 0; r < OS_ITEMS; ++r)
+        if (base + r * 32 + lane < n) s_val[lp[r]] = val[r];
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < OS_ITEMS; ++j)
+        if (dst[j] != 0xffffffffu) vals_out[dst[j]] = s_val[j * OS_THREADS + threadIdx.x];
 }
-// Sorts (keys, vals) by `bits` low bits of the key; result ends in keys_a/vals_a (bits/8 must be even) .
-static void radix_sort_pairs(uint32_t* keys_a, uint32_t* vals_a, uint32_t* keys_b, uint32_t* vals_b, uint32_t n, uint32_t* hist,
-                             uint32_t* launches, cudaStream_t st) {
-    const uint32_t n_tiles = (n + RS_TILE - 1) / RS_TILE;
-    for (int pass = 0; pass < 4; ++pass) {
-        const int shift = 8 * pass;
-        const uint32_t* ki = (pass & 1) ? keys_b : keys_a;
+// Scratch of one sort: [PASSES][256] digit bases | [PASSES] tile counters | [PASSES][tiles][256] tile descriptors, zeroed by one memset.
+template <class KeyT>
+static size_t sort_scratch_words(uint32_t n) {
+    const size_t tiles = (n + OS_TILE - 1) / OS_TILE;
+    return (size_t)KeyTraits<KeyT>::PASSES * (256 + 64 + tiles * 256);
+}
+// Sorts (keys, vals) by the whole key; the result ends in keys_a / vals_a (the number of passes is even).
+template <class KeyT>
+static cudaError_t radix_sort_pairs(KeyT* keys_a, uint32_t* vals_a, KeyT* keys_b, uint32_t* vals_b, uint32_t n, uint32_t* scratch,
+                                    uint32_t* launches, cudaStream_t st) {
+    constexpr int P = KeyTraits<KeyT>::PASSES;
+    const uint32_t tiles = (n + OS_TILE - 1) / OS_TILE;
+    uint32_t* ghist = scratch;
+    uint32_t* counters = scratch + (size_t)P * 256;
+    uint32_t* desc = counters + (size_t)P * 64;
+    cudaError_t e = cudaMemsetAsync(scratch, 0, sizeof(uint32_t) * sort_scratch_words<KeyT>(n), st);
+    if (e != cudaSuccess) return e;
+    os_hist_kernel<KeyT><<<std::min<uint32_t>((n + 255) / 256, (uint32_t)sm_count() * 8), 256, 0, st>>>(keys_a, n, ghist);
+    os_scan_kernel<<<P, 256, 0, st>>>(ghist);
+    *launches += 2;
+    for (int pass = 0; pass < P; ++pass) {
+        const KeyT* ki = (pass & 1) ? keys_b : keys_a;
         const uint32_t* vi = (pass & 1) ? vals_b : vals_a;
-        uint32_t* ko = (pass & 1) ? keys_a : keys_b;
+        KeyT* ko = (pass & 1) ? keys_a : keys_b;
         uint32_t* vo = (pass & 1) ? vals_a : vals_b;
-        rs_hist_kernel<<<n_tiles, RS_THREADS, 0, st>>>(ki, n, shift, n_tiles, hist);
-        rs_scan_kernel<<<256, 1024, 0, st>>>(hist, n_tiles, hist + (size_t)256 * n_tiles);
-        rs_scan_totals_kernel<<<1, 256, 0, st>>>(hist + (size_t)256 * n_tiles);
-        rs_scatter_kernel<<<n_tiles, RS_THREADS, 0, st>>>(ki, vi, n, shift, n_tiles, hist, ko, vo);
-        *launches += 4;
+        os_pass_kernel<KeyT><<<tiles, OS_THREADS, 0, st>>>(ki, vi, ko, vo, n, 8 * pass, ghist + 256 * pass, desc + (size_t)pass * tiles * 256, counters + 64 * pass);
+        ++*launches;
     }
+    return cudaGetLastError();
 }
 
 // ------------------------------------------------------------------ Karras 2012 hierarchy
-__device__ __forceinline__ int delta(const uint32_t* __restrict__ keys, int n, int i, int j) {
+__device__ __forceinline__ int key_clz(uint32_t x) { return __clz(x); }
+__device__ __forceinline__ int key_clz(uint64_t x) { return __clzll((long long)x); }
+// length of the common prefix of keys i and j; equal keys are told apart by their position (longer than any key prefix)
+template <class KeyT>
+__device__ __forceinline__ int delta(const KeyT* __restrict__ keys, int n, int i, int j) {
     if (j < 0 || j >= n) return -1;
-    const uint32_t a = keys[i], b = keys[j];
-    if (a != b) return __clz(a ^ b);
-    return 32 + __clz((uint32_t)i ^ (uint32_t)j);
+    const KeyT a = keys[i], b = keys[j];
+    if (a != b) return key_clz(a ^ b);
+    return 8 * (int)sizeof(KeyT) + __clz((uint32_t)i ^ (uint32_t)j);
 }
 // node ids: internal i in [0, n-1), leaf k -> (n-1) + k
-__global__ void hierarchy_kernel(const uint32_t* __restrict__ keys, int n, int2* __restrict__ children, uint32_t* __restrict__ parent) {
+// parent[] entries carry FF_PARENT_CROSS in bit 31 when the parent's leaf range [lo, hi] is not contained in one block of
+// FF_TREELET consecutive sorted leaves: that is where the shared-memory phase of refit_treelet_kernel hands a subtree over to
+// the global hand-off protocol.  (An internal node's index always lies inside its own range, so a contained node also has
+// its index inside the block.)
+#define FF_TREELET 512
+#define FF_PARENT_CROSS 0x80000000u
+#define FF_PARENT_ROOT 0xffffffffu
+template <class KeyT>
+__global__ void hierarchy_kernel(const KeyT* __restrict__ keys, int n, int2* __restrict__ children, uint32_t* __restrict__ parent) {
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n - 1; i += gridDim.x * blockDim.x) {
         const int d = (delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
         const int dmin = delta(keys, n, i, i - d);
@@ -321,9 +421,10 @@ __global__ void hierarchy_kernel(const uint32_t* __restrict__ keys, int n, int2*
         const int left = (lo == gamma) ? (n - 1 + gamma) : gamma;
         const int right = (hi == gamma + 1) ? (n - 1 + gamma + 1) : gamma + 1;
         children[i] = make_int2(left, right);
-        parent[left] = (uint32_t)i;
-        parent[right] = (uint32_t)i;
-        if (i == 0) parent[0] = 0xffffffffu;
+        const uint32_t tag = (uint32_t)i | ((lo / FF_TREELET) != (hi / FF_TREELET) ? FF_PARENT_CROSS : 0u);
+        parent[left] = tag;
+        parent[right] = tag;
+        if (i == 0) parent[0] = FF_PARENT_ROOT;
     }
 }
 
@@ -349,97 +450,193 @@ __device__ __forceinline__ float box_area_lohi(const float4& lo, const float4& h
 // in units of one triangle test.  dp[2v] = {F1..F4}, dp[2v+1] = {F5, F6, F7, decisions}: decisions bits 3(j-2).. = the
 // left child's share k for budget j (0 = take a single slot), bits 21.. = k of the node's own 8 slots.  The greedy
 // "open the largest child" collapse this replaces left 40 % of C2's nodes with two children (profiles/r01g_node_stats).
+// One step of the bottom-up pass: the box, triangle count and F table of a binary node from those of its two children.
+// fl / fr = F(left, 1..7), F(right, 1..7) (index 0 unused); a child that is a single triangle has the constant table
+// area * (slot + 1) (leaf_table).  Results: lo (w = count), hi (w = first sorted position, the left child's), f[1..7], dec.
+__device__ __forceinline__ void leaf_table(const float4& l, const float4& h, float slot_cost, float f[8]) {
+    const float f1 = box_area_lohi(l, h) * (slot_cost + 1.0f);
+#pragma unroll
+    for (int q = 1; q <= 7; ++q) f[q] = f1;
+}
+__device__ __forceinline__ void dp_combine(const float4& l0, const float4& h0, const float fl[8], const float4& l1, const float4& h1, const float fr[8],
+                                           float slot_cost, float node_cost, float4& lo, float4& hi, float f[8], uint32_t& dec) {
+    const int cnt = (__float_as_int(l0.w) & FF_COUNT_MASK) + (__float_as_int(l1.w) & FF_COUNT_MASK);
+    lo = make_float4(fminf(l0.x, l1.x), fminf(l0.y, l1.y), fminf(l0.z, l1.z), __int_as_float(cnt));
+    hi = make_float4(fmaxf(h0.x, h1.x), fmaxf(h0.y, h1.y), fmaxf(h0.z, h1.z), h0.w);
+    const float area = box_area_lohi(lo, hi);
+    dec = 0;
+    {
+        float g = FLT_MAX;
+        uint32_t k8 = 1;
+#pragma unroll
+        for (int q = 1; q <= 7; ++q) { const float v = fl[q] + fr[8 - q]; if (v < g) { g = v; k8 = (uint32_t)q; } }
+        dec |= k8 << 21;
+        f[1] = (cnt <= FF_LEAF_MAX) ? area * (slot_cost + (float)cnt) : area * (slot_cost + node_cost) + g;
+    }
+#pragma unroll
+    for (int j = 2; j <= 7; ++j) {
+        float g = f[1];
+        uint32_t kj = 0;
+#pragma unroll
+        for (int q = 1; q < j; ++q) { const float v = fl[q] + fr[j - q]; if (v < g) { g = v; kj = (uint32_t)q; } }
+        f[j] = g;
+        dec |= kj << (3 * (j - 2));
+    }
+}
+__device__ __forceinline__ void unpack_table(const float4& d0, const float4& d1, float f[8]) {
+    f[1] = d0.x; f[2] = d0.y; f[3] = d0.z; f[4] = d0.w; f[5] = d1.x; f[6] = d1.y; f[7] = d1.z;
+}
+// Climbs from `node` (whose box / table are already in global memory) towards the root with the global hand-off: the first
+// thread to arrive at a parent stops, the second finishes it.
+// acq_rel: RELEASE so this thread's box and table are visible before its arrival is counted; ACQUIRE so the second arrival's
+// loads of its sibling's box and table are ordered after the atomic by the PTX memory model itself (a compiler barrier plus
+// a control dependency is not an ordering there).  One atomic instead of the fence.sc + L1 invalidate that __threadfence()
+// cost twice per level (39 % of the stall samples, profiles/r01i_refit_before_stalls.txt); the loads bypass L1 (ld.global.cg).
+__device__ __forceinline__ void refit_climb_global(uint32_t node, int n, const int2* __restrict__ children, const uint32_t* __restrict__ parent,
+                                                   uint32_t* __restrict__ flags, float4* __restrict__ box_lo, float4* __restrict__ box_hi,
+                                                   float4* __restrict__ dp, float slot_cost, float node_cost) {
+    for (;;) {
+        const uint32_t pp = parent[node];
+        if (pp == FF_PARENT_ROOT) break;
+        const uint32_t p = pp & ~FF_PARENT_CROSS;
+        uint32_t arrived;
+        asm volatile("atom.global.add.acq_rel.gpu.u32 %0, [%1], 1;" : "=r"(arrived) : "l"(__cvta_generic_to_global(flags + p)) : "memory");
+        if (arrived == 0u) break;  // first arrival: the sibling's thread finishes this node
+        const int2 ch = children[p];
+        const float4 l0 = __ldcg(box_lo + ch.x), l1 = __ldcg(box_lo + ch.y), h0 = __ldcg(box_hi + ch.x), h1 = __ldcg(box_hi + ch.y);
+        float fl[8], fr[8];
+        if ((uint32_t)ch.x < (uint32_t)(n - 1)) unpack_table(__ldcg(dp + 2 * (size_t)ch.x), __ldcg(dp + 2 * (size_t)ch.x + 1), fl);
+        else leaf_table(l0, h0, slot_cost, fl);  // a triangle: one leaf child whatever the budget (only internal nodes have a table)
+        if ((uint32_t)ch.y < (uint32_t)(n - 1)) unpack_table(__ldcg(dp + 2 * (size_t)ch.y), __ldcg(dp + 2 * (size_t)ch.y + 1), fr);
+        else leaf_table(l1, h1, slot_cost, fr);
+        float4 lo, hi;
+        float f[8];
+        uint32_t dec;
+        dp_combine(l0, h0, fl, l1, h1, fr, slot_cost, node_cost, lo, hi, f, dec);
+        dp[2 * (size_t)p] = make_float4(f[1], f[2], f[3], f[4]);
+        dp[2 * (size_t)p + 1] = make_float4(f[5], f[6], f[7], __uint_as_float(dec));
+        box_lo[p] = lo;
+        box_hi[p] = hi;
+        node = p;
+    }
+}
+__device__ __forceinline__ void leaf_box(const float4* __restrict__ flat_tris, uint32_t src, int k, float pad, float4& lo, float4& hi) {
+    const float4 a = flat_tris[3 * (size_t)src], b = flat_tris[3 * (size_t)src + 1], c = flat_tris[3 * (size_t)src + 2];
+    lo = make_float4(fminf(fminf(a.x, b.x), c.x) - pad, fminf(fminf(a.y, b.y), c.y) - pad, fminf(fminf(a.z, b.z), c.z) - pad, __int_as_float(1));
+    hi = make_float4(fmaxf(fmaxf(a.x, b.x), c.x) + pad, fmaxf(fmaxf(a.y, b.y), c.y) + pad, fmaxf(fmaxf(a.z, b.z), c.z) + pad, __int_as_float(k));
+}
+// Any binary hierarchy (the binned-SAH builder's): one thread per leaf, every level through the global hand-off.
 __global__ void refit_kernel(const float4* __restrict__ flat_tris, const uint32_t* __restrict__ sorted_idx, int n, float pad,
                              const int2* __restrict__ children, const uint32_t* __restrict__ parent, uint32_t* __restrict__ flags,
                              float4* __restrict__ box_lo, float4* __restrict__ box_hi, float4* __restrict__ dp, float slot_cost,
                              float node_cost) {
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
-        const uint32_t src = sorted_idx[k];
-        const float4 a = flat_tris[3 * (size_t)src], b = flat_tris[3 * (size_t)src + 1], c = flat_tris[3 * (size_t)src + 2];
-        float4 lo = make_float4(fminf(fminf(a.x, b.x), c.x) - pad, fminf(fminf(a.y, b.y), c.y) - pad, fminf(fminf(a.z, b.z), c.z) - pad, __int_as_float(1));
-        float4 hi = make_float4(fmaxf(fmaxf(a.x, b.x), c.x) + pad, fmaxf(fmaxf(a.y, b.y), c.y) + pad, fmaxf(fmaxf(a.z, b.z), c.z) + pad, __int_as_float(k));
-        uint32_t node = (uint32_t)(n - 1 + k);
+        float4 lo, hi;
+        leaf_box(flat_tris, sorted_idx[k], k, pad, lo, hi);
+        const uint32_t node = (uint32_t)(n - 1 + k);
         box_lo[node] = lo;
         box_hi[node] = hi;
         if (n == 1) return;   // (a single triangle has no F table: F(leaf, j) = area * (slot + 1) is formed by its parent)
+        refit_climb_global(node, n, children, parent, flags, box_lo, box_hi, dp, slot_cost, node_cost);
+    }
+}
+
+// The same pass for the LBVH hierarchy, in treelets.  In Karras's numbering a node's index lies inside its own leaf range,
+// so the subtrees over a block of FF_TREELET consecutive sorted leaves -- all but the ~log levels above them -- live in a
+// contiguous index range: one CTA resolves them in SHARED memory (hand-off by shared-memory atomics, children read back
+// from shared memory), writes the block's boxes and tables out with coalesced stores, and only the few nodes whose parent's
+// range crosses the block boundary (FF_PARENT_CROSS) continue through the global hand-off above.  At 20 M triangles the
+// all-global version was a 25-level chain of global atomic -> L2 loads -> stores per node, 6.5 of the build's 12 ms
+// (71 % long-scoreboard, 21 % membar stalls: profiles/r01i_refit_20m_stalls.txt).
+#define FF_TREELET_THREADS 256
+__global__ void __launch_bounds__(FF_TREELET_THREADS) refit_treelet_kernel(const float4* __restrict__ flat_tris, const uint32_t* __restrict__ sorted_idx,
+                                                                            int n, float pad, const int2* __restrict__ children,
+                                                                            const uint32_t* __restrict__ parent, uint32_t* __restrict__ flags,
+                                                                            float4* __restrict__ box_lo, float4* __restrict__ box_hi,
+                                                                            float4* __restrict__ dp, float slot_cost, float node_cost) {
+    constexpr int S = FF_TREELET, T = FF_TREELET_THREADS;
+    extern __shared__ float4 sm4[];
+    float4* s_lo = sm4;              // [0, S): internal nodes of the block (index - base), [S, 2S): its leaves
+    float4* s_hi = sm4 + 2 * S;
+    float4* s_dp = sm4 + 4 * S;      // 2 per internal node
+    uint32_t* s_flag = reinterpret_cast<uint32_t*>(sm4 + 6 * S);
+    uint32_t* s_parent = s_flag + S;                              // [0, S): parents of the internal nodes, [S, 2S): of the leaves
+    int2* s_children = reinterpret_cast<int2*>(s_parent + 2 * S); // children of the internal nodes
+    const int base = blockIdx.x * S;
+    const int m = min(S, n - base);
+    const uint32_t n_internal = (uint32_t)(n - 1);
+    // The links of the block, staged with coalesced loads: the climb below is then a chain of shared-memory accesses only
+    // (with parent[] / children[] read from global memory inside the chain, the ~9 levels of a block cost two dependent L2
+    // round trips each and a CTA spent most of its life waiting: 3.1 ms at 20 M triangles instead of 6.5, still latency-bound).
+    for (int i = threadIdx.x; i < S; i += T) {
+        s_flag[i] = 0u;
+        const uint32_t g = (uint32_t)(base + i);
+        s_parent[i] = g < n_internal ? parent[g] : FF_PARENT_ROOT;
+        s_children[i] = g < n_internal ? children[g] : make_int2(0, 0);
+        s_parent[S + i] = i < m ? parent[n_internal + g] : FF_PARENT_ROOT;
+    }
+    __syncthreads();
+    for (int t = threadIdx.x; t < m; t += T) {
+        const int k = base + t;
+        float4 lo, hi;
+        leaf_box(flat_tris, sorted_idx[k], k, pad, lo, hi);
+        s_lo[S + t] = lo;
+        s_hi[S + t] = hi;
+        int local = S + t;
+        if (n == 1) break;
         for (;;) {
-            const uint32_t p = parent[node];
-            if (p == 0xffffffffu) break;
-            // acq_rel: RELEASE so this thread's box and table are visible before its arrival is counted; ACQUIRE so the second
-            // arrival's loads of its sibling's box and table are ordered after the atomic by the PTX memory model itself (a
-            // compiler barrier plus a control dependency is not an ordering there).  One atomic instead of the fence.sc + L1
-            // invalidate that __threadfence() cost twice per level (39 % of the kernel's stall samples,
-            // profiles/r01i_refit_before_stalls.txt); the loads below additionally bypass L1 (ld.global.cg).
-#if FF_REFIT_FENCE == 2
-            __threadfence();
-            if (atomicAdd(&flags[p], 1u) == 0u) break;  // first arrival: the sibling's thread finishes this node
-            __threadfence();
-#else
-            uint32_t arrived;
-            asm volatile("atom.global.add.acq_rel.gpu.u32 %0, [%1], 1;" : "=r"(arrived) : "l"(__cvta_generic_to_global(flags + p)) : "memory");
-            if (arrived == 0u) break;  // first arrival: the sibling's thread finishes this node
-#endif
-            const int2 ch = children[p];
-#if FF_REFIT_FENCE == 2
-            const volatile float4* vlo = box_lo;
-            const volatile float4* vhi = box_hi;
-            float4 l0, l1, h0, h1;
-            l0.x = vlo[ch.x].x; l0.y = vlo[ch.x].y; l0.z = vlo[ch.x].z; l0.w = vlo[ch.x].w;
-            l1.x = vlo[ch.y].x; l1.y = vlo[ch.y].y; l1.z = vlo[ch.y].z; l1.w = vlo[ch.y].w;
-            h0.x = vhi[ch.x].x; h0.y = vhi[ch.x].y; h0.z = vhi[ch.x].z; h0.w = vhi[ch.x].w;
-            h1.x = vhi[ch.y].x; h1.y = vhi[ch.y].y; h1.z = vhi[ch.y].z; h1.w = vhi[ch.y].w;
-#else
-            // ld.global.cg: 128-bit loads served by L2 (never a stale L1 line), ordered after the atomic by its "memory" clobber
-            const float4 l0 = __ldcg(box_lo + ch.x), l1 = __ldcg(box_lo + ch.y), h0 = __ldcg(box_hi + ch.x), h1 = __ldcg(box_hi + ch.y);
-#endif
-            const int cnt = (__float_as_int(l0.w) & FF_COUNT_MASK) + (__float_as_int(l1.w) & FF_COUNT_MASK);
-            lo = make_float4(fminf(l0.x, l1.x), fminf(l0.y, l1.y), fminf(l0.z, l1.z), 0.f);
-            hi = make_float4(fmaxf(h0.x, h1.x), fmaxf(h0.y, h1.y), fmaxf(h0.z, h1.z), h0.w);
-            // F(left, 1..7), F(right, 1..7)
+            const uint32_t pp = s_parent[local];
+            if (pp == FF_PARENT_ROOT) break;
+            if (pp & FF_PARENT_CROSS) break;   // handed over to refit_cross_kernel
+            const int pl = (int)pp - base;
+            __threadfence_block();   // this node's box / table (shared memory) before its arrival is counted
+            if (atomicAdd(&s_flag[pl], 1u) == 0u) break;
+            __threadfence_block();
+            const int2 ch = s_children[pl];
+            const bool leaf0 = (uint32_t)ch.x >= n_internal, leaf1 = (uint32_t)ch.y >= n_internal;
+            const int c0 = leaf0 ? S + (ch.x - (int)n_internal - base) : ch.x - base, c1 = leaf1 ? S + (ch.y - (int)n_internal - base) : ch.y - base;
+            const float4 l0 = s_lo[c0], h0 = s_hi[c0], l1 = s_lo[c1], h1 = s_hi[c1];
             float fl[8], fr[8];
-            if ((uint32_t)ch.x < (uint32_t)(n - 1)) {
-                const float4 d0 = __ldcg(dp + 2 * (size_t)ch.x), d1 = __ldcg(dp + 2 * (size_t)ch.x + 1);
-                fl[1] = d0.x; fl[2] = d0.y; fl[3] = d0.z; fl[4] = d0.w; fl[5] = d1.x; fl[6] = d1.y; fl[7] = d1.z;
-            } else {  // a triangle: one leaf child whatever the budget (only internal nodes have a table)
-                const float f1 = box_area_lohi(l0, h0) * (slot_cost + 1.0f);
-#pragma unroll
-                for (int q = 1; q <= 7; ++q) fl[q] = f1;
-            }
-            if ((uint32_t)ch.y < (uint32_t)(n - 1)) {
-                const float4 d0 = __ldcg(dp + 2 * (size_t)ch.y), d1 = __ldcg(dp + 2 * (size_t)ch.y + 1);
-                fr[1] = d0.x; fr[2] = d0.y; fr[3] = d0.z; fr[4] = d0.w; fr[5] = d1.x; fr[6] = d1.y; fr[7] = d1.z;
-            } else {
-                const float f1 = box_area_lohi(l1, h1) * (slot_cost + 1.0f);
-#pragma unroll
-                for (int q = 1; q <= 7; ++q) fr[q] = f1;
-            }
-            const float area = box_area_lohi(lo, hi);
+            if (leaf0) leaf_table(l0, h0, slot_cost, fl); else unpack_table(s_dp[2 * c0], s_dp[2 * c0 + 1], fl);
+            if (leaf1) leaf_table(l1, h1, slot_cost, fr); else unpack_table(s_dp[2 * c1], s_dp[2 * c1 + 1], fr);
             float f[8];
-            uint32_t dec = 0;
-            {
-                float g = FLT_MAX;
-                uint32_t k8 = 1;
-#pragma unroll
-                for (int q = 1; q <= 7; ++q) { const float v = fl[q] + fr[8 - q]; if (v < g) { g = v; k8 = (uint32_t)q; } }
-                dec |= k8 << 21;
-                f[1] = (cnt <= 3) ? area * (slot_cost + (float)cnt) : area * (slot_cost + node_cost) + g;
-            }
-#pragma unroll
-            for (int j = 2; j <= 7; ++j) {
-                float g = f[1];
-                uint32_t kj = 0;
-#pragma unroll
-                for (int q = 1; q < j; ++q) { const float v = fl[q] + fr[j - q]; if (v < g) { g = v; kj = (uint32_t)q; } }
-                f[j] = g;
-                dec |= kj << (3 * (j - 2));
-            }
-            dp[2 * (size_t)p] = make_float4(f[1], f[2], f[3], f[4]);
-            dp[2 * (size_t)p + 1] = make_float4(f[5], f[6], f[7], __uint_as_float(dec));
-            lo.w = __int_as_float(cnt);
-            box_lo[p] = lo;
-            box_hi[p] = hi;
-            node = p;
+            uint32_t dec;
+            dp_combine(l0, h0, fl, l1, h1, fr, slot_cost, node_cost, lo, hi, f, dec);
+            s_lo[pl] = lo;
+            s_hi[pl] = hi;
+            s_dp[2 * pl] = make_float4(f[1], f[2], f[3], f[4]);
+            s_dp[2 * pl + 1] = make_float4(f[5], f[6], f[7], __uint_as_float(dec));
+            local = pl;
         }
+    }
+    __syncthreads();
+    // the block's leaves and finished internal nodes to global memory, coalesced
+    for (int t = threadIdx.x; t < m; t += T) {
+        box_lo[n_internal + (uint32_t)(base + t)] = s_lo[S + t];
+        box_hi[n_internal + (uint32_t)(base + t)] = s_hi[S + t];
+    }
+    for (int i = threadIdx.x; i < S; i += T)
+        if (s_flag[i] == 2u) {
+            const size_t g = (size_t)base + i;
+            box_lo[g] = s_lo[i];
+            box_hi[g] = s_hi[i];
+            dp[2 * g] = s_dp[2 * i];
+            dp[2 * g + 1] = s_dp[2 * i + 1];
+        }
+}
+// The levels above the treelets: every node (or leaf) that was finished inside a block but whose PARENT's range crosses a block
+// boundary starts a climb through the global hand-off.  A separate launch, not a tail of the treelet kernel: a climb is a
+// chain of up to ~15 global atomic -> load -> store round trips, and a treelet CTA that waited for its climbs kept its 58 KB
+// of shared memory -- and with it a third of an SM -- for tens of microseconds (3.1 ms at 20 M triangles).
+__global__ void refit_cross_kernel(int n, const int2* __restrict__ children, const uint32_t* __restrict__ parent, uint32_t* __restrict__ flags,
+                                   float4* __restrict__ box_lo, float4* __restrict__ box_hi, float4* __restrict__ dp, float slot_cost, float node_cost) {
+    const uint32_t n_internal = (uint32_t)(n - 1), total = 2u * (uint32_t)n - 1u;
+    for (uint32_t node = blockIdx.x * blockDim.x + threadIdx.x; node < total; node += gridDim.x * blockDim.x) {
+        const uint32_t pp = parent[node];
+        if (pp == FF_PARENT_ROOT || !(pp & FF_PARENT_CROSS)) continue;
+        // an internal node that itself crosses a boundary is finished by whichever of its children arrives second, not from here
+        if (node < n_internal && (parent[children[node].x] & FF_PARENT_CROSS)) continue;
+        refit_climb_global(node, n, children, parent, flags, box_lo, box_hi, dp, slot_cost, node_cost);
     }
 }
 
@@ -482,39 +679,67 @@ __device__ __forceinline__ uint32_t quant_hi(float c, float p, float sc) {
 }
 
 // One thread per wide node.  node_src[w] = the binary node wide node w is built from.  Wide-node indices are handed out
-// by one counter, so the nodes of a level are a contiguous index range and the levels need no host round trip: the kernel
-// reads its range from the counters block, collapse_advance_kernel moves the range to the nodes the level allocated.
+// by one counter, so the nodes of a level are a contiguous index range and the levels need no host round trip
+// (collapse_persistent_kernel).
 __device__ __forceinline__ void collapse_one(uint32_t bnode, uint32_t wnode, uint32_t* __restrict__ node_src, uint32_t node_capacity, int n,
                                 const int2* __restrict__ children, const float4* __restrict__ box_lo, const float4* __restrict__ box_hi,
                                 const float4* __restrict__ flat_tris, const uint32_t* __restrict__ sorted_idx,
                                 float4* __restrict__ nodes, float4* __restrict__ tris_out, uint32_t* __restrict__ leaf_slot,
-                                CollapseCounters* ctr, float root_area, const float4* __restrict__ dp) {
+                                CollapseCounters* ctr, float root_area, const float4* __restrict__ dp, uint32_t (*e_node)[8][128], uint32_t (*e_bud)[8][128]) {
     const uint32_t n_internal = (uint32_t)(n - 1);
 
     uint32_t ch[8];
     int nch = 0;
     float4 plo = box_lo[bnode], phi = box_hi[bnode];
-    if (bnode >= n_internal || (__float_as_int(plo.w) & FF_COUNT_MASK) <= 3) {
+    if (bnode >= n_internal || (__float_as_int(plo.w) & FF_COUNT_MASK) <= FF_LEAF_MAX) {
         ch[nch++] = bnode;  // tiny scene: the whole tree is one leaf child
     } else {
-        // follow the decisions of the refit DP: (binary node, slot budget) pairs, at most 8 slots in flight
-        uint32_t st_node[8];
-        uint32_t st_bud[8];
-        int sp = 0;
+        // Follow the decisions of the refit DP: a list of (binary node, slot budget) pairs in left-to-right order, budgets
+        // summing to 8.  Every round expands ALL entries that the DP splits, with the loads of the round (decision word and
+        // children of each entry) issued together: 3-4 memory round trips per wide node.  (The depth-first walk this replaces
+        // did one entry at a time, two dependent loads each: up to ~30 round trips, and the collapse of 1 M triangles spent
+        // 0.42 ms in nine levels of that whether it ran as 24 launches or as one persistent kernel.)
+        // e_node / e_bud: this thread's column of two [8][128] shared arrays per buffer (dynamic indexing without local memory).
+        const int t = threadIdx.x;
+        int cur = 0, c = 2;
         {
-            const uint32_t k8 = (__float_as_uint(dp[2 * (size_t)bnode + 1].w) >> 21) & 7u;
-            st_node[sp] = (uint32_t)children[bnode].y; st_bud[sp++] = 8u - k8;
-            st_node[sp] = (uint32_t)children[bnode].x; st_bud[sp++] = k8;
+            const uint32_t k8 = (__float_as_uint(__ldg(&dp[2 * (size_t)bnode + 1].w)) >> 21) & 7u;
+            const int2 c2 = __ldg(children + bnode);
+            e_node[0][0][t] = (uint32_t)c2.x; e_bud[0][0][t] = k8;
+            e_node[0][1][t] = (uint32_t)c2.y; e_bud[0][1][t] = 8u - k8;
         }
-        while (sp > 0 && nch < 8) {
-            const uint32_t m = st_node[--sp], j = st_bud[sp];
-            uint32_t d = 0;
-            if (m < n_internal && j >= 2u) d = (__float_as_uint(dp[2 * (size_t)m + 1].w) >> (3u * (j - 2u))) & 7u;
-            if (d == 0u || d >= j || sp + 2 > 8) { ch[nch++] = m; continue; }   // one slot: a leaf (<= 3 triangles) or an inner child
-            const int2 c2 = children[m];
-            st_node[sp] = (uint32_t)c2.y; st_bud[sp++] = j - d;
-            st_node[sp] = (uint32_t)c2.x; st_bud[sp++] = d;
+        for (;;) {
+            uint32_t dec[8];
+            int2 kid[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                dec[i] = 0u; kid[i] = make_int2(0, 0);
+                if (i < c) {
+                    const uint32_t m = e_node[cur][i][t], j = e_bud[cur][i][t];
+                    if (m < n_internal && j >= 2u) { dec[i] = __float_as_uint(__ldg(&dp[2 * (size_t)m + 1].w)); kid[i] = __ldg(children + m); }
+                }
+            }
+            int nc = 0;
+            bool changed = false;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                if (i < c) {
+                    const uint32_t m = e_node[cur][i][t], j = e_bud[cur][i][t];
+                    const uint32_t d = (m < n_internal && j >= 2u) ? (dec[i] >> (3u * (j - 2u))) & 7u : 0u;
+                    if (d == 0u || d >= j || nc + 2 + (c - 1 - i) > 8) {   // one slot: a leaf (<= FF_LEAF_MAX triangles) or an inner child; budget 1 = settled
+                        e_node[cur ^ 1][nc][t] = m; e_bud[cur ^ 1][nc][t] = 1u; ++nc;
+                    } else {
+                        e_node[cur ^ 1][nc][t] = (uint32_t)kid[i].x; e_bud[cur ^ 1][nc][t] = d; ++nc;
+                        e_node[cur ^ 1][nc][t] = (uint32_t)kid[i].y; e_bud[cur ^ 1][nc][t] = j - d; ++nc;
+                        changed = true;
+                    }
+                }
+            }
+            cur ^= 1; c = nc;
+            if (!changed) break;
         }
+        for (int i = 0; i < c; ++i) ch[i] = e_node[cur][i][t];
+        nch = c;
     }
 
     // slot assignment: greedy maximisation of dot(child centre - node centre, octant direction of the slot)
@@ -562,7 +787,7 @@ __device__ __forceinline__ void collapse_one(uint32_t bnode, uint32_t wnode, uin
         if (k < 0) continue;
         const uint32_t c = ch[k];
         const int cnt = __float_as_int(box_lo[c].w) & FF_COUNT_MASK;
-        if (c < n_internal && cnt > 3) { imask |= 1u << s; ++n_inner; }
+        if (c < n_internal && cnt > FF_LEAF_MAX) { imask |= 1u << s; ++n_inner; }
         else n_leaf_tris += (uint32_t)cnt;
     }
     // Allocation is aggregated over the lanes that arrive here together (one atomicAdd per counter and warp instead of one
@@ -649,30 +874,61 @@ __device__ __forceinline__ void collapse_one(uint32_t bnode, uint32_t wnode, uin
         if (g.thread_rank() == 0) atomicAdd(&ctr->sah, sum);
     }
 }
-__global__ void __launch_bounds__(128) collapse_kernel(uint32_t* __restrict__ node_src, uint32_t node_capacity, int n,
-                                const int2* __restrict__ children, const float4* __restrict__ box_lo, const float4* __restrict__ box_hi,
-                                const float4* __restrict__ flat_tris, const uint32_t* __restrict__ sorted_idx,
-                                float4* __restrict__ nodes, float4* __restrict__ tris_out, uint32_t* __restrict__ leaf_slot,
-                                CollapseCounters* ctr, float root_area, const float4* __restrict__ dp) {
-    const uint32_t begin = ctr->level_begin, end = ctr->level_end;   // constant during the level
-    for (uint32_t w = begin + blockIdx.x * blockDim.x + threadIdx.x; w < end; w += gridDim.x * blockDim.x)
-        collapse_one(node_src[w], w, node_src, node_capacity, n, children, box_lo, box_hi, flat_tris, sorted_idx, nodes, tris_out, leaf_slot,
-                     ctr, root_area, dp);
-}
 // Triangles into BVH-leaf order: sorted position p -> slot leaf_slot[p] (written by the collapse).
 __global__ void gather_tris_kernel(const float4* __restrict__ flat_tris, const uint32_t* __restrict__ sorted_idx,
                                    const uint32_t* __restrict__ leaf_slot, uint32_t n, float4* __restrict__ tris_out) {
     for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
         const size_t src = sorted_idx[p], slot = leaf_slot[p];
+        if (slot >= n) continue;   // (only after a node-capacity overflow, which bvh_build reports: the slot was never assigned)
         const float4 a = __ldg(flat_tris + 3 * src), b = __ldg(flat_tris + 3 * src + 1), c = __ldg(flat_tris + 3 * src + 2);
         tris_out[3 * slot] = a; tris_out[3 * slot + 1] = b; tris_out[3 * slot + 2] = c;
     }
 }
-__global__ void collapse_advance_kernel(CollapseCounters* ctr, uint32_t node_capacity) {
-    const uint32_t end = ctr->level_end, allocated = min(ctr->node_count, node_capacity);
-    if (end > ctr->level_begin) ctr->levels += 1;
-    ctr->level_begin = end;
-    ctr->level_end = ctr->overflow ? end : allocated;
+// All levels in ONE launch: a persistent grid (every CTA resident: cooperative launch) walks the levels with a grid barrier in
+// between.  The last CTA to arrive at the barrier moves the level range to the nodes the level allocated before it releases the others, so one barrier per level is enough.  The
+// per-level launches cost 24 kernel launches and two host round trips per build whatever the depth -- 0.4 of the 0.93 ms of a
+// 1 M-triangle build (profiles/r02a_launches_bench_summary.json).
+struct GridBarrier { uint32_t arrived; uint32_t generation; };
+__global__ void __launch_bounds__(128) collapse_persistent_kernel(uint32_t* __restrict__ node_src, uint32_t node_capacity, int n,
+                                const int2* __restrict__ children, const float4* __restrict__ box_lo, const float4* __restrict__ box_hi,
+                                const float4* __restrict__ flat_tris, const uint32_t* __restrict__ sorted_idx,
+                                float4* __restrict__ nodes, float4* __restrict__ tris_out, uint32_t* __restrict__ leaf_slot,
+                                CollapseCounters* ctr, const float4* __restrict__ root_lo, const float4* __restrict__ root_hi,
+                                const float4* __restrict__ dp, GridBarrier* bar) {
+    const float4 rl = __ldg(root_lo), rh = __ldg(root_hi);
+    const float root_area = box_area(rl, rh);
+    __shared__ uint32_t s_range[2];
+    __shared__ uint32_t e_node[2][8][128], e_bud[2][8][128];
+    for (uint32_t gen = 0;; ++gen) {
+        if (threadIdx.x == 0) {
+            s_range[0] = *(volatile uint32_t*)&ctr->level_begin;
+            s_range[1] = *(volatile uint32_t*)&ctr->level_end;
+        }
+        __syncthreads();
+        const uint32_t begin = s_range[0], end = s_range[1];
+        if (begin == end) return;   // uniform over the grid: every CTA reads the range the barrier published
+        for (uint32_t w = begin + blockIdx.x * blockDim.x + threadIdx.x; w < end; w += gridDim.x * blockDim.x)
+            collapse_one(__ldcg(node_src + w), w, node_src, node_capacity, n, children, box_lo, box_hi, flat_tris, sorted_idx, nodes, tris_out, leaf_slot,
+                         ctr, root_area, dp, e_node, e_bud);
+        // ---- grid barrier; the last arrival advances the level
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();
+            const uint32_t ticket = atomicAdd(&bar->arrived, 1u);
+            if (ticket == (gen + 1u) * gridDim.x - 1u) {
+                const uint32_t allocated = min(*(volatile uint32_t*)&ctr->node_count, node_capacity);
+                if (end > begin) ctr->levels += 1;
+                ctr->level_begin = end;
+                ctr->level_end = *(volatile uint32_t*)&ctr->overflow ? end : allocated;
+                __threadfence();
+                atomicExch(&bar->generation, gen + 1u);
+            } else {
+                while (*(volatile uint32_t*)&bar->generation <= gen) __nanosleep(40);
+            }
+            __threadfence();
+        }
+        __syncthreads();
+    }
 }
 
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return e_; } while (0)
@@ -699,39 +955,47 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
         fprintf(stderr, "[ff build] %-28s %9.3f ms\n", what, std::chrono::duration<double, std::milli>(now - t_last).count());
         t_last = now;
     };
-    const uint32_t n_tiles = (n + RS_TILE - 1) / RS_TILE;
+    // 63-bit Morton keys above 2^20 triangles (FF_MORTON_BITS=30 / 63 forces one or the other: development knob)
+    const char* mb_env = getenv("FF_MORTON_BITS");
+    const bool wide_keys = mb_env ? atoi(mb_env) > 32 : n > (1u << 20);
+    const size_t key_bytes = wide_keys ? sizeof(uint64_t) : sizeof(uint32_t);
+    const size_t sort_words = wide_keys ? sort_scratch_words<uint64_t>(n) : sort_scratch_words<uint32_t>(n);
     int* d_bounds = nullptr;
-    uint32_t *d_keys_a = nullptr, *d_keys_b = nullptr, *d_vals_a = nullptr, *d_vals_b = nullptr, *d_hist = nullptr;
+    void *d_keys_a = nullptr, *d_keys_b = nullptr;
+    uint32_t *d_vals_a = nullptr, *d_vals_b = nullptr, *d_hist = nullptr;
     uint32_t *d_parent = nullptr, *d_flags = nullptr;
     float4* d_dp = nullptr;
     uint32_t* d_src = nullptr;
     CollapseCounters* d_ctr = nullptr;
     {
-        size_t need = Arena::padded(12 * sizeof(int)) + 4 * Arena::padded(sizeof(uint32_t) * n) + Arena::padded(sizeof(uint32_t) * 256 * ((size_t)n_tiles + 1)) +
+        size_t need = Arena::padded(12 * sizeof(int)) + 2 * Arena::padded(sizeof(uint32_t) * n) + 2 * Arena::padded(key_bytes * n) + Arena::padded(sizeof(uint32_t) * sort_words) +
                       Arena::padded(sizeof(uint32_t) * 2 * (size_t)n) + Arena::padded(sizeof(uint32_t) * n) + Arena::padded(sizeof(float4) * 2 * (size_t)n) +
-                      Arena::padded(sizeof(uint32_t) * (size_t)node_capacity) + Arena::padded(sizeof(CollapseCounters));
+                      Arena::padded(sizeof(uint32_t) * (size_t)node_capacity) + Arena::padded(sizeof(CollapseCounters)) + Arena::padded(sizeof(GridBarrier));
         if (builder == FF_BUILDER_SAH) need += sah_scratch_bytes(n);
         CK(arena.reserve(need));
     }
     d_bounds = arena.take<int>(12);
-    d_keys_a = arena.take<uint32_t>(n); d_keys_b = arena.take<uint32_t>(n);
+    d_keys_a = arena.take<char>(key_bytes * n); d_keys_b = arena.take<char>(key_bytes * n);
     d_vals_a = arena.take<uint32_t>(n); d_vals_b = arena.take<uint32_t>(n);
-    d_hist = arena.take<uint32_t>(256 * ((size_t)n_tiles + 1));   // [256][n_tiles] counters + 256 row totals
+    d_hist = arena.take<uint32_t>(sort_words);   // digit bases, tile counters, tile descriptors of the sort
     d_parent = arena.take<uint32_t>(2 * (size_t)n);
     d_flags = arena.take<uint32_t>(n);
     d_dp = arena.take<float4>(2 * (size_t)n);   // F table + decisions of the n - 1 internal binary nodes
     d_src = arena.take<uint32_t>(node_capacity);
     d_ctr = arena.take<CollapseCounters>(1);
-    if (!d_ctr) return cudaErrorMemoryAllocation;
+    GridBarrier* d_bar = arena.take<GridBarrier>(1);
+    if (!d_ctr || !d_bar) return cudaErrorMemoryAllocation;
     CK(cudaMemsetAsync(d_flags, 0, sizeof(uint32_t) * n, st));
     mark("reserve scratch");
 
     bounds_init_kernel<<<1, 32, 0, st>>>(d_bounds);
     bounds_kernel<<<grid_for(n, 256, sm_count() * 8), 256, 0, st>>>(d_flat_tris, n, d_bounds);
-    morton_kernel<<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(d_flat_tris, n, d_bounds, d_keys_a, d_vals_a);
+    if (wide_keys) morton_kernel<uint64_t><<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(d_flat_tris, n, d_bounds, (uint64_t*)d_keys_a, d_vals_a);
+    else morton_kernel<uint32_t><<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(d_flat_tris, n, d_bounds, (uint32_t*)d_keys_a, d_vals_a);
     *launches += 3;
     mark("bounds + morton");
-    radix_sort_pairs(d_keys_a, d_vals_a, d_keys_b, d_vals_b, n, d_hist, launches, st);
+    if (wide_keys) CK(radix_sort_pairs<uint64_t>((uint64_t*)d_keys_a, d_vals_a, (uint64_t*)d_keys_b, d_vals_b, n, d_hist, launches, st));
+    else CK(radix_sort_pairs<uint32_t>((uint32_t*)d_keys_a, d_vals_a, (uint32_t*)d_keys_b, d_vals_b, n, d_hist, launches, st));
     mark("radix sort");
     int h_bounds[12];
     CK(cudaMemcpyAsync(h_bounds, d_bounds, sizeof(h_bounds), cudaMemcpyDeviceToHost, st));
@@ -745,7 +1009,8 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
         d_order = d_vals_b;
         mark("binned-SAH hierarchy");
     } else if (n > 1) {
-        hierarchy_kernel<<<grid_for(n - 1, 256, sm_count() * 16), 256, 0, st>>>(d_keys_a, (int)n, d_bvh2_children, d_parent);
+        if (wide_keys) hierarchy_kernel<uint64_t><<<grid_for(n - 1, 256, sm_count() * 16), 256, 0, st>>>((const uint64_t*)d_keys_a, (int)n, d_bvh2_children, d_parent);
+        else hierarchy_kernel<uint32_t><<<grid_for(n - 1, 256, sm_count() * 16), 256, 0, st>>>((const uint32_t*)d_keys_a, (int)n, d_bvh2_children, d_parent);
         ++*launches;
         mark("karras hierarchy");
     }
@@ -753,44 +1018,68 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
     const float slot_cost = sc_env ? (float)atof(sc_env) : FF_SLOT_COST;
     const char* nc_env = getenv("FF_NODE_COST");
     const float node_cost = nc_env ? (float)atof(nc_env) : FF_NODE_COST;
-    refit_kernel<<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(d_flat_tris, d_order, (int)n, pad, d_bvh2_children, d_parent, d_flags,
-                                                            d_bvh2_lo, d_bvh2_hi, d_dp, slot_cost, node_cost);
+    if (builder == FF_BUILDER_LBVH && !getenv("FF_REFIT_GLOBAL")) {
+        const size_t smem = sizeof(float4) * 6 * FF_TREELET + sizeof(uint32_t) * 3 * FF_TREELET + sizeof(int2) * FF_TREELET;
+        static bool attr_set[64] = {false};
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+            CK(cudaFuncSetAttribute(refit_treelet_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            attr_set[dev] = true;
+        }
+        refit_treelet_kernel<<<(n + FF_TREELET - 1) / FF_TREELET, FF_TREELET_THREADS, smem, st>>>(d_flat_tris, d_order, (int)n, pad, d_bvh2_children, d_parent,
+                                                                                             d_flags, d_bvh2_lo, d_bvh2_hi, d_dp, slot_cost, node_cost);
+        if (n > 1) {
+            refit_cross_kernel<<<grid_for(2 * (size_t)n, 256, sm_count() * 16), 256, 0, st>>>((int)n, d_bvh2_children, d_parent, d_flags, d_bvh2_lo, d_bvh2_hi, d_dp,
+                                                                                         slot_cost, node_cost);
+            ++*launches;
+        }
+    } else {
+        refit_kernel<<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(d_flat_tris, d_order, (int)n, pad, d_bvh2_children, d_parent, d_flags,
+                                                                d_bvh2_lo, d_bvh2_hi, d_dp, slot_cost, node_cost);
+    }
     ++*launches;
     mark("refit + collapse DP");
 
-    float4 root_lo, root_hi;
-    const uint32_t root = (n == 1) ? 0u : 0u;  // internal node 0, or the single leaf (id n-1+0 = 0)
-    CK(cudaMemcpyAsync(&root_lo, d_bvh2_lo + root, sizeof(float4), cudaMemcpyDeviceToHost, st));
-    CK(cudaMemcpyAsync(&root_hi, d_bvh2_hi + root, sizeof(float4), cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
-    for (int k = 0; k < 3; ++k) { bounds_lo[k] = ordered_to_float(h_bounds[k]); bounds_hi[k] = ordered_to_float(h_bounds[3 + k]); }
-    const float dx = root_hi.x - root_lo.x, dy = root_hi.y - root_lo.y, dz = root_hi.z - root_lo.z;
-    const float root_area = 2.0f * (dx * dy + dy * dz + dz * dx);
-
+    const uint32_t root = 0u;  // internal node 0, or the single leaf (id n-1+0 = 0)
     CollapseCounters h_ctr;
     memset(&h_ctr, 0, sizeof(h_ctr));
     h_ctr.node_count = 1; h_ctr.level_begin = 0; h_ctr.level_end = 1;
     CK(cudaMemcpyAsync(d_ctr, &h_ctr, sizeof(h_ctr), cudaMemcpyHostToDevice, st));
     CK(cudaMemcpyAsync(d_src, &root, sizeof(uint32_t), cudaMemcpyHostToDevice, st));
-    // Levels in flights of 12 without host round trips (a hierarchy of 20 M triangles is 10 levels deep): fixed grid,
-    // grid-stride over the level's index range read from the device; an exhausted hierarchy costs empty launches.
-    for (int flight = 0; flight < 8; ++flight) {
-        for (int l = 0; l < 12; ++l) {
-            collapse_kernel<<<sm_count() * 8, 128, 0, st>>>(d_src, node_capacity, (int)n, d_bvh2_children, d_bvh2_lo, d_bvh2_hi, d_flat_tris, d_order,
-                                                    d_nodes_out, d_tris_out, d_bvh2_leaf_slot, d_ctr, root_area, d_dp);
-            collapse_advance_kernel<<<1, 1, 0, st>>>(d_ctr, node_capacity);
-            *launches += 2;
+    CK(cudaMemsetAsync(d_bar, 0, sizeof(GridBarrier), st));
+    {
+        // one launch for all levels; grid = what is co-resident on this device (the barrier needs every CTA running)
+        static int blocks_per_sm[64] = {0};
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (dev < 0 || dev >= 64) dev = 0;
+        if (blocks_per_sm[dev] == 0) {
+            int b = 0;
+            CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, collapse_persistent_kernel, 128, 0));
+            blocks_per_sm[dev] = b > 0 ? b : 1;
         }
-        CK(cudaMemcpyAsync(&h_ctr, d_ctr, sizeof(h_ctr), cudaMemcpyDeviceToHost, st));
-        CK(cudaStreamSynchronize(st));
-        if (h_ctr.overflow) { CK(cudaErrorMemoryAllocation); }
-        if (h_ctr.level_begin == h_ctr.level_end) break;
-    }
-    if (h_ctr.level_begin != h_ctr.level_end) return cudaErrorUnknown;  // deeper than 96 levels: not a hierarchy this builder makes
-    if (h_ctr.tri_count == n) {
-        gather_tris_kernel<<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(d_flat_tris, d_order, d_bvh2_leaf_slot, n, d_tris_out);
+        const int grid = sm_count() * std::min(blocks_per_sm[dev], 8);
+        int n_arg = (int)n;
+        const float4* rl = d_bvh2_lo + root;
+        const float4* rh = d_bvh2_hi + root;
+        const int2* ch_arg = d_bvh2_children;
+        const float4 *lo_arg = d_bvh2_lo, *hi_arg = d_bvh2_hi, *flat_arg = d_flat_tris, *dp_arg = d_dp;
+        const uint32_t* ord_arg = d_order;
+        void* args[] = {&d_src, &node_capacity, &n_arg, &ch_arg, &lo_arg, &hi_arg, &flat_arg, &ord_arg, &d_nodes_out, &d_tris_out, &d_bvh2_leaf_slot,
+                        &d_ctr, &rl, &rh, &dp_arg, &d_bar};
+        CK(cudaLaunchCooperativeKernel((const void*)collapse_persistent_kernel, dim3(grid), dim3(128), args, 0, st));
         ++*launches;
     }
+    // the triangle gather needs leaf_slot[] complete, nothing from the host: queue it behind the collapse, then read the counters
+    gather_tris_kernel<<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(d_flat_tris, d_order, d_bvh2_leaf_slot, n, d_tris_out);
+    ++*launches;
+    CK(cudaMemcpyAsync(&h_ctr, d_ctr, sizeof(h_ctr), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    CK(cudaGetLastError());
+    for (int k = 0; k < 3; ++k) { bounds_lo[k] = ordered_to_float(h_bounds[k]); bounds_hi[k] = ordered_to_float(h_bounds[3 + k]); }
+    if (h_ctr.overflow) { CK(cudaErrorMemoryAllocation); }
+    if (h_ctr.level_begin != h_ctr.level_end) return cudaErrorUnknown;
     const uint32_t depth = h_ctr.levels;
     mark("collapse to 8-wide");
     out->n_nodes = h_ctr.node_count;

@@ -9,9 +9,19 @@
 #include "../../include/firefly.h"
 #include "ff_math.h"
 
+#ifndef FF_SM_STACK
 #define FF_SM_STACK 8      // traversal stack entries kept in shared memory per thread
+#endif
+#ifndef FF_TRI_QUEUE
 #define FF_TRI_QUEUE 8     // ring of pending triangle groups per thread in shared memory (power of two)
-#define FF_LOCAL_STACK 56  // spill entries in local memory
+#endif
+#define FF_LOCAL_STACK (64 - FF_SM_STACK)  // spill entries in local memory
+#ifndef FF_LEAF_MAX
+#define FF_LEAF_MAX 3      // most triangles one leaf child of a wide node may hold (collapse DP, ff_bvh.cu)
+#endif
+#ifndef FF_TRI_EVERY
+#define FF_TRI_EVERY 1     // >1 (probe): a lane that still has node work runs its triangle phase only every k-th iteration
+#endif
 #define FF_MAX_WIDE_DEPTH (FF_SM_STACK + FF_LOCAL_STACK)
 #define FF_TRACE_BLOCK 128
 #define FF_REFILL_LANES 28            // persistent trace: refill idle lanes when fewer than this many still traverse
@@ -128,9 +138,10 @@ struct TraceCounters { unsigned long long nodes, tris; };
 // What the wavefront's extend stage leaves for its shade stage: 8 bytes instead of the 16-byte API record (the closest-hit
 // key and the scan-order id matter to callers of ff_trace_closest*, not to shading).
 struct HitLite { float t; int slot; };
-// Bounce 0 of a wavefront pass: the extend stage generates the camera ray of path p = (sample, pixel) itself instead of
-// reading 32 bytes a ray-generation kernel would have had to write (and the shade stage re-derives it the same way).
-struct WaveGen { CamDev cam; RenderDev rp; };
+// Bounce 0 of a wavefront pass: every camera ray starts at the camera position and path p sits at queue index p, so the
+// ray-generation kernel writes 16 bytes per path (the direction) instead of 64 (origin + path id, direction, throughput),
+// and the extend and shade stages of bounce 0 read those 16 bytes and take the rest from the kernel parameters.
+struct WaveGen { float ox, oy, oz; };
 
 // ---------------------------------------------------------------- kernel launch wrappers
 // (implemented in the .cu files; all asynchronous on `st`)

@@ -233,17 +233,22 @@ __device__ __forceinline__ bool shade_event(const DevScene& sc, const RenderDev&
 }
 
 // ------------------------------------------------------------------ wavefront stages
-// Start of a pass: the queue counters, and (next-event estimation only) radiance[p] = 0 for the shadow stages to add to.
-// There is no ray-generation kernel any more: bounce 0's extend stage makes the camera ray of path p from p itself
-// (FetchCamera in ff_trace.cu) and the shade stage of bounce 0 repeats the same arithmetic, so the 64 B per path that
-// wf_raygen_kernel wrote -- and the 32 B that each of the two stages read back -- are gone (C2: 4.2 GB + 4.2 GB per frame).
-__global__ void wf_reset_kernel(RenderDev rp, float4* __restrict__ radiance, uint32_t* __restrict__ counts, int n_counts) {
+// Start of a pass: the queue counters, the camera-ray DIRECTION of every path (16 B; the origin is the camera position and
+// path p sits at queue index p, so bounce 0 needs neither ray_o nor beta: 64 B per path written and 2 x 32 B read back
+// before this change, C2: 4.2 GB + 4.2 GB per frame), and -- next-event estimation only -- radiance[p] = 0 for the shadow
+// stages to add to.
+__global__ void wf_raygen_kernel(CamDev cam, RenderDev rp, float4* __restrict__ ray_d, float4* __restrict__ radiance, uint32_t* __restrict__ counts, int n_counts) {
     const uint32_t n = rp.samples * rp.npix;
     if (blockIdx.x == 0)  // paths per bounce | extend work counters | shadow rays per bounce | shadow work counters
         for (int k = threadIdx.x; k < 4 * n_counts; k += blockDim.x) counts[k] = k == 0 ? n : 0u;
-    // radiance[p] is written exactly once, when the path ends -- only the shadow stage of next-event estimation adds to it before that
-    if (rp.nee)
-        for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) radiance[p] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
+        const uint32_t s = p / rp.npix, pixel = frame_pixel(rp, p - s * rp.npix);
+        V3 o, d;
+        primary_ray(cam, rp, pixel, rp.first_sample + s, o, d);
+        ray_d[p] = make_float4(d.x, d.y, d.z, 0.f);
+        // radiance[p] is written exactly once, when the path ends -- only the shadow stage of next-event estimation adds to it before that
+        if (rp.nee) radiance[p] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
 }
 
 // shade + BSDF sampling + queue compaction: survivors are appended to the next bounce's queue (ballot + popc inside a
@@ -290,9 +295,9 @@ __global__ void __launch_bounds__(FF_SHADE_BLOCK) wf_shade_kernel(DevScene sc, C
 #else
 #define FF_PF "prefetch.global.L2 [%0];"
 #endif
+                asm volatile(FF_PF ::"l"(ray_d_in + k2));
                 if (!FIRST) {
                     asm volatile(FF_PF ::"l"(ray_o_in + k2));
-                    asm volatile(FF_PF ::"l"(ray_d_in + k2));
                     asm volatile(FF_PF ::"l"(beta_in + k2));
                 }
                 if ((lane & 15) == 0) asm volatile(FF_PF ::"l"(hits + k2));
@@ -304,10 +309,11 @@ __global__ void __launch_bounds__(FF_SHADE_BLOCK) wf_shade_kernel(DevScene sc, C
             HitRec h;
             h.key = 0.f; h.t = hl.t; h.slot = hl.slot; h.ord = 0;   // shading reads t and slot only
             uint32_t s, pixel;
-            if (FIRST) {   // camera segment: path k is (sample, pixel) = (k / npix, k % npix); its ray is re-derived, beta = 1
+            if (FIRST) {   // camera segment: path k is (sample, pixel) = (k / npix, k % npix), starts at the camera, beta = 1
                 path = k;
                 s = path / rp.npix; pixel = frame_pixel(rp, path - s * rp.npix);
-                primary_ray(cam, rp, pixel, rp.first_sample + s, o, d);
+                o = v3(cam.pos[0], cam.pos[1], cam.pos[2]);
+                d = ld3(ray_d_in[k]);
                 beta = v3(1.f, 1.f, 1.f);
             } else {
                 const float4 o4 = ray_o_in[k], d4 = ray_d_in[k], b4 = beta_in[k];
@@ -371,9 +377,9 @@ void k_wavefront_pass(const DevScene& sc, const CamDev& cam, const RenderDev& rp
                       cudaStream_t st) {
     const uint32_t n = rp.samples * rp.npix;
     const int n_counts = rp.max_bounces + 2;
-    wf_reset_kernel<<<rp.nee ? grid_for(n, 256, sm_count() * 16) : 1, 256, 0, st>>>(rp, wb.radiance, wb.counts, n_counts);
+    wf_raygen_kernel<<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(cam, rp, wb.ray_d[0], wb.radiance, wb.counts, n_counts);
     ++*launches;
-    const WaveGen gen = {cam, rp};
+    const WaveGen gen = {cam.pos[0], cam.pos[1], cam.pos[2]};
     const bool nee = rp.nee && sc.n_lights != 0;
     const int shade_grid = grid_for(n, FF_SHADE_BLOCK, sm_count() * 16 * 256 / FF_SHADE_BLOCK);
     for (int b = 0; b <= rp.max_bounces; ++b) {

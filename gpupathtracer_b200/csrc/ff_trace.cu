@@ -39,9 +39,11 @@ __device__ __forceinline__ void store_hit(HitRec* hits, size_t i, const Best& b)
 }
 
 // Where a closest-hit kernel takes its rays from and what it leaves behind.  The API entry points read ray arrays and write
-// the 16-byte record; the wavefront's extend stage writes 8-byte records and, on bounce 0, makes the camera ray of path i
-// itself (primary_ray: the same arithmetic the shade stage repeats), so no ray-generation kernel has to write 32 bytes per
-// path for this one to read back.  `skipbits` = slot + 1 of the triangle the ray starts on (0: none), see make_ray_ctx.
+// the 16-byte record; the wavefront's extend stage writes 8-byte records and, on bounce 0, reads only the 16-byte direction
+// (the origin of every camera ray is the camera position).  Generating the camera ray INSIDE this kernel was tried and lost:
+// the fetch path runs at ~11 active lanes, and ~100 instructions of matrix product and IEEE normalise there cost more
+// (+1.1 ms per C2 frame) than the 32 bytes per path they saved (profiles/r02c_bench.json).
+// `skipbits` = slot + 1 of the triangle the ray starts on (0: none), see make_ray_ctx.
 struct FetchArrays {
     const float4* __restrict__ ray_o;
     const float4* __restrict__ ray_d;
@@ -50,13 +52,11 @@ struct FetchArrays {
         o = ld3(__ldg(ray_o + i)); draw = ld3(d4); skipbits = __float_as_uint(d4.w);
     }
 };
-struct FetchCamera {
-    CamDev cam;
-    RenderDev rp;
+struct FetchPrimary {   // bounce 0 of the wavefront: origin = the camera position, direction from the ray-generation kernel, no self-skip
+    const float4* __restrict__ ray_d;
+    float ox, oy, oz;
     __device__ __forceinline__ void operator()(uint32_t i, V3& o, V3& draw, uint32_t& skipbits) const {
-        const uint32_t s = i / rp.npix, pixel = frame_pixel(rp, i - s * rp.npix);
-        primary_ray(cam, rp, pixel, rp.first_sample + s, o, draw);
-        skipbits = 0u;
+        o = ffm::v3(ox, oy, oz); draw = ld3(__ldg(ray_d + i)); skipbits = 0u;
     }
 };
 struct StoreRec {
@@ -158,8 +158,16 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK, FF_TRACE_MINB) trace_closest_p
         }
 #else
         if (has) {
+#if FF_TRI_EVERY > 1
+            unsigned it = 0;
+#endif
             for (;;) {
+#if FF_TRI_EVERY > 1
+                const bool do_tri = (++it % FF_TRI_EVERY) == 0;
+                if (!bvh8_step<false, false, SKIP>(sc, r, tv, best, my_stack, FF_TRACE_BLOCK, lstack, cn, ct, true, do_tri)) {
+#else
                 if (!bvh8_step<false, false, SKIP>(sc, r, tv, best, my_stack, FF_TRACE_BLOCK, lstack, cn, ct)) {
+#endif
                     store(ray_index, best);
                     has = false;
                     break;
@@ -257,7 +265,7 @@ void k_trace_closest(const DevScene& sc, const float4* d_ray_o, const float4* d_
 void k_trace_extend(const DevScene& sc, const WaveGen* gen, const float4* d_ray_o, const float4* d_ray_d, const uint32_t* d_count,
                     uint32_t n_max, int mode, HitLite* d_hits, TraceCounters* d_counters, uint32_t* d_work_counter, cudaStream_t st) {
     if (n_max == 0) return;
-    if (gen) launch_closest(sc, FetchCamera{gen->cam, gen->rp}, StoreLite{d_hits}, d_count, n_max, mode & ~FF_TRACE_SELFSKIP, d_counters, d_work_counter, st);
+    if (gen) launch_closest(sc, FetchPrimary{d_ray_d, gen->ox, gen->oy, gen->oz}, StoreLite{d_hits}, d_count, n_max, mode & ~FF_TRACE_SELFSKIP, d_counters, d_work_counter, st);
     else launch_closest(sc, FetchArrays{d_ray_o, d_ray_d}, StoreLite{d_hits}, d_count, n_max, mode, d_counters, d_work_counter, st);
 }
 

@@ -351,7 +351,8 @@ __device__ __forceinline__ bool bvh8_step(const DevScene& sc, const RayCtx& r, T
             }
         }
     }
-    if (do_tri && tv.tgroup.y != 0u) {
+    // (do_tri false = hold the triangle phase back this iteration, unless the lane has nothing else to do)
+    if ((do_tri || (tv.ngroup.y & 0xff000000u) == 0u) && tv.tgroup.y != 0u) {
         if (bvh8_test_one<ANY, COUNT>(sc, r, tv, best, n_tris)) return false;
         if (tv.tgroup.y == 0u && tv.qcount > 0) tv.tgroup = tv.dequeue(sm, stride);
     }

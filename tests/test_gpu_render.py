@@ -410,3 +410,46 @@ def test_obj_attributes_through_the_scene(ff, ctx, orc, meshes, attrs, tmp_path)
         sc.set_face_materials(0, np.full(n, 3, np.int32), mats)   # index 3 of 3 materials
     with pytest.raises(ff.FireflyError):
         sc.set_uvs(7, uv6)
+
+
+@pytest.mark.gpu
+def test_converged_renders_agree_within_monte_carlo_tolerance(ff, ctx, meshes):
+    """North-star correctness part 3 on the GPU at a converged sample count: config 2 at 128 x 128, 4096 spp.  The plain loop
+    and next-event estimation are two unbiased estimators of the same image, so their means must agree within the noise that
+    two independent seeds of each estimator show.  Tolerances (written here, as the contract asks): per 8 x 8-pixel block the
+    difference of the two estimators' means is measured in units of its own standard error, estimated from the seed pairs --
+    |z| of the WHOLE-IMAGE mean below 4, fewer than 2 % of the blocks beyond 6 standard errors (seed-pair variances have one
+    degree of freedom, hence the wide per-block bar), image means within 1 %.  Sample-split accumulation at this size stays
+    within the fp32 re-association bound of 1e-5 relative."""
+    w = h = 128
+    spp, bounces = 4096, 4
+    desc = S.config2(meshes, w, h, spp, bounces)
+    sc, cam = S.instantiate(desc, ctx, meshes, builder=1)
+    img = {}
+    for nee in (0, 1):
+        for seed in (11, 2222):
+            img[nee, seed] = sc.render(cam, spp, bounces, nee=nee, seed=seed, aa=1)[..., :3].astype(np.float64)
+
+    def blocks(a):
+        return a.reshape(h // 8, 8, w // 8, 8, 3).mean(axis=(1, 3, 4))
+    m0, m1 = blocks((img[0, 11] + img[0, 2222]) / 2), blocks((img[1, 11] + img[1, 2222]) / 2)
+    v0, v1 = blocks(img[0, 11] - img[0, 2222]) ** 2 / 4, blocks(img[1, 11] - img[1, 2222]) ** 2 / 4   # variance of a two-seed mean
+    # block variances from ONE seed pair are noisy: pool them over the image for the per-block bar, keep them for the global one
+    se_block = np.sqrt(np.mean(v0 + v1))
+    z_blocks = (m1 - m0) / se_block
+    z_global = (m1 - m0).sum() / np.sqrt((v0 + v1).sum())
+    assert m0.mean() > 0.05, "the frame is not lit"
+    assert abs(z_global) < 4.0, z_global
+    assert (np.abs(z_blocks) > 6.0).mean() < 0.02, np.abs(z_blocks).max()
+    assert abs(m1.mean() - m0.mean()) < 0.01 * m0.mean(), (m0.mean(), m1.mean())
+    # next-event estimation has the lower variance on this scene (a small ceiling light): the reason the stage exists
+    assert np.mean(v1) < np.mean(v0)
+    # disjoint sample ranges summed == one render of all samples (Philox is keyed by the global sample index)
+    npix = w * h
+    buf = ctx.alloc(npix * 16)
+    buf.zero()
+    for k in range(4):
+        sc.render_accumulate(cam, buf, spp // 4, bounces, first_sample=k * (spp // 4), seed=11, aa=1)
+    split = ctx.resolve(buf, w, h, spp)[..., :3]
+    one = img[0, 11]
+    assert np.abs(split - one).max() <= 1e-5 * max(1.0, float(one.max()))

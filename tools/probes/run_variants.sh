@@ -7,6 +7,6 @@ import sys,json
 for l in sys.stdin:
     try: d=json.loads(l)
     except Exception: print(l.strip()[:200]); continue
-    print(d['case'], d.get('integrator',''), round(d['mrays_s']))
+    print(d['case'], d.get('integrator',''), round(d['mrays_s']), 'n/r %.2f t/r %.2f' % (d.get('nodes_per_ray',0), d.get('tris_per_ray',0)), ('gpu_ms %.2f' % d['gpu_ms']) if 'gpu_ms' in d else '')
 "
 done

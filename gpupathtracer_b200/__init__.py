@@ -87,7 +87,8 @@ class CStats(C.Structure):
 class CSceneInfo(C.Structure):
     _fields_ = [("n_triangles", C.c_uint64), ("n_geometries", C.c_uint64), ("n_planes", C.c_uint64), ("n_nodes", C.c_uint64),
                 ("node_bytes", C.c_uint64), ("triangle_bytes", C.c_uint64), ("depth", C.c_uint32), ("builder", C.c_uint32),
-                ("bounds_lo", C.c_float * 3), ("bounds_hi", C.c_float * 3), ("build_ms", C.c_double), ("sah_cost", C.c_double)]
+                ("bounds_lo", C.c_float * 3), ("bounds_hi", C.c_float * 3), ("build_ms", C.c_double), ("sah_cost", C.c_double),
+                ("morton_bits", C.c_uint32), ("reserved", C.c_uint32)]
 
     def as_dict(self):
         d = {k: getattr(self, k) for k, _ in self._fields_}

@@ -439,7 +439,7 @@ int ff_scene_commit(ff_scene* scene, int builder, double* out_build_ms) {
     FF_CUDA(upload(&scene->d_attr_uvs, attr_uvs, st));
     FF_CUDA(upload(&scene->d_attr_facemat, attr_facemat, st));
 
-    BuildOut bo; bo.n_nodes = 0; bo.depth = 0; bo.sah_cost = 0;
+    BuildOut bo; bo.n_nodes = 0; bo.depth = 0; bo.sah_cost = 0; bo.morton_bits = 0;
     float blo[3] = {0, 0, 0}, bhi[3] = {0, 0, 0};
     double build_ms = 0;
     uint32_t launches = 0;
@@ -536,7 +536,7 @@ int ff_scene_commit(ff_scene* scene, int builder, double* out_build_ms) {
     in.n_triangles = n_tris; in.n_geometries = scene->geoms.size(); in.n_planes = n_planes; in.n_nodes = bo.n_nodes;
     in.node_bytes = 16ull * FF_NODE_F4 * bo.n_nodes; in.triangle_bytes = 48ull * n_tris; in.depth = bo.depth; in.builder = (uint32_t)builder;
     for (int k = 0; k < 3; ++k) { in.bounds_lo[k] = blo[k]; in.bounds_hi[k] = bhi[k]; }
-    in.build_ms = build_ms; in.sah_cost = bo.sah_cost;
+    in.build_ms = build_ms; in.sah_cost = bo.sah_cost; in.morton_bits = bo.morton_bits;
     scene->committed = true;
     if (out_build_ms) *out_build_ms = build_ms;
     return FF_OK;

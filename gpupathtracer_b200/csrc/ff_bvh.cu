@@ -188,6 +188,14 @@ __global__ void morton_kernel(const float4* __restrict__ tris, uint32_t n, const
     }
 }
 
+// how many sorted keys repeat their predecessor: the measure of whether the 30-bit grid resolves the scene
+__global__ void count_duplicate_keys_kernel(const uint32_t* __restrict__ keys, uint32_t n, uint32_t* __restrict__ out) {
+    uint32_t c = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x + 1u; i < n; i += gridDim.x * blockDim.x) c += keys[i] == keys[i - 1] ? 1u : 0u;
+    for (int off = 16; off; off >>= 1) c += __shfl_xor_sync(0xffffffffu, c, off);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, c);
+}
+
 // ------------------------------------------------------------------ LSD radix sort, 8-bit digits, ONE sweep per pass
 // Keys are 32-bit (30-bit Morton codes, 4 passes) or 64-bit (63-bit codes, 8 passes); values are the 32-bit triangle indices.
 //   os_hist_kernel   one read of the keys: the digit histograms of ALL passes (shared-memory atomics), added to global counters
@@ -396,7 +404,9 @@ __device__ __forceinline__ int delta(const KeyT* __restrict__ keys, int n, int i
 // FF_TREELET consecutive sorted leaves: that is where the shared-memory phase of refit_treelet_kernel hands a subtree over to
 // the global hand-off protocol.  (An internal node's index always lies inside its own range, so a contained node also has
 // its index inside the block.)
+#ifndef FF_TREELET
 #define FF_TREELET 512
+#endif
 #define FF_PARENT_CROSS 0x80000000u
 #define FF_PARENT_ROOT 0xffffffffu
 template <class KeyT>
@@ -562,6 +572,8 @@ __global__ void __launch_bounds__(FF_TREELET_THREADS) refit_treelet_kernel(const
     uint32_t* s_flag = reinterpret_cast<uint32_t*>(sm4 + 6 * S);
     uint32_t* s_parent = s_flag + S;                              // [0, S): parents of the internal nodes, [S, 2S): of the leaves
     int2* s_children = reinterpret_cast<int2*>(s_parent + 2 * S); // children of the internal nodes
+    uint32_t (*s_q)[FF_TREELET] = reinterpret_cast<uint32_t (*)[FF_TREELET]>(s_children + S);   // two queues of finished-children nodes
+    uint32_t* s_qn = reinterpret_cast<uint32_t*>(s_q + 2);
     const int base = blockIdx.x * S;
     const int m = min(S, n - base);
     const uint32_t n_internal = (uint32_t)(n - 1);
@@ -576,22 +588,36 @@ __global__ void __launch_bounds__(FF_TREELET_THREADS) refit_treelet_kernel(const
         s_parent[S + i] = i < m ? parent[n_internal + g] : FF_PARENT_ROOT;
     }
     __syncthreads();
+    // Level-synchronous inside the block: a node whose second child has just been finished is appended to the NEXT round's
+    // queue instead of being computed by the arriving thread, and each round hands its queue to consecutive threads.  (With
+    // the classic climb -- the second arrival computes the parent at once -- half of the lanes drop out per level while the
+    // warp keeps executing the ~250 instructions of the DP: 7 of 32 lanes active on average, and the kernel was bound by
+    // instruction issue, profiles/r02g_build1m_full details.)
+    if (threadIdx.x < 2) s_qn[threadIdx.x] = 0u;
+    __syncthreads();
+    auto arrive = [&](int local, int buf) {   // the node at `local` is finished: count it at its parent
+        const uint32_t pp = s_parent[local];
+        if (pp == FF_PARENT_ROOT || (pp & FF_PARENT_CROSS)) return;   // the root, or handed over to refit_cross_kernel
+        const int pl = (int)pp - base;
+        if (atomicAdd(&s_flag[pl], 1u) == 1u) s_q[buf][atomicAdd(&s_qn[buf], 1u)] = (uint32_t)pl;
+    };
     for (int t = threadIdx.x; t < m; t += T) {
         const int k = base + t;
         float4 lo, hi;
         leaf_box(flat_tris, sorted_idx[k], k, pad, lo, hi);
         s_lo[S + t] = lo;
         s_hi[S + t] = hi;
-        int local = S + t;
-        if (n == 1) break;
-        for (;;) {
-            const uint32_t pp = s_parent[local];
-            if (pp == FF_PARENT_ROOT) break;
-            if (pp & FF_PARENT_CROSS) break;   // handed over to refit_cross_kernel
-            const int pl = (int)pp - base;
-            __threadfence_block();   // this node's box / table (shared memory) before its arrival is counted
-            if (atomicAdd(&s_flag[pl], 1u) == 0u) break;
-            __threadfence_block();
+        if (n > 1) arrive(S + t, 0);
+    }
+    __syncthreads();
+    for (int cur = 0;; cur ^= 1) {
+        const uint32_t count = s_qn[cur];
+        if (count == 0u) break;
+        __syncthreads();                       // everybody has read the count before the other queue is reset
+        if (threadIdx.x == 0) s_qn[cur ^ 1] = 0u;
+        __syncthreads();
+        for (uint32_t i = threadIdx.x; i < count; i += T) {
+            const int pl = (int)s_q[cur][i];
             const int2 ch = s_children[pl];
             const bool leaf0 = (uint32_t)ch.x >= n_internal, leaf1 = (uint32_t)ch.y >= n_internal;
             const int c0 = leaf0 ? S + (ch.x - (int)n_internal - base) : ch.x - base, c1 = leaf1 ? S + (ch.y - (int)n_internal - base) : ch.y - base;
@@ -599,6 +625,7 @@ __global__ void __launch_bounds__(FF_TREELET_THREADS) refit_treelet_kernel(const
             float fl[8], fr[8];
             if (leaf0) leaf_table(l0, h0, slot_cost, fl); else unpack_table(s_dp[2 * c0], s_dp[2 * c0 + 1], fl);
             if (leaf1) leaf_table(l1, h1, slot_cost, fr); else unpack_table(s_dp[2 * c1], s_dp[2 * c1 + 1], fr);
+            float4 lo, hi;
             float f[8];
             uint32_t dec;
             dp_combine(l0, h0, fl, l1, h1, fr, slot_cost, node_cost, lo, hi, f, dec);
@@ -606,8 +633,9 @@ __global__ void __launch_bounds__(FF_TREELET_THREADS) refit_treelet_kernel(const
             s_hi[pl] = hi;
             s_dp[2 * pl] = make_float4(f[1], f[2], f[3], f[4]);
             s_dp[2 * pl + 1] = make_float4(f[5], f[6], f[7], __uint_as_float(dec));
-            local = pl;
+            arrive(pl, cur ^ 1);
         }
+        __syncthreads();                       // this round's boxes and tables, and the next round's queue, are complete
     }
     __syncthreads();
     // the block's leaves and finished internal nodes to global memory, coalesced
@@ -678,9 +706,9 @@ __device__ __forceinline__ uint32_t quant_hi(float c, float p, float sc) {
     return (uint32_t)q;
 }
 
-// One thread per wide node.  node_src[w] = the binary node wide node w is built from.  Wide-node indices are handed out
-// by one counter, so the nodes of a level are a contiguous index range and the levels need no host round trip
-// (collapse_persistent_kernel).
+// ONE THREAD per wide node: the throughput version, used for the large levels of the hierarchy (collapse_persistent_kernel).
+// node_src[w] = the binary node wide node w is built from.  Wide-node indices are handed out by one counter, so the nodes of
+// a level are a contiguous index range and the levels need no host round trip.
 __device__ __forceinline__ void collapse_one(uint32_t bnode, uint32_t wnode, uint32_t* __restrict__ node_src, uint32_t node_capacity, int n,
                                 const int2* __restrict__ children, const float4* __restrict__ box_lo, const float4* __restrict__ box_hi,
                                 const float4* __restrict__ flat_tris, const uint32_t* __restrict__ sorted_idx,
@@ -874,6 +902,214 @@ __device__ __forceinline__ void collapse_one(uint32_t bnode, uint32_t wnode, uin
         if (g.thread_rank() == 0) atomicAdd(&ctr->sah, sum);
     }
 }
+// EIGHT LANES per wide node (a cg tile), lane k owning child k through the whole job: the latency version, used for the small
+// levels at the top of the hierarchy.
+//   One thread per node is ~6000 dependent instructions (512 slot-cost evaluations of the greedy assignment, 48 quantisations
+//   with a division each) executed by a single lane: ~30 us per node, and since a level cannot start before its parent level
+//   has allocated its nodes, nine levels cost 270 us before any throughput mattered -- the grid barrier was 29 of the 47 stall
+//   cycles per issued instruction (profiles/r02g_build1m_full).  Spread over 8 lanes the critical path of a node is ~1/6; on
+//   a level with millions of nodes the eight-fold thread count costs more than the shorter path saves (20 M triangles: 3.7 ms
+//   against 2.9), hence the two versions.
+// The tree is the same as the one-thread version built: same children in the same order, the same greedy assignment with the
+// same tie-breaks (lowest child, then lowest slot), the same quantisation arithmetic.
+typedef cg::thread_block_tile<8> Tile8;
+__device__ __forceinline__ uint32_t tile_or(const Tile8& t, uint32_t v) {
+    v |= t.shfl_xor(v, 1); v |= t.shfl_xor(v, 2); v |= t.shfl_xor(v, 4);
+    return v;
+}
+__device__ __forceinline__ uint32_t tile_add(const Tile8& t, uint32_t v) {
+    v += t.shfl_xor(v, 1); v += t.shfl_xor(v, 2); v += t.shfl_xor(v, 4);
+    return v;
+}
+__device__ __forceinline__ void collapse_group(const Tile8& tile, uint32_t bnode, uint32_t wnode, uint32_t* __restrict__ node_src, uint32_t node_capacity, int n,
+                                const int2* __restrict__ children, const float4* __restrict__ box_lo, const float4* __restrict__ box_hi,
+                                float4* __restrict__ nodes, uint32_t* __restrict__ leaf_slot, CollapseCounters* ctr, float root_area,
+                                const float4* __restrict__ dp, uint2* e_list /* this tile's 8 entries in shared memory */) {
+    const uint32_t n_internal = (uint32_t)(n - 1);
+    const int L = (int)tile.thread_rank();
+    float4 plo = __ldg(box_lo + bnode), phi = __ldg(box_hi + bnode);
+
+    // ---- the children: follow the decisions of the refit DP.  A list of (binary node, slot budget) pairs in left-to-right order,
+    // budgets summing to 8, lane i holding entry i; every round expands ALL entries the DP splits (their loads in flight
+    // together) and the list is re-packed through a prefix sum: 3-4 memory round trips per wide node.
+    uint32_t my_node = 0xffffffffu, my_bud = 0u;
+    int c;
+    if (bnode >= n_internal || (__float_as_int(plo.w) & FF_COUNT_MASK) <= FF_LEAF_MAX) {
+        c = 1;   // tiny scene: the whole tree is one leaf child
+        if (L == 0) { my_node = bnode; my_bud = 1u; }
+    } else {
+        const uint32_t k8 = (__float_as_uint(__ldg(&dp[2 * (size_t)bnode + 1].w)) >> 21) & 7u;
+        const int2 c2 = __ldg(children + bnode);
+        c = 2;
+        if (L == 0) { my_node = (uint32_t)c2.x; my_bud = k8; }
+        if (L == 1) { my_node = (uint32_t)c2.y; my_bud = 8u - k8; }
+        for (;;) {
+            uint32_t d = 0u;
+            int2 kid = make_int2(0, 0);
+            if (L < c && my_node < n_internal && my_bud >= 2u) {
+                d = (__float_as_uint(__ldg(&dp[2 * (size_t)my_node + 1].w)) >> (3u * (my_bud - 2u))) & 7u;
+                kid = __ldg(children + my_node);
+            }
+            const bool split = d != 0u && d < my_bud;
+            const uint32_t splits = tile.ballot(split);
+            if (splits == 0u || c + __popc(splits) > 8) break;   // (budgets sum to 8, so the list cannot outgrow the tile)
+            const int pos = L + __popc(splits & ((1u << L) - 1u));   // entries before mine after the re-pack
+            tile.sync();
+            if (L < c) {
+                if (split) { e_list[pos] = make_uint2((uint32_t)kid.x, d); e_list[pos + 1] = make_uint2((uint32_t)kid.y, my_bud - d); }
+                else e_list[pos] = make_uint2(my_node, 1u);   // one slot: a leaf (<= FF_LEAF_MAX triangles) or an inner child; settled
+            }
+            c += __popc(splits);
+            tile.sync();
+            if (L < c) { const uint2 e = e_list[L]; my_node = e.x; my_bud = e.y; }
+        }
+    }
+    const int nch = c;
+    const bool have = L < nch;
+    const uint32_t ch = my_node;
+
+    // ---- my child's box, and its centre relative to the node's
+    float4 cl = make_float4(0.f, 0.f, 0.f, 0.f), chh = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (have) { cl = __ldg(box_lo + ch); chh = __ldg(box_hi + ch); }
+    const int cnt = __float_as_int(cl.w) & FF_COUNT_MASK;
+    const float pcx = 0.5f * (plo.x + phi.x), pcy = 0.5f * (plo.y + phi.y), pcz = 0.5f * (plo.z + phi.z);
+    const float cdx = have ? 0.5f * (cl.x + chh.x) - pcx : 0.f, cdy = have ? 0.5f * (cl.y + chh.y) - pcy : 0.f, cdz = have ? 0.5f * (cl.z + chh.z) - pcz : 0.f;
+
+    // ---- slot assignment: greedy maximisation of dot(child centre - node centre, octant direction of the slot); the pair
+    // (child, slot) with the largest value is fixed, ties go to the lowest child and then the lowest slot; repeat.
+    int my_slot = -1;
+    uint32_t used = 0u;
+    for (int it = 0; it < nch; ++it) {
+        float bestc = -FLT_MAX;
+        int bs = -1;
+        if (have && my_slot < 0) {
+#pragma unroll
+            for (int sl = 0; sl < 8; ++sl) {
+                if (used & (1u << sl)) continue;
+                const float v = ((sl & 4) ? cdx : -cdx) + ((sl & 2) ? cdy : -cdy) + ((sl & 1) ? cdz : -cdz);
+                if (v > bestc) { bestc = v; bs = sl; }
+            }
+        }
+        // arg max over the lanes: larger value wins, equal values go to the lower lane
+        float wc = bestc;
+        int wk = bs >= 0 ? L : 8, ws = bs;
+#pragma unroll
+        for (int off = 1; off < 8; off <<= 1) {
+            const float oc = tile.shfl_xor(wc, off);
+            const int ok = tile.shfl_xor(wk, off), os = tile.shfl_xor(ws, off);
+            if (ok < 8 && (wk >= 8 || oc > wc || (oc == wc && ok < wk))) { wc = oc; wk = ok; ws = os; }
+        }
+        if (wk >= 8) {   // NaN costs everywhere: first unassigned child, first free slot
+            const uint32_t un = tile.ballot(have && my_slot < 0);
+            wk = __ffs(un) - 1;
+            ws = __ffs(~used & 0xffu) - 1;
+        }
+        if (L == wk) my_slot = ws;
+        used |= 1u << ws;
+    }
+
+    // ---- classify, allocate
+    const bool inner = have && ch < n_internal && cnt > FF_LEAF_MAX;
+    const bool leaf = have && !inner;
+    const uint32_t imask = tile_or(tile, inner ? 1u << my_slot : 0u);
+    const uint32_t n_inner = __popc(imask);
+    const uint32_t n_leaf_tris = tile_add(tile, leaf ? (uint32_t)cnt : 0u);
+    // One atomicAdd per counter and WARP (a scan over the first lanes of the tiles that arrive together): per wide node the
+    // three counters of a 20 M-triangle build took 8.4 M same-address atomics, which the L2 serialises.
+    uint32_t child_base = 0, tri_base = 0;
+    if (L == 0) {
+        cg::coalesced_group g = cg::coalesced_threads();
+        const uint32_t pre_n = cg::exclusive_scan(g, n_inner), pre_t = cg::exclusive_scan(g, n_leaf_tris);
+        const unsigned last = g.size() - 1;
+        const uint32_t tot_n = g.shfl(pre_n + n_inner, last), tot_t = g.shfl(pre_t + n_leaf_tris, last);
+        uint32_t bn = 0, bt = 0;
+        if (g.thread_rank() == 0) {
+            if (tot_n) bn = atomicAdd(&ctr->node_count, tot_n);
+            if (tot_t) bt = atomicAdd(&ctr->tri_count, tot_t);
+        }
+        bn = g.shfl(bn, 0); bt = g.shfl(bt, 0);
+        if (n_inner) child_base = bn + pre_n;
+        if (n_leaf_tris) tri_base = bt + pre_t;
+    }
+    child_base = tile.shfl(child_base, 0);
+    tri_base = tile.shfl(tri_base, 0);
+    bool fits = true;
+    if (n_inner) {
+        fits = child_base + n_inner <= node_capacity;
+        if (!fits && L == 0) atomicExch(&ctr->overflow, 1u);   // reported by bvh_build; the children are not queued, nothing is written out of bounds
+    }
+    // children keep slot order in both index spaces: inner children as wide nodes child_base + rank, leaf triangles as
+    // slots tri_base + offset
+    uint32_t tri_off = 0;
+    {
+        const uint32_t mine = have ? ((uint32_t)my_slot | (leaf ? (uint32_t)cnt << 4 : 0u)) : 0xfu;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const uint32_t o = tile.shfl(mine, j);
+            if ((o & 0xfu) < (uint32_t)(my_slot < 0 ? 0 : my_slot)) tri_off += o >> 4;
+        }
+    }
+    if (inner && fits) node_src[child_base + __popc(imask & ((1u << my_slot) - 1u))] = ch;
+
+    // ---- quantisation frame: the node box pushed out by 2^-13 of its extent per side.  The traversal evaluates a plane as
+    // u*A + B with A = 2^15 * scale / d (byte_unit in ff_trace.cuh); the rounding of B moves a plane by at most 2^-16 of
+    // the extent, and floor/ceil against the wider frame keeps every child box inside its quantised box by 8x that.
+    {
+        const float gx = (phi.x - plo.x) * 0x1p-13f, gy = (phi.y - plo.y) * 0x1p-13f, gz = (phi.z - plo.z) * 0x1p-13f;
+        plo.x -= gx; plo.y -= gy; plo.z -= gz;
+        phi.x += gx; phi.y += gy; phi.z += gz;
+    }
+    const uint32_t ebx = exponent_for(phi.x - plo.x), eby = exponent_for(phi.y - plo.y), ebz = exponent_for(phi.z - plo.z);
+    const float sx = __uint_as_float(ebx << 23), sy = __uint_as_float(eby << 23), sz = __uint_as_float(ebz << 23);
+    uint32_t b_meta = 0, b_qlx = 0, b_qly = 0, b_qlz = 0, b_qhx = 0, b_qhy = 0, b_qhz = 0;
+    double sah = 0.0;
+    if (have) {
+        if (inner) b_meta = 0x20u | (24u + (uint32_t)my_slot);
+        else {
+            const uint32_t first = (uint32_t)__float_as_int(chh.w);
+            b_meta = (((1u << cnt) - 1u) << 5) | tri_off;
+            // only the destination is recorded here; gather_tris_kernel moves the 48-byte records afterwards, one thread per triangle
+            for (int t = 0; t < cnt; ++t) leaf_slot[first + t] = tri_base + tri_off + (uint32_t)t;
+            sah = (double)box_area(cl, chh) * cnt;
+        }
+        const float gx = (chh.x - cl.x) * 0x1p-13f + (phi.x - plo.x) * 0x1p-15f, gy = (chh.y - cl.y) * 0x1p-13f + (phi.y - plo.y) * 0x1p-15f,
+                    gz = (chh.z - cl.z) * 0x1p-13f + (phi.z - plo.z) * 0x1p-15f;
+        b_qlx = quant_lo(cl.x - gx, plo.x, sx); b_qly = quant_lo(cl.y - gy, plo.y, sy); b_qlz = quant_lo(cl.z - gz, plo.z, sz);
+        b_qhx = quant_hi(chh.x + gx, plo.x, sx); b_qhy = quant_hi(chh.y + gy, plo.y, sy); b_qhz = quant_hi(chh.z + gz, plo.z, sz);
+    }
+    // bytes of the 8 lanes -> the packed words of the node: word w of an array holds slots 4w .. 4w+3
+    const int sh = have ? 8 * (my_slot & 3) : 0;
+    const bool w0 = have && my_slot < 4, w1 = have && my_slot >= 4;
+#define FF_PACK(b, lo_word, hi_word) const uint32_t lo_word = tile_or(tile, w0 ? (b) << sh : 0u), hi_word = tile_or(tile, w1 ? (b) << sh : 0u)
+    FF_PACK(b_meta, meta0, meta1);
+    FF_PACK(b_qlx, qlx0, qlx1); FF_PACK(b_qly, qly0, qly1); FF_PACK(b_qlz, qlz0, qlz1);
+    FF_PACK(b_qhx, qhx0, qhx1); FF_PACK(b_qhy, qhy0, qhy1); FF_PACK(b_qhz, qhz0, qhz1);
+#undef FF_PACK
+    float4* out = nodes + FF_NODE_F4 * (size_t)wnode;
+    const uint32_t xb = FF_NODE_EXP_BIAS;  // the node stores the exponents of 2^15 * scale
+    if (L == 0) out[0] = make_float4(plo.x, plo.y, plo.z, __uint_as_float((ebx + xb) | ((eby + xb) << 8) | ((ebz + xb) << 16) | (imask << 24)));
+    if (L == 1) out[1] = make_float4(__uint_as_float(child_base), __uint_as_float(tri_base), __uint_as_float(meta0), __uint_as_float(meta1));
+#if FF_NODE_256
+    if (L == 2) out[2] = make_float4(__uint_as_float(qlx0), __uint_as_float(qlx1), __uint_as_float(qly0), __uint_as_float(qly1));
+    if (L == 3) out[3] = make_float4(__uint_as_float(qlz0), __uint_as_float(qlz1), 0.f, 0.f);
+    if (L == 4) out[4] = make_float4(__uint_as_float(qhx0), __uint_as_float(qhx1), __uint_as_float(qhy0), __uint_as_float(qhy1));
+    if (L == 5) out[5] = make_float4(__uint_as_float(qhz0), __uint_as_float(qhz1), 0.f, 0.f);
+#else
+    if (L == 2) out[2] = make_float4(__uint_as_float(qlx0), __uint_as_float(qlx1), __uint_as_float(qly0), __uint_as_float(qly1));
+    if (L == 3) out[3] = make_float4(__uint_as_float(qlz0), __uint_as_float(qlz1), __uint_as_float(qhx0), __uint_as_float(qhx1));
+    if (L == 4) out[4] = make_float4(__uint_as_float(qhy0), __uint_as_float(qhy1), __uint_as_float(qhz0), __uint_as_float(qhz1));
+#endif
+    // SAH cost of the wide tree: C_node * area(node) + C_tri * sum(leaf area * count), normalised by the root area
+    if (root_area > 0.f) {
+        double tot = sah;
+        tot += tile.shfl_xor(tot, 1); tot += tile.shfl_xor(tot, 2); tot += tile.shfl_xor(tot, 4);
+        if (L == 0) {
+            cg::coalesced_group g = cg::coalesced_threads();
+            const double sum = cg::reduce(g, ((double)box_area(plo, phi) + tot) / (double)root_area, cg::plus<double>());
+            if (g.thread_rank() == 0) atomicAdd(&ctr->sah, sum);
+        }
+    }
+}
 // Triangles into BVH-leaf order: sorted position p -> slot leaf_slot[p] (written by the collapse).
 __global__ void gather_tris_kernel(const float4* __restrict__ flat_tris, const uint32_t* __restrict__ sorted_idx,
                                    const uint32_t* __restrict__ leaf_slot, uint32_t n, float4* __restrict__ tris_out) {
@@ -889,6 +1125,9 @@ __global__ void gather_tris_kernel(const float4* __restrict__ flat_tris, const u
 // per-level launches cost 24 kernel launches and two host round trips per build whatever the depth -- 0.4 of the 0.93 ms of a
 // 1 M-triangle build (profiles/r02a_launches_bench_summary.json).
 struct GridBarrier { uint32_t arrived; uint32_t generation; };
+#ifndef FF_COLLAPSE_TILE_LEVEL
+#define FF_COLLAPSE_TILE_LEVEL 16384u   // levels of at most this many wide nodes are collapsed by 8-lane tiles, larger ones by one thread per node
+#endif
 __global__ void __launch_bounds__(128) collapse_persistent_kernel(uint32_t* __restrict__ node_src, uint32_t node_capacity, int n,
                                 const int2* __restrict__ children, const float4* __restrict__ box_lo, const float4* __restrict__ box_hi,
                                 const float4* __restrict__ flat_tris, const uint32_t* __restrict__ sorted_idx,
@@ -899,6 +1138,9 @@ __global__ void __launch_bounds__(128) collapse_persistent_kernel(uint32_t* __re
     const float root_area = box_area(rl, rh);
     __shared__ uint32_t s_range[2];
     __shared__ uint32_t e_node[2][8][128], e_bud[2][8][128];
+    uint2 (*e_lists)[8] = reinterpret_cast<uint2 (*)[8]>(&e_node[0][0][0]);   // the tile version's lists alias the thread version's
+    const Tile8 tile = cg::tiled_partition<8>(cg::this_thread_block());
+    const uint32_t tile_in_block = threadIdx.x >> 3, tiles_per_block = blockDim.x >> 3;
     for (uint32_t gen = 0;; ++gen) {
         if (threadIdx.x == 0) {
             s_range[0] = *(volatile uint32_t*)&ctr->level_begin;
@@ -907,9 +1149,15 @@ __global__ void __launch_bounds__(128) collapse_persistent_kernel(uint32_t* __re
         __syncthreads();
         const uint32_t begin = s_range[0], end = s_range[1];
         if (begin == end) return;   // uniform over the grid: every CTA reads the range the barrier published
-        for (uint32_t w = begin + blockIdx.x * blockDim.x + threadIdx.x; w < end; w += gridDim.x * blockDim.x)
-            collapse_one(__ldcg(node_src + w), w, node_src, node_capacity, n, children, box_lo, box_hi, flat_tris, sorted_idx, nodes, tris_out, leaf_slot,
-                         ctr, root_area, dp, e_node, e_bud);
+        if (end - begin <= FF_COLLAPSE_TILE_LEVEL) {   // a small level: latency matters, eight lanes per node
+            for (uint32_t w = begin + blockIdx.x * tiles_per_block + tile_in_block; w < end; w += gridDim.x * tiles_per_block)
+                collapse_group(tile, __ldcg(node_src + w), w, node_src, node_capacity, n, children, box_lo, box_hi, nodes, leaf_slot, ctr, root_area, dp,
+                               e_lists[tile_in_block]);
+        } else {
+            for (uint32_t w = begin + blockIdx.x * blockDim.x + threadIdx.x; w < end; w += gridDim.x * blockDim.x)
+                collapse_one(__ldcg(node_src + w), w, node_src, node_capacity, n, children, box_lo, box_hi, flat_tris, sorted_idx, nodes, tris_out, leaf_slot,
+                             ctr, root_area, dp, e_node, e_bud);
+        }
         // ---- grid barrier; the last arrival advances the level
         __syncthreads();
         if (threadIdx.x == 0) {
@@ -942,7 +1190,7 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
                       uint32_t node_capacity, int2* d_bvh2_children, float4* d_bvh2_lo, float4* d_bvh2_hi,
                       uint32_t* d_bvh2_leaf_slot, float bounds_lo[3], float bounds_hi[3], BuildOut* out, uint32_t* launches,
                       Arena& arena, cudaStream_t st) {
-    out->n_nodes = 0; out->depth = 0; out->sah_cost = 0;
+    out->n_nodes = 0; out->depth = 0; out->sah_cost = 0; out->morton_bits = 0;
     for (int k = 0; k < 3; ++k) { bounds_lo[k] = 0; bounds_hi[k] = 0; }
     if (n == 0) return cudaSuccess;
     // FF_BUILD_TRACE=1: per-stage wall times on stderr (synchronises after every stage; development aid)
@@ -955,11 +1203,17 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
         fprintf(stderr, "[ff build] %-28s %9.3f ms\n", what, std::chrono::duration<double, std::milli>(now - t_last).count());
         t_last = now;
     };
-    // 63-bit Morton keys above 2^20 triangles (FF_MORTON_BITS=30 / 63 forces one or the other: development knob)
+    // Morton keys: 30 bits (u32, 4 sort passes) unless that grid does not resolve the scene.  Above 2^20 triangles the build
+    // sorts with 30-bit keys first, counts the sorted keys that repeat their predecessor and, if more than 1/16 of them do,
+    // redoes codes + sort with 63-bit keys (u64, 8 passes): inside a cell the hierarchy can only fall back to the input
+    // order.  A uniform 20 M-triangle soup has 2 % duplicates on the 1024^3 grid and gains nothing from the wide keys
+    // (35.9108 vs 35.9107 nodes per ray, 9.3 vs 7.7 ms build: profiles/r02f, r02g); a scene whose triangles sit in a small
+    // part of its bounding box does.  FF_MORTON_BITS=30 / 63 forces one or the other (development knob).
     const char* mb_env = getenv("FF_MORTON_BITS");
-    const bool wide_keys = mb_env ? atoi(mb_env) > 32 : n > (1u << 20);
-    const size_t key_bytes = wide_keys ? sizeof(uint64_t) : sizeof(uint32_t);
-    const size_t sort_words = wide_keys ? sort_scratch_words<uint64_t>(n) : sort_scratch_words<uint32_t>(n);
+    const bool may_widen = mb_env ? atoi(mb_env) > 32 : n > (1u << 20);
+    bool wide_keys = mb_env ? atoi(mb_env) > 32 : false;
+    const size_t key_bytes = may_widen ? sizeof(uint64_t) : sizeof(uint32_t);
+    const size_t sort_words = may_widen ? sort_scratch_words<uint64_t>(n) : sort_scratch_words<uint32_t>(n);
     int* d_bounds = nullptr;
     void *d_keys_a = nullptr, *d_keys_b = nullptr;
     uint32_t *d_vals_a = nullptr, *d_vals_b = nullptr, *d_hist = nullptr;
@@ -990,13 +1244,29 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
 
     bounds_init_kernel<<<1, 32, 0, st>>>(d_bounds);
     bounds_kernel<<<grid_for(n, 256, sm_count() * 8), 256, 0, st>>>(d_flat_tris, n, d_bounds);
-    if (wide_keys) morton_kernel<uint64_t><<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(d_flat_tris, n, d_bounds, (uint64_t*)d_keys_a, d_vals_a);
-    else morton_kernel<uint32_t><<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(d_flat_tris, n, d_bounds, (uint32_t*)d_keys_a, d_vals_a);
-    *launches += 3;
-    mark("bounds + morton");
-    if (wide_keys) CK(radix_sort_pairs<uint64_t>((uint64_t*)d_keys_a, d_vals_a, (uint64_t*)d_keys_b, d_vals_b, n, d_hist, launches, st));
-    else CK(radix_sort_pairs<uint32_t>((uint32_t*)d_keys_a, d_vals_a, (uint32_t*)d_keys_b, d_vals_b, n, d_hist, launches, st));
-    mark("radix sort");
+    mark("bounds");
+    *launches += 2;
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        if (wide_keys) {
+            morton_kernel<uint64_t><<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(d_flat_tris, n, d_bounds, (uint64_t*)d_keys_a, d_vals_a);
+            CK(radix_sort_pairs<uint64_t>((uint64_t*)d_keys_a, d_vals_a, (uint64_t*)d_keys_b, d_vals_b, n, d_hist, launches, st));
+        } else {
+            morton_kernel<uint32_t><<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(d_flat_tris, n, d_bounds, (uint32_t*)d_keys_a, d_vals_a);
+            CK(radix_sort_pairs<uint32_t>((uint32_t*)d_keys_a, d_vals_a, (uint32_t*)d_keys_b, d_vals_b, n, d_hist, launches, st));
+        }
+        ++*launches;
+        if (wide_keys || !may_widen || mb_env) break;
+        uint32_t dups = 0;
+        CK(cudaMemsetAsync(d_hist, 0, sizeof(uint32_t), st));
+        count_duplicate_keys_kernel<<<grid_for(n, 256, sm_count() * 8), 256, 0, st>>>((const uint32_t*)d_keys_a, n, d_hist);
+        CK(cudaMemcpyAsync(&dups, d_hist, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        ++*launches;
+        if ((uint64_t)dups * 16u <= n) break;
+        wide_keys = true;
+    }
+    out->morton_bits = wide_keys ? 63u : 30u;
+    mark("morton codes + radix sort");
     int h_bounds[12];
     CK(cudaMemcpyAsync(h_bounds, d_bounds, sizeof(h_bounds), cudaMemcpyDeviceToHost, st));
     uint32_t* d_order = d_vals_a;  // position in the binary tree's leaf order -> flat triangle index
@@ -1019,7 +1289,7 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
     const char* nc_env = getenv("FF_NODE_COST");
     const float node_cost = nc_env ? (float)atof(nc_env) : FF_NODE_COST;
     if (builder == FF_BUILDER_LBVH && !getenv("FF_REFIT_GLOBAL")) {
-        const size_t smem = sizeof(float4) * 6 * FF_TREELET + sizeof(uint32_t) * 3 * FF_TREELET + sizeof(int2) * FF_TREELET;
+        const size_t smem = sizeof(float4) * 6 * FF_TREELET + sizeof(uint32_t) * 3 * FF_TREELET + sizeof(int2) * FF_TREELET + sizeof(uint32_t) * (2 * FF_TREELET + 4);
         static bool attr_set[64] = {false};
         int dev = 0;
         cudaGetDevice(&dev);

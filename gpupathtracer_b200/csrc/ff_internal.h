@@ -180,7 +180,7 @@ struct Arena {
 };
 
 struct BuildOut {
-    uint32_t n_nodes, depth;
+    uint32_t n_nodes, depth, morton_bits;
     double sah_cost;
 };
 // Builds into caller-allocated arrays; returns via *out after synchronising `st`.

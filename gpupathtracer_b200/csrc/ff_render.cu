@@ -261,6 +261,15 @@ __global__ void wf_raygen_kernel(CamDev cam, RenderDev rp, float4* __restrict__ 
 #define FF_SHADE_PREFETCH 1  // +0.5 .. 1 %
 #endif
 static_assert(FF_SHADE_BLOCK >= 64 && FF_SHADE_BLOCK <= 512 && (FF_SHADE_BLOCK & (FF_SHADE_BLOCK - 1)) == 0, "two warp groups of warp 0 scan the CTA's warps");
+// Ray-coherence regrouping (north star, subsystem 3): the survivors a CTA appends to the next bounce's queue in one iteration
+// are ordered by the OCTANT of their new direction (match_any inside each warp, one 32-lane scan over the 8 octants x 4 warps
+// of the CTA), so that the extend stage, which hands consecutive queue entries to the lanes of a warp, gets rays that visit
+// the children of a node in the same front-to-back order.  No extra pass and no extra traffic: only the position inside the
+// CTA's block of the queue changes.  Results do not change (radiance is indexed by path id).
+#ifndef FF_SHADE_REGROUP
+#define FF_SHADE_REGROUP 1
+#endif
+static_assert(!FF_SHADE_REGROUP || FF_SHADE_BLOCK == 128, "the octant scan is one warp wide: 8 octants x 4 warps");
 template <bool NEE, bool FIRST>
 __global__ void __launch_bounds__(FF_SHADE_BLOCK) wf_shade_kernel(DevScene sc, CamDev cam, RenderDev rp, int bounce, const uint32_t* __restrict__ count_in,
                                                         uint32_t cap, const HitLite* __restrict__ hits,
@@ -274,6 +283,9 @@ __global__ void __launch_bounds__(FF_SHADE_BLOCK) wf_shade_kernel(DevScene sc, C
     // warp-level atomic the 430 k same-address atomics of a 14 M-path launch were the kernel's top stall (53 % of the warp
     // samples sat on the shuffle that broadcasts the returned base, profiles/r01i_shade_c2_before_details.txt).
     __shared__ uint32_t s_cnt[2][FF_SHADE_BLOCK / 32], s_off[2][FF_SHADE_BLOCK / 32];
+#if FF_SHADE_REGROUP
+    __shared__ uint32_t s_oct[8][FF_SHADE_BLOCK / 32];   // counts, then queue offsets, of (octant, warp)
+#endif
     const uint32_t n = min(*count_in, cap);
     const uint32_t total = ((n + FF_SHADE_BLOCK - 1u) / FF_SHADE_BLOCK) * FF_SHADE_BLOCK;  // uniform trip count per CTA
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -335,6 +347,13 @@ __global__ void __launch_bounds__(FF_SHADE_BLOCK) wf_shade_kernel(DevScene sc, C
         }
         const unsigned m = __ballot_sync(0xffffffffu, alive);
         const unsigned ms = NEE ? __ballot_sync(0xffffffffu, sr.valid) : 0u;
+#if FF_SHADE_REGROUP
+        const uint32_t oct = alive ? ((d.x < 0.f ? 4u : 0u) | (d.y < 0.f ? 2u : 0u) | (d.z < 0.f ? 1u : 0u)) : 8u;
+        const unsigned peers = __match_any_sync(0xffffffffu, oct);   // the lanes of this warp whose ray continues into the same octant
+        if (lane < 8) s_oct[lane][warp] = 0u;
+        __syncwarp();
+        if (alive && lane == __ffs(peers) - 1) s_oct[oct][warp] = (uint32_t)__popc(peers);
+#endif
         if (lane == 0) {
             s_cnt[0][warp] = (uint32_t)__popc(m);
             if (NEE) s_cnt[1][warp] = (uint32_t)__popc(ms);
@@ -342,7 +361,12 @@ __global__ void __launch_bounds__(FF_SHADE_BLOCK) wf_shade_kernel(DevScene sc, C
         __syncthreads();
         if (warp == 0) {  // lanes [0, NW): the next bounce's queue; lanes [NW, 2 NW): the shadow queue
             const int g = lane / NW, j = lane % NW;
-            const uint32_t c = (g == 0 || (NEE && g == 1)) ? s_cnt[g][j] : 0u;
+#if FF_SHADE_REGROUP
+            const bool scan_g = NEE && g == 1;   // the next bounce's queue is laid out by the octant scan below
+#else
+            const bool scan_g = g == 0 || (NEE && g == 1);
+#endif
+            const uint32_t c = scan_g ? s_cnt[g][j] : 0u;
             uint32_t incl = c;
 #pragma unroll
             for (int off = 1; off < NW; off <<= 1) {
@@ -351,13 +375,33 @@ __global__ void __launch_bounds__(FF_SHADE_BLOCK) wf_shade_kernel(DevScene sc, C
             }
             const uint32_t sum = __shfl_sync(0xffffffffu, incl, NW - 1, NW);
             uint32_t base = 0;
-            if (j == 0 && sum != 0u && g < 2) base = atomicAdd(g == 0 ? count_out : shadow_count, sum);
+            if (j == 0 && sum != 0u && scan_g) base = atomicAdd(g == 0 ? count_out : shadow_count, sum);
             base = __shfl_sync(0xffffffffu, base, 0, NW);
-            if (g == 0 || (NEE && g == 1)) s_off[g][j] = base + incl - c;
+            if (scan_g) s_off[g][j] = base + incl - c;
+#if FF_SHADE_REGROUP
+            {   // lane = octant * NW + warp: the CTA's block of the queue is octant-major
+                const uint32_t co = s_oct[lane / NW][lane % NW];
+                uint32_t io = co;
+#pragma unroll
+                for (int off = 1; off < 32; off <<= 1) {
+                    const uint32_t t = __shfl_up_sync(0xffffffffu, io, off);
+                    if (lane >= off) io += t;
+                }
+                const uint32_t total = __shfl_sync(0xffffffffu, io, 31);
+                uint32_t bo = 0;
+                if (lane == 0 && total != 0u) bo = atomicAdd(count_out, total);
+                bo = __shfl_sync(0xffffffffu, bo, 0);
+                s_oct[lane / NW][lane % NW] = bo + io - co;
+            }
+#endif
         }
         __syncthreads();
         if (alive) {
+#if FF_SHADE_REGROUP
+            const uint32_t q = s_oct[oct][warp] + __popc(peers & ((1u << lane) - 1u));
+#else
             const uint32_t q = s_off[0][warp] + __popc(m & ((1u << lane) - 1u));
+#endif
             ray_o_out[q] = make_float4(o.x, o.y, o.z, __uint_as_float(path));
             ray_d_out[q] = make_float4(d.x, d.y, d.z, __uint_as_float(from));
             beta_out[q] = make_float4(beta.x, beta.y, beta.z, specular ? 1.0f : 0.0f);

@@ -111,6 +111,9 @@ typedef struct ff_scene_info {
     float bounds_lo[3], bounds_hi[3];
     double build_ms;         /* device time of the last commit (sort + hierarchy + refit + collapse) */
     double sah_cost;         /* SAH cost of the wide hierarchy, for comparing builders */
+    uint32_t morton_bits;    /* width of the Morton keys the last commit sorted: 30, or 63 when the 30-bit grid left more than
+                              * 1/16 of a large scene's triangles sharing a cell with their neighbour; 0 without triangles */
+    uint32_t reserved;
 } ff_scene_info;
 
 const char* ff_last_error(void);
@@ -228,6 +231,11 @@ int ff_render(ff_scene* scene, const ff_camera* cam, const ff_render_params* par
               void* out_rgba_device, ff_stats* stats);
 int ff_render_u8(ff_scene* scene, const ff_camera* cam, const ff_render_params* params,
                  unsigned char* out_rgb, int out_is_device, ff_stats* stats);
+/*    With FF_INTEGRATOR_AS_CODED the frame is the reference's own (kernel.cu:178-216), quirks included: the colour is
+ *    |inverse(transpose(M)) * n| for the OBJECT-space unit normal n of the hit triangle, not re-normalised (a mesh scaled by s
+ *    is 1/s as bright, kernel.cu:117), and make_uchar3 converts with cvt.rzi.u32.f32 + an 8-bit store, so a component above
+ *    255 wraps modulo 256 (kernel.cu:214).  Byte-identical to the reference's frame wherever the same primitive is hit
+ *    (tests/golden/ref_main.npz, ref_scaled.npz).  With the path-tracing integrators the radiance is clamped to [0, 1]. */
 /* Multi-GPU building blocks: add this call's samples (as SUMS, not means) into a caller-owned
  * device accumulator of W*H float4 (zero it first with ff_device_memset), then after the
  * framebuffer reduce, divide by the total sample count. */

@@ -333,3 +333,41 @@ def test_sah_builder_config_scenes_vs_oracle(ff, ctx, orc, meshes, cfg):
     assert_hits_equal(sc.trace_closest(rays), osc.intersect(rays, mode=1), "sah " + cfg)
     want, _ = osc.render(desc["camera"], 2, 3, seed=3)
     assert (bits(sc.render(cam, 2, 3, seed=3)) == bits(want)).all()
+
+
+@pytest.mark.gpu
+def test_clustered_scene_switches_to_63_bit_morton_keys(ff, ctx, monkeypatch):
+    """A large scene whose triangles occupy a tiny part of its bounding box: on the 30-bit Morton grid nearly every triangle
+    shares a cell with its neighbour, so the builder redoes codes + sort with 63-bit keys (ff_scene_info.morton_bits).  The
+    hierarchy stays exact (BVH == brute force, bit for bit) and visits far fewer nodes than the one built from 30-bit keys."""
+    rng = np.random.default_rng(63)
+    n = (1 << 20) + 5000
+    c = rng.random((n, 1, 3), dtype=np.float32) * np.float32(0.5)   # (triangles much smaller than this fall under the reference's det < 1e-6 rule)
+    tris = (c + np.float32(5e-3) * (rng.random((n, 3, 3), dtype=np.float32) * 2 - 1)).reshape(n, 9).astype(np.float32)
+    tris[-1] = np.array([900, 900, 900, 901, 900, 900, 900, 901, 900], np.float32)   # one far triangle stretches the bounds
+    o = (rng.random((4096, 3), dtype=np.float32) * np.float32(0.5)).astype(np.float32)
+    d = rng.normal(size=(4096, 3)).astype(np.float32)
+    rays = np.concatenate([o, d], 1)
+    sc = ctx.scene()
+    sc.add_triangles(tris)
+    sc.commit(ff.BUILDER_LBVH)
+    assert sc.info()["morton_bits"] == 63
+    got, st = sc.trace_closest(rays, mode=ff.TRACE_BVH8 | ff.TRACE_COUNT, want_stats=True)
+    want = sc.trace_closest(rays, mode=ff.TRACE_BRUTE)
+    assert (got["geom"] == want["geom"]).all() and (got["tri"] == want["tri"]).all() and (bits(got["t"]) == bits(want["t"])).all()
+    assert got["hit"].sum() > 1000
+    monkeypatch.setenv("FF_MORTON_BITS", "30")
+    sc.commit(ff.BUILDER_LBVH)
+    assert sc.info()["morton_bits"] == 30
+    got30, st30 = sc.trace_closest(rays, mode=ff.TRACE_BVH8 | ff.TRACE_COUNT, want_stats=True)
+    assert (got30["tri"] == want["tri"]).all() and (bits(got30["t"]) == bits(want["t"])).all()
+    assert st["nodes_visited"] * 2 < st30["nodes_visited"], (st["nodes_visited"], st30["nodes_visited"])
+    monkeypatch.delenv("FF_MORTON_BITS")
+    # a uniform soup of the same size keeps the 30-bit keys: its duplicates are a few per cent
+    soup = ctx.make_soup(n)
+    sc2 = ctx.scene()
+    sc2.add_triangles(soup)
+    sc2.commit(ff.BUILDER_LBVH)
+    assert sc2.info()["morton_bits"] == 30
+    sc.close()
+    sc2.close()

@@ -266,8 +266,12 @@ static_assert(FF_SHADE_BLOCK >= 64 && FF_SHADE_BLOCK <= 512 && (FF_SHADE_BLOCK &
 // of the CTA), so that the extend stage, which hands consecutive queue entries to the lanes of a warp, gets rays that visit
 // the children of a node in the same front-to-back order.  No extra pass and no extra traffic: only the position inside the
 // CTA's block of the queue changes.  Results do not change (radiance is indexed by path id).
+// Measured on BOUNCE rays (profiles/r02k_variants_regroup.txt): C2 frame 49.03 -> 49.20 ms, C3 5.72 -> 5.73 ms, batch B of
+// the 1 M soup 1883 -> 1903 Mrays/s: no gain -- these frames are bound by instruction issue with lanes idling in the
+// node / triangle phase imbalance, not by the order in which lanes walk a node's children -- so the stage is compiled
+// out by default (round 1 had measured +1.5 % on the uniform batch with a full host-side sort).
 #ifndef FF_SHADE_REGROUP
-#define FF_SHADE_REGROUP 1
+#define FF_SHADE_REGROUP 0
 #endif
 static_assert(!FF_SHADE_REGROUP || FF_SHADE_BLOCK == 128, "the octant scan is one warp wide: 8 octants x 4 warps");
 template <bool NEE, bool FIRST>

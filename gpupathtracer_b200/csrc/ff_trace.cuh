@@ -171,7 +171,7 @@ struct RayCtx {
 // A ray the integrators spawn at P + n*eps (or P - n*eps under glass) cannot hit the triangle it starts on: it leaves the
 // triangle's plane (reflection, diffuse bounce: d.n > 0, t < 0) or looks at its back face (refraction: culled).  The
 // integrators pass that triangle's slot in ray_d.w (as slot + 1; 0 = none, which is what every API ray carries) and the
-// SKIP instantiations of the traversal drop it from the leaf masks instead of running a test whose answer is known (C2: 6.5 ->
+// SKIP instantiations of the traversal drop it from the leaf mask of the node visit that finds it instead of running a test whose answer is known (C2: 6.5 ->
 // 5.7 triangle tests per ray).  The API entry points (ff_trace_closest*) run the plain instantiation: every triangle tested.
 __device__ __forceinline__ uint32_t skip_from_bits(float w) { return __float_as_uint(w) - 1u; }
 __device__ __forceinline__ RayCtx make_ray_ctx(V3 o, V3 dn, uint32_t skip = 0xffffffffu) {

@@ -49,6 +49,7 @@ MAT_EMITTER, MAT_DIFFUSE, MAT_MIRROR, MAT_GLASS = 0, 1, 2, 3
 SPLIT_SAMPLES, SPLIT_TILES = 0, 1
 REDUCE_NCCL, REDUCE_PEER = 0, 1
 GROUP_ID_BYTES = 128
+HITS_UNPACK_STATIC_MAX = 1 << 20   # FF_HITS_UNPACK_STATIC_MAX
 
 
 class FireflyError(RuntimeError):
@@ -137,6 +138,7 @@ def _bind(lib):
     lib.ff_trace_closest_device.argtypes = [_vp, _vp, _sz, C.c_int, _vp, C.POINTER(CStats)]
     lib.ff_trace_any.argtypes = [_vp, _vp, _vp, _sz, C.c_int, _vp, C.POINTER(CStats)]
     lib.ff_hits_unpack.argtypes = [_vp, _vp, _sz, _vp, _vp, _vp]
+    lib.ff_hits_unpack_static.argtypes = [_vp, _vp, _sz, _vp, _vp, _vp]
     lib.ff_camera_rays.argtypes = [_vp, C.POINTER(CCamera), _vp, _vp]
     lib.ff_camera_basis.argtypes = [C.POINTER(CCamera), _vp, _vp, _vp]
     lib.ff_camera_inverse_matrices.argtypes = [C.POINTER(CCamera), _vp, _vp]
@@ -580,6 +582,12 @@ class Scene:
     def hits_unpack(self, d_hits, n):
         geom, tri, t = np.empty(n, np.int32), np.empty(n, np.int32), np.empty(n, np.float32)
         _check(lib.ff_hits_unpack(self.h, d_hits.ptr, int(n), _p(geom), _p(tri), _p(t)))
+        return dict(hit=(geom >= 0).astype(np.uint8), geom=geom, tri=tri, t=t)
+
+    def hits_unpack_static(self, d_hits, n):
+        """hits_unpack through ff_hits_unpack_static: no device allocation, at most HITS_UNPACK_STATIC_MAX records."""
+        geom, tri, t = np.empty(n, np.int32), np.empty(n, np.int32), np.empty(n, np.float32)
+        _check(lib.ff_hits_unpack_static(self.h, d_hits.ptr, int(n), _p(geom), _p(tri), _p(t)))
         return dict(hit=(geom >= 0).astype(np.uint8), geom=geom, tri=tri, t=t)
 
     def trace_any(self, rays, tmax=None, mode=TRACE_BVH8):

@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libfirefly_b200.so")
-SOURCES = ["ff_trace.cu", "ff_bvh.cu", "ff_sah.cu", "ff_render.cu", "ff_api.cpp", "ff_group.cpp", "ff_io.cpp", "ff_obj.cpp", "ff_scenefile.cpp"]
+SOURCES = ["ff_trace.cu", "ff_bvh.cu", "ff_sah.cu", "ff_render.cu", "ff_static.cu", "ff_api.cpp", "ff_group.cpp", "ff_io.cpp", "ff_obj.cpp", "ff_scenefile.cpp"]
 CLI = os.path.join(HERE, "firefly_cli")   # headless front end, links against the C ABI only
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]

@@ -216,6 +216,15 @@ int ff_trace_any(ff_scene* scene, const float* rays6, const float* tmax, size_t 
 int ff_trace_closest_uv(ff_scene* scene, const float* rays6, size_t n, int mode, int* out_geom, int* out_tri,
                         float* out_t, float* out_u, float* out_v, ff_stats* stats);
 int ff_hits_unpack(ff_scene* scene, const void* d_hits, size_t n, int* out_geom, int* out_tri, float* out_t);
+/* ff_hits_unpack without allocation.  No counterpart in the reference: added for
+ * callers that may not call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same
+ * arguments, same outputs bit for bit; the three device temporaries ff_hits_unpack allocates per call live instead in a
+ * static device array of FF_HITS_UNPACK_STATIC_MAX records (12 bytes each = 12 MiB, held by every GPU that loads the
+ * library until the process exits).  Calls no cudaMalloc / cudaFree / allocating routine.  n above the maximum is
+ * FF_ERR_INVALID (split the batch, or use ff_hits_unpack).  Every call on a device shares the array: calls that overlap
+ * on one GPU (two host threads, two contexts of one device) race -- serialise them.  Synchronous like ff_hits_unpack. */
+#define FF_HITS_UNPACK_STATIC_MAX (1u << 20)
+int ff_hits_unpack_static(ff_scene* scene, const void* d_hits, size_t n, int* out_geom, int* out_tri, float* out_t);
 
 /* -- camera rays exactly as generateRays builds them (kernel.cu:198-205), host or device output. */
 int ff_camera_rays(ff_context* ctx, const ff_camera* cam, float* rays6_host, void* d_rays);

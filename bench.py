@@ -441,7 +441,7 @@ def run_gpu_one(args):
         bvh=dict(builder="lbvh", build_ms=builds["lbvh"]["build_ms"], nodes=info["n_nodes"], depth=info["depth"], builders=builds),
         hit_id_mismatches=mism, roofline=roofline, cpu_baseline=cpu,
         e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=n * 24, d2h_bytes_per_step=n * 12, ms_per_step=1e3 * e_secs / args.steps,
-                 trace_ms_per_step=e_trace_ms / args.steps, call="ff_trace_closest: page-locked host rays6 in, geometry / triangle ids + t out, pipelined in 1 Mi-ray chunks"),
+                 trace_ms_per_step=e_trace_ms / args.steps, call="ff_trace_closest: page-locked host rays6 in, geometry / triangle ids + t out; one persistent launch consumes the rays as the copy engine lands them and hands finished chunks to the copy-out stream"),
         batch_b=batch_b, primary_coherent=primary, sah_tree_batch_a=sah_a,
         gpu_launches=launches + e_launches, clocks=clocks)
 

@@ -103,6 +103,8 @@ void ff_context_destroy(ff_context* ctx) {
         for (int k = 0; k < FF_PIPE_SLOTS; ++k) { cudaFree(tp.block[k]); cudaEventDestroy(tp.in_done[k]); cudaEventDestroy(tp.comp_done[k]); cudaEventDestroy(tp.out_done[k]); }
         for (int k = 0; k < 5; ++k) cudaEventDestroy(tp.span[k]);
         cudaFree(tp.work);
+        cudaFree(tp.sblock); cudaFree(tp.d_sync); cudaFreeHost(tp.h_flags); cudaFreeHost(tp.h_marks);
+        if (tp.s_go) cudaEventDestroy(tp.s_go);
         cudaStreamDestroy(tp.s_in); cudaStreamDestroy(tp.s_out); cudaStreamDestroy(tp.s_comp);
     }
     ctx->arena.release();
@@ -672,6 +674,10 @@ static int ensure_pipe(ff_context* c, size_t chunk) {
         }
         for (int k = 0; k < 5; ++k) FF_CUDA(cudaEventCreate(&tp.span[k]));
         FF_CUDA(cudaMalloc((void**)&tp.work, sizeof(uint32_t) * FF_PIPE_SLOTS));
+        FF_CUDA(cudaMalloc((void**)&tp.d_sync, sizeof(StreamSync)));
+        FF_CUDA(cudaHostAlloc((void**)&tp.h_flags, sizeof(uint32_t) * (FF_STREAM_MAX_CHUNKS + 1), cudaHostAllocPortable | cudaHostAllocMapped));
+        FF_CUDA(cudaHostAlloc((void**)&tp.h_marks, sizeof(uint32_t) * (FF_STREAM_MAX_CHUNKS + 8), cudaHostAllocPortable));
+        FF_CUDA(cudaEventCreateWithFlags(&tp.s_go, cudaEventDisableTiming));
         tp.ready = true;
     }
     chunk = (chunk + 3) & ~(size_t)3;  // keeps every sub-array of a slot 16-byte aligned
@@ -683,6 +689,129 @@ static int ensure_pipe(ff_context* c, size_t chunk) {
     }
     return FF_OK;
 }
+// Streaming path of ff_trace_closest: the whole batch (in super-batches of <= kStreamSuper rays) is traced by ONE persistent
+// launch that starts as soon as the first chunk has landed, draws rays as the copy-in stream delivers them and hands finished
+// chunks to the copy-out stream -- so the batch pays for one kernel tail instead of one per chunk (the chunked pipeline below
+// lost ~1.2 ms of an 8.3 M-ray batch to eight tails).  Kernel side: ff_trace.cu "Host batches".
+static const size_t kStreamSuper = (size_t)1 << 24;
+static const size_t kStreamBytesPerRay = 24 + 4 + 4 + 4;
+static const int kStreamFellBack = 1;   // (positive: not an ff_status) the streaming launch timed out, nothing was delivered
+static int trace_closest_stream(ff_scene* scene, const float* rays6, size_t n, int* out_geom, int* out_tri, float* out_t, ff_stats* stats) {
+    ff_context* c = scene->ctx;
+    int rc = ensure_pipe(c, 0);
+    if (rc) return rc;
+    TracePipe& tp = c->pipe;
+    cudaStream_t st = c->stream;
+    static const uint32_t shift_pref = [] {
+        const char* e = getenv("FF_STREAM_CHUNK_SHIFT"); const long v = e ? atol(e) : 0; return (uint32_t)(v >= 12 && v <= 24 ? v : 19); }();
+    const size_t super = std::min(n, kStreamSuper);
+    if (tp.scap < super) {
+        FF_CUDA(cudaStreamSynchronize(st));
+        cudaFree(tp.sblock); tp.sblock = nullptr; tp.scap = 0;
+        const size_t cap = (super + 63) & ~(size_t)63;   // keeps the four sub-arrays 256-byte aligned
+        FF_CUDA(cudaMalloc((void**)&tp.sblock, kStreamBytesPerRay * cap));
+        tp.scap = cap;
+    }
+    float* d6 = (float*)tp.sblock;
+    int* dg = (int*)(tp.sblock + 24 * tp.scap);
+    int* dt = dg + tp.scap;
+    float* dk = (float*)(dt + tp.scap);
+    uint32_t* d_flags = nullptr;
+    FF_CUDA(cudaHostGetDevicePointer((void**)&d_flags, tp.h_flags, 0));
+    while (c->trace_events.size() < 2) { cudaEvent_t e; FF_CUDA(cudaEventCreate(&e)); c->trace_events.push_back(e); }
+    FF_CUDA(cudaEventRecord(tp.span[0], st));
+    double trace_ms = 0, h2d_ms = 0, d2h_ms = 0;
+    uint32_t launches = 0;
+    for (size_t first = 0; first < n; first += kStreamSuper) {
+        const size_t m = std::min(kStreamSuper, n - first);
+        uint32_t shift = shift_pref;
+        while (((m + ((size_t)1 << shift) - 1) >> shift) > FF_STREAM_MAX_CHUNKS) ++shift;
+        const size_t chunk = (size_t)1 << shift, n_chunks = (m + chunk - 1) >> shift;
+        for (size_t k = 0; k < n_chunks; ++k) { tp.h_flags[k] = 0u; tp.h_marks[k] = (uint32_t)std::min(m, (k + 1) << shift); }
+        tp.h_flags[FF_STREAM_MAX_CHUNKS] = 0u;   // raised by a lane that timed out
+        // zero the shared words, then let the copy streams go (a super-batch reuses the staging of the one before it)
+        FF_CUDA(cudaMemsetAsync(tp.d_sync, 0, sizeof(StreamSync), st));
+        FF_CUDA(cudaMemsetAsync(tp.work, 0, sizeof(uint32_t), st));
+        FF_CUDA(cudaEventRecord(tp.s_go, st));
+        FF_CUDA(cudaStreamWaitEvent(tp.s_in, tp.s_go, 0));
+        FF_CUDA(cudaStreamWaitEvent(tp.s_out, tp.s_go, 0));
+        if (first == 0) FF_CUDA(cudaEventRecord(tp.span[2], tp.s_out));
+        auto copy_in = [&](size_t k) -> cudaError_t {
+            const size_t a = k << shift, cnt = std::min(chunk, m - a);
+            cudaError_t e = cudaMemcpyAsync(d6 + 6 * a, rays6 + 6 * (first + a), sizeof(float) * 6 * cnt, cudaMemcpyHostToDevice, tp.s_in);
+            if (e != cudaSuccess) return e;
+            return cudaMemcpyAsync(&tp.d_sync->avail, tp.h_marks + k, sizeof(uint32_t), cudaMemcpyHostToDevice, tp.s_in);
+        };
+        static const bool preload = [] { const char* e = getenv("FF_STREAM_PRELOAD"); return e && atoi(e) != 0; }();
+        if (preload) {   // probe: every ray lands before the launch, so the launch's time is the kernel's own cost without copies in
+            for (size_t k = 0; k < n_chunks; ++k) FF_CUDA(copy_in(k));
+            FF_CUDA(cudaStreamSynchronize(tp.s_in));
+        }
+        // the launch goes first: its latency (and the first warps' spin on `avail`) overlaps the host's queueing of the copies
+        FF_CUDA(cudaEventRecord(c->trace_events[0], st));
+        k_trace_closest_stream(scene->dev, d6, (uint32_t)m, shift, tp.d_sync, d_flags, dg, dt, dk, tp.work, st);
+        FF_CUDA(cudaEventRecord(c->trace_events[1], st));
+        if (!preload) {
+            {   // the first chunk lands in growing pieces (32 Ki, 32 Ki, 64 Ki, ... rays), so the kernel's first warps start after ~20 us of copy
+                const size_t c0 = std::min(chunk, m);
+                size_t a = 0, piece = (size_t)1 << 15;
+                for (int j = 0; a < c0; ++j) {
+                    const size_t cnt = (j == 7 || a + piece > c0) ? c0 - a : piece;
+                    FF_CUDA(cudaMemcpyAsync(d6 + 6 * a, rays6 + 6 * (first + a), sizeof(float) * 6 * cnt, cudaMemcpyHostToDevice, tp.s_in));
+                    a += cnt;
+                    tp.h_marks[FF_STREAM_MAX_CHUNKS + j] = (uint32_t)a;
+                    FF_CUDA(cudaMemcpyAsync(&tp.d_sync->avail, tp.h_marks + FF_STREAM_MAX_CHUNKS + j, sizeof(uint32_t), cudaMemcpyHostToDevice, tp.s_in));
+                    if (j > 0) piece <<= 1;
+                }
+            }
+            for (size_t k = 1; k < n_chunks; ++k) FF_CUDA(copy_in(k));
+        }
+        if (first + m == n) FF_CUDA(cudaEventRecord(tp.span[1], tp.s_in));
+        // hand finished chunks to the copy-out stream in order; the kernel cannot outlive its own time-out, so neither can this loop
+        size_t next = 0;
+        bool kernel_over = false;
+        while (next < n_chunks) {
+            if (*(volatile uint32_t*)(tp.h_flags + next) == 0u) {
+                if (kernel_over) break;   // the kernel ended without completing the chunk: it timed out (err is read below)
+                kernel_over = cudaEventQuery(c->trace_events[1]) != cudaErrorNotReady;
+                if (!kernel_over) (void)cudaGetLastError();   // cudaErrorNotReady is recorded as the thread's last error: clear it
+                continue;                 // (one more look at the flag after the kernel is known to be over)
+            }
+            const size_t a = next << shift, cnt = std::min(chunk, m - a);
+            if (out_geom) FF_CUDA(cudaMemcpyAsync(out_geom + first + a, dg + a, sizeof(int) * cnt, cudaMemcpyDeviceToHost, tp.s_out));
+            if (out_tri) FF_CUDA(cudaMemcpyAsync(out_tri + first + a, dt + a, sizeof(int) * cnt, cudaMemcpyDeviceToHost, tp.s_out));
+            if (out_t) FF_CUDA(cudaMemcpyAsync(out_t + first + a, dk + a, sizeof(float) * cnt, cudaMemcpyDeviceToHost, tp.s_out));
+            ++next;
+        }
+        FF_CUDA(cudaEventRecord(tp.span[3], tp.s_out));
+        FF_CUDA(cudaStreamWaitEvent(st, tp.span[3], 0));   // the context's stream (and an open ff_timer) ends after the last copy
+        FF_CUDA(cudaStreamWaitEvent(st, tp.span[1], 0));
+        FF_CUDA(cudaEventRecord(tp.span[4], st));
+        FF_CUDA(cudaEventSynchronize(tp.span[4]));
+        FF_CUDA(cudaStreamSynchronize(tp.s_in));
+        FF_CUDA(cudaGetLastError());
+        if (tp.h_flags[FF_STREAM_MAX_CHUNKS] || next < n_chunks) {
+            // The kernel gave up waiting for rays: something serialises kernels against copies (a profiler that replays
+            // kernels, CUDA_LAUNCH_BLOCKING).  The caller redoes the batch through the chunked pipeline; after two such
+            // calls the context stops trying.
+            ++tp.stream_failures;
+            return kStreamFellBack;
+        }
+        float ms = 0;
+        cudaEventElapsedTime(&ms, c->trace_events[0], c->trace_events[1]); trace_ms += ms;
+        ++launches;
+    }
+    if (stats) {
+        float ms = 0;
+        cudaEventElapsedTime(&ms, tp.span[0], tp.span[4]); stats->gpu_ms = ms;
+        cudaEventElapsedTime(&ms, tp.span[0], tp.span[1]); h2d_ms = ms;
+        cudaEventElapsedTime(&ms, tp.span[2], tp.span[3]); d2h_ms = ms;
+        stats->h2d_ms = h2d_ms; stats->d2h_ms = d2h_ms; stats->trace_ms = trace_ms; stats->rays = n;
+        stats->passes = launches; stats->kernel_launches = launches;
+    }
+    return FF_OK;
+}
+
 int ff_trace_closest_uv(ff_scene* scene, const float* rays6, size_t n, int mode, int* out_geom, int* out_tri, float* out_t,
                         float* out_u, float* out_v, ff_stats* stats) {
     int rc = check_scene(scene, "ff_trace_closest");
@@ -694,6 +823,12 @@ int ff_trace_closest_uv(ff_scene* scene, const float* rays6, size_t n, int mode,
     FF_REQUIRE(n < 0xffffffffull, "ff_trace_closest: batch too large");
     ff_context* c = scene->ctx;
     if ((rc = ensure_counters(scene))) return rc;
+    static const bool stream_on = [] { const char* e = getenv("FF_TRACE_STREAM"); return !e || atoi(e) != 0; }();
+    if (stream_on && c->pipe.stream_failures < 2 && (mode & 0xff) == FF_TRACE_BVH8 && !(mode & (FF_TRACE_COUNT | FF_TRACE_STATIC)) && !out_u && !out_v) {
+        rc = trace_closest_stream(scene, rays6, n, out_geom, out_tri, out_t, stats);
+        if (rc != kStreamFellBack) return rc;
+        if (stats) memset(stats, 0, sizeof(*stats));
+    }
     // ~1 Mi rays per chunk: large enough that the persistent kernel's tail is a few per cent of a chunk, small enough that
     // the first copy-in and the last copy-out (the only transfers nothing overlaps) are a small part of the call
     static const size_t chunk_pref = [] { const char* e = getenv("FF_TRACE_CHUNK"); const long v = e ? atol(e) : 0; return v > 0 ? (size_t)v : (size_t)1 << 20; }();

@@ -38,6 +38,14 @@ struct TracePipe {
     cudaStream_t s_in = nullptr, s_out = nullptr, s_comp = nullptr;  // copy-in, copy-out, second compute stream
     cudaEvent_t in_done[FF_PIPE_SLOTS], comp_done[FF_PIPE_SLOTS], out_done[FF_PIPE_SLOTS], span[5];
     bool ready = false;
+    // streaming path (one persistent launch per batch, see ff_trace.cu "Host batches"): whole-batch staging
+    char* sblock = nullptr;            // rays6 (24 B) | geom | tri | t (4 B each) per ray
+    size_t scap = 0;                   // rays the block holds
+    ff::StreamSync* d_sync = nullptr;
+    uint32_t* h_flags = nullptr;       // page-locked: chunk c is complete on the device (written by the kernel)
+    uint32_t* h_marks = nullptr;       // page-locked: values the copy-in stream writes into StreamSync::avail
+    cudaEvent_t s_go = nullptr;
+    int stream_failures = 0;           // launches that timed out waiting for rays (kernels serialised against copies); 2 = stop trying
 };
 
 struct ff_context {

@@ -205,6 +205,17 @@ void k_trace_shadow(const DevScene& sc, const float4* d_ray_o, const float4* d_r
 void k_camera_rays(const CamDev& cam, float4* d_ray_o, float4* d_ray_d, cudaStream_t st);
 void k_pack_rays(const float* d_rays6, size_t n, float4* d_ray_o, float4* d_ray_d, cudaStream_t st);
 void k_unpack_rays(const float4* d_ray_o, const float4* d_ray_d, size_t n, float* d_rays6, cudaStream_t st);
+// Host-batch streaming trace (ff_trace.cu, "Host batches"): device words shared by the kernel and the copy streams.
+#define FF_STREAM_MAX_CHUNKS 256
+struct StreamSync {       // zeroed before every launch
+    uint32_t avail;       // rays landed so far (advanced by 4-byte copies on the copy-in stream); alone in its 128-byte line
+    uint32_t pad0[31];
+    uint32_t err;         // a lane timed out waiting for rays
+    uint32_t pad1[31];
+    uint32_t done[FF_STREAM_MAX_CHUNKS];   // finished rays per chunk
+};
+void k_trace_closest_stream(const DevScene& sc, const float* d_rays6, uint32_t n, uint32_t chunk_shift, StreamSync* d_sync, uint32_t* host_flags,
+                            int* d_geom, int* d_tri, float* d_t, uint32_t* d_work_counter, cudaStream_t st);
 void k_unpack_hits(const DevScene& sc, const HitRec* d_hits, size_t n, int* d_geom, int* d_tri, float* d_t,
                    cudaStream_t st);
 void k_make_soup(size_t n, float s, float* d_xyz9, cudaStream_t st);

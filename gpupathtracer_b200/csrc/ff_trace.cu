@@ -45,6 +45,7 @@ __device__ __forceinline__ void store_hit(HitRec* hits, size_t i, const Best& b)
 // (+1.1 ms per C2 frame) than the 32 bytes per path they saved (profiles/r02c_bench.json).
 // `skipbits` = slot + 1 of the triangle the ray starts on (0: none), see make_ray_ctx.
 struct FetchArrays {
+    static constexpr bool kStreams = false;
     const float4* __restrict__ ray_o;
     const float4* __restrict__ ray_d;
     __device__ __forceinline__ void operator()(uint32_t i, V3& o, V3& draw, uint32_t& skipbits) const {
@@ -53,6 +54,7 @@ struct FetchArrays {
     }
 };
 struct FetchPrimary {   // bounce 0 of the wavefront: origin = the camera position, direction from the ray-generation kernel, no self-skip
+    static constexpr bool kStreams = false;
     const float4* __restrict__ ray_d;
     float ox, oy, oz;
     __device__ __forceinline__ void operator()(uint32_t i, V3& o, V3& draw, uint32_t& skipbits) const {
@@ -60,13 +62,118 @@ struct FetchPrimary {   // bounce 0 of the wavefront: origin = the camera positi
     }
 };
 struct StoreRec {
+    static constexpr bool kCompletion = false;
     HitRec* __restrict__ hits;
     __device__ __forceinline__ void operator()(size_t i, const Best& b) const { store_hit(hits, i, b); }
 };
 struct StoreLite {
+    static constexpr bool kCompletion = false;
     HitLite* __restrict__ hits;
     __device__ __forceinline__ void operator()(size_t i, const Best& b) const {
         reinterpret_cast<int2*>(hits)[i] = b.slot < 0 ? make_int2(0, -1) : make_int2(__float_as_int(b.t), b.slot);
+    }
+};
+
+// Host batches (ff_trace_closest): ONE persistent launch traces the batch while the copy engines are still delivering it and
+// already taking results away.  The host queues the rays as chunks of 2^chunk_shift on a copy stream, each followed by a
+// 4-byte copy that advances `avail` (rays landed so far); a lane that draws a ray beyond `avail` waits for it.  Results go out
+// in the reference's numbering (no hit-record pass, no unpack pass), written when the warp next refills; each warp counts
+// the rays it finished and reports them to the chunk's counter when it moves on to another chunk, and the warp that completes
+// a chunk raises its flag in page-locked host memory, on which the host queues the chunk's device-to-host copies.  Nothing here can wait for ever: a lane gives up after kStreamTimeoutNs, sets `err`,
+// and every later wait returns at once (the host then redoes the batch through the chunked pipeline).
+static constexpr unsigned long long kStreamTimeoutNs = 1000000000ull;
+// Neither side of the hand-off may use an ACQUIRE (ld.acquire, fence.acq_rel): on this machine an acquire invalidates the
+// SM's whole L1 (CCTL.IVALL), and one per refill took the node / triangle hit rate with it (the first version of this path
+// traced the C4 batch in 6.7 ms against 5.4 ms device-resident).  None is needed: the rays are read with ld.cg, which does
+// not look at L1, and are requested only after the branch on `avail` has resolved (the copy engine wrote them before it
+// wrote `avail`); results are published with a RELEASE on the counting atomic.
+__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint32_t atom_add_release_gpu(uint32_t* p, uint32_t v) {
+    uint32_t old;
+    asm volatile("atom.add.release.gpu.global.u32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
+    return old;
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+struct FetchRays6Stream {
+    static constexpr bool kStreams = true;
+    const float* __restrict__ rays6;
+    StreamSync* sync;
+    uint32_t* host_err;     // page-locked host word: a lane timed out (the host reads it after the launch, without a copy)
+    // `known` = the lane's last reading of `avail`: one load per lane and chunk, not per ray
+    __device__ __forceinline__ void wait(uint32_t i, uint32_t& known) const {
+        if (i < known) return;
+        const unsigned long long t0 = global_ns();
+        for (;;) {
+            known = ld_relaxed_sys(&sync->avail);
+            if (i < known) return;
+            if (*(volatile uint32_t*)&sync->err) { known = 0xffffffffu; return; }
+            if (global_ns() - t0 > kStreamTimeoutNs) { atomicExch(&sync->err, 1u); *(volatile uint32_t*)host_err = 1u; known = 0xffffffffu; return; }
+            __nanosleep(256);
+        }
+    }
+    __device__ __forceinline__ void operator()(uint32_t i, V3& o, V3& draw, uint32_t& skipbits) const {
+        // written by the copy engine while this kernel runs: read through L2 (.cg), never through the read-only path
+        const float2* p = reinterpret_cast<const float2*>(rays6 + 6 * (size_t)i);
+        const float2 a = __ldcg(p), b = __ldcg(p + 1), c = __ldcg(p + 2);
+        o = ffm::v3(a.x, a.y, b.x); draw = ffm::v3(b.y, c.x, c.y); skipbits = 0u;
+    }
+};
+struct StoreIdsStream {
+    static constexpr bool kCompletion = true;
+    const int* __restrict__ ord_geom;
+    const int* __restrict__ ord_tri;
+    int* __restrict__ geom;
+    int* __restrict__ tri;
+    float* __restrict__ t;
+    StreamSync* sync;
+    uint32_t* host_flags;   // page-locked host memory, one word per chunk
+    uint32_t chunk_shift, n;
+    // Nothing is written when a ray finishes: that happens in the divergent traversal loop, where the two dependent loads of
+    // the reference numbering would stall the whole warp once per ray.  The lane keeps its result in `best` (untouched until it
+    // draws its next ray) and writes it in retire(), at the warp's next refill, together with the other lanes that finished.
+    __device__ __forceinline__ void operator()(size_t, const Best&) const {}
+    // Warp-converged.  `pending` = index of the ray this lane finished since the last call (0xffffffff: none), `best` its result
+    // (== unpack_hits_kernel on store_hit's record).  Finished rays are counted per warp in (acc_chunk, acc_count) and reported
+    // to the chunk's counter -- one release atomic, which is what publishes the warp's result stores -- when the warp first
+    // retires a ray of another chunk, and when it exits.
+    __device__ __forceinline__ void retire(uint32_t& pending, const Best& b, int lane, uint32_t& acc_chunk, uint32_t& acc_count) const {
+        unsigned pend = __ballot_sync(0xffffffffu, pending != 0xffffffffu);
+        if (pend == 0u) return;
+        if (pending != 0xffffffffu) {
+            const bool hit = b.slot >= 0 && b.ord >= 0;
+            geom[pending] = hit ? __ldg(ord_geom + b.ord) : -1;
+            tri[pending] = hit ? __ldg(ord_tri + b.ord) : -1;
+            t[pending] = b.slot < 0 ? INFINITY : b.key;
+        }
+        while (pend) {
+            const int leader = __ffs(pend) - 1;
+            const uint32_t mine = pending >> chunk_shift;
+            const uint32_t c = __shfl_sync(0xffffffffu, mine, leader);
+            const unsigned same = __ballot_sync(0xffffffffu, pending != 0xffffffffu && mine == c);
+            if (c != acc_chunk) { flush(lane, acc_chunk, acc_count); acc_chunk = c; acc_count = 0u; }
+            acc_count += (uint32_t)__popc(same);
+            pend &= ~same;
+        }
+        pending = 0xffffffffu;
+    }
+    __device__ __forceinline__ void flush(int lane, uint32_t c, uint32_t cnt) const {
+        if (cnt == 0u) return;
+        __syncwarp();   // orders every lane's result stores before lane 0's release below (which is cumulative over them)
+        if (lane == 0) {
+            const uint32_t old = atom_add_release_gpu(&sync->done[c], cnt);
+            if (old + cnt == min(1u << chunk_shift, n - (c << chunk_shift))) {
+                __threadfence_system();
+                *(volatile uint32_t*)(host_flags + c) = 1u;
+            }
+        }
     }
 };
 
@@ -114,8 +221,12 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK, FF_TRACE_MINB) trace_closest_p
     uint2 lstack[FF_LOCAL_STACK];
     Best best;
     unsigned cn = 0, ct = 0;
+    uint32_t pending = 0xffffffffu;   // Store::kCompletion: the ray this lane finished and has not reported yet
+    uint32_t avail_known = 0u;        // Fetch::kStreams: rays known to have landed
+    uint32_t acc_chunk = 0u, acc_count = 0u;   // Store::kCompletion: finished rays of chunk acc_chunk this warp has not reported yet
     for (;;) {
         const unsigned need = __ballot_sync(0xffffffffu, !has);
+        if constexpr (Store::kCompletion) { if (need) store.retire(pending, best, lane, acc_chunk, acc_count); }
         if (need && !exhausted) {
             uint32_t base = 0;
             const int leader = __ffs(need) - 1;
@@ -127,6 +238,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK, FF_TRACE_MINB) trace_closest_p
                 if (i < n) {
                     V3 o, draw;
                     uint32_t skipbits;
+                    if constexpr (Fetch::kStreams) fetch.wait(i, avail_known);
                     fetch(i, o, draw, skipbits);
                     const V3 dn = normalize(draw);  // kernel.cu:138
                     best_init(best, INFINITY);
@@ -135,7 +247,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK, FF_TRACE_MINB) trace_closest_p
                     tv.start(best.key);
                     ray_index = i;
                     has = sc.n_nodes != 0;
-                    if (!has) store(i, best);
+                    if (!has) { store(i, best); pending = i; }
                 }
             }
         }
@@ -150,7 +262,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK, FF_TRACE_MINB) trace_closest_p
             bool do_tri = (__popc(tb) >= FF_TRI_MIN) || nb == 0u;
             if (!do_node && !do_tri) do_node = do_tri = true;
             if (has && !bvh8_step<false, false, SKIP>(sc, r, tv, best, my_stack, FF_TRACE_BLOCK, lstack, cn, ct, do_node, do_tri)) {
-                store(ray_index, best);
+                store(ray_index, best); pending = ray_index;
                 has = false;
             }
             const unsigned hb = __ballot_sync(0xffffffffu, has);
@@ -168,7 +280,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK, FF_TRACE_MINB) trace_closest_p
 #else
                 if (!bvh8_step<false, false, SKIP>(sc, r, tv, best, my_stack, FF_TRACE_BLOCK, lstack, cn, ct)) {
 #endif
-                    store(ray_index, best);
+                    store(ray_index, best); pending = ray_index;
                     has = false;
                     break;
                 }
@@ -178,6 +290,8 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK, FF_TRACE_MINB) trace_closest_p
 #endif
         __syncwarp();
     }
+    // rays that finished in the fetch path of the last round (no hierarchy) have not been reported yet; the break is warp-uniform
+    if constexpr (Store::kCompletion) { store.retire(pending, best, lane, acc_chunk, acc_count); store.flush(lane, acc_chunk, acc_count); }
 }
 
 // Brute force: the reference's own algorithm (every ray against every triangle), tiles of triangles staged
@@ -261,6 +375,14 @@ void k_trace_closest(const DevScene& sc, const float4* d_ray_o, const float4* d_
         return;
     }
     launch_closest(sc, FetchArrays{d_ray_o, d_ray_d}, StoreRec{d_hits}, d_count, n_max, mode, d_counters, d_work_counter, st);
+}
+void k_trace_closest_stream(const DevScene& sc, const float* d_rays6, uint32_t n, uint32_t chunk_shift, StreamSync* d_sync, uint32_t* host_flags,
+                            int* d_geom, int* d_tri, float* d_t, uint32_t* d_work_counter, cudaStream_t st) {
+    if (n == 0) return;
+    const FetchRays6Stream fetch{d_rays6, d_sync, host_flags + FF_STREAM_MAX_CHUNKS};
+    const StoreIdsStream store{sc.ord_geom, sc.ord_tri, d_geom, d_tri, d_t, d_sync, host_flags, chunk_shift, n};
+    const int g = grid_for(n, FF_TRACE_BLOCK, sm_count() * tuning().blocks_per_sm);
+    trace_closest_persistent_kernel<false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, fetch, store, nullptr, n, d_work_counter);
 }
 void k_trace_extend(const DevScene& sc, const WaveGen* gen, const float4* d_ray_o, const float4* d_ray_d, const uint32_t* d_count,
                     uint32_t n_max, int mode, HitLite* d_hits, TraceCounters* d_counters, uint32_t* d_work_counter, cudaStream_t st) {

@@ -198,10 +198,16 @@ int ff_scene_get_matrices(const ff_scene* scene, int geometry_index, float model
 #define FF_TRACE_COUNT 0x100 /* OR into `mode`: instrumented kernel, fills nodes_visited / tris_tested */
 int ff_trace_closest(ff_scene* scene, const float* rays6, size_t n, int mode, int* out_geom, int* out_tri,
                      float* out_t, ff_stats* stats);
-/*    Host batches run as a three-stage pipeline over chunks of ~1 Mi rays (copy in | pack + trace + unpack | copy out on
- *    three streams, device staging owned by the context and reused across calls), so with page-locked host buffers
- *    (ff_host_alloc_pinned) the PCIe transfers of one chunk overlap the traversal of its neighbours.  Pageable buffers work
- *    and are simply slower.  stats: gpu_ms = device time from the first copy to the last, trace_ms = traversal kernels only. */
+/*    Host batches are traced by ONE persistent launch that starts before the rays have arrived: the copy-in stream delivers
+ *    them in chunks of 512 Ki rays and advances a device word after each, lanes that draw a ray beyond it wait; results leave
+ *    in the reference's numbering, and a chunk whose rays are all done is handed to the copy-out stream while the launch is
+ *    still running (device staging: 36 bytes per ray, at most 16 Mi rays at a time, owned by the context and reused).  With
+ *    page-locked host buffers (ff_host_alloc_pinned) both PCIe directions overlap the traversal; pageable buffers work and are
+ *    simply slower.  FF_TRACE_COUNT, the other modes and ff_trace_closest_uv use a chunked three-stage pipeline (copy in |
+ *    pack + trace + unpack | copy out, ~1 Mi rays per chunk), and so does a context on which the streaming launch has twice
+ *    timed out waiting for rays (a tool that serialises kernels against copies: a replaying profiler, CUDA_LAUNCH_BLOCKING=1;
+ *    the batch is then redone, nothing is lost).  FF_TRACE_STREAM=0 in the environment selects the chunked pipeline outright.
+ *    stats: gpu_ms = device time from the first copy to the last, trace_ms = traversal launches only. */
 /* Same with device-resident buffers (no copies): d_rays = 2n float4, SoA: n origins {o.xyz, 0} followed by
  * n directions {d.xyz, 0}; d_hits = n 16-byte records {key t (f32), t along the ray (f32), triangle slot
  * (i32), scan-order id (i32)} -- see ff_hits_unpack. */

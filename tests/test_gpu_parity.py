@@ -371,3 +371,34 @@ def test_clustered_scene_switches_to_63_bit_morton_keys(ff, ctx, monkeypatch):
     assert sc2.info()["morton_bits"] == 30
     sc.close()
     sc2.close()
+
+
+def test_host_batches_stream_through_one_launch(ff, ctx):
+    """ff_trace_closest on host rays (the streaming launch: rays consumed while they are still being copied in, finished chunks
+    copied out while it runs) == the device-resident entry point, bit for bit, for batches of several chunks with ragged ends,
+    from page-locked and from pageable memory, on a scene with a hierarchy and on one without (rays finish in the fetch path)."""
+    sc = ctx.scene()
+    sc.add_triangles(ctx.make_soup(40000))
+    sc.add_plane([0, 0, -0.5], [0, 0, 0], [4, 4, 4])
+    sc.commit()
+    empty = ctx.scene()
+    empty.add_plane([0, 0, 0.5], [0, 0, 0], [1, 1, 1])
+    empty.commit()
+    n = (1 << 20) + (1 << 19) + 12345   # three full copy-in chunks (512 Ki rays) and a ragged fourth
+    d_rays, d_hits = ctx.alloc(n * 32), ctx.alloc(n * 16)
+    rays = ctx.make_rays_uniform(0, n, salt=5, device_buffer=d_rays)
+    for scene in (sc, empty):
+        scene.trace_closest_device(d_rays, n, d_hits)
+        want = scene.hits_unpack(d_hits, n)
+        assert 0 < want["hit"].sum() < n
+        got = scene.trace_closest(rays)                       # pageable numpy memory
+        assert_hits_equal(got, want, "host batch (pageable) vs device entry")
+        h_rays = ctx.pinned_array((n, 6), np.float32, key="t_rays")
+        h_rays[:] = rays
+        g, t, k = ctx.pinned_array((n,), np.int32, key="t_g"), ctx.pinned_array((n,), np.int32, key="t_t"), ctx.pinned_array((n,), np.float32, key="t_k")
+        for m in (n, (1 << 19) + 1, (1 << 19), 77):           # chunk boundary + 1, exactly one chunk, tiny
+            g[:], t[:], k[:] = -9, -9, -9.0
+            st = scene.trace_closest_into(h_rays[:m], g[:m], t[:m], k[:m])
+            assert st["rays"] == m
+            assert (g[:m] == want["geom"][:m]).all() and (t[:m] == want["tri"][:m]).all() and (bits(k[:m]) == bits(want["t"][:m])).all()
+            assert (g[m:] == -9).all() and (k[m:] == -9.0).all()   # nothing written past the batch

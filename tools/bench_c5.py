@@ -59,11 +59,12 @@ def main():
             torch.cuda.synchronize()
             dist.barrier()
 
-    # warm-up frame at 1 spp per rank (allocations, NCCL channels)
-    M.render_distributed(sc, cam, world, a.bounces, dist, mode=a.reduce, split="strong", to_host=False, nee=a.nee)
+    # one group for both frames (creating one costs an NCCL communicator); warm-up frame at 1 spp per rank (allocations, NCCL channels)
+    group = M.Group.from_torch(ctx, dist) if dist is not None else M.Group.single(ctx)
+    M.render_distributed(sc, cam, world, a.bounces, dist, mode=a.reduce, split="strong", to_host=False, nee=a.nee, group=group)
     barrier()
     ctx.timer_begin()
-    img, st = M.render_distributed(sc, cam, a.spp, a.bounces, dist, mode=a.reduce, split="strong", to_host=bool(a.out), nee=a.nee)
+    img, st = M.render_distributed(sc, cam, a.spp, a.bounces, dist, mode=a.reduce, split="strong", to_host=bool(a.out), nee=a.nee, group=group)
     barrier()
     ms = ctx.timer_end()
     vals = [ms, st["gpu_ms"], float(st["rays"] + st.get("shadow_rays", 0)), float(st["paths"])]
@@ -86,6 +87,7 @@ def main():
         real_stdout.flush()
         if a.out and img is not None:
             ff.write_image(a.out, img)
+    group.close()
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()

@@ -400,7 +400,7 @@ def run_gpu_one(args):
         try:
             arm = CpuArm(C4_TRIS)
             _, t = arm.intersect(np.ascontiguousarray(h_rays[:256]))
-            n_chk = int(min(65536, max(2048, 2 ** int(np.log2(max(1.0, 256 / t * 20.0))))))  # ~20 s of CPU work, at most 65 536 rays
+            n_chk = int(min(65536, max(2048, int(256 / max(t, 1e-6) * 22.0) // 1024 * 1024)))  # ~22 s of CPU work (multiple of 1024 rays), at most 65 536
             sample = np.ascontiguousarray(h_rays[:n_chk])
             want, t = arm.intersect(sample)
             cpu = dict(value=n_chk / t / 1e6, unit=UNIT, cores=arm.cores, kind=arm.kind, sample=arm.describe(n_chk), seconds=t)

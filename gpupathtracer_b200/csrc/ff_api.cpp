@@ -30,6 +30,7 @@ static void free_scene_device(ff_scene* s) {
     cudaFree(s->d_materials); cudaFree(s->d_planes); cudaFree(s->d_bvh2_children); cudaFree(s->d_bvh2_lo);
     cudaFree(s->d_bvh2_hi); cudaFree(s->d_leaf_slot); cudaFree(s->d_lights); s->d_lights = nullptr;
     cudaFree(s->d_as_coded_normals); s->d_as_coded_normals = nullptr;
+    cudaFree(s->d_bounds); s->d_bounds = nullptr;
     cudaFree(s->d_geom_attr); cudaFree(s->d_attr_normals); cudaFree(s->d_attr_uvs); cudaFree(s->d_attr_facemat);
     s->d_geom_attr = nullptr; s->d_attr_normals = nullptr; s->d_attr_uvs = nullptr; s->d_attr_facemat = nullptr;
     s->d_flat = s->d_tris = s->d_nodes = nullptr; s->d_ord_geom = s->d_ord_tri = nullptr; s->d_materials = nullptr;
@@ -470,7 +471,8 @@ int ff_scene_commit(ff_scene* scene, int builder, double* out_build_ms) {
         FF_CUDA(cudaMalloc((void**)&scene->d_bvh2_lo, sizeof(float4) * 2 * n_tris));
         FF_CUDA(cudaMalloc((void**)&scene->d_bvh2_hi, sizeof(float4) * 2 * n_tris));
         FF_CUDA(cudaMalloc((void**)&scene->d_leaf_slot, sizeof(uint32_t) * n_tris));
-        k_bake_triangles(d_obj, t_models.as<M4>(), t_geom_of.as<uint32_t>(), t_ord_of.as<uint32_t>(), (uint32_t)n_tris, scene->d_flat, st);
+        if (!scene->d_bounds) FF_CUDA(cudaMalloc((void**)&scene->d_bounds, 12 * sizeof(int)));
+        k_bake_triangles(d_obj, t_models.as<M4>(), t_geom_of.as<uint32_t>(), t_ord_of.as<uint32_t>(), (uint32_t)n_tris, scene->d_flat, scene->d_bounds, st);
         FF_CUDA(cudaStreamSynchronize(st));
         t_obj.alloc(0); t_models.alloc(0); t_geom_of.alloc(0); t_ord_of.alloc(0);  // give the staging back before the build
         // the conservative pad needs the scene's largest |coordinate|: take it from the host copies' model-space
@@ -490,7 +492,7 @@ int ff_scene_commit(ff_scene* scene, int builder, double* out_build_ms) {
         FF_CUDA(cudaEventRecord(ctx->ev[0], st));
         cudaError_t be = bvh_build(scene->d_flat, (uint32_t)n_tris, builder, pad, scene->d_tris, scene->d_nodes, node_cap,
                                    scene->d_bvh2_children, scene->d_bvh2_lo, scene->d_bvh2_hi, scene->d_leaf_slot, blo, bhi, &bo,
-                                   &launches, ctx->arena, st);
+                                   &launches, ctx->arena, st, scene->d_bounds);
         if (be != cudaSuccess) { set_error(std::string("bvh_build: ") + cudaGetErrorString(be)); cudaGetLastError(); return FF_ERR_CUDA; }
         FF_CUDA(cudaEventRecord(ctx->ev[1], st));
         FF_CUDA(cudaEventSynchronize(ctx->ev[1]));

@@ -44,8 +44,72 @@ __device__ __forceinline__ V3 xform_point(const M4& m, float x, float y, float z
     r.z = fadd(fadd(fmul(m.c[0].z, x), fmul(m.c[1].z, y)), fadd(fmul(m.c[2].z, z), fmul(m.c[3].z, 1.0f)));
     return r;
 }
+// ------------------------------------------------------------------ bounds
+__device__ __forceinline__ int float_to_ordered(float f) { int i = __float_as_int(f); return i >= 0 ? i : i ^ 0x7fffffff; }
+__host__ __device__ __forceinline__ float ordered_to_float(int i) {
+    int b = i >= 0 ? i : i ^ 0x7fffffff;
+#if defined(__CUDA_ARCH__)
+    return __int_as_float(b);
+#else
+    float f; memcpy(&f, &b, 4); return f;
+#endif
+}
+// bounds[0..2] = scene min, [3..5] = scene max, [6..8] = centroid min, [9..11] = centroid max (ordered ints)
+__global__ void bounds_init_kernel(int* bounds) {
+    if (threadIdx.x < 12) bounds[threadIdx.x] = ((threadIdx.x / 3) & 1) ? float_to_ordered(-FLT_MAX) : float_to_ordered(FLT_MAX);
+}
+// Adds one triangle to a thread's running bounds (scene box and box of the leaf-box centres).
+__device__ __forceinline__ void bounds_add(const float av[3], const float bv[3], const float cv[3], float lo[3], float hi[3], float clo[3], float chi[3]) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float l = fminf(fminf(av[k], bv[k]), cv[k]), h = fmaxf(fmaxf(av[k], bv[k]), cv[k]);
+        const float ce = 0.5f * (l + h);
+        lo[k] = fminf(lo[k], l); hi[k] = fmaxf(hi[k], h);
+        clo[k] = fminf(clo[k], ce); chi[k] = fmaxf(chi[k], ce);
+    }
+}
+// Every thread of the CTA calls this once with its running bounds (blockDim.x <= 256).
+__device__ __forceinline__ void bounds_block_reduce(float lo[3], float hi[3], float clo[3], float chi[3], int* bounds) {
+    // warp shuffle -> shared memory -> warp 0: 12 atomics per CTA.  (One set per WARP was 375 k same-address atomics at 1 M
+    // triangles, which the L2 serialises: 80 of the build's 930 us, profiles/r02a_launches_bench_summary.json.)
+    __shared__ float s_red[12][8];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        for (int off = 16; off; off >>= 1) {
+            lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], off));
+            hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], off));
+            clo[k] = fminf(clo[k], __shfl_xor_sync(0xffffffffu, clo[k], off));
+            chi[k] = fmaxf(chi[k], __shfl_xor_sync(0xffffffffu, chi[k], off));
+        }
+        if (lane == 0) { s_red[k][warp] = lo[k]; s_red[3 + k][warp] = hi[k]; s_red[6 + k][warp] = clo[k]; s_red[9 + k][warp] = chi[k]; }
+    }
+    __syncthreads();
+    if (threadIdx.x < 12) {
+        const int q = threadIdx.x;
+        const bool is_max = ((q / 3) & 1) != 0;
+        float v = s_red[q][0];
+        for (int w = 1; w < (int)(blockDim.x >> 5); ++w) v = is_max ? fmaxf(v, s_red[q][w]) : fminf(v, s_red[q][w]);
+        if (is_max) atomicMax(bounds + q, float_to_ordered(v)); else atomicMin(bounds + q, float_to_ordered(v));
+    }
+}
+__global__ void bounds_kernel(const float4* __restrict__ tris, uint32_t n, int* bounds) {
+    float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    float clo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, chi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float4 a = tris[3 * (size_t)i], b = tris[3 * (size_t)i + 1], c = tris[3 * (size_t)i + 2];
+        const float av[3] = {a.x, a.y, a.z}, bv[3] = {b.x, b.y, b.z}, cv[3] = {c.x, c.y, c.z};
+        bounds_add(av, bv, cv, lo, hi, clo, chi);
+    }
+    bounds_block_reduce(lo, hi, clo, chi, bounds);
+}
+
+// `bounds` (optional): the scene / centroid bounds of bounds_kernel, reduced here while the baked vertices are in registers,
+// so the build that follows does not have to read all triangles once more just for them (146 us at 20 M triangles).
 __global__ void bake_kernel(const float* __restrict__ xyz9, const M4* __restrict__ models, const uint32_t* __restrict__ geom_of,
-                            const uint32_t* __restrict__ ord_of, uint32_t n, float4* __restrict__ out) {
+                            const uint32_t* __restrict__ ord_of, uint32_t n, float4* __restrict__ out, int* bounds) {
+    float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    float clo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, chi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const uint32_t g = geom_of[i];
         const M4 m = models[g];
@@ -54,11 +118,15 @@ __global__ void bake_kernel(const float* __restrict__ xyz9, const M4* __restrict
         out[3 * (size_t)i] = make_float4(a.x, a.y, a.z, __int_as_float((int)ord_of[i]));
         out[3 * (size_t)i + 1] = make_float4(b.x, b.y, b.z, __int_as_float((int)g));
         out[3 * (size_t)i + 2] = make_float4(c.x, c.y, c.z, __int_as_float((int)i));
+        const float av[3] = {a.x, a.y, a.z}, bv[3] = {b.x, b.y, b.z}, cv[3] = {c.x, c.y, c.z};
+        bounds_add(av, bv, cv, lo, hi, clo, chi);
     }
+    if (bounds) bounds_block_reduce(lo, hi, clo, chi, bounds);
 }
 void k_bake_triangles(const float* d_xyz9_obj, const M4* d_model_per_geom, const uint32_t* d_geom_of_flat,
-                      const uint32_t* d_ord_of_flat, uint32_t n, float4* d_flat_tris, cudaStream_t st) {
-    if (n) bake_kernel<<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(d_xyz9_obj, d_model_per_geom, d_geom_of_flat, d_ord_of_flat, n, d_flat_tris);
+                      const uint32_t* d_ord_of_flat, uint32_t n, float4* d_flat_tris, int* d_bounds, cudaStream_t st) {
+    if (d_bounds) bounds_init_kernel<<<1, 32, 0, st>>>(d_bounds);
+    if (n) bake_kernel<<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(d_xyz9_obj, d_model_per_geom, d_geom_of_flat, d_ord_of_flat, n, d_flat_tris, d_bounds);
 }
 
 // As-coded shading normal of every triangle, flat order: inverse(transpose(M)) * vec4(normalize(cross(e1, e2)), 0) with
@@ -82,58 +150,6 @@ __global__ void as_coded_normals_kernel(const float* __restrict__ xyz9, const M4
 void k_as_coded_normals(const float* d_xyz9_obj, const M4* d_nrm_per_geom, const uint32_t* d_geom_of_flat, uint32_t n,
                         float4* d_out, cudaStream_t st) {
     if (n) as_coded_normals_kernel<<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(d_xyz9_obj, d_nrm_per_geom, d_geom_of_flat, n, d_out);
-}
-
-// ------------------------------------------------------------------ bounds
-__device__ __forceinline__ int float_to_ordered(float f) { int i = __float_as_int(f); return i >= 0 ? i : i ^ 0x7fffffff; }
-__host__ __device__ __forceinline__ float ordered_to_float(int i) {
-    int b = i >= 0 ? i : i ^ 0x7fffffff;
-#if defined(__CUDA_ARCH__)
-    return __int_as_float(b);
-#else
-    float f; memcpy(&f, &b, 4); return f;
-#endif
-}
-// bounds[0..2] = scene min, [3..5] = scene max, [6..8] = centroid min, [9..11] = centroid max (ordered ints)
-__global__ void bounds_init_kernel(int* bounds) {
-    if (threadIdx.x < 12) bounds[threadIdx.x] = ((threadIdx.x / 3) & 1) ? float_to_ordered(-FLT_MAX) : float_to_ordered(FLT_MAX);
-}
-__global__ void bounds_kernel(const float4* __restrict__ tris, uint32_t n, int* bounds) {
-    float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
-    float clo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, chi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const float4 a = tris[3 * (size_t)i], b = tris[3 * (size_t)i + 1], c = tris[3 * (size_t)i + 2];
-        const float av[3] = {a.x, a.y, a.z}, bv[3] = {b.x, b.y, b.z}, cv[3] = {c.x, c.y, c.z};
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            const float l = fminf(fminf(av[k], bv[k]), cv[k]), h = fmaxf(fmaxf(av[k], bv[k]), cv[k]);
-            const float ce = 0.5f * (l + h);
-            lo[k] = fminf(lo[k], l); hi[k] = fmaxf(hi[k], h);
-            clo[k] = fminf(clo[k], ce); chi[k] = fmaxf(chi[k], ce);
-        }
-    }
-    // warp shuffle -> shared memory -> warp 0: 12 atomics per CTA.  (One set per WARP was 375 k same-address atomics at 1 M
-    // triangles, which the L2 serialises: 80 of the build's 930 us, profiles/r02a_launches_bench_summary.json.)
-    __shared__ float s_red[12][8];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        for (int off = 16; off; off >>= 1) {
-            lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], off));
-            hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], off));
-            clo[k] = fminf(clo[k], __shfl_xor_sync(0xffffffffu, clo[k], off));
-            chi[k] = fmaxf(chi[k], __shfl_xor_sync(0xffffffffu, chi[k], off));
-        }
-        if (lane == 0) { s_red[k][warp] = lo[k]; s_red[3 + k][warp] = hi[k]; s_red[6 + k][warp] = clo[k]; s_red[9 + k][warp] = chi[k]; }
-    }
-    __syncthreads();
-    if (threadIdx.x < 12) {
-        const int q = threadIdx.x;
-        const bool is_max = ((q / 3) & 1) != 0;
-        float v = s_red[q][0];
-        for (int w = 1; w < (int)(blockDim.x >> 5); ++w) v = is_max ? fmaxf(v, s_red[q][w]) : fminf(v, s_red[q][w]);
-        if (is_max) atomicMax(bounds + q, float_to_ordered(v)); else atomicMin(bounds + q, float_to_ordered(v));
-    }
 }
 
 // ------------------------------------------------------------------ Morton codes of the box centres inside the centroid bounds
@@ -282,7 +298,17 @@ __global__ void __launch_bounds__(OS_THREADS) os_pass_kernel(const KeyT* __restr
     for (int r = 0; r < OS_ITEMS; ++r) {
         const bool live = base + r * 32 + lane < n;
         const uint32_t d = (uint32_t)(key[r] >> shift) & 0xffu;
-        const unsigned peers = __match_any_sync(0xffffffffu, live ? d : 0x100u);
+        // lanes with the same digit, by eight ballots (one per digit bit) instead of MATCH.ANY: the match unit serialises on the
+        // ~30 distinct digits of a warp, and the BREV that consumes its result was 48 % of this kernel's stall samples
+        // (short scoreboard, profiles/r02w_build20m_details.txt)
+        unsigned peers = __ballot_sync(0xffffffffu, live);
+#pragma unroll
+        for (int b = 0; b < 8; ++b) {
+            const bool bit = (d >> b) & 1u;
+            const unsigned m = __ballot_sync(0xffffffffu, bit);
+            peers &= bit ? m : ~m;
+        }
+        if (!live) peers = 1u << lane;
         const int leader = __ffs(peers) - 1;
         uint32_t start = 0;
         if (live && lane == leader) { start = warp_hist[warp][d]; warp_hist[warp][d] = start + __popc(peers); }
@@ -315,12 +341,24 @@ __global__ void __launch_bounds__(OS_THREADS) os_pass_kernel(const KeyT* __restr
         digit_off[d] = off_d;
         uint32_t prefix = 0;
         if (tile != 0) {
+            // four predecessors per round trip (the loads are independent; a tile of the first wave walks back over hundreds)
             for (int t = (int)tile - 1; t >= 0;) {
-                const uint32_t v = *(volatile uint32_t*)(desc + (size_t)t * 256 + d);
-                if ((v & (OS_FLAG_LOCAL | OS_FLAG_PREFIX)) == 0u) { __nanosleep(20); continue; }   // not published yet
-                prefix += v & OS_VALUE_MASK;
-                if (v & OS_FLAG_PREFIX) break;
-                --t;
+                uint32_t v[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) v[j] = t - j >= 0 ? *(volatile uint32_t*)(desc + (size_t)(t - j) * 256 + d) : OS_FLAG_PREFIX;
+                int used = 0;
+                bool done = false;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    if (done || used != j) continue;
+                    if ((v[j] & (OS_FLAG_LOCAL | OS_FLAG_PREFIX)) == 0u) continue;   // not published yet: retry from here
+                    prefix += v[j] & OS_VALUE_MASK;
+                    ++used;
+                    if (v[j] & OS_FLAG_PREFIX) done = true;
+                }
+                if (done) break;
+                if (used == 0) __nanosleep(20);
+                t -= used;
             }
             atomicExch(my, (prefix + count) | OS_FLAG_PREFIX);
         }
@@ -405,7 +443,9 @@ __device__ __forceinline__ int delta(const KeyT* __restrict__ keys, int n, int i
 // the global hand-off protocol.  (An internal node's index always lies inside its own range, so a contained node also has
 // its index inside the block.)
 #ifndef FF_TREELET
-#define FF_TREELET 512
+#ifndef FF_TREELET
+#define FF_TREELET 256   // leaves per block (r02z: 20 M triangles 6.46 / 6.10 / 7.34 ms with 512 / 256 / 1024)
+#endif
 #endif
 #define FF_PARENT_CROSS 0x80000000u
 #define FF_PARENT_ROOT 0xffffffffu
@@ -563,7 +603,8 @@ __global__ void __launch_bounds__(FF_TREELET_THREADS) refit_treelet_kernel(const
                                                                             int n, float pad, const int2* __restrict__ children,
                                                                             const uint32_t* __restrict__ parent, uint32_t* __restrict__ flags,
                                                                             float4* __restrict__ box_lo, float4* __restrict__ box_hi,
-                                                                            float4* __restrict__ dp, float slot_cost, float node_cost) {
+                                                                            float4* __restrict__ dp, float slot_cost, float node_cost,
+                                                                            uint32_t* __restrict__ starters, uint32_t* __restrict__ starter_count) {
     constexpr int S = FF_TREELET, T = FF_TREELET_THREADS;
     extern __shared__ float4 sm4[];
     float4* s_lo = sm4;              // [0, S): internal nodes of the block (index - base), [S, 2S): its leaves
@@ -573,7 +614,8 @@ __global__ void __launch_bounds__(FF_TREELET_THREADS) refit_treelet_kernel(const
     uint32_t* s_parent = s_flag + S;                              // [0, S): parents of the internal nodes, [S, 2S): of the leaves
     int2* s_children = reinterpret_cast<int2*>(s_parent + 2 * S); // children of the internal nodes
     uint32_t (*s_q)[FF_TREELET] = reinterpret_cast<uint32_t (*)[FF_TREELET]>(s_children + S);   // two queues of finished-children nodes
-    uint32_t* s_qn = reinterpret_cast<uint32_t*>(s_q + 2);
+    uint32_t* s_qn = reinterpret_cast<uint32_t*>(s_q + 2);   // [0], [1]: queue lengths; [2]: starters of this block; [3]: their place in the global list
+    uint32_t* s_start = s_qn + 4;                               // nodes finished here whose parent crosses the block boundary (global ids)
     const int base = blockIdx.x * S;
     const int m = min(S, n - base);
     const uint32_t n_internal = (uint32_t)(n - 1);
@@ -593,11 +635,15 @@ __global__ void __launch_bounds__(FF_TREELET_THREADS) refit_treelet_kernel(const
     // the classic climb -- the second arrival computes the parent at once -- half of the lanes drop out per level while the
     // warp keeps executing the ~250 instructions of the DP: 7 of 32 lanes active on average, and the kernel was bound by
     // instruction issue, profiles/r02g_build1m_full details.)
-    if (threadIdx.x < 2) s_qn[threadIdx.x] = 0u;
+    if (threadIdx.x < 4) s_qn[threadIdx.x] = 0u;
     __syncthreads();
     auto arrive = [&](int local, int buf) {   // the node at `local` is finished: count it at its parent
         const uint32_t pp = s_parent[local];
-        if (pp == FF_PARENT_ROOT || (pp & FF_PARENT_CROSS)) return;   // the root, or handed over to refit_cross_kernel
+        if (pp == FF_PARENT_ROOT) return;
+        if (pp & FF_PARENT_CROSS) {   // handed over to refit_cross_kernel, which starts its climbs from the list this block appends to
+            s_start[atomicAdd(&s_qn[2], 1u)] = local < S ? (uint32_t)(base + local) : n_internal + (uint32_t)(base + local - S);
+            return;
+        }
         const int pl = (int)pp - base;
         if (atomicAdd(&s_flag[pl], 1u) == 1u) s_q[buf][atomicAdd(&s_qn[buf], 1u)] = (uint32_t)pl;
     };
@@ -651,21 +697,24 @@ __global__ void __launch_bounds__(FF_TREELET_THREADS) refit_treelet_kernel(const
             dp[2 * g] = s_dp[2 * i];
             dp[2 * g + 1] = s_dp[2 * i + 1];
         }
+    // this block's starters join the global list (one atomic per block); the kernel boundary publishes them and the boxes above
+    if (threadIdx.x == 0) s_qn[3] = atomicAdd(starter_count, s_qn[2]);
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < s_qn[2]; i += T) starters[s_qn[3] + i] = s_start[i];
 }
 // The levels above the treelets: every node (or leaf) that was finished inside a block but whose PARENT's range crosses a block
 // boundary starts a climb through the global hand-off.  A separate launch, not a tail of the treelet kernel: a climb is a
 // chain of up to ~15 global atomic -> load -> store round trips, and a treelet CTA that waited for its climbs kept its 58 KB
 // of shared memory -- and with it a third of an SM -- for tens of microseconds (3.1 ms at 20 M triangles).
 __global__ void refit_cross_kernel(int n, const int2* __restrict__ children, const uint32_t* __restrict__ parent, uint32_t* __restrict__ flags,
-                                   float4* __restrict__ box_lo, float4* __restrict__ box_hi, float4* __restrict__ dp, float slot_cost, float node_cost) {
-    const uint32_t n_internal = (uint32_t)(n - 1), total = 2u * (uint32_t)n - 1u;
-    for (uint32_t node = blockIdx.x * blockDim.x + threadIdx.x; node < total; node += gridDim.x * blockDim.x) {
-        const uint32_t pp = parent[node];
-        if (pp == FF_PARENT_ROOT || !(pp & FF_PARENT_CROSS)) continue;
-        // an internal node that itself crosses a boundary is finished by whichever of its children arrives second, not from here
-        if (node < n_internal && (parent[children[node].x] & FF_PARENT_CROSS)) continue;
-        refit_climb_global(node, n, children, parent, flags, box_lo, box_hi, dp, slot_cost, node_cost);
-    }
+                                   float4* __restrict__ box_lo, float4* __restrict__ box_hi, float4* __restrict__ dp, float slot_cost, float node_cost,
+                                   const uint32_t* __restrict__ starters, const uint32_t* __restrict__ starter_count) {
+    // One thread per starter, all resident at once: the launch lasts as long as the longest chain of hand-offs.  (Finding the
+    // starters by scanning parent[] of all 2n - 1 nodes took 1.3 ms at 20 M triangles: a starter late in a thread's scan began
+    // its chain late, and everything above it waited -- profiles/r02w_build20m_details.txt.)
+    const uint32_t count = *starter_count;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
+        refit_climb_global(starters[i], n, children, parent, flags, box_lo, box_hi, dp, slot_cost, node_cost);
 }
 
 // ------------------------------------------------------------------ collapse to 8-wide compressed nodes
@@ -1189,7 +1238,7 @@ size_t sah_scratch_bytes(uint32_t n);
 cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float pad, float4* d_tris_out, float4* d_nodes_out,
                       uint32_t node_capacity, int2* d_bvh2_children, float4* d_bvh2_lo, float4* d_bvh2_hi,
                       uint32_t* d_bvh2_leaf_slot, float bounds_lo[3], float bounds_hi[3], BuildOut* out, uint32_t* launches,
-                      Arena& arena, cudaStream_t st) {
+                      Arena& arena, cudaStream_t st, const int* d_bounds_ready) {
     out->n_nodes = 0; out->depth = 0; out->sah_cost = 0; out->morton_bits = 0;
     for (int k = 0; k < 3; ++k) { bounds_lo[k] = 0; bounds_hi[k] = 0; }
     if (n == 0) return cudaSuccess;
@@ -1242,10 +1291,14 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
     CK(cudaMemsetAsync(d_flags, 0, sizeof(uint32_t) * n, st));
     mark("reserve scratch");
 
-    bounds_init_kernel<<<1, 32, 0, st>>>(d_bounds);
-    bounds_kernel<<<grid_for(n, 256, sm_count() * 8), 256, 0, st>>>(d_flat_tris, n, d_bounds);
+    if (d_bounds_ready) {
+        d_bounds = const_cast<int*>(d_bounds_ready);   // reduced by the bake kernel (k_bake_triangles)
+    } else {
+        bounds_init_kernel<<<1, 32, 0, st>>>(d_bounds);
+        bounds_kernel<<<grid_for(n, 256, sm_count() * 8), 256, 0, st>>>(d_flat_tris, n, d_bounds);
+        *launches += 2;
+    }
     mark("bounds");
-    *launches += 2;
     for (int attempt = 0; attempt < 2; ++attempt) {
         if (wide_keys) {
             morton_kernel<uint64_t><<<grid_for(n, 256, sm_count() * 16), 256, 0, st>>>(d_flat_tris, n, d_bounds, (uint64_t*)d_keys_a, d_vals_a);
@@ -1289,7 +1342,7 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
     const char* nc_env = getenv("FF_NODE_COST");
     const float node_cost = nc_env ? (float)atof(nc_env) : FF_NODE_COST;
     if (builder == FF_BUILDER_LBVH && !getenv("FF_REFIT_GLOBAL")) {
-        const size_t smem = sizeof(float4) * 6 * FF_TREELET + sizeof(uint32_t) * 3 * FF_TREELET + sizeof(int2) * FF_TREELET + sizeof(uint32_t) * (2 * FF_TREELET + 4);
+        const size_t smem = sizeof(float4) * 6 * FF_TREELET + sizeof(uint32_t) * 3 * FF_TREELET + sizeof(int2) * FF_TREELET + sizeof(uint32_t) * (2 * FF_TREELET + 4) + sizeof(uint32_t) * 2 * FF_TREELET;   // + s_start: up to 2S - 1 starters
         static bool attr_set[64] = {false};
         int dev = 0;
         cudaGetDevice(&dev);
@@ -1297,11 +1350,17 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
             CK(cudaFuncSetAttribute(refit_treelet_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             attr_set[dev] = true;
         }
-        refit_treelet_kernel<<<(n + FF_TREELET - 1) / FF_TREELET, FF_TREELET_THREADS, smem, st>>>(d_flat_tris, d_order, (int)n, pad, d_bvh2_children, d_parent,
-                                                                                             d_flags, d_bvh2_lo, d_bvh2_hi, d_dp, slot_cost, node_cost);
+        // the sort's second buffers are free by now: starters (at most one per node finished in a block) and their count
+        uint32_t* d_starters = d_vals_b;
+        uint32_t* d_starter_count = (uint32_t*)d_keys_b;
+        CK(cudaMemsetAsync(d_starter_count, 0, sizeof(uint32_t), st));
+        const uint32_t blocks = (n + FF_TREELET - 1) / FF_TREELET;
+        refit_treelet_kernel<<<blocks, FF_TREELET_THREADS, smem, st>>>(d_flat_tris, d_order, (int)n, pad, d_bvh2_children, d_parent, d_flags, d_bvh2_lo,
+                                                                       d_bvh2_hi, d_dp, slot_cost, node_cost, d_starters, d_starter_count);
         if (n > 1) {
-            refit_cross_kernel<<<grid_for(2 * (size_t)n, 256, sm_count() * 16), 256, 0, st>>>((int)n, d_bvh2_children, d_parent, d_flags, d_bvh2_lo, d_bvh2_hi, d_dp,
-                                                                                         slot_cost, node_cost);
+            // ~ 2 log2(FF_TREELET) starters per block on a balanced hierarchy; the grid-stride loop covers a degenerate one
+            refit_cross_kernel<<<grid_for((size_t)blocks * 24, 128, sm_count() * 64), 128, 0, st>>>((int)n, d_bvh2_children, d_parent, d_flags, d_bvh2_lo,
+                                                                                                 d_bvh2_hi, d_dp, slot_cost, node_cost, d_starters, d_starter_count);
             ++*launches;
         }
     } else {

@@ -82,6 +82,7 @@ struct ff_scene {
     bool committed = false;
     // device
     float4* d_flat = nullptr;  // baked triangles in flat order
+    int* d_bounds = nullptr;   // scene / centroid bounds reduced by the bake kernel (12 ordered ints), read by the build
     float4* d_tris = nullptr;  // baked triangles in leaf order
     float4* d_nodes = nullptr;
     int* d_ord_geom = nullptr;

@@ -146,7 +146,7 @@ struct WaveGen { float ox, oy, oz; };
 // ---------------------------------------------------------------- kernel launch wrappers
 // (implemented in the .cu files; all asynchronous on `st`)
 void k_bake_triangles(const float* d_xyz9_obj, const ffm::M4* d_model_per_geom, const uint32_t* d_geom_of_flat,
-                      const uint32_t* d_ord_of_flat, uint32_t n, float4* d_flat_tris, cudaStream_t st);
+                      const uint32_t* d_ord_of_flat, uint32_t n, float4* d_flat_tris, int* d_bounds, cudaStream_t st);
 
 // Per flat triangle: inverse(transpose(M)) * (normalize(cross(e1, e2)), 0) from OBJECT-space vertices: the normal the
 // reference's frame shows (kernel.cu:101,117,183).  d_nrm_per_geom = inverse(transpose(model)) of every geometry.
@@ -187,7 +187,8 @@ struct BuildOut {
 cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float pad, float4* d_tris_out,
                       float4* d_nodes_out, uint32_t node_capacity, int2* d_bvh2_children, float4* d_bvh2_lo,
                       float4* d_bvh2_hi, uint32_t* d_bvh2_leaf_slot, float bounds_lo[3], float bounds_hi[3],
-                      BuildOut* out, uint32_t* launches, Arena& arena, cudaStream_t st);
+                      BuildOut* out, uint32_t* launches, Arena& arena, cudaStream_t st, const int* d_bounds_ready = nullptr);
+// d_bounds_ready (optional): 12 ordered ints already reduced over d_flat_tris by k_bake_triangles; the build then skips its bounds pass.
 
 void k_trace_closest(const DevScene& sc, const float4* d_ray_o, const float4* d_ray_d, const uint32_t* d_count,
                      uint32_t n_max, int mode, HitRec* d_hits, TraceCounters* d_counters, uint32_t* d_work_counter, cudaStream_t st);

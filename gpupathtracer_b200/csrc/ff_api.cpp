@@ -729,7 +729,13 @@ static int trace_closest_stream(ff_scene* scene, const float* rays6, size_t n, i
         uint32_t shift = shift_pref;
         while (((m + ((size_t)1 << shift) - 1) >> shift) > FF_STREAM_MAX_CHUNKS) ++shift;
         const size_t chunk = (size_t)1 << shift, n_chunks = (m + chunk - 1) >> shift;
-        for (size_t k = 0; k < n_chunks; ++k) { tp.h_flags[k] = 0u; tp.h_marks[k] = (uint32_t)std::min(m, (k + 1) << shift); }
+        for (size_t k = 0; k < n_chunks; ++k) tp.h_marks[k] = (uint32_t)std::min(m, (k + 1) << shift);
+        // completion (copy-out) chunks may be finer than the copy-in chunks: the only copy-out nothing overlaps is the last one
+        static const uint32_t dshift_pref = [] { const char* e = getenv("FF_STREAM_DONE_SHIFT"); const long v = e ? atol(e) : 0; return (uint32_t)(v >= 12 && v <= 24 ? v : 0); }();
+        uint32_t dshift = dshift_pref ? std::min(dshift_pref, shift) : shift;
+        while (((m + ((size_t)1 << dshift) - 1) >> dshift) > FF_STREAM_MAX_CHUNKS) ++dshift;
+        const size_t dchunk = (size_t)1 << dshift, d_chunks = (m + dchunk - 1) >> dshift;
+        for (size_t k = 0; k < d_chunks; ++k) tp.h_flags[k] = 0u;
         tp.h_flags[FF_STREAM_MAX_CHUNKS] = 0u;   // raised by a lane that timed out
         // zero the shared words, then let the copy streams go (a super-batch reuses the staging of the one before it)
         FF_CUDA(cudaMemsetAsync(tp.d_sync, 0, sizeof(StreamSync), st));
@@ -751,7 +757,7 @@ static int trace_closest_stream(ff_scene* scene, const float* rays6, size_t n, i
         }
         // the launch goes first: its latency (and the first warps' spin on `avail`) overlaps the host's queueing of the copies
         FF_CUDA(cudaEventRecord(c->trace_events[0], st));
-        k_trace_closest_stream(scene->dev, d6, (uint32_t)m, shift, tp.d_sync, d_flags, dg, dt, dk, tp.work, st);
+        k_trace_closest_stream(scene->dev, d6, (uint32_t)m, dshift, tp.d_sync, d_flags, dg, dt, dk, tp.work, st);
         FF_CUDA(cudaEventRecord(c->trace_events[1], st));
         if (!preload) {
             {   // the first chunk lands in growing pieces (32 Ki, 32 Ki, 64 Ki, ... rays), so the kernel's first warps start after ~20 us of copy
@@ -772,14 +778,14 @@ static int trace_closest_stream(ff_scene* scene, const float* rays6, size_t n, i
         // hand finished chunks to the copy-out stream in order; the kernel cannot outlive its own time-out, so neither can this loop
         size_t next = 0;
         bool kernel_over = false;
-        while (next < n_chunks) {
+        while (next < d_chunks) {
             if (*(volatile uint32_t*)(tp.h_flags + next) == 0u) {
                 if (kernel_over) break;   // the kernel ended without completing the chunk: it timed out (err is read below)
                 kernel_over = cudaEventQuery(c->trace_events[1]) != cudaErrorNotReady;
                 if (!kernel_over) (void)cudaGetLastError();   // cudaErrorNotReady is recorded as the thread's last error: clear it
                 continue;                 // (one more look at the flag after the kernel is known to be over)
             }
-            const size_t a = next << shift, cnt = std::min(chunk, m - a);
+            const size_t a = next << dshift, cnt = std::min(dchunk, m - a);
             if (out_geom) FF_CUDA(cudaMemcpyAsync(out_geom + first + a, dg + a, sizeof(int) * cnt, cudaMemcpyDeviceToHost, tp.s_out));
             if (out_tri) FF_CUDA(cudaMemcpyAsync(out_tri + first + a, dt + a, sizeof(int) * cnt, cudaMemcpyDeviceToHost, tp.s_out));
             if (out_t) FF_CUDA(cudaMemcpyAsync(out_t + first + a, dk + a, sizeof(float) * cnt, cudaMemcpyDeviceToHost, tp.s_out));
@@ -792,7 +798,7 @@ static int trace_closest_stream(ff_scene* scene, const float* rays6, size_t n, i
         FF_CUDA(cudaEventSynchronize(tp.span[4]));
         FF_CUDA(cudaStreamSynchronize(tp.s_in));
         FF_CUDA(cudaGetLastError());
-        if (tp.h_flags[FF_STREAM_MAX_CHUNKS] || next < n_chunks) {
+        if (tp.h_flags[FF_STREAM_MAX_CHUNKS] || next < d_chunks) {
             // The kernel gave up waiting for rays: something serialises kernels against copies (a profiler that replays
             // kernels, CUDA_LAUNCH_BLOCKING).  The caller redoes the batch through the chunked pipeline; after two such
             // calls the context stops trying.

@@ -442,13 +442,7 @@ __device__ __forceinline__ int delta(const KeyT* __restrict__ keys, int n, int i
 // FF_TREELET consecutive sorted leaves: that is where the shared-memory phase of refit_treelet_kernel hands a subtree over to
 // the global hand-off protocol.  (An internal node's index always lies inside its own range, so a contained node also has
 // its index inside the block.)
-#ifndef FF_TREELET
-#ifndef FF_TREELET
-#define FF_TREELET 256   // leaves per block (r02z: 20 M triangles 6.46 / 6.10 / 7.34 ms with 512 / 256 / 1024)
-#endif
-#endif
-#define FF_PARENT_CROSS 0x80000000u
-#define FF_PARENT_ROOT 0xffffffffu
+// (FF_TREELET, FF_PARENT_CROSS, FF_PARENT_ROOT: ff_internal.h -- the binned-SAH builder tags its links the same way.)
 template <class KeyT>
 __global__ void hierarchy_kernel(const KeyT* __restrict__ keys, int n, int2* __restrict__ children, uint32_t* __restrict__ parent) {
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n - 1; i += gridDim.x * blockDim.x) {
@@ -1341,7 +1335,7 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
     const float slot_cost = sc_env ? (float)atof(sc_env) : FF_SLOT_COST;
     const char* nc_env = getenv("FF_NODE_COST");
     const float node_cost = nc_env ? (float)atof(nc_env) : FF_NODE_COST;
-    if (builder == FF_BUILDER_LBVH && !getenv("FF_REFIT_GLOBAL")) {
+    if (!getenv("FF_REFIT_GLOBAL")) {   // both builders number their nodes like Karras 2012 and tag the links that cross a block
         const size_t smem = sizeof(float4) * 6 * FF_TREELET + sizeof(uint32_t) * 3 * FF_TREELET + sizeof(int2) * FF_TREELET + sizeof(uint32_t) * (2 * FF_TREELET + 4) + sizeof(uint32_t) * 2 * FF_TREELET;   // + s_start: up to 2S - 1 starters
         static bool attr_set[64] = {false};
         int dev = 0;
@@ -1351,7 +1345,7 @@ cudaError_t bvh_build(const float4* d_flat_tris, uint32_t n, int builder, float 
             attr_set[dev] = true;
         }
         // the sort's second buffers are free by now: starters (at most one per node finished in a block) and their count
-        uint32_t* d_starters = d_vals_b;
+        uint32_t* d_starters = d_order == d_vals_b ? d_vals_a : d_vals_b;   // (the SAH hierarchy leaves its order in the second buffer)
         uint32_t* d_starter_count = (uint32_t*)d_keys_b;
         CK(cudaMemsetAsync(d_starter_count, 0, sizeof(uint32_t), st));
         const uint32_t blocks = (n + FF_TREELET - 1) / FF_TREELET;

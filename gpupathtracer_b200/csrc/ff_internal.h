@@ -23,6 +23,14 @@
 #define FF_TRI_EVERY 1     // >1 (probe): a lane that still has node work runs its triangle phase only every k-th iteration
 #endif
 #define FF_MAX_WIDE_DEPTH (FF_SM_STACK + FF_LOCAL_STACK)
+// Binary hierarchy links (both builders, Karras 2012 numbering: an internal node's index lies inside its own leaf range):
+// parent[] entries carry FF_PARENT_CROSS when the PARENT's leaf range is not contained in one block of FF_TREELET consecutive
+// leaves of the tree's order -- where refit_treelet_kernel (shared memory) hands a subtree over to refit_cross_kernel.
+#ifndef FF_TREELET
+#define FF_TREELET 256   // leaves per block (r02z: 20 M triangles 6.46 / 6.10 / 7.34 ms with 512 / 256 / 1024)
+#endif
+#define FF_PARENT_CROSS 0x80000000u
+#define FF_PARENT_ROOT 0xffffffffu
 #define FF_TRACE_BLOCK 128
 #define FF_REFILL_LANES 28            // persistent trace: refill idle lanes when fewer than this many still traverse
 #define FF_PERSISTENT_BLOCKS_PER_SM 12

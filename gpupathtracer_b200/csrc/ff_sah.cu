@@ -68,8 +68,9 @@ __device__ __forceinline__ void sah_link(uint32_t n, uint32_t id, uint32_t b, ui
     lid = (m - b == 1u) ? (n - 1u + b) : (m - 1u);
     rid = (e - m == 1u) ? (n - 1u + m) : m;
     children[id] = make_int2((int)lid, (int)rid);
-    parent[lid] = id;
-    parent[rid] = id;
+    const uint32_t tag = id | ((b / FF_TREELET) != ((e - 1u) / FF_TREELET) ? FF_PARENT_CROSS : 0u);   // ff_internal.h: this node's range crosses a refit block
+    parent[lid] = tag;
+    parent[rid] = tag;
 }
 
 // ------------------------------------------------------------------ one CTA per segment of more than SAH_SMALL triangles
@@ -104,6 +105,44 @@ __device__ __forceinline__ int sah_bin_of(float c2, float lo2, float scale) {
     return min(max(b, 0), SAH_BINS - 1);
 }
 
+// One warp adds (up to) 32 triangle boxes to a shared [3][SAH_BINS][7] bin table.  Morton-sorted neighbours mostly share a bin,
+// and 32 lanes doing 7 shared atomics each on the same words serialise (the binning passes were 25 of the 47 ms of a
+// 20 M-triangle build at 0.56 TB/s, profiles/r03a_launches_sah_20000000.csv).  When the whole warp agrees on the bin of an axis
+// (one match.all) the boxes are reduced by a shuffle butterfly and lane 0 does the 7 atomics; otherwise every lane does its
+// own.  min / max / + commute, so the table -- and the tree -- is the same.  (Grouping the lanes of each bin with ballots and
+// reducing with redux.sync over the group masks was measured first: 47 -> 77 ms, redux over partial masks is slow.)
+__device__ __forceinline__ void sah_bin_warp(int (*bins)[SAH_BINS][7], bool live, const int bin_of[3], const int ol[3], const int oh[3]) {
+    const int lane = threadIdx.x & 31;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const int b = bin_of[a];
+        int same = 0;
+        __match_all_sync(0xffffffffu, live ? b : -1 - lane, &same);
+        if (same) {
+            int v[6] = {ol[0], ol[1], ol[2], oh[0], oh[1], oh[2]};
+#pragma unroll
+            for (int off = 16; off; off >>= 1) {
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    v[k] = min(v[k], __shfl_xor_sync(0xffffffffu, v[k], off));
+                    v[3 + k] = max(v[3 + k], __shfl_xor_sync(0xffffffffu, v[3 + k], off));
+                }
+            }
+            if (lane == 0) {
+                int* bin = bins[a][b];
+                atomicMin(bin + 0, v[0]); atomicMin(bin + 1, v[1]); atomicMin(bin + 2, v[2]);
+                atomicMax(bin + 3, v[3]); atomicMax(bin + 4, v[4]); atomicMax(bin + 5, v[5]);
+                atomicAdd(bin + 6, 32);
+            }
+        } else if (live) {
+            int* bin = bins[a][b];
+            atomicMin(bin + 0, ol[0]); atomicMin(bin + 1, ol[1]); atomicMin(bin + 2, ol[2]);
+            atomicMax(bin + 3, oh[0]); atomicMax(bin + 4, oh[1]); atomicMax(bin + 5, oh[2]);
+            atomicAdd(bin + 6, 1);
+        }
+    }
+}
+
 // Candidate plane t (axis t / 15, left = bins [0, t % 15]) of a [3][SAH_BINS][7] bin table: SAH cost and left count.
 __device__ __forceinline__ void sah_eval_plane(const int* bins, int t, bool forced, float& cost_out, uint32_t& nl_out) {
     const int a = t / (SAH_BINS - 1), plane = t % (SAH_BINS - 1);
@@ -125,7 +164,11 @@ __device__ __forceinline__ void sah_eval_plane(const int* bins, int t, bool forc
     nl_out = nl;
 }
 
-__global__ void __launch_bounds__(SAH_BLOCK) sah_level_kernel(const SahSeg* __restrict__ segs, const uint32_t* __restrict__ idx_in,
+// BLOCK threads per segment: 256 while the segments are thousands of triangles, 128 / 64 for the last levels, where a CTA's life
+// is a fixed chain of barriers and the segments per SM are what counts (the three launches over 40..150-triangle segments were
+// 7.9 of the 47 ms of a 20 M-triangle build, profiles/r03a).  The partition is stable and the bins commute: same tree for any BLOCK.
+template <int BLOCK>
+__global__ void __launch_bounds__(BLOCK) sah_level_kernel(const SahSeg* __restrict__ segs, const uint32_t* __restrict__ idx_in,
                                                                uint32_t* __restrict__ idx_out, const float4* __restrict__ box_lo,
                                                                const float4* __restrict__ box_hi, SahLists lists, int2* children,
                                                                uint32_t* parent, uint32_t* __restrict__ final_order, uint32_t n) {
@@ -134,7 +177,7 @@ __global__ void __launch_bounds__(SAH_BLOCK) sah_level_kernel(const SahSeg* __re
     __shared__ uint32_t s_nleft[3 * (SAH_BINS - 1)];
     __shared__ int s_axis, s_plane;
     __shared__ uint32_t s_nl;
-    __shared__ uint32_t s_warp_l[SAH_BLOCK / 32], s_warp_r[SAH_BLOCK / 32];
+    __shared__ uint32_t s_warp_l[BLOCK / 32], s_warp_r[BLOCK / 32];
     __shared__ uint32_t s_base_l, s_base_r;
     __shared__ int s_cb[2][6];                  // children's centre bounds (ordered ints): [side][lo.xyz, hi.xyz]
 
@@ -142,7 +185,7 @@ __global__ void __launch_bounds__(SAH_BLOCK) sah_level_kernel(const SahSeg* __re
     const uint32_t b = s.b, e = s.e, cnt = e - b;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
-    for (int k = tid; k < 3 * SAH_BINS * 7; k += SAH_BLOCK) {
+    for (int k = tid; k < 3 * SAH_BINS * 7; k += BLOCK) {
         const int f = k % 7;
         (&s_bins[0][0][0])[k] = f < 3 ? sah_f2o(FLT_MAX) : (f < 6 ? sah_f2o(-FLT_MAX) : 0);
     }
@@ -158,18 +201,15 @@ __global__ void __launch_bounds__(SAH_BLOCK) sah_level_kernel(const SahSeg* __re
     // pass A: bin the triangle boxes by centre
     const bool forced = s.level >= SAH_MAX_LEVELS;
     if (!forced) {
-        for (uint32_t i = b + tid; i < e; i += SAH_BLOCK) {
-            const uint32_t p = idx_in[i];
-            const float4 lo = __ldg(box_lo + p), hi = __ldg(box_hi + p);
+        for (uint32_t base = b; base < e; base += BLOCK) {   // warp-uniform trip count: sah_bin_warp votes
+            const uint32_t i = base + tid;
+            const bool live = i < e;
+            float4 lo = make_float4(0.f, 0.f, 0.f, 0.f), hi = lo;
+            if (live) { const uint32_t p = idx_in[i]; lo = __ldg(box_lo + p); hi = __ldg(box_hi + p); }
             const float c2[3] = {lo.x + hi.x, lo.y + hi.y, lo.z + hi.z};
             const int ol[3] = {sah_f2o(lo.x), sah_f2o(lo.y), sah_f2o(lo.z)}, oh[3] = {sah_f2o(hi.x), sah_f2o(hi.y), sah_f2o(hi.z)};
-#pragma unroll
-            for (int a = 0; a < 3; ++a) {
-                int* bin = s_bins[a][sah_bin_of(c2[a], s.clo[a], scale[a])];
-                atomicMin(bin + 0, ol[0]); atomicMin(bin + 1, ol[1]); atomicMin(bin + 2, ol[2]);
-                atomicMax(bin + 3, oh[0]); atomicMax(bin + 4, oh[1]); atomicMax(bin + 5, oh[2]);
-                atomicAdd(bin + 6, 1);
-            }
+            const int bo[3] = {sah_bin_of(c2[0], s.clo[0], scale[0]), sah_bin_of(c2[1], s.clo[1], scale[1]), sah_bin_of(c2[2], s.clo[2], scale[2])};
+            sah_bin_warp(s_bins, live, bo, ol, oh);
         }
     }
     __syncthreads();
@@ -193,7 +233,7 @@ __global__ void __launch_bounds__(SAH_BLOCK) sah_level_kernel(const SahSeg* __re
 
     // pass B: stable partition into idx_out, and the centre bounds of the two sides
     float cl[6] = {FLT_MAX, FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX}, cr[6] = {FLT_MAX, FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX};
-    for (uint32_t base = b; base < e; base += SAH_BLOCK) {
+    for (uint32_t base = b; base < e; base += BLOCK) {
         const uint32_t i = base + tid;
         const bool live = i < e;
         uint32_t p = 0;
@@ -212,7 +252,7 @@ __global__ void __launch_bounds__(SAH_BLOCK) sah_level_kernel(const SahSeg* __re
         __syncthreads();
         uint32_t off_l = 0, off_r = 0, tot_l = 0, tot_r = 0;
 #pragma unroll
-        for (int w = 0; w < SAH_BLOCK / 32; ++w) {
+        for (int w = 0; w < BLOCK / 32; ++w) {
             if (w < warp) { off_l += s_warp_l[w]; off_r += s_warp_r[w]; }
             tot_l += s_warp_l[w]; tot_r += s_warp_r[w];
         }
@@ -304,18 +344,15 @@ __global__ void __launch_bounds__(SAH_BLOCK) sah_big_bin_kernel(SahBig B, const 
         scale[a] = ext > 0.f ? (float)SAH_BINS / ext : 0.f;
     }
     __syncthreads();
-    for (uint32_t i = cb + tid; i < ce; i += SAH_BLOCK) {
-        const uint32_t p = idx_in[i];
-        const float4 lo = __ldg(box_lo + p), hi = __ldg(box_hi + p);
+    for (uint32_t base = cb; base < ce; base += SAH_BLOCK) {   // warp-uniform trip count: sah_bin_warp votes
+        const uint32_t i = base + tid;
+        const bool live = i < ce;
+        float4 lo = make_float4(0.f, 0.f, 0.f, 0.f), hi = lo;
+        if (live) { const uint32_t p = idx_in[i]; lo = __ldg(box_lo + p); hi = __ldg(box_hi + p); }
         const float c2[3] = {lo.x + hi.x, lo.y + hi.y, lo.z + hi.z};
         const int ol[3] = {sah_f2o(lo.x), sah_f2o(lo.y), sah_f2o(lo.z)}, oh[3] = {sah_f2o(hi.x), sah_f2o(hi.y), sah_f2o(hi.z)};
-#pragma unroll
-        for (int a = 0; a < 3; ++a) {
-            int* bin = s_bins[a][sah_bin_of(c2[a], s.clo[a], scale[a])];
-            atomicMin(bin + 0, ol[0]); atomicMin(bin + 1, ol[1]); atomicMin(bin + 2, ol[2]);
-            atomicMax(bin + 3, oh[0]); atomicMax(bin + 4, oh[1]); atomicMax(bin + 5, oh[2]);
-            atomicAdd(bin + 6, 1);
-        }
+        const int bo[3] = {sah_bin_of(c2[0], s.clo[0], scale[0]), sah_bin_of(c2[1], s.clo[1], scale[1]), sah_bin_of(c2[2], s.clo[2], scale[2])};
+        sah_bin_warp(s_bins, live, bo, ol, oh);
     }
     __syncthreads();
     int* g = B.gbins + (size_t)si * 3 * SAH_BINS * 7;
@@ -657,7 +694,10 @@ cudaError_t sah_build_hierarchy(const float4* d_flat_tris, const uint32_t* d_sor
             *launches += 5;
         }
         if (n_mid) {
-            sah_level_kernel<<<n_mid, SAH_BLOCK, 0, st>>>(seg_in, idx_in, idx_out, d_lo, d_hi, lists, d_children, d_parent, d_order_k, n);
+            const uint32_t avg = n / n_mid;   // upper bound of the level's mean segment size
+            if (avg <= 96u) sah_level_kernel<64><<<n_mid, 64, 0, st>>>(seg_in, idx_in, idx_out, d_lo, d_hi, lists, d_children, d_parent, d_order_k, n);
+            else if (avg <= 320u) sah_level_kernel<128><<<n_mid, 128, 0, st>>>(seg_in, idx_in, idx_out, d_lo, d_hi, lists, d_children, d_parent, d_order_k, n);
+            else sah_level_kernel<SAH_BLOCK><<<n_mid, SAH_BLOCK, 0, st>>>(seg_in, idx_in, idx_out, d_lo, d_hi, lists, d_children, d_parent, d_order_k, n);
             ++*launches;
         }
         uint32_t h[8];

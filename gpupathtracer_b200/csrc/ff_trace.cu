@@ -141,9 +141,11 @@ struct StoreIdsStream {
     // draws its next ray) and writes it in retire(), at the warp's next refill, together with the other lanes that finished.
     __device__ __forceinline__ void operator()(size_t, const Best&) const {}
     // Warp-converged.  `pending` = index of the ray this lane finished since the last call (0xffffffff: none), `best` its result
-    // (== unpack_hits_kernel on store_hit's record).  Finished rays are counted per warp in (acc_chunk, acc_count) and reported
-    // to the chunk's counter -- one release atomic, which is what publishes the warp's result stores -- when the warp first
-    // retires a ray of another chunk, and when it exits.
+    // (== unpack_hits_kernel on store_hit's record).  Finished rays are counted per warp -- acc_chunk is the newest chunk seen,
+    // acc_count holds its count (low half) and that of the chunk before it (high half) -- and reported to the chunk's counter
+    // by one release atomic, which is what publishes the warp's result stores, when the warp has moved two chunks on, and
+    // when it exits: about one report per warp and chunk (a report costs a MEMBAR; with one open chunk per warp the late rays
+    // of a chunk made the warp flip between two chunks and report several times).
     __device__ __forceinline__ void retire(uint32_t& pending, const Best& b, int lane, uint32_t& acc_chunk, uint32_t& acc_count) const {
         unsigned pend = __ballot_sync(0xffffffffu, pending != 0xffffffffu);
         if (pend == 0u) return;
@@ -158,8 +160,20 @@ struct StoreIdsStream {
             const uint32_t mine = pending >> chunk_shift;
             const uint32_t c = __shfl_sync(0xffffffffu, mine, leader);
             const unsigned same = __ballot_sync(0xffffffffu, pending != 0xffffffffu && mine == c);
-            if (c != acc_chunk) { flush(lane, acc_chunk, acc_count); acc_chunk = c; acc_count = 0u; }
-            acc_count += (uint32_t)__popc(same);
+            // two chunks are open per warp (late rays of chunk c finish among the first of c + 1): the counts of the older one
+            // ride in the top half of acc_count and are reported when a third chunk shows up
+            const uint32_t k = (uint32_t)__popc(same);
+            if (c == acc_chunk) acc_count += k;
+            else if (c + 1u == acc_chunk) acc_count += k << 16;
+            else {
+                if (c == acc_chunk + 1u) { flush(lane, acc_chunk - 1u, acc_count >> 16); acc_count = (acc_count & 0xffffu) << 16; }
+                else { flush(lane, acc_chunk - 1u, acc_count >> 16); flush(lane, acc_chunk, acc_count & 0xffffu); acc_count = 0u; }
+                acc_chunk = c;
+                acc_count += k;
+            }
+            if ((acc_count & 0xffffu) > 0xff00u || (acc_count >> 16) > 0xff00u) {   // (cannot happen with 2^16+ rays per chunk and warp; keeps the halves apart)
+                flush(lane, acc_chunk - 1u, acc_count >> 16); flush(lane, acc_chunk, acc_count & 0xffffu); acc_count = 0u;
+            }
             pend &= ~same;
         }
         pending = 0xffffffffu;
@@ -291,7 +305,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK, FF_TRACE_MINB) trace_closest_p
         __syncwarp();
     }
     // rays that finished in the fetch path of the last round (no hierarchy) have not been reported yet; the break is warp-uniform
-    if constexpr (Store::kCompletion) { store.retire(pending, best, lane, acc_chunk, acc_count); store.flush(lane, acc_chunk, acc_count); }
+    if constexpr (Store::kCompletion) { store.retire(pending, best, lane, acc_chunk, acc_count); store.flush(lane, acc_chunk - 1u, acc_count >> 16); store.flush(lane, acc_chunk, acc_count & 0xffffu); }
 }
 
 // Brute force: the reference's own algorithm (every ray against every triangle), tiles of triangles staged

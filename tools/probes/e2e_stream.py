@@ -54,7 +54,7 @@ def one():
     g = sc.trace_closest(np.array(h_rays[:1500000]))
     ragged += int((g["geom"] != want["geom"][:1500000]).sum())
     print(json.dumps(dict(stream=os.environ.get("FF_TRACE_STREAM", "1"), shift=os.environ.get("FF_STREAM_CHUNK_SHIFT", "default"),
-                          chunk=os.environ.get("FF_TRACE_CHUNK", "default"), preload=os.environ.get("FF_STREAM_PRELOAD", "0"), device_ms=float(np.mean(dev_ms)), e2e_ms=float(np.mean(ms)),
+                          chunk=os.environ.get("FF_TRACE_CHUNK", "default"), preload=os.environ.get("FF_STREAM_PRELOAD", "0"), done_shift=os.environ.get("FF_STREAM_DONE_SHIFT", "same"), device_ms=float(np.mean(dev_ms)), e2e_ms=float(np.mean(ms)),
                           e2e_ms_min=float(np.min(ms)), mrays_s=n / float(np.mean(ms)) / 1e3, trace_ms=float(np.mean(tr)), h2d_ms=float(np.mean(h2d)),
                           d2h_ms=float(np.mean(d2h)), passes=st["passes"], mismatches=bad, ragged_mismatches=ragged)), flush=True)
 
@@ -62,7 +62,7 @@ def one():
 def main():
     if "--one" in sys.argv:
         return one()
-    configs = [dict(FF_TRACE_STREAM="0")] + [dict(FF_TRACE_STREAM="1", FF_STREAM_CHUNK_SHIFT=str(s)) for s in (19,)] + [
+    configs = [dict(FF_TRACE_STREAM="0"), dict(FF_TRACE_STREAM="1")] + [dict(FF_TRACE_STREAM="1", FF_STREAM_DONE_SHIFT=str(s)) for s in (18, 17, 16)] + [
         dict(FF_TRACE_STREAM="1", FF_STREAM_PRELOAD="1")]
     for cfg in configs:
         env = dict(os.environ)

@@ -427,6 +427,7 @@ __global__ void __launch_bounds__(SAH_BLOCK) sah_big_scatter_kernel(SahBig B, co
                                                                      const float4* __restrict__ box_lo, const float4* __restrict__ box_hi) {
     __shared__ uint32_t s_warp_l[SAH_BLOCK / 32], s_warp_r[SAH_BLOCK / 32];
     __shared__ uint32_t s_base_l, s_base_r;
+    __shared__ int s_cb[12];   // the chunk's contribution to the children's centre bounds (ordered ints)
     const uint32_t si = B.chunk_seg[blockIdx.x];
     const SahSeg s = B.segs[si];
     const SahBigSplit sp = B.split[si];
@@ -441,6 +442,7 @@ __global__ void __launch_bounds__(SAH_BLOCK) sah_big_scatter_kernel(SahBig B, co
         s_base_l = s.b + off.x;
         s_base_r = s.b + nl + off.y;
     }
+    if (tid < 12) s_cb[tid] = (tid % 6) < 3 ? sah_f2o(FLT_MAX) : sah_f2o(-FLT_MAX);
     __syncthreads();
     float cl[6] = {FLT_MAX, FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX}, cr[6] = {FLT_MAX, FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX};
     for (uint32_t base = cb; base < ce; base += SAH_BLOCK) {
@@ -483,10 +485,14 @@ __global__ void __launch_bounds__(SAH_BLOCK) sah_big_scatter_kernel(SahBig B, co
             vl = k < 3 ? fminf(vl, ol) : fmaxf(vl, ol);
             vr = k < 3 ? fminf(vr, orr) : fmaxf(vr, orr);
         }
-        if (lane == 0) {
-            if (k < 3) { atomicMin(gcb + k, sah_f2o(vl)); atomicMin(gcb + 6 + k, sah_f2o(vr)); }
-            else { atomicMax(gcb + k, sah_f2o(vl)); atomicMax(gcb + 6 + k, sah_f2o(vr)); }
+        if (lane == 0) {   // per CTA first: at the top levels every chunk of the scene lands on the same 12 words (937 k global atomics at 20 M)
+            if (k < 3) { atomicMin(s_cb + k, sah_f2o(vl)); atomicMin(s_cb + 6 + k, sah_f2o(vr)); }
+            else { atomicMax(s_cb + k, sah_f2o(vl)); atomicMax(s_cb + 6 + k, sah_f2o(vr)); }
         }
+    }
+    __syncthreads();
+    if (tid < 12) {
+        if ((tid % 6) < 3) atomicMin(gcb + tid, s_cb[tid]); else atomicMax(gcb + tid, s_cb[tid]);
     }
 }
 
@@ -507,6 +513,11 @@ __global__ void sah_big_emit_kernel(SahBig B, SahLists lists, const uint32_t* __
 // Lane k holds the triangle at position b + k.  Exact sweep SAH without sorting: lane j's candidate sends every
 // triangle whose (centre, lane) is not after (centre_j, j) to the left, which enumerates the prefixes of the order
 // sorted by centre.  The cheapest (cost, axis, lane) wins; the sub-range is partitioned stably through shared memory.
+// Level-synchronous: every lane carries the sub-range [rb, re) it currently belongs to, and ALL sub-ranges of a level are
+// evaluated and partitioned together (a lane meets the lanes of its own range through shuffles with a per-lane source).  The
+// first version took the sub-ranges one at a time from a stack -- 31 serial steps and 160 sweep iterations for a 32-triangle
+// segment instead of 5 and 62 -- and was 14.9 of the 47 ms of a 20 M-triangle build (profiles/r03a).  Same candidates, same
+// tie-breaks, same tree.
 #define SAH_WARPS 4
 __global__ void __launch_bounds__(SAH_WARPS * 32) sah_small_kernel(const SahSeg* __restrict__ segs, uint32_t n_segs,
                                                                    const uint32_t* __restrict__ idx_in, const float4* __restrict__ box_lo,
@@ -514,7 +525,6 @@ __global__ void __launch_bounds__(SAH_WARPS * 32) sah_small_kernel(const SahSeg*
                                                                    uint32_t* __restrict__ final_order, uint32_t n) {
     __shared__ float s_box[SAH_WARPS][6][32];
     __shared__ uint32_t s_prim[SAH_WARPS][32];
-    __shared__ uint32_t s_stack[SAH_WARPS][32][3];   // {first lane, end lane, node id}
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t si = blockIdx.x * SAH_WARPS + warp;
     if (si >= n_segs) return;
@@ -527,16 +537,12 @@ __global__ void __launch_bounds__(SAH_WARPS * 32) sah_small_kernel(const SahSeg*
         const float4 l = __ldg(box_lo + prim), h = __ldg(box_hi + prim);
         lo[0] = l.x; lo[1] = l.y; lo[2] = l.z; hi[0] = h.x; hi[1] = h.y; hi[2] = h.z;
     }
-    int sp = 0;
-    if (lane == 0) { s_stack[warp][0][0] = 0; s_stack[warp][0][1] = cnt; s_stack[warp][0][2] = s.id; }
-    sp = 1;
-    __syncwarp();
-    while (sp > 0) {
-        --sp;
-        const uint32_t rb = s_stack[warp][sp][0], re = s_stack[warp][sp][1], id = s_stack[warp][sp][2];
-        __syncwarp();
+    uint32_t rb = 0, re = cnt, id = s.id;                     // the lane's current sub-range (lanes) and its node
+    bool active = (uint32_t)lane < cnt && cnt >= 2u;          // ... which still has to be split
+    const unsigned lt = (1u << lane) - 1u;
+    while (__any_sync(0xffffffffu, active)) {
         const uint32_t rc = re - rb;
-        const bool in = (uint32_t)lane >= rb && (uint32_t)lane < re;
+        const uint32_t maxlen = __reduce_max_sync(0xffffffffu, active ? rc : 0u);
         const float cj[3] = {lo[0] + hi[0], lo[1] + hi[1], lo[2] + hi[2]};
         float L[3][6], R[3][6];
         uint32_t nl[3] = {0, 0, 0};
@@ -544,27 +550,31 @@ __global__ void __launch_bounds__(SAH_WARPS * 32) sah_small_kernel(const SahSeg*
         for (int a = 0; a < 3; ++a)
 #pragma unroll
             for (int k = 0; k < 6; ++k) { L[a][k] = k < 3 ? FLT_MAX : -FLT_MAX; R[a][k] = k < 3 ? FLT_MAX : -FLT_MAX; }
-        for (uint32_t k = rb; k < re; ++k) {
+        for (uint32_t t = 0; t < maxlen; ++t) {
+            const bool valid = active && t < rc;
+            const uint32_t k = valid ? rb + t : (uint32_t)lane;   // the t-th lane of my range
             float kl[3], kh[3];
 #pragma unroll
             for (int a = 0; a < 3; ++a) { kl[a] = __shfl_sync(0xffffffffu, lo[a], (int)k); kh[a] = __shfl_sync(0xffffffffu, hi[a], (int)k); }
+            if (valid) {
 #pragma unroll
-            for (int a = 0; a < 3; ++a) {
-                const float ck = kl[a] + kh[a];
-                const bool left = ck < cj[a] || (ck == cj[a] && k <= (uint32_t)lane);
-                if (left) {
-                    ++nl[a];
+                for (int a = 0; a < 3; ++a) {
+                    const float ck = kl[a] + kh[a];
+                    const bool left = ck < cj[a] || (ck == cj[a] && k <= (uint32_t)lane);
+                    if (left) {
+                        ++nl[a];
 #pragma unroll
-                    for (int q = 0; q < 3; ++q) { L[a][q] = fminf(L[a][q], kl[q]); L[a][3 + q] = fmaxf(L[a][3 + q], kh[q]); }
-                } else {
+                        for (int q = 0; q < 3; ++q) { L[a][q] = fminf(L[a][q], kl[q]); L[a][3 + q] = fmaxf(L[a][3 + q], kh[q]); }
+                    } else {
 #pragma unroll
-                    for (int q = 0; q < 3; ++q) { R[a][q] = fminf(R[a][q], kl[q]); R[a][3 + q] = fmaxf(R[a][3 + q], kh[q]); }
+                        for (int q = 0; q < 3; ++q) { R[a][q] = fminf(R[a][q], kl[q]); R[a][3 + q] = fmaxf(R[a][3 + q], kh[q]); }
+                    }
                 }
             }
         }
         float best = FLT_MAX;
         uint32_t code = 0xffffffffu;  // axis * 32 + lane of the winning candidate
-        if (in) {
+        if (active) {
 #pragma unroll
             for (int a = 0; a < 3; ++a) {
                 if (nl[a] == 0 || nl[a] >= rc) continue;
@@ -573,44 +583,46 @@ __global__ void __launch_bounds__(SAH_WARPS * 32) sah_small_kernel(const SahSeg*
                 if (c < best) { best = c; code = (uint32_t)a * 32u + (uint32_t)lane; }
             }
         }
-        for (int off = 16; off; off >>= 1) {
-            const float ob = __shfl_xor_sync(0xffffffffu, best, off);
-            const uint32_t oc = __shfl_xor_sync(0xffffffffu, code, off);
-            if (ob < best || (ob == best && oc < code)) { best = ob; code = oc; }
+        // the range's cheapest candidate (ties: smallest code), by a sweep over the range like the one above
+        float rbest = FLT_MAX;
+        uint32_t rcode = 0xffffffffu;
+        for (uint32_t t = 0; t < maxlen; ++t) {
+            const bool valid = active && t < rc;
+            const int k = valid ? (int)(rb + t) : lane;
+            const float ob = __shfl_sync(0xffffffffu, best, k);
+            const uint32_t oc = __shfl_sync(0xffffffffu, code, k);
+            if (valid && (ob < rbest || (ob == rbest && oc < rcode))) { rbest = ob; rcode = oc; }
         }
         bool left;
-        if (code != 0xffffffffu) {
-            const int a = (int)(code >> 5), j = (int)(code & 31u);
+        {
+            const int a = rcode != 0xffffffffu ? (int)(rcode >> 5) : 0, j = rcode != 0xffffffffu ? (int)(rcode & 31u) : lane;
             const float mine = a == 0 ? cj[0] : (a == 1 ? cj[1] : cj[2]);
             const float cjw = __shfl_sync(0xffffffffu, mine, j);
-            left = mine < cjw || (mine == cjw && lane <= j);
-        } else {
-            left = (uint32_t)lane < rb + rc / 2;   // NaN boxes: halve by position
+            if (rcode != 0xffffffffu) left = mine < cjw || (mine == cjw && lane <= j);
+            else left = (uint32_t)lane < rb + rc / 2;   // NaN boxes: halve by position
         }
-        const unsigned ml = __ballot_sync(0xffffffffu, in && left), mr = __ballot_sync(0xffffffffu, in && !left);
-        const uint32_t nleft = __popc(ml);
-        const unsigned lt = (1u << lane) - 1u;
-        if (in) {
-            const uint32_t dst = left ? rb + __popc(ml & lt) : rb + nleft + __popc(mr & lt);
+        const unsigned ml = __ballot_sync(0xffffffffu, active && left), mr = __ballot_sync(0xffffffffu, active && !left);
+        const unsigned range = (re >= 32u ? 0xffffffffu : (1u << re) - 1u) & ~((1u << rb) - 1u);
+        const uint32_t nleft = __popc(ml & range);
+        if (active) {
+            const uint32_t dst = left ? rb + __popc(ml & range & lt) : rb + nleft + __popc(mr & range & lt);
 #pragma unroll
             for (int q = 0; q < 3; ++q) { s_box[warp][q][dst] = lo[q]; s_box[warp][3 + q][dst] = hi[q]; }
             s_prim[warp][dst] = prim;
         }
         __syncwarp();
-        if (in) {
+        if (active) {
 #pragma unroll
             for (int q = 0; q < 3; ++q) { lo[q] = s_box[warp][q][lane]; hi[q] = s_box[warp][3 + q][lane]; }
             prim = s_prim[warp][lane];
-        }
-        const uint32_t rm = rb + nleft;
-        if (lane == 0) {
+            const uint32_t rm = rb + nleft;
             uint32_t lid, rid;
-            sah_link(n, id, s.b + rb, s.b + rm, s.b + re, children, parent, lid, rid);
-            int t = sp;
-            if (re - rm >= 2u) { s_stack[warp][t][0] = rm; s_stack[warp][t][1] = re; s_stack[warp][t][2] = rid; ++t; }
-            if (rm - rb >= 2u) { s_stack[warp][t][0] = rb; s_stack[warp][t][1] = rm; s_stack[warp][t][2] = lid; ++t; }
+            if ((uint32_t)lane == rb) sah_link(n, id, s.b + rb, s.b + rm, s.b + re, children, parent, lid, rid);   // one lane per range writes the links
+            lid = (rm - rb == 1u) ? (n - 1u + s.b + rb) : (s.b + rm - 1u);   // (the ids sah_link assigns, for every lane of the range)
+            rid = (re - rm == 1u) ? (n - 1u + s.b + rm) : (s.b + rm);
+            if ((uint32_t)lane < rm) { re = rm; id = lid; } else { rb = rm; id = rid; }
+            active = re - rb >= 2u;
         }
-        sp += (re - rm >= 2u ? 1 : 0) + (rm - rb >= 2u ? 1 : 0);
         __syncwarp();
     }
     if ((uint32_t)lane < cnt) final_order[s.b + lane] = prim;

@@ -6,4 +6,4 @@ ctx = ff.Context(0)
 soup = ctx.make_soup(n)
 sc = ctx.scene(); sc.add_triangles(soup)
 sc.commit(1); sc.commit(1)
-print(n, sc.info()["build_ms"], sc.info()["n_nodes"])
+print(n, sc.info()["build_ms"], sc.info()["n_nodes"], repr(sc.info()["sah_cost"]))

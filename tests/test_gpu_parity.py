@@ -402,3 +402,43 @@ def test_host_batches_stream_through_one_launch(ff, ctx):
             assert st["rays"] == m
             assert (g[:m] == want["geom"][:m]).all() and (t[:m] == want["tri"][:m]).all() and (bits(k[:m]) == bits(want["t"][:m])).all()
             assert (g[m:] == -9).all() and (k[m:] == -9.0).all()   # nothing written past the batch
+
+
+def test_streaming_trace_falls_back_when_kernels_are_serialised_against_copies():
+    """Under CUDA_LAUNCH_BLOCKING=1 (as under a profiler that replays kernels) the streaming launch can never see its rays: its
+    lanes give up after a second, and ff_trace_closest must redo the batch through the chunked pipeline and return the same
+    hits -- twice, after which the context stops trying the streaming path.  Own process: the variable is read at CUDA start-up."""
+    import os
+    import subprocess
+    import sys
+    code = r'''
+import sys, time
+import numpy as np
+sys.path.insert(0, %r)
+import gpupathtracer_b200 as ff
+if ff.device_count() == 0:
+    print("NO_DEVICE"); sys.exit(0)
+ctx = ff.Context(0)
+sc = ctx.scene(); sc.add_triangles(ctx.make_soup(20000)); sc.commit()
+n = 200000
+d_rays, d_hits = ctx.alloc(n * 32), ctx.alloc(n * 16)
+rays = ctx.make_rays_uniform(0, n, device_buffer=d_rays)
+sc.trace_closest_device(d_rays, n, d_hits)
+want = sc.hits_unpack(d_hits, n)
+times = []
+for _ in range(3):
+    t0 = time.time()
+    got = sc.trace_closest(rays)
+    times.append(time.time() - t0)
+    assert (got["geom"] == want["geom"]).all() and (got["tri"] == want["tri"]).all()
+    assert (got["t"].view(np.uint32) == want["t"].view(np.uint32)).all()
+print("OK", " ".join("%%.2f" %% t for t in times))
+''' % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))),)
+    env = dict(os.environ, CUDA_LAUNCH_BLOCKING="1")
+    r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr[-2000:]
+    if "NO_DEVICE" in r.stdout:
+        pytest.skip("no CUDA device")
+    assert r.stdout.startswith("OK"), r.stdout
+    t = [float(x) for x in r.stdout.split()[1:]]
+    assert t[0] > 0.9 and t[1] > 0.9 and t[2] < 0.5, t   # two time-outs of one second, then the chunked pipeline straight away

@@ -1191,6 +1191,15 @@ __global__ void __launch_bounds__(128) collapse_persistent_kernel(uint32_t* __re
         }
         __syncthreads();
         const uint32_t begin = s_range[0], end = s_range[1];
+#if FF_COLLAPSE_TRACE   // development aid (-DFF_COLLAPSE_TRACE=1): when each level started on block 0, printed at the end.  1 M triangles:
+        // levels of 1 / 8 / 64 / 512 / 4096 nodes take 11 / 14 / 15 / 16 / 18 us each (the latency of one node: barrier, DP descent,
+        // allocation), 32 768 nodes 56 us, 108 871 nodes 101 us (profiles/r04b_collapse_levels.txt).  Lighter barrier fences: no change.
+        __shared__ unsigned long long s_t[40];
+        __shared__ uint32_t s_cnt[40];
+        if (blockIdx.x == 0 && threadIdx.x == 0 && gen < 40) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); s_t[gen] = t; s_cnt[gen] = end - begin; }
+        if (begin == end && blockIdx.x == 0 && threadIdx.x == 0)
+            for (uint32_t g = 0; g + 1 <= gen && g < 39; ++g) printf("[collapse] level %u: %u nodes, %.1f us\n", g, s_cnt[g], (double)(s_t[g + 1] - s_t[g]) * 1e-3);
+#endif
         if (begin == end) return;   // uniform over the grid: every CTA reads the range the barrier published
         if (end - begin <= FF_COLLAPSE_TILE_LEVEL) {   // a small level: latency matters, eight lanes per node
             for (uint32_t w = begin + blockIdx.x * tiles_per_block + tile_in_block; w < end; w += gridDim.x * tiles_per_block)

@@ -76,20 +76,20 @@ struct StoreLite {
 
 // Host batches (ff_trace_closest): ONE persistent launch traces the batch while the copy engines are still delivering it and
 // already taking results away.  The host queues the rays as chunks of 2^chunk_shift on a copy stream, each followed by a
-// 4-byte copy that advances `avail` (rays landed so far); a lane that draws a ray beyond `avail` waits for it.  Results go out
+// 4-byte copy that advances `avail` (rays landed so far); a warp whose refill reaches beyond `avail` waits for it.  Results go out
 // in the reference's numbering (no hit-record pass, no unpack pass), written when the warp next refills; each warp counts
 // the rays it finished and reports them to the chunk's counter when it moves on to another chunk, and the warp that completes
 // a chunk raises its flag in page-locked host memory, on which the host queues the chunk's device-to-host copies.  Nothing here can wait for ever: a lane gives up after kStreamTimeoutNs, sets `err`,
 // and every later wait returns at once (the host then redoes the batch through the chunked pipeline).
 static constexpr unsigned long long kStreamTimeoutNs = 1000000000ull;
-// Neither side of the hand-off may use an ACQUIRE (ld.acquire, fence.acq_rel): on this machine an acquire invalidates the
-// SM's whole L1 (CCTL.IVALL), and one per refill took the node / triangle hit rate with it (the first version of this path
-// traced the C4 batch in 6.7 ms against 5.4 ms device-resident).  None is needed: the rays are read with ld.cg, which does
-// not look at L1, and are requested only after the branch on `avail` has resolved (the copy engine wrote them before it
-// wrote `avail`); results are published with a RELEASE on the counting atomic.
-__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
+// Acquires are rationed: on this machine an acquire (ld.acquire, fence.acq_rel) invalidates the SM's whole L1 (CCTL.IVALL).  The
+// first version of this path did one per lane and chunk for `avail` and one fence per refill for the results, and traced the C4
+// batch in 6.7 ms against 5.4 ms device-resident: the node / triangle hit rate went with the L1.  Now ONE lane per warp acquires
+// `avail`, and only when the warp's refill reaches past what it already knows has landed (about once per warp and chunk: a few
+// hundred per SM and batch); results are published with a RELEASE on the counting atomic, which invalidates nothing.
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
     uint32_t v;
-    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
 __device__ __forceinline__ uint32_t atom_add_release_gpu(uint32_t* p, uint32_t v) {
@@ -107,17 +107,23 @@ struct FetchRays6Stream {
     const float* __restrict__ rays6;
     StreamSync* sync;
     uint32_t* host_err;     // page-locked host word: a lane timed out (the host reads it after the launch, without a copy)
-    // `known` = the lane's last reading of `avail`: one load per lane and chunk, not per ray
-    __device__ __forceinline__ void wait(uint32_t i, uint32_t& known) const {
-        if (i < known) return;
-        const unsigned long long t0 = global_ns();
-        for (;;) {
-            known = ld_relaxed_sys(&sync->avail);
-            if (i < known) return;
-            if (*(volatile uint32_t*)&sync->err) { known = 0xffffffffu; return; }
-            if (global_ns() - t0 > kStreamTimeoutNs) { atomicExch(&sync->err, 1u); *(volatile uint32_t*)host_err = 1u; known = 0xffffffffu; return; }
-            __nanosleep(256);
+    // Warp-converged.  Returns a count of landed rays that is >= `want` (lane 0 spins on `avail` with acquire loads; the
+    // __syncwarp orders every lane's ray loads after them), or 0xffffffff once a time-out has been raised.
+    __device__ __forceinline__ uint32_t wait_warp(uint32_t want, int lane) const {
+        uint32_t known = 0u;
+        if (lane == 0) {
+            const unsigned long long t0 = global_ns();
+            for (;;) {
+                known = ld_acquire_sys(&sync->avail);
+                if (known >= want) break;
+                if (*(volatile uint32_t*)&sync->err) { known = 0xffffffffu; break; }
+                if (global_ns() - t0 > kStreamTimeoutNs) { atomicExch(&sync->err, 1u); *(volatile uint32_t*)host_err = 1u; known = 0xffffffffu; break; }
+                __nanosleep(256);
+            }
         }
+        known = __shfl_sync(0xffffffffu, known, 0);
+        __syncwarp();
+        return known;
     }
     __device__ __forceinline__ void operator()(uint32_t i, V3& o, V3& draw, uint32_t& skipbits) const {
         // written by the copy engine while this kernel runs: read through L2 (.cg), never through the read-only path
@@ -236,7 +242,7 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK, FF_TRACE_MINB) trace_closest_p
     Best best;
     unsigned cn = 0, ct = 0;
     uint32_t pending = 0xffffffffu;   // Store::kCompletion: the ray this lane finished and has not reported yet
-    uint32_t avail_known = 0u;        // Fetch::kStreams: rays known to have landed
+    uint32_t avail_known = 0u;        // Fetch::kStreams: rays known to have landed (warp-uniform)
     uint32_t acc_chunk = 0u, acc_count = 0u;   // Store::kCompletion: finished rays of chunk acc_chunk this warp has not reported yet
     for (;;) {
         const unsigned need = __ballot_sync(0xffffffffu, !has);
@@ -247,12 +253,15 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK, FF_TRACE_MINB) trace_closest_p
             if (lane == leader) base = atomicAdd(work_counter, (uint32_t)__popc(need));
             base = __shfl_sync(0xffffffffu, base, leader);
             if (base + (uint32_t)__popc(need) >= n) exhausted = true;
+            if constexpr (Fetch::kStreams) {   // host batches: the rays of this refill may still be on their way
+                const uint32_t want = min(n, base + (uint32_t)__popc(need));
+                if (want > avail_known) avail_known = fetch.wait_warp(want, lane);
+            }
             if (!has) {
                 const uint32_t i = base + __popc(need & ((1u << lane) - 1u));
                 if (i < n) {
                     V3 o, draw;
                     uint32_t skipbits;
-                    if constexpr (Fetch::kStreams) fetch.wait(i, avail_known);
                     fetch(i, o, draw, skipbits);
                     const V3 dn = normalize(draw);  // kernel.cu:138
                     best_init(best, INFINITY);

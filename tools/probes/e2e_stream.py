@@ -62,8 +62,7 @@ def one():
 def main():
     if "--one" in sys.argv:
         return one()
-    configs = [dict(FF_TRACE_STREAM="0"), dict(FF_TRACE_STREAM="1")] + [dict(FF_TRACE_STREAM="1", FF_STREAM_DONE_SHIFT=str(s)) for s in (18, 17, 16)] + [
-        dict(FF_TRACE_STREAM="1", FF_STREAM_PRELOAD="1")]
+    configs = [dict(FF_TRACE_STREAM="0"), dict(FF_TRACE_STREAM="1"), dict(FF_TRACE_STREAM="1"), dict(FF_TRACE_STREAM="1", FF_STREAM_PRELOAD="1")]
     for cfg in configs:
         env = dict(os.environ)
         env.update(cfg)

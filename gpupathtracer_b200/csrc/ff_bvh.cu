@@ -1171,7 +1171,11 @@ struct GridBarrier { uint32_t arrived; uint32_t generation; };
 #ifndef FF_COLLAPSE_TILE_LEVEL
 #define FF_COLLAPSE_TILE_LEVEL 16384u   // levels of at most this many wide nodes are collapsed by 8-lane tiles, larger ones by one thread per node
 #endif
-__global__ void __launch_bounds__(128) collapse_persistent_kernel(uint32_t* __restrict__ node_src, uint32_t node_capacity, int n,
+#ifndef FF_COLLAPSE_MINB
+#define FF_COLLAPSE_MINB 6   // resident CTAs per SM the collapse is compiled for: 85-register cap (uncapped: 94 registers, 5 CTAs).  20 M triangles:
+                             // 6.00 / 5.80 / 5.95 ms with no cap / 6 / 8; 1 M unchanged (profiles/r04h_build_variants_minb.txt)
+#endif
+__global__ void __launch_bounds__(128, FF_COLLAPSE_MINB) collapse_persistent_kernel(uint32_t* __restrict__ node_src, uint32_t node_capacity, int n,
                                 const int2* __restrict__ children, const float4* __restrict__ box_lo, const float4* __restrict__ box_hi,
                                 const float4* __restrict__ flat_tris, const uint32_t* __restrict__ sorted_idx,
                                 float4* __restrict__ nodes, float4* __restrict__ tris_out, uint32_t* __restrict__ leaf_slot,

@@ -14,7 +14,7 @@ N = 1  -- workload = BASELINE.json configs[3] (C4, the configuration the north-s
           own source), the diffuse-bounce batch B, BVH build times, and secondary blocks for the other configs --
           c2 (configs[1], the frame round 1 reported), c3 (configs[2], wavefront vs megakernel) and c5 at one GPU (the
           base of the strong-scaling series below), c2 / c3 each with an oracle crop check of the benchmarked frame.
-N > 1  -- (torchrun, one rank per GPU) workload = BASELINE.json configs[4] (C5): 20M-triangle soup, 7680x4320, a FIXED
+N > 1  -- (torchrun, one rank per GPU) workload = BASELINE.json configs[4] (C5): 20M-triangle soup (binned-SAH tree), 7680x4320, a FIXED
           total of 64 spp split over the ranks as disjoint sample ranges (strong scaling), the 531 MB accumulators
           combined by ONE framebuffer reduce per frame inside the library (ff_group_render: NCCL reduce, or the fused
           reduce-scatter + resolve kernel over NVLink peer memory with --reduce peer).  `value` = closest-hit rays of all
@@ -289,7 +289,11 @@ def frame_block(ff, S, ctx, meshes, name, desc, dims, tile, steps, skip_cpu, int
     return out
 
 
-def c5_scene(ff, S, ctx, n_tris, builder=0):
+C5_BUILDER = 1   # binned SAH: 31 ms instead of 5.9 ms of (replicated, untimed) build for a frame that renders 3 % faster (profiles/r04i_c5_builders.jsonl)
+BUILDER_NAMES = {0: "lbvh", 1: "binned-sah"}
+
+
+def c5_scene(ff, S, ctx, n_tris, builder=C5_BUILDER):
     soup = ctx.make_soup(n_tris)
     desc = S.config5(soup, C5_W, C5_H, C5_SPP, C5_BOUNCES)
     sc, cam = S.instantiate(desc, ctx, builder=builder)
@@ -458,6 +462,9 @@ def run_gpu_one(args):
         try:
             import gpupathtracer_b200.multigpu as M
             sc5, cam5 = c5_scene(ff, S, ctx, C5_TRIS)
+            sc5.commit(0)                      # the fast builder on the same scene, for the record
+            lbvh5 = sc5.info()["build_ms"]
+            sc5.commit(C5_BUILDER)
             i5 = sc5.info()
             grp = M.Group.single(ctx)
             grp.render(sc5, cam5, 2, C5_BOUNCES, to_host=False)
@@ -469,8 +476,8 @@ def run_gpu_one(args):
                 _, st = grp.render(sc5, cam5, C5_SPP, C5_BOUNCES, to_host=False)
                 secs5 += 1e-3 * ctx.timer_end()
                 rays5 += st["rays"]
-            line["c5"] = dict(n_gpus=1, triangles=i5["n_triangles"], bvh_nodes=i5["n_nodes"], builder="lbvh", build_ms=i5["build_ms"], image=[C5_W, C5_H],
-                              total_spp=C5_SPP, max_bounces=C5_BOUNCES, frame_ms=1e3 * secs5 / reps5, mrays_s=rays5 / secs5 / 1e6,
+            line["c5"] = dict(n_gpus=1, triangles=i5["n_triangles"], bvh_nodes=i5["n_nodes"], builder=BUILDER_NAMES[C5_BUILDER], build_ms=i5["build_ms"], lbvh_build_ms=lbvh5,
+                              image=[C5_W, C5_H], total_spp=C5_SPP, max_bounces=C5_BOUNCES, frame_ms=1e3 * secs5 / reps5, mrays_s=rays5 / secs5 / 1e6,
                               msamples_s=C5_SPP * C5_W * C5_H * reps5 / secs5 / 1e6,
                               note="one-GPU base of the strong-scaling series that bench.py --gpus N reports as `value`")
             log("c5:", json.dumps(line["c5"]))
@@ -577,7 +584,7 @@ def run_gpu_multi(args):
         value = rays / secs / 1e6
         line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=max(3, args.warmup), ms_per_step=1e3 * secs / steps,
                     higher_is_better=True, scaling="strong", vs_baseline=None, dtype="f32", data="synthetic", config=bench_config(world),
-                    bvh=dict(builder="lbvh", build_ms=info["build_ms"], nodes=info["n_nodes"], replicated=True),
+                    bvh=dict(builder=BUILDER_NAMES[C5_BUILDER], build_ms=info["build_ms"], nodes=info["n_nodes"], replicated=True),
                     parallelism="sample-split x%d behind the C ABI (ff_group_render), 1 framebuffer reduce per frame (%s)" % (world, args.reduce),
                     samples_per_sec=C5_SPP * npix * steps / secs, samples_per_sec_per_gpu=C5_SPP * npix * steps / secs / world,
                     rays_per_step=rays / steps, render_ms_per_step=render_ms / steps, reduce_ms=reduce_ms / steps, reduce_bytes_per_rank=npix * 16,

@@ -81,7 +81,7 @@ struct StoreLite {
 // the rays it finished and reports them to the chunk's counter when it moves on to another chunk, and the warp that completes
 // a chunk raises its flag in page-locked host memory, on which the host queues the chunk's device-to-host copies.  Nothing here can wait for ever: a lane gives up after kStreamTimeoutNs, sets `err`,
 // and every later wait returns at once (the host then redoes the batch through the chunked pipeline).
-static constexpr unsigned long long kStreamTimeoutNs = 1000000000ull;
+static constexpr unsigned long long kStreamTimeoutNs = 250000000ull;   // 0.25 s: rays are normally a few ms away at most; a spurious time-out only costs the fallback
 // Acquires are rationed: on this machine an acquire (ld.acquire, fence.acq_rel) invalidates the SM's whole L1 (CCTL.IVALL).  The
 // first version of this path did one per lane and chunk for `avail` and one fence per refill for the results, and traced the C4
 // batch in 6.7 ms against 5.4 ms device-resident: the node / triangle hit rate went with the L1.  Now ONE lane per warp acquires

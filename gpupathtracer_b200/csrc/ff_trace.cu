@@ -226,8 +226,14 @@ __global__ void __launch_bounds__(FF_TRACE_BLOCK) trace_closest_kernel(DevScene 
 // Warps pull rays from a global counter; when fewer than FF_REFILL_LANES lanes of a warp are still traversing, the
 // idle lanes fetch new rays instead of waiting for the slowest one (Aila & Laine 2009).  Results do not depend on
 // the schedule (the accept rule is order independent).
-template <bool SKIP, class Fetch, class Store>
-__global__ void __launch_bounds__(FF_TRACE_BLOCK, FF_TRACE_MINB) trace_closest_persistent_kernel(DevScene sc, Fetch fetch, Store store,
+// MINB = resident CTAs per SM the instantiation is compiled for: FF_TRACE_MINB (7: 72 registers) for scenes that live in L2,
+// FF_TRACE_MINB_BIG (8: 64 registers) for scenes far larger than L2, where four more warps per SM hide DRAM latency: the 20 M-triangle
+// C5 frame renders 3 % faster with 8 (326.0 -> 315.5 ms at 8 spp), the 1 M-triangle soup does not care, C3 loses 2.5 %
+// (profiles/r04n_c5_minb.txt, r02c_variants.txt).
+#define FF_TRACE_MINB_BIG 8
+#define FF_TRACE_BIG_SCENE (1u << 21)   // triangles: ~130 MB of nodes + triangles, more than the 126 MB L2
+template <bool SKIP, class Fetch, class Store, int MINB = FF_TRACE_MINB>
+__global__ void __launch_bounds__(FF_TRACE_BLOCK, MINB) trace_closest_persistent_kernel(DevScene sc, Fetch fetch, Store store,
                                                                                    const uint32_t* __restrict__ count_ptr, uint32_t n_max,
                                                                                    uint32_t* work_counter) {
     __shared__ uint2 sm_stack[(FF_SM_STACK + FF_TRI_QUEUE) * FF_TRACE_BLOCK];
@@ -372,8 +378,13 @@ static void launch_closest(const DevScene& sc, const Fetch& fetch, const Store& 
         // persistent: enough warps to fill the machine, each pulling rays until the batch is drained.
         // *d_work_counter must be zero (the caller clears it on the same stream).
         const int g = grid_for(n_max, FF_TRACE_BLOCK, sm_count() * tuning().blocks_per_sm);
-        if (skip) trace_closest_persistent_kernel<true><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, fetch, store, d_count, n_max, d_work_counter);
-        else trace_closest_persistent_kernel<false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, fetch, store, d_count, n_max, d_work_counter);
+        if (sc.n_tris > FF_TRACE_BIG_SCENE) {
+            if (skip) trace_closest_persistent_kernel<true, Fetch, Store, FF_TRACE_MINB_BIG><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, fetch, store, d_count, n_max, d_work_counter);
+            else trace_closest_persistent_kernel<false, Fetch, Store, FF_TRACE_MINB_BIG><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, fetch, store, d_count, n_max, d_work_counter);
+        } else {
+            if (skip) trace_closest_persistent_kernel<true><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, fetch, store, d_count, n_max, d_work_counter);
+            else trace_closest_persistent_kernel<false><<<g, FF_TRACE_BLOCK, 0, st>>>(sc, fetch, store, d_count, n_max, d_work_counter);
+        }
         return;
     }
     const int g = grid_for(n_max, FF_TRACE_BLOCK, sm_count() * 64);

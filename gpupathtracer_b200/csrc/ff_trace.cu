@@ -31,11 +31,19 @@ static inline int grid_for(size_t n, int block, int max_blocks) {
     return (int)g;
 }
 
+#ifndef FF_STREAM_HINT
+#define FF_STREAM_HINT 1   // rays are read and hits written with the cache-streaming (evict-first) hint, so that they do not push the scene out of L2:
+                           // C4 batch A 1526 -> 1540 Mrays/s, everything else unchanged (profiles/r04q_variants_hint.txt)
+#endif
 __device__ __forceinline__ void store_hit(HitRec* hits, size_t i, const Best& b) {
     int4 v;
     if (b.slot < 0) { v.x = __float_as_int(INFINITY); v.y = 0; v.z = -1; v.w = -1; }
     else { v.x = __float_as_int(b.key); v.y = __float_as_int(b.t); v.z = b.slot; v.w = b.ord; }
+#if FF_STREAM_HINT
+    __stcs(reinterpret_cast<int4*>(hits) + i, v);
+#else
     reinterpret_cast<int4*>(hits)[i] = v;
+#endif
 }
 
 // Where a closest-hit kernel takes its rays from and what it leaves behind.  The API entry points read ray arrays and write
@@ -49,8 +57,13 @@ struct FetchArrays {
     const float4* __restrict__ ray_o;
     const float4* __restrict__ ray_d;
     __device__ __forceinline__ void operator()(uint32_t i, V3& o, V3& draw, uint32_t& skipbits) const {
+#if FF_STREAM_HINT
+        const float4 d4 = __ldcs(ray_d + i);
+        o = ld3(__ldcs(ray_o + i)); draw = ld3(d4); skipbits = __float_as_uint(d4.w);
+#else
         const float4 d4 = __ldg(ray_d + i);
         o = ld3(__ldg(ray_o + i)); draw = ld3(d4); skipbits = __float_as_uint(d4.w);
+#endif
     }
 };
 struct FetchPrimary {   // bounce 0 of the wavefront: origin = the camera position, direction from the ray-generation kernel, no self-skip

@@ -71,7 +71,11 @@ struct FetchPrimary {   // bounce 0 of the wavefront: origin = the camera positi
     const float4* __restrict__ ray_d;
     float ox, oy, oz;
     __device__ __forceinline__ void operator()(uint32_t i, V3& o, V3& draw, uint32_t& skipbits) const {
+#if FF_STREAM_HINT
+        o = ffm::v3(ox, oy, oz); draw = ld3(__ldcs(ray_d + i)); skipbits = 0u;
+#else
         o = ffm::v3(ox, oy, oz); draw = ld3(__ldg(ray_d + i)); skipbits = 0u;
+#endif
     }
 };
 struct StoreRec {
@@ -83,7 +87,11 @@ struct StoreLite {
     static constexpr bool kCompletion = false;
     HitLite* __restrict__ hits;
     __device__ __forceinline__ void operator()(size_t i, const Best& b) const {
+#if FF_STREAM_HINT
+        __stcs(reinterpret_cast<int2*>(hits) + i, b.slot < 0 ? make_int2(0, -1) : make_int2(__float_as_int(b.t), b.slot));
+#else
         reinterpret_cast<int2*>(hits)[i] = b.slot < 0 ? make_int2(0, -1) : make_int2(__float_as_int(b.t), b.slot);
+#endif
     }
 };
 
